@@ -1,0 +1,276 @@
+/*
+ * zenith_b200.h — C ABI of the B200-native backend for Zenith's path-tracing hot path.
+ *
+ * The reference (jarek1992/raytracer_project) has no FFI layer; its seam is the C++ member
+ *   void camera::render(const hittable& world, const EnvironmentSettings& env,
+ *                       const post_processor& post, std::atomic<bool>& render_flag)   camera.hpp:236
+ * whose hot body is camera::execute_render_threads (camera.hpp:404-579).  Every entry point below
+ * cites the piece of that interface it replaces.  Plain pointers and sizes only; no C++ or torch
+ * types cross this boundary.  All functions return ZB_OK (0) or a negative zb_status; the message
+ * for the last failure on the calling thread is available from zb_last_error().
+ *
+ * There is no CPU fallback behind this ABI: every compute entry point fails with ZB_ERR_CUDA when
+ * no sm_100 device is usable.
+ */
+#ifndef ZENITH_B200_H
+#define ZENITH_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define ZB_ABI_VERSION 1
+
+typedef enum zb_status {
+    ZB_OK = 0,
+    ZB_ERR_INVALID = -1,   /* bad argument / malformed flat scene                     */
+    ZB_ERR_CUDA = -2,      /* CUDA runtime failure or no usable device                */
+    ZB_ERR_IO = -3,        /* scene / asset file could not be read                    */
+    ZB_ERR_CANCELLED = -4, /* cancel flag observed; outputs hold the finished batches */
+    ZB_ERR_UNSUPPORTED = -5
+} zb_status;
+
+/* ------------------------------------------------------------------------------------------
+ * Flat scene: structure-of-arrays, POD, produced once by the C++20 host flattener
+ * (raytracer_project_b200/host/flatten.hpp) from the reference-shaped scene graph
+ * (hittable_list / bvh_node / sphere / triangle / cube / translate / rotate_* / scale /
+ * material_instance / constant_medium / model; hittable.hpp:29-36 and Appendix C of SURVEY.md).
+ * ---------------------------------------------------------------------------------------- */
+
+/* BVH2 node, 64 B, 32-byte aligned: the boxes of BOTH children live in the parent so one node
+ * fetch (4 x LDG.128) decides both slab tests.  Replaces bvh_node {left,right,bbox} bvh.hpp:119-122.
+ * child >= 0 : absolute index of an inner node in nodes[]
+ * child <  0 : leaf, code = ~child, first = code >> 3, count = (code & 7) + 1 (items or triangles)
+ * child == ZB_CHILD_EMPTY : no child (box is inverted and never hit). */
+typedef struct zb_bvh_node {
+    float lx_ly[4]; /* left.lo.x, left.hi.x, left.lo.y, left.hi.y   */
+    float rx_ry[4]; /* right.lo.x, right.hi.x, right.lo.y, right.hi.y */
+    float lz_rz[4]; /* left.lo.z, left.hi.z, right.lo.z, right.hi.z */
+    int32_t left, right;
+    uint32_t pad0, pad1;
+} zb_bvh_node;
+#define ZB_CHILD_EMPTY ((int32_t)0x80000000)
+
+/* Top-level leaf item, 32 B.  One per leaf object of the world (DFS order of the scene graph
+ * gives `leaf_id`; items are stored in BVH leaf order).  Spheres that sit directly in the world
+ * (no non-trivial wrapper) are inlined so a test costs one 32-byte load (sphere.hpp:18-64). */
+enum {
+    ZB_ITEM_SPHERE = 0,   /* geom = centre.xyz, radius; world space                        */
+    ZB_ITEM_CUBE = 1,     /* aux = index into cubes[]; world space (cube.hpp:44-86)        */
+    ZB_ITEM_TRIANGLE = 2, /* aux = index into tris[] (a loose triangle in the world)       */
+    ZB_ITEM_INSTANCE = 3, /* aux = index into instances[]                                  */
+    ZB_ITEM_MEDIUM = 4    /* aux = index into media[] (constant_medium.hpp:39-77)          */
+};
+#define ZB_FLAG_FORCE_FRONT 0x100u /* translate / rotate_y above the primitive: front_face forced
+                                      to true (translate.hpp:29, rotate_y.hpp:70, SURVEY A.q1) */
+typedef struct zb_item {
+    float geom[4];
+    uint32_t kind_flags; /* low 8 bits kind, then ZB_FLAG_*                                 */
+    uint32_t material;   /* index into materials[]                                          */
+    uint32_t leaf_id;    /* DFS index of the leaf object in the scene graph                 */
+    uint32_t aux;
+} zb_item;
+
+/* Origin-slab cube (cube.hpp:44-86): slabs are +-half about the WORLD origin of the local frame,
+ * face classification uses p - centre (cube.hpp:75, :100-142).  32 B. */
+typedef struct zb_cube {
+    float half[4];   /* half extents, w unused */
+    float centre[4]; /* cube::center, w unused */
+} zb_cube;
+
+/* Triangle, 48 B for the test + 48 B normals fetched only at the accepted hit (triangle.hpp:17-82).
+ * v0.w carries the face id (bit pattern of a uint32). */
+typedef struct zb_tri {
+    float v0[4], v1[4], v2[4];
+} zb_tri;
+typedef struct zb_tri_normals {
+    float n0[4], n1[4], n2[4];
+} zb_tri_normals;
+
+/* Instance = collapsed wrapper chain translate/rotate_x/rotate_y/rotate_z/scale (+ material_instance)
+ * over one shared geometry (translate.hpp:15-32, rotate_*.hpp, scale.hpp:20-36).  128 B.
+ * Ray directions are never renormalised, so t is invariant under the transform (SURVEY A.q7). */
+enum { ZB_GEOM_SPHERE = 0, ZB_GEOM_CUBE = 1, ZB_GEOM_MESH = 2, ZB_GEOM_TRIANGLE = 3 };
+typedef struct zb_instance {
+    float w2o[12]; /* world -> object, row-major 3x4 */
+    float o2w[12]; /* object -> world, row-major 3x4 */
+    uint32_t geom_kind;
+    uint32_t geom_index; /* spheres_obj[] / cubes[] / meshes[] / tris[] */
+    uint32_t flags;      /* ZB_FLAG_FORCE_FRONT */
+    uint32_t pad[5];
+} zb_instance;
+
+typedef struct zb_mesh {
+    uint32_t node_root; /* first node of this mesh's BLAS inside nodes[]        */
+    uint32_t node_count;
+    uint32_t tri_first; /* first triangle of this mesh inside tris[] (BLAS leaf order) */
+    uint32_t tri_count;
+} zb_mesh;
+
+/* constant_medium (constant_medium.hpp:27-77): boundary is a sphere or cube, optionally under an
+ * instance transform.  One free-flight draw per (ray, medium) (SURVEY A.q6). */
+typedef struct zb_medium {
+    uint32_t boundary_kind;  /* ZB_ITEM_SPHERE (geom in sphere[]), ZB_ITEM_CUBE, ZB_ITEM_INSTANCE */
+    uint32_t boundary_index; /* cubes[] / instances[] index; unused for an inline sphere          */
+    float neg_inv_density;
+    uint32_t pad;
+    float sphere[4];         /* inline boundary sphere                                            */
+} zb_medium;
+
+enum { ZB_MAT_LAMBERTIAN = 0, ZB_MAT_METAL = 1, ZB_MAT_DIELECTRIC = 2, ZB_MAT_LIGHT = 3, ZB_MAT_ISOTROPIC = 4 };
+#define ZB_NO_TEXTURE 0xFFFFFFFFu
+/* Tagged-union material replacing shared_ptr<material> virtual dispatch (material.hpp:7-279,
+ * constant_medium.hpp:9-22).  32 B. */
+typedef struct zb_material {
+    uint32_t type;
+    uint32_t albedo_tex; /* ZB_NO_TEXTURE: use the inline colour (solid_color fast path)          */
+    uint32_t bump_tex;   /* ZB_NO_TEXTURE: none (material.hpp:35-54)                              */
+    float bump_strength;
+    float rgb[3];        /* albedo / tint / emission when albedo_tex == ZB_NO_TEXTURE             */
+    float param;         /* metal: fuzz (clamped <=1, material.hpp:116); dielectric: ior          */
+} zb_material;
+
+enum { ZB_TEX_SOLID = 0, ZB_TEX_CHECKER = 1, ZB_TEX_IMAGE_U8 = 2, ZB_TEX_IMAGE_F32 = 3, ZB_TEX_MISSING = 4 };
+/* texture.hpp:12-133.  32 B.  Images: a = width, b = height, c = first texel (uchar4 / float4 units)
+ * in texels_u8 / texels_f32.  Checker: f[0] = 1/scale, a = odd texture, b = even texture. */
+typedef struct zb_texture {
+    uint32_t kind, a, b, c;
+    float f[4];
+} zb_texture;
+
+typedef struct zb_flat_scene {
+    uint32_t abi_version; /* ZB_ABI_VERSION */
+    uint32_t n_nodes;     /* TLAS nodes come first (root = node 0); mesh BLASes follow */
+    uint32_t n_tlas_nodes;
+    uint32_t n_items, n_cubes, n_tris, n_instances, n_meshes, n_media, n_materials, n_textures;
+    uint32_t n_spheres_obj; /* object-space spheres referenced by instances                  */
+    uint64_t n_texels_u8;   /* uchar4 units                                                  */
+    uint64_t n_texels_f32;  /* float4 units                                                  */
+    const zb_bvh_node* nodes;
+    const zb_item* items;
+    const zb_cube* cubes;
+    const zb_tri* tris;
+    const zb_tri_normals* tri_normals;
+    const zb_instance* instances;
+    const zb_mesh* meshes;
+    const zb_medium* media;
+    const zb_material* materials;
+    const zb_texture* textures;
+    const float* spheres_obj;  /* 4 floats each */
+    const uint8_t* texels_u8;  /* RGBA8 */
+    const float* texels_f32;   /* RGBA32F */
+    uint32_t n_leaves;         /* number of leaf ids handed out */
+    uint32_t pad;
+} zb_flat_scene;
+
+/* The 13 public camera parameters (camera.hpp:26-42); derived quantities are computed in double by
+ * the library exactly as camera::initialize does (camera.hpp:358-402). */
+typedef struct zb_camera {
+    int32_t image_width, image_height;
+    double vfov;
+    double lookfrom[3], lookat[3], vup[3];
+    double defocus_angle, focus_dist;
+} zb_camera;
+
+/* EnvironmentSettings (environment.hpp:8-77) as consumed by camera::get_background_color
+ * (camera.hpp:828-925). */
+enum { ZB_ENV_PHYSICAL_SUN = 0, ZB_ENV_HDR_MAP = 1, ZB_ENV_SOLID_COLOR = 2 };
+typedef struct zb_environment {
+    int32_t mode;
+    uint32_t hdr_texture; /* index into the scene's textures[] or ZB_NO_TEXTURE */
+    double background_color[3];
+    double intensity;
+    double hdri_rotation, hdri_tilt, hdri_roll;
+    double sun_direction[3], sun_color[3];
+    double sun_intensity, sun_size;
+} zb_environment;
+
+enum { ZB_PARTITION_SAMPLES = 0, ZB_PARTITION_TILES = 1 };
+/* camera.hpp:28-31, :53-57 and post_processor::z_depth_max_dist (camera.hpp:247). */
+typedef struct zb_render_opts {
+    int32_t samples_per_pixel;
+    int32_t max_depth;
+    uint64_t seed;
+    /* this rank's share of the frame (multi-GPU) */
+    int32_t sample_begin, sample_end; /* [begin,end) of the global sample index; 0,spp = all  */
+    int32_t tile_rank, tile_ranks;    /* tile stripes: this rank owns tiles t % ranks == rank  */
+    int32_t use_albedo, use_normal, use_z_depth;
+    double z_depth_max_dist;
+    int32_t collect_stats;            /* 1: STATS kernel variant (node visits / primitive tests) */
+    int32_t samples_per_launch;       /* 0 = library default; cancel is polled between launches   */
+} zb_render_opts;
+
+/* Host-side outputs in the reference's own layout: row-major, top row first, 3 doubles per pixel
+ * (std::vector<color>, camera.hpp:63,80-85).  Any pointer may be NULL. */
+typedef struct zb_outputs {
+    double* beauty;  /* render_accumulator */
+    double* albedo;  /* albedo_buffer      */
+    double* normal;  /* normal_buffer      */
+    double* z_depth; /* z_depth_buffer     */
+    float* beauty_f4; /* optional: RGBA32F mean radiance, 4 floats per pixel */
+} zb_outputs;
+
+typedef struct zb_stats {
+    uint64_t paths, rays, node_visits, box_tests, prim_tests, instance_visits;
+    double kernel_ms;  /* device time of the path-tracing launches of the last render   */
+    double resolve_ms; /* device time of the resolve kernel                             */
+    double h2d_ms, d2h_ms;
+    uint32_t launches; /* kernels launched by the last render                           */
+    uint32_t pad;
+} zb_stats;
+
+typedef struct zb_context zb_context;
+typedef struct zb_scene zb_scene;
+typedef void (*zb_progress_fn)(int lines_rendered, void* user); /* camera::lines_rendered camera.hpp:88 */
+
+int zb_abi_version(void);
+const char* zb_last_error(void);
+
+/* one context per process/GPU; `stream` is a cudaStream_t (or NULL for the default stream) */
+int zb_context_create(int device, zb_context** out);
+int zb_context_set_stream(zb_context* ctx, void* stream);
+int zb_context_destroy(zb_context* ctx);
+int zb_device_info(zb_context* ctx, int* sm_count, int* cc_major, int* cc_minor, size_t* l2_bytes);
+
+/* copies the flat scene to the GPU; the caller keeps ownership of the host arrays */
+int zb_scene_upload(zb_context* ctx, const zb_flat_scene* flat, zb_scene** out);
+int zb_scene_destroy(zb_scene* scene);
+
+/* Drop-in for camera::render's hot part (camera.hpp:236-250 -> :404-579): blocking; fills host
+ * buffers.  `cancel` mirrors render_flag inverted (non-zero = stop, camera.hpp:441). */
+int zb_render(zb_context* ctx, const zb_scene* scene, const zb_camera* cam, const zb_environment* env,
+              const zb_render_opts* opts, zb_outputs* out, const volatile int* cancel,
+              zb_progress_fn progress, void* user);
+
+/* Device-resident variant used for multi-GPU and kernel-only timing: accumulates radiance SUMS of
+ * this rank's share into `accum_f4` (W*H float4 on the device, overwritten) on the context stream
+ * without synchronising; aux sums (albedo, normal, z) go to accum_aux_f4 (3*W*H float4) if non-NULL. */
+int zb_render_device(zb_context* ctx, const zb_scene* scene, const zb_camera* cam,
+                     const zb_environment* env, const zb_render_opts* opts, void* accum_f4,
+                     void* accum_aux_f4);
+/* K5 resolve: out_f4[i] = accum_f4[i] * scale (device -> device), or to the reference's double RGB */
+int zb_resolve_device(zb_context* ctx, const void* accum_f4, size_t n_pixels, double scale, void* out_f4,
+                      void* out_rgb_f64);
+
+/* K7 parity artefact: centre-of-pixel pinhole primary hit (camera::get_center_ray camera.hpp:809-814
+ * + world.hit with interval(0.001, inf) camera.hpp:459).  leaf_id = 0xFFFFFFFF on a miss;
+ * prim_id = face index inside a mesh, else 0.  Host pointers, W*H entries each; any may be NULL. */
+int zb_primary_ids(zb_context* ctx, const zb_scene* scene, const zb_camera* cam, uint32_t* leaf_id,
+                   uint32_t* prim_id, float* t);
+
+int zb_get_stats(zb_context* ctx, zb_stats* out);
+
+/* Host side of the boundary (C++20 scene API + flattener behind a C handle): parse a neutral scene
+ * description ("zscene" text, raytracer_project_b200/host/zscene.hpp) through the reference-shaped
+ * scene API and flatten it.  The returned zb_flat_scene stays valid until zb_flat_scene_free. */
+int zb_flat_scene_from_zscene(const char* path, const zb_flat_scene** out);
+int zb_flat_scene_from_zscene_text(const char* text, size_t len, const zb_flat_scene** out);
+int zb_flat_scene_free(const zb_flat_scene* flat);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* ZENITH_B200_H */
