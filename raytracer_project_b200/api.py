@@ -1,0 +1,153 @@
+"""Thin Python driver over the C ABI, used by tests/ and bench.py.
+
+Mirrors the reference's call sequence (main.cpp:1500-1521): build scene -> (flatten + upload) ->
+camera parameters -> render -> six row-major double-RGB buffers (camera.hpp:63,80-85).
+All compute happens in libzenith_b200.so on the GPU; nothing here falls back to the CPU.
+"""
+from __future__ import annotations
+
+import ctypes as C
+
+import numpy as np
+
+from . import _lib
+from ._lib import Camera, Environment, FlatScene, Outputs, RenderOpts, Stats, check
+from .scenes import RenderConfig
+
+
+def flatten_zscene(text: str | None = None, path: str | None = None):
+    """zscene text/file -> host scene API -> flatten(); returns a ctypes pointer to zb_flat_scene."""
+    lib = _lib.load()
+    out = C.POINTER(FlatScene)()
+    if path is not None:
+        check(lib.zb_flat_scene_from_zscene(path.encode(), C.byref(out)))
+    else:
+        data = text.encode()
+        check(lib.zb_flat_scene_from_zscene_text(data, len(data), C.byref(out)))
+    return out
+
+
+def free_flat(flat):
+    _lib.load().zb_flat_scene_free(flat)
+
+
+def camera_struct(cfg: RenderConfig) -> Camera:
+    cam = Camera()
+    cam.image_width, cam.image_height = cfg.image_width, cfg.image_height
+    cam.vfov = cfg.vfov
+    cam.lookfrom[:] = cfg.lookfrom
+    cam.lookat[:] = cfg.lookat
+    cam.vup[:] = cfg.vup
+    cam.defocus_angle, cam.focus_dist = cfg.defocus_angle, cfg.focus_dist
+    return cam
+
+
+def env_struct(cfg: RenderConfig) -> Environment:
+    env = Environment()
+    env.mode = _lib.ENV_MODES[cfg.env_mode]
+    env.hdr_texture = _lib.ZB_NO_TEXTURE
+    env.background_color[:] = cfg.background
+    env.intensity = cfg.env_intensity
+    env.hdri_rotation, env.hdri_tilt, env.hdri_roll = cfg.hdri_rotation, cfg.hdri_tilt, cfg.hdri_roll
+    env.sun_direction[:] = cfg.sun_direction
+    env.sun_color[:] = cfg.sun_color
+    env.sun_intensity, env.sun_size = cfg.sun_intensity, cfg.sun_size
+    return env
+
+
+def opts_struct(cfg: RenderConfig, seed=1, sample_range=None, tile=None, stats=False, samples_per_launch=0) -> RenderOpts:
+    o = RenderOpts()
+    o.samples_per_pixel, o.max_depth, o.seed = cfg.samples_per_pixel, cfg.max_depth, seed
+    o.sample_begin, o.sample_end = sample_range if sample_range else (0, cfg.samples_per_pixel)
+    o.tile_rank, o.tile_ranks = tile if tile else (0, 1)
+    o.use_albedo, o.use_normal, o.use_z_depth = int(cfg.use_albedo), int(cfg.use_normal), int(cfg.use_z_depth)
+    o.z_depth_max_dist = cfg.z_depth_max_dist
+    o.collect_stats = int(stats)
+    o.samples_per_launch = samples_per_launch
+    return o
+
+
+class Context:
+    def __init__(self, device: int = 0, stream: int | None = None):
+        self.lib = _lib.load()
+        self.h = C.c_void_p()
+        check(self.lib.zb_context_create(device, C.byref(self.h)))
+        if stream is not None:
+            check(self.lib.zb_context_set_stream(self.h, C.c_void_p(stream)))
+
+    def close(self):
+        if self.h:
+            self.lib.zb_context_destroy(self.h)
+            self.h = C.c_void_p()
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        self.close()
+
+    def device_info(self):
+        sm, ma, mi, l2 = C.c_int(), C.c_int(), C.c_int(), C.c_size_t()
+        check(self.lib.zb_device_info(self.h, C.byref(sm), C.byref(ma), C.byref(mi), C.byref(l2)))
+        return {"sm_count": sm.value, "cc": (ma.value, mi.value), "l2_bytes": l2.value}
+
+    def upload(self, flat) -> "Scene":
+        s = C.c_void_p()
+        check(self.lib.zb_scene_upload(self.h, flat, C.byref(s)))
+        return Scene(self, s)
+
+    def stats(self) -> dict:
+        st = Stats()
+        check(self.lib.zb_get_stats(self.h, C.byref(st)))
+        return {k: getattr(st, k) for k, _ in Stats._fields_ if k != "pad"}
+
+
+class Scene:
+    def __init__(self, ctx: Context, handle):
+        self.ctx, self.h = ctx, handle
+
+    def close(self):
+        if self.h:
+            self.ctx.lib.zb_scene_destroy(self.h)
+            self.h = C.c_void_p()
+
+    def render(self, cfg: RenderConfig, seed=1, stats=False, want_f4=False, sample_range=None, tile=None,
+               samples_per_launch=0, progress=None, cancel=None):
+        """zb_render: returns dict of (H, W, 3) float64 arrays like the reference's buffers."""
+        n = cfg.image_width * cfg.image_height
+        cam, env = camera_struct(cfg), env_struct(cfg)
+        o = opts_struct(cfg, seed, sample_range, tile, stats, samples_per_launch)
+        out = Outputs()
+        res = {"beauty": np.empty((cfg.image_height, cfg.image_width, 3), np.float64)}
+        out.beauty = res["beauty"].ctypes.data
+        for key, flag in (("albedo", cfg.use_albedo), ("normal", cfg.use_normal), ("z_depth", cfg.use_z_depth)):
+            if flag:
+                res[key] = np.empty((cfg.image_height, cfg.image_width, 3), np.float64)
+                setattr(out, key, res[key].ctypes.data)
+        if want_f4:
+            res["beauty_f4"] = np.empty((cfg.image_height, cfg.image_width, 4), np.float32)
+            out.beauty_f4 = res["beauty_f4"].ctypes.data
+        cb = _lib.PROGRESS_FN(progress) if progress else C.cast(None, _lib.PROGRESS_FN)
+        cancel_p = C.byref(cancel) if cancel is not None else None
+        check(self.ctx.lib.zb_render(self.ctx.h, self.h, C.byref(cam), C.byref(env), C.byref(o), C.byref(out), cancel_p,
+                                     cb, None))
+        assert n == res["beauty"].shape[0] * res["beauty"].shape[1]
+        return res
+
+    def render_device(self, cfg: RenderConfig, accum_ptr: int, aux_ptr: int = 0, seed=1, sample_range=None, tile=None,
+                      stats=False):
+        """zb_render_device: radiance SUMS of this rank's share into a device float4 buffer (async)."""
+        cam, env = camera_struct(cfg), env_struct(cfg)
+        o = opts_struct(cfg, seed, sample_range, tile, stats)
+        check(self.ctx.lib.zb_render_device(self.ctx.h, self.h, C.byref(cam), C.byref(env), C.byref(o),
+                                            C.c_void_p(accum_ptr), C.c_void_p(aux_ptr) if aux_ptr else None))
+
+    def primary_ids(self, cfg: RenderConfig):
+        n = cfg.image_width * cfg.image_height
+        leaf = np.empty(n, np.uint32)
+        prim = np.empty(n, np.uint32)
+        t = np.empty(n, np.float32)
+        cam = camera_struct(cfg)
+        check(self.ctx.lib.zb_primary_ids(self.ctx.h, self.h, C.byref(cam), leaf.ctypes.data, prim.ctypes.data, t.ctypes.data))
+        shape = (cfg.image_height, cfg.image_width)
+        return leaf.reshape(shape), prim.reshape(shape), t.reshape(shape)

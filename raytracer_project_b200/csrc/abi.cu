@@ -1,0 +1,189 @@
+// abi.cu — implementation of the C ABI declared in include/zenith_b200.h (device side).
+// Context = one GPU + one stream; scene = device copies of the flat SoA arrays; render = camera and
+// environment set-up in double exactly as camera::initialize (camera.hpp:358-402) followed by the
+// kernels of kernels.cu.  No CPU fallback: without a usable sm_100 device every entry point fails.
+#include "abi_internal.h"
+
+extern "C" int zb_abi_version(void) { return ZB_ABI_VERSION; }
+std::string& zb_err_slot() {
+    static thread_local std::string err;
+    return err;
+}
+extern "C" const char* zb_last_error(void) { return zb_err_slot().c_str(); }
+
+extern "C" int zb_context_create(int device, zb_context** out) {
+    if (!out) return fail(ZB_ERR_INVALID, "zb_context_create: out is NULL");
+    int n = 0;
+    cudaError_t e = cudaGetDeviceCount(&n);
+    if (e != cudaSuccess || n == 0)
+        return fail(ZB_ERR_CUDA, std::string("no CUDA device (this backend has no CPU fallback): ") + cudaGetErrorString(e));
+    if (device < 0 || device >= n) return fail(ZB_ERR_INVALID, "zb_context_create: device index out of range");
+    ZB_CUDA(cudaSetDevice(device));
+    cudaDeviceProp prop;
+    ZB_CUDA(cudaGetDeviceProperties(&prop, device));
+    if (prop.major < 10) return fail(ZB_ERR_CUDA, "device is not sm_100 class; kernels are built for sm_100a only");
+    zb_context* c = new zb_context();
+    c->device = device;
+    c->sm_count = prop.multiProcessorCount;
+    c->cc_major = prop.major;
+    c->cc_minor = prop.minor;
+    c->l2_bytes = size_t(prop.l2CacheSize);
+    ZB_CUDA(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
+    c->own_stream = true;
+    ZB_CUDA(cudaMalloc(&c->counters, 8 * sizeof(unsigned long long)));
+    for (auto& ev : c->ev) ZB_CUDA(cudaEventCreate(&ev));
+    *out = c;
+    return ZB_OK;
+}
+
+extern "C" int zb_context_set_stream(zb_context* ctx, void* stream) {
+    if (!ctx) return fail(ZB_ERR_INVALID, "ctx is NULL");
+    if (ctx->own_stream) {
+        cudaStreamSynchronize(ctx->stream);
+        cudaStreamDestroy(ctx->stream);
+        ctx->own_stream = false;
+    }
+    ctx->stream = static_cast<cudaStream_t>(stream);
+    return ZB_OK;
+}
+
+extern "C" int zb_context_destroy(zb_context* ctx) {
+    if (!ctx) return ZB_OK;
+    cudaSetDevice(ctx->device);
+    cudaStreamSynchronize(ctx->stream);
+    cudaFree(ctx->counters);
+    cudaFree(ctx->accum);
+    cudaFree(ctx->accum_aux);
+    cudaFree(ctx->out_f64);
+    cudaFree(ctx->out_f4);
+    cudaFree(ctx->id_scratch);
+    if (ctx->pinned) cudaFreeHost(ctx->pinned);
+    for (auto& ev : ctx->ev) cudaEventDestroy(ev);
+    if (ctx->own_stream) cudaStreamDestroy(ctx->stream);
+    delete ctx;
+    return ZB_OK;
+}
+
+extern "C" int zb_device_info(zb_context* ctx, int* sm_count, int* cc_major, int* cc_minor, size_t* l2_bytes) {
+    if (!ctx) return fail(ZB_ERR_INVALID, "ctx is NULL");
+    if (sm_count) *sm_count = ctx->sm_count;
+    if (cc_major) *cc_major = ctx->cc_major;
+    if (cc_minor) *cc_minor = ctx->cc_minor;
+    if (l2_bytes) *l2_bytes = ctx->l2_bytes;
+    return ZB_OK;
+}
+
+// ------------------------------------------------------------------------------------ scene
+
+template <class T>
+static int upload(zb_scene* s, const void* host, size_t count, size_t elem, const T** dev) {
+    *dev = nullptr;
+    if (count == 0) return ZB_OK;
+    if (!host) return fail(ZB_ERR_INVALID, "zb_scene_upload: array pointer is NULL but its count is not 0");
+    void* d = nullptr;
+    ZB_CUDA(cudaMalloc(&d, count * elem));
+    s->allocs.push_back(d);
+    ZB_CUDA(cudaMemcpyAsync(d, host, count * elem, cudaMemcpyHostToDevice, s->ctx->stream));
+    s->bytes += count * elem;
+    *dev = static_cast<const T*>(d);
+    return ZB_OK;
+}
+
+static int validate(const zb_flat_scene* f) {
+    if (f->abi_version != ZB_ABI_VERSION) return fail(ZB_ERR_INVALID, "flat scene: ABI version mismatch");
+    if (f->n_tlas_nodes > f->n_nodes) return fail(ZB_ERR_INVALID, "flat scene: n_tlas_nodes > n_nodes");
+    if (f->n_items && !f->n_nodes) return fail(ZB_ERR_INVALID, "flat scene: items without BVH nodes");
+    for (uint32_t i = 0; i < f->n_nodes; i++) {
+        const int32_t ch[2] = {f->nodes[i].left, f->nodes[i].right};
+        const bool tlas = i < f->n_tlas_nodes;
+        for (int32_t c : ch) {
+            if (c == ZB_CHILD_EMPTY) continue;
+            if (c >= 0) {
+                if (uint32_t(c) >= f->n_nodes) return fail(ZB_ERR_INVALID, "flat scene: node child index out of range");
+            } else {
+                uint32_t code = ~uint32_t(c), first = code >> 3, end = first + (code & 7u) + 1u;
+                if (end > (tlas ? f->n_items : f->n_tris)) return fail(ZB_ERR_INVALID, "flat scene: leaf range out of bounds");
+            }
+        }
+    }
+    for (uint32_t i = 0; i < f->n_items; i++) {
+        const zb_item& it = f->items[i];
+        uint32_t kind = it.kind_flags & 0xFFu;
+        if (it.material >= f->n_materials) return fail(ZB_ERR_INVALID, "flat scene: item material out of range");
+        uint32_t lim = kind == ZB_ITEM_SPHERE ? 0xFFFFFFFFu
+                       : kind == ZB_ITEM_CUBE ? f->n_cubes
+                       : kind == ZB_ITEM_TRIANGLE ? f->n_tris
+                       : kind == ZB_ITEM_INSTANCE ? f->n_instances
+                       : kind == ZB_ITEM_MEDIUM ? f->n_media : 0u;
+        if (lim == 0u || (kind != ZB_ITEM_SPHERE && it.aux >= lim)) return fail(ZB_ERR_INVALID, "flat scene: item reference out of range");
+    }
+    for (uint32_t i = 0; i < f->n_instances; i++) {
+        const zb_instance& in = f->instances[i];
+        uint32_t lim = in.geom_kind == ZB_GEOM_SPHERE ? f->n_spheres_obj
+                       : in.geom_kind == ZB_GEOM_CUBE ? f->n_cubes
+                       : in.geom_kind == ZB_GEOM_MESH ? f->n_meshes
+                       : in.geom_kind == ZB_GEOM_TRIANGLE ? f->n_tris : 0u;
+        if (in.geom_index >= lim) return fail(ZB_ERR_INVALID, "flat scene: instance geometry out of range");
+        if (in.geom_kind == ZB_GEOM_MESH && in.pad[0] != f->meshes[in.geom_index].node_root)
+            return fail(ZB_ERR_INVALID, "flat scene: instance BLAS root does not match its mesh");
+    }
+    for (uint32_t i = 0; i < f->n_materials; i++) {
+        const zb_material& m = f->materials[i];
+        if (m.type > ZB_MAT_ISOTROPIC) return fail(ZB_ERR_INVALID, "flat scene: unknown material type");
+        if ((m.albedo_tex != ZB_NO_TEXTURE && m.albedo_tex >= f->n_textures) ||
+            (m.bump_tex != ZB_NO_TEXTURE && m.bump_tex >= f->n_textures))
+            return fail(ZB_ERR_INVALID, "flat scene: material texture out of range");
+    }
+    for (uint32_t i = 0; i < f->n_textures; i++) {
+        const zb_texture& t = f->textures[i];
+        if (t.kind == ZB_TEX_CHECKER && (t.a >= f->n_textures || t.b >= f->n_textures))
+            return fail(ZB_ERR_INVALID, "flat scene: checker sub-texture out of range");
+        if (t.kind == ZB_TEX_IMAGE_U8 && uint64_t(t.c) + uint64_t(t.a) * t.b > f->n_texels_u8)
+            return fail(ZB_ERR_INVALID, "flat scene: u8 texture outside the texel pool");
+        if (t.kind == ZB_TEX_IMAGE_F32 && uint64_t(t.c) + uint64_t(t.a) * t.b > f->n_texels_f32)
+            return fail(ZB_ERR_INVALID, "flat scene: f32 texture outside the texel pool");
+    }
+    return ZB_OK;
+}
+
+extern "C" int zb_scene_upload(zb_context* ctx, const zb_flat_scene* f, zb_scene** out) {
+    if (!ctx || !f || !out) return fail(ZB_ERR_INVALID, "zb_scene_upload: NULL argument");
+    int rc = validate(f);
+    if (rc) return rc;
+    ZB_CUDA(cudaSetDevice(ctx->device));
+    zb_scene* s = new zb_scene();
+    s->ctx = ctx;
+    SceneDev& d = s->dev;
+    rc = upload(s, f->nodes, f->n_nodes, sizeof(zb_bvh_node), &d.nodes);
+    if (!rc) rc = upload(s, f->items, f->n_items, sizeof(zb_item), &d.items);
+    if (!rc) rc = upload(s, f->cubes, f->n_cubes, sizeof(zb_cube), &d.cubes);
+    if (!rc) rc = upload(s, f->tris, f->n_tris, sizeof(zb_tri), &d.tris);
+    if (!rc) rc = upload(s, f->tri_normals, f->n_tris, sizeof(zb_tri_normals), &d.tri_normals);
+    if (!rc) rc = upload(s, f->instances, f->n_instances, sizeof(zb_instance), &d.instances);
+    if (!rc) rc = upload(s, f->media, f->n_media, sizeof(zb_medium), &d.media);
+    if (!rc) rc = upload(s, f->materials, f->n_materials, sizeof(zb_material), &d.materials);
+    if (!rc) rc = upload(s, f->textures, f->n_textures, sizeof(zb_texture), &d.textures);
+    if (!rc) rc = upload(s, f->spheres_obj, f->n_spheres_obj, 16, &d.spheres_obj);
+    if (!rc) rc = upload(s, f->texels_u8, f->n_texels_u8, 4, &d.texels_u8);
+    if (!rc) rc = upload(s, f->texels_f32, f->n_texels_f32, 16, &d.texels_f32);
+    if (rc) {
+        zb_scene_destroy(s);
+        return rc;
+    }
+    d.n_nodes = f->n_nodes;
+    d.n_items = f->n_items;
+    d.n_media = f->n_media;
+    s->env_hdr_texture = f->pad;
+    ZB_CUDA(cudaStreamSynchronize(ctx->stream));  // host arrays may be freed by the caller on return
+    *out = s;
+    return ZB_OK;
+}
+
+extern "C" int zb_scene_destroy(zb_scene* s) {
+    if (!s) return ZB_OK;
+    cudaSetDevice(s->ctx->device);
+    cudaStreamSynchronize(s->ctx->stream);
+    for (void* p : s->allocs) cudaFree(p);
+    delete s;
+    return ZB_OK;
+}

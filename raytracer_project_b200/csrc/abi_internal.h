@@ -1,0 +1,52 @@
+// abi_internal.h — state shared by the C-ABI translation units (abi.cu, abi_render.cu).
+#pragma once
+#include <cmath>
+#include <cstdio>
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include "../../include/zenith_b200.h"
+#include "kernels.h"
+
+std::string& zb_err_slot();
+inline int fail(int code, const std::string& msg) {
+    zb_err_slot() = msg;
+    return code;
+}
+#define ZB_CUDA(expr)                                                                                     \
+    do {                                                                                                  \
+        cudaError_t e__ = (expr);                                                                         \
+        if (e__ != cudaSuccess)                                                                           \
+            return fail(ZB_ERR_CUDA, std::string(#expr) + ": " + cudaGetErrorString(e__));                \
+    } while (0)
+
+struct zb_context {
+    int device = 0;
+    cudaStream_t stream = nullptr;
+    bool own_stream = false;
+    int sm_count = 0, cc_major = 0, cc_minor = 0;
+    size_t l2_bytes = 0;
+    unsigned long long* counters = nullptr;  // 8 x u64 on the device
+    // scratch reused across renders
+    float4* accum = nullptr;
+    float4* accum_aux = nullptr;
+    size_t accum_pixels = 0;
+    double* out_f64 = nullptr;
+    float4* out_f4 = nullptr;
+    void* pinned = nullptr;
+    size_t pinned_bytes = 0;
+    uint32_t* id_scratch = nullptr;
+    size_t id_pixels = 0;
+    cudaEvent_t ev[6] = {};
+    zb_stats stats{};
+};
+
+struct zb_scene {
+    zb_context* ctx = nullptr;
+    SceneDev dev{};
+    std::vector<void*> allocs;
+    uint32_t env_hdr_texture = ZB_NO_TEXTURE;
+    size_t bytes = 0;
+};
+

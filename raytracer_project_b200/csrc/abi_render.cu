@@ -1,0 +1,355 @@
+// abi_render.cu — zb_render / zb_render_device / zb_resolve_device / zb_primary_ids / zb_get_stats.
+// The drop-in for camera::render's hot part (camera.hpp:236-250 -> execute_render_threads :404-579).
+#include <algorithm>
+
+#include "abi_internal.h"
+
+namespace {
+
+struct d3 {
+    double x, y, z;
+};
+d3 operator+(d3 a, d3 b) { return {a.x + b.x, a.y + b.y, a.z + b.z}; }
+d3 operator-(d3 a, d3 b) { return {a.x - b.x, a.y - b.y, a.z - b.z}; }
+d3 operator*(double s, d3 a) { return {s * a.x, s * a.y, s * a.z}; }
+double dot(d3 a, d3 b) { return a.x * b.x + a.y * b.y + a.z * b.z; }
+d3 cross(d3 a, d3 b) { return {a.y * b.z - a.z * b.y, a.z * b.x - a.x * b.z, a.x * b.y - a.y * b.x}; }
+d3 unit(d3 a) {
+    double l = std::sqrt(dot(a, a));
+    return l < 1e-8 ? d3{0, 0, 0} : (1.0 / l) * a;
+}
+d3 from(const double* p) { return {p[0], p[1], p[2]}; }
+float3 to_f3(d3 a) { return make_float3(float(a.x), float(a.y), float(a.z)); }
+double clampd(double x, double lo, double hi) { return x < lo ? lo : (x > hi ? hi : x); }
+
+// camera::initialize (camera.hpp:358-402), in double; narrowed to fp32 only at the end.
+int setup_camera(const zb_camera* c, CameraDev& cam) {
+    if (c->image_width < 1 || c->image_height < 1) return fail(ZB_ERR_INVALID, "camera: image size must be >= 1");
+    if (double(c->image_width) * c->image_height > 2.0e9) return fail(ZB_ERR_INVALID, "camera: image too large");
+    const double pi = 3.14159265358979323846;
+    double aspect = double(c->image_width) / c->image_height;
+    d3 lookfrom = from(c->lookfrom), lookat = from(c->lookat), vup = from(c->vup);
+    double theta = c->vfov * pi / 180.0;
+    double h = std::tan(theta / 2);
+    double vh = 2 * h * c->focus_dist, vw = vh * aspect;
+    d3 w = unit(lookfrom - lookat), u = unit(cross(vup, w)), v = cross(w, u);
+    d3 vu = vw * u, vv = vh * (-1.0 * v);
+    d3 du = (1.0 / c->image_width) * vu, dv = (1.0 / c->image_height) * vv;
+    d3 upper_left = lookfrom - c->focus_dist * w - 0.5 * vu - 0.5 * vv;
+    d3 pix00 = upper_left + 0.5 * (du + dv);
+    double radius = c->focus_dist * std::tan((c->defocus_angle / 2) * pi / 180.0);
+    d3 rel = pix00 - lookfrom;
+    cam.center = to_f3(lookfrom);
+    cam.pix00_rel = to_f3(rel);
+    cam.du = to_f3(du);
+    cam.dv = to_f3(dv);
+    cam.disk_u = to_f3(radius * u);
+    cam.disk_v = to_f3(radius * v);
+    cam.u = to_f3(u);
+    cam.v = to_f3(v);
+    cam.w = to_f3(w);
+    // the primary-ID kernel subtracts the fp32-rounded centre it really uses as the origin
+    d3 cf = {double(cam.center.x), double(cam.center.y), double(cam.center.z)};
+    d3 rel_id = pix00 - cf;
+    cam.pix00_rel_d[0] = rel_id.x; cam.pix00_rel_d[1] = rel_id.y; cam.pix00_rel_d[2] = rel_id.z;
+    cam.du_d[0] = du.x; cam.du_d[1] = du.y; cam.du_d[2] = du.z;
+    cam.dv_d[0] = dv.x; cam.dv_d[1] = dv.y; cam.dv_d[2] = dv.z;
+    cam.width = c->image_width;
+    cam.height = c->image_height;
+    cam.defocus = c->defocus_angle > 0 ? 1 : 0;
+    cam.pad = 0;
+    return ZB_OK;
+}
+
+// The ray-independent part of camera::get_background_color (camera.hpp:828-925), in double.
+int setup_env(const zb_environment* e, const zb_scene* scene, EnvDev& env) {
+    std::memset(&env, 0, sizeof(env));
+    env.mode = e->mode;
+    env.intensity = float(e->intensity);
+    env.hdr_texture = ZB_NO_TEXTURE;
+    if (e->mode == ZB_ENV_SOLID_COLOR) {
+        env.background = to_f3(e->intensity * from(e->background_color));
+    } else if (e->mode == ZB_ENV_HDR_MAP) {
+        env.hdr_texture = e->hdr_texture != ZB_NO_TEXTURE ? e->hdr_texture : scene->env_hdr_texture;
+        // yaw (Y), then tilt (X), then roll (Z): d3 = Rz * Rx * Ry * d   (camera.hpp:843-862)
+        double cy = std::cos(e->hdri_rotation), sy = std::sin(e->hdri_rotation);
+        double cp = std::cos(e->hdri_tilt), sp = std::sin(e->hdri_tilt);
+        double cr = std::cos(e->hdri_roll), sr = std::sin(e->hdri_roll);
+        double Ry[3][3] = {{cy, 0, sy}, {0, 1, 0}, {-sy, 0, cy}};
+        double Rx[3][3] = {{1, 0, 0}, {0, cp, -sp}, {0, sp, cp}};
+        double Rz[3][3] = {{cr, -sr, 0}, {sr, cr, 0}, {0, 0, 1}};
+        double T[3][3], M[3][3];
+        for (int i = 0; i < 3; i++)
+            for (int j = 0; j < 3; j++) {
+                T[i][j] = 0;
+                for (int k = 0; k < 3; k++) T[i][j] += Rx[i][k] * Ry[k][j];
+            }
+        for (int i = 0; i < 3; i++)
+            for (int j = 0; j < 3; j++) {
+                M[i][j] = 0;
+                for (int k = 0; k < 3; k++) M[i][j] += Rz[i][k] * T[k][j];
+            }
+        env.hdr_r0 = make_float3(float(M[0][0]), float(M[0][1]), float(M[0][2]));
+        env.hdr_r1 = make_float3(float(M[1][0]), float(M[1][1]), float(M[1][2]));
+        env.hdr_r2 = make_float3(float(M[2][0]), float(M[2][1]), float(M[2][2]));
+    } else if (e->mode == ZB_ENV_PHYSICAL_SUN) {
+        d3 sun = unit(from(e->sun_direction));
+        double sun_height = sun.y, adj = sun_height - 0.05;
+        double sky_exposure = clampd(adj * 8.0 + 1.4, 0.0, 1.0);
+        double day = clampd(adj * 10.0 + 1.1, 0.0, 1.0);
+        double sunset_int = clampd(1.0 - std::fabs(adj + 0.05) * 30.0, 0.0, 1.0);
+        double sunset = adj > -0.1 ? sunset_int : 0.0;
+        if (sun_height < 0) sunset *= (sun_height * 10.0 + 1.0);
+        sunset = clampd(sunset, 0.0, 1.0);
+        d3 zen = (1.0 - day) * d3{0.01, 0.03, 0.1} + day * d3{0.2, 0.5, 1.0};
+        d3 hor = (1.0 - day) * d3{0.05, 0.02, 0.01} + day * d3{0.6, 0.8, 1.0};
+        hor = (1.0 - sunset) * hor + sunset * d3{1.0, 0.35, 0.1};
+        d3 s_color = (1.0 - sunset) * from(e->sun_color) + sunset * d3{1.0, 0.3, 0.1};
+        double vis = clampd(sun_height * 5.0 + 1.0, 0.0, 1.0);
+        env.sun_dir = to_f3(sun);
+        env.zenith = to_f3(zen);
+        env.horizon = to_f3(hor);
+        env.sun_add = to_f3((e->sun_intensity * vis) * s_color);
+        env.sky_scale = float(e->intensity * 1.5 * sky_exposure);
+        env.sun_threshold = float(1.0 - e->sun_size * 0.001);
+        env.sun_visible = adj > -0.1 ? 1 : 0;
+    } else {
+        return fail(ZB_ERR_INVALID, "environment: unknown mode");
+    }
+    return ZB_OK;
+}
+
+int ensure_scratch(zb_context* ctx, size_t pixels, bool aux) {
+    if (ctx->accum_pixels < pixels) {
+        cudaFree(ctx->accum);
+        cudaFree(ctx->accum_aux);
+        cudaFree(ctx->out_f64);
+        cudaFree(ctx->out_f4);
+        ctx->accum = nullptr;
+        ctx->accum_aux = nullptr;
+        ctx->out_f64 = nullptr;
+        ctx->out_f4 = nullptr;
+        ctx->accum_pixels = 0;
+        ZB_CUDA(cudaMalloc(&ctx->accum, pixels * sizeof(float4)));
+        ZB_CUDA(cudaMalloc(&ctx->out_f64, pixels * 3 * sizeof(double)));
+        ZB_CUDA(cudaMalloc(&ctx->out_f4, pixels * sizeof(float4)));
+        ctx->accum_pixels = pixels;
+    }
+    if (aux && !ctx->accum_aux) ZB_CUDA(cudaMalloc(&ctx->accum_aux, 3 * ctx->accum_pixels * sizeof(float4)));
+    size_t need = pixels * 3 * sizeof(double);
+    if (ctx->pinned_bytes < need) {
+        if (ctx->pinned) cudaFreeHost(ctx->pinned);
+        ctx->pinned = nullptr;
+        ctx->pinned_bytes = 0;
+        ZB_CUDA(cudaMallocHost(&ctx->pinned, need));
+        ctx->pinned_bytes = need;
+    }
+    return ZB_OK;
+}
+
+int fill_params(zb_context* ctx, const zb_scene* scene, const zb_camera* cam, const zb_environment* env,
+                const zb_render_opts* o, RenderParams& P) {
+    if (!ctx || !scene || !cam || !env || !o) return fail(ZB_ERR_INVALID, "render: NULL argument");
+    if (scene->ctx != ctx) return fail(ZB_ERR_INVALID, "render: scene belongs to another context");
+    if (o->samples_per_pixel < 1 || o->max_depth < 0) return fail(ZB_ERR_INVALID, "render: bad spp / max_depth");
+    std::memset(&P, 0, sizeof(P));
+    P.sc = scene->dev;
+    int rc = setup_camera(cam, P.cam);
+    if (rc) return rc;
+    rc = setup_env(env, scene, P.env);
+    if (rc) return rc;
+    P.counters = ctx->counters;
+    P.seed_lo = uint32_t(o->seed);
+    P.seed_hi = uint32_t(o->seed >> 32);
+    int sb = o->sample_begin, se = o->sample_end;
+    if (sb == 0 && se == 0) se = o->samples_per_pixel;
+    if (sb < 0 || se < sb || se > o->samples_per_pixel) return fail(ZB_ERR_INVALID, "render: bad sample range");
+    P.sample_begin = sb;
+    P.sample_end = se;
+    P.max_depth = o->max_depth;
+    P.aux_samples = std::min(std::max(o->samples_per_pixel / 8, 64), 1024);  // camera.hpp:433
+    P.use_albedo = o->use_albedo;
+    P.use_normal = o->use_normal;
+    P.use_z = o->use_z_depth;
+    P.inv_z_max = o->z_depth_max_dist > 0 ? float(1.0 / o->z_depth_max_dist) : 0.f;
+    P.tile_rank = o->tile_ranks > 1 ? o->tile_rank : 0;
+    P.tile_ranks = o->tile_ranks > 1 ? o->tile_ranks : 1;
+    if (P.tile_rank < 0 || P.tile_rank >= P.tile_ranks) return fail(ZB_ERR_INVALID, "render: bad tile rank");
+    P.tiles_x = (cam->image_width + ZB_TILE_W - 1) / ZB_TILE_W;
+    P.tiles_y = (cam->image_height + ZB_TILE_H - 1) / ZB_TILE_H;
+    return ZB_OK;
+}
+
+int owned_tiles(const RenderParams& P) {
+    int total = P.tiles_x * P.tiles_y;
+    return (total - P.tile_rank + P.tile_ranks - 1) / P.tile_ranks;
+}
+
+// Launch this rank's share in batches of samples; accum is overwritten by the first batch.
+int launch_share(zb_context* ctx, RenderParams P, const zb_render_opts* o, const volatile int* cancel,
+                 zb_progress_fn progress, void* user, bool zero_first) {
+    const int sb = P.sample_begin, se = P.sample_end;
+    int per = o->samples_per_launch > 0 ? o->samples_per_launch : (cancel || progress ? 16 : se - sb);
+    per = std::max(per, 1);
+    const size_t pixels = size_t(P.cam.width) * P.cam.height;
+    if (zero_first && (P.tile_ranks > 1 || se == sb)) {
+        // tile stripes leave other ranks' pixels untouched: they must read as zero sums
+        ZB_CUDA(cudaMemsetAsync(P.accum, 0, pixels * sizeof(float4), ctx->stream));
+        if (P.accum_aux) ZB_CUDA(cudaMemsetAsync(P.accum_aux, 0, 3 * pixels * sizeof(float4), ctx->stream));
+    }
+    int done = 0;
+    for (int s = sb; s < se; s += per) {
+        if (cancel && *cancel) return fail(ZB_ERR_CANCELLED, "render cancelled");
+        P.sample_begin = s;
+        P.sample_end = std::min(s + per, se);
+        P.accumulate = s > sb ? 1 : 0;
+        ZB_CUDA(zbk_launch_render(P, owned_tiles(P), o->collect_stats != 0, ctx->stream));
+        ctx->stats.launches++;
+        done = P.sample_end - sb;
+        if (progress || cancel) {
+            ZB_CUDA(cudaStreamSynchronize(ctx->stream));
+            if (progress) progress(int((long long)P.cam.height * done / std::max(se - sb, 1)), user);
+        }
+    }
+    return ZB_OK;
+}
+
+int d2h(zb_context* ctx, void* host, const void* dev, size_t bytes) {
+    ZB_CUDA(cudaMemcpyAsync(ctx->pinned, dev, bytes, cudaMemcpyDeviceToHost, ctx->stream));
+    ZB_CUDA(cudaStreamSynchronize(ctx->stream));
+    std::memcpy(host, ctx->pinned, bytes);
+    return ZB_OK;
+}
+
+int read_counters(zb_context* ctx) {
+    unsigned long long c[8];
+    ZB_CUDA(cudaMemcpyAsync(c, ctx->counters, sizeof(c), cudaMemcpyDeviceToHost, ctx->stream));
+    ZB_CUDA(cudaStreamSynchronize(ctx->stream));
+    ctx->stats.rays = c[0];
+    ctx->stats.node_visits = c[1];
+    ctx->stats.box_tests = 2 * c[1];
+    ctx->stats.prim_tests = c[2];
+    ctx->stats.instance_visits = c[3];
+    ctx->stats.paths = c[4];
+    return ZB_OK;
+}
+
+}  // namespace
+
+extern "C" int zb_render_device(zb_context* ctx, const zb_scene* scene, const zb_camera* cam,
+                                const zb_environment* env, const zb_render_opts* opts, void* accum_f4,
+                                void* accum_aux_f4) {
+    RenderParams P;
+    int rc = fill_params(ctx, scene, cam, env, opts, P);
+    if (rc) return rc;
+    if (!accum_f4) return fail(ZB_ERR_INVALID, "zb_render_device: accum_f4 is NULL");
+    ZB_CUDA(cudaSetDevice(ctx->device));
+    P.accum = static_cast<float4*>(accum_f4);
+    P.accum_aux = static_cast<float4*>(accum_aux_f4);
+    ZB_CUDA(cudaMemsetAsync(ctx->counters, 0, 8 * sizeof(unsigned long long), ctx->stream));
+    ctx->stats = zb_stats{};
+    return launch_share(ctx, P, opts, nullptr, nullptr, nullptr, true);
+}
+
+extern "C" int zb_resolve_device(zb_context* ctx, const void* accum_f4, size_t n_pixels, double scale, void* out_f4,
+                                 void* out_rgb_f64) {
+    if (!ctx || !accum_f4) return fail(ZB_ERR_INVALID, "zb_resolve_device: NULL argument");
+    ZB_CUDA(cudaSetDevice(ctx->device));
+    ZB_CUDA(zbk_launch_resolve(static_cast<const float4*>(accum_f4), n_pixels, float(scale), static_cast<float4*>(out_f4),
+                               static_cast<double*>(out_rgb_f64), ctx->stream));
+    ctx->stats.launches++;
+    return ZB_OK;
+}
+
+extern "C" int zb_render(zb_context* ctx, const zb_scene* scene, const zb_camera* cam, const zb_environment* env,
+                         const zb_render_opts* opts, zb_outputs* out, const volatile int* cancel,
+                         zb_progress_fn progress, void* user) {
+    RenderParams P;
+    int rc = fill_params(ctx, scene, cam, env, opts, P);
+    if (rc) return rc;
+    if (!out) return fail(ZB_ERR_INVALID, "zb_render: outputs is NULL");
+    ZB_CUDA(cudaSetDevice(ctx->device));
+    const size_t pixels = size_t(cam->image_width) * cam->image_height;
+    const bool aux = out->albedo || out->normal || out->z_depth;
+    rc = ensure_scratch(ctx, pixels, aux);
+    if (rc) return rc;
+    P.accum = ctx->accum;
+    P.accum_aux = aux ? ctx->accum_aux : nullptr;
+    if (!out->albedo) P.use_albedo = 0;
+    if (!out->normal) P.use_normal = 0;
+    if (!out->z_depth) P.use_z = 0;
+    ctx->stats = zb_stats{};
+    ZB_CUDA(cudaMemsetAsync(ctx->counters, 0, 8 * sizeof(unsigned long long), ctx->stream));
+    ZB_CUDA(cudaEventRecord(ctx->ev[0], ctx->stream));
+    rc = launch_share(ctx, P, opts, cancel, progress, user, true);
+    if (rc) return rc;
+    ZB_CUDA(cudaEventRecord(ctx->ev[1], ctx->stream));
+    // K5 resolve + copy back in the reference's layout (3 doubles per pixel, camera.hpp:531)
+    const double scale = 1.0 / opts->samples_per_pixel;
+    const double aux_scale = 1.0 / std::min(P.aux_samples, opts->samples_per_pixel);  // camera.hpp:535-541
+    if (out->beauty || out->beauty_f4) {
+        ZB_CUDA(zbk_launch_resolve(ctx->accum, pixels, float(scale), out->beauty_f4 ? ctx->out_f4 : nullptr,
+                                   out->beauty ? ctx->out_f64 : nullptr, ctx->stream));
+        ctx->stats.launches++;
+    }
+    ZB_CUDA(cudaEventRecord(ctx->ev[2], ctx->stream));
+    if (out->beauty) rc = d2h(ctx, out->beauty, ctx->out_f64, pixels * 3 * sizeof(double));
+    if (!rc && out->beauty_f4) rc = d2h(ctx, out->beauty_f4, ctx->out_f4, pixels * sizeof(float4));
+    double* aux_out[3] = {out->albedo, out->normal, out->z_depth};
+    for (int k = 0; k < 3 && !rc; k++) {
+        if (!aux_out[k]) continue;
+        ZB_CUDA(zbk_launch_resolve(ctx->accum_aux + k * pixels, pixels, float(aux_scale), nullptr, ctx->out_f64, ctx->stream));
+        ctx->stats.launches++;
+        rc = d2h(ctx, aux_out[k], ctx->out_f64, pixels * 3 * sizeof(double));
+    }
+    if (rc) return rc;
+    ZB_CUDA(cudaEventRecord(ctx->ev[3], ctx->stream));
+    rc = read_counters(ctx);
+    if (rc) return rc;
+    float ms = 0;
+    ZB_CUDA(cudaEventElapsedTime(&ms, ctx->ev[0], ctx->ev[1]));
+    ctx->stats.kernel_ms = ms;
+    ZB_CUDA(cudaEventElapsedTime(&ms, ctx->ev[1], ctx->ev[2]));
+    ctx->stats.resolve_ms = ms;
+    ZB_CUDA(cudaEventElapsedTime(&ms, ctx->ev[2], ctx->ev[3]));
+    ctx->stats.d2h_ms = ms;
+    if (progress) progress(cam->image_height, user);  // camera.hpp:576-578
+    return ZB_OK;
+}
+
+extern "C" int zb_primary_ids(zb_context* ctx, const zb_scene* scene, const zb_camera* cam, uint32_t* leaf_id,
+                              uint32_t* prim_id, float* t) {
+    if (!ctx || !scene || !cam) return fail(ZB_ERR_INVALID, "zb_primary_ids: NULL argument");
+    ZB_CUDA(cudaSetDevice(ctx->device));
+    RenderParams P;
+    std::memset(&P, 0, sizeof(P));
+    P.sc = scene->dev;
+    int rc = setup_camera(cam, P.cam);
+    if (rc) return rc;
+    const size_t pixels = size_t(cam->image_width) * cam->image_height;
+    if (ctx->id_pixels < pixels) {
+        cudaFree(ctx->id_scratch);
+        ctx->id_scratch = nullptr;
+        ctx->id_pixels = 0;
+        ZB_CUDA(cudaMalloc(&ctx->id_scratch, pixels * 3 * sizeof(uint32_t)));
+        ctx->id_pixels = pixels;
+    }
+    uint32_t* d_leaf = ctx->id_scratch;
+    uint32_t* d_prim = ctx->id_scratch + pixels;
+    float* d_t = reinterpret_cast<float*>(ctx->id_scratch + 2 * pixels);
+    ZB_CUDA(zbk_launch_primary_ids(P, d_leaf, d_prim, d_t, ctx->stream));
+    ctx->stats.launches++;
+    if (leaf_id) ZB_CUDA(cudaMemcpyAsync(leaf_id, d_leaf, pixels * 4, cudaMemcpyDeviceToHost, ctx->stream));
+    if (prim_id) ZB_CUDA(cudaMemcpyAsync(prim_id, d_prim, pixels * 4, cudaMemcpyDeviceToHost, ctx->stream));
+    if (t) ZB_CUDA(cudaMemcpyAsync(t, d_t, pixels * 4, cudaMemcpyDeviceToHost, ctx->stream));
+    ZB_CUDA(cudaStreamSynchronize(ctx->stream));
+    return ZB_OK;
+}
+
+extern "C" int zb_get_stats(zb_context* ctx, zb_stats* out) {
+    if (!ctx || !out) return fail(ZB_ERR_INVALID, "zb_get_stats: NULL argument");
+    int rc = read_counters(ctx);
+    if (rc) return rc;
+    *out = ctx->stats;
+    return ZB_OK;
+}

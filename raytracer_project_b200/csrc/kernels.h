@@ -1,0 +1,12 @@
+// kernels.h — launch entry points of kernels.cu, used by the C-ABI implementation (abi.cu).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "scene_dev.cuh"
+
+cudaError_t zbk_launch_render(const RenderParams& P, int n_tiles_owned, bool stats, cudaStream_t stream);
+cudaError_t zbk_launch_primary_ids(const RenderParams& P, uint32_t* leaf_id, uint32_t* prim_id, float* t,
+                                   cudaStream_t stream);
+cudaError_t zbk_launch_resolve(const float4* accum, size_t n, float scale, float4* out_f4, double* out_f64,
+                               cudaStream_t stream);

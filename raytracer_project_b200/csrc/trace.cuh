@@ -1,0 +1,306 @@
+// trace.cuh — K2: closest-hit query over the flat two-level BVH (replaces the recursive virtual
+// world.hit() of bvh.hpp:46-118 / hittable_list.hpp:28-41 and every primitive's hit()).
+//
+// One thread = one ray.  The TLAS leaf holds 32-byte items (inline spheres, or references to cubes,
+// loose triangles, instances and media); an instance over a mesh switches the same loop into that
+// mesh's BLAS with the ray moved to object space (directions are never renormalised, so t is
+// invariant — translate.hpp:16-19, scale.hpp:21-24) and a sentinel on the stack brings it back.
+// Node = 64 B holding both child boxes: four 16-byte non-coherent loads, then two slab tests; the
+// nearer child is visited first and the other pushed on a short per-thread stack.
+#pragma once
+#include "../../include/zenith_b200.h"
+#include "scene_dev.cuh"
+
+#define ZB_STACK 64
+#define ZB_EXIT_INSTANCE ((int)0x80000000)
+
+struct Hit {
+    float t;
+    uint32_t item;  // index into items[] (TLAS leaf order); 0xFFFFFFFF = miss
+    uint32_t prim;  // absolute triangle index for mesh / triangle hits
+};
+
+struct Counters {
+    uint32_t rays, nodes, prims, insts;
+};
+
+// Per-ray source of the free-flight draw of constant_medium::hit (constant_medium.hpp:64): one draw
+// per (ray, medium), so the result does not depend on traversal order.
+struct MediumRng {
+    Philox ph;
+    uint32_t pixel, sample, bounce;
+    ZB_DEV float draw(uint32_t medium) const {
+        uint4 r = ph(pixel, sample, bounce, 0x10000u + (medium >> 2));
+        uint32_t v = (medium & 3) == 0 ? r.x : (medium & 3) == 1 ? r.y : (medium & 3) == 2 ? r.z : r.w;
+        return u01_open(v);
+    }
+};
+
+// ---------------------------------------------------------------------------------- primitives
+
+// sphere::hit (sphere.hpp:18-39): roots of a t^2 - 2 h t + c = 0 accepted only strictly inside
+// (tmin, tmax), nearer root first.  fp32 with two safeguards for the r = 1000 ground sphere and for
+// rays that start 1e-4 above a surface: the discriminant uses the perpendicular-distance form
+// a (r^2 - |oc - (h/a) d|^2), and c = |oc|^2 - r^2 is evaluated in fp64 (B200 runs fp64 at half the
+// fp32 rate) and the roots come from q = h + sgn(h) sqrt(disc): t = q/a and t = c/q.
+ZB_DEV bool hit_sphere(float4 s, float3 o, float3 d, float tmin, float tmax, float& t_out) {
+    float3 oc = f3(s.x - o.x, s.y - o.y, s.z - o.z);
+    float a = dot(d, d);
+    float h = dot(d, oc);
+    float inv_a = __frcp_rn(a);
+    float3 l = fma3(-h * inv_a, d, oc);
+    float disc = fmaf(s.w, s.w, -dot(l, l));
+    if (disc < 0.f) return false;
+    double ocx = double(s.x) - double(o.x), ocy = double(s.y) - double(o.y), ocz = double(s.z) - double(o.z);
+    float c = float(fma(ocx, ocx, fma(ocy, ocy, fma(ocz, ocz, -double(s.w) * double(s.w)))));
+    float sq = sqrtf(a * disc);
+    float q = h + copysignf(sq, h);
+    float ta = q * inv_a;
+    float tb = q != 0.f ? c / q : ta;
+    float t0 = fminf(ta, tb), t1 = fmaxf(ta, tb);
+    if (t0 > tmin && t0 < tmax) { t_out = t0; return true; }
+    if (t1 > tmin && t1 < tmax) { t_out = t1; return true; }
+    return false;
+}
+
+// cube::hit (cube.hpp:44-70): slabs +-half about the origin of the current frame, t = entry distance
+// or tmin when the origin is inside; accepted whenever tmax >= tmin.
+ZB_DEV bool hit_cube(float3 half, float3 o, float3 d, float tmin, float tmax, float& t_out) {
+    float lo = tmin, hi = tmax;
+    {
+        float inv = 1.0f / d.x;
+        float t0 = (-half.x - o.x) * inv, t1 = (half.x - o.x) * inv;
+        if (inv < 0.f) { float s = t0; t0 = t1; t1 = s; }
+        lo = fmaxf(t0, lo); hi = fminf(t1, hi);
+        if (hi < lo) return false;
+    }
+    {
+        float inv = 1.0f / d.y;
+        float t0 = (-half.y - o.y) * inv, t1 = (half.y - o.y) * inv;
+        if (inv < 0.f) { float s = t0; t0 = t1; t1 = s; }
+        lo = fmaxf(t0, lo); hi = fminf(t1, hi);
+        if (hi < lo) return false;
+    }
+    {
+        float inv = 1.0f / d.z;
+        float t0 = (-half.z - o.z) * inv, t1 = (half.z - o.z) * inv;
+        if (inv < 0.f) { float s = t0; t0 = t1; t1 = s; }
+        lo = fmaxf(t0, lo); hi = fminf(t1, hi);
+        if (hi < lo) return false;
+    }
+    t_out = lo;
+    return true;
+}
+
+// triangle::hit (triangle.hpp:17-66) restated as Moeller-Trumbore with the reference's acceptance
+// rules: degenerate (|N| < 1e-8) and parallel (|N.d|/|N| < 1e-8) triangles rejected, t accepted
+// INCLUSIVELY in [tmin, tmax], edges inclusive (a point on a shared edge hits both triangles).
+ZB_DEV bool hit_tri(float3 v0, float3 v1, float3 v2, float3 o, float3 d, float tmin, float tmax, float& t_out) {
+    float3 e1 = v1 - v0, e2 = v2 - v0;
+    float3 n = cross(e1, e2);
+    float n2 = dot(n, n);
+    if (n2 < 1e-16f) return false;
+    float nd = dot(n, d);
+    if (nd * nd < 1e-16f * n2) return false;
+    float inv = 1.0f / nd;
+    float3 tv = v0 - o;
+    float t = dot(n, tv) * inv;
+    if (!(t >= tmin && t <= tmax)) return false;
+    float3 q = cross(tv, d);
+    float u = dot(q, e2) * inv;   // weight of v1
+    float v = -dot(q, e1) * inv;  // weight of v2
+    if (u < 0.f || v < 0.f || u + v > 1.0f) return false;
+    t_out = t;
+    return true;
+}
+
+struct InstanceHead {
+    Affine w2o;
+    uint32_t geom_kind, geom_index, flags, node_root;
+};
+ZB_DEV InstanceHead load_instance_head(const SceneDev& sc, uint32_t idx) {
+    const float4* p = sc.instances + 8 * size_t(idx);
+    InstanceHead h;
+    h.w2o.r0 = __ldg(p + 0);
+    h.w2o.r1 = __ldg(p + 1);
+    h.w2o.r2 = __ldg(p + 2);
+    float4 m = __ldg(p + 6);
+    float4 m2 = __ldg(p + 7);
+    h.geom_kind = __float_as_uint(m.x);
+    h.geom_index = __float_as_uint(m.y);
+    h.flags = __float_as_uint(m.z);
+    h.node_root = __float_as_uint(m.w);
+    (void)m2;
+    return h;
+}
+
+// boundary->hit() of a constant_medium for sphere / cube boundaries (optionally instanced)
+ZB_DEV bool hit_simple_geom(const SceneDev& sc, uint32_t geom_kind, uint32_t geom_index, float3 o, float3 d,
+                            float tmin, float tmax, float& t) {
+    if (geom_kind == ZB_GEOM_SPHERE) return hit_sphere(__ldg(sc.spheres_obj + geom_index), o, d, tmin, tmax, t);
+    if (geom_kind == ZB_GEOM_CUBE) return hit_cube(f3(__ldg(sc.cubes + 2 * size_t(geom_index))), o, d, tmin, tmax, t);
+    if (geom_kind == ZB_GEOM_TRIANGLE) {
+        const float4* tp = sc.tris + 3 * size_t(geom_index);
+        return hit_tri(f3(__ldg(tp)), f3(__ldg(tp + 1)), f3(__ldg(tp + 2)), o, d, tmin, tmax, t);
+    }
+    return false;
+}
+
+ZB_DEV bool hit_medium_boundary(const SceneDev& sc, float4 m0, float4 sph, float3 o, float3 d, float tmin, float tmax,
+                                float& t) {
+    uint32_t kind = __float_as_uint(m0.x), index = __float_as_uint(m0.y);
+    if (kind == ZB_ITEM_SPHERE) return hit_sphere(sph, o, d, tmin, tmax, t);
+    if (kind == ZB_ITEM_CUBE) return hit_cube(f3(__ldg(sc.cubes + 2 * size_t(index))), o, d, tmin, tmax, t);
+    InstanceHead ih = load_instance_head(sc, index);
+    return hit_simple_geom(sc, ih.geom_kind, ih.geom_index, xform_point(ih.w2o, o), xform_vector(ih.w2o, d), tmin,
+                           tmax, t);
+}
+
+// constant_medium::hit (constant_medium.hpp:39-77)
+ZB_DEV bool hit_medium(const SceneDev& sc, uint32_t medium, float3 o, float3 d, float tmin, float tmax,
+                       const MediumRng& rng, float& t_out) {
+    float4 m0 = __ldg(sc.media + 2 * size_t(medium));
+    float4 sph = __ldg(sc.media + 2 * size_t(medium) + 1);
+    float t1, t2;
+    if (!hit_medium_boundary(sc, m0, sph, o, d, -INFINITY, INFINITY, t1)) return false;
+    if (!hit_medium_boundary(sc, m0, sph, o, d, t1 + 0.0001f, INFINITY, t2)) return false;
+    if (t1 < tmin) t1 = tmin;
+    if (t2 > tmax) t2 = tmax;
+    if (t1 >= t2) return false;
+    if (t1 < 0.f) t1 = 0.f;
+    float len = length(d);
+    float inside = (t2 - t1) * len;
+    float dist = m0.z * __logf(rng.draw(medium));  // neg_inv_density * log(xi)
+    if (dist > inside) return false;
+    t_out = t1 + dist / len;
+    return true;
+}
+
+// ---------------------------------------------------------------------------------- traversal
+
+struct RayBox {
+    float3 inv, ood;
+    ZB_DEV void set(float3 o, float3 d) {
+        float dx = fabsf(d.x) > 1e-20f ? d.x : copysignf(1e-20f, d.x);
+        float dy = fabsf(d.y) > 1e-20f ? d.y : copysignf(1e-20f, d.y);
+        float dz = fabsf(d.z) > 1e-20f ? d.z : copysignf(1e-20f, d.z);
+        inv = f3(1.0f / dx, 1.0f / dy, 1.0f / dz);
+        ood = f3(o.x * inv.x, o.y * inv.y, o.z * inv.z);
+    }
+};
+
+template <bool STATS>
+ZB_DEV bool trace(const SceneDev& sc, float3 o, float3 d, float tmin, float tmax, const MediumRng& rng, Hit& hit,
+                  Counters& cnt) {
+    hit.t = tmax;
+    hit.item = 0xFFFFFFFFu;
+    hit.prim = 0;
+    cnt.rays++;
+    if (sc.n_nodes == 0) return false;
+
+    int stack[ZB_STACK];
+    int sp = 0;
+    int cur = 0;
+    bool in_blas = false;
+    uint32_t blas_item = 0;
+    float3 ro = o, rd = d;
+    RayBox rb;
+    rb.set(ro, rd);
+
+    for (;;) {
+        if (cur >= 0) {
+            const float4* np = sc.nodes + 4 * size_t(cur);
+            float4 n0 = __ldg(np), n1 = __ldg(np + 1), n2 = __ldg(np + 2);
+            float4 nc = __ldg(np + 3);
+            if (STATS) cnt.nodes++;
+            float lx0 = fmaf(n0.x, rb.inv.x, -rb.ood.x), lx1 = fmaf(n0.y, rb.inv.x, -rb.ood.x);
+            float ly0 = fmaf(n0.z, rb.inv.y, -rb.ood.y), ly1 = fmaf(n0.w, rb.inv.y, -rb.ood.y);
+            float lz0 = fmaf(n2.x, rb.inv.z, -rb.ood.z), lz1 = fmaf(n2.y, rb.inv.z, -rb.ood.z);
+            float rx0 = fmaf(n1.x, rb.inv.x, -rb.ood.x), rx1 = fmaf(n1.y, rb.inv.x, -rb.ood.x);
+            float ry0 = fmaf(n1.z, rb.inv.y, -rb.ood.y), ry1 = fmaf(n1.w, rb.inv.y, -rb.ood.y);
+            float rz0 = fmaf(n2.z, rb.inv.z, -rb.ood.z), rz1 = fmaf(n2.w, rb.inv.z, -rb.ood.z);
+            float ln = fmaxf(max3(fminf(lx0, lx1), fminf(ly0, ly1), fminf(lz0, lz1)), tmin);
+            float lf = fminf(min3(fmaxf(lx0, lx1), fmaxf(ly0, ly1), fmaxf(lz0, lz1)), hit.t) * 1.0000004f;
+            float rn = fmaxf(max3(fminf(rx0, rx1), fminf(ry0, ry1), fminf(rz0, rz1)), tmin);
+            float rf = fminf(min3(fmaxf(rx0, rx1), fmaxf(ry0, ry1), fmaxf(rz0, rz1)), hit.t) * 1.0000004f;
+            bool hl = ln <= lf, hr = rn <= rf;
+            int cl = __float_as_int(nc.x), cr = __float_as_int(nc.y);
+            if (hl && hr) {
+                bool swap = rn < ln;
+                int nearc = swap ? cr : cl, farc = swap ? cl : cr;
+                if (sp < ZB_STACK) stack[sp++] = farc;
+                cur = nearc;
+                continue;
+            }
+            if (hl) { cur = cl; continue; }
+            if (hr) { cur = cr; continue; }
+        } else if (cur == ZB_EXIT_INSTANCE) {
+            in_blas = false;
+            ro = o;
+            rd = d;
+            rb.set(ro, rd);
+        } else {
+            uint32_t code = ~uint32_t(cur);
+            uint32_t first = code >> 3, end = first + (code & 7u) + 1u;
+            if (in_blas) {
+                for (uint32_t i = first; i < end; i++) {
+                    const float4* tp = sc.tris + 3 * size_t(i);
+                    float4 a = __ldg(tp), b = __ldg(tp + 1), c = __ldg(tp + 2);
+                    if (STATS) cnt.prims++;
+                    float t;
+                    if (hit_tri(f3(a), f3(b), f3(c), ro, rd, tmin, hit.t, t)) {
+                        hit.t = t;
+                        hit.item = blas_item;
+                        hit.prim = i;
+                    }
+                }
+            } else {
+                for (uint32_t i = first; i < end; i++) {
+                    float4 g = __ldg(sc.items + 2 * size_t(i));
+                    float4 mf = __ldg(sc.items + 2 * size_t(i) + 1);
+                    uint32_t kind = __float_as_uint(mf.x) & 0xFFu, aux = __float_as_uint(mf.w);
+                    if (STATS) cnt.prims++;
+                    float t;
+                    if (kind == ZB_ITEM_SPHERE) {
+                        if (hit_sphere(g, o, d, tmin, hit.t, t)) { hit.t = t; hit.item = i; }
+                    } else if (kind == ZB_ITEM_INSTANCE) {
+                        InstanceHead ih = load_instance_head(sc, aux);
+                        if (STATS) cnt.insts++;
+                        float3 lo = xform_point(ih.w2o, o), ld = xform_vector(ih.w2o, d);
+                        if (ih.geom_kind == ZB_GEOM_MESH) {
+                            // defer the rest of this leaf, then dive into the BLAS in object space
+                            if (i + 1 < end && sp < ZB_STACK) stack[sp++] = int(~(((i + 1) << 3) | (end - i - 2)));
+                            if (sp < ZB_STACK) stack[sp++] = ZB_EXIT_INSTANCE;
+                            if (sp < ZB_STACK) stack[sp++] = int(ih.node_root);
+                            in_blas = true;
+                            blas_item = i;
+                            ro = lo;
+                            rd = ld;
+                            rb.set(ro, rd);
+                            break;
+                        }
+                        if (hit_simple_geom(sc, ih.geom_kind, ih.geom_index, lo, ld, tmin, hit.t, t)) {
+                            hit.t = t;
+                            hit.item = i;
+                            hit.prim = ih.geom_index;
+                        }
+                    } else if (kind == ZB_ITEM_CUBE) {
+                        if (hit_cube(f3(__ldg(sc.cubes + 2 * size_t(aux))), o, d, tmin, hit.t, t)) { hit.t = t; hit.item = i; }
+                    } else if (kind == ZB_ITEM_TRIANGLE) {
+                        const float4* tp = sc.tris + 3 * size_t(aux);
+                        if (hit_tri(f3(__ldg(tp)), f3(__ldg(tp + 1)), f3(__ldg(tp + 2)), o, d, tmin, hit.t, t)) {
+                            hit.t = t;
+                            hit.item = i;
+                            hit.prim = aux;
+                        }
+                    } else {  // ZB_ITEM_MEDIUM
+                        if (hit_medium(sc, aux, o, d, tmin, hit.t, rng, t)) { hit.t = t; hit.item = i; }
+                    }
+                }
+            }
+        }
+        if (sp == 0) break;
+        cur = stack[--sp];
+    }
+    return hit.item != 0xFFFFFFFFu;
+}

@@ -1,0 +1,143 @@
+"""CPU-side checks: the C-ABI library loads, exports every declared symbol, the host scene API
+flattens scenes correctly, malformed flat scenes are rejected, and compute fails loudly without a GPU."""
+import ctypes as C
+import os
+import re
+
+import numpy as np
+import pytest
+
+from raytracer_project_b200 import _lib, api, scenes
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def test_header_symbols_all_exported(lib):
+    hdr = open(os.path.join(ROOT, "include", "zenith_b200.h")).read()
+    declared = set(re.findall(r"^(?:int|const char\*)\s+(zb_\w+)\s*\(", hdr, flags=re.M))
+    assert declared, "no declarations parsed"
+    assert declared == set(_lib.SYMBOLS), declared ^ set(_lib.SYMBOLS)
+    for name in declared:
+        assert hasattr(lib, name), name
+    assert lib.zb_abi_version() == 1
+
+
+def test_struct_sizes_match_header():
+    # the PODs of include/zenith_b200.h as laid out by the C compiler
+    assert C.sizeof(_lib.Camera) == 8 + 8 + 72 + 16
+    assert C.sizeof(_lib.Environment) == 8 + 24 + 8 + 24 + 48 + 16
+    assert C.sizeof(_lib.Stats) == 6 * 8 + 4 * 8 + 8
+
+
+def _views(f):
+    nodes = np.ctypeslib.as_array(C.cast(f.nodes, C.POINTER(C.c_float)), (f.n_nodes, 16))
+    items = np.ctypeslib.as_array(C.cast(f.items, C.POINTER(C.c_float)), (f.n_items, 8))
+    return nodes, items
+
+
+def test_weekend_flatten_counts_and_bvh_invariants():
+    txt, cfg = scenes.weekend(seed=1)
+    flat = api.flatten_zscene(txt)
+    f = flat.contents
+    assert f.n_items == 484 and f.n_leaves == 484 and f.n_materials == 484 and f.n_instances == 0
+    nodes, items = _views(f)
+    child = nodes[:, 12:14].copy().view(np.int32)
+    meta = items[:, 4:8].copy().view(np.uint32)
+    # every leaf id appears exactly once; every item is referenced by exactly one leaf
+    assert sorted(meta[:, 2].tolist()) == list(range(484))
+    seen = np.zeros(f.n_items, int)
+    for node in range(f.n_nodes):
+        boxes = {0: (nodes[node, [0, 2, 8]], nodes[node, [1, 3, 9]]), 1: (nodes[node, [4, 6, 10]], nodes[node, [5, 7, 11]])}
+        for side in (0, 1):
+            c = int(child[node, side])
+            if c == -2**31:
+                continue
+            lo, hi = boxes[side]
+            if c >= 0:
+                # child's own two boxes are inside the box stored for it in the parent
+                clo = np.minimum(nodes[c, [0, 2, 8]], nodes[c, [4, 6, 10]])
+                chi = np.maximum(nodes[c, [1, 3, 9]], nodes[c, [5, 7, 11]])
+                assert np.all(clo >= lo) and np.all(chi <= hi)
+            else:
+                code = (~c) & 0xFFFFFFFF
+                first, count = code >> 3, (code & 7) + 1
+                for i in range(first, first + count):
+                    seen[i] += 1
+                    cx, cy, cz, r = items[i, :4]
+                    assert np.all(np.array([cx - r, cy - r, cz - r]) >= lo - 1e-3)
+                    assert np.all(np.array([cx + r, cy + r, cz + r]) <= hi + 1e-3)
+    assert np.all(seen == 1)
+    api.free_flat(flat)
+
+
+def test_flatten_wrappers_and_flags():
+    w = scenes.SceneWriter()
+    glass = w.dielectric(1.5)
+    red = w.lambertian((0.8, 0.1, 0.1))
+    s = w.sphere((0, 0, 0), 1.0, glass)
+    objs = [
+        w.translate(s, (1, 2, 3)),                       # baked sphere + force-front flag (SURVEY A.q1)
+        w.scale(s, (1, 2, 1)),                           # instance, keeps front_face (A.q2)
+        w.translate(w.matinst(w.rotate("y", w.scale(s, (2, 2, 2)), 0.5), red), (5, 0, 0)),
+        w.cube((-1, -1, -1), (1, 1, 1), red),
+        w.matinst(s, None),                              # null material -> magenta lambertian
+    ]
+    w.world(w.container("list", objs))
+    flat = api.flatten_zscene(w.text())
+    f = flat.contents
+    assert (f.n_items, f.n_instances, f.n_cubes, f.n_spheres_obj) == (5, 2, 1, 1)   # master sphere shared
+    _, items = _views(f)
+    meta = items[:, 4:8].copy().view(np.uint32)
+    by_leaf = {int(m[2]): (items[i, :4], m) for i, m in enumerate(meta)}
+    g0, m0 = by_leaf[0]
+    assert m0[0] == (0 | 0x100) and np.allclose(g0, [1, 2, 3, 1])
+    assert by_leaf[1][1][0] & 0xFF == 3 and by_leaf[2][1][0] & 0xFF == 3 and by_leaf[3][1][0] & 0xFF == 1
+    inst = np.ctypeslib.as_array(C.cast(f.instances, C.POINTER(C.c_float)), (f.n_instances, 32))
+    flags = inst[:, 24:28].copy().view(np.uint32)[:, 2]
+    i1, i2 = int(by_leaf[1][1][3]), int(by_leaf[2][1][3])
+    assert flags[i1] == 0 and flags[i2] == 0x100
+    # o2w of leaf 2 = T(5,0,0) * Ry(0.5) * S(2): column 3 is the translation, w2o is its inverse
+    o2w = np.vstack([inst[i2, 12:24].reshape(3, 4), [0, 0, 0, 1]])
+    w2o = np.vstack([inst[i2, 0:12].reshape(3, 4), [0, 0, 0, 1]])
+    assert np.allclose(o2w[:3, 3], [5, 0, 0]) and np.allclose(o2w @ w2o, np.eye(4), atol=1e-6)
+    c, s_ = np.cos(0.5), np.sin(0.5)
+    assert np.allclose(o2w[:3, :3], 2 * np.array([[c, 0, -s_], [0, 1, 0], [s_, 0, c]]), atol=1e-6)  # rotate_y.hpp:56-62
+    mats = np.ctypeslib.as_array(C.cast(f.materials, C.POINTER(C.c_float)), (f.n_materials, 8))
+    magenta = mats[int(by_leaf[4][1][1])]
+    assert np.allclose(magenta[4:7], [1, 0, 1])
+    api.free_flat(flat)
+
+
+def test_zscene_errors_are_reported():
+    with pytest.raises(_lib.ZbError) as e:
+        api.flatten_zscene("obj a sphere 0 0 0 1 nomat\nworld a\n")
+    assert "unknown material" in str(e.value)
+    with pytest.raises(_lib.ZbError):
+        api.flatten_zscene("obj a sphere 0 0 0 1\n")  # no world
+
+
+def test_empty_world_flattens():
+    flat = api.flatten_zscene("obj w list\nworld w\n")
+    assert flat.contents.n_items == 0 and flat.contents.n_nodes == 0
+    api.free_flat(flat)
+
+
+def test_upload_rejects_malformed_scene_before_touching_cuda(lib):
+    txt, _ = scenes.weekend(seed=1)
+    flat = api.flatten_zscene(txt)
+    bad = _lib.FlatScene.from_buffer_copy(flat.contents)
+    bad.n_materials = 3  # items now reference materials out of range
+    out = C.c_void_p()
+    fake_ctx = C.c_void_p(1)
+    rc = lib.zb_scene_upload(fake_ctx, C.byref(bad), C.byref(out))
+    assert rc == -1 and b"material out of range" in lib.zb_last_error()
+    api.free_flat(flat)
+
+
+def test_no_cpu_fallback_without_gpu(lib):
+    import torch
+    if torch.cuda.is_available():
+        pytest.skip("GPU present")
+    h = C.c_void_p()
+    rc = lib.zb_context_create(0, C.byref(h))
+    assert rc == -2 and b"no CPU fallback" in lib.zb_last_error()
