@@ -9,7 +9,8 @@ import ctypes as C
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libzenith_b200.so")
+# ZB_LIB selects an alternative build of the same library (kernel tuning variants under _build/)
+LIB_PATH = os.environ.get("ZB_LIB") or os.path.join(_HERE, "libzenith_b200.so")
 
 ZB_OK = 0
 ZB_NO_TEXTURE = 0xFFFFFFFF

@@ -5,11 +5,13 @@ cd "$(dirname "$0")/csrc"
 NVCC=${NVCC:-/usr/local/cuda/bin/nvcc}
 ARCH="-gencode arch=compute_100a,code=sm_100a"
 FLAGS="-O3 -std=c++20 -lineinfo -Xcompiler -fPIC,-Wall,-Wno-unused-function ${ZB_NVCC_EXTRA:-}"
-mkdir -p ../_build
-$NVCC $ARCH $FLAGS -c kernels.cu -o ../_build/kernels.o &
-$NVCC $ARCH $FLAGS -c abi.cu -o ../_build/abi.o &
-$NVCC $ARCH $FLAGS -c abi_render.cu -o ../_build/abi_render.o &
-g++ -O2 -std=c++20 -fPIC -Wall -c host_glue.cpp -o ../_build/host_glue.o &
+OUT=${ZB_OUT:-../libzenith_b200.so}
+B=../_build/${ZB_TAG:-main}
+mkdir -p $B
+$NVCC $ARCH $FLAGS -c kernels.cu -o $B/kernels.o &
+$NVCC $ARCH $FLAGS -c abi.cu -o $B/abi.o &
+$NVCC $ARCH $FLAGS -c abi_render.cu -o $B/abi_render.o &
+g++ -O2 -std=c++20 -fPIC -Wall -c host_glue.cpp -o $B/host_glue.o &
 wait
-$NVCC $ARCH -shared -o ../libzenith_b200.so ../_build/kernels.o ../_build/abi.o ../_build/abi_render.o ../_build/host_glue.o -cudart static
-echo "built $(cd .. && pwd)/libzenith_b200.so"
+$NVCC $ARCH -shared -o $OUT $B/kernels.o $B/abi.o $B/abi_render.o $B/host_glue.o -cudart static
+echo "built $OUT"

@@ -8,30 +8,70 @@
 #include "kernels.h"
 #include "shade.cuh"
 
-// One thread owns one pixel and walks its samples in order, so the per-pixel sum is deterministic
-// and needs no atomics.  A block renders a 16x8 pixel tile (each warp an 8x4 sub-tile, for coherent
-// primary rays); tiles are dealt to ranks round-robin for the tile-stripe partition.
+// Work decomposition.  A block renders a 16x8 pixel tile (tiles are dealt to ranks round-robin for the
+// tile-stripe partition); each of its four warps owns an 8x4 sub-tile and works through the
+// 32 x n_samples paths of that sub-tile as a queue: a lane whose path has ended takes the next
+// (pixel, sample) from the warp's counter, pixel-major, so at any time the 32 lanes trace samples of
+// the same one or two pixels (coherent primary rays, similar bounce rays) and no lane idles while the
+// queue is non-empty.  Lanes are never bound to a pixel, so per-pixel sums are kept in shared memory
+// as 64-bit fixed point (2^-22 units): integer addition is associative, which makes the result
+// independent of the order in which lanes finish — the frame is bit-reproducible and identical under
+// any tile / sample partition of the work.
+#define ZB_FIX_SCALE 4194304.0f
+#define ZB_FIX_INV (1.0 / 4194304.0)
+
+ZB_DEV void fix_add(unsigned long long* slot, float v) {
+    atomicAdd(slot, (unsigned long long)__float2ll_rn(v * ZB_FIX_SCALE));
+}
+ZB_DEV float fix_get(unsigned long long v) { return float(double((long long)v) * ZB_FIX_INV); }
+
 template <bool STATS>
-__global__ void __launch_bounds__(ZB_BLOCK_THREADS) k_render(const __grid_constant__ RenderParams P) {
+__global__ void __launch_bounds__(ZB_BLOCK_THREADS, ZB_MIN_BLOCKS) k_render(const __grid_constant__ RenderParams P) {
+    constexpr int WARPS = ZB_BLOCK_THREADS / 32;
+    __shared__ unsigned long long s_sum[WARPS][32][3];
+    __shared__ unsigned long long s_aux[WARPS][32][7];  // albedo rgb, normal xyz, z
+    __shared__ int s_next[WARPS];
+
     const int tile = blockIdx.x * P.tile_ranks + P.tile_rank;
     const int tx = tile % P.tiles_x, ty = tile / P.tiles_x;
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int px = tx * ZB_TILE_W + (warp & 1) * 8 + (lane & 7);
-    const int py = ty * ZB_TILE_H + (warp >> 1) * 4 + (lane >> 3);
-    const bool active = px < P.cam.width && py < P.cam.height && ty < P.tiles_y;
+    const int px0 = tx * ZB_TILE_W + (warp & 1) * 8, py0 = ty * ZB_TILE_H + (warp >> 1) * 4;
+    const bool aux_on = P.accum_aux != nullptr;
+
+#pragma unroll
+    for (int c = 0; c < 3; c++) s_sum[warp][lane][c] = 0ull;
+    if (aux_on) {
+#pragma unroll
+        for (int c = 0; c < 7; c++) s_aux[warp][lane][c] = 0ull;
+    }
+    if (lane == 0) s_next[warp] = 0;
+    __syncwarp();
+
+    const int n_s = P.sample_end - P.sample_begin;
+    const int total = (ty < P.tiles_y && P.max_depth > 0) ? 32 * n_s : 0;
+    const Philox ph{P.seed_lo, P.seed_hi};
     Counters cnt = {0, 0, 0, 0};
     uint32_t paths = 0;
-    if (active) {
-        const uint32_t pixel = uint32_t(py) * uint32_t(P.cam.width) + uint32_t(px);
-        const Philox ph{P.seed_lo, P.seed_hi};
-        float3 sum = f3(0, 0, 0), s_alb = f3(0, 0, 0), s_nrm = f3(0, 0, 0);
-        float s_z = 0.f;
-        const float3 base = P.cam.pix00_rel + float(px) * P.cam.du + float(py) * P.cam.dv;
-        for (int s = P.sample_begin; s < P.sample_end; s++) {
+
+    // path state of this lane
+    int p = 0, seg = 0;
+    uint32_t pixel = 0, s = 0;
+    float3 o = f3(0, 0, 0), d = f3(0, 0, 0), L = f3(0, 0, 0), beta = f3(1, 1, 1);
+
+    // next path of this warp's queue whose pixel lies inside the image
+    auto fetch = [&]() -> bool {
+        for (;;) {
+            int k = atomicAdd(&s_next[warp], 1);
+            if (k >= total) return false;
+            p = k / n_s;
+            int px = px0 + (p & 7), py = py0 + (p >> 3);
+            if (px >= P.cam.width || py >= P.cam.height) continue;
+            s = uint32_t(P.sample_begin + (k - p * n_s));
+            pixel = uint32_t(py) * uint32_t(P.cam.width) + uint32_t(px);
             // ---- K1 raygen: get_ray (camera.hpp:784-794), sample_square (:817), defocus disk (:822)
-            uint4 r0 = ph(pixel, uint32_t(s), 0u, 0u);
-            float3 d = base + (u01(r0.x) - 0.5f) * P.cam.du + (u01(r0.y) - 0.5f) * P.cam.dv;
-            float3 o = P.cam.center;
+            uint4 r0 = ph(pixel, s, 0u, 0u);
+            d = P.cam.pix00_rel + (float(px) + u01(r0.x) - 0.5f) * P.cam.du + (float(py) + u01(r0.y) - 0.5f) * P.cam.dv;
+            o = P.cam.center;
             if (P.cam.defocus) {
                 float rr = sqrtf(u01(r0.z)), sn, cs;
                 sincospif(2.0f * u01(r0.w), &sn, &cs);
@@ -39,62 +79,100 @@ __global__ void __launch_bounds__(ZB_BLOCK_THREADS) k_render(const __grid_consta
                 o += off;
                 d = d - off;
             }
+            seg = 0;
+            L = f3(0, 0, 0);
+            beta = f3(1, 1, 1);
             paths++;
-            float3 L = f3(0, 0, 0), beta = f3(1, 1, 1);
-            for (int seg = 0; seg < P.max_depth; seg++) {
-                MediumRng mr{ph, pixel, uint32_t(s), uint32_t(seg + 1)};
-                Hit hit;
-                if (!trace<STATS>(P.sc, o, d, 0.001f, INFINITY, mr, hit, cnt)) {
-                    L += beta * background(P.sc, P.env, d);
-                    if (seg == 0 && s < P.aux_samples && P.use_normal) s_nrm += f3(0.5f, 0.5f, 1.0f);
-                    break;
+            return true;
+        }
+    };
+
+    bool have = fetch();
+    while (have) {
+        // ---- one segment of ray_color (camera.hpp:928-1004): K2 trace, then K3 shade
+        MediumRng mr{ph, pixel, s, uint32_t(seg + 1)};
+        Hit hit;
+        bool done;
+        if (!trace<STATS>(P.sc, o, d, 0.001f, INFINITY, mr, hit, cnt)) {
+            L += beta * background(P.sc, P.env, d);
+            if (seg == 0 && aux_on && int(s) < P.aux_samples && P.use_normal) {  // camera.hpp:518-526
+                fix_add(&s_aux[warp][p][3], 0.5f);
+                fix_add(&s_aux[warp][p][4], 0.5f);
+                fix_add(&s_aux[warp][p][5], 1.0f);
+            }
+            done = true;
+        } else {
+            Surface sf;
+            make_surface(P.sc, hit, o, d, sf);
+            if (seg == 0 && aux_on && int(s) < P.aux_samples) {  // K8 first-hit AOVs (camera.hpp:464-488)
+                if (P.use_albedo) {
+                    float3 a = material_get_albedo(P.sc, sf);
+                    fix_add(&s_aux[warp][p][0], a.x);
+                    fix_add(&s_aux[warp][p][1], a.y);
+                    fix_add(&s_aux[warp][p][2], a.z);
                 }
-                Surface sf;
-                make_surface(P.sc, hit, o, d, sf);
-                if (seg == 0 && s < P.aux_samples) {
-                    if (P.use_albedo) s_alb += material_get_albedo(P.sc, sf);
-                    if (P.use_normal) {
-                        float3 n = unit_vector(sf.n);
-                        s_nrm += f3((dot(n, P.cam.u) + 1.f) * 0.5f, (dot(n, P.cam.v) + 1.f) * 0.5f, (dot(n, P.cam.w) + 1.f) * 0.5f);
-                    }
-                    if (P.use_z) s_z += 1.0f - clamp01(hit.t * P.inv_z_max);
+                if (P.use_normal) {
+                    float3 n = unit_vector(sf.n);
+                    fix_add(&s_aux[warp][p][3], (dot(n, P.cam.u) + 1.f) * 0.5f);
+                    fix_add(&s_aux[warp][p][4], (dot(n, P.cam.v) + 1.f) * 0.5f);
+                    fix_add(&s_aux[warp][p][5], (dot(n, P.cam.w) + 1.f) * 0.5f);
                 }
-                L += beta * material_emitted(P.sc, sf);
-                uint4 rb = ph(pixel, uint32_t(s), uint32_t(seg + 1), 0u);
-                float3 atten = f3(1, 1, 1), no, nd;
-                if (!material_scatter(P.sc, sf, d, f3(u01(rb.x), u01(rb.y), u01(rb.z)), atten, no, nd)) break;
+                if (P.use_z) fix_add(&s_aux[warp][p][6], 1.0f - clamp01(hit.t * P.inv_z_max));
+            }
+            L += beta * material_emitted(P.sc, sf);
+            uint4 rb = ph(pixel, s, uint32_t(seg + 1), 0u);
+            float3 atten = f3(1, 1, 1), no, nd;
+            done = !material_scatter(P.sc, sf, d, f3(u01(rb.x), u01(rb.y), u01(rb.z)), atten, no, nd);
+            if (!done) {
                 beta *= atten;
                 o = no;
                 d = nd;
                 // ray_color's loop index is seg-1; its `i > 10` rules start at seg 12 (camera.hpp:968-983)
                 if (seg >= 12) {
-                    if (dot(beta, beta) < 1e-8f) break;
-                    float p = fminf(fmaxf(max3(beta.x, beta.y, beta.z), 0.05f), 0.95f);
-                    if (u01(rb.w) > p) break;
-                    beta *= 1.0f / p;
+                    float pr = fminf(fmaxf(max3(beta.x, beta.y, beta.z), 0.05f), 0.95f);
+                    if (dot(beta, beta) < 1e-8f || u01(rb.w) > pr) done = true;
+                    beta *= 1.0f / pr;
                 }
+                if (++seg >= P.max_depth) done = true;  // hard stop keeps the light gathered so far
             }
-            sum += L;
         }
-        float4 acc = make_float4(sum.x, sum.y, sum.z, float(P.sample_end - P.sample_begin));
-        if (P.accumulate) {
-            float4 old = P.accum[pixel];
-            acc.x += old.x; acc.y += old.y; acc.z += old.z; acc.w += old.w;
+        if (done) {
+            fix_add(&s_sum[warp][p][0], L.x);
+            fix_add(&s_sum[warp][p][1], L.y);
+            fix_add(&s_sum[warp][p][2], L.z);
+            have = fetch();
         }
-        P.accum[pixel] = acc;
-        if (P.accum_aux) {
-            const size_t n = size_t(P.cam.width) * P.cam.height;
-            float4 a0 = make_float4(s_alb.x, s_alb.y, s_alb.z, 0.f), a1 = make_float4(s_nrm.x, s_nrm.y, s_nrm.z, 0.f),
-                   a2 = make_float4(s_z, s_z, s_z, 0.f);
+    }
+    __syncwarp();
+
+    // ---- K5 accumulate: lane l writes pixel l of the sub-tile
+    {
+        const int px = px0 + (lane & 7), py = py0 + (lane >> 3);
+        if (px < P.cam.width && py < P.cam.height && ty < P.tiles_y) {
+            const size_t pix = size_t(py) * P.cam.width + px;
+            float4 acc = make_float4(fix_get(s_sum[warp][lane][0]), fix_get(s_sum[warp][lane][1]),
+                                     fix_get(s_sum[warp][lane][2]), float(n_s));
             if (P.accumulate) {
-                float4 b0 = P.accum_aux[pixel], b1 = P.accum_aux[n + pixel], b2 = P.accum_aux[2 * n + pixel];
-                a0.x += b0.x; a0.y += b0.y; a0.z += b0.z;
-                a1.x += b1.x; a1.y += b1.y; a1.z += b1.z;
-                a2.x += b2.x; a2.y += b2.y; a2.z += b2.z;
+                float4 old = P.accum[pix];
+                acc.x += old.x; acc.y += old.y; acc.z += old.z; acc.w += old.w;
             }
-            P.accum_aux[pixel] = a0;
-            P.accum_aux[n + pixel] = a1;
-            P.accum_aux[2 * n + pixel] = a2;
+            P.accum[pix] = acc;
+            if (aux_on) {
+                const size_t n = size_t(P.cam.width) * P.cam.height;
+                float z = fix_get(s_aux[warp][lane][6]);
+                float4 a0 = make_float4(fix_get(s_aux[warp][lane][0]), fix_get(s_aux[warp][lane][1]), fix_get(s_aux[warp][lane][2]), 0.f);
+                float4 a1 = make_float4(fix_get(s_aux[warp][lane][3]), fix_get(s_aux[warp][lane][4]), fix_get(s_aux[warp][lane][5]), 0.f);
+                float4 a2 = make_float4(z, z, z, 0.f);
+                if (P.accumulate) {
+                    float4 b0 = P.accum_aux[pix], b1 = P.accum_aux[n + pix], b2 = P.accum_aux[2 * n + pix];
+                    a0.x += b0.x; a0.y += b0.y; a0.z += b0.z;
+                    a1.x += b1.x; a1.y += b1.y; a1.z += b1.z;
+                    a2.x += b2.x; a2.y += b2.y; a2.z += b2.z;
+                }
+                P.accum_aux[pix] = a0;
+                P.accum_aux[n + pix] = a1;
+                P.accum_aux[2 * n + pix] = a2;
+            }
         }
     }
     // one atomic per warp and counter

@@ -71,3 +71,6 @@ struct RenderParams {
 #define ZB_TILE_W 16
 #define ZB_TILE_H 8
 #define ZB_BLOCK_THREADS (ZB_TILE_W * ZB_TILE_H)
+#ifndef ZB_MIN_BLOCKS
+#define ZB_MIN_BLOCKS 6  // resident blocks per SM the render kernel is compiled for (80 registers; measured best of 3..12)
+#endif

@@ -13,6 +13,7 @@ struct Surface {
     bool front_face;
     uint32_t material;
     uint32_t leaf_id, prim_id;
+    float4 m0, m1;          // the zb_material record of the hit (type, textures, bump | rgb, param)
 };
 
 ZB_DEV float4 load_mat0(const SceneDev& sc, uint32_t m) { return __ldg(sc.materials + 2 * size_t(m)); }
@@ -90,7 +91,10 @@ ZB_DEV void make_surface(const SceneDev& sc, const Hit& hit, float3 o, float3 d,
     sf.prim_id = 0;
     sf.u = sf.v = 0.f;
     sf.tangent = sf.bitangent = f3(0, 0, 0);
-    bool want_uv = true;
+    sf.m0 = load_mat0(sc, sf.material);
+    sf.m1 = load_mat1(sc, sf.material);
+    // sphere uv / tangent frame (sphere.hpp:44-58) feed only texture lookups and bump mapping
+    const bool want_uv = __float_as_uint(sf.m0.y) != ZB_NO_TEXTURE || __float_as_uint(sf.m0.z) != ZB_NO_TEXTURE;
     if (kind == ZB_ITEM_SPHERE) {
         sf.p = fma3(hit.t, d, o);
         sphere_surface(g, sf.p, d, sf, want_uv);
@@ -179,14 +183,13 @@ ZB_DEV float3 random_unit_vector(float x1, float x2) {
 
 // material::emitted (material.hpp:12-14, :261-263)
 ZB_DEV float3 material_emitted(const SceneDev& sc, const Surface& sf) {
-    float4 m0 = load_mat0(sc, sf.material);
-    if (__float_as_uint(m0.x) != ZB_MAT_LIGHT) return f3(0, 0, 0);
-    return material_albedo_tex(sc, m0, load_mat1(sc, sf.material), sf);
+    if (__float_as_uint(sf.m0.x) != ZB_MAT_LIGHT) return f3(0, 0, 0);
+    return material_albedo_tex(sc, sf.m0, sf.m1, sf);
 }
 
 // material::get_albedo (material.hpp:28-30, :98-100, :153-155, :226-228, :265-272)
 ZB_DEV float3 material_get_albedo(const SceneDev& sc, const Surface& sf) {
-    float4 m0 = load_mat0(sc, sf.material), m1 = load_mat1(sc, sf.material);
+    const float4 m0 = sf.m0, m1 = sf.m1;
     uint32_t type = __float_as_uint(m0.x);
     if (type == ZB_MAT_DIELECTRIC) return f3(1, 1, 1);
     if (type == ZB_MAT_ISOTROPIC) return f3(0, 0, 0);
@@ -199,7 +202,7 @@ ZB_DEV float3 material_get_albedo(const SceneDev& sc, const Surface& sf) {
 // ends here (light, absorbed metal sample).
 ZB_DEV bool material_scatter(const SceneDev& sc, const Surface& sf, float3 d_in, float3 xi, float3& atten,
                              float3& o_out, float3& d_out) {
-    float4 m0 = load_mat0(sc, sf.material), m1 = load_mat1(sc, sf.material);
+    const float4 m0 = sf.m0, m1 = sf.m1;
     uint32_t type = __float_as_uint(m0.x);
     const float ray_epsilon = 0.0001f;  // common.hpp:16
     if (type == ZB_MAT_LAMBERTIAN) {  // material.hpp:74-96

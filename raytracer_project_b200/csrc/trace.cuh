@@ -189,6 +189,14 @@ struct RayBox {
     }
 };
 
+// Stack codes: >= 0 inner node, < 0 leaf (~code), and two reserved leaf codes that no real leaf can
+// take (they would need first >= 0x0FFFFFFF): ZB_EXIT_INSTANCE pops the ray back to world space,
+// ZB_TRAVERSAL_DONE is the sentinel at the bottom of the stack.
+#define ZB_TRAVERSAL_DONE ((int)0x80000001)
+
+// "while-while" traversal (Aila & Laine 2009): every lane first descends through inner nodes until it
+// holds a leaf, then the warp runs the primitive tests together; this keeps more lanes on the same
+// instruction than one loop that alternates between a node step and a leaf step per lane.
 template <bool STATS>
 ZB_DEV bool trace(const SceneDev& sc, float3 o, float3 d, float tmin, float tmax, const MediumRng& rng, Hit& hit,
                   Counters& cnt) {
@@ -199,7 +207,8 @@ ZB_DEV bool trace(const SceneDev& sc, float3 o, float3 d, float tmin, float tmax
     if (sc.n_nodes == 0) return false;
 
     int stack[ZB_STACK];
-    int sp = 0;
+    stack[0] = ZB_TRAVERSAL_DONE;
+    int sp = 1;
     int cur = 0;
     bool in_blas = false;
     uint32_t blas_item = 0;
@@ -208,7 +217,7 @@ ZB_DEV bool trace(const SceneDev& sc, float3 o, float3 d, float tmin, float tmax
     rb.set(ro, rd);
 
     for (;;) {
-        if (cur >= 0) {
+        while (cur >= 0) {
             const float4* np = sc.nodes + 4 * size_t(cur);
             float4 n0 = __ldg(np), n1 = __ldg(np + 1), n2 = __ldg(np + 2);
             float4 nc = __ldg(np + 3);
@@ -227,14 +236,19 @@ ZB_DEV bool trace(const SceneDev& sc, float3 o, float3 d, float tmin, float tmax
             int cl = __float_as_int(nc.x), cr = __float_as_int(nc.y);
             if (hl && hr) {
                 bool swap = rn < ln;
-                int nearc = swap ? cr : cl, farc = swap ? cl : cr;
+                int farc = swap ? cl : cr;
+                cur = swap ? cr : cl;
                 if (sp < ZB_STACK) stack[sp++] = farc;
-                cur = nearc;
-                continue;
+            } else if (hl) {
+                cur = cl;
+            } else if (hr) {
+                cur = cr;
+            } else {
+                cur = stack[--sp];
             }
-            if (hl) { cur = cl; continue; }
-            if (hr) { cur = cr; continue; }
-        } else if (cur == ZB_EXIT_INSTANCE) {
+        }
+        if (cur == ZB_TRAVERSAL_DONE) break;
+        if (cur == ZB_EXIT_INSTANCE) {
             in_blas = false;
             ro = o;
             rd = d;
@@ -299,7 +313,6 @@ ZB_DEV bool trace(const SceneDev& sc, float3 o, float3 d, float tmin, float tmax
                 }
             }
         }
-        if (sp == 0) break;
         cur = stack[--sp];
     }
     return hit.item != 0xFFFFFFFFu;

@@ -1,0 +1,49 @@
+#!/usr/bin/env python
+"""Kernel-tuning helper (GPU box): time zb_render_device on a named scene with the library selected by
+ZB_LIB, CUDA events on the context stream, L2 flushed between runs.  Prints one JSON line."""
+import argparse, json, os, sys
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import torch
+from raytracer_project_b200 import api, scenes
+
+ap = argparse.ArgumentParser()
+ap.add_argument("--scene", default="weekend")
+ap.add_argument("--width", type=int, default=1920)
+ap.add_argument("--height", type=int, default=1080)
+ap.add_argument("--spp", type=int, default=64)
+ap.add_argument("--reps", type=int, default=3)
+ap.add_argument("--stats", action="store_true")
+ap.add_argument("--tag", default=os.environ.get("ZB_LIB", "main"))
+a = ap.parse_args()
+gen = getattr(scenes, a.scene)
+out = gen(seed=1, width=a.width, height=a.height, spp=a.spp)
+txt, cfg = out[0], out[1]
+base = out[2] if len(out) > 2 else None
+flat = api.flatten_zscene(txt) if base is None else api.flatten_zscene(path=base)
+dev = torch.device("cuda", 0)
+stream = torch.cuda.current_stream()
+ctx = api.Context(0, stream=stream.cuda_stream)
+sc = ctx.upload(flat)
+n = a.width * a.height
+acc = torch.empty(n, 4, device=dev)
+flush = torch.empty(256 << 20, device=dev, dtype=torch.uint8)
+res = {"tag": a.tag, "scene": a.scene}
+if a.stats:
+    sc.render_device(cfg, acc.data_ptr(), seed=1, stats=True)
+    torch.cuda.synchronize()
+    st = ctx.stats()
+    res.update(rays_per_path=st["rays"] / st["paths"], nodes_per_ray=st["node_visits"] / st["rays"],
+               prims_per_ray=st["prim_tests"] / st["rays"])
+ms = []
+for i in range(a.reps + 1):
+    flush.zero_()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    sc.render_device(cfg, acc.data_ptr(), seed=1)
+    e1.record()
+    torch.cuda.synchronize()
+    if i:
+        ms.append(e0.elapsed_time(e1))
+res.update(ms=min(ms), ms_all=[round(x, 3) for x in ms], mpaths=n * a.spp / min(ms) * 1e-3,
+           mean=[round(x, 6) for x in (acc[:, :3].mean(0) / a.spp).tolist()])
+print(json.dumps(res), flush=True)
