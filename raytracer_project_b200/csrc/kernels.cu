@@ -20,8 +20,16 @@
 #define ZB_FIX_SCALE 4194304.0f
 #define ZB_FIX_INV (1.0 / 4194304.0)
 
+// 64-bit shared-memory add from two native 32-bit atomics (a 64-bit ATOMS add is a CAS spin loop):
+// the low word wraps, and exactly the operation whose addition wrapped it carries one into the high
+// word, so (hi, lo) ends as the exact sum whatever the order.  Radiance is never negative.
 ZB_DEV void fix_add(unsigned long long* slot, float v) {
-    atomicAdd(slot, (unsigned long long)__float2ll_rn(v * ZB_FIX_SCALE));
+    const unsigned long long q = __float2ull_rn(fmaxf(v, 0.f) * ZB_FIX_SCALE);
+    const uint32_t ql = uint32_t(q), qh = uint32_t(q >> 32);
+    uint32_t* w = reinterpret_cast<uint32_t*>(slot);
+    const uint32_t old = atomicAdd(w, ql);
+    const uint32_t up = qh + (old + ql < old ? 1u : 0u);
+    if (up) atomicAdd(w + 1, up);
 }
 ZB_DEV float fix_get(unsigned long long v) { return float(double((long long)v) * ZB_FIX_INV); }
 
@@ -35,7 +43,7 @@ __global__ void __launch_bounds__(ZB_BLOCK_THREADS, ZB_MIN_BLOCKS) k_render(cons
     const int tile = blockIdx.x * P.tile_ranks + P.tile_rank;
     const int tx = tile % P.tiles_x, ty = tile / P.tiles_x;
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int px0 = tx * ZB_TILE_W + (warp & 1) * 8, py0 = ty * ZB_TILE_H + (warp >> 1) * 4;
+    const int px0 = tx * ZB_TILE_W + (warp % (ZB_TILE_W / 8)) * 8, py0 = ty * ZB_TILE_H + (warp / (ZB_TILE_W / 8)) * 4;
     const bool aux_on = P.accum_aux != nullptr;
 
 #pragma unroll
@@ -87,60 +95,68 @@ __global__ void __launch_bounds__(ZB_BLOCK_THREADS, ZB_MIN_BLOCKS) k_render(cons
         }
     };
 
+    // Main loop: one iteration = one path segment of this lane (trace to completion, then shade).
+    // Leaving the traversal early to refill finished lanes (Aila & Laine's ray-level persistence) was
+    // measured and lost 7-40 % on this kernel: shading under a partial warp costs more than it saves.
     bool have = fetch();
     while (have) {
-        // ---- one segment of ray_color (camera.hpp:928-1004): K2 trace, then K3 shade
-        MediumRng mr{ph, pixel, s, uint32_t(seg + 1)};
         Hit hit;
-        bool done;
-        if (!trace<STATS>(P.sc, o, d, 0.001f, INFINITY, mr, hit, cnt)) {
-            L += beta * background(P.sc, P.env, d);
-            if (seg == 0 && aux_on && int(s) < P.aux_samples && P.use_normal) {  // camera.hpp:518-526
-                fix_add(&s_aux[warp][p][3], 0.5f);
-                fix_add(&s_aux[warp][p][4], 0.5f);
-                fix_add(&s_aux[warp][p][5], 1.0f);
-            }
-            done = true;
-        } else {
-            Surface sf;
-            make_surface(P.sc, hit, o, d, sf);
-            if (seg == 0 && aux_on && int(s) < P.aux_samples) {  // K8 first-hit AOVs (camera.hpp:464-488)
-                if (P.use_albedo) {
-                    float3 a = material_get_albedo(P.sc, sf);
-                    fix_add(&s_aux[warp][p][0], a.x);
-                    fix_add(&s_aux[warp][p][1], a.y);
-                    fix_add(&s_aux[warp][p][2], a.z);
-                }
-                if (P.use_normal) {
-                    float3 n = unit_vector(sf.n);
-                    fix_add(&s_aux[warp][p][3], (dot(n, P.cam.u) + 1.f) * 0.5f);
-                    fix_add(&s_aux[warp][p][4], (dot(n, P.cam.v) + 1.f) * 0.5f);
-                    fix_add(&s_aux[warp][p][5], (dot(n, P.cam.w) + 1.f) * 0.5f);
-                }
-                if (P.use_z) fix_add(&s_aux[warp][p][6], 1.0f - clamp01(hit.t * P.inv_z_max));
-            }
-            L += beta * material_emitted(P.sc, sf);
-            uint4 rb = ph(pixel, s, uint32_t(seg + 1), 0u);
-            float3 atten = f3(1, 1, 1), no, nd;
-            done = !material_scatter(P.sc, sf, d, f3(u01(rb.x), u01(rb.y), u01(rb.z)), atten, no, nd);
-            if (!done) {
-                beta *= atten;
-                o = no;
-                d = nd;
-                // ray_color's loop index is seg-1; its `i > 10` rules start at seg 12 (camera.hpp:968-983)
-                if (seg >= 12) {
-                    float pr = fminf(fmaxf(max3(beta.x, beta.y, beta.z), 0.05f), 0.95f);
-                    if (dot(beta, beta) < 1e-8f || u01(rb.w) > pr) done = true;
-                    beta *= 1.0f / pr;
-                }
-                if (++seg >= P.max_depth) done = true;  // hard stop keeps the light gathered so far
-            }
+        {
+            MediumRng mr{ph, pixel, s, uint32_t(seg + 1)};
+            trace<STATS>(P.sc, o, d, 0.001f, INFINITY, mr, hit, cnt);
         }
-        if (done) {
-            fix_add(&s_sum[warp][p][0], L.x);
-            fix_add(&s_sum[warp][p][1], L.y);
-            fix_add(&s_sum[warp][p][2], L.z);
-            have = fetch();
+        {
+            // ---- K3 shade: one segment of ray_color (camera.hpp:928-1004)
+            bool done;
+            if (hit.item == 0xFFFFFFFFu) {
+                L += beta * background(P.sc, P.env, d);
+                if (seg == 0 && aux_on && int(s) < P.aux_samples && P.use_normal) {  // camera.hpp:518-526
+                    fix_add(&s_aux[warp][p][3], 0.5f);
+                    fix_add(&s_aux[warp][p][4], 0.5f);
+                    fix_add(&s_aux[warp][p][5], 1.0f);
+                }
+                done = true;
+            } else {
+                Surface sf;
+                make_surface(P.sc, hit, o, d, sf);
+                if (seg == 0 && aux_on && int(s) < P.aux_samples) {  // K8 first-hit AOVs (camera.hpp:464-488)
+                    if (P.use_albedo) {
+                        float3 a = material_get_albedo(P.sc, sf);
+                        fix_add(&s_aux[warp][p][0], a.x);
+                        fix_add(&s_aux[warp][p][1], a.y);
+                        fix_add(&s_aux[warp][p][2], a.z);
+                    }
+                    if (P.use_normal) {
+                        float3 n = unit_vector(sf.n);
+                        fix_add(&s_aux[warp][p][3], (dot(n, P.cam.u) + 1.f) * 0.5f);
+                        fix_add(&s_aux[warp][p][4], (dot(n, P.cam.v) + 1.f) * 0.5f);
+                        fix_add(&s_aux[warp][p][5], (dot(n, P.cam.w) + 1.f) * 0.5f);
+                    }
+                    if (P.use_z) fix_add(&s_aux[warp][p][6], 1.0f - clamp01(hit.t * P.inv_z_max));
+                }
+                L += beta * material_emitted(P.sc, sf);
+                uint4 rb = ph(pixel, s, uint32_t(seg + 1), 0u);
+                float3 atten = f3(1, 1, 1), no, nd;
+                done = !material_scatter(P.sc, sf, d, f3(u01(rb.x), u01(rb.y), u01(rb.z)), atten, no, nd);
+                if (!done) {
+                    beta *= atten;
+                    o = no;
+                    d = nd;
+                    // ray_color's loop index is seg-1; its `i > 10` rules start at seg 12 (camera.hpp:968-983)
+                    if (seg >= 12) {
+                        float pr = fminf(fmaxf(max3(beta.x, beta.y, beta.z), 0.05f), 0.95f);
+                        if (dot(beta, beta) < 1e-8f || u01(rb.w) > pr) done = true;
+                        beta *= 1.0f / pr;
+                    }
+                    if (++seg >= P.max_depth) done = true;  // hard stop keeps the light gathered so far
+                }
+            }
+            if (done) {
+                fix_add(&s_sum[warp][p][0], L.x);
+                fix_add(&s_sum[warp][p][1], L.y);
+                fix_add(&s_sum[warp][p][2], L.z);
+                have = fetch();
+            }
         }
     }
     __syncwarp();

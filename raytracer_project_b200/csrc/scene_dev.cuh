@@ -68,8 +68,10 @@ struct RenderParams {
     int pad;
 };
 
-#define ZB_TILE_W 16
+#ifndef ZB_TILE_W
+#define ZB_TILE_W 16  // block tile in pixels: (ZB_TILE_W/8) x (ZB_TILE_H/4) warps of 8x4 pixels each
 #define ZB_TILE_H 8
+#endif
 #define ZB_BLOCK_THREADS (ZB_TILE_W * ZB_TILE_H)
 #ifndef ZB_MIN_BLOCKS
 #define ZB_MIN_BLOCKS 6  // resident blocks per SM the render kernel is compiled for (80 registers; measured best of 3..12)
