@@ -131,7 +131,7 @@ def ours(args):
     import torch
     import torch.distributed as dist
 
-    from raytracer_project_b200 import api, scenes
+    from raytracer_project_b200 import api, partition, scenes
 
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -154,15 +154,14 @@ def ours(args):
     n_pix = WIDTH * HEIGHT
     paths_per_step = n_pix * SPP
     # sample slices: rank g renders samples [g*spp/n, (g+1)*spp/n) of the whole frame
-    s0, s1 = rank * SPP // world, (rank + 1) * SPP // world
+    s0, s1 = partition.sample_slice(rank, world, SPP)
     accum = torch.empty(n_pix, 4, device=dev, dtype=torch.float32)
     out_f4 = torch.empty(n_pix, 4, device=dev, dtype=torch.float32)
     flush = torch.empty(256 * 1024 * 1024, device=dev, dtype=torch.uint8)  # > 126 MB L2
 
     def step_device():
         scene.render_device(cfg, accum.data_ptr(), seed=1, sample_range=(s0, s1))
-        if world > 1:
-            dist.reduce(accum, dst=0, op=dist.ReduceOp.SUM)
+        partition.combine(accum, dst=0)
         if rank == 0:
             api.check(ctx.lib.zb_resolve_device(ctx.h, accum.data_ptr(), n_pix, 1.0 / SPP, out_f4.data_ptr(), None))
 
@@ -197,8 +196,7 @@ def ours(args):
         ev[k][0].record()
         scene.render_device(cfg, accum.data_ptr(), seed=1, sample_range=(s0, s1))
         ev[k][1].record()
-        if world > 1:
-            dist.reduce(accum, dst=0, op=dist.ReduceOp.SUM)
+        partition.combine(accum, dst=0)
         if rank == 0:
             api.check(ctx.lib.zb_resolve_device(ctx.h, accum.data_ptr(), n_pix, 1.0 / SPP, out_f4.data_ptr(), None))
         ev[k][2].record()
@@ -229,7 +227,7 @@ def ours(args):
             checksum = float(res["beauty"][HEIGHT // 2, WIDTH // 2, 0])
         else:
             sc2.render_device(cfg, accum.data_ptr(), seed=1, sample_range=(s0, s1))
-            dist.reduce(accum, dst=0, op=dist.ReduceOp.SUM)
+            partition.combine(accum, dst=0)
             if rank == 0:
                 api.check(ctx.lib.zb_resolve_device(ctx.h, accum.data_ptr(), n_pix, 1.0 / SPP, None, out_f64.data_ptr()))
                 pinned.copy_(out_f64, non_blocking=True)

@@ -33,7 +33,9 @@ int load(std::istream& in, const std::string& base_dir, const zb_flat_scene** ou
         ld.parse(in);
         std::shared_ptr<hittable> world = ld.build_world();
         flattener fl;
-        std::unique_ptr<flat_scene> fs = fl.run(*world, nullptr);
+        EnvironmentSettings env;
+        if (!ld.env_hdr_path.empty()) env.load_hdr(ld.path_of(ld.env_hdr_path));  // environment.hpp:46-69
+        std::unique_ptr<flat_scene> fs = fl.run(*world, &env);
         const zb_flat_scene* view = &fs->view;
         std::lock_guard<std::mutex> lock(g_mu);
         g_live[view] = std::move(fs);

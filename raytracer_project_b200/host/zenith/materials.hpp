@@ -43,9 +43,10 @@ public:
 };
 
 // image_texture(filename, is_hdr) texture.hpp:14-43.  The reference decodes JPG/PNG/HDR with the
-// stb_image it vendors; this host reads the decoded texels from a ".zbtex" raw dump
-// ("ZBTX" u32 width u32 height u32 is_float, then RGB8 or RGB32F rows, top row first) so both sides
-// see identical bytes (the oracle harness writes the dumps with the reference's own decoder).
+// stb_image it vendors; this host decodes Radiance .hdr itself and reads everything else from a
+// ".zbtex" raw dump ("ZBTX" u32 width u32 height u32 is_float, then RGB8 or RGB32F rows, top row
+// first) so both sides see identical bytes (the oracle harness writes the dumps with the reference's
+// own decoder; raytracer_project_b200/ztex.py writes them from numpy arrays).
 // A file that cannot be read gives the reference's "missing" texture (cyan, texture.hpp:52-54).
 class image_texture : public texture {
 public:
@@ -60,34 +61,105 @@ public:
     std::vector<float> f32;
 
 private:
+    // "NAME.zbtex" beside the image wins (same texels as the oracle's decoder); a file that is itself a
+    // ZBTX dump is read directly; Radiance .hdr files are decoded natively (RGBE, flat or RLE scanlines,
+    // value = mantissa * 2^(E-136) as stb_image does); anything else is "missing".
     void load(const char* filename) {
         std::string path(filename);
+        if (read_zbtex(path + ".zbtex") || read_zbtex(path) || read_radiance_hdr(path)) return;
+        std::cerr << "ERROR: Could not load texture (need a .zbtex dump or a Radiance .hdr): " << filename << "\n";
+        width = height = 0;
+    }
+
+    bool read_zbtex(const std::string& path) {
         FILE* f = std::fopen(path.c_str(), "rb");
-        if (!f) {
-            path += ".zbtex";
-            f = std::fopen(path.c_str(), "rb");
-        }
+        if (!f) return false;
         uint32_t hdr[4] = {0, 0, 0, 0};
-        if (!f || std::fread(hdr, 4, 4, f) != 4 || std::memcmp(&hdr[0], "ZBTX", 4) != 0) {
-            if (f) std::fclose(f);
-            std::cerr << "ERROR: Could not load texture (need a .zbtex dump): " << filename << "\n";
-            width = height = 0;
-            return;
-        }
-        width = int(hdr[1]);
-        height = int(hdr[2]);
-        is_float = hdr[3] != 0;
-        size_t n = size_t(width) * height * 3;
-        bool ok;
-        if (is_float) {
-            f32.resize(n);
-            ok = std::fread(f32.data(), 4, n, f) == n;
-        } else {
-            u8.resize(n);
-            ok = std::fread(u8.data(), 1, n, f) == n;
+        bool ok = std::fread(hdr, 4, 4, f) == 4 && std::memcmp(&hdr[0], "ZBTX", 4) == 0 && hdr[1] > 0 && hdr[2] > 0;
+        if (ok) {
+            width = int(hdr[1]);
+            height = int(hdr[2]);
+            is_float = hdr[3] != 0;
+            size_t n = size_t(width) * height * 3;
+            if (is_float) {
+                f32.resize(n);
+                ok = std::fread(f32.data(), 4, n, f) == n;
+            } else {
+                u8.resize(n);
+                ok = std::fread(u8.data(), 1, n, f) == n;
+            }
         }
         std::fclose(f);
-        if (!ok) width = height = 0;
+        if (!ok) { width = height = 0; u8.clear(); f32.clear(); }
+        return ok;
+    }
+
+    bool read_radiance_hdr(const std::string& path) {
+        FILE* f = std::fopen(path.c_str(), "rb");
+        if (!f) return false;
+        auto line = [&](std::string& out) {
+            out.clear();
+            int c;
+            while ((c = std::fgetc(f)) != EOF && c != '\n') out.push_back(char(c));
+            return c != EOF || !out.empty();
+        };
+        std::string l;
+        bool ok = line(l) && (l == "#?RADIANCE" || l == "#?RGBE"), fmt = false;
+        while (ok && line(l) && !l.empty())
+            if (l == "FORMAT=32-bit_rle_rgbe") fmt = true;
+        int w = 0, h = 0;
+        ok = ok && fmt && line(l) && std::sscanf(l.c_str(), "-Y %d +X %d", &h, &w) == 2 && w > 0 && h > 0;
+        std::vector<uint8_t> rgbe;
+        if (ok) {
+            rgbe.resize(size_t(w) * h * 4);
+            std::vector<uint8_t> rest;
+            int c;
+            while ((c = std::fgetc(f)) != EOF) rest.push_back(uint8_t(c));
+            size_t at = 0;
+            auto need = [&](size_t n) { return at + n <= rest.size(); };
+            bool flat = w < 8 || w >= 32768;
+            for (int y = 0; ok && y < h && !flat; y++) {
+                if (!need(4)) { ok = false; break; }
+                if (rest[at] != 2 || rest[at + 1] != 2 || (rest[at + 2] & 0x80)) {
+                    if (y == 0) flat = true; else ok = false;
+                    break;
+                }
+                if (((int(rest[at + 2]) << 8) | rest[at + 3]) != w) { ok = false; break; }
+                at += 4;
+                for (int k = 0; ok && k < 4; k++) {
+                    int x = 0;
+                    while (ok && x < w) {
+                        if (!need(1)) { ok = false; break; }
+                        int count = rest[at++];
+                        if (count > 128) {
+                            count -= 128;
+                            if (!need(1) || x + count > w) { ok = false; break; }
+                            uint8_t v = rest[at++];
+                            for (int z = 0; z < count; z++) rgbe[(size_t(y) * w + x++) * 4 + k] = v;
+                        } else {
+                            if (count == 0 || !need(size_t(count)) || x + count > w) { ok = false; break; }
+                            for (int z = 0; z < count; z++) rgbe[(size_t(y) * w + x++) * 4 + k] = rest[at++];
+                        }
+                    }
+                }
+            }
+            if (ok && flat) {
+                ok = rest.size() >= rgbe.size();
+                if (ok) std::memcpy(rgbe.data(), rest.data(), rgbe.size());
+            }
+        }
+        std::fclose(f);
+        if (!ok) return false;
+        width = w;
+        height = h;
+        is_float = true;
+        f32.resize(size_t(w) * h * 3);
+        for (size_t i = 0; i < size_t(w) * h; i++) {
+            const uint8_t* px = &rgbe[4 * i];
+            float s = px[3] ? std::ldexp(1.0f, int(px[3]) - 136) : 0.0f;
+            for (int k = 0; k < 3; k++) f32[3 * i + k] = px[3] ? float(px[k]) * s : 0.0f;
+        }
+        return true;
     }
 };
 

@@ -23,6 +23,7 @@
 //   obj  NAME medium CHILD DENSITY (color R G B | tex TEX)
 //   obj  NAME list CHILD...                       obj NAME bvh CHILD...
 //   world NAME
+//   envmap PATH                                   (lat-long HDRI for EnvironmentSettings::load_hdr)
 // Objects are built on demand from `world` in DFS order; non-container objects are built once and
 // shared (DAG).  ZSCENE_TAG(object, leaf_id) is applied at every site where a non-container object
 // is added to a container — the oracle harness uses it to wrap the object in an id recorder; the
@@ -52,6 +53,7 @@ public:
     std::map<std::string, std::shared_ptr<texture>> textures;
     std::map<std::string, std::shared_ptr<material>> materials;
     std::string base_dir;  // prefix for relative asset paths
+    std::string env_hdr_path;  // `envmap PATH`: the HDRI handed to EnvironmentSettings::load_hdr by the caller
     int next_leaf_id = 0;
 
     void parse(std::istream& in) {
@@ -68,6 +70,8 @@ public:
             if (tok.empty()) continue;
             if (tok[0] == "world" && tok.size() == 2) {
                 world_name = tok[1];
+            } else if (tok[0] == "envmap" && tok.size() == 2) {
+                env_hdr_path = tok[1];
             } else if ((tok[0] == "tex" || tok[0] == "mat" || tok[0] == "obj") && tok.size() >= 3) {
                 record r;
                 r.type = tok[2];
@@ -79,6 +83,11 @@ public:
                 throw std::runtime_error("zscene: bad record at line " + std::to_string(lineno));
             }
         }
+    }
+
+    std::string path_of(const std::string& p) const {
+        if (p.empty() || p[0] == '/' || base_dir.empty()) return p;
+        return base_dir + "/" + p;
     }
 
     std::shared_ptr<hittable> build_world() {
@@ -102,10 +111,6 @@ private:
         return r.args[i];
     }
     static vec3 v3(const record& r, size_t i) { return vec3(num(arg(r, i)), num(arg(r, i + 1)), num(arg(r, i + 2))); }
-    std::string path_of(const std::string& p) const {
-        if (p.empty() || p[0] == '/' || base_dir.empty()) return p;
-        return base_dir + "/" + p;
-    }
     std::shared_ptr<texture> tex(const std::string& n) const {
         auto it = textures.find(n);
         if (it == textures.end()) throw std::runtime_error("zscene: unknown texture " + n);

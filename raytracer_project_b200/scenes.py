@@ -140,23 +140,23 @@ class SceneWriter:
 
     def sphere(self, c, r, mat, name=None):
         name = name or self._name("o")
-        self.lines.append(f"obj {name} sphere {_f(c[0])} {_f(c[1])} {_f(c[2])} {_f(r)} {mat}")
+        self.lines.append(f"obj {name} sphere {_f(c[0])} {_f(c[1])} {_f(c[2])} {_f(r)} {mat or 'null'}")
         return name
 
     def cube(self, lo, hi, mat, name=None):
         name = name or self._name("o")
-        self.lines.append(f"obj {name} cube {' '.join(_f(x) for x in lo)} {' '.join(_f(x) for x in hi)} {mat}")
+        self.lines.append(f"obj {name} cube {' '.join(_f(x) for x in lo)} {' '.join(_f(x) for x in hi)} {mat or 'null'}")
         return name
 
     def cube1(self, c, mat, name=None):
         name = name or self._name("o")
-        self.lines.append(f"obj {name} cube1 {' '.join(_f(x) for x in c)} {mat}")
+        self.lines.append(f"obj {name} cube1 {' '.join(_f(x) for x in c)} {mat or 'null'}")
         return name
 
     def triangle(self, a, b, c, n0, n1, n2, mat, name=None):
         name = name or self._name("o")
         nums = " ".join(_f(x) for v in (a, b, c, n0, n1, n2) for x in v)
-        self.lines.append(f"obj {name} triangle {nums} {mat}")
+        self.lines.append(f"obj {name} triangle {nums} {mat or 'null'}")
         return name
 
     def translate(self, child, d, name=None):
@@ -233,3 +233,277 @@ def weekend(seed: int = 1, width: int = 1200, height: int = 675, spp: int = 10, 
         lookfrom=(13.0, 2.0, 3.0), lookat=(0.0, 0.0, 0.0), vup=(0.0, 1.0, 0.0), defocus_angle=0.6, focus_dist=10.0,
         env_mode="solid", background=(0.7, 0.8, 1.0), env_intensity=1.0)
     return w.text(), cfg
+
+
+def materialize(directory: str, text: str, cfg: RenderConfig, files: dict | None = None):
+    """Write `s.zscene`, `s.cfg` and the scene's asset files into `directory`; returns the zscene path."""
+    import os
+    os.makedirs(directory, exist_ok=True)
+    for rel, data in (files or {}).items():
+        path = os.path.join(directory, rel)
+        os.makedirs(os.path.dirname(path) or directory, exist_ok=True)
+        with open(path, "wb" if isinstance(data, (bytes, bytearray)) else "w") as f:
+            f.write(data)
+    with open(os.path.join(directory, "s.zscene"), "w") as f:
+        f.write(text)
+    with open(os.path.join(directory, "s.cfg"), "w") as f:
+        f.write(cfg.to_text())
+    return os.path.join(directory, "s.zscene")
+
+
+def _quad(w: SceneWriter, p0, p1, p2, p3, n, mat):
+    """A quad as the two triangles the reference needs (it has no quad primitive)."""
+    return [w.triangle(p0, p1, p2, n, n, n, mat), w.triangle(p0, p2, p3, n, n, n, mat)]
+
+
+def cornell(seed: int = 2, width: int = 1920, height: int = 1080, spp: int = 256, max_depth: int = 50, fog: bool = True):
+    """C2: 555^3 Cornell room from triangle pairs, two translate(rotate_y(cube)) boxes
+    (rotate_y takes RADIANS, Appendix A q3), a 130x105 diffuse_light(15) patch, and a sphere-bounded
+    constant_medium (density 0.002) kept BESIDE the bvh_node in a list root (Appendix A q5, q6)."""
+    w = SceneWriter()
+    red, white, green = w.lambertian((0.65, 0.05, 0.05)), w.lambertian((0.73, 0.73, 0.73)), w.lambertian((0.12, 0.45, 0.15))
+    light = w.light((15.0, 15.0, 15.0))
+    objs = []
+    objs += _quad(w, (555, 0, 0), (555, 555, 0), (555, 555, 555), (555, 0, 555), (-1, 0, 0), green)
+    objs += _quad(w, (0, 0, 0), (0, 0, 555), (0, 555, 555), (0, 555, 0), (1, 0, 0), red)
+    objs += _quad(w, (0, 0, 0), (555, 0, 0), (555, 0, 555), (0, 0, 555), (0, 1, 0), white)
+    objs += _quad(w, (0, 555, 0), (0, 555, 555), (555, 555, 555), (555, 555, 0), (0, -1, 0), white)
+    objs += _quad(w, (0, 0, 555), (555, 0, 555), (555, 555, 555), (0, 555, 555), (0, 0, -1), white)
+    objs += _quad(w, (213, 554, 227), (343, 554, 227), (343, 554, 332), (213, 554, 332), (0, -1, 0), light)
+    box1 = w.cube((-82.5, -82.5, -82.5), (82.5, 82.5, 82.5), white)
+    objs.append(w.translate(w.rotate("y", box1, math.radians(-18.0)), (212.5, 82.5, 147.5)))
+    box2 = w.cube((-82.5, -165.0, -82.5), (82.5, 165.0, 82.5), white)
+    objs.append(w.translate(w.rotate("y", box2, math.radians(15.0)), (347.5, 165.0, 377.5)))
+    root = [w.container("bvh", objs, name="room")]
+    if fog:
+        boundary = w.sphere((278, 278, 278), 400.0, white)
+        root.append(w.medium(boundary, 0.002, rgb=(1.0, 1.0, 1.0)))
+    w.world(w.container("list", root, name="world"))
+    cfg = RenderConfig(
+        image_width=width, image_height=height, samples_per_pixel=spp, max_depth=max_depth, vfov=40.0,
+        lookfrom=(278.0, 278.0, -800.0), lookat=(278.0, 278.0, 0.0), vup=(0.0, 1.0, 0.0), defocus_angle=0.0,
+        focus_dist=10.0, env_mode="solid", background=(0.0, 0.0, 0.0), env_intensity=1.0)
+    return w.text(), cfg, {}
+
+
+def _heightfield_obj(n: int, seed: int) -> str:
+    """n x n vertices over [-5,5]^2, y = .3 sin(3x) cos(3z) + .05 noise, analytic vertex normals."""
+    import numpy as np
+    rng = np.random.default_rng(seed)
+    xs = np.linspace(-5.0, 5.0, n)
+    x, z = np.meshgrid(xs, xs, indexing="ij")
+    y = 0.3 * np.sin(3 * x) * np.cos(3 * z) + 0.05 * rng.random((n, n))
+    dydx, dydz = 0.9 * np.cos(3 * x) * np.cos(3 * z), -0.9 * np.sin(3 * x) * np.sin(3 * z)
+    nrm = np.stack([-dydx, np.ones_like(y), -dydz], axis=-1)
+    nrm /= np.linalg.norm(nrm, axis=-1, keepdims=True)
+    v = np.stack([x, y, z], axis=-1).reshape(-1, 3)
+    out = ["# synthetic heightfield"]
+    out += ["v %.6f %.6f %.6f" % tuple(r) for r in v]
+    out += ["vn %.6f %.6f %.6f" % tuple(r) for r in nrm.reshape(-1, 3)]
+    i, j = np.meshgrid(np.arange(n - 1), np.arange(n - 1), indexing="ij")
+    a = (i * n + j + 1).ravel()  # 1-based
+    b, c, d = a + n, a + n + 1, a + 1
+    f1 = np.stack([a, d, c], axis=1)  # counter-clockwise seen from +y
+    f2 = np.stack([a, c, b], axis=1)
+    faces = np.concatenate([f1, f2], axis=0)
+    out += ["f %d//%d %d//%d %d//%d" % (r[0], r[0], r[1], r[1], r[2], r[2]) for r in faces]
+    return "\n".join(out) + "\n"
+
+
+def _torus_obj(nu: int = 48, nv: int = 24, R: float = 1.0, r: float = 0.35) -> str:
+    import numpy as np
+    u = np.linspace(0, 2 * np.pi, nu, endpoint=False)
+    v = np.linspace(0, 2 * np.pi, nv, endpoint=False)
+    uu, vv = np.meshgrid(u, v, indexing="ij")
+    p = np.stack([(R + r * np.cos(vv)) * np.cos(uu), r * np.sin(vv), (R + r * np.cos(vv)) * np.sin(uu)], -1).reshape(-1, 3)
+    nn = np.stack([np.cos(vv) * np.cos(uu), np.sin(vv), np.cos(vv) * np.sin(uu)], -1).reshape(-1, 3)
+    out = ["# synthetic torus"]
+    out += ["v %.6f %.6f %.6f" % tuple(x) for x in p]
+    out += ["vn %.6f %.6f %.6f" % tuple(x) for x in nn]
+    for i in range(nu):
+        for j in range(nv):
+            a, b = i * nv + j + 1, ((i + 1) % nu) * nv + j + 1
+            c, d = ((i + 1) % nu) * nv + (j + 1) % nv + 1, i * nv + (j + 1) % nv + 1
+            out.append(f"f {a}//{a} {d}//{d} {c}//{c}")
+            out.append(f"f {a}//{a} {c}//{c} {b}//{b}")
+    return "\n".join(out) + "\n"
+
+
+def mesh(seed: int = 3, width: int = 1920, height: int = 1080, spp: int = 64, max_depth: int = 50, grid: int = 708,
+         knots: int = 12):
+    """C3: an OBJ heightfield of 2 (grid-1)^2 triangles (grid 708 -> 999 698) loaded by
+    model(path, nullptr, 1.0) under a material_instance, plus `knots` instances of one shared torus OBJ as
+    translate(rotate_y(scale(model))) with library-style materials (scene_management.hpp:57-99)."""
+    rng = random.Random(seed)
+    w = SceneWriter()
+    files = {"heightfield.obj": _heightfield_obj(grid, seed), "torus.obj": _torus_obj()}
+    ground = w.lambertian((0.45, 0.55, 0.35))
+    objs = [w.matinst(w.model("heightfield.obj", None, 1.0), ground)]
+    checker = w.tex_checker(0.5, w.tex_solid((0.1, 0.1, 0.1)), w.tex_solid((0.9, 0.9, 0.9)))
+    mats = [w.metal((1.0, 0.8, 0.4), 0.0), w.dielectric(1.5), w.metal((0.89, 0.58, 0.51), 0.2),
+            w.light((0.0, 2.0, 4.0)), w.metal(tex=checker, fuzz=0.95), w.lambertian((0.8, 0.1, 0.1))]
+    torus = w.model("torus.obj", None, 1.0)
+    for k in range(knots):
+        ang = 2 * math.pi * k / max(knots, 1)
+        rad = 2.2 + 1.6 * rng.random()
+        s = 0.35 + 0.4 * rng.random()
+        inst = w.rotate("y", w.scale(torus, (s, s * (0.7 + 0.6 * rng.random()), s)), rng.random() * math.pi)
+        inst = w.matinst(inst, mats[k % len(mats)])
+        objs.append(w.translate(inst, (rad * math.cos(ang), 0.9 + 0.8 * rng.random(), rad * math.sin(ang))))
+    w.world(w.container("bvh", objs, name="world"))
+    cfg = RenderConfig(
+        image_width=width, image_height=height, samples_per_pixel=spp, max_depth=max_depth, vfov=40.0,
+        lookfrom=(8.0, 5.0, 8.0), lookat=(0.0, 0.0, 0.0), vup=(0.0, 1.0, 0.0), defocus_angle=0.0, focus_dist=10.0,
+        env_mode="solid", background=(0.7, 0.8, 1.0), env_intensity=1.0)
+    return w.text(), cfg, files
+
+
+def _sky_hdr(width: int = 2048, height: int = 1024):
+    """Synthetic lat-long sky: vertical gradient + a 1-degree-radius sun of radiance 5e4."""
+    import numpy as np
+    v = (np.arange(height) + 0.5) / height           # 0 = +y (zenith) ... 1 = -y, as texture.hpp:50-78 indexes it
+    u = (np.arange(width) + 0.5) / width
+    theta, phi = np.pi * v[:, None], 2 * np.pi * u[None, :] - np.pi
+    d = np.stack([np.sin(theta) * np.cos(phi), np.cos(theta) * np.ones_like(phi), np.sin(theta) * np.sin(phi)], -1)
+    up = np.clip(d[..., 1], 0.0, 1.0)[..., None]
+    sky = (1.0 - up) * np.array([0.9, 0.95, 1.0]) + up * np.array([0.25, 0.45, 0.95])
+    sky = np.where(d[..., 1:2] < 0.0, np.array([0.12, 0.11, 0.10]), sky)
+    sun = np.array([0.5, 0.6, -0.62])
+    sun /= np.linalg.norm(sun)
+    cosang = (d * sun).sum(-1, keepdims=True)
+    sky = np.where(cosang > math.cos(math.radians(1.0)), np.array([5.0e4, 4.6e4, 4.0e4]), sky)
+    return sky.astype(np.float32)
+
+
+def _noise_tex(size: int, seed: int, octaves: int = 4, channels: int = 1):
+    """Smooth value noise in [0, 255] as an (size, size, 3) uint8 image (bump / albedo source)."""
+    import numpy as np
+    rng = np.random.default_rng(seed)
+    img = np.zeros((size, size, channels))
+    amp, total = 1.0, 0.0
+    for o in range(octaves):
+        n = 4 << o
+        g = rng.random((n + 1, n + 1, channels))
+        g[-1], g[:, -1] = g[0], g[:, 0]  # tile in u and v
+        t = np.arange(size) * n / size
+        i = t.astype(int)
+        f = (t - i)[:, None]
+        f = f * f * (3 - 2 * f)
+        rows = g[i] * (1 - f[..., None]) + g[i + 1] * f[..., None]           # (size, n+1, c)
+        fc = (t - i)[None, :, None]
+        fc = fc * fc * (3 - 2 * fc)
+        img += amp * (rows[:, i] * (1 - fc) + rows[:, i + 1] * fc)
+        total += amp
+        amp *= 0.5
+    img = np.clip(img / total, 0, 1)
+    if channels == 1:
+        img = np.repeat(img, 3, axis=2)
+    return (img * 255.0 + 0.5).astype(np.uint8)
+
+
+def exterior(seed: int = 4, width: int = 1920, height: int = 1080, spp: int = 128, max_depth: int = 50, small: int = 200,
+             hdr_size: int = 2048):
+    """C4: HDRI-lit exterior with thin-lens DOF (defocus_angle 3.0, focus_dist 9.0):
+    r=1000 ground with a reflective checker metal, bump-mapped mirror / gold / wood spheres, a bumpy-glass
+    2x2x2 cube, and `small` instanced cubes/spheres built exactly like the reference's demo grid
+    translate(material_instance(rotate_y?(scale(master)))) (scene_management.hpp:139-203).  Textures are
+    synthetic (the reference's JPGs cannot travel); every image exists as PNG/HDR for the reference's
+    stb_image and as .zbtex for the host, with identical texels (ztex.py)."""
+    from . import ztex
+    rng = random.Random(seed)
+    w = SceneWriter()
+    files = {}
+    files.update(ztex.ldr_pair("scratches.png", _noise_tex(512, seed * 10 + 1, octaves=6)))
+    files.update(ztex.ldr_pair("woodbump.png", _noise_tex(512, seed * 10 + 2, octaves=3)))
+    files.update(ztex.ldr_pair("concrete.png", _noise_tex(256, seed * 10 + 3, octaves=5)))
+    files.update(ztex.ldr_pair("wood.png", _noise_tex(512, seed * 10 + 4, octaves=4, channels=3)))
+    files.update(ztex.hdr_pair("sky.hdr", _sky_hdr(hdr_size, hdr_size // 2)))
+    scratches, woodbump, concrete = (w.tex_image(n) for n in ("scratches.png", "woodbump.png", "concrete.png"))
+    wood = w.tex_image("wood.png")
+    checker = w.tex_checker(0.5, w.tex_solid((0.1, 0.1, 0.1)), w.tex_solid((0.9, 0.9, 0.9)))
+    objs = [w.matinst(w.sphere((0, -1000, 0), 1000.0, None), w.metal(tex=checker, fuzz=0.02))]
+    objs.append(w.translate(w.matinst(w.sphere((0, 0, 0), 1.0, None), w.metal((1, 1, 1), 0.0, bump=scratches, strength=1.0)), (0, 1, 0)))
+    objs.append(w.translate(w.matinst(w.sphere((0, 0, 0), 0.5, None), w.metal((1.0, 0.8, 0.4), 0.0, bump=scratches, strength=-1.0)), (2.0, 0.5, 1.5)))
+    objs.append(w.translate(w.matinst(w.sphere((0, 0, 0), 0.5, None), w.lambertian(tex=wood, bump=woodbump, strength=8.0)), (2.0, 0.5, -1.5)))
+    objs.append(w.translate(w.matinst(w.cube1((0, 0, 0), None), w.dielectric(1.5, bump=concrete, strength=0.02)), (-3.0, 1.0, 2.5)))
+    master_cube = w.cube((-0.2, -0.2, -0.2), (0.2, 0.2, 0.2), None)
+    master_sphere = w.sphere((0, 0, 0), 0.2, None)
+    neon = [w.light((3.0, 0.0, 1.5)), w.light((0.0, 2.0, 4.0)), w.light((0.4, 4.0, 0.4)), w.light((6.0, 4.8, 0.0))]
+    regular = [w.lambertian((0.8, 0.1, 0.1)), w.metal((0.95, 0.64, 0.54), 0.0), w.metal((1.0, 0.84, 0.0), 0.15),
+               w.lambertian((0.1, 0.4, 0.9)), w.metal((1, 1, 1), 0.25), w.lambertian(tex=checker),
+               w.metal((0.9, 0.9, 0.9), 0.6, bump=concrete, strength=2.0), w.lambertian(tex=wood)]
+    glass, bubble = w.dielectric(1.5), w.dielectric(1.0 / 1.5)
+    side = max(1, int(math.ceil(math.sqrt(small))))
+    placed = 0
+    for a in range(-side // 2, side - side // 2):
+        for b in range(-side // 2, side - side // 2):
+            if placed >= small:
+                break
+            c = (a + 0.9 * rng.random(), 0.2, b + 0.9 * rng.random())
+            if math.dist(c, (4.0, 0.2, 0.0)) <= 0.9 or math.dist(c, (0, 0.2, 0)) < 1.3:
+                continue
+            dice = rng.random()
+            if dice < 0.25:
+                m, geom, sv = rng.choice(neon), master_cube, (0.4, 1.5 + 3.0 * rng.random(), 0.4)
+            elif dice < 0.55:
+                m, geom = (glass if rng.random() < 0.7 else bubble), master_sphere
+                s = 0.5 + 0.5 * rng.random()
+                sv = (s, s, s)
+            else:
+                m, geom = rng.choice(regular), (master_sphere if rng.random() < 0.5 else master_cube)
+                s = 0.8 + 0.4 * rng.random()
+                sv = (s, s, s)
+            o = w.scale(geom, sv)
+            if geom == master_cube:
+                o = w.rotate("y", o, 90.0 * rng.random())  # radians, as the demo passes U[0,90) (Appendix A q3)
+            objs.append(w.translate(w.matinst(o, m), c))
+            placed += 1
+    w.world(w.container("bvh", objs, name="world"))
+    w.lines.append("envmap sky.hdr")
+    cfg = RenderConfig(
+        image_width=width, image_height=height, samples_per_pixel=spp, max_depth=max_depth, vfov=30.0,
+        lookfrom=(10.0, 1.5, 0.0), lookat=(0.0, 0.0, 0.0), vup=(0.0, 1.0, 0.0), defocus_angle=3.0, focus_dist=9.0,
+        env_mode="hdr", env_intensity=1.0, hdr_path="sky.hdr", hdri_rotation=0.5)
+    return w.text(), cfg, files
+
+
+def quirks(seed: int = 5, width: int = 640, height: int = 360, spp: int = 64, max_depth: int = 50, env: str = "sun"):
+    """A small scene that puts every wrapper / primitive quirk of SURVEY.md Appendix A in view: glass under
+    translate / rotate_y (front_face forced, q1) and under rotate_x / rotate_z / scale (kept, q2), degrees vs
+    radians (q3), an off-origin cube (q4: slab test about the origin), a camera ray starting inside a cube
+    (q5) is avoided but a glass cube is present, loose triangles, a null material_instance (magenta),
+    checker with negative coordinates (q9), metal fuzz 0 (q10), a light, nested list in bvh; PHYSICAL_SUN sky."""
+    w = SceneWriter()
+    glass = w.dielectric(1.5, tint=(0.9, 1.0, 0.95))
+    red, blue = w.lambertian((0.8, 0.15, 0.1)), w.lambertian((0.1, 0.3, 0.8))
+    mirror, gold = w.metal((0.95, 0.95, 0.95), 0.0), w.metal((1.0, 0.8, 0.4), 0.3)
+    checker = w.lambertian(tex=w.tex_checker(0.7, w.tex_solid((0.15, 0.15, 0.15)), w.tex_solid((0.85, 0.85, 0.85))))
+    lamp = w.light((4.0, 3.5, 3.0))
+    s1 = w.sphere((0, 0, 0), 0.5, glass)
+    c1 = w.cube((-0.4, -0.4, -0.4), (0.4, 0.4, 0.4), glass)
+    objs = [
+        w.sphere((0, -200, 0), 200.0, checker),
+        w.sphere((-3.0, 0.5, -2.0), 0.5, glass),                                   # plain: front_face real
+        w.translate(s1, (-1.8, 0.5, -2.0)),                                        # q1 forced
+        w.translate(w.rotate("y", w.scale(s1, (1.0, 1.6, 0.7)), 0.6), (-0.4, 0.8, -2.0)),  # ellipsoid, q1 via rotate_y
+        w.scale(w.sphere((1.0, 0.5, -2.0), 0.5, glass), (1.0, 1.0, 1.0)),          # q2 kept (identity scale instance)
+        w.rotate("x", w.sphere((2.4, 0.5, -2.0), 0.5, glass), 0.0),               # q2 kept (degrees)
+        w.translate(w.rotate("z", w.rotate("x", c1, 30.0), 20.0), (-2.6, 0.6, 0.0)),      # degrees
+        w.translate(w.rotate("y", c1, 0.7), (-1.2, 0.4, 0.2)),                     # radians
+        w.translate(w.matinst(w.cube1((0, 0, 0), None), mirror), (3.2, 1.0, -0.2)),
+        w.cube((-0.3, -0.3, -0.3), (0.3, 0.3, 0.3), gold),                         # origin-centred plain cube
+        w.cube((0.8, 0.0, 0.3), (1.4, 0.6, 0.9), red),                             # q4: off-origin cube
+        w.matinst(w.sphere((1.9, 0.35, 0.9), 0.35, red), None),                    # magenta
+        w.translate(w.matinst(w.scale(w.sphere((0, 0, 0), 0.3, None), (1.0, 0.5, 1.0)), blue), (0.3, 0.15, 1.4)),
+        w.triangle((-2.2, 0.0, 1.2), (-1.2, 0.0, 1.6), (-1.7, 1.1, 1.3), (0, 0, 1), (0, 0, 1), (0.3, 0.2, 0.9), gold),
+        w.translate(w.triangle((0, 0, 0), (0.8, 0, 0.1), (0.4, 0.9, 0), (0, 0, 1), (0, 0, 1), (0, 0, 1), blue), (-0.6, 0.0, 1.9)),
+        w.sphere((0.0, 3.2, 0.0), 0.6, lamp),
+        w.container("list", [w.sphere((2.6, 0.3, 1.6), 0.3, mirror), w.sphere((3.1, 0.25, 1.1), 0.25, blue)]),
+    ]
+    w.world(w.container("bvh", objs, name="world"))
+    cfg = RenderConfig(
+        image_width=width, image_height=height, samples_per_pixel=spp, max_depth=max_depth, vfov=38.0,
+        lookfrom=(0.5, 2.2, 7.5), lookat=(0.2, 0.5, 0.0), vup=(0.0, 1.0, 0.0), defocus_angle=0.0, focus_dist=8.0,
+        env_mode=env, background=(0.6, 0.7, 0.9), env_intensity=1.0, sun_direction=(0.6, 0.45, 0.5),
+        sun_color=(1.0, 0.95, 0.85), sun_intensity=1.0, sun_size=1.0)
+    return w.text(), cfg, {}

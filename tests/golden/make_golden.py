@@ -58,30 +58,41 @@ def scratch_dir():
     return d
 
 
-def make_ids(name, scene_text, cfg, extra_files=None):
+def scene_digest(scene_text, cfg, files):
+    """sha256 over the scene text, config and asset bytes: the GPU test regenerates the scene from the same
+    seeded generator and refuses to compare if it does not reproduce what the reference rendered."""
+    import hashlib
+    h = hashlib.sha256()
+    h.update(scene_text.encode())
+    h.update(cfg.to_text().encode())
+    for k in sorted(files or {}):
+        if k.endswith(".zbtex"):
+            continue  # derived from the same arrays; the reference never reads them
+        v = files[k]
+        h.update(k.encode())
+        h.update(v if isinstance(v, (bytes, bytearray)) else v.encode())
+    return h.hexdigest()
+
+
+def make_ids(name, scene_text, cfg, files=None):
     d = scratch_dir()
-    sp, cp, op = (os.path.join(d, x) for x in ("s.zscene", "s.cfg", "ids.bin"))
-    open(sp, "w").write(scene_text)
-    open(cp, "w").write(cfg.to_text())
-    for fn, data in (extra_files or {}).items():
-        open(os.path.join(d, fn), "wb" if isinstance(data, bytes) else "w").write(data)
-    info = run_harness(["ids", sp, cp, op], d)
+    scenes.materialize(d, scene_text, cfg, files)
+    op = os.path.join(d, "ids.bin")
+    info = run_harness(["ids", "s.zscene", "s.cfg", op], d)
     leaf, tri, t = read_ids(op)
-    np.savez_compressed(os.path.join(GOLDEN, f"{name}_ids.npz"), leaf=leaf, tri=tri, t=t.astype(np.float32))
+    np.savez_compressed(os.path.join(GOLDEN, f"{name}_ids.npz"), leaf=leaf, tri=tri, t=t.astype(np.float32),
+                        digest=scene_digest(scene_text, cfg, files))
     print(name, "ids", info, "hit fraction", float((leaf != 0xFFFFFFFF).mean()))
 
 
-def make_stats(name, scene_text, cfg, batches, extra_files=None):
+def make_stats(name, scene_text, cfg, batches, files=None):
     d = scratch_dir()
-    sp, cp, op = (os.path.join(d, x) for x in ("s.zscene", "s.cfg", "stats.bin"))
-    open(sp, "w").write(scene_text)
-    open(cp, "w").write(cfg.to_text())
-    for fn, data in (extra_files or {}).items():
-        open(os.path.join(d, fn), "wb" if isinstance(data, bytes) else "w").write(data)
-    info = run_harness(["stats", sp, cp, op, str(batches)], d)
+    scenes.materialize(d, scene_text, cfg, files)
+    op = os.path.join(d, "stats.bin")
+    info = run_harness(["stats", "s.zscene", "s.cfg", op, str(batches)], d)
     mean, var = read_stats(op)
     np.savez_compressed(os.path.join(GOLDEN, f"{name}_stats.npz"), mean=mean, var_of_mean=var,
-                        spp=cfg.samples_per_pixel, batches=batches)
+                        spp=cfg.samples_per_pixel, batches=batches, digest=scene_digest(scene_text, cfg, files))
     print(name, "stats", info)
 
 
@@ -96,7 +107,26 @@ def weekend_stats():
     make_stats("weekend_300x169", txt, cfg, 16)
 
 
-TARGETS = {"weekend_ids": weekend_ids, "weekend_stats": weekend_stats}
+# Reduced-size instances of configs C2-C4 and the quirk scene: same generators as the bench, sized so the
+# reference finishes 4096 spp in minutes on 8 cores.  GOLDEN_SCENES is shared with tests/test_gpu_parity.py.
+from tests.golden.golden_scenes import GOLDEN_SCENES  # noqa: E402
+
+
+def scene_targets():
+    t = {}
+    for name, (gen, kw, ids_wh, stats_wh, ids_kw) in GOLDEN_SCENES.items():
+        def ids(name=name, gen=gen, kw={**kw, **ids_kw}, wh=ids_wh):
+            txt, cfg, files = getattr(scenes, gen)(width=wh[0], height=wh[1], spp=1, **kw)
+            make_ids(f"{name}_{wh[0]}x{wh[1]}", txt, cfg, files)
+
+        def stats(name=name, gen=gen, kw=kw, wh=stats_wh):
+            txt, cfg, files = getattr(scenes, gen)(width=wh[0], height=wh[1], spp=256, **kw)
+            make_stats(f"{name}_{wh[0]}x{wh[1]}", txt, cfg, 16, files)
+        t[f"{name}_ids"], t[f"{name}_stats"] = ids, stats
+    return t
+
+
+TARGETS = {"weekend_ids": weekend_ids, "weekend_stats": weekend_stats, **scene_targets()}
 
 if __name__ == "__main__":
     names = sys.argv[1:] or list(TARGETS)

@@ -110,3 +110,72 @@ def test_aovs(weekend_scene):
     sky = r["normal"][0, 0]
     assert np.allclose(sky, [0.5, 0.5, 1.0], atol=1e-6)      # miss writes (.5,.5,1) (camera.hpp:522-525)
     assert np.allclose(r["z_depth"][0, 0], 0.0) and r["z_depth"].max() > 0.3
+
+
+# ------------------------------------------------------------------ configs C2-C4 + quirk scene
+from tests.golden.golden_scenes import GOLDEN_SCENES  # noqa: E402
+from tests.golden.make_golden import scene_digest  # noqa: E402
+
+
+def _load_scene(gpu_ctx, tmp_path, name, wh, spp, extra=None):
+    gen, kw, _, _, _ = GOLDEN_SCENES[name]
+    txt, cfg, files = getattr(scenes, gen)(width=wh[0], height=wh[1], spp=spp, **{**kw, **(extra or {})})
+    path = scenes.materialize(str(tmp_path), txt, cfg, files)
+    flat = api.flatten_zscene(path=path)
+    sc = gpu_ctx.upload(flat)
+    api.free_flat(flat)
+    return sc, cfg, scene_digest(txt, cfg, files)
+
+
+@pytest.mark.parametrize("name", list(GOLDEN_SCENES))
+def test_scene_primary_ids_match_reference(name, gpu_ctx, tmp_path):
+    """Primary-hit leaf ids (and mesh face ids) against the reference on cubes, triangles, OBJ meshes,
+    transformed instances and textured objects; mismatches only at silhouettes / grazing ties."""
+    _, _, wh, _, ids_kw = GOLDEN_SCENES[name]
+    gold = np.load(os.path.join(GOLDEN, f"{name}_{wh[0]}x{wh[1]}_ids.npz"))
+    sc, cfg, digest = _load_scene(gpu_ctx, tmp_path, name, wh, 1, ids_kw)
+    assert digest == str(gold["digest"]), "the regenerated scene differs from the one the reference rendered"
+    leaf, prim, t = sc.primary_ids(cfg)
+    sc.close()
+    same = leaf == gold["leaf"]
+    print(f"{name}: leaf-id agreement {same.mean() * 100:.5f} % ({(~same).sum()} of {same.size} differ)")
+    assert same.mean() >= 0.9999
+    hit = same & (gold["leaf"] != 0xFFFFFFFF)
+    rel = np.abs(t[hit] - gold["t"][hit]) / np.maximum(gold["t"][hit], 1e-6)
+    assert np.quantile(rel, 0.999) < 2e-4 and rel.max() < 2e-2, (np.quantile(rel, 0.999), rel.max())
+    # mesh faces: same triangle wherever the same leaf was hit, except on shared edges (inclusive edge rule,
+    # triangle.hpp:62) where either neighbour is a legitimate answer
+    face_same = (prim == gold["tri"])[hit]
+    print(f"{name}: face-id agreement {face_same.mean() * 100:.4f} %")
+    assert face_same.mean() >= 0.999
+    ys, xs = np.nonzero(~same)
+    g = np.pad(gold["leaf"], 1, mode="edge")
+    for y, x in zip(ys, xs):
+        assert leaf[y, x] in g[y:y + 3, x:x + 3], (y, x)
+
+
+@pytest.mark.parametrize("name", list(GOLDEN_SCENES))
+def test_scene_radiance_converges_to_reference(name, gpu_ctx, tmp_path):
+    """Converged radiance against 16 x 256 spp of the reference.  Bar (north_star): image-level relative
+    RMSE <= 1 % beyond the Monte-Carlo noise of the two estimates, per-pixel means within 3 sigma, no bias."""
+    _, _, _, wh, _ = GOLDEN_SCENES[name]
+    gold = np.load(os.path.join(GOLDEN, f"{name}_{wh[0]}x{wh[1]}_stats.npz"))
+    ref, var_ref = gold["mean"].astype(np.float64), gold["var_of_mean"].astype(np.float64)
+    sc, cfg, digest = _load_scene(gpu_ctx, tmp_path, name, wh, 256)
+    assert digest == str(gold["digest"]), "the regenerated scene differs from the one the reference rendered"
+    cfg.samples_per_pixel = 16384
+    img = sc.render(cfg, seed=11)["beauty"]
+    sc.close()
+    assert np.isfinite(img).all()
+    noise2 = 1.25 * var_ref.sum() / (ref ** 2).sum()   # reference noise + GPU noise at 4x the samples
+    rrmse = np.sqrt(((img - ref) ** 2).sum() / (ref ** 2).sum())
+    print(f"{name}: rRMSE {rrmse * 100:.3f} % (noise floor {np.sqrt(noise2) * 100:.3f} %)  mean gpu "
+          f"{img.mean(axis=(0, 1))} ref {ref.mean(axis=(0, 1))}")
+    assert rrmse <= np.sqrt(0.01 ** 2 + noise2)
+    sigma = np.sqrt(1.25 * var_ref + 1e-12)
+    out = np.abs(img - ref) > 3 * sigma
+    print(f"{name}: outside 3 sigma: {out.mean() * 100:.3f} % of pixel channels")
+    assert out.mean() <= 0.02
+    m_gpu, m_ref = img.mean(axis=(0, 1)), ref.mean(axis=(0, 1))
+    sem = np.sqrt(1.25 * var_ref.sum(axis=(0, 1))) / (ref.shape[0] * ref.shape[1])
+    assert np.all(np.abs(m_gpu - m_ref) <= 0.005 * m_ref + 4 * sem), (m_gpu, m_ref, sem)
