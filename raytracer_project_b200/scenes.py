@@ -358,7 +358,7 @@ def mesh(seed: int = 3, width: int = 1920, height: int = 1080, spp: int = 64, ma
     return w.text(), cfg, files
 
 
-def _sky_hdr(width: int = 2048, height: int = 1024):
+def _sky_hdr(width: int = 2048, height: int = 1024, sun_radiance: float = 5.0e4):
     """Synthetic lat-long sky: vertical gradient + a 1-degree-radius sun of radiance 5e4."""
     import numpy as np
     v = (np.arange(height) + 0.5) / height           # 0 = +y (zenith) ... 1 = -y, as texture.hpp:50-78 indexes it
@@ -371,7 +371,7 @@ def _sky_hdr(width: int = 2048, height: int = 1024):
     sun = np.array([0.5, 0.6, -0.62])
     sun /= np.linalg.norm(sun)
     cosang = (d * sun).sum(-1, keepdims=True)
-    sky = np.where(cosang > math.cos(math.radians(1.0)), np.array([5.0e4, 4.6e4, 4.0e4]), sky)
+    sky = np.where(cosang > math.cos(math.radians(1.0)), sun_radiance * np.array([1.0, 0.92, 0.8]), sky)
     return sky.astype(np.float32)
 
 
@@ -402,7 +402,7 @@ def _noise_tex(size: int, seed: int, octaves: int = 4, channels: int = 1):
 
 
 def exterior(seed: int = 4, width: int = 1920, height: int = 1080, spp: int = 128, max_depth: int = 50, small: int = 200,
-             hdr_size: int = 2048):
+             hdr_size: int = 2048, sun_radiance: float = 5.0e4):
     """C4: HDRI-lit exterior with thin-lens DOF (defocus_angle 3.0, focus_dist 9.0):
     r=1000 ground with a reflective checker metal, bump-mapped mirror / gold / wood spheres, a bumpy-glass
     2x2x2 cube, and `small` instanced cubes/spheres built exactly like the reference's demo grid
@@ -417,7 +417,7 @@ def exterior(seed: int = 4, width: int = 1920, height: int = 1080, spp: int = 12
     files.update(ztex.ldr_pair("woodbump.png", _noise_tex(512, seed * 10 + 2, octaves=3)))
     files.update(ztex.ldr_pair("concrete.png", _noise_tex(256, seed * 10 + 3, octaves=5)))
     files.update(ztex.ldr_pair("wood.png", _noise_tex(512, seed * 10 + 4, octaves=4, channels=3)))
-    files.update(ztex.hdr_pair("sky.hdr", _sky_hdr(hdr_size, hdr_size // 2)))
+    files.update(ztex.hdr_pair("sky.hdr", _sky_hdr(hdr_size, hdr_size // 2, sun_radiance)))
     scratches, woodbump, concrete = (w.tex_image(n) for n in ("scratches.png", "woodbump.png", "concrete.png"))
     wood = w.tex_image("wood.png")
     checker = w.tex_checker(0.5, w.tex_solid((0.1, 0.1, 0.1)), w.tex_solid((0.9, 0.9, 0.9)))
@@ -470,8 +470,8 @@ def exterior(seed: int = 4, width: int = 1920, height: int = 1080, spp: int = 12
 def quirks(seed: int = 5, width: int = 640, height: int = 360, spp: int = 64, max_depth: int = 50, env: str = "sun"):
     """A small scene that puts every wrapper / primitive quirk of SURVEY.md Appendix A in view: glass under
     translate / rotate_y (front_face forced, q1) and under rotate_x / rotate_z / scale (kept, q2), degrees vs
-    radians (q3), an off-origin cube (q4: slab test about the origin), a camera ray starting inside a cube
-    (q5) is avoided but a glass cube is present, loose triangles, a null material_instance (magenta),
+    radians (q3), glass cubes (q5), (an off-origin cube, q4, is NOT here: its phantom hit about the origin lies
+    outside its own bounding box, so whether the reference reports it depends on its random BVH order), loose triangles, a null material_instance (magenta),
     checker with negative coordinates (q9), metal fuzz 0 (q10), a light, nested list in bvh; PHYSICAL_SUN sky."""
     w = SceneWriter()
     glass = w.dielectric(1.5, tint=(0.9, 1.0, 0.95))
@@ -491,8 +491,7 @@ def quirks(seed: int = 5, width: int = 640, height: int = 360, spp: int = 64, ma
         w.translate(w.rotate("z", w.rotate("x", c1, 30.0), 20.0), (-2.6, 0.6, 0.0)),      # degrees
         w.translate(w.rotate("y", c1, 0.7), (-1.2, 0.4, 0.2)),                     # radians
         w.translate(w.matinst(w.cube1((0, 0, 0), None), mirror), (3.2, 1.0, -0.2)),
-        w.cube((-0.3, -0.3, -0.3), (0.3, 0.3, 0.3), gold),                         # origin-centred plain cube
-        w.cube((0.8, 0.0, 0.3), (1.4, 0.6, 0.9), red),                             # q4: off-origin cube
+        w.cube((-0.25, -0.35, -0.25), (0.25, 0.35, 0.25), gold),                   # origin-centred plain cube
         w.matinst(w.sphere((1.9, 0.35, 0.9), 0.35, red), None),                    # magenta
         w.translate(w.matinst(w.scale(w.sphere((0, 0, 0), 0.3, None), (1.0, 0.5, 1.0)), blue), (0.3, 0.15, 1.4)),
         w.triangle((-2.2, 0.0, 1.2), (-1.2, 0.0, 1.6), (-1.7, 1.1, 1.3), (0, 0, 1), (0, 0, 1), (0.3, 0.2, 0.9), gold),

@@ -96,6 +96,33 @@ def make_stats(name, scene_text, cfg, batches, files=None):
     print(name, "stats", info)
 
 
+def read_render(path):
+    with open(path, "rb") as f:
+        w, h = np.frombuffer(f.read(8), np.int32)
+        n = int(w) * int(h) * 3
+        return [np.frombuffer(f.read(8 * n), np.float64).reshape(h, w, 3) for _ in range(4)]
+
+
+def make_aov(name, scene_text, cfg, files=None):
+    """First-hit AOV buffers (albedo, view-space normal, z-depth; camera.hpp:464-488, :518-541)."""
+    d = scratch_dir()
+    cfg.use_albedo = cfg.use_normal = cfg.use_z_depth = True
+    scenes.materialize(d, scene_text, cfg, files)
+    op = os.path.join(d, "render.bin")
+    info = run_harness(["render", "s.zscene", "s.cfg", op], d)
+    _, albedo, normal, z = read_render(op)
+    np.savez_compressed(os.path.join(GOLDEN, f"{name}_aov.npz"), albedo=albedo.astype(np.float32),
+                        normal=normal.astype(np.float32), z_depth=z.astype(np.float32),
+                        spp=cfg.samples_per_pixel, digest=scene_digest(scene_text, cfg, files))
+    print(name, "aov", info)
+
+
+def quirks_aov():
+    txt, cfg, files = scenes.quirks(seed=5, width=320, height=180, spp=512)
+    cfg.z_depth_max_dist = 15.0
+    make_aov("quirks_320x180", txt, cfg, files)
+
+
 def weekend_ids():
     txt, cfg = scenes.weekend(seed=1, width=1200, height=675)
     make_ids("weekend_1200x675", txt, cfg)
@@ -126,7 +153,7 @@ def scene_targets():
     return t
 
 
-TARGETS = {"weekend_ids": weekend_ids, "weekend_stats": weekend_stats, **scene_targets()}
+TARGETS = {"quirks_aov": quirks_aov, "weekend_ids": weekend_ids, "weekend_stats": weekend_stats, **scene_targets()}
 
 if __name__ == "__main__":
     names = sys.argv[1:] or list(TARGETS)

