@@ -15,11 +15,16 @@ ap.add_argument("--reps", type=int, default=3)
 ap.add_argument("--stats", action="store_true")
 ap.add_argument("--tag", default=os.environ.get("ZB_LIB", "main"))
 a = ap.parse_args()
+import tempfile, time
 gen = getattr(scenes, a.scene)
-out = gen(seed=1, width=a.width, height=a.height, spp=a.spp)
+out = gen(width=a.width, height=a.height, spp=a.spp)
 txt, cfg = out[0], out[1]
-base = out[2] if len(out) > 2 else None
-flat = api.flatten_zscene(txt) if base is None else api.flatten_zscene(path=base)
+t0 = time.time()
+if len(out) > 2:
+    flat = api.flatten_zscene(path=scenes.materialize(tempfile.mkdtemp(prefix="zb_tune_"), txt, cfg, out[2]))
+else:
+    flat = api.flatten_zscene(txt)
+flatten_s = time.time() - t0
 dev = torch.device("cuda", 0)
 stream = torch.cuda.current_stream()
 ctx = api.Context(0, stream=stream.cuda_stream)
@@ -27,7 +32,7 @@ sc = ctx.upload(flat)
 n = a.width * a.height
 acc = torch.empty(n, 4, device=dev)
 flush = torch.empty(256 << 20, device=dev, dtype=torch.uint8)
-res = {"tag": a.tag, "scene": a.scene}
+res = {"tag": a.tag, "scene": a.scene, "flatten_s": round(flatten_s, 2), "scene_mb": round(flat.contents.nbytes() / 1e6, 2)}
 if a.stats:
     sc.render_device(cfg, acc.data_ptr(), seed=1, stats=True)
     torch.cuda.synchronize()
