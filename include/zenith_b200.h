@@ -255,6 +255,11 @@ int zb_render_device(zb_context* ctx, const zb_scene* scene, const zb_camera* ca
 int zb_resolve_device(zb_context* ctx, const void* accum_f4, size_t n_pixels, double scale, void* out_f4,
                       void* out_rgb_f64);
 
+/* Device float4 means (the out_f4 of zb_resolve_device) -> caller-owned host buffer in the reference's layout
+ * (row-major, 3 doubles per pixel, std::vector<color> camera.hpp:63).  Blocking; the frame crosses PCIe as
+ * float4 in chunks and is widened by host threads while later chunks are in flight. */
+int zb_read_frame(zb_context* ctx, const void* mean_f4, size_t n_pixels, double* out_rgb_f64);
+
 /* K7 parity artefact: centre-of-pixel pinhole primary hit (camera::get_center_ray camera.hpp:809-814
  * + world.hit with interval(0.001, inf) camera.hpp:459).  leaf_id = 0xFFFFFFFF on a miss;
  * prim_id = face index inside a mesh, else 0.  Host pointers, W*H entries each; any may be NULL. */

@@ -89,6 +89,7 @@ SYMBOLS = {
     "zb_scene_destroy": (C.c_int, [C.c_void_p]),
     "zb_render": (C.c_int, [C.c_void_p, C.c_void_p, C.POINTER(Camera), C.POINTER(Environment), C.POINTER(RenderOpts),
                             C.POINTER(Outputs), C.POINTER(C.c_int), PROGRESS_FN, C.c_void_p]),
+    "zb_read_frame": (C.c_int, [C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p]),
     "zb_render_device": (C.c_int, [C.c_void_p, C.c_void_p, C.POINTER(Camera), C.POINTER(Environment),
                                    C.POINTER(RenderOpts), C.c_void_p, C.c_void_p]),
     "zb_resolve_device": (C.c_int, [C.c_void_p, C.c_void_p, C.c_size_t, C.c_double, C.c_void_p, C.c_void_p]),

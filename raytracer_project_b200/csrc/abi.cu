@@ -54,11 +54,11 @@ extern "C" int zb_context_destroy(zb_context* ctx) {
     cudaFree(ctx->counters);
     cudaFree(ctx->accum);
     cudaFree(ctx->accum_aux);
-    cudaFree(ctx->out_f64);
     cudaFree(ctx->out_f4);
     cudaFree(ctx->id_scratch);
     if (ctx->pinned) cudaFreeHost(ctx->pinned);
     for (auto& ev : ctx->ev) cudaEventDestroy(ev);
+    for (auto& ev : ctx->chunk_ev) cudaEventDestroy(ev);
     if (ctx->own_stream) cudaStreamDestroy(ctx->stream);
     delete ctx;
     return ZB_OK;

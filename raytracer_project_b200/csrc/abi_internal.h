@@ -32,13 +32,13 @@ struct zb_context {
     float4* accum = nullptr;
     float4* accum_aux = nullptr;
     size_t accum_pixels = 0;
-    double* out_f64 = nullptr;
     float4* out_f4 = nullptr;
     void* pinned = nullptr;
     size_t pinned_bytes = 0;
     uint32_t* id_scratch = nullptr;
     size_t id_pixels = 0;
     cudaEvent_t ev[6] = {};
+    std::vector<cudaEvent_t> chunk_ev;  // one per 4 MiB chunk of the frame copy (abi_render.cu d2h_rgb_f64)
     zb_stats stats{};
 };
 

@@ -1,6 +1,8 @@
 // abi_render.cu — zb_render / zb_render_device / zb_resolve_device / zb_primary_ids / zb_get_stats.
 // The drop-in for camera::render's hot part (camera.hpp:236-250 -> execute_render_threads :404-579).
 #include <algorithm>
+#include <atomic>
+#include <thread>
 
 #include "abi_internal.h"
 
@@ -123,15 +125,12 @@ int ensure_scratch(zb_context* ctx, size_t pixels, bool aux) {
     if (ctx->accum_pixels < pixels) {
         cudaFree(ctx->accum);
         cudaFree(ctx->accum_aux);
-        cudaFree(ctx->out_f64);
         cudaFree(ctx->out_f4);
         ctx->accum = nullptr;
         ctx->accum_aux = nullptr;
-        ctx->out_f64 = nullptr;
         ctx->out_f4 = nullptr;
         ctx->accum_pixels = 0;
         ZB_CUDA(cudaMalloc(&ctx->accum, pixels * sizeof(float4)));
-        ZB_CUDA(cudaMalloc(&ctx->out_f64, pixels * 3 * sizeof(double)));
         ZB_CUDA(cudaMalloc(&ctx->out_f4, pixels * sizeof(float4)));
         ctx->accum_pixels = pixels;
     }
@@ -221,6 +220,51 @@ int d2h(zb_context* ctx, void* host, const void* dev, size_t bytes) {
     return ZB_OK;
 }
 
+// Device float4 means -> the reference's host layout (3 doubles per pixel, camera.hpp:531).  The frame
+// crosses PCIe as float4 (16 B/pixel instead of 24) in chunks; while chunk c+1 is in flight, host threads
+// widen chunk c into the caller's buffer, so the copy, the widening and the pageable-memory write overlap.
+int d2h_rgb_f64(zb_context* ctx, double* host, const float4* dev, size_t pixels) {
+    const size_t chunk = size_t(1) << 18;  // 256 Ki pixels = 4 MiB per copy
+    const size_t n_chunks = (pixels + chunk - 1) / chunk;
+    while (ctx->chunk_ev.size() < n_chunks) {
+        cudaEvent_t e;
+        ZB_CUDA(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+        ctx->chunk_ev.push_back(e);
+    }
+    float4* stage = static_cast<float4*>(ctx->pinned);
+    for (size_t c = 0; c < n_chunks; c++) {
+        const size_t b = c * chunk, n = std::min(chunk, pixels - b);
+        ZB_CUDA(cudaMemcpyAsync(stage + b, dev + b, n * sizeof(float4), cudaMemcpyDeviceToHost, ctx->stream));
+        ZB_CUDA(cudaEventRecord(ctx->chunk_ev[c], ctx->stream));
+    }
+    const unsigned hw = std::max(1u, std::thread::hardware_concurrency());
+    const size_t n_thr = std::min<size_t>(std::min<size_t>(hw, 8), n_chunks);
+    std::atomic<size_t> next{0};
+    std::atomic<int> err{0};
+    auto work = [&]() {
+        for (;;) {
+            const size_t c = next.fetch_add(1);
+            if (c >= n_chunks) return;
+            if (cudaEventSynchronize(ctx->chunk_ev[c]) != cudaSuccess) { err.store(1); return; }
+            const size_t b = c * chunk, n = std::min(chunk, pixels - b);
+            const float4* src = stage + b;
+            double* dst = host + 3 * b;
+            for (size_t i = 0; i < n; i++) {
+                dst[3 * i + 0] = double(src[i].x);
+                dst[3 * i + 1] = double(src[i].y);
+                dst[3 * i + 2] = double(src[i].z);
+            }
+        }
+    };
+    std::vector<std::thread> pool;
+    for (size_t t = 1; t < n_thr; t++) pool.emplace_back(work);
+    work();
+    for (auto& t : pool) t.join();
+    if (err.load()) return fail(ZB_ERR_CUDA, "device-to-host copy of the frame failed");
+    ZB_CUDA(cudaStreamSynchronize(ctx->stream));
+    return ZB_OK;
+}
+
 int read_counters(zb_context* ctx) {
     unsigned long long c[8];
     ZB_CUDA(cudaMemcpyAsync(c, ctx->counters, sizeof(c), cudaMemcpyDeviceToHost, ctx->stream));
@@ -261,6 +305,20 @@ extern "C" int zb_resolve_device(zb_context* ctx, const void* accum_f4, size_t n
     return ZB_OK;
 }
 
+extern "C" int zb_read_frame(zb_context* ctx, const void* mean_f4, size_t n_pixels, double* out_rgb_f64) {
+    if (!ctx || !mean_f4 || !out_rgb_f64) return fail(ZB_ERR_INVALID, "zb_read_frame: NULL argument");
+    ZB_CUDA(cudaSetDevice(ctx->device));
+    const size_t need = n_pixels * sizeof(float4);
+    if (ctx->pinned_bytes < need) {
+        if (ctx->pinned) cudaFreeHost(ctx->pinned);
+        ctx->pinned = nullptr;
+        ctx->pinned_bytes = 0;
+        ZB_CUDA(cudaMallocHost(&ctx->pinned, need));
+        ctx->pinned_bytes = need;
+    }
+    return d2h_rgb_f64(ctx, out_rgb_f64, static_cast<const float4*>(mean_f4), n_pixels);
+}
+
 extern "C" int zb_render(zb_context* ctx, const zb_scene* scene, const zb_camera* cam, const zb_environment* env,
                          const zb_render_opts* opts, zb_outputs* out, const volatile int* cancel,
                          zb_progress_fn progress, void* user) {
@@ -288,19 +346,18 @@ extern "C" int zb_render(zb_context* ctx, const zb_scene* scene, const zb_camera
     const double scale = 1.0 / opts->samples_per_pixel;
     const double aux_scale = 1.0 / std::min(P.aux_samples, opts->samples_per_pixel);  // camera.hpp:535-541
     if (out->beauty || out->beauty_f4) {
-        ZB_CUDA(zbk_launch_resolve(ctx->accum, pixels, float(scale), out->beauty_f4 ? ctx->out_f4 : nullptr,
-                                   out->beauty ? ctx->out_f64 : nullptr, ctx->stream));
+        ZB_CUDA(zbk_launch_resolve(ctx->accum, pixels, float(scale), ctx->out_f4, nullptr, ctx->stream));
         ctx->stats.launches++;
     }
     ZB_CUDA(cudaEventRecord(ctx->ev[2], ctx->stream));
-    if (out->beauty) rc = d2h(ctx, out->beauty, ctx->out_f64, pixels * 3 * sizeof(double));
+    if (out->beauty) rc = d2h_rgb_f64(ctx, out->beauty, ctx->out_f4, pixels);
     if (!rc && out->beauty_f4) rc = d2h(ctx, out->beauty_f4, ctx->out_f4, pixels * sizeof(float4));
     double* aux_out[3] = {out->albedo, out->normal, out->z_depth};
     for (int k = 0; k < 3 && !rc; k++) {
         if (!aux_out[k]) continue;
-        ZB_CUDA(zbk_launch_resolve(ctx->accum_aux + k * pixels, pixels, float(aux_scale), nullptr, ctx->out_f64, ctx->stream));
+        ZB_CUDA(zbk_launch_resolve(ctx->accum_aux + k * pixels, pixels, float(aux_scale), ctx->out_f4, nullptr, ctx->stream));
         ctx->stats.launches++;
-        rc = d2h(ctx, aux_out[k], ctx->out_f64, pixels * 3 * sizeof(double));
+        rc = d2h_rgb_f64(ctx, aux_out[k], ctx->out_f4, pixels);
     }
     if (rc) return rc;
     ZB_CUDA(cudaEventRecord(ctx->ev[3], ctx->stream));
