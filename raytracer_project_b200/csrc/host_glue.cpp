@@ -2,6 +2,8 @@
 // This is the piece a Zenith maintainer would NOT need (they already hold a hittable graph and call
 // zenith::flattener directly); it exists so that language bindings and tests can
 // drive the same host code through the C ABI.
+#include <algorithm>
+#include <cstdlib>
 #include <fstream>
 #include <map>
 #include <memory>
@@ -33,6 +35,8 @@ int load(std::istream& in, const std::string& base_dir, const zb_flat_scene** ou
         ld.parse(in);
         std::shared_ptr<hittable> world = ld.build_world();
         flattener fl;
+        if (const char* e = std::getenv("ZB_TLAS_LEAF")) fl.tlas_leaf = std::max(1, std::min(8, std::atoi(e)));  // tuning knobs
+        if (const char* e = std::getenv("ZB_BLAS_LEAF")) fl.blas_leaf = std::max(1, std::min(8, std::atoi(e)));
         EnvironmentSettings env;
         if (!ld.env_hdr_path.empty()) env.load_hdr(ld.path_of(ld.env_hdr_path));  // environment.hpp:46-69
         std::unique_ptr<flat_scene> fs = fl.run(*world, &env);

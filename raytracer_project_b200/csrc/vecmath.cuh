@@ -53,12 +53,15 @@ ZB_DEV float3 xform_vector_t(const Affine& m, float3 v) {
 }
 
 // ---------------------------------------------------------------- Philox4x32-10 (Salmon et al. 2011)
+#ifndef ZB_PHILOX_ROUNDS
+#define ZB_PHILOX_ROUNDS 10
+#endif
 struct Philox {
     uint32_t key0, key1;
     ZB_DEV uint4 operator()(uint32_t c0, uint32_t c1, uint32_t c2, uint32_t c3) const {
         uint32_t k0 = key0, k1 = key1;
 #pragma unroll
-        for (int r = 0; r < 10; r++) {
+        for (int r = 0; r < ZB_PHILOX_ROUNDS; r++) {
             uint32_t hi0 = __umulhi(0xD2511F53u, c0), lo0 = 0xD2511F53u * c0;
             uint32_t hi1 = __umulhi(0xCD9E8D57u, c2), lo1 = 0xCD9E8D57u * c2;
             c0 = hi1 ^ c1 ^ k0;
