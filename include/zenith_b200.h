@@ -266,6 +266,24 @@ int zb_read_frame(zb_context* ctx, const void* mean_f4, size_t n_pixels, double*
 int zb_primary_ids(zb_context* ctx, const zb_scene* scene, const zb_camera* cam, uint32_t* leaf_id,
                    uint32_t* prim_id, float* t);
 
+/* Per-ray known-answer probe (parity tool, and a plain ray-query API): closest hit of arbitrary rays with
+ * the reference's interval (0.001, inf) and the hit_record the reference would build for it
+ * (hittable.hpp:9-26: t, p, normal, front_face, u, v) plus material::get_albedo / emitted at the hit, or
+ * camera::get_background_color for a miss (stored in `albedo`).  Host pointers; origins / directions are
+ * n x 3 floats. */
+typedef struct zb_probe {
+    float t;             /* INFINITY on a miss */
+    uint32_t leaf_id;    /* 0xFFFFFFFF on a miss */
+    uint32_t prim_id;
+    uint32_t front_face;
+    float p[3], normal[3];
+    float u, v;
+    float albedo[3];     /* get_albedo(rec), or the background colour on a miss */
+    float emitted[3];
+} zb_probe;
+int zb_probe_rays(zb_context* ctx, const zb_scene* scene, const zb_environment* env, size_t n,
+                  const float* origins, const float* directions, zb_probe* out);
+
 int zb_get_stats(zb_context* ctx, zb_stats* out);
 
 /* Host side of the boundary (C++20 scene API + flattener behind a C handle): parse a neutral scene

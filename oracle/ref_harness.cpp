@@ -6,6 +6,7 @@
 //           world.hit(interval(0.001, inf)) (camera.hpp:459), with every leaf wrapped in an id recorder
 //   render  camera::initialize + camera::execute_render_threads (camera.hpp:358, :404), timed
 //   stats   N independent renders -> per-pixel mean and variance of the mean (for the 3-sigma test)
+//   probe   per-ray hit_record / albedo / emitted / background for arbitrary rays (known-answer vectors)
 //   decode  stb_image decode of a texture into a .zbtex raw dump (identical texels on both sides)
 //   kat     known-answer values of single reference functions (tests/golden/kat.json)
 // Built by oracle/Makefile into oracle/_ref/ref_harness with -fno-access-control so private members
@@ -382,6 +383,57 @@ static int cmd_stats(const std::string& scene, const std::string& cfg, const std
     return 0;
 }
 
+// per-ray hit records of the reference for arbitrary rays (rays file: int32 n, n x 3 float32 origins,
+// n x 3 float32 directions; output: n x 19 float64 = t, leaf, tri, front_face, p, normal, u, v, albedo, emitted)
+static int cmd_probe(const std::string& scene, const std::string& cfg, const std::string& rays, const std::string& out) {
+    scene_bundle sb = load_scene(scene, true);
+    config c = config::load(cfg);
+    camera cam;
+    apply_camera(c, cam);
+    cam.initialize();
+    EnvironmentSettings env;
+    apply_env(c, dir_of(cfg), env);
+    FILE* f = std::fopen(rays.c_str(), "rb");
+    if (!f) return 2;
+    int32_t n = 0;
+    if (std::fread(&n, 4, 1, f) != 1 || n < 0) return 2;
+    std::vector<float> o(size_t(n) * 3), d(size_t(n) * 3);
+    if (std::fread(o.data(), 4, o.size(), f) != o.size() || std::fread(d.data(), 4, d.size(), f) != d.size()) return 2;
+    std::fclose(f);
+    std::vector<double> rec_out(size_t(n) * 19, 0.0);
+#pragma omp parallel for schedule(dynamic, 64)
+    for (int i = 0; i < n; i++) {
+        ray r(point3(o[3 * i], o[3 * i + 1], o[3 * i + 2]), vec3(d[3 * i], d[3 * i + 1], d[3 * i + 2]));
+        hit_record rec;
+        tl_leaf = -1;
+        tl_tri = -1;
+        double* q = &rec_out[size_t(i) * 19];
+        if (sb.world->hit(r, interval(0.001, infinity), rec)) {
+            q[0] = rec.t;
+            q[1] = double(tl_leaf);
+            q[2] = tl_tri >= 0 ? double(tl_tri) : 0.0;
+            q[3] = rec.front_face ? 1.0 : 0.0;
+            for (int k = 0; k < 3; k++) { q[4 + k] = rec.p[k]; q[7 + k] = rec.normal[k]; }
+            q[10] = rec.u;
+            q[11] = rec.v;
+            color a = rec.mat->get_albedo(rec), e = rec.mat->emitted(rec.u, rec.v, rec.p);
+            for (int k = 0; k < 3; k++) { q[12 + k] = a[k]; q[15 + k] = e[k]; }
+        } else {
+            q[0] = infinity;
+            q[1] = -1.0;
+            color b = cam.get_background_color(r, env);
+            for (int k = 0; k < 3; k++) q[12 + k] = b[k];
+        }
+    }
+    f = std::fopen(out.c_str(), "wb");
+    if (!f) return 2;
+    std::fwrite(&n, 4, 1, f);
+    std::fwrite(rec_out.data(), 8, rec_out.size(), f);
+    std::fclose(f);
+    std::printf("{\"cmd\": \"probe\", \"rays\": %d}\n", n);
+    return 0;
+}
+
 static int cmd_decode(const std::string& in, const std::string& out, bool is_hdr) {
     int w = 0, h = 0, comp = 3;
     FILE* f = nullptr;
@@ -418,6 +470,7 @@ int main(int argc, char** argv) {
     if (a.size() >= 4 && a[0] == "ids") return cmd_ids(a[1], a[2], a[3]);
     if (a.size() >= 4 && a[0] == "render") return cmd_render(a[1], a[2], a[3], a.size() > 4 && a[4] == "--count-rays");
     if (a.size() >= 5 && a[0] == "stats") return cmd_stats(a[1], a[2], a[3], std::atoi(a[4].c_str()));
+    if (a.size() >= 5 && a[0] == "probe") return cmd_probe(a[1], a[2], a[3], a[4]);
     if (a.size() >= 4 && a[0] == "decode") return cmd_decode(a[1], a[2], a[3] == "1");
     if (a.size() >= 2 && a[0] == "kat") return cmd_kat(a[1]);
     std::fprintf(stderr,

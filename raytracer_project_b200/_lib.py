@@ -55,6 +55,12 @@ class Environment(C.Structure):
                 ("sun_intensity", C.c_double), ("sun_size", C.c_double)]
 
 
+class Probe(C.Structure):
+    _fields_ = [("t", C.c_float), ("leaf_id", C.c_uint32), ("prim_id", C.c_uint32), ("front_face", C.c_uint32),
+                ("p", C.c_float * 3), ("normal", C.c_float * 3), ("u", C.c_float), ("v", C.c_float),
+                ("albedo", C.c_float * 3), ("emitted", C.c_float * 3)]
+
+
 class RenderOpts(C.Structure):
     _fields_ = [("samples_per_pixel", C.c_int32), ("max_depth", C.c_int32), ("seed", C.c_uint64),
                 ("sample_begin", C.c_int32), ("sample_end", C.c_int32), ("tile_rank", C.c_int32),
@@ -89,6 +95,7 @@ SYMBOLS = {
     "zb_scene_destroy": (C.c_int, [C.c_void_p]),
     "zb_render": (C.c_int, [C.c_void_p, C.c_void_p, C.POINTER(Camera), C.POINTER(Environment), C.POINTER(RenderOpts),
                             C.POINTER(Outputs), C.POINTER(C.c_int), PROGRESS_FN, C.c_void_p]),
+    "zb_probe_rays": (C.c_int, [C.c_void_p, C.c_void_p, C.POINTER(Environment), C.c_size_t, C.c_void_p, C.c_void_p, C.c_void_p]),
     "zb_read_frame": (C.c_int, [C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p]),
     "zb_render_device": (C.c_int, [C.c_void_p, C.c_void_p, C.POINTER(Camera), C.POINTER(Environment),
                                    C.POINTER(RenderOpts), C.c_void_p, C.c_void_p]),

@@ -142,6 +142,20 @@ class Scene:
         check(self.ctx.lib.zb_render_device(self.ctx.h, self.h, C.byref(cam), C.byref(env), C.byref(o),
                                             C.c_void_p(accum_ptr), C.c_void_p(aux_ptr) if aux_ptr else None))
 
+    PROBE_DTYPE = np.dtype([("t", "f4"), ("leaf_id", "u4"), ("prim_id", "u4"), ("front_face", "u4"), ("p", "f4", 3),
+                            ("normal", "f4", 3), ("u", "f4"), ("v", "f4"), ("albedo", "f4", 3), ("emitted", "f4", 3)])
+
+    def probe(self, cfg: RenderConfig, origins, directions):
+        """zb_probe_rays: per-ray hit records (structured numpy array, fields of zb_probe)."""
+        o = np.ascontiguousarray(origins, np.float32).reshape(-1, 3)
+        d = np.ascontiguousarray(directions, np.float32).reshape(-1, 3)
+        out = np.zeros(len(o), self.PROBE_DTYPE)
+        assert out.dtype.itemsize == C.sizeof(_lib.Probe)
+        env = env_struct(cfg)
+        check(self.ctx.lib.zb_probe_rays(self.ctx.h, self.h, C.byref(env), len(o), o.ctypes.data, d.ctypes.data,
+                                         out.ctypes.data))
+        return out
+
     def primary_ids(self, cfg: RenderConfig):
         n = cfg.image_width * cfg.image_height
         leaf = np.empty(n, np.uint32)

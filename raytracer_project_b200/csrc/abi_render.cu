@@ -403,6 +403,34 @@ extern "C" int zb_primary_ids(zb_context* ctx, const zb_scene* scene, const zb_c
     return ZB_OK;
 }
 
+extern "C" int zb_probe_rays(zb_context* ctx, const zb_scene* scene, const zb_environment* env, size_t n,
+                             const float* origins, const float* directions, zb_probe* out) {
+    if (!ctx || !scene || !env || (n && (!origins || !directions || !out))) return fail(ZB_ERR_INVALID, "zb_probe_rays: NULL argument");
+    if (scene->ctx != ctx) return fail(ZB_ERR_INVALID, "zb_probe_rays: scene belongs to another context");
+    ZB_CUDA(cudaSetDevice(ctx->device));
+    RenderParams P;
+    std::memset(&P, 0, sizeof(P));
+    P.sc = scene->dev;
+    int rc = setup_env(env, scene, P.env);
+    if (rc || n == 0) return rc;
+    float *d_o = nullptr, *d_d = nullptr;
+    zb_probe* d_out = nullptr;
+    cudaError_t e = cudaMalloc(&d_o, n * 12);
+    if (e == cudaSuccess) e = cudaMalloc(&d_d, n * 12);
+    if (e == cudaSuccess) e = cudaMalloc(&d_out, n * sizeof(zb_probe));
+    if (e == cudaSuccess) e = cudaMemcpyAsync(d_o, origins, n * 12, cudaMemcpyHostToDevice, ctx->stream);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(d_d, directions, n * 12, cudaMemcpyHostToDevice, ctx->stream);
+    if (e == cudaSuccess) e = zbk_launch_probe(P, n, d_o, d_d, d_out, ctx->stream);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(out, d_out, n * sizeof(zb_probe), cudaMemcpyDeviceToHost, ctx->stream);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
+    cudaFree(d_o);
+    cudaFree(d_d);
+    cudaFree(d_out);
+    if (e != cudaSuccess) return fail(ZB_ERR_CUDA, std::string("zb_probe_rays: ") + cudaGetErrorString(e));
+    ctx->stats.launches++;
+    return ZB_OK;
+}
+
 extern "C" int zb_get_stats(zb_context* ctx, zb_stats* out) {
     if (!ctx || !out) return fail(ZB_ERR_INVALID, "zb_get_stats: NULL argument");
     int rc = read_counters(ctx);

@@ -213,6 +213,47 @@ __global__ void __launch_bounds__(128) k_primary_ids(const __grid_constant__ Ren
     if (t_out) t_out[idx] = t;
 }
 
+// Per-ray probe: closest hit + the reference's hit_record + albedo / emitted / background (zb_probe_rays).
+__global__ void __launch_bounds__(128) k_probe(const __grid_constant__ RenderParams P, size_t n, const float* __restrict__ org,
+                                               const float* __restrict__ dir, zb_probe* __restrict__ out) {
+    const size_t i = size_t(blockIdx.x) * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const float3 o = f3(org[3 * i], org[3 * i + 1], org[3 * i + 2]), d = f3(dir[3 * i], dir[3 * i + 1], dir[3 * i + 2]);
+    Counters cnt = {0, 0, 0, 0};
+    MediumRng mr{Philox{P.seed_lo, P.seed_hi}, uint32_t(i), 0u, 0u};
+    Hit hit;
+    zb_probe r;
+    memset(&r, 0, sizeof(r));
+    if (trace<false>(P.sc, o, d, 0.001f, INFINITY, mr, hit, cnt)) {
+        Surface sf;
+        make_surface(P.sc, hit, o, d, sf, true);
+        r.t = hit.t;
+        r.leaf_id = sf.leaf_id;
+        r.prim_id = sf.prim_id;
+        r.front_face = sf.front_face ? 1u : 0u;
+        r.p[0] = sf.p.x; r.p[1] = sf.p.y; r.p[2] = sf.p.z;
+        r.normal[0] = sf.n.x; r.normal[1] = sf.n.y; r.normal[2] = sf.n.z;
+        r.u = sf.u;
+        r.v = sf.v;
+        float3 a = material_get_albedo(P.sc, sf), e = material_emitted(P.sc, sf);
+        r.albedo[0] = a.x; r.albedo[1] = a.y; r.albedo[2] = a.z;
+        r.emitted[0] = e.x; r.emitted[1] = e.y; r.emitted[2] = e.z;
+    } else {
+        r.t = INFINITY;
+        r.leaf_id = 0xFFFFFFFFu;
+        float3 b = background(P.sc, P.env, d);
+        r.albedo[0] = b.x; r.albedo[1] = b.y; r.albedo[2] = b.z;
+    }
+    out[i] = r;
+}
+
+cudaError_t zbk_launch_probe(const RenderParams& P, size_t n, const float* org, const float* dir, zb_probe* out,
+                             cudaStream_t stream) {
+    if (n == 0) return cudaSuccess;
+    k_probe<<<unsigned((n + 127) / 128), 128, 0, stream>>>(P, n, org, dir, out);
+    return cudaGetLastError();
+}
+
 // K5 resolve: mean = sum * scale.  Writes float4 and/or the reference's 3-double layout.
 __global__ void __launch_bounds__(256) k_resolve(const float4* __restrict__ accum, size_t n, float scale,
                                                  float4* __restrict__ out_f4, double* __restrict__ out_f64) {

@@ -3,6 +3,7 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 
+#include "../../include/zenith_b200.h"
 #include "scene_dev.cuh"
 
 cudaError_t zbk_launch_render(const RenderParams& P, int n_tiles_owned, bool stats, cudaStream_t stream);
@@ -10,3 +11,5 @@ cudaError_t zbk_launch_primary_ids(const RenderParams& P, uint32_t* leaf_id, uin
                                    cudaStream_t stream);
 cudaError_t zbk_launch_resolve(const float4* accum, size_t n, float scale, float4* out_f4, double* out_f64,
                                cudaStream_t stream);
+cudaError_t zbk_launch_probe(const RenderParams& P, size_t n, const float* org, const float* dir, zb_probe* out,
+                             cudaStream_t stream);

@@ -82,7 +82,7 @@ ZB_DEV void tri_surface(const SceneDev& sc, uint32_t tri, float3 o, float3 d, Su
 }
 
 // Rebuild the reference's final hit_record for the winning item.
-ZB_DEV void make_surface(const SceneDev& sc, const Hit& hit, float3 o, float3 d, Surface& sf) {
+ZB_DEV void make_surface(const SceneDev& sc, const Hit& hit, float3 o, float3 d, Surface& sf, bool force_uv = false) {
     float4 g = __ldg(sc.items + 2 * size_t(hit.item));
     float4 mf = __ldg(sc.items + 2 * size_t(hit.item) + 1);
     uint32_t kf = __float_as_uint(mf.x), kind = kf & 0xFFu, aux = __float_as_uint(mf.w);
@@ -94,7 +94,7 @@ ZB_DEV void make_surface(const SceneDev& sc, const Hit& hit, float3 o, float3 d,
     sf.m0 = load_mat0(sc, sf.material);
     sf.m1 = load_mat1(sc, sf.material);
     // sphere uv / tangent frame (sphere.hpp:44-58) feed only texture lookups and bump mapping
-    const bool want_uv = __float_as_uint(sf.m0.y) != ZB_NO_TEXTURE || __float_as_uint(sf.m0.z) != ZB_NO_TEXTURE;
+    const bool want_uv = force_uv || __float_as_uint(sf.m0.y) != ZB_NO_TEXTURE || __float_as_uint(sf.m0.z) != ZB_NO_TEXTURE;
     if (kind == ZB_ITEM_SPHERE) {
         sf.p = fma3(hit.t, d, o);
         sphere_surface(g, sf.p, d, sf, want_uv);

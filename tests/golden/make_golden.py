@@ -117,6 +117,45 @@ def make_aov(name, scene_text, cfg, files=None):
     print(name, "aov", info)
 
 
+def probe_rays(cfg, n, seed):
+    """Known-answer rays for a scene: a third camera rays through random image positions (un-normalised, as
+    get_ray builds them), the rest random origins in a ball around the look-at point with random directions of
+    random length (epsilons scale with |dir|).  float32, identical on both sides."""
+    rng = np.random.default_rng(seed)
+    lf, la = np.array(cfg.lookfrom, float), np.array(cfg.lookat, float)
+    dist = np.linalg.norm(lf - la)
+    n_cam = n // 3
+    w = (lf - la) / dist
+    u = np.cross(np.array(cfg.vup, float), w)
+    u /= np.linalg.norm(u)
+    v = np.cross(w, u)
+    half_h = np.tan(np.radians(cfg.vfov) / 2) * cfg.focus_dist
+    half_w = half_h * cfg.image_width / cfg.image_height
+    sx, sy = rng.uniform(-1, 1, n_cam), rng.uniform(-1, 1, n_cam)
+    d_cam = -cfg.focus_dist * w[None] + (sx * half_w)[:, None] * u[None] + (sy * half_h)[:, None] * v[None]
+    o_cam = np.repeat(lf[None], n_cam, 0)
+    m = n - n_cam
+    g = rng.normal(size=(m, 3))
+    o_rnd = la[None] + 0.8 * dist * g / np.linalg.norm(g, axis=1, keepdims=True) * rng.random((m, 1)) ** (1 / 3)
+    g = rng.normal(size=(m, 3))
+    d_rnd = g / np.linalg.norm(g, axis=1, keepdims=True) * rng.uniform(0.3, 3.0, (m, 1))
+    return (np.concatenate([o_cam, o_rnd]).astype(np.float32), np.concatenate([d_cam, d_rnd]).astype(np.float32))
+
+
+def make_probe(name, scene_text, cfg, files=None, n=6000, seed=99):
+    d = scratch_dir()
+    scenes.materialize(d, scene_text, cfg, files)
+    o, dr = probe_rays(cfg, n, seed)
+    with open(os.path.join(d, "rays.bin"), "wb") as f:
+        f.write(np.int32(n).tobytes() + o.tobytes() + dr.tobytes())
+    info = run_harness(["probe", "s.zscene", "s.cfg", "rays.bin", "probe.bin"], d)
+    raw = open(os.path.join(d, "probe.bin"), "rb").read()
+    rec = np.frombuffer(raw[4:], np.float64).reshape(n, 19)
+    np.savez_compressed(os.path.join(GOLDEN, f"{name}_probe.npz"), o=o, d=dr, rec=rec,
+                        digest=scene_digest(scene_text, cfg, files))
+    print(name, "probe", info, "hit fraction", float(np.isfinite(rec[:, 0]).mean()))
+
+
 def quirks_aov():
     txt, cfg, files = scenes.quirks(seed=5, width=320, height=180, spp=512)
     cfg.z_depth_max_dist = 15.0
@@ -126,6 +165,11 @@ def quirks_aov():
 def weekend_ids():
     txt, cfg = scenes.weekend(seed=1, width=1200, height=675)
     make_ids("weekend_1200x675", txt, cfg)
+
+
+def weekend_probe():
+    txt, cfg = scenes.weekend(seed=1, width=1200, height=675)
+    make_probe("weekend", txt, cfg)
 
 
 def weekend_stats():
@@ -149,11 +193,14 @@ def scene_targets():
         def stats(name=name, gen=gen, kw=kw, wh=stats_wh):
             txt, cfg, files = getattr(scenes, gen)(width=wh[0], height=wh[1], spp=256, **kw)
             make_stats(f"{name}_{wh[0]}x{wh[1]}", txt, cfg, 16, files)
-        t[f"{name}_ids"], t[f"{name}_stats"] = ids, stats
+        def probe(name=name, gen=gen, kw={**kw, **ids_kw}, wh=ids_wh):
+            txt, cfg, files = getattr(scenes, gen)(width=wh[0], height=wh[1], spp=1, **kw)
+            make_probe(name, txt, cfg, files)
+        t[f"{name}_ids"], t[f"{name}_stats"], t[f"{name}_probe"] = ids, stats, probe
     return t
 
 
-TARGETS = {"quirks_aov": quirks_aov, "weekend_ids": weekend_ids, "weekend_stats": weekend_stats, **scene_targets()}
+TARGETS = {"quirks_aov": quirks_aov, "weekend_ids": weekend_ids, "weekend_probe": weekend_probe, "weekend_stats": weekend_stats, **scene_targets()}
 
 if __name__ == "__main__":
     names = sys.argv[1:] or list(TARGETS)

@@ -202,3 +202,82 @@ def test_quirks_aovs_match_reference(gpu_ctx, tmp_path):
         # checker / silhouette pixels carry binomial jitter noise (64 samples); no systematic offset allowed
         signed = (r[key] - gold[key].astype(np.float64)).mean()
         assert diff.mean() < 8e-3 and np.quantile(diff, 0.95) < 0.05 and abs(signed) < 1e-3, (key, signed)
+
+
+# ------------------------------------------------------------------ per-ray known answers (zb_probe_rays)
+import ctypes as C  # noqa: E402
+
+
+def _leaf_has_uv(flat):
+    """leaf id -> True when the reference fills rec.u / rec.v for that object (spheres and cubes; triangles leave
+    them stale, triangle.hpp:75-79)."""
+    f = flat.contents
+    items = np.ctypeslib.as_array(C.cast(f.items, C.POINTER(C.c_uint32)), (f.n_items, 8))
+    inst = (np.ctypeslib.as_array(C.cast(f.instances, C.POINTER(C.c_uint32)), (f.n_instances, 32))
+            if f.n_instances else np.zeros((1, 32), np.uint32))
+    has = np.zeros(f.n_leaves, bool)
+    for row in items:
+        kind, leaf, aux = row[4] & 0xFF, row[6], row[7]
+        if kind == 3:
+            kind = {0: 0, 1: 1, 2: 2, 3: 2}[int(inst[aux, 24])]
+        has[leaf] = kind in (0, 1)
+    return has
+
+
+PROBE_SCENES = ["weekend"] + list(GOLDEN_SCENES)
+
+
+@pytest.mark.parametrize("name", PROBE_SCENES)
+def test_probe_hit_records_match_reference(name, gpu_ctx, tmp_path):
+    """6000 rays per scene (camera rays + random rays, many starting inside objects): leaf id, t, hit point,
+    normal, front_face (Appendix A q1/q2/q5), u/v, material::get_albedo, emitted and the background colour of
+    misses against the reference's hit_record for the same float32 rays."""
+    gold = np.load(os.path.join(GOLDEN, f"{name}_probe.npz"))
+    if name == "weekend":
+        txt, cfg = scenes.weekend(seed=1, width=1200, height=675)
+        files = {}
+    else:
+        gen, kw, wh, _, ids_kw = GOLDEN_SCENES[name]
+        txt, cfg, files = getattr(scenes, gen)(width=wh[0], height=wh[1], spp=1, **{**kw, **ids_kw})
+    assert scene_digest(txt, cfg, files) == str(gold["digest"])
+    flat = api.flatten_zscene(path=scenes.materialize(str(tmp_path), txt, cfg, files))
+    has_uv = _leaf_has_uv(flat)
+    sc = gpu_ctx.upload(flat)
+    api.free_flat(flat)
+    r = sc.probe(cfg, gold["o"], gold["d"])
+    sc.close()
+    ref = gold["rec"]
+    ref_hit = np.isfinite(ref[:, 0])
+    ref_leaf = np.where(ref_hit, ref[:, 1], -1).astype(np.int64)
+    gpu_leaf = np.where(r["leaf_id"] == 0xFFFFFFFF, -1, r["leaf_id"].astype(np.int64))
+    same = ref_leaf == gpu_leaf
+    print(f"{name}: leaf agreement {same.mean() * 100:.3f} % of {len(same)} rays ({ref_hit.mean() * 100:.1f} % hits)")
+    assert same.mean() >= 0.998
+    h = same & ref_hit
+    scale = np.maximum(np.abs(ref[h, 4:7]).max(axis=1), 1.0)
+    rel_t = np.abs(r["t"][h] - ref[h, 0]) / np.maximum(np.abs(ref[h, 0]), 1e-6)
+    dp = np.abs(r["p"][h] - ref[h, 4:7]).max(axis=1) / scale
+    dn = np.abs(r["normal"][h] - ref[h, 7:10]).max(axis=1)
+    ff = r["front_face"][h] == ref[h, 3].astype(np.uint32)
+    print(f"  t rel q99.9 {np.quantile(rel_t, 0.999):.2e}  p q99.9 {np.quantile(dp, 0.999):.2e}  "
+          f"normal q99 {np.quantile(dn, 0.99):.2e}  front_face {ff.mean() * 100:.3f} %")
+    assert np.quantile(rel_t, 0.999) < 5e-4 and np.quantile(dp, 0.999) < 1e-3
+    assert np.quantile(dn, 0.99) < 5e-3 and ff.mean() >= 0.999
+    uvm = h.copy()
+    uvm[h] = has_uv[ref_leaf[h]]
+    if uvm.any():
+        du = np.abs(r["u"][uvm] - ref[uvm, 10])
+        du = np.minimum(du, 1.0 - du)
+        dv = np.abs(r["v"][uvm] - ref[uvm, 11])
+        print(f"  uv: {uvm.sum()} rays, u q99 {np.quantile(du, 0.99):.2e} v q99 {np.quantile(dv, 0.99):.2e}")
+        assert np.quantile(du, 0.99) < 2e-3 and np.quantile(dv, 0.99) < 2e-3
+    da = np.abs(r["albedo"][h] - ref[h, 12:15]).max(axis=1)
+    de = np.abs(r["emitted"][h] - ref[h, 15:18]).max(axis=1)
+    print(f"  albedo within 2e-3: {(da < 2e-3).mean() * 100:.2f} %  emitted max diff {de.max():.2e}")
+    assert (da < 2e-3).mean() >= 0.98 and de.max() < 1e-3
+    m = same & ~ref_hit
+    if m.any():
+        bg_ref = ref[m, 12:15]
+        db = np.abs(r["albedo"][m] - bg_ref).max(axis=1) / np.maximum(bg_ref.max(axis=1), 1e-3)
+        print(f"  background within 1e-3 rel: {(db < 1e-3).mean() * 100:.2f} % of {m.sum()} misses")
+        assert (db < 1e-3).mean() >= 0.98
