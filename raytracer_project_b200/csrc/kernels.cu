@@ -6,9 +6,23 @@
 //   k_resolve     K5: sums -> means, float4 or the reference's double RGB.
 // Replaces render_rows (camera.hpp:430-554).  No tensor cores: nothing here is a dense contraction.
 #include "kernels.h"
-#include "render_pool.cuh"
-#include <cstdlib>
-#include <string>
+#include "shade.cuh"
+
+#define ZB_FIX_SCALE 4194304.0f
+#define ZB_FIX_INV (1.0 / 4194304.0)
+
+// 64-bit shared-memory add from two native 32-bit atomics (a 64-bit ATOMS add is a CAS spin loop):
+// the low word wraps, and exactly the operation whose addition wrapped it carries one into the high
+// word, so (hi, lo) ends as the exact sum whatever the order.  Radiance is never negative.
+ZB_DEV void fix_add(unsigned long long* slot, float v) {
+    const unsigned long long q = __float2ull_rn(fmaxf(v, 0.f) * ZB_FIX_SCALE);
+    const uint32_t ql = uint32_t(q), qh = uint32_t(q >> 32);
+    uint32_t* w = reinterpret_cast<uint32_t*>(slot);
+    const uint32_t old = atomicAdd(w, ql);
+    const uint32_t up = qh + (old + ql < old ? 1u : 0u);
+    if (up) atomicAdd(w + 1, up);
+}
+ZB_DEV float fix_get(unsigned long long v) { return float(double((long long)v) * ZB_FIX_INV); }
 
 // Work decomposition.  A block renders a 16x8 pixel tile (tiles are dealt to ranks round-robin for the
 // tile-stripe partition); each of its four warps owns an 8x4 sub-tile and works through the
@@ -271,16 +285,10 @@ __global__ void __launch_bounds__(256) k_resolve(const float4* __restrict__ accu
 
 cudaError_t zbk_launch_render(const RenderParams& P, int n_tiles_owned, bool stats, cudaStream_t stream) {
     if (n_tiles_owned <= 0) return cudaSuccess;
-    // ZB_KERNEL=pool selects the shared-memory ray-pool variant (render_pool.cuh), kept for A/B runs: it was
-    // measured 20-40 % slower than k_render on the headline frame (profiles/r01_pool_vs_queue.txt)
-    static const bool use_queue = [] { const char* e = std::getenv("ZB_KERNEL"); return !(e && std::string(e) == "pool"); }();
-    if (use_queue) {
-        if (stats) k_render<true><<<n_tiles_owned, ZB_BLOCK_THREADS, 0, stream>>>(P);
-        else k_render<false><<<n_tiles_owned, ZB_BLOCK_THREADS, 0, stream>>>(P);
-    } else {
-        if (stats) k_render_pool<true><<<n_tiles_owned, ZB_BLOCK_THREADS, 0, stream>>>(P);
-        else k_render_pool<false><<<n_tiles_owned, ZB_BLOCK_THREADS, 0, stream>>>(P);
-    }
+    // A shared-memory ray-pool variant of this kernel was measured 20-40 % slower on the headline frame
+    // (profiles/r01_pool_vs_queue.txt) and removed.
+    if (stats) k_render<true><<<n_tiles_owned, ZB_BLOCK_THREADS, 0, stream>>>(P);
+    else k_render<false><<<n_tiles_owned, ZB_BLOCK_THREADS, 0, stream>>>(P);
     return cudaGetLastError();
 }
 

@@ -197,43 +197,84 @@ struct RayBox {
 // ZB_TRAVERSAL_DONE is the sentinel at the bottom of the stack.
 #define ZB_TRAVERSAL_DONE ((int)0x80000001)
 
-// "while-while" traversal (Aila & Laine 2009): every lane first descends through inner nodes until it
-// holds a leaf, then the warp runs the primitive tests together; this keeps more lanes on the same
-// instruction than one loop that alternates between a node step and a leaf step per lane.
-//
-// The whole traversal state lives in this struct (step() is one descent + one leaf), so a caller may
-// interleave other work between steps.
-struct Traversal {
-    int cur, sp;
-    bool in_blas;
-    uint32_t blas_item;
-    float3 ro, rd;  // ray in the current frame (world, or the object space of the instance being traversed)
-    RayBox rb;
-    Hit hit;
-    int stack[ZB_STACK];
-
-    ZB_DEV void begin(const SceneDev& sc, float3 o, float3 d, float tmax) {
-        hit.t = tmax;
-        hit.item = 0xFFFFFFFFu;
-        hit.prim = 0;
-        stack[0] = ZB_TRAVERSAL_DONE;
-        sp = 1;
-        cur = sc.n_nodes ? 0 : ZB_TRAVERSAL_DONE;
-        in_blas = false;
-        blas_item = 0;
-        ro = o;
-        rd = d;
-        rb.set(ro, rd);
+// primitive tests of TLAS leaf `code` (items first .. first + n).  Returns true when the ray has to dive
+// into a mesh BLAS: the rest of the leaf, the exit marker and the BLAS root are then on the stack and
+// (ro, rd) is the ray in the object space of instance item `blas_item`.
+template <bool STATS>
+ZB_DEV bool tlas_leaf(const SceneDev& sc, uint32_t code, float3 o, float3 d, float tmin, const MediumRng& rng, Hit& hit,
+                      int* stack, int& sp, float3& ro, float3& rd, uint32_t& blas_item, Counters& cnt) {
+    const uint32_t first = code >> 3, end = first + (code & 7u) + 1u;
+    for (uint32_t i = first; i < end; i++) {
+        float4 g = __ldg(sc.items + 2 * size_t(i));
+        float4 mf = __ldg(sc.items + 2 * size_t(i) + 1);
+        uint32_t kind = __float_as_uint(mf.x) & 0xFFu, aux = __float_as_uint(mf.w);
+        if (STATS) cnt.prims++;
+        float t;
+        if (kind == ZB_ITEM_SPHERE) {
+            if (hit_sphere(g, o, d, tmin, hit.t, t)) { hit.t = t; hit.item = i; }
+        } else if (kind == ZB_ITEM_INSTANCE) {
+            InstanceHead ih = load_instance_head(sc, aux);
+            if (STATS) cnt.insts++;
+            float3 lo = xform_point(ih.w2o, o), ld = xform_vector(ih.w2o, d);
+            if (ih.geom_kind == ZB_GEOM_MESH) {
+                // defer the rest of this leaf, then dive into the BLAS in object space
+                if (sp + 3 > ZB_STACK) return false;
+                if (i + 1 < end) stack[sp++] = int(~(((i + 1) << 3) | (end - i - 2)));
+                stack[sp++] = ZB_EXIT_INSTANCE;
+                stack[sp++] = int(ih.node_root);
+                blas_item = i;
+                ro = lo;
+                rd = ld;
+                return true;
+            }
+            if (hit_simple_geom(sc, ih.geom_kind, ih.geom_index, lo, ld, tmin, hit.t, t)) {
+                hit.t = t;
+                hit.item = i;
+                hit.prim = ih.geom_index;
+            }
+        } else if (kind == ZB_ITEM_CUBE) {
+            if (hit_cube(f3(__ldg(sc.cubes + 2 * size_t(aux))), o, d, tmin, hit.t, t)) { hit.t = t; hit.item = i; }
+        } else if (kind == ZB_ITEM_TRIANGLE) {
+            const float4* tp = sc.tris + 3 * size_t(aux);
+            if (hit_tri(f3(__ldg(tp)), f3(__ldg(tp + 1)), f3(__ldg(tp + 2)), o, d, tmin, hit.t, t)) {
+                hit.t = t;
+                hit.item = i;
+                hit.prim = aux;
+            }
+        } else {  // ZB_ITEM_MEDIUM
+            if (hit_medium(sc, aux, o, d, tmin, hit.t, rng, t)) { hit.t = t; hit.item = i; }
+        }
     }
-    ZB_DEV bool finished() const { return cur == ZB_TRAVERSAL_DONE; }
+    return false;
+}
 
-    // One descent to the next leaf and its primitive tests.  (o, d) is the world-space ray of begin().
-    template <bool STATS>
-    ZB_DEV void step(const SceneDev& sc, float3 o, float3 d, float tmin, const MediumRng& rng, Counters& cnt) {
+// Closest hit of one ray.  "while-while" traversal (Aila & Laine 2009): every lane first descends through
+// inner nodes until it holds a leaf, then the warp runs the primitive tests together; this keeps more
+// lanes on the same instruction than one loop that alternates between a node step and a leaf step.
+// Only the stack is addressed dynamically (local memory); every other piece of traversal state is a
+// scalar the compiler keeps in registers, and the four-way child selection is written as selects plus
+// one predicated push / pop so that the node step has no divergent branches.
+template <bool STATS>
+ZB_DEV bool trace(const SceneDev& sc, float3 o, float3 d, float tmin, float tmax, const MediumRng& rng, Hit& hit,
+                  Counters& cnt) {
+    int stack[ZB_STACK];
+    cnt.rays++;
+    hit.t = tmax;
+    hit.item = 0xFFFFFFFFu;
+    hit.prim = 0;
+    stack[0] = ZB_TRAVERSAL_DONE;
+    int sp = 1;
+    int cur = sc.n_nodes ? 0 : ZB_TRAVERSAL_DONE;
+    bool in_blas = false;
+    uint32_t blas_item = 0;
+    float3 ro = o, rd = d;  // ray in the current frame (world, or the object space of the instance traversed)
+    RayBox rb;
+    rb.set(o, d);
+    while (cur != ZB_TRAVERSAL_DONE) {
         while (cur >= 0) {
             const float4* np = sc.nodes + 4 * size_t(cur);
-            float4 n0 = __ldg(np), n1 = __ldg(np + 1), n2 = __ldg(np + 2);
-            float4 nc = __ldg(np + 3);
+            const float4 n0 = __ldg(np), n1 = __ldg(np + 1), n2 = __ldg(np + 2);
+            const float2 nc = __ldg(reinterpret_cast<const float2*>(np + 3));
             if (STATS) cnt.nodes++;
             float lx0 = fmaf(n0.x, rb.inv.x, -rb.ood.x), lx1 = fmaf(n0.y, rb.inv.x, -rb.ood.x);
             float ly0 = fmaf(n0.z, rb.inv.y, -rb.ood.y), ly1 = fmaf(n0.w, rb.inv.y, -rb.ood.y);
@@ -245,45 +286,27 @@ struct Traversal {
             float lf = fminf(min3(fmaxf(lx0, lx1), fmaxf(ly0, ly1), fmaxf(lz0, lz1)), hit.t) * ZB_BOX_INFLATE;
             float rn = fmaxf(max3(fminf(rx0, rx1), fminf(ry0, ry1), fminf(rz0, rz1)), tmin);
             float rf = fminf(min3(fmaxf(rx0, rx1), fmaxf(ry0, ry1), fmaxf(rz0, rz1)), hit.t) * ZB_BOX_INFLATE;
-            bool hl = ln <= lf, hr = rn <= rf;
-            int cl = __float_as_int(nc.x), cr = __float_as_int(nc.y);
+            const bool hl = ln <= lf, hr = rn <= rf;
+            const int cl = __float_as_int(nc.x), cr = __float_as_int(nc.y);
+            const bool right_first = hr && (!hl || rn < ln);
+            int next = right_first ? cr : cl;
             if (hl && hr) {
-                bool swap = rn < ln;
-                int farc = swap ? cl : cr;
-                cur = swap ? cr : cl;
-                if (sp < ZB_STACK) stack[sp++] = farc;
-            } else if (hl) {
-                cur = cl;
-            } else if (hr) {
-                cur = cr;
-            } else {
-                cur = stack[--sp];
+                stack[sp] = right_first ? cl : cr;
+                sp = min(sp + 1, ZB_STACK - 1);  // deeper than any tree the host builder emits (bvh_build.hpp)
             }
+            if (!(hl || hr)) next = stack[--sp];
+            cur = next;
         }
-        if (cur == ZB_TRAVERSAL_DONE) return;
+        if (cur == ZB_TRAVERSAL_DONE) break;
         if (cur == ZB_EXIT_INSTANCE) {
             in_blas = false;
             ro = o;
             rd = d;
-            rb.set(ro, rd);
-        } else {
-            leaf<STATS>(sc, o, d, tmin, rng, cnt);
-        }
-        cur = stack[--sp];
-    }
-
-    // Run to completion (single ray, no warp cooperation).
-    template <bool STATS>
-    ZB_DEV void run(const SceneDev& sc, float3 o, float3 d, float tmin, const MediumRng& rng, Counters& cnt) {
-        while (cur != ZB_TRAVERSAL_DONE) step<STATS>(sc, o, d, tmin, rng, cnt);
-    }
-
-    // primitive tests of the leaf encoded in `cur` (TLAS items, or the triangles of a mesh BLAS)
-    template <bool STATS>
-    ZB_DEV void leaf(const SceneDev& sc, float3 o, float3 d, float tmin, const MediumRng& rng, Counters& cnt) {
-        uint32_t code = ~uint32_t(cur);
-        uint32_t first = code >> 3, end = first + (code & 7u) + 1u;
-        if (in_blas) {
+            rb.set(o, d);
+        } else if (in_blas) {
+            // triangles of a mesh BLAS leaf, in object space
+            const uint32_t code = ~uint32_t(cur);
+            const uint32_t first = code >> 3, end = first + (code & 7u) + 1u;
             for (uint32_t i = first; i < end; i++) {
                 const float4* tp = sc.tris + 3 * size_t(i);
                 float4 a = __ldg(tp), b = __ldg(tp + 1), c = __ldg(tp + 2);
@@ -295,63 +318,11 @@ struct Traversal {
                     hit.prim = i;
                 }
             }
-            return;
+        } else if (tlas_leaf<STATS>(sc, ~uint32_t(cur), o, d, tmin, rng, hit, stack, sp, ro, rd, blas_item, cnt)) {
+            in_blas = true;
+            rb.set(ro, rd);
         }
-        for (uint32_t i = first; i < end; i++) {
-            float4 g = __ldg(sc.items + 2 * size_t(i));
-            float4 mf = __ldg(sc.items + 2 * size_t(i) + 1);
-            uint32_t kind = __float_as_uint(mf.x) & 0xFFu, aux = __float_as_uint(mf.w);
-            if (STATS) cnt.prims++;
-            float t;
-            if (kind == ZB_ITEM_SPHERE) {
-                if (hit_sphere(g, o, d, tmin, hit.t, t)) { hit.t = t; hit.item = i; }
-            } else if (kind == ZB_ITEM_INSTANCE) {
-                InstanceHead ih = load_instance_head(sc, aux);
-                if (STATS) cnt.insts++;
-                float3 lo = xform_point(ih.w2o, o), ld = xform_vector(ih.w2o, d);
-                if (ih.geom_kind == ZB_GEOM_MESH) {
-                    // defer the rest of this leaf, then dive into the BLAS in object space
-                    if (sp + 3 <= ZB_STACK) {
-                        if (i + 1 < end) stack[sp++] = int(~(((i + 1) << 3) | (end - i - 2)));
-                        stack[sp++] = ZB_EXIT_INSTANCE;
-                        stack[sp++] = int(ih.node_root);
-                        in_blas = true;
-                        blas_item = i;
-                        ro = lo;
-                        rd = ld;
-                        rb.set(ro, rd);
-                    }
-                    return;
-                }
-                if (hit_simple_geom(sc, ih.geom_kind, ih.geom_index, lo, ld, tmin, hit.t, t)) {
-                    hit.t = t;
-                    hit.item = i;
-                    hit.prim = ih.geom_index;
-                }
-            } else if (kind == ZB_ITEM_CUBE) {
-                if (hit_cube(f3(__ldg(sc.cubes + 2 * size_t(aux))), o, d, tmin, hit.t, t)) { hit.t = t; hit.item = i; }
-            } else if (kind == ZB_ITEM_TRIANGLE) {
-                const float4* tp = sc.tris + 3 * size_t(aux);
-                if (hit_tri(f3(__ldg(tp)), f3(__ldg(tp + 1)), f3(__ldg(tp + 2)), o, d, tmin, hit.t, t)) {
-                    hit.t = t;
-                    hit.item = i;
-                    hit.prim = aux;
-                }
-            } else {  // ZB_ITEM_MEDIUM
-                if (hit_medium(sc, aux, o, d, tmin, hit.t, rng, t)) { hit.t = t; hit.item = i; }
-            }
-        }
+        cur = stack[--sp];
     }
-};
-
-// Closest hit of one ray, run to completion (used by the primary-id kernel).
-template <bool STATS>
-ZB_DEV bool trace(const SceneDev& sc, float3 o, float3 d, float tmin, float tmax, const MediumRng& rng, Hit& hit,
-                  Counters& cnt) {
-    Traversal tv;
-    cnt.rays++;
-    tv.begin(sc, o, d, tmax);
-    tv.run<STATS>(sc, o, d, tmin, rng, cnt);
-    hit = tv.hit;
     return hit.item != 0xFFFFFFFFu;
 }
