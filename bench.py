@@ -32,7 +32,17 @@ sys.path.insert(0, ROOT)
 
 WIDTH, HEIGHT, SPP, DEPTH = 1920, 1080, 64, 50
 WORKLOAD = f"weekend_seed1_{WIDTH}x{HEIGHT}_{SPP}spp_depth{DEPTH}"
-HARNESS = os.path.join(ROOT, "oracle", "_ref", "ref_harness")
+HARNESS = os.path.join(ROOT, "oracle", "_ref", "ref_harness")   # the unmodified reference (kind "reference")
+PORT = os.path.join(ROOT, "oracle", "_build", "zoracle")         # CPU restatement, used only if the former is absent
+
+
+def cpu_arm():
+    """(binary, kind) of the CPU arm: the compiled reference if it travelled with the repo, else the restatement."""
+    if os.path.exists(HARNESS):
+        return HARNESS, "reference"
+    if not os.path.exists(PORT):
+        subprocess.run(["make", "-C", os.path.join(ROOT, "oracle"), "port"], check=True, capture_output=True)
+    return PORT, "port"
 
 
 def measured_peaks():
@@ -47,17 +57,18 @@ def measured_peaks():
 def run_reference_sample(spp: int):
     """Time the reference's camera::initialize + execute_render_threads on this box's host cores."""
     from raytracer_project_b200 import scenes
-    if not os.path.exists(HARNESS):
-        raise RuntimeError(f"{HARNESS} missing: build it with `make -C oracle ref` where /root/reference exists")
+    binary, kind = cpu_arm()
     txt, cfg = scenes.weekend(seed=1, width=WIDTH, height=HEIGHT, spp=spp, max_depth=DEPTH)
     d = tempfile.mkdtemp(prefix="zb_cpu_")
     try:
         os.makedirs(os.path.join(d, "assets", "hdr_maps"))  # camera::initialize side effect (camera.hpp:123-140)
         open(os.path.join(d, "s.zscene"), "w").write(txt)
         open(os.path.join(d, "s.cfg"), "w").write(cfg.to_text())
-        out = subprocess.run([HARNESS, "render", "s.zscene", "s.cfg", "-"], cwd=d, check=True, capture_output=True,
+        out = subprocess.run([binary, "render", "s.zscene", "s.cfg", "-"], cwd=d, check=True, capture_output=True,
                              text=True).stdout
-        return json.loads(out.strip().splitlines()[-1])
+        r = json.loads(out.strip().splitlines()[-1])
+        r["kind"] = kind
+        return r
     finally:
         shutil.rmtree(d, ignore_errors=True)
 
@@ -69,11 +80,11 @@ def reference_arm(args):
     spp = 4
     for _ in range(args.warmup):
         run_reference_sample(spp)
-    secs, threads, paths = [], 0, 0.0
+    secs, threads, paths, kind = [], 0, 0.0, "reference"
     for _ in range(args.steps):
         r = run_reference_sample(spp)
         secs.append(r["seconds"])
-        threads, paths = r["threads"], r["paths"]
+        threads, paths, kind = r["threads"], r["paths"], r["kind"]
     ms = 1e3 * sum(secs) / len(secs)
     value = paths / (ms * 1e-3) * 1e-6
     sample = f"{WIDTH}x{HEIGHT} x {spp} spp of the same scene and camera per step (Mpaths/s is spp-independent)"
@@ -82,7 +93,7 @@ def reference_arm(args):
         "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True,
         "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
         "config": {"workload": WORKLOAD, "sample": sample},
-        "cpu_baseline": {"value": value, "unit": "Mpaths/s", "cores": threads, "kind": "reference", "sample": sample},
+        "cpu_baseline": {"value": value, "unit": "Mpaths/s", "cores": threads, "kind": kind, "sample": sample},
         "e2e": {"value": value, "unit": "Mpaths/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
@@ -290,7 +301,7 @@ def ours(args):
                 spp_cpu = 8
                 r = run_reference_sample(spp_cpu)
                 line["cpu_baseline"] = {
-                    "value": r["mpaths_per_s"], "unit": "Mpaths/s", "cores": r["threads"], "kind": "reference",
+                    "value": r["mpaths_per_s"], "unit": "Mpaths/s", "cores": r["threads"], "kind": r["kind"],
                     "sample": f"{WIDTH}x{HEIGHT} x {spp_cpu} spp of the same scene and camera, {r['seconds']:.1f} s "
                               "(reference renders with std::thread x hardware_concurrency, camera.hpp:426)"}
             except Exception as e:  # the harness is prebuilt in the build container; report, don't hide
