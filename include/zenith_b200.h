@@ -22,7 +22,7 @@
 extern "C" {
 #endif
 
-#define ZB_ABI_VERSION 1
+#define ZB_ABI_VERSION 2
 
 typedef enum zb_status {
     ZB_OK = 0,
@@ -201,6 +201,13 @@ typedef struct zb_render_opts {
     double z_depth_max_dist;
     int32_t collect_stats;            /* 1: STATS kernel variant (node visits / primitive tests) */
     int32_t samples_per_launch;       /* 0 = library default; cancel is polled between launches   */
+    /* camera::use_reflection / use_refraction (camera.hpp:56-57): the two light passes of render_rows
+     * (camera.hpp:492-517).  zb_render fills zb_outputs::reflection / refraction when set; for
+     * zb_render_device, light_pass = 1 renders the light passes INSTEAD of the beauty pass: reflection
+     * sums go to accum_f4 and refraction sums to the first W*H float4 of accum_aux_f4. */
+    int32_t use_reflection, use_refraction;
+    int32_t light_pass;
+    int32_t pad;
 } zb_render_opts;
 
 /* Host-side outputs in the reference's own layout: row-major, top row first, 3 doubles per pixel
@@ -211,6 +218,8 @@ typedef struct zb_outputs {
     double* normal;  /* normal_buffer      */
     double* z_depth; /* z_depth_buffer     */
     float* beauty_f4; /* optional: RGBA32F mean radiance, 4 floats per pixel */
+    double* reflection; /* reflection_buffer (needs opts.use_reflection) */
+    double* refraction; /* refraction_buffer (needs opts.use_refraction) */
 } zb_outputs;
 
 typedef struct zb_stats {

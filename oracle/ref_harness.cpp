@@ -179,6 +179,8 @@ static void apply_camera(const config& c, camera& cam) {
     cam.use_albedo_buffer = c.num("use_albedo", 0) != 0;
     cam.use_normal_buffer = c.num("use_normal", 0) != 0;
     cam.use_z_depth_buffer = c.num("use_z_depth", 0) != 0;
+    cam.use_reflection = c.num("use_reflection", 0) != 0;
+    cam.use_refraction = c.num("use_refraction", 0) != 0;
 }
 
 static void apply_env(const config& c, const std::string& base_dir, EnvironmentSettings& env) {
@@ -336,6 +338,8 @@ static int cmd_render(const std::string& scene, const std::string& cfg, const st
         write_colors(f, cam.albedo_buffer);
         write_colors(f, cam.normal_buffer);
         write_colors(f, cam.z_depth_buffer);
+        write_colors(f, cam.reflection_buffer);
+        write_colors(f, cam.refraction_buffer);
         std::fclose(f);
     }
     double paths = double(cam.image_width) * cam.image_height * cam.samples_per_pixel;

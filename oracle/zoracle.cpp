@@ -546,7 +546,7 @@ struct cam_t {
     double vfov = 30, defocus_angle = 0, focus_dist = 10, z_max = 20;
     point3 lookfrom = point3(10, 1.5, 0), lookat = point3(0, 0, 0);
     vec3 vup = vec3(0, 1, 0);
-    bool use_albedo = false, use_normal = false, use_z = false;
+    bool use_albedo = false, use_normal = false, use_z = false, use_reflection = false, use_refraction = false;
     // derived (camera.hpp:346-353)
     point3 center, pixel00;
     vec3 du, dv, u, v, w, disk_u, disk_v;
@@ -565,6 +565,8 @@ struct cam_t {
         use_normal = c.num("use_normal", 0) != 0;
         use_z = c.num("use_z_depth", 0) != 0;
         z_max = c.num("z_depth_max_dist", 20.0);
+        use_reflection = c.num("use_reflection", 0) != 0;
+        use_refraction = c.num("use_refraction", 0) != 0;
     }
     void initialize() {  // camera.hpp:358-402
         double aspect = double(W) / H;
@@ -803,7 +805,7 @@ int cmd_probe(const std::string& scene, const std::string& cfg, const std::strin
     return 0;
 }
 
-// render_rows (camera.hpp:430-554) without the light passes; rows are independent and seeded by (seed, row)
+// render_rows (camera.hpp:430-554); rows are independent and seeded by (seed, row)
 int cmd_render(const std::string& scene, const std::string& cfg, const std::string& out, unsigned long long seed) {
     auto world = load_scene(scene);
     config c = config::load(cfg);
@@ -813,7 +815,7 @@ int cmd_render(const std::string& scene, const std::string& cfg, const std::stri
     load_env(c, dir_of(cfg), env);
     const int W = cam.W, H = cam.H, spp = cam.spp;
     const size_t n = size_t(W) * H;
-    std::vector<color> beauty(n), albedo(n), normal(n), zdepth(n);
+    std::vector<color> beauty(n), albedo(n), normal(n), zdepth(n), reflection(n), refraction(n);
     unsigned long long rays = 0;
     auto t0 = std::chrono::steady_clock::now();
     cam.initialize();
@@ -823,7 +825,7 @@ int cmd_render(const std::string& scene, const std::string& cfg, const std::stri
     for (int j = 0; j < H; j++) {
         tl_gen.seed(seed * 0x9E3779B97F4A7C15ull + j);
         for (int i = 0; i < W; i++) {
-            color pc(0, 0, 0), pa(0, 0, 0), pn(0, 0, 0), pz(0, 0, 0);
+            color pc(0, 0, 0), pa(0, 0, 0), pn(0, 0, 0), pz(0, 0, 0), prefl(0, 0, 0), prefr(0, 0, 0);
             for (int s = 0; s < spp; s++) {
                 ray r = cam.get_ray(i, j);
                 hit_rec rec;
@@ -841,6 +843,19 @@ int cmd_render(const std::string& scene, const std::string& cfg, const std::stri
                             pz += color(z, z, z);
                         }
                     }
+                    if (cam.use_reflection || cam.use_refraction) {  // light passes, camera.hpp:492-517
+                        ray scattered;
+                        color attenuation;
+                        if (material_scatter(*rec.mat, r, rec, attenuation, scattered)) {
+                            unsigned long long unused = 0;  // light-pass rays are not counted
+                            color sc = ray_color(scattered, *world, cam.max_depth - 1, env, unused);
+                            double luma = 0.2126 * sc.length();  // vector length, not luminance
+                            if (luma > 2.0) sc *= (2.0 / luma);
+                            vec3 mirror = reflect(unit_vector(r.d), unit_vector(rec.normal));
+                            if (dot(unit_vector(scattered.d), mirror) > 0.9) prefl += attenuation * sc;
+                            else if (dot(scattered.d, rec.normal) < 0) prefr += attenuation * sc;
+                        }
+                    }
                 } else {
                     pc += background(r, env);
                     if (s < aux_sample && cam.use_normal) pn += color(0.5, 0.5, 1.0);  // camera.hpp:518-526
@@ -851,6 +866,8 @@ int cmd_render(const std::string& scene, const std::string& cfg, const std::stri
             albedo[idx] = pa * aux_scale;
             normal[idx] = pn * aux_scale;
             zdepth[idx] = pz * aux_scale;
+            reflection[idx] = prefl * light_scale;
+            refraction[idx] = prefr * light_scale;
         }
     }
     double secs = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
@@ -858,7 +875,7 @@ int cmd_render(const std::string& scene, const std::string& cfg, const std::stri
         FILE* f = std::fopen(out.c_str(), "wb");
         if (!f) return 2;
         write_header(f, W, H);
-        for (auto* buf : {&beauty, &albedo, &normal, &zdepth})
+        for (auto* buf : {&beauty, &albedo, &normal, &zdepth, &reflection, &refraction})
             for (const color& v : *buf) {
                 double e[3] = {v.x(), v.y(), v.z()};
                 std::fwrite(e, 8, 3, f);

@@ -66,12 +66,13 @@ class RenderOpts(C.Structure):
                 ("sample_begin", C.c_int32), ("sample_end", C.c_int32), ("tile_rank", C.c_int32),
                 ("tile_ranks", C.c_int32), ("use_albedo", C.c_int32), ("use_normal", C.c_int32),
                 ("use_z_depth", C.c_int32), ("z_depth_max_dist", C.c_double), ("collect_stats", C.c_int32),
-                ("samples_per_launch", C.c_int32)]
+                ("samples_per_launch", C.c_int32), ("use_reflection", C.c_int32), ("use_refraction", C.c_int32),
+                ("light_pass", C.c_int32), ("pad", C.c_int32)]
 
 
 class Outputs(C.Structure):
     _fields_ = [("beauty", C.c_void_p), ("albedo", C.c_void_p), ("normal", C.c_void_p), ("z_depth", C.c_void_p),
-                ("beauty_f4", C.c_void_p)]
+                ("beauty_f4", C.c_void_p), ("reflection", C.c_void_p), ("refraction", C.c_void_p)]
 
 
 class Stats(C.Structure):

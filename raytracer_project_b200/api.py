@@ -64,6 +64,7 @@ def opts_struct(cfg: RenderConfig, seed=1, sample_range=None, tile=None, stats=F
     o.z_depth_max_dist = cfg.z_depth_max_dist
     o.collect_stats = int(stats)
     o.samples_per_launch = samples_per_launch
+    o.use_reflection, o.use_refraction = int(cfg.use_reflection), int(cfg.use_refraction)
     return o
 
 
@@ -120,7 +121,8 @@ class Scene:
         out = Outputs()
         res = {"beauty": np.empty((cfg.image_height, cfg.image_width, 3), np.float64)}
         out.beauty = res["beauty"].ctypes.data
-        for key, flag in (("albedo", cfg.use_albedo), ("normal", cfg.use_normal), ("z_depth", cfg.use_z_depth)):
+        for key, flag in (("albedo", cfg.use_albedo), ("normal", cfg.use_normal), ("z_depth", cfg.use_z_depth),
+                          ("reflection", cfg.use_reflection), ("refraction", cfg.use_refraction)):
             if flag:
                 res[key] = np.empty((cfg.image_height, cfg.image_width, 3), np.float64)
                 setattr(out, key, res[key].ctypes.data)
@@ -135,10 +137,12 @@ class Scene:
         return res
 
     def render_device(self, cfg: RenderConfig, accum_ptr: int, aux_ptr: int = 0, seed=1, sample_range=None, tile=None,
-                      stats=False):
-        """zb_render_device: radiance SUMS of this rank's share into a device float4 buffer (async)."""
+                      stats=False, light_pass=False):
+        """zb_render_device: radiance SUMS of this rank's share into a device float4 buffer (async).
+        light_pass: reflection sums -> accum, refraction sums -> first plane of aux (camera.hpp:492-517)."""
         cam, env = camera_struct(cfg), env_struct(cfg)
         o = opts_struct(cfg, seed, sample_range, tile, stats)
+        o.light_pass = int(light_pass)
         check(self.ctx.lib.zb_render_device(self.ctx.h, self.h, C.byref(cam), C.byref(env), C.byref(o),
                                             C.c_void_p(accum_ptr), C.c_void_p(aux_ptr) if aux_ptr else None))
 

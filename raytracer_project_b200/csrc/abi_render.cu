@@ -176,6 +176,7 @@ int fill_params(zb_context* ctx, const zb_scene* scene, const zb_camera* cam, co
     if (P.tile_rank < 0 || P.tile_rank >= P.tile_ranks) return fail(ZB_ERR_INVALID, "render: bad tile rank");
     P.tiles_x = (cam->image_width + ZB_TILE_W - 1) / ZB_TILE_W;
     P.tiles_y = (cam->image_height + ZB_TILE_H - 1) / ZB_TILE_H;
+    P.light_pass = o->light_pass ? 1 : 0;
     return ZB_OK;
 }
 
@@ -287,6 +288,7 @@ extern "C" int zb_render_device(zb_context* ctx, const zb_scene* scene, const zb
     int rc = fill_params(ctx, scene, cam, env, opts, P);
     if (rc) return rc;
     if (!accum_f4) return fail(ZB_ERR_INVALID, "zb_render_device: accum_f4 is NULL");
+    if (P.light_pass && !accum_aux_f4) return fail(ZB_ERR_INVALID, "zb_render_device: light_pass needs accum_aux_f4");
     ZB_CUDA(cudaSetDevice(ctx->device));
     P.accum = static_cast<float4*>(accum_f4);
     P.accum_aux = static_cast<float4*>(accum_aux_f4);
@@ -328,8 +330,10 @@ extern "C" int zb_render(zb_context* ctx, const zb_scene* scene, const zb_camera
     if (!out) return fail(ZB_ERR_INVALID, "zb_render: outputs is NULL");
     ZB_CUDA(cudaSetDevice(ctx->device));
     const size_t pixels = size_t(cam->image_width) * cam->image_height;
+    const bool light = (opts->use_reflection && out->reflection) || (opts->use_refraction && out->refraction);
     const bool aux = out->albedo || out->normal || out->z_depth;
-    rc = ensure_scratch(ctx, pixels, aux);
+    P.light_pass = 0;
+    rc = ensure_scratch(ctx, pixels, aux || light);
     if (rc) return rc;
     P.accum = ctx->accum;
     P.accum_aux = aux ? ctx->accum_aux : nullptr;
@@ -360,6 +364,22 @@ extern "C" int zb_render(zb_context* ctx, const zb_scene* scene, const zb_camera
         rc = d2h_rgb_f64(ctx, aux_out[k], ctx->out_f4, pixels);
     }
     if (rc) return rc;
+    if (light) {
+        // reflection / refraction light passes (camera.hpp:492-517): one more pass over the same samples, with the
+        // scratch buffers of the beauty pass reused (their contents are already on the host)
+        P.light_pass = 1;
+        P.accum_aux = ctx->accum_aux;
+        rc = launch_share(ctx, P, opts, cancel, nullptr, nullptr, true);
+        double* light_out[2] = {opts->use_reflection ? out->reflection : nullptr, opts->use_refraction ? out->refraction : nullptr};
+        const float4* light_src[2] = {ctx->accum, ctx->accum_aux};
+        for (int k = 0; k < 2 && !rc; k++) {
+            if (!light_out[k]) continue;
+            ZB_CUDA(zbk_launch_resolve(light_src[k], pixels, float(scale), ctx->out_f4, nullptr, ctx->stream));
+            ctx->stats.launches++;
+            rc = d2h_rgb_f64(ctx, light_out[k], ctx->out_f4, pixels);
+        }
+        if (rc) return rc;
+    }
     ZB_CUDA(cudaEventRecord(ctx->ev[3], ctx->stream));
     rc = read_counters(ctx);
     if (rc) return rc;

@@ -33,7 +33,13 @@ ZB_DEV float fix_get(unsigned long long v) { return float(double((long long)v) *
 // as 64-bit fixed point (2^-22 units): integer addition is associative, which makes the result
 // independent of the order in which lanes finish — the frame is bit-reproducible and identical under
 // any tile / sample partition of the work.
-template <bool STATS>
+//
+// LIGHT = true renders the reflection / refraction light passes of render_rows (camera.hpp:492-517) instead of
+// the beauty pass: a second, independent scatter of the primary hit, the full ray_color estimator behind it
+// (same termination rules), the luma clamp 0.2126 |c| <= 2, and the split by direction — "specular" when the
+// scattered direction is within acos(0.9) of the mirror direction, "transmitted" when it crosses the surface.
+// Reflection sums go to accum, refraction sums to plane 0 of accum_aux.
+template <bool STATS, bool LIGHT>
 __global__ void __launch_bounds__(ZB_BLOCK_THREADS, ZB_MIN_BLOCKS) k_render(const __grid_constant__ RenderParams P) {
     constexpr int WARPS = ZB_BLOCK_THREADS / 32;
     __shared__ unsigned long long s_sum[WARPS][32][3];
@@ -44,7 +50,7 @@ __global__ void __launch_bounds__(ZB_BLOCK_THREADS, ZB_MIN_BLOCKS) k_render(cons
     const int tx = tile % P.tiles_x, ty = tile / P.tiles_x;
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int px0 = tx * ZB_TILE_W + (warp % (ZB_TILE_W / 8)) * 8, py0 = ty * ZB_TILE_H + (warp / (ZB_TILE_W / 8)) * 4;
-    const bool aux_on = P.accum_aux != nullptr;
+    const bool aux_on = LIGHT || P.accum_aux != nullptr;
 
 #pragma unroll
     for (int c = 0; c < 3; c++) s_sum[warp][lane][c] = 0ull;
@@ -57,7 +63,7 @@ __global__ void __launch_bounds__(ZB_BLOCK_THREADS, ZB_MIN_BLOCKS) k_render(cons
 
     const int n_s = P.sample_end - P.sample_begin;
     const int total = (ty < P.tiles_y && P.max_depth > 0) ? 32 * n_s : 0;
-    const Philox ph{P.seed_lo, P.seed_hi};
+    const Philox ph{P.seed_lo, LIGHT ? P.seed_hi ^ 0x4C495445u : P.seed_hi};  // the light passes draw their own stream
     Counters cnt = {0, 0, 0, 0};
     uint32_t paths = 0;
 
@@ -65,6 +71,8 @@ __global__ void __launch_bounds__(ZB_BLOCK_THREADS, ZB_MIN_BLOCKS) k_render(cons
     int p = 0, seg = 0;
     uint32_t pixel = 0, s = 0;
     float3 o = f3(0, 0, 0), d = f3(0, 0, 0), L = f3(0, 0, 0), beta = f3(1, 1, 1);
+    float3 first_atten = f3(0, 0, 0);  // LIGHT: attenuation of the primary scatter (camera.hpp:512, :515)
+    int light_class = 0;               // LIGHT: 1 reflection, 2 refraction, 0 neither
 
     // next path of this warp's queue whose pixel lies inside the image
     auto fetch = [&]() -> bool {
@@ -108,9 +116,32 @@ __global__ void __launch_bounds__(ZB_BLOCK_THREADS, ZB_MIN_BLOCKS) k_render(cons
         {
             // ---- K3 shade: one segment of ray_color (camera.hpp:928-1004)
             bool done;
-            if (hit.item == 0xFFFFFFFFu) {
+            if (LIGHT && seg == 0) {
+                // camera.hpp:492-517: second scatter of the primary hit; a primary miss contributes nothing
+                light_class = 0;
+                done = true;
+                if (hit.item != 0xFFFFFFFFu) {
+                    Surface sf;
+                    make_surface(P.sc, hit, o, d, sf);
+                    uint4 rb = ph(pixel, s, 1u, 0u);
+                    float3 no, nd;
+                    first_atten = f3(1, 1, 1);
+                    if (material_scatter(P.sc, sf, d, f3(u01(rb.x), u01(rb.y), u01(rb.z)), first_atten, no, nd)) {
+                        float3 ud = unit_vector(d), un = unit_vector(sf.n);
+                        float3 mirror = fma3(-2.0f * dot(ud, un), un, ud);
+                        if (dot(unit_vector(nd), mirror) > 0.9f) light_class = 1;
+                        else if (dot(nd, sf.n) < 0.f) light_class = 2;
+                        if (light_class) {  // otherwise the sample lands in neither buffer: skip its path
+                            o = no;
+                            d = nd;
+                            seg = 1;
+                            done = P.max_depth <= 1;
+                        }
+                    }
+                }
+            } else if (hit.item == 0xFFFFFFFFu) {
                 L += beta * background(P.sc, P.env, d);
-                if (seg == 0 && aux_on && int(s) < P.aux_samples && P.use_normal) {  // camera.hpp:518-526
+                if (!LIGHT && seg == 0 && aux_on && int(s) < P.aux_samples && P.use_normal) {  // camera.hpp:518-526
                     fix_add(&s_aux[warp][p][3], 0.5f);
                     fix_add(&s_aux[warp][p][4], 0.5f);
                     fix_add(&s_aux[warp][p][5], 1.0f);
@@ -119,7 +150,7 @@ __global__ void __launch_bounds__(ZB_BLOCK_THREADS, ZB_MIN_BLOCKS) k_render(cons
             } else {
                 Surface sf;
                 make_surface(P.sc, hit, o, d, sf);
-                if (seg == 0 && aux_on && int(s) < P.aux_samples) {  // K8 first-hit AOVs (camera.hpp:464-488)
+                if (!LIGHT && seg == 0 && aux_on && int(s) < P.aux_samples) {  // K8 first-hit AOVs (camera.hpp:464-488)
                     if (P.use_albedo) {
                         float3 a = material_get_albedo(P.sc, sf);
                         fix_add(&s_aux[warp][p][0], a.x);
@@ -152,9 +183,21 @@ __global__ void __launch_bounds__(ZB_BLOCK_THREADS, ZB_MIN_BLOCKS) k_render(cons
                 }
             }
             if (done) {
-                fix_add(&s_sum[warp][p][0], L.x);
-                fix_add(&s_sum[warp][p][1], L.y);
-                fix_add(&s_sum[warp][p][2], L.z);
+                if (LIGHT) {
+                    if (light_class) {
+                        float luma = 0.2126f * length(L);  // vector length, not luminance (camera.hpp:500)
+                        if (luma > 2.0f) L *= 2.0f / luma;
+                        L = first_atten * L;
+                        unsigned long long* dst = light_class == 1 ? s_sum[warp][p] : s_aux[warp][p];
+                        fix_add(dst + 0, L.x);
+                        fix_add(dst + 1, L.y);
+                        fix_add(dst + 2, L.z);
+                    }
+                } else {
+                    fix_add(&s_sum[warp][p][0], L.x);
+                    fix_add(&s_sum[warp][p][1], L.y);
+                    fix_add(&s_sum[warp][p][2], L.z);
+                }
                 have = fetch();
             }
         }
@@ -173,7 +216,14 @@ __global__ void __launch_bounds__(ZB_BLOCK_THREADS, ZB_MIN_BLOCKS) k_render(cons
                 acc.x += old.x; acc.y += old.y; acc.z += old.z; acc.w += old.w;
             }
             P.accum[pix] = acc;
-            if (aux_on) {
+            if (LIGHT) {
+                float4 a0 = make_float4(fix_get(s_aux[warp][lane][0]), fix_get(s_aux[warp][lane][1]), fix_get(s_aux[warp][lane][2]), float(n_s));
+                if (P.accumulate) {
+                    float4 b0 = P.accum_aux[pix];
+                    a0.x += b0.x; a0.y += b0.y; a0.z += b0.z; a0.w += b0.w;
+                }
+                P.accum_aux[pix] = a0;
+            } else if (aux_on) {
                 const size_t n = size_t(P.cam.width) * P.cam.height;
                 float z = fix_get(s_aux[warp][lane][6]);
                 float4 a0 = make_float4(fix_get(s_aux[warp][lane][0]), fix_get(s_aux[warp][lane][1]), fix_get(s_aux[warp][lane][2]), 0.f);
@@ -287,8 +337,9 @@ cudaError_t zbk_launch_render(const RenderParams& P, int n_tiles_owned, bool sta
     if (n_tiles_owned <= 0) return cudaSuccess;
     // A shared-memory ray-pool variant of this kernel was measured 20-40 % slower on the headline frame
     // (profiles/r01_pool_vs_queue.txt) and removed.
-    if (stats) k_render<true><<<n_tiles_owned, ZB_BLOCK_THREADS, 0, stream>>>(P);
-    else k_render<false><<<n_tiles_owned, ZB_BLOCK_THREADS, 0, stream>>>(P);
+    if (P.light_pass) k_render<false, true><<<n_tiles_owned, ZB_BLOCK_THREADS, 0, stream>>>(P);
+    else if (stats) k_render<true, false><<<n_tiles_owned, ZB_BLOCK_THREADS, 0, stream>>>(P);
+    else k_render<false, false><<<n_tiles_owned, ZB_BLOCK_THREADS, 0, stream>>>(P);
     return cudaGetLastError();
 }
 

@@ -65,7 +65,7 @@ struct RenderParams {
     int tile_rank, tile_ranks;     // tile stripes: block b renders tile b*tile_ranks + tile_rank
     int tiles_x, tiles_y;
     int accumulate;                // 0: overwrite accum, 1: add to it
-    int pad;
+    int light_pass;                // 1: reflection / refraction passes (camera.hpp:492-517) instead of beauty
 };
 
 #ifndef ZB_TILE_W

@@ -48,6 +48,8 @@ class RenderConfig:
     use_normal: bool = False
     use_z_depth: bool = False
     z_depth_max_dist: float = 20.0
+    use_reflection: bool = False  # camera.hpp:56-57: the two light passes
+    use_refraction: bool = False
     extra: dict = field(default_factory=dict)
 
     def to_text(self) -> str:
@@ -80,6 +82,8 @@ class RenderConfig:
         ]
         if self.hdr_path:
             lines.append(f"hdr_path {self.hdr_path}")
+        if self.use_reflection or self.use_refraction:  # written only when set: fixture digests cover this text
+            lines += [f"use_reflection {int(self.use_reflection)}", f"use_refraction {int(self.use_refraction)}"]
         return "\n".join(lines) + "\n"
 
 

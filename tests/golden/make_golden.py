@@ -96,11 +96,11 @@ def make_stats(name, scene_text, cfg, batches, files=None):
     print(name, "stats", info)
 
 
-def read_render(path):
+def read_render(path, want=4):
     with open(path, "rb") as f:
         w, h = np.frombuffer(f.read(8), np.int32)
         n = int(w) * int(h) * 3
-        return [np.frombuffer(f.read(8 * n), np.float64).reshape(h, w, 3) for _ in range(4)]
+        return [np.frombuffer(f.read(8 * n), np.float64).reshape(h, w, 3) for _ in range(6)][:want]
 
 
 def make_aov(name, scene_text, cfg, files=None):
@@ -115,6 +115,25 @@ def make_aov(name, scene_text, cfg, files=None):
                         normal=normal.astype(np.float32), z_depth=z.astype(np.float32),
                         spp=cfg.samples_per_pixel, digest=scene_digest(scene_text, cfg, files))
     print(name, "aov", info)
+
+
+def make_light(name, scene_text, cfg, files=None):
+    """Reflection / refraction light passes (camera.hpp:492-517) of the reference at high spp."""
+    d = scratch_dir()
+    cfg.use_reflection = cfg.use_refraction = True
+    scenes.materialize(d, scene_text, cfg, files)
+    op = os.path.join(d, "render.bin")
+    info = run_harness(["render", "s.zscene", "s.cfg", op], d)
+    bufs = read_render(op, 6)
+    np.savez_compressed(os.path.join(GOLDEN, f"{name}_light.npz"), beauty=bufs[0].astype(np.float32),
+                        reflection=bufs[4].astype(np.float32), refraction=bufs[5].astype(np.float32),
+                        spp=cfg.samples_per_pixel, digest=scene_digest(scene_text, cfg, files))
+    print(name, "light", info)
+
+
+def quirks_light():
+    txt, cfg, files = scenes.quirks(seed=5, width=200, height=112, spp=2048)
+    make_light("quirks_200x112", txt, cfg, files)
 
 
 def probe_rays(cfg, n, seed):
@@ -200,7 +219,7 @@ def scene_targets():
     return t
 
 
-TARGETS = {"quirks_aov": quirks_aov, "weekend_ids": weekend_ids, "weekend_probe": weekend_probe, "weekend_stats": weekend_stats, **scene_targets()}
+TARGETS = {"quirks_aov": quirks_aov, "quirks_light": quirks_light, "weekend_ids": weekend_ids, "weekend_probe": weekend_probe, "weekend_stats": weekend_stats, **scene_targets()}
 
 if __name__ == "__main__":
     names = sys.argv[1:] or list(TARGETS)

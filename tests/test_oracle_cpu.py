@@ -152,3 +152,22 @@ def test_restatement_radiance_is_consistent_with_reference(zoracle, name, spp, t
     rrmse = float(np.sqrt(((img - ref) ** 2).sum() / (ref ** 2).sum()))
     assert rrmse < tol, rrmse
     assert abs(img.mean() / ref.mean() - 1.0) < 0.005
+
+
+def test_restatement_light_passes_are_consistent_with_reference(zoracle):
+    """Reflection / refraction light passes (camera.hpp:492-517): restatement at 512 spp vs the reference's
+    2048-spp buffers — image means within 2 %, rRMSE at the Monte-Carlo noise level of the two estimates."""
+    gold = np.load(os.path.join(GOLDEN, "quirks_200x112_light.npz"))
+    txt, cfg, files = scenes.quirks(seed=5, width=200, height=112, spp=512)
+    cfg.use_reflection = cfg.use_refraction = True
+    d = _scratch(txt, cfg, files)
+    subprocess.run([zoracle, "render", "s.zscene", "s.cfg", "img.bin", "3"], cwd=d, check=True, capture_output=True)
+    raw = open(os.path.join(d, "img.bin"), "rb").read()
+    bufs = [np.frombuffer(raw[8 + k * 200 * 112 * 24:8 + (k + 1) * 200 * 112 * 24], np.float64).reshape(112, 200, 3) for k in range(6)]
+    for key, img in (("reflection", bufs[4]), ("refraction", bufs[5])):
+        ref = gold[key].astype(np.float64)
+        assert ref.mean() > 1e-3, key  # the scene exercises both buffers
+        rrmse = float(np.sqrt(((img - ref) ** 2).sum() / (ref ** 2).sum()))
+        print(key, "mean", img.mean(), ref.mean(), "rRMSE", rrmse)
+        assert abs(img.mean() / ref.mean() - 1.0) < 0.02, (key, img.mean(), ref.mean())
+        assert rrmse < 0.12, (key, rrmse)
