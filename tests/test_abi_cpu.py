@@ -19,7 +19,7 @@ def test_header_symbols_all_exported(lib):
     assert declared == set(_lib.SYMBOLS), declared ^ set(_lib.SYMBOLS)
     for name in declared:
         assert hasattr(lib, name), name
-    assert lib.zb_abi_version() == 1
+    assert lib.zb_abi_version() == 2
 
 
 def test_struct_sizes_match_header():
@@ -141,3 +141,15 @@ def test_no_cpu_fallback_without_gpu(lib):
     h = C.c_void_p()
     rc = lib.zb_context_create(0, C.byref(h))
     assert rc == -2 and b"no CPU fallback" in lib.zb_last_error()
+
+
+def test_drop_in_camera_adapter_compiles_and_links(tmp_path):
+    """zenith::camera::render (host/zenith/camera.hpp) with reference-style scene code: C++20, header-only over
+    the C ABI; must compile and link against the in-tree library without a GPU."""
+    import subprocess
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    exe = str(tmp_path / "drop_in_render")
+    subprocess.run(["g++", "-std=c++20", "-O1", "-Wall", "-Wno-unused-function", os.path.join(root, "tests", "cpp", "drop_in_render.cpp"),
+                    "-o", exe, "-L" + os.path.join(root, "raytracer_project_b200"), "-lzenith_b200",
+                    "-Wl,-rpath," + os.path.join(root, "raytracer_project_b200")], check=True)
+    assert subprocess.run([exe]).returncode == 2  # usage error: no compute without arguments
