@@ -295,6 +295,48 @@ int zb_probe_rays(zb_context* ctx, const zb_scene* scene, const zb_environment* 
 
 int zb_get_stats(zb_context* ctx, zb_stats* out);
 
+/* ------------------------------------------------------------------------------------------------
+ * Finishing chain on the device-resident frame: what camera::render does after the
+ * path tracer — post_processor::analyze_framebuffer + apply_auto_exposure (color_processing.hpp:153-210,
+ * camera.hpp:258-267) and camera::update_post_processing (camera.hpp:142-207): exposure, bloom
+ * (bloom.hpp:18-68), 5-tap sharpening (color_processing.hpp:212-232) and post_processor::process
+ * (color_processing.hpp:76-150: balance, contrast, vignette, HSV, ACES, debug views, gamma).
+ * The fields mirror post_processor (color_processing.hpp:44-74). */
+typedef struct zb_post {
+    float exposure, saturation, contrast, hue_shift, vignette_intensity;
+    float color_balance[3];
+    float exposure_compensation_stops, target_luminance;
+    int32_t use_aces_tone_mapping, use_auto_exposure;
+    int32_t debug_red, debug_green, debug_blue, debug_luminance, debug_bvh;
+    int32_t use_bloom;
+    float bloom_threshold, bloom_intensity;
+    int32_t bloom_radius;
+    int32_t use_sharpening;
+    double sharpen_amount;
+} zb_post;
+
+/* image_statistics (color_processing.hpp:9-28) */
+typedef struct zb_image_stats {
+    float average_luminance; /* 2^(mean log2 max(lum, 1e-4)) */
+    float max_luminance;
+    int32_t histogram[256];  /* log2 luminance in [-10, 10] mapped to 256 bins */
+} zb_image_stats;
+
+enum { ZB_PASS_BEAUTY = 0, ZB_PASS_LIGHT = 1, ZB_PASS_AUX = 2 }; /* RGB/DENOISE | REFLECTIONS/REFRACTIONS | ALBEDO/NORMALS/Z_DEPTH */
+
+/* post_processor::analyze_framebuffer over W*H float4 means on the device (blocking, small D2H of the result) */
+int zb_analyze_device(zb_context* ctx, const void* mean_f4, size_t n_pixels, zb_image_stats* out);
+/* post_processor::apply_auto_exposure (host arithmetic, no device work): the exposure render() stores back */
+double zb_auto_exposure(const zb_post* post, const zb_image_stats* stats);
+/* camera::update_post_processing for one pass: mean_f4 (W*H float4, device) -> display-referred colour in
+ * out_f4 (float4, device, may be NULL) and/or out_rgba8 (uchar4, device, may be NULL).  Asynchronous on the
+ * context stream.  Bloom needs two W*H float4 scratch planes, owned by the context. */
+int zb_finish_device(zb_context* ctx, const void* mean_f4, int width, int height, const zb_post* post,
+                     int pass_kind, void* out_f4, void* out_rgba8);
+/* Host-buffer variant in the reference's layout (3 doubles per pixel in, final_framebuffer out); blocking. */
+int zb_finish(zb_context* ctx, const double* rgb_f64, int width, int height, const zb_post* post, int pass_kind,
+              double* out_rgb_f64);
+
 /* Host side of the boundary (C++20 scene API + flattener behind a C handle): parse a neutral scene
  * description ("zscene" text, raytracer_project_b200/host/zscene.hpp) through the reference-shaped
  * scene API and flatten it.  The returned zb_flat_scene stays valid until zb_flat_scene_free. */

@@ -438,6 +438,70 @@ static int cmd_probe(const std::string& scene, const std::string& cfg, const std
     return 0;
 }
 
+
+// Finishing chain of the reference: analyze_framebuffer + apply_auto_exposure
+// (color_processing.hpp:153-210, camera.hpp:258-267) and camera::update_post_processing (camera.hpp:142-207) on a raw
+// image (int32 w, h, then w*h*3 doubles).  Output: int32 w, h; final_framebuffer (w*h*3 doubles); average luminance,
+// max luminance, exposure after auto-exposure (3 doubles); histogram (256 int32).
+static int cmd_finish(const std::string& in, const std::string& cfg, const std::string& out) {
+    FILE* f = std::fopen(in.c_str(), "rb");
+    if (!f) return 2;
+    int32_t wh[2];
+    if (std::fread(wh, 4, 2, f) != 2) return 2;
+    const size_t n = size_t(wh[0]) * wh[1];
+    std::vector<color> img(n);
+    for (size_t i = 0; i < n; i++) {
+        double v[3];
+        if (std::fread(v, 8, 3, f) != 3) return 2;
+        img[i] = color(v[0], v[1], v[2]);
+    }
+    std::fclose(f);
+    config c = config::load(cfg);
+    post_processor post;
+    post.exposure = float(c.num("exposure", 0.5));
+    post.saturation = float(c.num("saturation", 1.0));
+    post.contrast = float(c.num("contrast", 1.0));
+    post.hue_shift = float(c.num("hue_shift", 0.0));
+    post.vignette_intensity = float(c.num("vignette_intensity", 1.0));
+    post.color_balance = c.v3("color_balance", vec3(1, 1, 1));
+    post.exposure_compensation_stops = float(c.num("exposure_compensation_stops", 0.0));
+    post.target_luminance = float(c.num("target_luminance", 0.12));
+    post.use_aces_tone_mapping = c.num("use_aces", 0) != 0;
+    post.use_auto_exposure = c.num("use_auto_exposure", 0) != 0;
+    post.debug.red = c.num("debug_red", 0) != 0;
+    post.debug.green = c.num("debug_green", 0) != 0;
+    post.debug.blue = c.num("debug_blue", 0) != 0;
+    post.debug.luminance = c.num("debug_luminance", 0) != 0;
+    post.debug.bvh = c.num("debug_bvh", 0) != 0;
+    post.use_bloom = c.num("use_bloom", 0) != 0;
+    post.bloom_threshold = float(c.num("bloom_threshold", 1.0));
+    post.bloom_intensity = float(c.num("bloom_intensity", 0.3));
+    post.bloom_radius = int(c.num("bloom_radius", 4));
+    post.use_sharpening = c.num("use_sharpening", 0) != 0;
+    post.sharpen_amount = c.num("sharpen_amount", 0.2);
+    const int pass = int(c.num("pass", 0));
+    image_statistics stats = post.analyze_framebuffer(img);
+    if (post.use_auto_exposure) post.exposure = static_cast<float>(post.apply_auto_exposure(stats));  // camera.hpp:259-263
+    camera cam;
+    cam.image_width = wh[0];
+    cam.image_height = wh[1];
+    cam.render_accumulator = img;
+    cam.reflection_buffer = img;
+    cam.albedo_buffer = img;
+    cam.current_display_pass = pass == 0 ? render_pass::RGB : pass == 1 ? render_pass::REFLECTIONS : render_pass::ALBEDO;
+    cam.update_post_processing(post, wh[0], wh[1]);
+    f = std::fopen(out.c_str(), "wb");
+    if (!f) return 2;
+    std::fwrite(wh, 4, 2, f);
+    write_colors(f, cam.final_framebuffer);
+    double s3[3] = {stats.average_luminance, stats.max_luminance, post.exposure};
+    std::fwrite(s3, 8, 3, f);
+    std::fwrite(stats.histogram, 4, 256, f);
+    std::fclose(f);
+    std::printf("{\"cmd\": \"finish\", \"width\": %d, \"height\": %d, \"exposure\": %.9g}\n", wh[0], wh[1], double(post.exposure));
+    return 0;
+}
+
 static int cmd_decode(const std::string& in, const std::string& out, bool is_hdr) {
     int w = 0, h = 0, comp = 3;
     FILE* f = nullptr;
@@ -475,6 +539,7 @@ int main(int argc, char** argv) {
     if (a.size() >= 4 && a[0] == "render") return cmd_render(a[1], a[2], a[3], a.size() > 4 && a[4] == "--count-rays");
     if (a.size() >= 5 && a[0] == "stats") return cmd_stats(a[1], a[2], a[3], std::atoi(a[4].c_str()));
     if (a.size() >= 5 && a[0] == "probe") return cmd_probe(a[1], a[2], a[3], a[4]);
+    if (a.size() >= 4 && a[0] == "finish") return cmd_finish(a[1], a[2], a[3]);
     if (a.size() >= 4 && a[0] == "decode") return cmd_decode(a[1], a[2], a[3] == "1");
     if (a.size() >= 2 && a[0] == "kat") return cmd_kat(a[1]);
     std::fprintf(stderr,

@@ -15,6 +15,7 @@
 //   zoracle ids    SCENE CFG OUT          centre-of-pixel primary hits (camera.hpp:809-814 + :459)
 //   zoracle probe  SCENE CFG RAYS OUT     per-ray hit_record / albedo / emitted / background
 //   zoracle render SCENE CFG OUT|- [SEED] render_rows (camera.hpp:430-554), OpenMP over rows
+//   zoracle finish IMAGE CFG OUT          finishing chain (camera.hpp:142-207, color_processing.hpp, bloom.hpp)
 // File formats are those of oracle/ref_harness.cpp, so the same test code reads both.
 #include <algorithm>
 #include <chrono>
@@ -893,6 +894,197 @@ int cmd_render(const std::string& scene, const std::string& cfg, const std::stri
     return 0;
 }
 
+
+// ------------------------------------------------------------------ finishing chain
+// analyze_framebuffer / apply_auto_exposure (color_processing.hpp:153-210), update_post_processing
+// (camera.hpp:142-207), bloom (bloom.hpp:18-68), sharpening (color_processing.hpp:212-232), process (:76-150).
+// Same file formats as ref_harness's `finish`.
+struct post_t {
+    float exposure = 0.5f, saturation = 1, contrast = 1, hue_shift = 0, vignette = 1, stops = 0, target = 0.12f;
+    vec3 balance = vec3(1, 1, 1);
+    bool aces = false, auto_exp = false, dr = false, dg = false, db = false, dl = false, dbvh = false, bloom = false, sharpen = false;
+    float bloom_threshold = 1, bloom_intensity = 0.3f;
+    int bloom_radius = 4;
+    double sharpen_amount = 0.2;
+};
+inline double lum709(const color& c) { return 0.2126 * c[0] + 0.7152 * c[1] + 0.0722 * c[2]; }  // vec3.hpp:106-108
+inline double gamma22(double v) { return v > 0 ? std::pow(v, 1.0 / 2.2) : 0; }                    // common.hpp:67-72
+inline color clamp_gamma(const color& c) { return color(gamma22(clamp01(c[0])), gamma22(clamp01(c[1])), gamma22(clamp01(c[2]))); }
+inline double aces1(double v) {                                                                    // common.hpp:48-64
+    if (std::isnan(v) || std::isinf(v)) return 0.0;
+    double x = std::max(0.0, v);
+    return (x * (2.51 * x + 0.03)) / (x * (2.43 * x + 0.59) + 0.14);
+}
+color post_process(color c, float u, float v, const post_t& P) {  // color_processing.hpp:76-150, beauty pass
+    c = c * double(P.exposure);
+    c = c * P.balance;
+    if (std::abs(P.contrast - 1.0f) > 0.001f)
+        c = color(std::max(0.0, (c[0] - 0.18) * P.contrast + 0.18), std::max(0.0, (c[1] - 0.18) * P.contrast + 0.18),
+                  std::max(0.0, (c[2] - 0.18) * P.contrast + 0.18));
+    if (P.vignette > 0.0f) {
+        float dist = std::sqrt((u - 0.5f) * (u - 0.5f) + (v - 0.5f) * (v - 0.5f));
+        c = c * double(std::clamp(1.0f - dist * P.vignette, 0.0f, 1.0f));
+    }
+    if (std::abs(P.saturation - 1.0f) > 0.001f || std::abs(P.hue_shift) > 0.001f) {
+        double luma = lum709(c);
+        if (luma > 0.0001) {
+            color nrm = c / luma;
+            float r = float(nrm[0]), g = float(nrm[1]), b = float(nrm[2]);  // rgb_to_hsv works in float (:280-306)
+            float mx = std::max({r, g, b}), mn = std::min({r, g, b}), d = mx - mn, h = 0.0f;
+            float sat = mx < 1e-6f ? 0.0f : d / mx;
+            if (mx != mn) {
+                if (mx == r) h = (g - b) / d + (g < b ? 6.0f : 0.0f);
+                else if (mx == g) h = (b - r) / d + 2.0f;
+                else h = (r - g) / d + 4.0f;
+                h /= 6.0f;
+            }
+            double hue = std::fmod(double(h * 360.0f) + P.hue_shift, 360.0);
+            if (hue < 0) hue += 360.0;
+            float s2 = std::clamp(float(double(sat) * P.saturation), 0.0f, 1.0f);
+            float hh = float(hue) / 360.0f, vv = mx;  // hsv_to_rgb (:308-343)
+            int i = int(hh * 6.0f);
+            float f = hh * 6.0f - float(i), p = vv * (1.0f - s2), q = vv * (1.0f - f * s2), t = vv * (1.0f - (1.0f - f) * s2);
+            color rgb;
+            switch (i % 6) {
+                case 0: rgb = color(vv, t, p); break;
+                case 1: rgb = color(q, vv, p); break;
+                case 2: rgb = color(p, vv, t); break;
+                case 3: rgb = color(p, q, vv); break;
+                case 4: rgb = color(t, p, vv); break;
+                case 5: rgb = color(vv, p, q); break;
+                default: rgb = color(0, 0, 0);
+            }
+            c = rgb * luma;
+        }
+    }
+    if (P.aces) c = color(aces1(c[0]), aces1(c[1]), aces1(c[2]));
+    if (P.dr || P.dg || P.db || P.dl || P.dbvh) {  // apply_debug_view (:246-278)
+        if (P.dl) {
+            double l = lum709(c);
+            c = l >= 1.0 ? color(1, 1, 1) : l > 0.95 ? color(1, 0, 0) : l > 0.70 ? color(1, 1, 0) : l > 0.40 ? color(.5, .5, .5)
+              : l > 0.10 ? color(0, .5, 0) : l > 0.02 ? color(0, 0, 1) : color(0.1, 0.0, 0.2);
+        } else if (!P.dbvh) {
+            c = color(P.dr ? c[0] : 0.0, P.dg ? c[1] : 0.0, P.db ? c[2] : 0.0);
+        }
+    }
+    return clamp_gamma(c);
+}
+
+void blur_pass(const std::vector<color>& in, std::vector<color>& out, int W, int H, int r, bool horizontal) {  // bloom.hpp:48-67
+    for (int y = 0; y < H; y++)
+        for (int x = 0; x < W; x++) {
+            color sum(0, 0, 0);
+            float total = 0.0f;
+            for (int o = -r; o <= r; o++) {
+                int sx = x + (horizontal ? o : 0), sy = y + (horizontal ? 0 : o);
+                if (sx < 0 || sx >= W || sy < 0 || sy >= H) continue;
+                float w = 1.0f - (std::abs(o) / float(r + 1));
+                sum += in[size_t(sy) * W + sx] * double(w);
+                total += w;
+            }
+            out[size_t(y) * W + x] = total > 0 ? sum / double(total) : color(0, 0, 0);
+        }
+}
+
+int cmd_finish(const std::string& in, const std::string& cfg, const std::string& out) {
+    FILE* f = std::fopen(in.c_str(), "rb");
+    if (!f) return 2;
+    int32_t wh[2];
+    if (std::fread(wh, 4, 2, f) != 2) return 2;
+    const int W = wh[0], H = wh[1];
+    const size_t n = size_t(W) * H;
+    std::vector<color> img(n);
+    for (size_t i = 0; i < n; i++) {
+        double v[3];
+        if (std::fread(v, 8, 3, f) != 3) return 2;
+        img[i] = color(v[0], v[1], v[2]);
+    }
+    std::fclose(f);
+    config c = config::load(cfg);
+    post_t P;
+    P.exposure = float(c.num("exposure", 0.5));
+    P.saturation = float(c.num("saturation", 1.0));
+    P.contrast = float(c.num("contrast", 1.0));
+    P.hue_shift = float(c.num("hue_shift", 0.0));
+    P.vignette = float(c.num("vignette_intensity", 1.0));
+    P.balance = c.v3("color_balance", vec3(1, 1, 1));
+    P.stops = float(c.num("exposure_compensation_stops", 0.0));
+    P.target = float(c.num("target_luminance", 0.12));
+    P.aces = c.num("use_aces", 0) != 0;
+    P.auto_exp = c.num("use_auto_exposure", 0) != 0;
+    P.dr = c.num("debug_red", 0) != 0; P.dg = c.num("debug_green", 0) != 0; P.db = c.num("debug_blue", 0) != 0;
+    P.dl = c.num("debug_luminance", 0) != 0; P.dbvh = c.num("debug_bvh", 0) != 0;
+    P.bloom = c.num("use_bloom", 0) != 0;
+    P.bloom_threshold = float(c.num("bloom_threshold", 1.0));
+    P.bloom_intensity = float(c.num("bloom_intensity", 0.3));
+    P.bloom_radius = int(c.num("bloom_radius", 4));
+    P.sharpen = c.num("use_sharpening", 0) != 0;
+    P.sharpen_amount = c.num("sharpen_amount", 0.2);
+    const int pass = int(c.num("pass", 0));
+    // analyze_framebuffer (color_processing.hpp:153-186)
+    int32_t hist[256] = {0};
+    double total_log = 0.0;
+    float max_lum = 0.0f;
+    for (const color& p : img) {
+        float lum = float(lum709(p));
+        if (lum > max_lum) max_lum = lum;
+        float cl = std::max(0.0001f, lum), l2 = std::log2(cl);
+        total_log += l2;
+        hist[std::clamp(int(((l2 - (-10.0f)) / 20.0f) * 255.0f), 0, 255)]++;
+    }
+    float avg = std::pow(2.0f, float(total_log / double(n)));
+    // apply_auto_exposure (color_processing.hpp:189-210), stored back by render() (camera.hpp:259-263)
+    if (P.auto_exp && avg > 0.0) {
+        double cur = (P.target / std::max(double(avg), 0.02)) * std::pow(2.0, double(P.stops));
+        P.exposure = std::clamp(float(cur), 0.01f, 4.0f);
+    }
+    // update_post_processing (camera.hpp:142-207)
+    std::vector<color> fin = img;
+    const double ev = std::pow(2.0, P.exposure);
+    if (pass == 0) {
+        for (color& p : fin) p *= ev;
+        if (P.bloom) {
+            std::vector<color> bright(n, color(0, 0, 0)), tmp(n), overlay(n);
+            for (size_t i = 0; i < n; i++) {  // bright pass, bloom.hpp:27-38 (exposure argument 1.0f)
+                color e = fin[i] * 1.0;
+                float lum = float(lum709(e));
+                if (lum > P.bloom_threshold) bright[i] = e * double((lum - P.bloom_threshold) * P.bloom_intensity / std::max(lum, 0.0001f));
+            }
+            blur_pass(bright, tmp, W, H, P.bloom_radius, true);
+            blur_pass(tmp, overlay, W, H, P.bloom_radius, false);
+            for (size_t i = 0; i < n; i++) fin[i] += overlay[i];
+        }
+        if (P.sharpen && P.sharpen_amount > 0.0) {  // color_processing.hpp:212-232
+            std::vector<color> orig = fin;
+            for (int y = 1; y < H - 1; y++)
+                for (int x = 1; x < W - 1; x++) {
+                    size_t i = size_t(y) * W + x;
+                    color sum = orig[i] * 5.0 - orig[i - W] - orig[i + W] - orig[i - 1] - orig[i + 1];
+                    fin[i] = (orig[i] * (1.0 - P.sharpen_amount)) + (sum * P.sharpen_amount);
+                }
+        }
+    }
+    for (size_t i = 0; i < n; i++) {
+        float u = float(i % W) / (W - 1), v = float(i / W) / (H - 1);
+        if (pass == 0) fin[i] = post_process(fin[i], u, v, P);
+        else if (pass == 1) fin[i] = post_process(fin[i] * ev, u, v, P);
+        else fin[i] = clamp_gamma(fin[i]);
+    }
+    f = std::fopen(out.c_str(), "wb");
+    if (!f) return 2;
+    std::fwrite(wh, 4, 2, f);
+    for (const color& p : fin) {
+        double e[3] = {p[0], p[1], p[2]};
+        std::fwrite(e, 8, 3, f);
+    }
+    double s3[3] = {avg, max_lum, P.exposure};
+    std::fwrite(s3, 8, 3, f);
+    std::fwrite(hist, 4, 256, f);
+    std::fclose(f);
+    std::printf("{\"cmd\": \"finish\", \"width\": %d, \"height\": %d, \"exposure\": %.9g}\n", W, H, double(P.exposure));
+    return 0;
+}
+
 }  // namespace
 
 int main(int argc, char** argv) {
@@ -900,6 +1092,7 @@ int main(int argc, char** argv) {
     std::cout.setstate(std::ios::failbit);  // silence the host model loader's progress line; results go through printf
     if (a.size() >= 4 && a[0] == "ids") return cmd_ids(a[1], a[2], a[3]);
     if (a.size() >= 5 && a[0] == "probe") return cmd_probe(a[1], a[2], a[3], a[4]);
+    if (a.size() >= 4 && a[0] == "finish") return cmd_finish(a[1], a[2], a[3]);
     if (a.size() >= 4 && a[0] == "render") return cmd_render(a[1], a[2], a[3], a.size() > 4 ? std::strtoull(a[4].c_str(), nullptr, 10) : 1ull);
     std::fprintf(stderr, "usage: zoracle ids SCENE CFG OUT | probe SCENE CFG RAYS OUT | render SCENE CFG OUT|- [SEED]\n");
     return 1;

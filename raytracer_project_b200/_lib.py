@@ -84,6 +84,22 @@ class Stats(C.Structure):
 
 PROGRESS_FN = C.CFUNCTYPE(None, C.c_int, C.c_void_p)
 
+class Post(C.Structure):
+    """zb_post: the fields of post_processor (color_processing.hpp:44-74)."""
+    _fields_ = [("exposure", C.c_float), ("saturation", C.c_float), ("contrast", C.c_float), ("hue_shift", C.c_float),
+                ("vignette_intensity", C.c_float), ("color_balance", C.c_float * 3),
+                ("exposure_compensation_stops", C.c_float), ("target_luminance", C.c_float),
+                ("use_aces_tone_mapping", C.c_int32), ("use_auto_exposure", C.c_int32), ("debug_red", C.c_int32),
+                ("debug_green", C.c_int32), ("debug_blue", C.c_int32), ("debug_luminance", C.c_int32),
+                ("debug_bvh", C.c_int32), ("use_bloom", C.c_int32), ("bloom_threshold", C.c_float),
+                ("bloom_intensity", C.c_float), ("bloom_radius", C.c_int32), ("use_sharpening", C.c_int32),
+                ("sharpen_amount", C.c_double)]
+
+
+class ImageStats(C.Structure):
+    _fields_ = [("average_luminance", C.c_float), ("max_luminance", C.c_float), ("histogram", C.c_int32 * 256)]
+
+
 # every symbol include/zenith_b200.h declares: name -> (restype, argtypes)
 SYMBOLS = {
     "zb_abi_version": (C.c_int, []),
@@ -103,6 +119,10 @@ SYMBOLS = {
     "zb_resolve_device": (C.c_int, [C.c_void_p, C.c_void_p, C.c_size_t, C.c_double, C.c_void_p, C.c_void_p]),
     "zb_primary_ids": (C.c_int, [C.c_void_p, C.c_void_p, C.POINTER(Camera), C.c_void_p, C.c_void_p, C.c_void_p]),
     "zb_get_stats": (C.c_int, [C.c_void_p, C.POINTER(Stats)]),
+    "zb_analyze_device": (C.c_int, [C.c_void_p, C.c_void_p, C.c_size_t, C.POINTER(ImageStats)]),
+    "zb_auto_exposure": (C.c_double, [C.POINTER(Post), C.POINTER(ImageStats)]),
+    "zb_finish_device": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.POINTER(Post), C.c_int, C.c_void_p, C.c_void_p]),
+    "zb_finish": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.POINTER(Post), C.c_int, C.c_void_p]),
     "zb_flat_scene_from_zscene": (C.c_int, [C.c_char_p, C.POINTER(C.POINTER(FlatScene))]),
     "zb_flat_scene_from_zscene_text": (C.c_int, [C.c_char_p, C.c_size_t, C.POINTER(C.POINTER(FlatScene))]),
     "zb_flat_scene_free": (C.c_int, [C.POINTER(FlatScene)]),

@@ -68,6 +68,37 @@ def opts_struct(cfg: RenderConfig, seed=1, sample_range=None, tile=None, stats=F
     return o
 
 
+POST_DEFAULTS = dict(exposure=0.5, saturation=1.0, contrast=1.0, hue_shift=0.0, vignette_intensity=1.0,
+                     color_balance=(1.0, 1.0, 1.0), exposure_compensation_stops=0.0, target_luminance=0.12, use_aces=0,
+                     use_auto_exposure=0, debug_red=0, debug_green=0, debug_blue=0, debug_luminance=0, debug_bvh=0,
+                     use_bloom=0, bloom_threshold=1.0, bloom_intensity=0.3, bloom_radius=4, use_sharpening=0,
+                     sharpen_amount=0.2)  # post_processor defaults (color_processing.hpp:44-74)
+
+
+def post_struct(**kw) -> "_lib.Post":
+    """zb_post from keyword overrides of the reference's post_processor defaults."""
+    v = {**POST_DEFAULTS, **kw}
+    p = _lib.Post()
+    for k in ("exposure", "saturation", "contrast", "hue_shift", "vignette_intensity", "exposure_compensation_stops",
+              "target_luminance", "bloom_threshold", "bloom_intensity", "sharpen_amount"):
+        setattr(p, k, float(v[k]))
+    for k in ("use_auto_exposure", "debug_red", "debug_green", "debug_blue", "debug_luminance", "debug_bvh", "use_bloom",
+              "bloom_radius", "use_sharpening"):
+        setattr(p, k, int(v[k]))
+    p.use_aces_tone_mapping = int(v["use_aces"])
+    p.color_balance = (C.c_float * 3)(*[float(x) for x in v["color_balance"]])
+    return p
+
+
+def post_text(pass_kind=0, **kw) -> str:
+    """The same parameters as the key-value text the oracle binaries read (`finish` command)."""
+    v = {**POST_DEFAULTS, **kw}
+    lines = [f"pass {int(pass_kind)}"]
+    for k, x in v.items():
+        lines.append(f"{k} " + (" ".join(repr(float(y)) for y in x) if isinstance(x, (tuple, list)) else repr(float(x))))
+    return "\n".join(lines) + "\n"
+
+
 class Context:
     def __init__(self, device: int = 0, stream: int | None = None):
         self.lib = _lib.load()
@@ -91,6 +122,29 @@ class Context:
         sm, ma, mi, l2 = C.c_int(), C.c_int(), C.c_int(), C.c_size_t()
         check(self.lib.zb_device_info(self.h, C.byref(sm), C.byref(ma), C.byref(mi), C.byref(l2)))
         return {"sm_count": sm.value, "cc": (ma.value, mi.value), "l2_bytes": l2.value}
+
+    def analyze_device(self, mean_ptr: int, n_pixels: int) -> dict:
+        """zb_analyze_device: post_processor::analyze_framebuffer over device float4 means."""
+        st = _lib.ImageStats()
+        check(self.lib.zb_analyze_device(self.h, C.c_void_p(mean_ptr), n_pixels, C.byref(st)))
+        return {"average_luminance": st.average_luminance, "max_luminance": st.max_luminance,
+                "histogram": np.array(st.histogram, np.int32), "_struct": st}
+
+    def auto_exposure(self, post, stats: dict) -> float:
+        return float(self.lib.zb_auto_exposure(C.byref(post), C.byref(stats["_struct"])))
+
+    def finish_device(self, mean_ptr: int, width: int, height: int, post, pass_kind=0, out_f4_ptr=0, out_u8_ptr=0):
+        """zb_finish_device: update_post_processing on device buffers (asynchronous on the context stream)."""
+        check(self.lib.zb_finish_device(self.h, C.c_void_p(mean_ptr), width, height, C.byref(post), pass_kind,
+                                        C.c_void_p(out_f4_ptr) if out_f4_ptr else None,
+                                        C.c_void_p(out_u8_ptr) if out_u8_ptr else None))
+
+    def finish(self, image, post, pass_kind=0):
+        """zb_finish: (H, W, 3) float64 linear image -> the reference's final_framebuffer (H, W, 3) float64."""
+        img = np.ascontiguousarray(image, np.float64)
+        out = np.empty_like(img)
+        check(self.lib.zb_finish(self.h, img.ctypes.data, img.shape[1], img.shape[0], C.byref(post), pass_kind, out.ctypes.data))
+        return out
 
     def upload(self, flat) -> "Scene":
         s = C.c_void_p()

@@ -56,6 +56,10 @@ extern "C" int zb_context_destroy(zb_context* ctx) {
     cudaFree(ctx->accum_aux);
     cudaFree(ctx->out_f4);
     cudaFree(ctx->id_scratch);
+    cudaFree(ctx->fin_a);
+    cudaFree(ctx->fin_b);
+    cudaFree(ctx->fin_in);
+    cudaFree(ctx->fin_stats);
     if (ctx->pinned) cudaFreeHost(ctx->pinned);
     for (auto& ev : ctx->ev) cudaEventDestroy(ev);
     for (auto& ev : ctx->chunk_ev) cudaEventDestroy(ev);

@@ -36,6 +36,11 @@ struct zb_context {
     void* pinned = nullptr;
     size_t pinned_bytes = 0;
     uint32_t* id_scratch = nullptr;
+    float4* fin_a = nullptr;   // finishing chain scratch: two W*H planes (bloom) + a staging plane for host input
+    float4* fin_b = nullptr;
+    float4* fin_in = nullptr;
+    size_t fin_pixels = 0;
+    unsigned long long* fin_stats = nullptr;  // 2 + 128 u64: log sum, max, 256-bin histogram
     size_t id_pixels = 0;
     cudaEvent_t ev[6] = {};
     std::vector<cudaEvent_t> chunk_ev;  // one per 4 MiB chunk of the frame copy (abi_render.cu d2h_rgb_f64)

@@ -136,6 +136,39 @@ def quirks_light():
     make_light("quirks_200x112", txt, cfg, files)
 
 
+def read_finish(path):
+    with open(path, "rb") as f:
+        w, h = np.frombuffer(f.read(8), np.int32)
+        img = np.frombuffer(f.read(8 * int(w) * int(h) * 3), np.float64).reshape(h, w, 3)
+        avg, mx, exposure = np.frombuffer(f.read(24), np.float64)
+        hist = np.frombuffer(f.read(1024), np.int32)
+    return img, float(avg), float(mx), float(exposure), hist
+
+
+def write_image(path, img):
+    with open(path, "wb") as f:
+        f.write(np.array([img.shape[1], img.shape[0]], np.int32).tobytes() + np.ascontiguousarray(img, np.float64).tobytes())
+
+
+def finish():
+    """Finishing chain of the reference (camera.hpp:142-207, color_processing.hpp, bloom.hpp) on the seeded HDR frame."""
+    from raytracer_project_b200 import api
+    from tests.golden.finish_cases import CASES, hdr_image
+    d = scratch_dir()
+    write_image(os.path.join(d, "in.bin"), hdr_image())
+    out = {}
+    for name, (pass_kind, kw) in CASES.items():
+        with open(os.path.join(d, "post.cfg"), "w") as f:
+            f.write(api.post_text(pass_kind, **kw))
+        info = run_harness(["finish", "in.bin", "post.cfg", "out.bin"], d)
+        img, avg, mx, exposure, hist = read_finish(os.path.join(d, "out.bin"))
+        out[name + "_image"] = img
+        out[name + "_stats"] = np.array([avg, mx, exposure])
+        out["histogram"] = hist
+        print("finish", name, info)
+    np.savez_compressed(os.path.join(GOLDEN, "finish_96x60.npz"), **out)
+
+
 def probe_rays(cfg, n, seed):
     """Known-answer rays for a scene: a third camera rays through random image positions (un-normalised, as
     get_ray builds them), the rest random origins in a ball around the look-at point with random directions of
@@ -219,7 +252,7 @@ def scene_targets():
     return t
 
 
-TARGETS = {"quirks_aov": quirks_aov, "quirks_light": quirks_light, "weekend_ids": weekend_ids, "weekend_probe": weekend_probe, "weekend_stats": weekend_stats, **scene_targets()}
+TARGETS = {"finish": finish, "quirks_aov": quirks_aov, "quirks_light": quirks_light, "weekend_ids": weekend_ids, "weekend_probe": weekend_probe, "weekend_stats": weekend_stats, **scene_targets()}
 
 if __name__ == "__main__":
     names = sys.argv[1:] or list(TARGETS)

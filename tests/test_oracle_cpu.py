@@ -171,3 +171,28 @@ def test_restatement_light_passes_are_consistent_with_reference(zoracle):
         print(key, "mean", img.mean(), ref.mean(), "rRMSE", rrmse)
         assert abs(img.mean() / ref.mean() - 1.0) < 0.02, (key, img.mean(), ref.mean())
         assert rrmse < 0.12, (key, rrmse)
+
+
+# ------------------------------------------------------------------ finishing chain
+def _run_finish(binary, img, pass_kind, kw, d):
+    from raytracer_project_b200 import api
+    from tests.golden.make_golden import read_finish, write_image
+    write_image(os.path.join(d, "in.bin"), img)
+    with open(os.path.join(d, "post.cfg"), "w") as f:
+        f.write(api.post_text(pass_kind, **kw))
+    subprocess.run([binary, "finish", "in.bin", "post.cfg", "out.bin"], cwd=d, check=True, capture_output=True)
+    return read_finish(os.path.join(d, "out.bin"))
+
+
+def test_restatement_finishing_chain_matches_reference(zoracle, tmp_path):
+    """analyze_framebuffer, auto-exposure, exposure, bloom, sharpening and process() restated in zoracle against
+    the reference's final_framebuffer for every parameter set (both compute in double, HSV in float)."""
+    from tests.golden.finish_cases import CASES, hdr_image
+    gold = np.load(os.path.join(GOLDEN, "finish_96x60.npz"))
+    img = hdr_image()
+    for name, (pass_kind, kw) in CASES.items():
+        out, avg, mx, exposure, hist = _run_finish(zoracle, img, pass_kind, kw, str(tmp_path))
+        assert np.allclose([avg, mx, exposure], gold[name + "_stats"], rtol=1e-6), name
+        assert np.array_equal(hist, gold["histogram"]), name
+        close = np.isclose(out, gold[name + "_image"], rtol=1e-6, atol=1e-7)
+        assert close.mean() == 1.0, (name, close.mean(), np.abs(out - gold[name + "_image"]).max())
