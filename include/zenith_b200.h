@@ -105,7 +105,7 @@ typedef struct zb_instance {
 
 typedef struct zb_mesh {
     uint32_t node_root; /* first node of this mesh's BLAS inside nodes[]        */
-    uint32_t node_count;
+    uint32_t node_count; /* 0 with tri_count > 0: no host BLAS, zb_scene_upload builds one on the device */
     uint32_t tri_first; /* first triangle of this mesh inside tris[] (BLAS leaf order) */
     uint32_t tri_count;
 } zb_mesh;
@@ -342,6 +342,11 @@ int zb_finish(zb_context* ctx, const double* rgb_f64, int width, int height, con
  * scene API and flatten it.  The returned zb_flat_scene stays valid until zb_flat_scene_free. */
 int zb_flat_scene_from_zscene(const char* path, const zb_flat_scene** out);
 int zb_flat_scene_from_zscene_text(const char* text, size_t len, const zb_flat_scene** out);
+/* Same with options.  ZB_FLATTEN_GPU_BLAS: skip the host SAH build of every mesh BLAS (bvh.hpp:11-44 equivalent) and
+ * let zb_scene_upload build linear BVHs on the device (csrc/lbvh.cu): time-to-first-pixel for multi-million-triangle
+ * meshes drops from seconds to milliseconds, at a lower tree quality.  Exactly one of path / text is given. */
+#define ZB_FLATTEN_GPU_BLAS 1u
+int zb_flat_scene_from_zscene_ex(const char* path, const char* text, size_t len, uint32_t flags, const zb_flat_scene** out);
 int zb_flat_scene_free(const zb_flat_scene* flat);
 
 #ifdef __cplusplus

@@ -35,6 +35,12 @@ class FlatScene(C.Structure):
         ("texels_u8", C.c_void_p), ("texels_f32", C.c_void_p), ("n_leaves", C.c_uint32), ("pad", C.c_uint32),
     ]
 
+    def meshes_array(self):
+        """zb_mesh records as an (n_meshes, 4) uint32 view: node_root, node_count, tri_first, tri_count."""
+        class Mesh(C.Structure):
+            _fields_ = [("node_root", C.c_uint32), ("node_count", C.c_uint32), ("tri_first", C.c_uint32), ("tri_count", C.c_uint32)]
+        return C.cast(self.meshes, C.POINTER(Mesh))
+
     def nbytes(self) -> int:
         """Bytes zb_scene_upload copies to the device for this scene."""
         return (self.n_nodes * 64 + self.n_items * 32 + self.n_cubes * 32 + self.n_tris * 96 + self.n_instances * 128
@@ -125,6 +131,7 @@ SYMBOLS = {
     "zb_finish": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.POINTER(Post), C.c_int, C.c_void_p]),
     "zb_flat_scene_from_zscene": (C.c_int, [C.c_char_p, C.POINTER(C.POINTER(FlatScene))]),
     "zb_flat_scene_from_zscene_text": (C.c_int, [C.c_char_p, C.c_size_t, C.POINTER(C.POINTER(FlatScene))]),
+    "zb_flat_scene_from_zscene_ex": (C.c_int, [C.c_char_p, C.c_char_p, C.c_size_t, C.c_uint32, C.POINTER(C.POINTER(FlatScene))]),
     "zb_flat_scene_free": (C.c_int, [C.POINTER(FlatScene)]),
 }
 

@@ -15,11 +15,16 @@ from ._lib import Camera, Environment, FlatScene, Outputs, RenderOpts, Stats, ch
 from .scenes import RenderConfig
 
 
-def flatten_zscene(text: str | None = None, path: str | None = None):
-    """zscene text/file -> host scene API -> flatten(); returns a ctypes pointer to zb_flat_scene."""
+def flatten_zscene(text: str | None = None, path: str | None = None, gpu_blas: bool = False):
+    """zscene text/file -> host scene API -> flatten(); returns a ctypes pointer to zb_flat_scene.
+    gpu_blas: leave the mesh BLAS builds to the device (linear BVH, csrc/lbvh.cu) at zb_scene_upload."""
     lib = _lib.load()
     out = C.POINTER(FlatScene)()
-    if path is not None:
+    if gpu_blas:
+        data = text.encode() if text is not None else None
+        check(lib.zb_flat_scene_from_zscene_ex(path.encode() if path is not None else None, data, len(data) if data else 0,
+                                               1, C.byref(out)))
+    elif path is not None:
         check(lib.zb_flat_scene_from_zscene(path.encode(), C.byref(out)))
     else:
         data = text.encode()

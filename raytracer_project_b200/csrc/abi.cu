@@ -150,6 +150,60 @@ static int validate(const zb_flat_scene* f) {
     return ZB_OK;
 }
 
+// csrc/lbvh.cu
+int zbk_build_blas_device(zb_context* ctx, const float4* tris_in, const float4* nrm_in, uint32_t n, uint32_t tri_first,
+                          uint32_t node_base, float4* tris_out, float4* nrm_out, zb_bvh_node* nodes_out, uint32_t* n_nodes);
+
+// Meshes the flattener left without a BLAS (node_count == 0): build linear BVHs on the device.
+// d.tris / d.tri_normals already hold the triangles in face order; nodes are appended after the host nodes and
+// the BLAS roots are written into `instances` (host copy, uploaded by the caller afterwards).
+static int build_device_blas(zb_scene* s, const zb_flat_scene* f, std::vector<zb_instance>& instances) {
+    SceneDev& d = s->dev;
+    size_t extra = 0, largest = 0;
+    for (uint32_t m = 0; m < f->n_meshes; m++)
+        if (f->meshes[m].node_count == 0 && f->meshes[m].tri_count > 0) {
+            extra += std::max<size_t>(f->meshes[m].tri_count - 1, 1);
+            largest = std::max<size_t>(largest, f->meshes[m].tri_count);
+        }
+    zb_bvh_node* nodes = nullptr;
+    ZB_CUDA(cudaMalloc(&nodes, (size_t(f->n_nodes) + extra) * sizeof(zb_bvh_node)));
+    s->allocs.push_back(nodes);
+    if (f->n_nodes)
+        ZB_CUDA(cudaMemcpyAsync(nodes, f->nodes, size_t(f->n_nodes) * sizeof(zb_bvh_node), cudaMemcpyHostToDevice, s->ctx->stream));
+    float4 *tmp_t = nullptr, *tmp_n = nullptr;
+    ZB_CUDA(cudaMalloc(&tmp_t, largest * 3 * sizeof(float4)));
+    if (cudaMalloc(&tmp_n, largest * 3 * sizeof(float4)) != cudaSuccess) {
+        cudaFree(tmp_t);
+        return fail(ZB_ERR_CUDA, "zb_scene_upload: out of device memory for the BLAS build");
+    }
+    uint32_t next = f->n_nodes;
+    std::vector<uint32_t> roots(f->n_meshes, 0);
+    int rc = ZB_OK;
+    for (uint32_t m = 0; m < f->n_meshes && !rc; m++) {
+        const zb_mesh& zm = f->meshes[m];
+        roots[m] = zm.node_root;
+        if (zm.node_count != 0 || zm.tri_count == 0) continue;
+        float4* t = const_cast<float4*>(d.tris) + 3 * size_t(zm.tri_first);
+        float4* n = const_cast<float4*>(d.tri_normals) + 3 * size_t(zm.tri_first);
+        const size_t bytes = size_t(zm.tri_count) * 3 * sizeof(float4);
+        cudaMemcpyAsync(tmp_t, t, bytes, cudaMemcpyDeviceToDevice, s->ctx->stream);
+        cudaMemcpyAsync(tmp_n, n, bytes, cudaMemcpyDeviceToDevice, s->ctx->stream);
+        uint32_t count = 0;
+        rc = zbk_build_blas_device(s->ctx, tmp_t, tmp_n, zm.tri_count, zm.tri_first, next, t, n, nodes + next, &count);
+        roots[m] = next;
+        next += count;
+    }
+    cudaFree(tmp_t);
+    cudaFree(tmp_n);
+    if (rc) return rc;
+    for (auto& in : instances)
+        if (in.geom_kind == ZB_GEOM_MESH) in.pad[0] = roots[in.geom_index];
+    d.nodes = reinterpret_cast<const float4*>(nodes);
+    d.n_nodes = next;
+    s->bytes += size_t(next) * sizeof(zb_bvh_node);
+    return ZB_OK;
+}
+
 extern "C" int zb_scene_upload(zb_context* ctx, const zb_flat_scene* f, zb_scene** out) {
     if (!ctx || !f || !out) return fail(ZB_ERR_INVALID, "zb_scene_upload: NULL argument");
     int rc = validate(f);
@@ -158,12 +212,22 @@ extern "C" int zb_scene_upload(zb_context* ctx, const zb_flat_scene* f, zb_scene
     zb_scene* s = new zb_scene();
     s->ctx = ctx;
     SceneDev& d = s->dev;
-    rc = upload(s, f->nodes, f->n_nodes, sizeof(zb_bvh_node), &d.nodes);
+    bool device_blas = false;
+    for (uint32_t m = 0; m < f->n_meshes; m++) device_blas |= f->meshes[m].node_count == 0 && f->meshes[m].tri_count > 0;
+    if (!device_blas) rc = upload(s, f->nodes, f->n_nodes, sizeof(zb_bvh_node), &d.nodes);
     if (!rc) rc = upload(s, f->items, f->n_items, sizeof(zb_item), &d.items);
     if (!rc) rc = upload(s, f->cubes, f->n_cubes, sizeof(zb_cube), &d.cubes);
     if (!rc) rc = upload(s, f->tris, f->n_tris, sizeof(zb_tri), &d.tris);
     if (!rc) rc = upload(s, f->tri_normals, f->n_tris, sizeof(zb_tri_normals), &d.tri_normals);
-    if (!rc) rc = upload(s, f->instances, f->n_instances, sizeof(zb_instance), &d.instances);
+    std::vector<zb_instance> patched;
+    const zb_instance* instances = f->instances;
+    d.n_nodes = f->n_nodes;
+    if (!rc && device_blas) {
+        patched.assign(f->instances, f->instances + f->n_instances);
+        rc = build_device_blas(s, f, patched);
+        instances = patched.data();
+    }
+    if (!rc) rc = upload(s, instances, f->n_instances, sizeof(zb_instance), &d.instances);
     if (!rc) rc = upload(s, f->media, f->n_media, sizeof(zb_medium), &d.media);
     if (!rc) rc = upload(s, f->materials, f->n_materials, sizeof(zb_material), &d.materials);
     if (!rc) rc = upload(s, f->textures, f->n_textures, sizeof(zb_texture), &d.textures);
@@ -174,7 +238,6 @@ extern "C" int zb_scene_upload(zb_context* ctx, const zb_flat_scene* f, zb_scene
         zb_scene_destroy(s);
         return rc;
     }
-    d.n_nodes = f->n_nodes;
     d.n_items = f->n_items;
     d.n_media = f->n_media;
     s->env_hdr_texture = f->pad;

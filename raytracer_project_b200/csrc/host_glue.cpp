@@ -27,7 +27,7 @@ namespace {
 std::mutex g_mu;
 std::map<const zb_flat_scene*, std::unique_ptr<flat_scene>> g_live;
 
-int load(std::istream& in, const std::string& base_dir, const zb_flat_scene** out) {
+int load(std::istream& in, const std::string& base_dir, const zb_flat_scene** out, uint32_t flags = 0) {
     if (!out) return fail_host(ZB_ERR_INVALID, "zb_flat_scene_from_zscene: out is NULL");
     try {
         zscene::loader ld;
@@ -35,6 +35,7 @@ int load(std::istream& in, const std::string& base_dir, const zb_flat_scene** ou
         ld.parse(in);
         std::shared_ptr<hittable> world = ld.build_world();
         flattener fl;
+        fl.gpu_blas = (flags & ZB_FLATTEN_GPU_BLAS) != 0;
         if (const char* e = std::getenv("ZB_TLAS_LEAF")) fl.tlas_leaf = std::max(1, std::min(8, std::atoi(e)));  // tuning knobs
         if (const char* e = std::getenv("ZB_BLAS_LEAF")) fl.blas_leaf = std::max(1, std::min(8, std::atoi(e)));
         EnvironmentSettings env;
@@ -65,6 +66,20 @@ extern "C" int zb_flat_scene_from_zscene_text(const char* text, size_t len, cons
     if (!text) return fail_host(ZB_ERR_INVALID, "text is NULL");
     std::istringstream in(std::string(text, len));
     return load(in, "", out);
+}
+
+extern "C" int zb_flat_scene_from_zscene_ex(const char* path, const char* text, size_t len, uint32_t flags, const zb_flat_scene** out) {
+    if (path) {
+        std::ifstream in(path);
+        if (!in) return fail_host(ZB_ERR_IO, std::string("cannot open ") + path);
+        std::string p(path), dir;
+        size_t slash = p.find_last_of('/');
+        if (slash != std::string::npos) dir = p.substr(0, slash);
+        return load(in, dir, out, flags);
+    }
+    if (!text) return fail_host(ZB_ERR_INVALID, "path and text are both NULL");
+    std::istringstream in(std::string(text, len));
+    return load(in, "", out, flags);
 }
 
 extern "C" int zb_flat_scene_free(const zb_flat_scene* flat) {

@@ -73,6 +73,9 @@ struct flat_scene {
 class flattener {
 public:
     int tlas_leaf = 4, blas_leaf = 4;
+    // true: leave every mesh BLAS to the device builder (csrc/lbvh.cu): triangles are emitted in face
+    // order, the mesh carries node_count == 0 and zb_scene_upload builds a linear BVH for it on the GPU
+    bool gpu_blas = false;
 
     std::unique_ptr<flat_scene> run(const hittable& world, const EnvironmentSettings* env = nullptr) {
         out = std::make_unique<flat_scene>();
@@ -97,7 +100,7 @@ public:
                 if (nd.right >= 0) nd.right += int32_t(root);
                 all.push_back(nd);
             }
-            out->meshes[m].node_root = root;
+            out->meshes[m].node_root = blas_nodes[m].empty() ? 0u : root;
             out->meshes[m].node_count = uint32_t(blas_nodes[m].size());
         }
         for (auto& inst : out->instances)
@@ -374,11 +377,15 @@ private:
             for (size_t i = 0; i < m.tris.size(); i++)
                 boxes[i] = build_box::from(triangle::box_of(m.tris[i].v[0], m.tris[i].v[1], m.tris[i].v[2]));
             uint32_t first = uint32_t(out->tris.size());
-            bvh_builder b;
             std::vector<zb_bvh_node> nd;
-            std::vector<uint32_t> order;
-            b.build(boxes, blas_leaf, first, nd, order);
-            for (uint32_t slot : order) push_tri(m.tris[slot].v, m.tris[slot].n, slot);
+            if (gpu_blas) {
+                for (uint32_t slot = 0; slot < uint32_t(m.tris.size()); slot++) push_tri(m.tris[slot].v, m.tris[slot].n, slot);
+            } else {
+                bvh_builder b;
+                std::vector<uint32_t> order;
+                b.build(boxes, blas_leaf, first, nd, order);
+                for (uint32_t slot : order) push_tri(m.tris[slot].v, m.tris[slot].n, slot);
+            }
             zb_mesh zm{0, 0, first, uint32_t(m.tris.size())};
             out->meshes.push_back(zm);
             blas_nodes.push_back(std::move(nd));

@@ -13,26 +13,32 @@ ap.add_argument("--height", type=int, default=1080)
 ap.add_argument("--spp", type=int, default=64)
 ap.add_argument("--reps", type=int, default=3)
 ap.add_argument("--stats", action="store_true")
+ap.add_argument("--gpu-blas", action="store_true")
+ap.add_argument("--grid", type=int, default=0)
 ap.add_argument("--tag", default=os.environ.get("ZB_LIB", "main"))
 a = ap.parse_args()
 import tempfile, time
 gen = getattr(scenes, a.scene)
-out = gen(width=a.width, height=a.height, spp=a.spp)
+kw = {'grid': a.grid} if a.grid else {}
+out = gen(width=a.width, height=a.height, spp=a.spp, **kw)
 txt, cfg = out[0], out[1]
 t0 = time.time()
 if len(out) > 2:
-    flat = api.flatten_zscene(path=scenes.materialize(tempfile.mkdtemp(prefix="zb_tune_"), txt, cfg, out[2]))
+    flat = api.flatten_zscene(path=scenes.materialize(tempfile.mkdtemp(prefix="zb_tune_"), txt, cfg, out[2]), gpu_blas=a.gpu_blas)
 else:
     flat = api.flatten_zscene(txt)
 flatten_s = time.time() - t0
 dev = torch.device("cuda", 0)
 stream = torch.cuda.current_stream()
 ctx = api.Context(0, stream=stream.cuda_stream)
+torch.cuda.synchronize()
+t1 = time.time()
 sc = ctx.upload(flat)
+upload_s = time.time() - t1
 n = a.width * a.height
 acc = torch.empty(n, 4, device=dev)
 flush = torch.empty(256 << 20, device=dev, dtype=torch.uint8)
-res = {"tag": a.tag, "scene": a.scene, "flatten_s": round(flatten_s, 2), "scene_mb": round(flat.contents.nbytes() / 1e6, 2)}
+res = {"tag": a.tag, "scene": a.scene, "flatten_s": round(flatten_s, 2), "scene_mb": round(flat.contents.nbytes() / 1e6, 2), "upload_s": round(upload_s, 4), "gpu_blas": a.gpu_blas}
 if a.stats:
     sc.render_device(cfg, acc.data_ptr(), seed=1, stats=True)
     torch.cuda.synchronize()
