@@ -238,6 +238,14 @@ extern "C" int zb_scene_upload(zb_context* ctx, const zb_flat_scene* f, zb_scene
         zb_scene_destroy(s);
         return rc;
     }
+    if (!rc) {
+        cudaError_t e = zbk_convert_nodes(const_cast<float4*>(d.nodes), d.n_nodes, ctx->stream);
+        if (e != cudaSuccess) rc = fail(ZB_ERR_CUDA, std::string("zb_scene_upload: node re-encoding: ") + cudaGetErrorString(e));
+    }
+    if (rc) {
+        zb_scene_destroy(s);
+        return rc;
+    }
     d.n_items = f->n_items;
     d.n_media = f->n_media;
     s->env_hdr_texture = f->pad;

@@ -356,3 +356,30 @@ cudaError_t zbk_launch_resolve(const float4* accum, size_t n, float scale, float
     k_resolve<<<unsigned((n + 255) / 256), 256, 0, stream>>>(accum, n, scale, out_f4, out_f64);
     return cudaGetLastError();
 }
+
+// Device-side re-encoding of the BVH nodes after upload / device build: (lo, hi) per axis -> (centre, half extent),
+// rounded outwards so that the re-encoded box contains the original one.  An empty child (inverted box) becomes
+// half extent -inf, which no ray can hit.  See ZB_BOX_CH in trace.cuh.
+__global__ void __launch_bounds__(256) k_convert_nodes(float4* __restrict__ nodes, uint32_t n) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= 3 * n) return;
+    const uint32_t node = i / 3, part = i - 3 * node;  // the three float4 that hold (lo, hi) pairs
+    float4 v = nodes[4 * size_t(node) + part];
+    auto enc = [](float lo, float hi, float& c, float& h) {
+        if (!(lo <= hi)) { c = 0.f; h = -INFINITY; return; }
+        c = 0.5f * lo + 0.5f * hi;
+        h = fmaxf(__fsub_ru(hi, c), __fsub_ru(c, lo));
+    };
+    float4 o;
+    enc(v.x, v.y, o.x, o.y);
+    enc(v.z, v.w, o.z, o.w);
+    nodes[4 * size_t(node) + part] = o;
+}
+
+bool zbk_nodes_center_half() { return ZB_BOX_CH != 0; }
+
+cudaError_t zbk_convert_nodes(float4* nodes, uint32_t n, cudaStream_t stream) {
+    if (!n || !ZB_BOX_CH) return cudaSuccess;
+    k_convert_nodes<<<(3 * n + 255) / 256, 256, 0, stream>>>(nodes, n);
+    return cudaGetLastError();
+}
