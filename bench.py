@@ -32,6 +32,10 @@ sys.path.insert(0, ROOT)
 
 WIDTH, HEIGHT, SPP, DEPTH = 1920, 1080, 64, 50
 WORKLOAD = f"weekend_seed1_{WIDTH}x{HEIGHT}_{SPP}spp_depth{DEPTH}"
+# DRAM traffic of one k_render launch on the headline frame (ncu, profiles/r01_k_render_v3_raw_key.txt): 0.18 MB read +
+# 2.34 MB written while the kernel runs — the 60 KB scene is L1-resident and most of the 33 MB of float4 sums is still
+# in the 126 MB L2 when the kernel ends.
+NCU_DRAM_BYTES_PER_LAUNCH = 177920 + 2336512
 HARNESS = os.path.join(ROOT, "oracle", "_ref", "ref_harness")   # the unmodified reference (kind "reference")
 PORT = os.path.join(ROOT, "oracle", "_build", "zoracle")         # CPU restatement, used only if the former is absent
 
@@ -286,8 +290,11 @@ def ours(args):
                             "3-double layout by host threads while later chunks are in flight"},
             "gpu_launches": 2 * args.steps,
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": hbm_peak, "unit": "GB/s", "frac": achieved / hbm_peak,
-                         "traffic": None, "peak_kind": f"{peak_kind} burst copy bandwidth",
-                         "kernel": "k_render<false>", "algorithmic_bytes_per_launch": per_gpu_bytes,
+                         "traffic": NCU_DRAM_BYTES_PER_LAUNCH if world == 1 else None,
+                         "traffic_source": "dram__bytes_read.sum + dram__bytes_write.sum of k_render<false,false> on this workload, "
+                                           "ncu --set full capture summarised in profiles/r01_k_render_v3_raw_key.txt",
+                         "peak_kind": f"{peak_kind} burst copy bandwidth",
+                         "kernel": "k_render<false,false>", "algorithmic_bytes_per_launch": per_gpu_bytes,
                          "note": "scene (60 KB) is L1/L2-resident: algorithmic bytes are served by L1, so this "
                                  "fraction can exceed 1; the binding roofline is FP32/issue (roofline_fp32)"},
             "roofline_fp32": {"achieved": alg_flop / world / (kernel_ms * 1e-3) * 1e-12, "peak": fp32_peak,
