@@ -207,7 +207,8 @@ typedef struct zb_render_opts {
      * sums go to accum_f4 and refraction sums to the first W*H float4 of accum_aux_f4. */
     int32_t use_reflection, use_refraction;
     int32_t light_pass;
-    int32_t pad;
+    int32_t accumulate;               /* zb_render_device: 1 = add this call's samples to the sums already in accum_f4
+                                         (progressive rendering, resume from a checkpoint) instead of overwriting */
 } zb_render_opts;
 
 /* Host-side outputs in the reference's own layout: row-major, top row first, 3 doubles per pixel
@@ -293,6 +294,15 @@ typedef struct zb_probe {
 int zb_probe_rays(zb_context* ctx, const zb_scene* scene, const zb_environment* env, size_t n,
                   const float* origins, const float* directions, zb_probe* out);
 
+/* Accumulation checkpoint: the float4 radiance sums + how many samples of which seed they hold, so a
+ * progressive render can stop and resume (the Philox counter carries the global sample index, so samples
+ * [0, k) + [k, n) give the frame of [0, n)).  "ZBCK" file: magic, u32 width, height, samples_done, reserved, u64 seed,
+ * then W*H float4. */
+int zb_checkpoint_save(zb_context* ctx, const char* path, const void* accum_f4, int width, int height, int samples_done,
+                       uint64_t seed);
+int zb_checkpoint_load(zb_context* ctx, const char* path, void* accum_f4, int width, int height, int* samples_done,
+                       uint64_t* seed);
+
 int zb_get_stats(zb_context* ctx, zb_stats* out);
 
 /* ------------------------------------------------------------------------------------------------
@@ -347,6 +357,10 @@ int zb_flat_scene_from_zscene_text(const char* text, size_t len, const zb_flat_s
  * meshes drops from seconds to milliseconds, at a lower tree quality.  Exactly one of path / text is given. */
 #define ZB_FLATTEN_GPU_BLAS 1u
 int zb_flat_scene_from_zscene_ex(const char* path, const char* text, size_t len, uint32_t flags, const zb_flat_scene** out);
+/* Flat scene on disk ("ZBFS" container): written once, loaded by every rank / later run without
+ * re-parsing assets or re-building the BVH.  A loaded scene is released with zb_flat_scene_free. */
+int zb_flat_scene_save(const zb_flat_scene* flat, const char* path);
+int zb_flat_scene_load(const char* path, const zb_flat_scene** out);
 int zb_flat_scene_free(const zb_flat_scene* flat);
 
 #ifdef __cplusplus

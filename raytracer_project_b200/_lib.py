@@ -73,7 +73,7 @@ class RenderOpts(C.Structure):
                 ("tile_ranks", C.c_int32), ("use_albedo", C.c_int32), ("use_normal", C.c_int32),
                 ("use_z_depth", C.c_int32), ("z_depth_max_dist", C.c_double), ("collect_stats", C.c_int32),
                 ("samples_per_launch", C.c_int32), ("use_reflection", C.c_int32), ("use_refraction", C.c_int32),
-                ("light_pass", C.c_int32), ("pad", C.c_int32)]
+                ("light_pass", C.c_int32), ("accumulate", C.c_int32)]
 
 
 class Outputs(C.Structure):
@@ -125,6 +125,8 @@ SYMBOLS = {
     "zb_resolve_device": (C.c_int, [C.c_void_p, C.c_void_p, C.c_size_t, C.c_double, C.c_void_p, C.c_void_p]),
     "zb_primary_ids": (C.c_int, [C.c_void_p, C.c_void_p, C.POINTER(Camera), C.c_void_p, C.c_void_p, C.c_void_p]),
     "zb_get_stats": (C.c_int, [C.c_void_p, C.POINTER(Stats)]),
+    "zb_checkpoint_save": (C.c_int, [C.c_void_p, C.c_char_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_uint64]),
+    "zb_checkpoint_load": (C.c_int, [C.c_void_p, C.c_char_p, C.c_void_p, C.c_int, C.c_int, C.POINTER(C.c_int), C.POINTER(C.c_uint64)]),
     "zb_analyze_device": (C.c_int, [C.c_void_p, C.c_void_p, C.c_size_t, C.POINTER(ImageStats)]),
     "zb_auto_exposure": (C.c_double, [C.POINTER(Post), C.POINTER(ImageStats)]),
     "zb_finish_device": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.POINTER(Post), C.c_int, C.c_void_p, C.c_void_p]),
@@ -132,6 +134,8 @@ SYMBOLS = {
     "zb_flat_scene_from_zscene": (C.c_int, [C.c_char_p, C.POINTER(C.POINTER(FlatScene))]),
     "zb_flat_scene_from_zscene_text": (C.c_int, [C.c_char_p, C.c_size_t, C.POINTER(C.POINTER(FlatScene))]),
     "zb_flat_scene_from_zscene_ex": (C.c_int, [C.c_char_p, C.c_char_p, C.c_size_t, C.c_uint32, C.POINTER(C.POINTER(FlatScene))]),
+    "zb_flat_scene_save": (C.c_int, [C.POINTER(FlatScene), C.c_char_p]),
+    "zb_flat_scene_load": (C.c_int, [C.c_char_p, C.POINTER(C.POINTER(FlatScene))]),
     "zb_flat_scene_free": (C.c_int, [C.POINTER(FlatScene)]),
 }
 

@@ -32,6 +32,18 @@ def flatten_zscene(text: str | None = None, path: str | None = None, gpu_blas: b
     return out
 
 
+def save_flat(flat, path: str):
+    """zb_flat_scene_save: the flattened scene as a ZBFS file."""
+    check(_lib.load().zb_flat_scene_save(flat, path.encode()))
+
+
+def load_flat(path: str):
+    """zb_flat_scene_load: a ZBFS file -> zb_flat_scene (free with free_flat)."""
+    out = C.POINTER(FlatScene)()
+    check(_lib.load().zb_flat_scene_load(path.encode(), C.byref(out)))
+    return out
+
+
 def free_flat(flat):
     _lib.load().zb_flat_scene_free(flat)
 
@@ -151,6 +163,14 @@ class Context:
         check(self.lib.zb_finish(self.h, img.ctypes.data, img.shape[1], img.shape[0], C.byref(post), pass_kind, out.ctypes.data))
         return out
 
+    def checkpoint_save(self, path: str, accum_ptr: int, width: int, height: int, samples_done: int, seed: int):
+        check(self.lib.zb_checkpoint_save(self.h, path.encode(), C.c_void_p(accum_ptr), width, height, samples_done, seed))
+
+    def checkpoint_load(self, path: str, accum_ptr: int, width: int, height: int):
+        done, seed = C.c_int(), C.c_uint64()
+        check(self.lib.zb_checkpoint_load(self.h, path.encode(), C.c_void_p(accum_ptr), width, height, C.byref(done), C.byref(seed)))
+        return done.value, seed.value
+
     def upload(self, flat) -> "Scene":
         s = C.c_void_p()
         check(self.lib.zb_scene_upload(self.h, flat, C.byref(s)))
@@ -196,12 +216,13 @@ class Scene:
         return res
 
     def render_device(self, cfg: RenderConfig, accum_ptr: int, aux_ptr: int = 0, seed=1, sample_range=None, tile=None,
-                      stats=False, light_pass=False):
+                      stats=False, light_pass=False, accumulate=False, samples_per_launch=0):
         """zb_render_device: radiance SUMS of this rank's share into a device float4 buffer (async).
         light_pass: reflection sums -> accum, refraction sums -> first plane of aux (camera.hpp:492-517)."""
         cam, env = camera_struct(cfg), env_struct(cfg)
-        o = opts_struct(cfg, seed, sample_range, tile, stats)
+        o = opts_struct(cfg, seed, sample_range, tile, stats, samples_per_launch)
         o.light_pass = int(light_pass)
+        o.accumulate = int(accumulate)
         check(self.ctx.lib.zb_render_device(self.ctx.h, self.h, C.byref(cam), C.byref(env), C.byref(o),
                                             C.c_void_p(accum_ptr), C.c_void_p(aux_ptr) if aux_ptr else None))
 

@@ -192,7 +192,8 @@ int launch_share(zb_context* ctx, RenderParams P, const zb_render_opts* o, const
     int per = o->samples_per_launch > 0 ? o->samples_per_launch : (cancel || progress ? 16 : se - sb);
     per = std::max(per, 1);
     const size_t pixels = size_t(P.cam.width) * P.cam.height;
-    if (zero_first && (P.tile_ranks > 1 || se == sb)) {
+    const bool keep = o->accumulate != 0;  // the caller's sums stay: progressive rendering / resume
+    if (zero_first && !keep && (P.tile_ranks > 1 || se == sb)) {
         // tile stripes leave other ranks' pixels untouched: they must read as zero sums
         ZB_CUDA(cudaMemsetAsync(P.accum, 0, pixels * sizeof(float4), ctx->stream));
         if (P.accum_aux) ZB_CUDA(cudaMemsetAsync(P.accum_aux, 0, 3 * pixels * sizeof(float4), ctx->stream));
@@ -202,7 +203,7 @@ int launch_share(zb_context* ctx, RenderParams P, const zb_render_opts* o, const
         if (cancel && *cancel) return fail(ZB_ERR_CANCELLED, "render cancelled");
         P.sample_begin = s;
         P.sample_end = std::min(s + per, se);
-        P.accumulate = s > sb ? 1 : 0;
+        P.accumulate = (s > sb || keep) ? 1 : 0;
         ZB_CUDA(zbk_launch_render(P, owned_tiles(P), o->collect_stats != 0, ctx->stream));
         ctx->stats.launches++;
         done = P.sample_end - sb;
@@ -448,6 +449,50 @@ extern "C" int zb_probe_rays(zb_context* ctx, const zb_scene* scene, const zb_en
     cudaFree(d_out);
     if (e != cudaSuccess) return fail(ZB_ERR_CUDA, std::string("zb_probe_rays: ") + cudaGetErrorString(e));
     ctx->stats.launches++;
+    return ZB_OK;
+}
+
+extern "C" int zb_checkpoint_save(zb_context* ctx, const char* path, const void* accum_f4, int width, int height,
+                                  int samples_done, uint64_t seed) {
+    if (!ctx || !path || !accum_f4 || width < 1 || height < 1) return fail(ZB_ERR_INVALID, "zb_checkpoint_save: bad argument");
+    ZB_CUDA(cudaSetDevice(ctx->device));
+    const size_t pixels = size_t(width) * height;
+    std::vector<float4> host(pixels);
+    ZB_CUDA(cudaMemcpyAsync(host.data(), accum_f4, pixels * sizeof(float4), cudaMemcpyDeviceToHost, ctx->stream));
+    ZB_CUDA(cudaStreamSynchronize(ctx->stream));
+    FILE* f = std::fopen(path, "wb");
+    if (!f) return fail(ZB_ERR_IO, std::string("cannot create ") + path);
+    const uint32_t hdr[4] = {uint32_t(width), uint32_t(height), uint32_t(samples_done), 0u};
+    bool ok = std::fwrite("ZBCK", 1, 4, f) == 4 && std::fwrite(hdr, 4, 4, f) == 4 && std::fwrite(&seed, 8, 1, f) == 1 &&
+              std::fwrite(host.data(), sizeof(float4), pixels, f) == pixels;
+    ok = (std::fclose(f) == 0) && ok;
+    return ok ? ZB_OK : fail(ZB_ERR_IO, std::string("short write to ") + path);
+}
+
+extern "C" int zb_checkpoint_load(zb_context* ctx, const char* path, void* accum_f4, int width, int height, int* samples_done,
+                                  uint64_t* seed) {
+    if (!ctx || !path || !accum_f4 || width < 1 || height < 1) return fail(ZB_ERR_INVALID, "zb_checkpoint_load: bad argument");
+    FILE* f = std::fopen(path, "rb");
+    if (!f) return fail(ZB_ERR_IO, std::string("cannot open ") + path);
+    char magic[4];
+    uint32_t hdr[4];
+    uint64_t sd = 0;
+    const size_t pixels = size_t(width) * height;
+    std::vector<float4> host(pixels);
+    bool ok = std::fread(magic, 1, 4, f) == 4 && std::memcmp(magic, "ZBCK", 4) == 0 && std::fread(hdr, 4, 4, f) == 4 &&
+              std::fread(&sd, 8, 1, f) == 1;
+    if (ok && (hdr[0] != uint32_t(width) || hdr[1] != uint32_t(height))) {
+        std::fclose(f);
+        return fail(ZB_ERR_INVALID, std::string(path) + ": checkpoint of another frame size");
+    }
+    ok = ok && std::fread(host.data(), sizeof(float4), pixels, f) == pixels;
+    std::fclose(f);
+    if (!ok) return fail(ZB_ERR_INVALID, std::string(path) + ": not a ZBCK checkpoint or truncated");
+    ZB_CUDA(cudaSetDevice(ctx->device));
+    ZB_CUDA(cudaMemcpyAsync(accum_f4, host.data(), pixels * sizeof(float4), cudaMemcpyHostToDevice, ctx->stream));
+    ZB_CUDA(cudaStreamSynchronize(ctx->stream));
+    if (samples_done) *samples_done = int(hdr[2]);
+    if (seed) *seed = sd;
     return ZB_OK;
 }
 

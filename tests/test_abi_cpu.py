@@ -153,3 +153,37 @@ def test_drop_in_camera_adapter_compiles_and_links(tmp_path):
                     "-o", exe, "-L" + os.path.join(root, "raytracer_project_b200"), "-lzenith_b200",
                     "-Wl,-rpath," + os.path.join(root, "raytracer_project_b200")], check=True)
     assert subprocess.run([exe]).returncode == 2  # usage error: no compute without arguments
+
+
+def test_flat_scene_file_round_trip(tmp_path):
+    """ZBFS container: save -> load reproduces every array byte for byte; garbage and truncated files
+    are rejected with an error, not a crash."""
+    # the exterior scene fills every array but media: meshes-free items, instances, cubes, u8 + f32 texel pools
+    txt, cfg, files = scenes.exterior(seed=4, width=64, height=36, spp=1, small=20, hdr_size=64)
+    flat = api.flatten_zscene(path=scenes.materialize(str(tmp_path), txt, cfg, files))
+    p = str(tmp_path / "scene.zbfs")
+    api.save_flat(flat, p)
+    back = api.load_flat(p)
+    a, b = flat.contents, back.contents
+    for name, _ in a._fields_:
+        if not isinstance(getattr(a, name), int):
+            continue
+        if name.startswith("n_") or name in ("abi_version", "pad"):
+            assert getattr(a, name) == getattr(b, name), name
+    sizes = {"nodes": a.n_nodes * 64, "items": a.n_items * 32, "cubes": a.n_cubes * 32, "tris": a.n_tris * 48,
+             "tri_normals": a.n_tris * 48, "instances": a.n_instances * 128, "meshes": a.n_meshes * 16, "media": a.n_media * 32,
+             "materials": a.n_materials * 32, "textures": a.n_textures * 32, "spheres_obj": a.n_spheres_obj * 16,
+             "texels_u8": a.n_texels_u8 * 4, "texels_f32": a.n_texels_f32 * 16}
+    assert sizes["texels_u8"] and sizes["texels_f32"] and sizes["instances"] and sizes["cubes"]
+    for name, nbytes in sizes.items():
+        if nbytes:
+            assert C.string_at(getattr(a, name), nbytes) == C.string_at(getattr(b, name), nbytes), name
+    api.free_flat(back)
+    api.free_flat(flat)
+    raw = open(p, "rb").read()
+    open(p, "wb").write(raw[: len(raw) // 2])
+    with pytest.raises(_lib.ZbError):
+        api.load_flat(p)
+    open(p, "wb").write(b"not a scene at all" * 10)
+    with pytest.raises(_lib.ZbError):
+        api.load_flat(p)

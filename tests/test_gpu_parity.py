@@ -484,3 +484,33 @@ def test_gpu_built_blas_gives_the_same_hits(gpu_ctx, tmp_path):
     rrmse = float(np.sqrt(((a - b) ** 2).sum() / (a ** 2).sum()))
     print(f"host-SAH vs device-LBVH image, same seed: rRMSE {rrmse * 100:.3f} %, means {a.mean():.5f} {b.mean():.5f}")
     assert abs(a.mean() / b.mean() - 1) < 0.005 and rrmse < 0.05
+
+
+# ------------------------------------------------------------------ on-disk formats
+def test_checkpoint_resume_and_scene_file_reproduce_the_frame(gpu_ctx, tmp_path):
+    """Progressive render stopped after 32 of 64 samples, checkpointed (ZBCK), resumed in a scene re-loaded from its
+    ZBFS file: the sums equal those of an uninterrupted 2 x 32-sample render bit for bit."""
+    import torch
+    txt, cfg = scenes.weekend(seed=1, width=320, height=180, spp=64)
+    flat = api.flatten_zscene(txt)
+    api.save_flat(flat, str(tmp_path / "w.zbfs"))
+    sc = gpu_ctx.upload(flat)
+    api.free_flat(flat)
+    n = 320 * 180
+    whole = torch.zeros(n, 4, device="cuda")
+    sc.render_device(cfg, whole.data_ptr(), seed=9, samples_per_launch=32)
+    part = torch.zeros(n, 4, device="cuda")
+    sc.render_device(cfg, part.data_ptr(), seed=9, sample_range=(0, 32))
+    gpu_ctx.checkpoint_save(str(tmp_path / "half.zbck"), part.data_ptr(), 320, 180, 32, 9)
+    sc.close()
+    flat2 = api.load_flat(str(tmp_path / "w.zbfs"))
+    sc2 = gpu_ctx.upload(flat2)
+    api.free_flat(flat2)
+    resumed = torch.full((n, 4), 7.0, device="cuda")
+    done, seed = gpu_ctx.checkpoint_load(str(tmp_path / "half.zbck"), resumed.data_ptr(), 320, 180)
+    assert (done, seed) == (32, 9)
+    sc2.render_device(cfg, resumed.data_ptr(), seed=seed, sample_range=(done, 64), accumulate=True)
+    torch.cuda.synchronize()
+    sc2.close()
+    assert torch.equal(resumed, whole)
+    assert float(whole[:, 3].min()) == 64.0 and float(whole[:, :3].mean()) > 1.0
