@@ -239,6 +239,25 @@ def weekend(seed: int = 1, width: int = 1200, height: int = 675, spp: int = 10, 
     return w.text(), cfg
 
 
+def big(seed: int = 5, width: int = 3840, height: int = 2160, spp: int = 1024, max_depth: int = 50, grid: int = 2237):
+    """C5: the C1 spheres + one OBJ heightfield of 2 (grid-1)^2 triangles (grid 2237 ->
+    10 000 712) under translate(scale(material_instance(model))), C1 camera pulled back."""
+    txt, cfg = weekend(seed=1, width=width, height=height, spp=spp, max_depth=max_depth)
+    lines = txt.rstrip("\n").split("\n")
+    world = [l for l in lines if l.startswith("obj world ")][0]
+    body = [l for l in lines if l is not world and not l.startswith("world ")]
+    body += ["mat terrain_mat lambertian color 0.45 0.55 0.35",
+             "obj terrain_model model heightfield.obj null 1.0",
+             "obj terrain_mi matinst terrain_model terrain_mat",
+             "obj terrain_s scale terrain_mi 2.0 1.0 2.0",
+             "obj terrain translate terrain_s 0.0 -0.25 0.0"]
+    body.append(world + " terrain")
+    body.append("world world")
+    cfg.lookfrom = (19.5, 3.0, 4.5)
+    cfg.focus_dist = 15.0
+    return "\n".join(body) + "\n", cfg, {"heightfield.obj": _heightfield_obj(grid, seed)}
+
+
 def materialize(directory: str, text: str, cfg: RenderConfig, files: dict | None = None):
     """Write `s.zscene`, `s.cfg` and the scene's asset files into `directory`; returns the zscene path."""
     import os
@@ -302,15 +321,15 @@ def _heightfield_obj(n: int, seed: int) -> str:
     nrm /= np.linalg.norm(nrm, axis=-1, keepdims=True)
     v = np.stack([x, y, z], axis=-1).reshape(-1, 3)
     out = ["# synthetic heightfield"]
-    out += ["v %.6f %.6f %.6f" % tuple(r) for r in v]
-    out += ["vn %.6f %.6f %.6f" % tuple(r) for r in nrm.reshape(-1, 3)]
+    out += ["v %.6f %.6f %.6f" % r for r in map(tuple, v.tolist())]
+    out += ["vn %.6f %.6f %.6f" % r for r in map(tuple, nrm.reshape(-1, 3).tolist())]
     i, j = np.meshgrid(np.arange(n - 1), np.arange(n - 1), indexing="ij")
     a = (i * n + j + 1).ravel()  # 1-based
     b, c, d = a + n, a + n + 1, a + 1
     f1 = np.stack([a, d, c], axis=1)  # counter-clockwise seen from +y
     f2 = np.stack([a, c, b], axis=1)
     faces = np.concatenate([f1, f2], axis=0)
-    out += ["f %d//%d %d//%d %d//%d" % (r[0], r[0], r[1], r[1], r[2], r[2]) for r in faces]
+    out += ["f %d//%d %d//%d %d//%d" % (r[0], r[0], r[1], r[1], r[2], r[2]) for r in faces.tolist()]
     return "\n".join(out) + "\n"
 
 
