@@ -60,6 +60,7 @@ extern "C" int zb_context_destroy(zb_context* ctx) {
     cudaFree(ctx->fin_b);
     cudaFree(ctx->fin_in);
     cudaFree(ctx->fin_stats);
+    zbk_wavefront_free(ctx->wf);
     if (ctx->pinned) cudaFreeHost(ctx->pinned);
     for (auto& ev : ctx->ev) cudaEventDestroy(ev);
     for (auto& ev : ctx->chunk_ev) cudaEventDestroy(ev);

@@ -198,14 +198,25 @@ int launch_share(zb_context* ctx, RenderParams P, const zb_render_opts* o, const
         ZB_CUDA(cudaMemsetAsync(P.accum, 0, pixels * sizeof(float4), ctx->stream));
         if (P.accum_aux) ZB_CUDA(cudaMemsetAsync(P.accum_aux, 0, 3 * pixels * sizeof(float4), ctx->stream));
     }
+    // experimental: ZB_WAVEFRONT=1 renders the beauty pass with the wavefront kernels (ZB_WF_SLOTS = path slots)
+    const char* wf_env = getenv("ZB_WAVEFRONT");
+    const bool wavefront = wf_env && atoi(wf_env) > 0 && !o->collect_stats;
+    const char* wf_slots_env = getenv("ZB_WF_SLOTS");
+    const size_t wf_slots = wf_slots_env ? size_t(atoll(wf_slots_env)) : 0;
     int done = 0;
     for (int s = sb; s < se; s += per) {
         if (cancel && *cancel) return fail(ZB_ERR_CANCELLED, "render cancelled");
         P.sample_begin = s;
         P.sample_end = std::min(s + per, se);
         P.accumulate = (s > sb || keep) ? 1 : 0;
-        ZB_CUDA(zbk_launch_render(P, owned_tiles(P), o->collect_stats != 0, ctx->stream));
-        ctx->stats.launches++;
+        if (wavefront && zbk_wavefront_supported(P)) {
+            int iters = 0;
+            ZB_CUDA(zbk_launch_wavefront(P, &ctx->wf, wf_slots, &iters, ctx->stream));
+            ctx->stats.launches += 2 + 2 * iters;
+        } else {
+            ZB_CUDA(zbk_launch_render(P, owned_tiles(P), o->collect_stats != 0, ctx->stream));
+            ctx->stats.launches++;
+        }
         done = P.sample_end - sb;
         if (progress || cancel) {
             ZB_CUDA(cudaStreamSynchronize(ctx->stream));

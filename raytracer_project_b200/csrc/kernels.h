@@ -16,3 +16,10 @@ cudaError_t zbk_launch_probe(const RenderParams& P, size_t n, const float* org, 
 // nodes (lo, hi) -> (centre, half extent) in place, when the traversal is compiled for that encoding (ZB_BOX_CH)
 cudaError_t zbk_convert_nodes(float4* nodes, uint32_t n, cudaStream_t stream);
 bool zbk_nodes_center_half();
+
+// wavefront form of the render (wavefront.cu): trace / shade kernels per bounce over a compacted path queue
+struct zb_wf_scratch;
+bool zbk_wavefront_supported(const RenderParams& P);
+cudaError_t zbk_launch_wavefront(const RenderParams& P, zb_wf_scratch** scratch, size_t want_slots, int* iterations,
+                                 cudaStream_t stream);
+void zbk_wavefront_free(zb_wf_scratch* w);

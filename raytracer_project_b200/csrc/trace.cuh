@@ -251,69 +251,77 @@ ZB_DEV bool tlas_leaf(const SceneDev& sc, uint32_t code, float3 o, float3 d, flo
     return false;
 }
 
-// Closest hit of one ray.  "while-while" traversal (Aila & Laine 2009): every lane first descends through
-// inner nodes until it holds a leaf, then the warp runs the primitive tests together; this keeps more
-// lanes on the same instruction than one loop that alternates between a node step and a leaf step.
-// Only the stack is addressed dynamically (local memory); every other piece of traversal state is a
-// scalar the compiler keeps in registers, and the four-way child selection is written as selects plus
-// one predicated push / pop so that the node step has no divergent branches.
-template <bool STATS>
-ZB_DEV bool trace(const SceneDev& sc, float3 o, float3 d, float tmin, float tmax, const MediumRng& rng, Hit& hit,
-                  Counters& cnt) {
-    int stack[ZB_STACK];
-    cnt.rays++;
-    hit.t = tmax;
-    hit.item = 0xFFFFFFFFu;
-    hit.prim = 0;
-    stack[0] = ZB_TRAVERSAL_DONE;
-    int sp = 1;
-    int cur = sc.n_nodes ? 0 : ZB_TRAVERSAL_DONE;
-    bool in_blas = false;
-    uint32_t blas_item = 0;
-    float3 ro = o, rd = d;  // ray in the current frame (world, or the object space of the instance traversed)
+// Traversal state of one ray.  Only the stack (owned by the caller, local memory) is addressed dynamically; every
+// other member is a scalar the compiler keeps in registers as long as the object itself never has its address taken
+// (all users are force-inlined).  node_step() = one visit of an inner node (both child boxes, near child first, far
+// child pushed); leaf_step() = the primitive tests of the leaf / marker in `cur`, then the next entry is popped.
+// The four-way child selection is written as selects plus one predicated push / pop: no divergent branch.
+struct RayWalk {
+    int cur, sp;
+    bool in_blas;
+    uint32_t blas_item;
+    float3 ro, rd;  // ray in the current frame (world, or the object space of the instance being traversed)
     RayBox rb;
-    rb.set(o, d);
-    while (cur != ZB_TRAVERSAL_DONE) {
-        while (cur >= 0) {
-            const float4* np = sc.nodes + 4 * size_t(cur);
-            const float4 n0 = __ldg(np), n1 = __ldg(np + 1), n2 = __ldg(np + 2);
-            const float2 nc = __ldg(reinterpret_cast<const float2*>(np + 3));
-            if (STATS) cnt.nodes++;
+    Hit hit;
+
+    ZB_DEV void begin(const SceneDev& sc, float3 o, float3 d, float tmax, int* stack) {
+        hit.t = tmax;
+        hit.item = 0xFFFFFFFFu;
+        hit.prim = 0;
+        stack[0] = ZB_TRAVERSAL_DONE;
+        sp = 1;
+        cur = sc.n_nodes ? 0 : ZB_TRAVERSAL_DONE;
+        in_blas = false;
+        blas_item = 0;
+        ro = o;
+        rd = d;
+        rb.set(o, d);
+    }
+
+    template <bool STATS>
+    ZB_DEV void node_step(const SceneDev& sc, float tmin, int* stack, Counters& cnt) {
+        const float4* np = sc.nodes + 4 * size_t(cur);
+        const float4 n0 = __ldg(np), n1 = __ldg(np + 1), n2 = __ldg(np + 2);
+        const float2 nc = __ldg(reinterpret_cast<const float2*>(np + 3));
+        if (STATS) cnt.nodes++;
 #if ZB_BOX_CH
-            // nodes re-encoded at upload as centre / half extent (zbk_convert_nodes): t = (c - o) / d -+ h / |d| needs
-            // no per-axis min / max, which moves 12 of the 20 FMNMX of a visit from the half-rate ALU pipe (the
-            // busiest pipe of this kernel, ncu: 66 %) to 6 more FFMA on the FMA pipe
-            const float mlx = fmaf(n0.x, rb.inv.x, -rb.ood.x), mly = fmaf(n0.z, rb.inv.y, -rb.ood.y), mlz = fmaf(n2.x, rb.inv.z, -rb.ood.z);
-            const float mrx = fmaf(n1.x, rb.inv.x, -rb.ood.x), mry = fmaf(n1.z, rb.inv.y, -rb.ood.y), mrz = fmaf(n2.z, rb.inv.z, -rb.ood.z);
-            const float ax = fabsf(rb.inv.x), ay = fabsf(rb.inv.y), az = fabsf(rb.inv.z);
-            float ln = fmaxf(max3(fmaf(-n0.y, ax, mlx), fmaf(-n0.w, ay, mly), fmaf(-n2.y, az, mlz)), tmin);
-            float lf = fminf(min3(fmaf(n0.y, ax, mlx), fmaf(n0.w, ay, mly), fmaf(n2.y, az, mlz)), hit.t) * ZB_BOX_INFLATE;
-            float rn = fmaxf(max3(fmaf(-n1.y, ax, mrx), fmaf(-n1.w, ay, mry), fmaf(-n2.w, az, mrz)), tmin);
-            float rf = fminf(min3(fmaf(n1.y, ax, mrx), fmaf(n1.w, ay, mry), fmaf(n2.w, az, mrz)), hit.t) * ZB_BOX_INFLATE;
+        // nodes re-encoded at upload as centre / half extent (zbk_convert_nodes): t = (c - o) / d -+ h / |d| needs
+        // no per-axis min / max, which moves 12 of the 20 FMNMX of a visit from the half-rate ALU pipe (the
+        // busiest pipe of this kernel, ncu: 66 %) to 6 more FFMA on the FMA pipe
+        const float mlx = fmaf(n0.x, rb.inv.x, -rb.ood.x), mly = fmaf(n0.z, rb.inv.y, -rb.ood.y), mlz = fmaf(n2.x, rb.inv.z, -rb.ood.z);
+        const float mrx = fmaf(n1.x, rb.inv.x, -rb.ood.x), mry = fmaf(n1.z, rb.inv.y, -rb.ood.y), mrz = fmaf(n2.z, rb.inv.z, -rb.ood.z);
+        const float ax = fabsf(rb.inv.x), ay = fabsf(rb.inv.y), az = fabsf(rb.inv.z);
+        float ln = fmaxf(max3(fmaf(-n0.y, ax, mlx), fmaf(-n0.w, ay, mly), fmaf(-n2.y, az, mlz)), tmin);
+        float lf = fminf(min3(fmaf(n0.y, ax, mlx), fmaf(n0.w, ay, mly), fmaf(n2.y, az, mlz)), hit.t) * ZB_BOX_INFLATE;
+        float rn = fmaxf(max3(fmaf(-n1.y, ax, mrx), fmaf(-n1.w, ay, mry), fmaf(-n2.w, az, mrz)), tmin);
+        float rf = fminf(min3(fmaf(n1.y, ax, mrx), fmaf(n1.w, ay, mry), fmaf(n2.w, az, mrz)), hit.t) * ZB_BOX_INFLATE;
 #else
-            float lx0 = fmaf(n0.x, rb.inv.x, -rb.ood.x), lx1 = fmaf(n0.y, rb.inv.x, -rb.ood.x);
-            float ly0 = fmaf(n0.z, rb.inv.y, -rb.ood.y), ly1 = fmaf(n0.w, rb.inv.y, -rb.ood.y);
-            float lz0 = fmaf(n2.x, rb.inv.z, -rb.ood.z), lz1 = fmaf(n2.y, rb.inv.z, -rb.ood.z);
-            float rx0 = fmaf(n1.x, rb.inv.x, -rb.ood.x), rx1 = fmaf(n1.y, rb.inv.x, -rb.ood.x);
-            float ry0 = fmaf(n1.z, rb.inv.y, -rb.ood.y), ry1 = fmaf(n1.w, rb.inv.y, -rb.ood.y);
-            float rz0 = fmaf(n2.z, rb.inv.z, -rb.ood.z), rz1 = fmaf(n2.w, rb.inv.z, -rb.ood.z);
-            float ln = fmaxf(max3(fminf(lx0, lx1), fminf(ly0, ly1), fminf(lz0, lz1)), tmin);
-            float lf = fminf(min3(fmaxf(lx0, lx1), fmaxf(ly0, ly1), fmaxf(lz0, lz1)), hit.t) * ZB_BOX_INFLATE;
-            float rn = fmaxf(max3(fminf(rx0, rx1), fminf(ry0, ry1), fminf(rz0, rz1)), tmin);
-            float rf = fminf(min3(fmaxf(rx0, rx1), fmaxf(ry0, ry1), fmaxf(rz0, rz1)), hit.t) * ZB_BOX_INFLATE;
+        float lx0 = fmaf(n0.x, rb.inv.x, -rb.ood.x), lx1 = fmaf(n0.y, rb.inv.x, -rb.ood.x);
+        float ly0 = fmaf(n0.z, rb.inv.y, -rb.ood.y), ly1 = fmaf(n0.w, rb.inv.y, -rb.ood.y);
+        float lz0 = fmaf(n2.x, rb.inv.z, -rb.ood.z), lz1 = fmaf(n2.y, rb.inv.z, -rb.ood.z);
+        float rx0 = fmaf(n1.x, rb.inv.x, -rb.ood.x), rx1 = fmaf(n1.y, rb.inv.x, -rb.ood.x);
+        float ry0 = fmaf(n1.z, rb.inv.y, -rb.ood.y), ry1 = fmaf(n1.w, rb.inv.y, -rb.ood.y);
+        float rz0 = fmaf(n2.z, rb.inv.z, -rb.ood.z), rz1 = fmaf(n2.w, rb.inv.z, -rb.ood.z);
+        float ln = fmaxf(max3(fminf(lx0, lx1), fminf(ly0, ly1), fminf(lz0, lz1)), tmin);
+        float lf = fminf(min3(fmaxf(lx0, lx1), fmaxf(ly0, ly1), fmaxf(lz0, lz1)), hit.t) * ZB_BOX_INFLATE;
+        float rn = fmaxf(max3(fminf(rx0, rx1), fminf(ry0, ry1), fminf(rz0, rz1)), tmin);
+        float rf = fminf(min3(fmaxf(rx0, rx1), fmaxf(ry0, ry1), fmaxf(rz0, rz1)), hit.t) * ZB_BOX_INFLATE;
 #endif
-            const bool hl = ln <= lf, hr = rn <= rf;
-            const int cl = __float_as_int(nc.x), cr = __float_as_int(nc.y);
-            const bool right_first = hr && (!hl || rn < ln);
-            int next = right_first ? cr : cl;
-            if (hl && hr) {
-                stack[sp] = right_first ? cl : cr;
-                sp = min(sp + 1, ZB_STACK - 1);  // deeper than any tree the host builder emits (bvh_build.hpp)
-            }
-            if (!(hl || hr)) next = stack[--sp];
-            cur = next;
+        const bool hl = ln <= lf, hr = rn <= rf;
+        const int cl = __float_as_int(nc.x), cr = __float_as_int(nc.y);
+        const bool right_first = hr && (!hl || rn < ln);
+        int next = right_first ? cr : cl;
+        if (hl && hr) {
+            stack[sp] = right_first ? cl : cr;
+            sp = min(sp + 1, ZB_STACK - 1);  // deeper than any tree the host builder emits (bvh_build.hpp)
         }
-        if (cur == ZB_TRAVERSAL_DONE) break;
+        if (!(hl || hr)) next = stack[--sp];
+        cur = next;
+    }
+
+    // (o, d) is the world-space ray given to begin()
+    template <bool STATS>
+    ZB_DEV void leaf_step(const SceneDev& sc, float3 o, float3 d, float tmin, const MediumRng& rng, int* stack, Counters& cnt) {
         if (cur == ZB_EXIT_INSTANCE) {
             in_blas = false;
             ro = o;
@@ -340,5 +348,23 @@ ZB_DEV bool trace(const SceneDev& sc, float3 o, float3 d, float tmin, float tmax
         }
         cur = stack[--sp];
     }
+};
+
+// Closest hit of one ray, run to completion.  "while-while" traversal (Aila & Laine 2009): every lane first descends
+// through inner nodes until it holds a leaf, then the warp runs the primitive tests together; this keeps more lanes
+// on the same instruction than one loop that alternates between a node step and a leaf step.
+template <bool STATS>
+ZB_DEV bool trace(const SceneDev& sc, float3 o, float3 d, float tmin, float tmax, const MediumRng& rng, Hit& hit,
+                  Counters& cnt) {
+    int stack[ZB_STACK];
+    cnt.rays++;
+    RayWalk w;
+    w.begin(sc, o, d, tmax, stack);
+    while (w.cur != ZB_TRAVERSAL_DONE) {
+        while (w.cur >= 0) w.node_step<STATS>(sc, tmin, stack, cnt);
+        if (w.cur == ZB_TRAVERSAL_DONE) break;
+        w.leaf_step<STATS>(sc, o, d, tmin, rng, stack, cnt);
+    }
+    hit = w.hit;
     return hit.item != 0xFFFFFFFFu;
 }

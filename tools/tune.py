@@ -56,5 +56,7 @@ for i in range(a.reps + 1):
     if i:
         ms.append(e0.elapsed_time(e1))
 res.update(ms=min(ms), ms_all=[round(x, 3) for x in ms], mpaths=n * a.spp / min(ms) * 1e-3,
-           mean=[round(x, 6) for x in (acc[:, :3].mean(0) / a.spp).tolist()])
+           mean=[round(x, 6) for x in (acc[:, :3].mean(0) / a.spp).tolist()],
+           acc_sha=__import__("hashlib").sha1(acc.cpu().numpy().tobytes()).hexdigest()[:12],
+           wavefront=os.environ.get("ZB_WAVEFRONT", "0"), wf_slots=os.environ.get("ZB_WF_SLOTS", ""))
 print(json.dumps(res), flush=True)
