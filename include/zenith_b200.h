@@ -347,6 +347,31 @@ int zb_finish_device(zb_context* ctx, const void* mean_f4, int width, int height
 int zb_finish(zb_context* ctx, const double* rgb_f64, int width, int height, const zb_post* post, int pass_kind,
               double* out_rgb_f64);
 
+/* ---- BVH debug view: bvh_node::hit with global_settings::bvh_debug_mode (bvh.hpp:46-110,
+ * camera.hpp:937-954).  `level` = global_settings::debug_bvh_level (-1: leaves), `thickness` = bvh_thickness
+ * (common.hpp:121-123, GUI range 0.001 .. 0.05).  Shows the product's own tree (see csrc/wireframe.cu for what that
+ * changes); level 0 is tree-independent.  A primary miss shows the regular background.  Writes per-pixel SUMS + sample count into accum_f4 (device, W*H float4),
+ * asynchronous on the context stream; zb_resolve_device / zb_finish_device / zb_save_pass take it from there. ---- */
+int zb_render_bvh_debug_device(zb_context* ctx, const zb_scene* scene, const zb_camera* cam, const zb_environment* env,
+                               const zb_render_opts* opts, int level, float thickness, void* accum_f4);
+
+/* ---- image export: camera::save_render_pass (camera.hpp:299-343), process_framebuffer_to_image
+ * (:701-780), file names "render_<Pass>.png" (main.cpp:1317) ---- */
+enum { ZB_RP_RGB = 0, ZB_RP_DENOISE = 1, ZB_RP_ALBEDO = 2, ZB_RP_NORMALS = 3, ZB_RP_REFLECTIONS = 4, ZB_RP_REFRACTIONS = 5,
+       ZB_RP_Z_DEPTH = 6 }; /* render_pass, common.hpp:110-118 */
+/* "render_RGB.png" ... "render_Z-Depth.png"; NULL for a value outside the enum */
+const char* zb_pass_file_name(int render_pass);
+/* mean_f4 (W*H float4 means, device) -> finishing chain of the pass -> 8-bit RGB PNG at `path`.  RGB / DENOISE: bloom,
+ * sharpening, exposure, process(); every other pass: clamp + gamma (the export treats the light passes as data). Blocking. */
+int zb_save_pass(zb_context* ctx, const void* mean_f4, int width, int height, const zb_post* post, int render_pass,
+                 const char* path);
+/* linear radiance as a flat Radiance RGBE file (readable by stbi_loadf, texture.hpp:23).  Blocking. */
+int zb_save_hdr(zb_context* ctx, const void* mean_f4, int width, int height, const char* path);
+/* host-side encoders behind the two calls above: 8-bit RGB PNG from RGB or RGBA rows (alpha dropped), RGBE from float
+ * rows of `channels` >= 3 floats per pixel; a stride of 0 means tightly packed rows */
+int zb_write_png(const char* path, int width, int height, const unsigned char* pixels, int channels, size_t row_stride);
+int zb_write_hdr(const char* path, int width, int height, const float* pixels, int channels, size_t row_stride_floats);
+
 /* Host side of the boundary (C++20 scene API + flattener behind a C handle): parse a neutral scene
  * description ("zscene" text, raytracer_project_b200/host/zscene.hpp) through the reference-shaped
  * scene API and flatten it.  The returned zb_flat_scene stays valid until zb_flat_scene_free. */

@@ -329,6 +329,11 @@ static int cmd_render(const std::string& scene, const std::string& cfg, const st
     apply_env(c, dir_of(cfg), env);
     shared_ptr<hittable> world = sb.world;
     if (count_rays) world = make_shared<ray_counter>(world);
+    if (c.num("bvh_debug", 0) != 0) {  // BVH debug view (bvh.hpp:56-110, camera.hpp:937-954; GUI: main.cpp:1039-1083)
+        global_settings::bvh_debug_mode = true;
+        global_settings::debug_bvh_level = int(c.num("debug_bvh_level", -1));
+        global_settings::bvh_thickness = float(c.num("bvh_thickness", 0.01));
+    }
     render_result r = run_render(cam, *world, env, c.num("z_depth_max_dist", 20.0));
     if (out != "-") {
         FILE* f = std::fopen(out.c_str(), "wb");
@@ -439,25 +444,7 @@ static int cmd_probe(const std::string& scene, const std::string& cfg, const std
 }
 
 
-// Finishing chain of the reference (SURVEY 8(f) f2): analyze_framebuffer + apply_auto_exposure
-// (color_processing.hpp:153-210, camera.hpp:258-267) and camera::update_post_processing (camera.hpp:142-207) on a raw
-// image (int32 w, h, then w*h*3 doubles).  Output: int32 w, h; final_framebuffer (w*h*3 doubles); average luminance,
-// max luminance, exposure after auto-exposure (3 doubles); histogram (256 int32).
-static int cmd_finish(const std::string& in, const std::string& cfg, const std::string& out) {
-    FILE* f = std::fopen(in.c_str(), "rb");
-    if (!f) return 2;
-    int32_t wh[2];
-    if (std::fread(wh, 4, 2, f) != 2) return 2;
-    const size_t n = size_t(wh[0]) * wh[1];
-    std::vector<color> img(n);
-    for (size_t i = 0; i < n; i++) {
-        double v[3];
-        if (std::fread(v, 8, 3, f) != 3) return 2;
-        img[i] = color(v[0], v[1], v[2]);
-    }
-    std::fclose(f);
-    config c = config::load(cfg);
-    post_processor post;
+static void load_post(const config& c, post_processor& post) {
     post.exposure = float(c.num("exposure", 0.5));
     post.saturation = float(c.num("saturation", 1.0));
     post.contrast = float(c.num("contrast", 1.0));
@@ -479,6 +466,28 @@ static int cmd_finish(const std::string& in, const std::string& cfg, const std::
     post.bloom_radius = int(c.num("bloom_radius", 4));
     post.use_sharpening = c.num("use_sharpening", 0) != 0;
     post.sharpen_amount = c.num("sharpen_amount", 0.2);
+}
+
+// Finishing chain of the reference (SURVEY 8(f) f2): analyze_framebuffer + apply_auto_exposure
+// (color_processing.hpp:153-210, camera.hpp:258-267) and camera::update_post_processing (camera.hpp:142-207) on a raw
+// image (int32 w, h, then w*h*3 doubles).  Output: int32 w, h; final_framebuffer (w*h*3 doubles); average luminance,
+// max luminance, exposure after auto-exposure (3 doubles); histogram (256 int32).
+static int cmd_finish(const std::string& in, const std::string& cfg, const std::string& out) {
+    FILE* f = std::fopen(in.c_str(), "rb");
+    if (!f) return 2;
+    int32_t wh[2];
+    if (std::fread(wh, 4, 2, f) != 2) return 2;
+    const size_t n = size_t(wh[0]) * wh[1];
+    std::vector<color> img(n);
+    for (size_t i = 0; i < n; i++) {
+        double v[3];
+        if (std::fread(v, 8, 3, f) != 3) return 2;
+        img[i] = color(v[0], v[1], v[2]);
+    }
+    std::fclose(f);
+    config c = config::load(cfg);
+    post_processor post;
+    load_post(c, post);
     const int pass = int(c.num("pass", 0));
     image_statistics stats = post.analyze_framebuffer(img);
     if (post.use_auto_exposure) post.exposure = static_cast<float>(post.apply_auto_exposure(stats));  // camera.hpp:259-263
@@ -499,6 +508,49 @@ static int cmd_finish(const std::string& in, const std::string& cfg, const std::
     std::fwrite(stats.histogram, 4, 256, f);
     std::fclose(f);
     std::printf("{\"cmd\": \"finish\", \"width\": %d, \"height\": %d, \"exposure\": %.9g}\n", wh[0], wh[1], double(post.exposure));
+    return 0;
+}
+
+
+// Image export of the reference: camera::save_render_pass (camera.hpp:299-343) ->
+// process_framebuffer_to_image (:701-780) -> stbi_write_png into ./output/.  Every pass buffer is set to the input image;
+// cfg `render_pass` is the reference's enum value (common.hpp:110-118).  The PNG is read back with stbi_load and
+// written as int32 w, h + w*h*3 bytes.
+static int cmd_export(const std::string& in, const std::string& cfg, const std::string& out) {
+    FILE* f = std::fopen(in.c_str(), "rb");
+    if (!f) return 2;
+    int32_t wh[2];
+    if (std::fread(wh, 4, 2, f) != 2) return 2;
+    const size_t n = size_t(wh[0]) * wh[1];
+    std::vector<color> img(n);
+    for (size_t i = 0; i < n; i++) {
+        double v[3];
+        if (std::fread(v, 8, 3, f) != 3) return 2;
+        img[i] = color(v[0], v[1], v[2]);
+    }
+    std::fclose(f);
+    config c = config::load(cfg);
+    post_processor post;
+    load_post(c, post);
+    const int rp = int(c.num("render_pass", 0));
+    camera cam;
+    cam.image_width = wh[0];
+    cam.image_height = wh[1];
+    cam.render_accumulator = cam.denoise_buffer = cam.albedo_buffer = cam.normal_buffer = cam.reflection_buffer =
+        cam.refraction_buffer = cam.z_depth_buffer = img;
+    const std::string name = std::string("render_") + camera::pass_names[rp] + ".png";  // main.cpp:1317
+    cam.save_render_pass(static_cast<render_pass>(rp), name, post);
+    int w = 0, h = 0, comp = 0;
+    unsigned char* d = stbi_load(("output/" + name).c_str(), &w, &h, &comp, 3);
+    if (!d) return 3;
+    f = std::fopen(out.c_str(), "wb");
+    if (!f) return 2;
+    int32_t wh2[2] = {w, h};
+    std::fwrite(wh2, 4, 2, f);
+    std::fwrite(d, 1, size_t(w) * h * 3, f);
+    std::fclose(f);
+    stbi_image_free(d);
+    std::printf("{\"cmd\": \"export\", \"file\": \"output/%s\", \"width\": %d, \"height\": %d, \"channels\": %d}\n", name.c_str(), w, h, comp);
     return 0;
 }
 
@@ -540,6 +592,7 @@ int main(int argc, char** argv) {
     if (a.size() >= 5 && a[0] == "stats") return cmd_stats(a[1], a[2], a[3], std::atoi(a[4].c_str()));
     if (a.size() >= 5 && a[0] == "probe") return cmd_probe(a[1], a[2], a[3], a[4]);
     if (a.size() >= 4 && a[0] == "finish") return cmd_finish(a[1], a[2], a[3]);
+    if (a.size() >= 4 && a[0] == "export") return cmd_export(a[1], a[2], a[3]);
     if (a.size() >= 4 && a[0] == "decode") return cmd_decode(a[1], a[2], a[3] == "1");
     if (a.size() >= 2 && a[0] == "kat") return cmd_kat(a[1]);
     std::fprintf(stderr,

@@ -16,6 +16,7 @@
 //   zoracle probe  SCENE CFG RAYS OUT     per-ray hit_record / albedo / emitted / background
 //   zoracle render SCENE CFG OUT|- [SEED] render_rows (camera.hpp:430-554), OpenMP over rows
 //   zoracle finish IMAGE CFG OUT          finishing chain (camera.hpp:142-207, color_processing.hpp, bloom.hpp)
+//   zoracle export IMAGE CFG OUT          image export up to the 8-bit rows (camera.hpp:299-343, :701-780)
 // File formats are those of oracle/ref_harness.cpp, so the same test code reads both.
 #include <algorithm>
 #include <chrono>
@@ -986,21 +987,24 @@ void blur_pass(const std::vector<color>& in, std::vector<color>& out, int W, int
         }
 }
 
-int cmd_finish(const std::string& in, const std::string& cfg, const std::string& out) {
+bool load_image(const std::string& in, int& W, int& H, std::vector<color>& img) {
     FILE* f = std::fopen(in.c_str(), "rb");
-    if (!f) return 2;
+    if (!f) return false;
     int32_t wh[2];
-    if (std::fread(wh, 4, 2, f) != 2) return 2;
-    const int W = wh[0], H = wh[1];
-    const size_t n = size_t(W) * H;
-    std::vector<color> img(n);
-    for (size_t i = 0; i < n; i++) {
+    if (std::fread(wh, 4, 2, f) != 2) return false;
+    W = wh[0];
+    H = wh[1];
+    img.resize(size_t(W) * H);
+    for (color& p : img) {
         double v[3];
-        if (std::fread(v, 8, 3, f) != 3) return 2;
-        img[i] = color(v[0], v[1], v[2]);
+        if (std::fread(v, 8, 3, f) != 3) return false;
+        p = color(v[0], v[1], v[2]);
     }
     std::fclose(f);
-    config c = config::load(cfg);
+    return true;
+}
+
+post_t load_post(const config& c) {
     post_t P;
     P.exposure = float(c.num("exposure", 0.5));
     P.saturation = float(c.num("saturation", 1.0));
@@ -1020,6 +1024,43 @@ int cmd_finish(const std::string& in, const std::string& cfg, const std::string&
     P.bloom_radius = int(c.num("bloom_radius", 4));
     P.sharpen = c.num("use_sharpening", 0) != 0;
     P.sharpen_amount = c.num("sharpen_amount", 0.2);
+    return P;
+}
+
+// bloom_filter::generate_bloom_overlay (bloom.hpp:18-46) with its exposure argument 1.0f
+std::vector<color> bloom_overlay(const std::vector<color>& src, int W, int H, const post_t& P) {
+    const size_t n = src.size();
+    std::vector<color> bright(n, color(0, 0, 0)), tmp(n), overlay(n);
+    for (size_t i = 0; i < n; i++) {  // bright pass, bloom.hpp:27-38
+        color e = src[i] * 1.0;
+        float lum = float(lum709(e));
+        if (lum > P.bloom_threshold) bright[i] = e * double((lum - P.bloom_threshold) * P.bloom_intensity / std::max(lum, 0.0001f));
+    }
+    blur_pass(bright, tmp, W, H, P.bloom_radius, true);
+    blur_pass(tmp, overlay, W, H, P.bloom_radius, false);
+    return overlay;
+}
+
+void sharpen(std::vector<color>& fin, int W, int H, double amount) {  // color_processing.hpp:212-232
+    if (amount <= 0.0) return;
+    std::vector<color> orig = fin;
+    for (int y = 1; y < H - 1; y++)
+        for (int x = 1; x < W - 1; x++) {
+            size_t i = size_t(y) * W + x;
+            color sum = orig[i] * 5.0 - orig[i - W] - orig[i + W] - orig[i - 1] - orig[i + 1];
+            fin[i] = (orig[i] * (1.0 - amount)) + (sum * amount);
+        }
+}
+
+int cmd_finish(const std::string& in, const std::string& cfg, const std::string& out) {
+    int W = 0, H = 0;
+    std::vector<color> img;
+    if (!load_image(in, W, H, img)) return 2;
+    const int32_t wh[2] = {W, H};
+    const size_t n = img.size();
+    FILE* f = nullptr;
+    config c = config::load(cfg);
+    post_t P = load_post(c);
     const int pass = int(c.num("pass", 0));
     // analyze_framebuffer (color_processing.hpp:153-186)
     int32_t hist[256] = {0};
@@ -1044,25 +1085,10 @@ int cmd_finish(const std::string& in, const std::string& cfg, const std::string&
     if (pass == 0) {
         for (color& p : fin) p *= ev;
         if (P.bloom) {
-            std::vector<color> bright(n, color(0, 0, 0)), tmp(n), overlay(n);
-            for (size_t i = 0; i < n; i++) {  // bright pass, bloom.hpp:27-38 (exposure argument 1.0f)
-                color e = fin[i] * 1.0;
-                float lum = float(lum709(e));
-                if (lum > P.bloom_threshold) bright[i] = e * double((lum - P.bloom_threshold) * P.bloom_intensity / std::max(lum, 0.0001f));
-            }
-            blur_pass(bright, tmp, W, H, P.bloom_radius, true);
-            blur_pass(tmp, overlay, W, H, P.bloom_radius, false);
+            std::vector<color> overlay = bloom_overlay(fin, W, H, P);
             for (size_t i = 0; i < n; i++) fin[i] += overlay[i];
         }
-        if (P.sharpen && P.sharpen_amount > 0.0) {  // color_processing.hpp:212-232
-            std::vector<color> orig = fin;
-            for (int y = 1; y < H - 1; y++)
-                for (int x = 1; x < W - 1; x++) {
-                    size_t i = size_t(y) * W + x;
-                    color sum = orig[i] * 5.0 - orig[i - W] - orig[i + W] - orig[i - 1] - orig[i + 1];
-                    fin[i] = (orig[i] * (1.0 - P.sharpen_amount)) + (sum * P.sharpen_amount);
-                }
-        }
+        if (P.sharpen) sharpen(fin, W, H, P.sharpen_amount);
     }
     for (size_t i = 0; i < n; i++) {
         float u = float(i % W) / (W - 1), v = float(i / W) / (H - 1);
@@ -1085,6 +1111,50 @@ int cmd_finish(const std::string& in, const std::string& cfg, const std::string&
     return 0;
 }
 
+// Image export: camera::save_render_pass (camera.hpp:299-343) -> process_framebuffer_to_image (:701-780), up to the
+// 8-bit RGB rows handed to the PNG encoder.  cfg `render_pass` is the reference's enum (common.hpp:110-118): RGB and
+// DENOISE take bloom (found on the exposed image, added back unexposed), sharpening, exposure and process(); every
+// other pass (the light passes too) is clamp + gamma.  Output: int32 w, h; w*h*3 bytes.
+int cmd_export(const std::string& in, const std::string& cfg, const std::string& out) {
+    int W = 0, H = 0;
+    std::vector<color> img;
+    if (!load_image(in, W, H, img)) return 2;
+    const size_t n = img.size();
+    config c = config::load(cfg);
+    const post_t P = load_post(c);
+    const int rp = int(c.num("render_pass", 0));
+    const bool is_data = rp != 0 && rp != 1;
+    const double ev = std::pow(2.0, double(P.exposure));
+    std::vector<color> buf = img;
+    if (!is_data && P.bloom) {
+        std::vector<color> exposed = img;
+        for (color& p : exposed) p *= ev;
+        std::vector<color> overlay = bloom_overlay(exposed, W, H, P);
+        const double inv_ev = 1.0 / ev;
+        for (size_t i = 0; i < n; i++) buf[i] = img[i] + overlay[i] * inv_ev;
+    }
+    if (!is_data && P.sharpen) sharpen(buf, W, H, P.sharpen_amount);
+    std::vector<unsigned char> rgb(n * 3);
+    for (size_t i = 0; i < n; i++) {
+        color px = buf[i];
+        if (!is_data) {
+            float u = float(i % W) / (W - 1), v = float(i / W) / (H - 1);
+            px = post_process(px * ev, u, v, P);
+        } else {
+            px = clamp_gamma(px);
+        }
+        for (int k = 0; k < 3; k++) rgb[3 * i + k] = static_cast<unsigned char>(255.999 * px[k]);
+    }
+    FILE* f = std::fopen(out.c_str(), "wb");
+    if (!f) return 2;
+    const int32_t wh[2] = {W, H};
+    std::fwrite(wh, 4, 2, f);
+    std::fwrite(rgb.data(), 1, rgb.size(), f);
+    std::fclose(f);
+    std::printf("{\"cmd\": \"export\", \"width\": %d, \"height\": %d, \"render_pass\": %d}\n", W, H, rp);
+    return 0;
+}
+
 }  // namespace
 
 int main(int argc, char** argv) {
@@ -1093,6 +1163,7 @@ int main(int argc, char** argv) {
     if (a.size() >= 4 && a[0] == "ids") return cmd_ids(a[1], a[2], a[3]);
     if (a.size() >= 5 && a[0] == "probe") return cmd_probe(a[1], a[2], a[3], a[4]);
     if (a.size() >= 4 && a[0] == "finish") return cmd_finish(a[1], a[2], a[3]);
+    if (a.size() >= 4 && a[0] == "export") return cmd_export(a[1], a[2], a[3]);
     if (a.size() >= 4 && a[0] == "render") return cmd_render(a[1], a[2], a[3], a.size() > 4 ? std::strtoull(a[4].c_str(), nullptr, 10) : 1ull);
     std::fprintf(stderr, "usage: zoracle ids SCENE CFG OUT | probe SCENE CFG RAYS OUT | render SCENE CFG OUT|- [SEED]\n");
     return 1;

@@ -131,6 +131,13 @@ SYMBOLS = {
     "zb_auto_exposure": (C.c_double, [C.POINTER(Post), C.POINTER(ImageStats)]),
     "zb_finish_device": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.POINTER(Post), C.c_int, C.c_void_p, C.c_void_p]),
     "zb_finish": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.POINTER(Post), C.c_int, C.c_void_p]),
+    "zb_render_bvh_debug_device": (C.c_int, [C.c_void_p, C.c_void_p, C.POINTER(Camera), C.POINTER(Environment), C.POINTER(RenderOpts), C.c_int,
+                                   C.c_float, C.c_void_p]),
+    "zb_pass_file_name": (C.c_char_p, [C.c_int]),
+    "zb_save_pass": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.POINTER(Post), C.c_int, C.c_char_p]),
+    "zb_save_hdr": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_char_p]),
+    "zb_write_png": (C.c_int, [C.c_char_p, C.c_int, C.c_int, C.c_void_p, C.c_int, C.c_size_t]),
+    "zb_write_hdr": (C.c_int, [C.c_char_p, C.c_int, C.c_int, C.c_void_p, C.c_int, C.c_size_t]),
     "zb_flat_scene_from_zscene": (C.c_int, [C.c_char_p, C.POINTER(C.POINTER(FlatScene))]),
     "zb_flat_scene_from_zscene_text": (C.c_int, [C.c_char_p, C.c_size_t, C.POINTER(C.POINTER(FlatScene))]),
     "zb_flat_scene_from_zscene_ex": (C.c_int, [C.c_char_p, C.c_char_p, C.c_size_t, C.c_uint32, C.POINTER(C.POINTER(FlatScene))]),

@@ -107,6 +107,88 @@ def post_struct(**kw) -> "_lib.Post":
     return p
 
 
+RENDER_PASS = {"RGB": 0, "Denoise": 1, "Albedo": 2, "Normals": 3, "Reflections": 4, "Refractions": 5, "Z-Depth": 6}
+
+
+def pass_file_name(render_pass: int) -> str:
+    """"render_<Pass>.png" as the reference's export names its files (main.cpp:1317)."""
+    name = _lib.load().zb_pass_file_name(render_pass)
+    if name is None:
+        raise ValueError(f"render_pass {render_pass} outside the reference's enum")
+    return name.decode()
+
+
+def write_png(path: str, rgb) -> None:
+    """(H, W, 3 | 4) uint8 -> 8-bit RGB PNG (alpha dropped)."""
+    a = np.ascontiguousarray(rgb, np.uint8)
+    check(_lib.load().zb_write_png(path.encode(), a.shape[1], a.shape[0], a.ctypes.data, a.shape[2], 0))
+
+
+def write_hdr(path: str, rgb) -> None:
+    """(H, W, >= 3) float32 linear radiance -> flat Radiance RGBE file."""
+    a = np.ascontiguousarray(rgb, np.float32)
+    check(_lib.load().zb_write_hdr(path.encode(), a.shape[1], a.shape[0], a.ctypes.data, a.shape[2], 0))
+
+
+def read_png(path: str):
+    """Decoder for the tests: 8-bit RGB / RGBA, non-interlaced PNG -> (H, W, C) uint8 (all five row filters)."""
+    import struct
+    import zlib
+    data = open(path, "rb").read()
+    assert data[:8] == b"\x89PNG\r\n\x1a\n", "not a PNG"
+    at, idat, w = 8, b"", 0
+    while at < len(data):
+        n, kind = struct.unpack(">I4s", data[at:at + 8])
+        body = data[at + 8:at + 8 + n]
+        assert zlib.crc32(kind + body) == struct.unpack(">I", data[at + 8 + n:at + 12 + n])[0], "PNG chunk CRC"
+        if kind == b"IHDR":
+            w, h, depth, ctype, _, _, interlace = struct.unpack(">IIBBBBB", body)
+            assert depth == 8 and ctype in (2, 6) and interlace == 0
+            ch = 3 if ctype == 2 else 4
+        elif kind == b"IDAT":
+            idat += body
+        at += 12 + n
+    raw = np.frombuffer(zlib.decompress(idat), np.uint8).reshape(h, w * ch + 1)
+    out = np.zeros((h, w * ch), np.uint8)
+    for y in range(h):
+        f, line = int(raw[y, 0]), raw[y, 1:].astype(np.int32)
+        up = out[y - 1].astype(np.int32) if y else np.zeros(w * ch, np.int32)
+        if f == 0:
+            cur = line
+        elif f == 2:
+            cur = line + up
+        else:
+            cur = np.zeros(w * ch, np.int32)
+            for i in range(w * ch):
+                a = cur[i - ch] if i >= ch else 0
+                b = up[i]
+                c = up[i - ch] if i >= ch else 0
+                if f == 1:
+                    pred = a
+                elif f == 3:
+                    pred = (a + b) // 2
+                else:
+                    p = a + b - c
+                    pa, pb, pc = abs(p - a), abs(p - b), abs(p - c)
+                    pred = a if pa <= pb and pa <= pc else (b if pb <= pc else c)
+                cur[i] = (line[i] + pred) & 255
+        out[y] = (cur & 255).astype(np.uint8)
+    return out.reshape(h, w, ch)
+
+
+def read_hdr(path: str):
+    """Decoder for the tests: flat Radiance RGBE -> (H, W, 3) float32, with stb_image's conversion (ldexp(1, e - 136))."""
+    data = open(path, "rb").read()
+    head, _, rest = data.partition(b"\n\n")
+    assert head.startswith(b"#?RADIANCE")
+    dims, _, pix = rest.partition(b"\n")
+    tok = dims.split()
+    h, w = int(tok[1]), int(tok[3])
+    q = np.frombuffer(pix[:w * h * 4], np.uint8).reshape(h, w, 4).astype(np.float32)
+    scale = np.where(q[..., 3:] > 0, np.exp2(q[..., 3:] - 136.0), 0.0)
+    return (q[..., :3] * scale).astype(np.float32)
+
+
 def post_text(pass_kind=0, **kw) -> str:
     """The same parameters as the key-value text the oracle binaries read (`finish` command)."""
     v = {**POST_DEFAULTS, **kw}
@@ -162,6 +244,13 @@ class Context:
         out = np.empty_like(img)
         check(self.lib.zb_finish(self.h, img.ctypes.data, img.shape[1], img.shape[0], C.byref(post), pass_kind, out.ctypes.data))
         return out
+
+    def save_pass(self, path: str, mean_ptr: int, width: int, height: int, post, render_pass=0):
+        """zb_save_pass: camera::save_render_pass for device-resident means -> 8-bit RGB PNG."""
+        check(self.lib.zb_save_pass(self.h, C.c_void_p(mean_ptr), width, height, C.byref(post), render_pass, path.encode()))
+
+    def save_hdr(self, path: str, mean_ptr: int, width: int, height: int):
+        check(self.lib.zb_save_hdr(self.h, C.c_void_p(mean_ptr), width, height, path.encode()))
 
     def checkpoint_save(self, path: str, accum_ptr: int, width: int, height: int, samples_done: int, seed: int):
         check(self.lib.zb_checkpoint_save(self.h, path.encode(), C.c_void_p(accum_ptr), width, height, samples_done, seed))
@@ -225,6 +314,13 @@ class Scene:
         o.accumulate = int(accumulate)
         check(self.ctx.lib.zb_render_device(self.ctx.h, self.h, C.byref(cam), C.byref(env), C.byref(o),
                                             C.c_void_p(accum_ptr), C.c_void_p(aux_ptr) if aux_ptr else None))
+
+    def render_bvh_debug_device(self, cfg: RenderConfig, accum_ptr: int, level=-1, thickness=0.01, seed=1, sample_range=None):
+        """zb_render_bvh_debug_device: the reference's BVH debug view (bvh.hpp:56-110), sums into a device float4 buffer."""
+        cam, env = camera_struct(cfg), env_struct(cfg)
+        o = opts_struct(cfg, seed, sample_range, None, False, 0)
+        check(self.ctx.lib.zb_render_bvh_debug_device(self.ctx.h, self.h, C.byref(cam), C.byref(env), C.byref(o), int(level),
+                                                      float(thickness), C.c_void_p(accum_ptr)))
 
     PROBE_DTYPE = np.dtype([("t", "f4"), ("leaf_id", "u4"), ("prim_id", "u4"), ("front_face", "u4"), ("p", "f4", 3),
                             ("normal", "f4", 3), ("u", "f4"), ("v", "f4"), ("albedo", "f4", 3), ("emitted", "f4", 3)])

@@ -309,6 +309,26 @@ extern "C" int zb_render_device(zb_context* ctx, const zb_scene* scene, const zb
     return launch_share(ctx, P, opts, nullptr, nullptr, nullptr, true);
 }
 
+// BVH debug view (bvh.hpp:56-110 + camera.hpp:937-954): sums of opts->samples_per_pixel (or the
+// sample_begin..sample_end slice) debug-coloured primary rays per pixel into accum_f4, like zb_render_device.
+extern "C" int zb_render_bvh_debug_device(zb_context* ctx, const zb_scene* scene, const zb_camera* cam,
+                                          const zb_environment* env, const zb_render_opts* opts, int level,
+                                          float thickness, void* accum_f4) {
+    RenderParams P;
+    int rc = fill_params(ctx, scene, cam, env, opts, P);
+    if (rc) return rc;
+    if (!accum_f4) return fail(ZB_ERR_INVALID, "zb_render_bvh_debug_device: accum_f4 is NULL");
+    if (level < -1 || level > 0xFFFF || !(thickness > 0.f)) return fail(ZB_ERR_INVALID, "zb_render_bvh_debug_device: bad level / thickness");
+    ZB_CUDA(cudaSetDevice(ctx->device));
+    P.accum = static_cast<float4*>(accum_f4);
+    P.accum_aux = nullptr;
+    P.accumulate = opts->accumulate ? 1 : 0;
+    ZB_CUDA(zbk_launch_wireframe(P, level, thickness, ctx->stream));
+    ctx->stats = zb_stats{};
+    ctx->stats.launches = 1;
+    return ZB_OK;
+}
+
 extern "C" int zb_resolve_device(zb_context* ctx, const void* accum_f4, size_t n_pixels, double scale, void* out_f4,
                                  void* out_rgb_f64) {
     if (!ctx || !accum_f4) return fail(ZB_ERR_INVALID, "zb_resolve_device: NULL argument");

@@ -413,3 +413,38 @@ extern "C" int zb_finish(zb_context* ctx, const double* rgb_f64, int width, int 
     }
     return ZB_OK;
 }
+
+// camera::save_render_pass (camera.hpp:299-343) -> process_framebuffer_to_image (:701-780): RGB / DENOISE take the
+// beauty chain (the export's order of bloom, sharpening and exposure equals update_post_processing's in exact
+// arithmetic), every other pass — the light passes too, unlike the preview — is clamp + gamma; 255.999 * v to 8 bits.
+extern "C" int zb_save_pass(zb_context* ctx, const void* mean_f4, int width, int height, const zb_post* post, int render_pass,
+                            const char* path) {
+    if (!ctx || !mean_f4 || !post || !path) return fail(ZB_ERR_INVALID, "zb_save_pass: NULL argument");
+    if (width < 1 || height < 1 || render_pass < ZB_RP_RGB || render_pass > ZB_RP_Z_DEPTH) return fail(ZB_ERR_INVALID, "zb_save_pass: bad size / pass");
+    ZB_CUDA(cudaSetDevice(ctx->device));
+    const size_t pixels = size_t(width) * height;
+    uchar4* dev = nullptr;
+    ZB_CUDA(cudaMalloc(&dev, pixels * sizeof(uchar4)));
+    const int kind = (render_pass == ZB_RP_RGB || render_pass == ZB_RP_DENOISE) ? ZB_PASS_BEAUTY : ZB_PASS_AUX;
+    int rc = zb_finish_device(ctx, mean_f4, width, height, post, kind, nullptr, dev);
+    std::vector<uchar4> host(pixels);
+    if (!rc) {
+        cudaError_t e = cudaMemcpyAsync(host.data(), dev, pixels * sizeof(uchar4), cudaMemcpyDeviceToHost, ctx->stream);
+        if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
+        if (e != cudaSuccess) rc = fail(ZB_ERR_CUDA, std::string("zb_save_pass: ") + cudaGetErrorString(e));
+    }
+    cudaFree(dev);
+    if (rc) return rc;
+    return zb_write_png(path, width, height, reinterpret_cast<const unsigned char*>(host.data()), 4, 0);
+}
+
+// Linear radiance (float4 means on the device) as a Radiance .hdr file: what stbi_loadf reads back as an environment.
+extern "C" int zb_save_hdr(zb_context* ctx, const void* mean_f4, int width, int height, const char* path) {
+    if (!ctx || !mean_f4 || !path || width < 1 || height < 1) return fail(ZB_ERR_INVALID, "zb_save_hdr: bad argument");
+    ZB_CUDA(cudaSetDevice(ctx->device));
+    const size_t pixels = size_t(width) * height;
+    std::vector<float4> host(pixels);
+    ZB_CUDA(cudaMemcpyAsync(host.data(), mean_f4, pixels * sizeof(float4), cudaMemcpyDeviceToHost, ctx->stream));
+    ZB_CUDA(cudaStreamSynchronize(ctx->stream));
+    return zb_write_hdr(path, width, height, reinterpret_cast<const float*>(host.data()), 4, 0);
+}

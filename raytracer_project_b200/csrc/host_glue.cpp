@@ -158,3 +158,107 @@ extern "C" int zb_flat_scene_free(const zb_flat_scene* flat) {
     g_live.erase(flat);
     return ZB_OK;
 }
+
+// ------------------------------------------------------------------ image files
+// The reference writes its passes with stbi_write_png (camera.hpp:779) and reads HDR environments with stbi_loadf
+// (texture.hpp:23).  These writers are written from the PNG (RFC 2083) and Radiance RGBE format definitions: 8-bit
+// RGB PNG, filter Sub on every row, one zlib stream; flat (not run-length encoded) RGBE.
+#include <zlib.h>
+
+#include <cmath>
+#include <cstdio>
+#include <cstring>
+
+namespace {
+void put_be32(std::vector<unsigned char>& v, uint32_t x) {
+    v.push_back(uint8_t(x >> 24));
+    v.push_back(uint8_t(x >> 16));
+    v.push_back(uint8_t(x >> 8));
+    v.push_back(uint8_t(x));
+}
+void png_chunk(std::vector<unsigned char>& out, const char* type, const unsigned char* data, size_t n) {
+    put_be32(out, uint32_t(n));
+    const size_t at = out.size();
+    out.insert(out.end(), type, type + 4);
+    if (n) out.insert(out.end(), data, data + n);
+    put_be32(out, uint32_t(crc32(0L, out.data() + at, uInt(n + 4))));
+}
+}  // namespace
+
+extern "C" int zb_write_png(const char* path, int width, int height, const unsigned char* pixels, int channels, size_t row_stride) {
+    if (!path || !pixels || width < 1 || height < 1 || (channels != 3 && channels != 4))
+        return fail_host(ZB_ERR_INVALID, "zb_write_png: bad argument");
+    if (!row_stride) row_stride = size_t(width) * channels;
+    const size_t line = size_t(width) * 3 + 1;
+    std::vector<unsigned char> raw(line * height);
+    for (int y = 0; y < height; y++) {
+        const unsigned char* src = pixels + size_t(y) * row_stride;
+        unsigned char* dst = raw.data() + size_t(y) * line;
+        dst[0] = 1;  // filter Sub: byte - byte of the pixel to the left
+        unsigned char prev[3] = {0, 0, 0};
+        for (int x = 0; x < width; x++)
+            for (int k = 0; k < 3; k++) {
+                const unsigned char v = src[size_t(x) * channels + k];
+                dst[1 + size_t(x) * 3 + k] = uint8_t(v - prev[k]);
+                prev[k] = v;
+            }
+    }
+    uLongf zlen = compressBound(uLong(raw.size()));
+    std::vector<unsigned char> z(zlen);
+    if (compress2(z.data(), &zlen, raw.data(), uLong(raw.size()), 4) != Z_OK) return fail_host(ZB_ERR_INVALID, "zb_write_png: deflate failed");
+    std::vector<unsigned char> out = {0x89, 'P', 'N', 'G', '\r', '\n', 0x1A, '\n'};
+    std::vector<unsigned char> ihdr;
+    put_be32(ihdr, uint32_t(width));
+    put_be32(ihdr, uint32_t(height));
+    const unsigned char tail[5] = {8, 2, 0, 0, 0};  // 8 bits, colour type 2 (RGB), deflate, adaptive filtering, no interlace
+    ihdr.insert(ihdr.end(), tail, tail + 5);
+    png_chunk(out, "IHDR", ihdr.data(), ihdr.size());
+    png_chunk(out, "IDAT", z.data(), zlen);
+    png_chunk(out, "IEND", nullptr, 0);
+    FILE* f = std::fopen(path, "wb");
+    if (!f) return fail_host(ZB_ERR_IO, std::string("zb_write_png: cannot open ") + path);
+    const bool ok = std::fwrite(out.data(), 1, out.size(), f) == out.size();
+    std::fclose(f);
+    return ok ? ZB_OK : fail_host(ZB_ERR_IO, std::string("zb_write_png: short write to ") + path);
+}
+
+extern "C" int zb_write_hdr(const char* path, int width, int height, const float* pixels, int channels, size_t row_stride_floats) {
+    if (!path || !pixels || width < 1 || height < 1 || channels < 3) return fail_host(ZB_ERR_INVALID, "zb_write_hdr: bad argument");
+    if (!row_stride_floats) row_stride_floats = size_t(width) * channels;
+    FILE* f = std::fopen(path, "wb");
+    if (!f) return fail_host(ZB_ERR_IO, std::string("zb_write_hdr: cannot open ") + path);
+    std::fprintf(f, "#?RADIANCE\nFORMAT=32-bit_rle_rgbe\n\n-Y %d +X %d\n", height, width);
+    std::vector<unsigned char> row(size_t(width) * 4);
+    bool ok = true;
+    for (int y = 0; y < height && ok; y++) {
+        const float* src = pixels + size_t(y) * row_stride_floats;
+        for (int x = 0; x < width; x++) {
+            float r = src[size_t(x) * channels], g = src[size_t(x) * channels + 1], b = src[size_t(x) * channels + 2];
+            r = std::isfinite(r) && r > 0.f ? r : 0.f;
+            g = std::isfinite(g) && g > 0.f ? g : 0.f;
+            b = std::isfinite(b) && b > 0.f ? b : 0.f;
+            const float m = std::max(r, std::max(g, b));
+            unsigned char* q = row.data() + size_t(x) * 4;
+            if (m < 1e-32f) {
+                q[0] = q[1] = q[2] = q[3] = 0;
+            } else {
+                int e = 0;
+                const float scale = std::frexp(m, &e) * 256.0f / m;  // shared exponent of the largest channel
+                q[0] = uint8_t(r * scale);
+                q[1] = uint8_t(g * scale);
+                q[2] = uint8_t(b * scale);
+                q[3] = uint8_t(e + 128);
+            }
+        }
+        ok = std::fwrite(row.data(), 1, row.size(), f) == row.size();
+    }
+    std::fclose(f);
+    return ok ? ZB_OK : fail_host(ZB_ERR_IO, std::string("zb_write_hdr: short write to ") + path);
+}
+
+// camera::pass_names (camera.hpp:66-74) and the export file name of main.cpp:1317
+extern "C" const char* zb_pass_file_name(int render_pass) {
+    static const char* names[] = {"render_RGB.png", "render_Denoise.png", "render_Albedo.png", "render_Normals.png",
+                                  "render_Reflections.png", "render_Refractions.png", "render_Z-Depth.png"};
+    return render_pass >= 0 && render_pass < 7 ? names[render_pass] : nullptr;
+}

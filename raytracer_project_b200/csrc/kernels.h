@@ -23,3 +23,6 @@ bool zbk_wavefront_supported(const RenderParams& P);
 cudaError_t zbk_launch_wavefront(const RenderParams& P, zb_wf_scratch** scratch, size_t want_slots, int* iterations,
                                  cudaStream_t stream);
 void zbk_wavefront_free(zb_wf_scratch* w);
+
+// BVH debug view (wireframe.cu): frames of the tree level `level` (-1 = leaves), sums into P.accum
+cudaError_t zbk_launch_wireframe(const RenderParams& P, int level, float thickness, cudaStream_t stream);

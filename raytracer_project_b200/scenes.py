@@ -529,3 +529,25 @@ def quirks(seed: int = 5, width: int = 640, height: int = 360, spp: int = 64, ma
         env_mode=env, background=(0.6, 0.7, 0.9), env_intensity=1.0, sun_direction=(0.6, 0.45, 0.5),
         sun_color=(1.0, 0.95, 0.85), sun_intensity=1.0, sun_size=1.0)
     return w.text(), cfg, {}
+
+
+def wire_demo(seed: int = 7, width: int = 240, height: int = 135, spp: int = 64, max_depth: int = 50):
+    """Scene of the BVH debug-view tests: 24 seeded spheres, two cubes and a lamp inside a region
+    the camera sees whole, so the root box of the tree (level 0 — the one level that does not depend on how the
+    tree was built) is in frame; one bvh root."""
+    rng = random.Random(seed)
+    w = SceneWriter()
+    mats = [w.lambertian((0.7, 0.3, 0.2)), w.metal((0.8, 0.8, 0.9), 0.1), w.dielectric(1.5), w.lambertian((0.2, 0.5, 0.7))]
+    objs = []
+    for i in range(24):
+        c = (rng.uniform(-2.0, 2.0), rng.uniform(0.2, 1.4), rng.uniform(-2.0, 2.0))
+        objs.append(w.sphere(c, rng.uniform(0.12, 0.3), mats[i % 4]))
+    objs.append(w.translate(w.cube((-0.3, -0.3, -0.3), (0.3, 0.3, 0.3), mats[0]), (0.8, 0.3, 0.4)))
+    objs.append(w.translate(w.rotate("y", w.cube((-0.2, -0.4, -0.2), (0.2, 0.4, 0.2), mats[1]), 0.5), (-1.1, 0.4, -0.6)))
+    objs.append(w.sphere((0.0, 1.9, 0.0), 0.25, w.light((6.0, 5.0, 4.0))))
+    w.world(w.container("bvh", objs, name="world"))
+    cfg = RenderConfig(
+        image_width=width, image_height=height, samples_per_pixel=spp, max_depth=max_depth, vfov=36.0,
+        lookfrom=(6.0, 4.5, 7.5), lookat=(0.0, 0.8, 0.0), vup=(0.0, 1.0, 0.0), defocus_angle=0.0, focus_dist=10.0,
+        env_mode="solid", background=(0.7, 0.8, 1.0), env_intensity=1.0)
+    return w.text(), cfg, {}

@@ -31,3 +31,17 @@ CASES = {
     "light_pass": (1, dict(exposure=1.0, contrast=0.9)),
     "aux_pass": (2, {}),
 }
+
+
+# Image export: (reference render_pass enum value, post parameters) run through
+# camera::save_render_pass -> PNG -> 8-bit RGB (tests/golden/make_golden.py export).
+RENDER_PASS = {"RGB": 0, "Denoise": 1, "Albedo": 2, "Normals": 3, "Reflections": 4, "Refractions": 5, "Z-Depth": 6}
+EXPORT_CASES = {
+    "rgb_default": (0, {}),
+    "rgb_bloom_sharpen_aces": (0, dict(use_bloom=1, bloom_threshold=0.8, bloom_intensity=0.4, bloom_radius=5, use_sharpening=1,
+                                       sharpen_amount=0.25, use_aces=1, contrast=1.2, color_balance=(1.1, 1.0, 0.9), exposure=0.8)),
+    "rgb_hsv": (0, dict(saturation=1.4, hue_shift=35.0, vignette_intensity=0.0, exposure=0.3)),
+    "albedo": (2, dict(exposure=1.0, use_bloom=1)),
+    "reflections": (4, dict(exposure=1.0, contrast=0.9)),
+    "z_depth": (6, {}),
+}

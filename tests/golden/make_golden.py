@@ -169,6 +169,46 @@ def finish():
     np.savez_compressed(os.path.join(GOLDEN, "finish_96x60.npz"), **out)
 
 
+def read_rgb8(path):
+    with open(path, "rb") as f:
+        w, h = np.frombuffer(f.read(8), np.int32)
+        return np.frombuffer(f.read(int(w) * int(h) * 3), np.uint8).reshape(h, w, 3)
+
+
+def export():
+    """Image export of the reference (camera.hpp:299-343, :701-780): the PNG bytes of each pass kind."""
+    from raytracer_project_b200 import api
+    from tests.golden.finish_cases import EXPORT_CASES, hdr_image
+    d = scratch_dir()
+    write_image(os.path.join(d, "in.bin"), hdr_image())
+    out = {}
+    for name, (rp, kw) in EXPORT_CASES.items():
+        with open(os.path.join(d, "post.cfg"), "w") as f:
+            f.write(api.post_text(0, **kw) + f"render_pass {rp}\n")
+        info = run_harness(["export", "in.bin", "post.cfg", "out.bin"], d)
+        out[name] = read_rgb8(os.path.join(d, "out.bin")).copy()
+        out[name + "_file"] = np.array(os.path.basename(info["file"]))
+        print("export", name, info)
+    np.savez_compressed(os.path.join(GOLDEN, "export_96x60.npz"), **out)
+
+
+def wire():
+    """BVH debug view of the reference (bvh.hpp:56-110) at level 0 — the root box, which does not depend on the
+    reference's random tree — and, for the record only, at the leaf level of ONE reference tree."""
+    txt, cfg, files = scenes.wire_demo(spp=256)
+    d = scratch_dir()
+    scenes.materialize(d, txt, cfg, files)
+    out = {"digest": np.array(scene_digest(txt, cfg, files)), "spp": cfg.samples_per_pixel}
+    for name, level, thick in (("level0", 0, 0.05), ("level0_thin", 0, 0.01), ("leaves", -1, 0.05)):
+        with open(os.path.join(d, "wire.cfg"), "w") as f:
+            f.write(cfg.to_text() + f"bvh_debug 1\ndebug_bvh_level {level}\nbvh_thickness {thick}\n")
+        info = run_harness(["render", "s.zscene", "wire.cfg", "out.bin"], d)
+        out[name] = read_render(os.path.join(d, "out.bin"))[0].astype(np.float32)
+        out[name + "_params"] = np.array([level, thick])
+        print("wire", name, info)
+    np.savez_compressed(os.path.join(GOLDEN, "wire_240x135.npz"), **out)
+
+
 def probe_rays(cfg, n, seed):
     """Known-answer rays for a scene: a third camera rays through random image positions (un-normalised, as
     get_ray builds them), the rest random origins in a ball around the look-at point with random directions of
@@ -252,7 +292,7 @@ def scene_targets():
     return t
 
 
-TARGETS = {"finish": finish, "quirks_aov": quirks_aov, "quirks_light": quirks_light, "weekend_ids": weekend_ids, "weekend_probe": weekend_probe, "weekend_stats": weekend_stats, **scene_targets()}
+TARGETS = {"finish": finish, "export": export, "wire": wire, "quirks_aov": quirks_aov, "quirks_light": quirks_light, "weekend_ids": weekend_ids, "weekend_probe": weekend_probe, "weekend_stats": weekend_stats, **scene_targets()}
 
 if __name__ == "__main__":
     names = sys.argv[1:] or list(TARGETS)

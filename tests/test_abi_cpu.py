@@ -187,3 +187,31 @@ def test_flat_scene_file_round_trip(tmp_path):
     open(p, "wb").write(b"not a scene at all" * 10)
     with pytest.raises(_lib.ZbError):
         api.load_flat(p)
+
+
+def test_png_and_hdr_writers_round_trip(tmp_path):
+    """zb_write_png / zb_write_hdr (host-side encoders of the export): the PNG decodes to the same
+    bytes, the RGBE file to the same radiance within the format's 8-bit mantissa."""
+    rng = np.random.default_rng(3)
+    rgb = rng.integers(0, 256, (37, 53, 3), dtype=np.uint8)
+    rgb[5:9, :, :] = 255
+    rgb[20:, 10:30, :] = 0
+    p = str(tmp_path / "a.png")
+    api.write_png(p, rgb)
+    back = api.read_png(p)
+    assert back.shape == rgb.shape and np.array_equal(back, rgb)
+    rgba = np.concatenate([rgb, rng.integers(0, 256, (37, 53, 1), dtype=np.uint8)], -1)
+    api.write_png(p, rgba)
+    assert np.array_equal(api.read_png(p), rgb), "alpha must be dropped"
+    hdr = (rng.lognormal(0.0, 2.5, (19, 31, 3))).astype(np.float32)
+    hdr[3, 4] = 0.0
+    hdr[5, 6] = [5.0e4, 1.0, 1e-3]
+    q = str(tmp_path / "a.hdr")
+    api.write_hdr(q, hdr)
+    got = api.read_hdr(q)
+    m = hdr.max(-1, keepdims=True)
+    assert np.all(np.abs(got - hdr) <= m / 128.0 + 1e-30), np.abs(got - hdr).max()
+    assert np.all(got[3, 4] == 0)
+    assert [api.pass_file_name(i) for i in (0, 2, 6)] == ["render_RGB.png", "render_Albedo.png", "render_Z-Depth.png"]
+    with pytest.raises(_lib.ZbError):
+        api.write_png(str(tmp_path / "missing_dir" / "x.png"), rgb)

@@ -196,3 +196,24 @@ def test_restatement_finishing_chain_matches_reference(zoracle, tmp_path):
         assert np.array_equal(hist, gold["histogram"]), name
         close = np.isclose(out, gold[name + "_image"], rtol=1e-6, atol=1e-7)
         assert close.mean() == 1.0, (name, close.mean(), np.abs(out - gold[name + "_image"]).max())
+
+
+# ------------------------------------------------------------------ image export
+def test_restatement_export_matches_reference_png_bytes(zoracle, tmp_path):
+    """process_framebuffer_to_image restated in zoracle against the pixels of the PNGs the reference wrote
+    (save_render_pass, camera.hpp:299-343).  Both in double: the 8-bit values agree except where 255.999 * v sits on
+    an integer boundary."""
+    from raytracer_project_b200 import api
+    from tests.golden.finish_cases import EXPORT_CASES, hdr_image
+    from tests.golden.make_golden import read_rgb8, write_image
+    gold = np.load(os.path.join(GOLDEN, "export_96x60.npz"))
+    d = str(tmp_path)
+    write_image(os.path.join(d, "in.bin"), hdr_image())
+    for name, (rp, kw) in EXPORT_CASES.items():
+        with open(os.path.join(d, "post.cfg"), "w") as f:
+            f.write(api.post_text(0, **kw) + f"render_pass {rp}\n")
+        subprocess.run([zoracle, "export", "in.bin", "post.cfg", "out.bin"], cwd=d, check=True, capture_output=True)
+        out = read_rgb8(os.path.join(d, "out.bin")).astype(np.int32)
+        ref = gold[name].astype(np.int32)
+        diff = np.abs(out - ref)
+        assert diff.max() <= 1 and (diff != 0).mean() < 1e-3, (name, diff.max(), (diff != 0).mean())
