@@ -336,6 +336,8 @@ enum { ZB_PASS_BEAUTY = 0, ZB_PASS_LIGHT = 1, ZB_PASS_AUX = 2 }; /* RGB/DENOISE 
 
 /* post_processor::analyze_framebuffer over W*H float4 means on the device (blocking, small D2H of the result) */
 int zb_analyze_device(zb_context* ctx, const void* mean_f4, size_t n_pixels, zb_image_stats* out);
+/* host-buffer variant (W*H*3 doubles, the reference's std::vector<color>); blocking */
+int zb_analyze_f64(zb_context* ctx, const double* rgb_f64, size_t n_pixels, zb_image_stats* out);
 /* post_processor::apply_auto_exposure (host arithmetic, no device work): the exposure render() stores back */
 double zb_auto_exposure(const zb_post* post, const zb_image_stats* stats);
 /* camera::update_post_processing for one pass: mean_f4 (W*H float4, device) -> display-referred colour in
@@ -354,6 +356,10 @@ int zb_finish(zb_context* ctx, const double* rgb_f64, int width, int height, con
  * asynchronous on the context stream; zb_resolve_device / zb_finish_device / zb_save_pass take it from there. ---- */
 int zb_render_bvh_debug_device(zb_context* ctx, const zb_scene* scene, const zb_camera* cam, const zb_environment* env,
                                const zb_render_opts* opts, int level, float thickness, void* accum_f4);
+/* host-buffer variant: means in the reference's layout (W*H*3 doubles), what camera::render leaves in
+ * render_accumulator when global_settings::bvh_debug_mode is set.  Blocking. */
+int zb_render_bvh_debug(zb_context* ctx, const zb_scene* scene, const zb_camera* cam, const zb_environment* env,
+                        const zb_render_opts* opts, int level, float thickness, double* rgb_f64);
 
 /* ---- image export: camera::save_render_pass (camera.hpp:299-343), process_framebuffer_to_image
  * (:701-780), file names "render_<Pass>.png" (main.cpp:1317) ---- */
@@ -365,6 +371,9 @@ const char* zb_pass_file_name(int render_pass);
  * sharpening, exposure, process(); every other pass: clamp + gamma (the export treats the light passes as data). Blocking. */
 int zb_save_pass(zb_context* ctx, const void* mean_f4, int width, int height, const zb_post* post, int render_pass,
                  const char* path);
+/* host-buffer variant: the reference's std::vector<color> (W*H*3 doubles) in */
+int zb_save_pass_f64(zb_context* ctx, const double* rgb_f64, int width, int height, const zb_post* post, int render_pass,
+                     const char* path);
 /* linear radiance as a flat Radiance RGBE file (readable by stbi_loadf, texture.hpp:23).  Blocking. */
 int zb_save_hdr(zb_context* ctx, const void* mean_f4, int width, int height, const char* path);
 /* host-side encoders behind the two calls above: 8-bit RGB PNG from RGB or RGBA rows (alpha dropped), RGBE from float

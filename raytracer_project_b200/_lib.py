@@ -128,11 +128,15 @@ SYMBOLS = {
     "zb_checkpoint_save": (C.c_int, [C.c_void_p, C.c_char_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_uint64]),
     "zb_checkpoint_load": (C.c_int, [C.c_void_p, C.c_char_p, C.c_void_p, C.c_int, C.c_int, C.POINTER(C.c_int), C.POINTER(C.c_uint64)]),
     "zb_analyze_device": (C.c_int, [C.c_void_p, C.c_void_p, C.c_size_t, C.POINTER(ImageStats)]),
+    "zb_analyze_f64": (C.c_int, [C.c_void_p, C.c_void_p, C.c_size_t, C.POINTER(ImageStats)]),
     "zb_auto_exposure": (C.c_double, [C.POINTER(Post), C.POINTER(ImageStats)]),
     "zb_finish_device": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.POINTER(Post), C.c_int, C.c_void_p, C.c_void_p]),
     "zb_finish": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.POINTER(Post), C.c_int, C.c_void_p]),
     "zb_render_bvh_debug_device": (C.c_int, [C.c_void_p, C.c_void_p, C.POINTER(Camera), C.POINTER(Environment), C.POINTER(RenderOpts), C.c_int,
                                    C.c_float, C.c_void_p]),
+    "zb_render_bvh_debug": (C.c_int, [C.c_void_p, C.c_void_p, C.POINTER(Camera), C.POINTER(Environment), C.POINTER(RenderOpts), C.c_int,
+                            C.c_float, C.c_void_p]),
+    "zb_save_pass_f64": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.POINTER(Post), C.c_int, C.c_char_p]),
     "zb_pass_file_name": (C.c_char_p, [C.c_int]),
     "zb_save_pass": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.POINTER(Post), C.c_int, C.c_char_p]),
     "zb_save_hdr": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_char_p]),

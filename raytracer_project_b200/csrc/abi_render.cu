@@ -329,6 +329,26 @@ extern "C" int zb_render_bvh_debug_device(zb_context* ctx, const zb_scene* scene
     return ZB_OK;
 }
 
+// Host-buffer variant in the reference's layout: what camera::render leaves in render_accumulator when
+// global_settings::bvh_debug_mode is set (3 doubles per pixel, means over the samples).  Blocking.
+extern "C" int zb_render_bvh_debug(zb_context* ctx, const zb_scene* scene, const zb_camera* cam, const zb_environment* env,
+                                   const zb_render_opts* opts, int level, float thickness, double* rgb_f64) {
+    if (!ctx || !cam || !opts || !rgb_f64) return fail(ZB_ERR_INVALID, "zb_render_bvh_debug: NULL argument");
+    if (cam->image_width < 1 || cam->image_height < 1 || opts->samples_per_pixel < 1) return fail(ZB_ERR_INVALID, "zb_render_bvh_debug: bad size");
+    ZB_CUDA(cudaSetDevice(ctx->device));
+    const size_t pixels = size_t(cam->image_width) * cam->image_height;
+    int rc = ensure_scratch(ctx, pixels, false);
+    if (rc) return rc;
+    zb_render_opts o = *opts;
+    o.accumulate = 0;
+    rc = zb_render_bvh_debug_device(ctx, scene, cam, env, &o, level, thickness, ctx->accum);
+    if (rc) return rc;
+    const int n_s = (o.sample_end > o.sample_begin ? o.sample_end - o.sample_begin : o.samples_per_pixel);
+    ZB_CUDA(zbk_launch_resolve(ctx->accum, pixels, float(1.0 / std::max(n_s, 1)), ctx->out_f4, nullptr, ctx->stream));
+    ctx->stats.launches++;
+    return d2h_rgb_f64(ctx, rgb_f64, ctx->out_f4, pixels);
+}
+
 extern "C" int zb_resolve_device(zb_context* ctx, const void* accum_f4, size_t n_pixels, double scale, void* out_f4,
                                  void* out_rgb_f64) {
     if (!ctx || !accum_f4) return fail(ZB_ERR_INVALID, "zb_resolve_device: NULL argument");

@@ -448,3 +448,32 @@ extern "C" int zb_save_hdr(zb_context* ctx, const void* mean_f4, int width, int 
     ZB_CUDA(cudaStreamSynchronize(ctx->stream));
     return zb_write_hdr(path, width, height, reinterpret_cast<const float*>(host.data()), 4, 0);
 }
+
+// Host-buffer variant of zb_save_pass: the reference's std::vector<color> (3 doubles per pixel) in.
+extern "C" int zb_save_pass_f64(zb_context* ctx, const double* rgb_f64, int width, int height, const zb_post* post,
+                                int render_pass, const char* path) {
+    if (!ctx || !rgb_f64 || !post || !path) return fail(ZB_ERR_INVALID, "zb_save_pass_f64: NULL argument");
+    if (width < 1 || height < 1) return fail(ZB_ERR_INVALID, "zb_save_pass_f64: bad size");
+    ZB_CUDA(cudaSetDevice(ctx->device));
+    const size_t pixels = size_t(width) * height;
+    int rc = ensure_finish_scratch(ctx, pixels, true);
+    if (rc) return rc;
+    std::vector<float4> stage(pixels);
+    for (size_t i = 0; i < pixels; i++) stage[i] = make_float4(float(rgb_f64[3 * i]), float(rgb_f64[3 * i + 1]), float(rgb_f64[3 * i + 2]), 1.f);
+    ZB_CUDA(cudaMemcpyAsync(ctx->fin_in, stage.data(), pixels * sizeof(float4), cudaMemcpyHostToDevice, ctx->stream));
+    ZB_CUDA(cudaStreamSynchronize(ctx->stream));  // `stage` leaves scope before zb_save_pass returns otherwise
+    return zb_save_pass(ctx, ctx->fin_in, width, height, post, render_pass, path);
+}
+
+// Host-buffer variant of zb_analyze_device (post_processor::analyze_framebuffer on a std::vector<color>).
+extern "C" int zb_analyze_f64(zb_context* ctx, const double* rgb_f64, size_t n_pixels, zb_image_stats* out) {
+    if (!ctx || !rgb_f64 || !out || !n_pixels) return fail(ZB_ERR_INVALID, "zb_analyze_f64: bad argument");
+    ZB_CUDA(cudaSetDevice(ctx->device));
+    int rc = ensure_finish_scratch(ctx, n_pixels, true);
+    if (rc) return rc;
+    std::vector<float4> stage(n_pixels);
+    for (size_t i = 0; i < n_pixels; i++) stage[i] = make_float4(float(rgb_f64[3 * i]), float(rgb_f64[3 * i + 1]), float(rgb_f64[3 * i + 2]), 1.f);
+    ZB_CUDA(cudaMemcpyAsync(ctx->fin_in, stage.data(), n_pixels * sizeof(float4), cudaMemcpyHostToDevice, ctx->stream));
+    ZB_CUDA(cudaStreamSynchronize(ctx->stream));
+    return zb_analyze_device(ctx, ctx->fin_in, n_pixels, out);
+}

@@ -7,13 +7,16 @@
 // GPU through the C ABI (include/zenith_b200.h): the scene graph is flattened once per world object
 // (flatten.hpp), uploaded, and zb_render fills the caller-visible std::vector<color> buffers in the reference's
 // layout (row-major, top row first, double RGB), reports progress through `lines_rendered` and honours
-// `render_flag` between sample batches.  The reference's tail of render() — auto-exposure, OIDN,
-// post-processing (camera.hpp:258-295) — is host/UI code and stays with the caller.
+// `render_flag` between sample batches.  The tail of render() runs too: auto-exposure (camera.hpp:258-267) and
+// update_post_processing into `final_framebuffer` (:294, :142-207) through the finishing-chain kernels; OIDN
+// (:270-291) is absent here, as in SURVEY 8(f).  save_render_pass (:299-343) writes "output/<file>" PNGs, and
+// global_settings::bvh_debug_mode switches render() to the BVH debug view (bvh.hpp:56-110).
 //
 // Header-only C++20 over the C ABI; link with libzenith_b200.so.  There is no CPU fallback: without a B200 the
 // call fails and `last_error` says why.
 #pragma once
 #include <atomic>
+#include <filesystem>
 #include <memory>
 #include <string>
 #include <vector>
@@ -23,9 +26,78 @@
 
 namespace zenith {
 
-// Only z_depth_max_dist reaches the hot path (camera.hpp:247); the other post-processing fields are UI state.
+// common.hpp:110-118
+enum class render_pass : int { RGB = 0, DENOISE, ALBEDO, NORMALS, REFLECTIONS, REFRACTIONS, Z_DEPTH };
+
+// common.hpp:120-124
+namespace global_settings {
+inline bool bvh_debug_mode = false;
+inline float bvh_thickness = 0.01f;
+inline int debug_bvh_level = -1;
+}  // namespace global_settings
+
+// color_processing.hpp:9-28
+struct image_statistics {
+    float average_luminance = 0.0f;
+    float max_luminance = 0.0f;
+    int histogram[256] = {0};
+};
+
+// color_processing.hpp:30-42
+struct debug_flags {
+    bool red = false, green = false, blue = false, luminance = false, bvh = false;
+    bool any_active() const { return red || green || blue || luminance || bvh; }
+};
+
+// The fields of the reference's post_processor (color_processing.hpp:44-74).  Its arithmetic lives in the finishing
+// kernels (csrc/finish.cu); this is the parameter block the caller edits.
 struct post_processor {
-    double z_depth_max_dist = 20.0;
+    mutable float exposure = 0.5f;
+    float saturation = 1.0f;
+    float contrast = 1.0f;
+    float hue_shift = 0.0f;
+    float vignette_intensity = 1.0f;
+    vec3 color_balance = vec3(1.0, 1.0, 1.0);
+    float z_depth_max_dist = 1.0f;
+    float exposure_compensation_stops = 0.0f;
+    bool use_aces_tone_mapping = false;
+    bool use_auto_exposure = false;
+    float target_luminance = 0.12f;
+    mutable debug_flags debug;
+    bool use_bloom = false;
+    float bloom_threshold = 1.0f;
+    float bloom_intensity = 0.3f;
+    int bloom_radius = 4;
+    bool needs_update = true;
+    mutable image_statistics last_stats;
+    bool use_sharpening = false;
+    double sharpen_amount = 0.2;
+
+    zb_post to_abi() const {
+        zb_post p{};
+        p.exposure = exposure;
+        p.saturation = saturation;
+        p.contrast = contrast;
+        p.hue_shift = hue_shift;
+        p.vignette_intensity = vignette_intensity;
+        for (int k = 0; k < 3; k++) p.color_balance[k] = float(color_balance[k]);
+        p.exposure_compensation_stops = exposure_compensation_stops;
+        p.target_luminance = target_luminance;
+        p.use_aces_tone_mapping = use_aces_tone_mapping;
+        p.use_auto_exposure = use_auto_exposure;
+        p.debug_red = debug.red;
+        p.debug_green = debug.green;
+        p.debug_blue = debug.blue;
+        p.debug_luminance = debug.luminance;
+        p.debug_bvh = debug.bvh;
+        p.use_bloom = use_bloom;
+        p.bloom_threshold = bloom_threshold;
+        p.bloom_intensity = bloom_intensity;
+        p.bloom_radius = bloom_radius;
+        p.use_sharpening = use_sharpening;
+        p.sharpen_amount = sharpen_amount;
+        return p;
+    }
 };
 
 class camera {
@@ -47,7 +119,11 @@ public:
     bool use_reflection = false, use_refraction = false;
     // camera.hpp:63, :80-85, :88
     std::vector<color> render_accumulator, albedo_buffer, normal_buffer, z_depth_buffer, reflection_buffer, refraction_buffer;
+    std::vector<color> final_framebuffer;  // camera.hpp:64: what the GUI shows, written by update_post_processing
     std::atomic<int> lines_rendered{0};
+    // camera.hpp:66-78
+    static inline const char* pass_names[] = {"RGB", "Denoise", "Albedo", "Normals", "Reflections", "Refractions", "Z-Depth"};
+    render_pass current_display_pass = render_pass::RGB;
 
     // backend knobs (no counterpart in the reference)
     int device = 0;
@@ -131,10 +207,69 @@ public:
         out.refraction = use_refraction ? reinterpret_cast<double*>(refraction_buffer.data()) : nullptr;
         watch w{this, &render_flag, 0};
         if (!render_flag.load()) return;  // camera.hpp:441-443
-        rc = zb_render(ctx, scene, &c, &e, &o, &out, &w.cancel, &camera::on_progress, &w);
+        if (global_settings::bvh_debug_mode)  // bvh.hpp:46-48: the traversal itself switches to the debug view
+            rc = zb_render_bvh_debug(ctx, scene, &c, &e, &o, global_settings::debug_bvh_level, global_settings::bvh_thickness,
+                                     reinterpret_cast<double*>(render_accumulator.data()));
+        else
+            rc = zb_render(ctx, scene, &c, &e, &o, &out, &w.cancel, &camera::on_progress, &w);
         if (rc == ZB_ERR_CANCELLED) return;  // partial buffers stay, like the reference's early return (camera.hpp:252-254)
         if (rc != ZB_OK) { set_error(rc, zb_last_error()); return; }
         lines_rendered.store(image_height);  // camera.hpp:576-578
+        if (!render_flag.load()) return;     // camera.hpp:252-254
+        if (post.use_auto_exposure) {        // camera.hpp:258-267
+            zb_image_stats st{};
+            if ((rc = zb_analyze_f64(ctx, reinterpret_cast<const double*>(render_accumulator.data()), n, &st)) != ZB_OK) { set_error(rc, zb_last_error()); return; }
+            const zb_post p = post.to_abi();
+            post.exposure = float(zb_auto_exposure(&p, &st));
+        }
+        update_post_processing(post, image_width, image_height);  // camera.hpp:294
+    }
+
+    // camera.hpp:90-113
+    const std::vector<color>& get_active_buffer() const {
+        switch (current_display_pass) {
+            case render_pass::ALBEDO: return albedo_buffer;
+            case render_pass::NORMALS: return normal_buffer;
+            case render_pass::REFLECTIONS: return reflection_buffer;
+            case render_pass::REFRACTIONS: return refraction_buffer;
+            case render_pass::Z_DEPTH: return z_depth_buffer;
+            default: return render_accumulator;  // RGB, and DENOISE (no denoiser here)
+        }
+    }
+
+    // camera.hpp:142-207: the displayed pass through exposure, bloom, sharpening and process() into final_framebuffer
+    void update_post_processing(const post_processor& post, int w, int h) {
+        if (render_accumulator.empty()) return;
+        const std::vector<color>& source = get_active_buffer();
+        if (source.size() < size_t(w) * size_t(h) || w < 1 || h < 1) return;
+        final_framebuffer.resize(source.size());
+        if (!ctx && (rc = zb_context_create(device, &ctx)) != ZB_OK) { set_error(rc, zb_last_error()); return; }
+        const bool beauty = current_display_pass == render_pass::RGB || current_display_pass == render_pass::DENOISE;
+        const bool light = current_display_pass == render_pass::REFLECTIONS || current_display_pass == render_pass::REFRACTIONS;
+        const zb_post p = post.to_abi();
+        rc = zb_finish(ctx, reinterpret_cast<const double*>(source.data()), w, h, &p, beauty ? ZB_PASS_BEAUTY : light ? ZB_PASS_LIGHT : ZB_PASS_AUX,
+                       reinterpret_cast<double*>(final_framebuffer.data()));
+        if (rc != ZB_OK) set_error(rc, zb_last_error());
+    }
+
+    // camera.hpp:299-343: "output/<filename>", created on demand
+    void save_render_pass(render_pass pass, const std::string& filename, const post_processor& pp) {
+        std::error_code ec;
+        std::filesystem::create_directory("output", ec);
+        const std::vector<color>* src = &render_accumulator;
+        switch (pass) {
+            case render_pass::ALBEDO: src = &albedo_buffer; break;
+            case render_pass::NORMALS: src = &normal_buffer; break;
+            case render_pass::REFLECTIONS: src = &reflection_buffer; break;
+            case render_pass::REFRACTIONS: src = &refraction_buffer; break;
+            case render_pass::Z_DEPTH: src = &z_depth_buffer; break;
+            default: break;
+        }
+        if (src->size() < size_t(image_width) * size_t(image_height)) { set_error(ZB_ERR_INVALID, "save_render_pass: the pass buffer is empty"); return; }
+        if (!ctx && (rc = zb_context_create(device, &ctx)) != ZB_OK) { set_error(rc, zb_last_error()); return; }
+        const zb_post p = pp.to_abi();
+        rc = zb_save_pass_f64(ctx, reinterpret_cast<const double*>(src->data()), image_width, image_height, &p, int(pass), ("output/" + filename).c_str());
+        if (rc != ZB_OK) set_error(rc, zb_last_error());
     }
 
     void release() {

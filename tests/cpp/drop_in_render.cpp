@@ -35,6 +35,7 @@ int main(int argc, char** argv) {
     env.set_mode(EnvironmentSettings::SOLID_COLOR);
     env.background_color = color(0.7, 0.8, 1.0);
     post_processor post;
+    post.z_depth_max_dist = 20.0f;  // the value the ABI-side render of the test uses (the reference's default is 1)
     camera cam;
     cam.image_width = std::atoi(argv[3]);
     cam.image_height = std::atoi(argv[4]);
@@ -87,6 +88,35 @@ int main(int argc, char** argv) {
     if (cam2.rc != ZB_OK || !finite_nonzero(cam2.render_accumulator) || cam2.lines_rendered.load() != 36) {
         std::fprintf(stderr, "hand-built scene failed: rc %d %s\n", cam2.rc, cam2.last_error.c_str());
         return 1;
+    }
+    // ---- 2b. the tail of render(): final_framebuffer (camera.hpp:294), auto-exposure stored back (:263), export (:299)
+    if (cam2.final_framebuffer.size() != cam2.render_accumulator.size() || !finite_nonzero(cam2.final_framebuffer)) { std::fprintf(stderr, "final_framebuffer missing\n"); return 1; }
+    for (const color& c : cam2.final_framebuffer)
+        if (c.x() < 0 || c.x() > 1 || c.y() < 0 || c.y() > 1 || c.z() < 0 || c.z() > 1) { std::fprintf(stderr, "final_framebuffer not display-referred\n"); return 1; }
+    post_processor auto_post;
+    auto_post.use_auto_exposure = true;
+    auto_post.use_bloom = true;
+    const float before = auto_post.exposure;
+    cam2.render(*bvh_world, sun, auto_post, is_rendering);
+    if (cam2.rc != ZB_OK || auto_post.exposure == before) { std::fprintf(stderr, "auto-exposure not applied: %s\n", cam2.last_error.c_str()); return 1; }
+    cam2.save_render_pass(render_pass::RGB, std::string("render_") + camera::pass_names[0] + ".png", auto_post);  // main.cpp:1317
+    if (cam2.rc != ZB_OK) { std::fprintf(stderr, "save_render_pass: %s\n", cam2.last_error.c_str()); return 1; }
+    {
+        std::ifstream png("output/render_RGB.png", std::ios::binary);
+        char sig[8] = {0};
+        png.read(sig, 8);
+        if (!png || sig[1] != 'P' || sig[2] != 'N' || sig[3] != 'G') { std::fprintf(stderr, "output/render_RGB.png missing\n"); return 1; }
+    }
+    // ---- 2c. BVH debug view through the reference's global switch (common.hpp:121-123, bvh.hpp:46-48)
+    global_settings::bvh_debug_mode = true;
+    global_settings::debug_bvh_level = 0;
+    global_settings::bvh_thickness = 0.05f;
+    cam2.render(*bvh_world, sun, post, is_rendering);
+    global_settings::bvh_debug_mode = false;
+    {
+        bool frame = false;
+        for (const color& c : cam2.render_accumulator) frame = frame || c.z() > 1.0;
+        if (cam2.rc != ZB_OK || !frame) { std::fprintf(stderr, "debug view drew no frame: %s\n", cam2.last_error.c_str()); return 1; }
     }
     // ---- 3. render_flag already false: returns at once and leaves the buffers untouched (camera.hpp:441-443)
     cam2.reset_accumulator();
