@@ -239,7 +239,7 @@ def ours(args):
         sc2 = ctx.upload(flat)  # H2D of the flattened scene
         t_up = time.perf_counter()
         if world == 1:
-            res = sc2.render(cfg, seed=1)  # blocking; fills a host (H, W, 3) float64 buffer
+            res = sc2.render(cfg, seed=1, beauty_out=host_rgb)  # blocking; fills the caller's (H, W, 3) float64 buffer
             checksum = float(res["beauty"][HEIGHT // 2, WIDTH // 2, 0])
         else:
             sc2.render_device(cfg, accum.data_ptr(), seed=1, sample_range=(s0, s1))

@@ -281,13 +281,19 @@ class Scene:
             self.h = C.c_void_p()
 
     def render(self, cfg: RenderConfig, seed=1, stats=False, want_f4=False, sample_range=None, tile=None,
-               samples_per_launch=0, progress=None, cancel=None):
-        """zb_render: returns dict of (H, W, 3) float64 arrays like the reference's buffers."""
+               samples_per_launch=0, progress=None, cancel=None, beauty_out=None):
+        """zb_render: returns dict of (H, W, 3) float64 arrays like the reference's buffers.  beauty_out: a caller-owned
+        C-contiguous float64 array of W*H*3 elements to fill instead of a new one (the reference's render_accumulator
+        is sized once by reset_accumulator and reused, camera.hpp:209-233)."""
         n = cfg.image_width * cfg.image_height
         cam, env = camera_struct(cfg), env_struct(cfg)
         o = opts_struct(cfg, seed, sample_range, tile, stats, samples_per_launch)
         out = Outputs()
-        res = {"beauty": np.empty((cfg.image_height, cfg.image_width, 3), np.float64)}
+        if beauty_out is not None:
+            assert beauty_out.dtype == np.float64 and beauty_out.flags.c_contiguous and beauty_out.size == 3 * n
+            res = {"beauty": beauty_out.reshape(cfg.image_height, cfg.image_width, 3)}
+        else:
+            res = {"beauty": np.empty((cfg.image_height, cfg.image_width, 3), np.float64)}
         out.beauty = res["beauty"].ctypes.data
         for key, flag in (("albedo", cfg.use_albedo), ("normal", cfg.use_normal), ("z_depth", cfg.use_z_depth),
                           ("reflection", cfg.use_reflection), ("refraction", cfg.use_refraction)):

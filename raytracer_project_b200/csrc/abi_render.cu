@@ -233,23 +233,11 @@ int d2h(zb_context* ctx, void* host, const void* dev, size_t bytes) {
     return ZB_OK;
 }
 
-// Device float4 means -> the reference's host layout (3 doubles per pixel, camera.hpp:531).  The frame
-// crosses PCIe as float4 (16 B/pixel instead of 24) in chunks; while chunk c+1 is in flight, host threads
-// widen chunk c into the caller's buffer, so the copy, the widening and the pageable-memory write overlap.
-int d2h_rgb_f64(zb_context* ctx, double* host, const float4* dev, size_t pixels) {
-    const size_t chunk = size_t(1) << 18;  // 256 Ki pixels = 4 MiB per copy
-    const size_t n_chunks = (pixels + chunk - 1) / chunk;
-    while (ctx->chunk_ev.size() < n_chunks) {
-        cudaEvent_t e;
-        ZB_CUDA(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
-        ctx->chunk_ev.push_back(e);
-    }
-    float4* stage = static_cast<float4*>(ctx->pinned);
-    for (size_t c = 0; c < n_chunks; c++) {
-        const size_t b = c * chunk, n = std::min(chunk, pixels - b);
-        ZB_CUDA(cudaMemcpyAsync(stage + b, dev + b, n * sizeof(float4), cudaMemcpyDeviceToHost, ctx->stream));
-        ZB_CUDA(cudaEventRecord(ctx->chunk_ev[c], ctx->stream));
-    }
+// Host side of the frame copy: chunk c (pixels [begin[c], begin[c + 1])) is widened from the pinned float4 stage into
+// the caller's 3-double layout (camera.hpp:531) as soon as its event has fired; up to 8 host threads.
+int widen_chunks(zb_context* ctx, double* host, const std::vector<size_t>& begin) {
+    const size_t n_chunks = begin.size() - 1;
+    const float4* stage = static_cast<const float4*>(ctx->pinned);
     const unsigned hw = std::max(1u, std::thread::hardware_concurrency());
     const size_t n_thr = std::min<size_t>(std::min<size_t>(hw, 8), n_chunks);
     std::atomic<size_t> next{0};
@@ -259,7 +247,7 @@ int d2h_rgb_f64(zb_context* ctx, double* host, const float4* dev, size_t pixels)
             const size_t c = next.fetch_add(1);
             if (c >= n_chunks) return;
             if (cudaEventSynchronize(ctx->chunk_ev[c]) != cudaSuccess) { err.store(1); return; }
-            const size_t b = c * chunk, n = std::min(chunk, pixels - b);
+            const size_t b = begin[c], n = begin[c + 1] - b;
             const float4* src = stage + b;
             double* dst = host + 3 * b;
             for (size_t i = 0; i < n; i++) {
@@ -274,8 +262,85 @@ int d2h_rgb_f64(zb_context* ctx, double* host, const float4* dev, size_t pixels)
     work();
     for (auto& t : pool) t.join();
     if (err.load()) return fail(ZB_ERR_CUDA, "device-to-host copy of the frame failed");
+    return ZB_OK;
+}
+
+int ensure_chunk_events(zb_context* ctx, size_t n) {
+    while (ctx->chunk_ev.size() < n) {
+        cudaEvent_t e;
+        ZB_CUDA(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+        ctx->chunk_ev.push_back(e);
+    }
+    return ZB_OK;
+}
+
+// Device float4 means -> the reference's host layout (3 doubles per pixel, camera.hpp:531).  The frame
+// crosses PCIe as float4 (16 B/pixel instead of 24) in chunks; while chunk c+1 is in flight, host threads
+// widen chunk c into the caller's buffer, so the copy, the widening and the pageable-memory write overlap.
+int d2h_rgb_f64(zb_context* ctx, double* host, const float4* dev, size_t pixels) {
+    const size_t chunk = size_t(1) << 18;  // 256 Ki pixels = 4 MiB per copy
+    const size_t n_chunks = (pixels + chunk - 1) / chunk;
+    int rc = ensure_chunk_events(ctx, n_chunks);
+    if (rc) return rc;
+    float4* stage = static_cast<float4*>(ctx->pinned);
+    std::vector<size_t> begin;
+    for (size_t c = 0; c < n_chunks; c++) {
+        const size_t b = c * chunk, n = std::min(chunk, pixels - b);
+        begin.push_back(b);
+        ZB_CUDA(cudaMemcpyAsync(stage + b, dev + b, n * sizeof(float4), cudaMemcpyDeviceToHost, ctx->stream));
+        ZB_CUDA(cudaEventRecord(ctx->chunk_ev[c], ctx->stream));
+    }
+    begin.push_back(pixels);
+    rc = widen_chunks(ctx, host, begin);
+    if (rc) return rc;
     ZB_CUDA(cudaStreamSynchronize(ctx->stream));
     return ZB_OK;
+}
+
+// Beauty-only frame with host output, rendered as horizontal bands of tile rows, band b on its own stream: render,
+// resolve and copy of a band are ordered on that stream, the bands overlap each other (blocks of band b + 1 fill the
+// SMs band b drains from), so all but the last band's copy and widening hide behind rendering.  Same pixels as the
+// single launch: a tile's result depends on the tile alone.
+int render_banded(zb_context* ctx, RenderParams P, const zb_render_opts* opts, double* host) {
+    const size_t W = size_t(P.cam.width), H = size_t(P.cam.height);
+    const int rows = P.tiles_y;
+    const int n_bands = std::min(rows, 6);
+    while (int(ctx->band_streams.size()) < n_bands) {
+        // earlier bands get the higher stream priority, so the block scheduler finishes them first instead of
+        // interleaving all bands (which would move every copy to the end of the frame again)
+        int least = 0, greatest = 0;
+        ZB_CUDA(cudaDeviceGetStreamPriorityRange(&least, &greatest));
+        const int prio = std::min(least, greatest + int(ctx->band_streams.size()));
+        cudaStream_t st;
+        ZB_CUDA(cudaStreamCreateWithPriority(&st, cudaStreamNonBlocking, prio));
+        ctx->band_streams.push_back(st);
+    }
+    if (!ctx->band_fork) ZB_CUDA(cudaEventCreateWithFlags(&ctx->band_fork, cudaEventDisableTiming));
+    int rc = ensure_chunk_events(ctx, size_t(n_bands));
+    if (rc) return rc;
+    ZB_CUDA(cudaEventRecord(ctx->band_fork, ctx->stream));
+    float4* stage = static_cast<float4*>(ctx->pinned);
+    const float scale = float(1.0 / opts->samples_per_pixel);
+    std::vector<size_t> begin;
+    for (int b = 0; b < n_bands; b++) {
+        const int r0 = int((long long)rows * b / n_bands), r1 = int((long long)rows * (b + 1) / n_bands);
+        const size_t p0 = std::min(size_t(r0) * ZB_TILE_H, H) * W, p1 = std::min(size_t(r1) * ZB_TILE_H, H) * W;
+        cudaStream_t st = ctx->band_streams[b];
+        ZB_CUDA(cudaStreamWaitEvent(st, ctx->band_fork, 0));
+        RenderParams B = P;
+        B.tile_ranks = 1;
+        B.tile_rank = r0 * P.tiles_x;  // block i renders tile i + offset
+        B.accumulate = 0;
+        ZB_CUDA(zbk_launch_render(B, (r1 - r0) * P.tiles_x, false, st));
+        ZB_CUDA(zbk_launch_resolve(ctx->accum + p0, p1 - p0, scale, ctx->out_f4 + p0, nullptr, st));
+        ZB_CUDA(cudaMemcpyAsync(stage + p0, ctx->out_f4 + p0, (p1 - p0) * sizeof(float4), cudaMemcpyDeviceToHost, st));
+        ZB_CUDA(cudaEventRecord(ctx->chunk_ev[b], st));
+        ZB_CUDA(cudaStreamWaitEvent(ctx->stream, ctx->chunk_ev[b], 0));  // join: later work on the context stream follows
+        ctx->stats.launches += 2;
+        begin.push_back(p0);
+    }
+    begin.push_back(W * H);
+    return widen_chunks(ctx, host, begin);
 }
 
 int read_counters(zb_context* ctx) {
@@ -395,6 +460,23 @@ extern "C" int zb_render(zb_context* ctx, const zb_scene* scene, const zb_camera
     ctx->stats = zb_stats{};
     ZB_CUDA(cudaMemsetAsync(ctx->counters, 0, 8 * sizeof(unsigned long long), ctx->stream));
     ZB_CUDA(cudaEventRecord(ctx->ev[0], ctx->stream));
+    const char* band_env = getenv("ZB_BANDS");
+    const bool banded = out->beauty && !out->beauty_f4 && !aux && !light && !cancel && !progress && opts->samples_per_launch <= 0 &&
+                        P.tile_ranks == 1 && !opts->accumulate && !opts->collect_stats && P.sample_end > P.sample_begin &&
+                        P.max_depth > 0 && P.tiles_y >= 12 && !(band_env && atoi(band_env) == 0) && !getenv("ZB_WAVEFRONT");
+    if (banded) {
+        rc = render_banded(ctx, P, opts, out->beauty);
+        if (rc) return rc;
+        ZB_CUDA(cudaEventRecord(ctx->ev[1], ctx->stream));
+        ZB_CUDA(cudaEventRecord(ctx->ev[2], ctx->stream));
+        ZB_CUDA(cudaEventRecord(ctx->ev[3], ctx->stream));
+        rc = read_counters(ctx);
+        if (rc) return rc;
+        float ms = 0;
+        ZB_CUDA(cudaEventElapsedTime(&ms, ctx->ev[0], ctx->ev[1]));
+        ctx->stats.kernel_ms = ms;  // render, resolve and copy of the bands overlap: one figure for all three
+        return ZB_OK;
+    }
     rc = launch_share(ctx, P, opts, cancel, progress, user, true);
     if (rc) return rc;
     ZB_CUDA(cudaEventRecord(ctx->ev[1], ctx->stream));
