@@ -6,7 +6,7 @@
   python -m torch.distributed.run --nnodes=1 --nproc-per-node N ... bench.py --gpus N ...
 
 A "step" = one full frame: every rank renders its sample slice of the whole frame into a float4 sum
-buffer (k_render), the partial sums are combined on rank 0 with one NCCL reduce over NVLink, and rank 0
+buffer (k_render_pq: frame-wide path queue, fixed-point sums, + k_pq_resolve), the partial sums are combined on rank 0 with one NCCL reduce over NVLink, and rank 0
 resolves sums -> means (k_resolve).  `value` is timed with inputs (the flattened scene) resident in
 HBM; `e2e` goes through the public C-ABI call zb_render with host buffers (scene upload H2D and the
 double-RGB frame D2H inside the timed region).  Prints ONE JSON line on rank 0.
@@ -32,10 +32,10 @@ sys.path.insert(0, ROOT)
 
 WIDTH, HEIGHT, SPP, DEPTH = 1920, 1080, 64, 50
 WORKLOAD = f"weekend_seed1_{WIDTH}x{HEIGHT}_{SPP}spp_depth{DEPTH}"
-# DRAM traffic of one k_render launch on the headline frame (ncu, profiles/r01_k_render_v3_raw_key.txt): 0.18 MB read +
-# 2.34 MB written while the kernel runs — the 60 KB scene is L1-resident and most of the 33 MB of float4 sums is still
-# in the 126 MB L2 when the kernel ends.
-NCU_DRAM_BYTES_PER_LAUNCH = 177920 + 2336512
+# DRAM traffic of one k_render_pq launch on the headline frame (ncu, profiles/r01_k_render_pq_raw_key.txt): 50.3 MB read +
+# 8.0 MB written while the kernel runs — the 60 KB scene is L1-resident; the traffic is the 50 MB of 64-bit fixed-point
+# per-pixel sums (zeroed before the launch, RED.ADDed in L2) entering and partly leaving the 126 MB L2.
+NCU_DRAM_BYTES_PER_LAUNCH = 50284288 + 7954944
 HARNESS = os.path.join(ROOT, "oracle", "_ref", "ref_harness")   # the unmodified reference (kind "reference")
 PORT = os.path.join(ROOT, "oracle", "_build", "zoracle")         # CPU restatement, used only if the former is absent
 
@@ -288,13 +288,13 @@ def ours(args):
                                  "scene_free": sum(p[2] for p in e2e_parts) / len(e2e_parts)},
                     "note": "frame crosses PCIe as float4 means (16 B/pixel) and is widened to the reference's "
                             "3-double layout by host threads while later chunks are in flight"},
-            "gpu_launches": 2 * args.steps,
+            "gpu_launches": 3 * args.steps,  # k_render_pq + k_pq_resolve (zb_render_device) + k_resolve per step
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": hbm_peak, "unit": "GB/s", "frac": achieved / hbm_peak,
                          "traffic": NCU_DRAM_BYTES_PER_LAUNCH if world == 1 else None,
-                         "traffic_source": "dram__bytes_read.sum + dram__bytes_write.sum of k_render<false,false> on this workload, "
-                                           "ncu --set full capture summarised in profiles/r01_k_render_v3_raw_key.txt",
+                         "traffic_source": "dram__bytes_read.sum + dram__bytes_write.sum of k_render_pq on this workload, "
+                                           "ncu --set full capture summarised in profiles/r01_k_render_pq_raw_key.txt",
                          "peak_kind": f"{peak_kind} burst copy bandwidth",
-                         "kernel": "k_render<false,false>", "algorithmic_bytes_per_launch": per_gpu_bytes,
+                         "kernel": "k_render_pq", "algorithmic_bytes_per_launch": per_gpu_bytes,
                          "note": "scene (60 KB) is L1/L2-resident: algorithmic bytes are served by L1, so this "
                                  "fraction can exceed 1; the binding roofline is FP32/issue (roofline_fp32)"},
             "roofline_fp32": {"achieved": alg_flop / world / (kernel_ms * 1e-3) * 1e-12, "peak": fp32_peak,

@@ -203,6 +203,9 @@ int launch_share(zb_context* ctx, RenderParams P, const zb_render_opts* o, const
     const bool wavefront = wf_env && atoi(wf_env) > 0 && !o->collect_stats;
     const char* wf_slots_env = getenv("ZB_WF_SLOTS");
     const size_t wf_slots = wf_slots_env ? size_t(atoll(wf_slots_env)) : 0;
+    // the beauty pass runs as k_render_pq (frame-wide path queue) unless ZB_PQ=0 asks for the tile-bound k_render
+    const char* pq_env = getenv("ZB_PQ");
+    const bool pq = !(pq_env && atoi(pq_env) == 0);
     int done = 0;
     for (int s = sb; s < se; s += per) {
         if (cancel && *cancel) return fail(ZB_ERR_CANCELLED, "render cancelled");
@@ -213,6 +216,16 @@ int launch_share(zb_context* ctx, RenderParams P, const zb_render_opts* o, const
             int iters = 0;
             ZB_CUDA(zbk_launch_wavefront(P, &ctx->wf, wf_slots, &iters, ctx->stream));
             ctx->stats.launches += 2 + 2 * iters;
+        } else if (pq && !P.light_pass && !P.accum_aux && !o->collect_stats && P.max_depth > 0 && P.sample_end > P.sample_begin) {
+            if (ctx->pq_pixels < pixels) {
+                cudaFree(ctx->pq_fix);
+                ctx->pq_fix = nullptr;
+                ctx->pq_pixels = 0;
+                ZB_CUDA(cudaMalloc(&ctx->pq_fix, (pixels * 3 + 1) * sizeof(unsigned long long)));
+                ctx->pq_pixels = pixels;
+            }
+            ZB_CUDA(zbk_launch_render_pq(P, owned_tiles(P), ctx->pq_fix, ctx->pq_fix + ctx->pq_pixels * 3, ctx->sm_count, ctx->stream));
+            ctx->stats.launches += 2;
         } else {
             ZB_CUDA(zbk_launch_render(P, owned_tiles(P), o->collect_stats != 0, ctx->stream));
             ctx->stats.launches++;
@@ -463,7 +476,7 @@ extern "C" int zb_render(zb_context* ctx, const zb_scene* scene, const zb_camera
     const char* band_env = getenv("ZB_BANDS");
     const bool banded = out->beauty && !out->beauty_f4 && !aux && !light && !cancel && !progress && opts->samples_per_launch <= 0 &&
                         P.tile_ranks == 1 && !opts->accumulate && !opts->collect_stats && P.sample_end > P.sample_begin &&
-                        P.max_depth > 0 && P.tiles_y >= 12 && !(band_env && atoi(band_env) == 0) && !getenv("ZB_WAVEFRONT");
+                        P.max_depth > 0 && P.tiles_y >= 12 && band_env && atoi(band_env) > 0 && !getenv("ZB_WAVEFRONT");
     if (banded) {
         rc = render_banded(ctx, P, opts, out->beauty);
         if (rc) return rc;

@@ -5,6 +5,8 @@
 //   k_primary_ids K7: centre-of-pixel pinhole primary hit (camera.hpp:809-814 + :459).
 //   k_resolve     K5: sums -> means, float4 or the reference's double RGB.
 // Replaces render_rows (camera.hpp:430-554).  No tensor cores: nothing here is a dense contraction.
+#include <algorithm>
+
 #include "kernels.h"
 #include "shade.cuh"
 
@@ -251,6 +253,160 @@ __global__ void __launch_bounds__(ZB_BLOCK_THREADS, ZB_MIN_BLOCKS) k_render(cons
     }
 }
 
+// ---------------------------------------------------------------------------------------------------------------
+// k_render_pq — the beauty pass with a frame-wide path queue ("persistent queue" form of k_render<false,false>).
+// k_render binds a warp to one 8x4 sub-tile: when the sub-tile's queue runs dry the lanes of the warp go idle one by
+// one until the longest path ends, then the block ends and a new one starts.  That drain is paid once per sub-tile —
+// under 1 % of the work at 64 samples per pixel, 13 % at the 10 spp of config C1 and 9 % on each GPU of an 8-GPU
+// sample-slice frame (8 spp per GPU).  Here warps are persistent and take the frame's paths in batches of PQ_BATCH
+// consecutive indices from one global counter (same order: tile, sub-tile, pixel-major, sample), so lanes only run
+// dry at the end of the frame.  Lanes that need a path are served at the top of the segment loop, where the warp is
+// converged, by ballot rank from the warp's batch (registers, no shared-memory atomics).  Per-pixel sums are 64-bit
+// fixed-point RED.ADDs into a frame-sized buffer in L2 / HBM (same 2^-22 format as k_render's shared-memory sums, so
+// the frame is bit-identical and order-independent); k_pq_resolve turns them into the float4 accumulation buffer.
+#ifndef PQ_BATCH
+#define PQ_BATCH 256u
+#endif
+#ifndef PQ_MIN_BLOCKS
+#define PQ_MIN_BLOCKS ZB_MIN_BLOCKS
+#endif
+
+__global__ void __launch_bounds__(ZB_BLOCK_THREADS, PQ_MIN_BLOCKS) k_render_pq(const __grid_constant__ RenderParams P,
+                                                                                  unsigned long long* __restrict__ fix,
+                                                                                  unsigned long long* __restrict__ head,
+                                                                                  unsigned long long total) {
+    const unsigned lane = threadIdx.x & 31u, lt = (1u << lane) - 1u;
+    const uint32_t n_s = uint32_t(P.sample_end - P.sample_begin);
+    const Philox ph{P.seed_lo, P.seed_hi};
+    Counters cnt = {0, 0, 0, 0};
+    uint32_t paths = 0;
+    bool have = false, dry = false;
+    int seg = 0;
+    uint32_t pixel = 0, s = 0;
+    float3 o = f3(0, 0, 0), d = f3(0, 0, 1), L = f3(0, 0, 0), beta = f3(1, 1, 1);
+    unsigned long long w_pos = 0, w_end = 0;  // the warp's batch of path indices (warp-uniform)
+    for (;;) {
+        // ---- lanes without a path take the next ones of the warp's batch; out-of-image pixels are skipped
+        for (;;) {
+            const unsigned need = __ballot_sync(0xFFFFFFFFu, !have && !dry);
+            if (!need) break;
+            const unsigned want = __popc(need);
+            const unsigned long long avail = w_end - w_pos;
+            unsigned long long base2 = 0;
+            if (avail < want) {
+                // fixed batches: shrinking them towards the end of the frame ("guided" scheduling) was measured and
+                // cost more in the segment loop than the shorter tail returned (profiles/r01_pq.txt)
+                if (lane == 0) base2 = atomicAdd(head, (unsigned long long)PQ_BATCH);
+                base2 = __shfl_sync(0xFFFFFFFFu, base2, 0);
+            }
+            if (!have && !dry) {
+                const unsigned r = __popc(need & lt);
+                const unsigned long long g = r < avail ? w_pos + r : base2 + (r - avail);
+                if (g >= total) {
+                    dry = true;
+                } else {
+                    // g -> (sub-tile u, pixel p of the sub-tile, sample): pixel-major inside a sub-tile, as in k_render
+                    const unsigned long long per = 32ull * n_s;
+                    const uint32_t u = uint32_t(g / per), r2 = uint32_t(g - (unsigned long long)u * per);
+                    const uint32_t p = r2 / n_s, sr = r2 - p * n_s;
+                    const int tile = int(u >> 2) * P.tile_ranks + P.tile_rank, w = int(u & 3u);
+                    const int tx = tile % P.tiles_x, ty = tile / P.tiles_x;
+                    const int px = tx * ZB_TILE_W + (w % (ZB_TILE_W / 8)) * 8 + int(p & 7u);
+                    const int py = ty * ZB_TILE_H + (w / (ZB_TILE_W / 8)) * 4 + int(p >> 3);
+                    if (px < P.cam.width && py < P.cam.height && ty < P.tiles_y) {
+                        s = uint32_t(P.sample_begin) + sr;
+                        pixel = uint32_t(py) * uint32_t(P.cam.width) + uint32_t(px);
+                        // ---- K1 raygen: get_ray (camera.hpp:784-794), sample_square (:817), defocus disk (:822)
+                        const uint4 r0 = ph(pixel, s, 0u, 0u);
+                        d = P.cam.pix00_rel + (float(px) + u01(r0.x) - 0.5f) * P.cam.du + (float(py) + u01(r0.y) - 0.5f) * P.cam.dv;
+                        o = P.cam.center;
+                        if (P.cam.defocus) {
+                            float rr = sqrtf(u01(r0.z)), sn, cs;
+                            sincospif(2.0f * u01(r0.w), &sn, &cs);
+                            const float3 off = (rr * cs) * P.cam.disk_u + (rr * sn) * P.cam.disk_v;
+                            o += off;
+                            d = d - off;
+                        }
+                        seg = 0;
+                        L = f3(0, 0, 0);
+                        beta = f3(1, 1, 1);
+                        paths++;
+                        have = true;
+                    }
+                }
+            }
+            if (avail < want) {
+                w_pos = base2 + (want - avail);
+                w_end = base2 + PQ_BATCH;
+            } else {
+                w_pos += want;
+            }
+        }
+        if (!__any_sync(0xFFFFFFFFu, have)) break;
+        if (have) {
+            Hit hit;
+            {
+                MediumRng mr{ph, pixel, s, uint32_t(seg + 1)};
+                trace<false>(P.sc, o, d, 0.001f, INFINITY, mr, hit, cnt);
+            }
+            // ---- K3 shade: one segment of ray_color (camera.hpp:928-1004), as in k_render
+            bool done;
+            if (hit.item == 0xFFFFFFFFu) {
+                L += beta * background(P.sc, P.env, d);
+                done = true;
+            } else {
+                Surface sf;
+                make_surface(P.sc, hit, o, d, sf);
+                L += beta * material_emitted(P.sc, sf);
+                const uint4 rb = ph(pixel, s, uint32_t(seg + 1), 0u);
+                float3 atten = f3(1, 1, 1), no, nd;
+                done = !material_scatter(P.sc, sf, d, f3(u01(rb.x), u01(rb.y), u01(rb.z)), atten, no, nd);
+                if (!done) {
+                    beta *= atten;
+                    o = no;
+                    d = nd;
+                    if (seg >= 12) {  // camera.hpp:968-983
+                        const float pr = fminf(fmaxf(max3(beta.x, beta.y, beta.z), 0.05f), 0.95f);
+                        if (dot(beta, beta) < 1e-8f || u01(rb.w) > pr) done = true;
+                        beta *= 1.0f / pr;
+                    }
+                    if (++seg >= P.max_depth) done = true;
+                }
+            }
+            if (done) {  // K5 accumulate
+                unsigned long long* f = fix + 3 * size_t(pixel);
+                atomicAdd(f + 0, __float2ull_rn(fmaxf(L.x, 0.f) * ZB_FIX_SCALE));
+                atomicAdd(f + 1, __float2ull_rn(fmaxf(L.y, 0.f) * ZB_FIX_SCALE));
+                atomicAdd(f + 2, __float2ull_rn(fmaxf(L.z, 0.f) * ZB_FIX_SCALE));
+                have = false;
+            }
+        }
+    }
+    uint32_t v[2] = {cnt.rays, paths};
+#pragma unroll
+    for (int k = 0; k < 2; k++) {
+        const uint32_t x = __reduce_add_sync(0xFFFFFFFFu, v[k]);
+        if (lane == 0 && x) atomicAdd(P.counters + (k ? 4 : 0), (unsigned long long)x);
+    }
+}
+
+// fixed-point frame sums of k_render_pq -> the float4 accumulation buffer (xyz sums, w = samples) for this rank's tiles
+__global__ void __launch_bounds__(256) k_pq_resolve(const __grid_constant__ RenderParams P, const unsigned long long* __restrict__ fix) {
+    const int px = blockIdx.x * 64 + (threadIdx.x & 63), py = blockIdx.y * 4 + (threadIdx.x >> 6);
+    if (px >= P.cam.width || py >= P.cam.height) return;
+    if (P.tile_ranks > 1) {  // tile stripes: the other ranks' pixels stay untouched
+        const int tile = (py / ZB_TILE_H) * P.tiles_x + px / ZB_TILE_W;
+        if (tile % P.tile_ranks != P.tile_rank) return;
+    }
+    const size_t i = size_t(py) * P.cam.width + px;
+    float4 a = make_float4(fix_get(fix[3 * i]), fix_get(fix[3 * i + 1]), fix_get(fix[3 * i + 2]), float(P.sample_end - P.sample_begin));
+    if (P.accumulate) {
+        const float4 old = P.accum[i];
+        a.x += old.x; a.y += old.y; a.z += old.z; a.w += old.w;
+    }
+    P.accum[i] = a;
+}
+
 __global__ void __launch_bounds__(128) k_primary_ids(const __grid_constant__ RenderParams P, uint32_t* leaf_id,
                                                      uint32_t* prim_id, float* t_out) {
     const int idx = blockIdx.x * blockDim.x + threadIdx.x;
@@ -340,6 +496,22 @@ cudaError_t zbk_launch_render(const RenderParams& P, int n_tiles_owned, bool sta
     if (P.light_pass) k_render<false, true><<<n_tiles_owned, ZB_BLOCK_THREADS, 0, stream>>>(P);
     else if (stats) k_render<true, false><<<n_tiles_owned, ZB_BLOCK_THREADS, 0, stream>>>(P);
     else k_render<false, false><<<n_tiles_owned, ZB_BLOCK_THREADS, 0, stream>>>(P);
+    return cudaGetLastError();
+}
+
+cudaError_t zbk_launch_render_pq(const RenderParams& P, int n_tiles_owned, unsigned long long* fix, unsigned long long* head,
+                                 int sm_count, cudaStream_t stream) {
+    if (n_tiles_owned <= 0) return cudaSuccess;
+    const size_t pixels = size_t(P.cam.width) * P.cam.height;
+    const unsigned long long total = (unsigned long long)n_tiles_owned * 4ull * 32ull * (unsigned long long)(P.sample_end - P.sample_begin);
+    cudaError_t e = cudaMemsetAsync(fix, 0, pixels * 3 * sizeof(unsigned long long), stream);
+    if (e != cudaSuccess) return e;
+    e = cudaMemsetAsync(head, 0, sizeof(unsigned long long), stream);
+    if (e != cudaSuccess) return e;
+    const unsigned long long warps_needed = (total + 31) / 32;
+    const unsigned blocks = unsigned(std::min<unsigned long long>((unsigned long long)sm_count * PQ_MIN_BLOCKS, (warps_needed + 3) / 4));
+    k_render_pq<<<blocks, ZB_BLOCK_THREADS, 0, stream>>>(P, fix, head, total);
+    k_pq_resolve<<<dim3((P.cam.width + 63) / 64, (P.cam.height + 3) / 4), 256, 0, stream>>>(P, fix);
     return cudaGetLastError();
 }
 

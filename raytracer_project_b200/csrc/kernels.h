@@ -7,6 +7,9 @@
 #include "scene_dev.cuh"
 
 cudaError_t zbk_launch_render(const RenderParams& P, int n_tiles_owned, bool stats, cudaStream_t stream);
+// beauty pass with a frame-wide path queue (k_render_pq): fix = W*H*3 u64 scratch, head = one u64 counter
+cudaError_t zbk_launch_render_pq(const RenderParams& P, int n_tiles_owned, unsigned long long* fix, unsigned long long* head,
+                                 int sm_count, cudaStream_t stream);
 cudaError_t zbk_launch_primary_ids(const RenderParams& P, uint32_t* leaf_id, uint32_t* prim_id, float* t,
                                    cudaStream_t stream);
 cudaError_t zbk_launch_resolve(const float4* accum, size_t n, float scale, float4* out_f4, double* out_f64,
