@@ -267,11 +267,12 @@ __global__ void __launch_bounds__(ZB_BLOCK_THREADS, ZB_MIN_BLOCKS) k_render(cons
 #ifndef PQ_BATCH
 #define PQ_BATCH 256u
 #endif
-#ifndef PQ_MIN_BLOCKS
-#define PQ_MIN_BLOCKS ZB_MIN_BLOCKS
-#endif
+// resident blocks per SM: 6 (80 registers) for scenes whose tree lives in L1 / L2, 7 (72 registers) when the tree is
+// large enough for memory latency to dominate (measured: 1 M-triangle mesh +6 %, Weekend -1 %, quirks -6 %)
+#define PQ_BIG_TREE_NODES 65536u
 
-__global__ void __launch_bounds__(ZB_BLOCK_THREADS, PQ_MIN_BLOCKS) k_render_pq(const __grid_constant__ RenderParams P,
+template <int MIN_BLOCKS>
+__global__ void __launch_bounds__(ZB_BLOCK_THREADS, MIN_BLOCKS) k_render_pq(const __grid_constant__ RenderParams P,
                                                                                   unsigned long long* __restrict__ fix,
                                                                                   unsigned long long* __restrict__ head,
                                                                                   unsigned long long total) {
@@ -509,8 +510,10 @@ cudaError_t zbk_launch_render_pq(const RenderParams& P, int n_tiles_owned, unsig
     e = cudaMemsetAsync(head, 0, sizeof(unsigned long long), stream);
     if (e != cudaSuccess) return e;
     const unsigned long long warps_needed = (total + 31) / 32;
-    const unsigned blocks = unsigned(std::min<unsigned long long>((unsigned long long)sm_count * PQ_MIN_BLOCKS, (warps_needed + 3) / 4));
-    k_render_pq<<<blocks, ZB_BLOCK_THREADS, 0, stream>>>(P, fix, head, total);
+    const int per_sm = P.sc.n_nodes >= PQ_BIG_TREE_NODES ? 7 : 6;
+    const unsigned blocks = unsigned(std::min<unsigned long long>((unsigned long long)sm_count * per_sm, (warps_needed + 3) / 4));
+    if (per_sm == 7) k_render_pq<7><<<blocks, ZB_BLOCK_THREADS, 0, stream>>>(P, fix, head, total);
+    else k_render_pq<6><<<blocks, ZB_BLOCK_THREADS, 0, stream>>>(P, fix, head, total);
     k_pq_resolve<<<dim3((P.cam.width + 63) / 64, (P.cam.height + 3) / 4), 256, 0, stream>>>(P, fix);
     return cudaGetLastError();
 }

@@ -656,3 +656,35 @@ def test_bvh_debug_view_levels_use_the_reference_palette(gpu_ctx, tmp_path):
             img = _wire_mean(sc2, cfg2, level, 0.05)
             assert np.isfinite(img).all() and (img[..., 2] > 1.0).mean() > 0.001, (name, level)
         sc2.close()
+
+
+@pytest.mark.parametrize("name", ["weekend", "big_mesh"] + list(GOLDEN_SCENES))
+def test_path_queue_kernel_equals_tile_kernel(name, gpu_ctx, tmp_path, weekend_scene, monkeypatch):
+    """k_render_pq (frame-wide path queue, the default beauty kernel) against k_render (tile-bound warps, ZB_PQ=0): the
+    same Philox keys, shading code and 64-bit fixed-point sums, so the frames are equal bit for bit — also under
+    tile stripes, sample slices with accumulation, a ragged image edge and a tree big enough for the 7-blocks-per-SM
+    instantiation."""
+    if name == "weekend":
+        sc, cfg = weekend_scene, scenes.weekend(seed=1, width=203, height=90, spp=24)[1]
+    elif name == "big_mesh":
+        txt, cfg, files = scenes.mesh(width=160, height=90, spp=8, grid=400, knots=2)
+        flat = api.flatten_zscene(path=scenes.materialize(str(tmp_path), txt, cfg, files))
+        assert flat.contents.n_nodes >= 65536
+        sc = gpu_ctx.upload(flat)
+        api.free_flat(flat)
+    else:
+        _, _, _, wh, _ = GOLDEN_SCENES[name]
+        sc, cfg, _ = _load_scene(gpu_ctx, tmp_path, name, wh, 24)
+    monkeypatch.setenv("ZB_PQ", "0")
+    a = sc.render(cfg, seed=5)["beauty"]
+    a_tiles = [sc.render(cfg, seed=5, tile=(r, 3))["beauty"] for r in range(3)]
+    monkeypatch.delenv("ZB_PQ")
+    b = sc.render(cfg, seed=5)["beauty"]
+    b_tiles = [sc.render(cfg, seed=5, tile=(r, 3))["beauty"] for r in range(3)]
+    c = sc.render(cfg, seed=5, samples_per_launch=5)["beauty"]
+    if name != "weekend":
+        sc.close()
+    assert np.array_equal(a, b), np.abs(a - b).max()
+    for r in range(3):
+        assert np.array_equal(a_tiles[r], b_tiles[r]), r
+    assert np.allclose(b, c, rtol=2e-6, atol=1e-7)
