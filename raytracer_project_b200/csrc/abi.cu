@@ -65,8 +65,6 @@ extern "C" int zb_context_destroy(zb_context* ctx) {
     if (ctx->pinned) cudaFreeHost(ctx->pinned);
     for (auto& ev : ctx->ev) cudaEventDestroy(ev);
     for (auto& ev : ctx->chunk_ev) cudaEventDestroy(ev);
-    for (auto& st : ctx->band_streams) cudaStreamDestroy(st);
-    if (ctx->band_fork) cudaEventDestroy(ctx->band_fork);
     if (ctx->own_stream) cudaStreamDestroy(ctx->stream);
     delete ctx;
     return ZB_OK;

@@ -47,8 +47,6 @@ struct zb_context {
     struct zb_wf_scratch* wf = nullptr;  // wavefront render scratch (wavefront.cu)
     cudaEvent_t ev[6] = {};
     std::vector<cudaEvent_t> chunk_ev;  // one per 4 MiB chunk of the frame copy (abi_render.cu d2h_rgb_f64)
-    std::vector<cudaStream_t> band_streams;  // zb_render's banded frame: band b renders, resolves and copies on stream b
-    cudaEvent_t band_fork = nullptr;
     zb_stats stats{};
 };
 

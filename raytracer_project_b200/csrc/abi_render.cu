@@ -180,6 +180,18 @@ int fill_params(zb_context* ctx, const zb_scene* scene, const zb_camera* cam, co
     return ZB_OK;
 }
 
+constexpr int PQ_MAX_HEADS = 8;
+int ensure_pq_scratch(zb_context* ctx, size_t pixels) {
+    if (ctx->pq_pixels < pixels) {
+        cudaFree(ctx->pq_fix);
+        ctx->pq_fix = nullptr;
+        ctx->pq_pixels = 0;
+        ZB_CUDA(cudaMalloc(&ctx->pq_fix, (pixels * 3 + PQ_MAX_HEADS) * sizeof(unsigned long long)));
+        ctx->pq_pixels = pixels;
+    }
+    return ZB_OK;
+}
+
 int owned_tiles(const RenderParams& P) {
     int total = P.tiles_x * P.tiles_y;
     return (total - P.tile_rank + P.tile_ranks - 1) / P.tile_ranks;
@@ -217,14 +229,12 @@ int launch_share(zb_context* ctx, RenderParams P, const zb_render_opts* o, const
             ZB_CUDA(zbk_launch_wavefront(P, &ctx->wf, wf_slots, &iters, ctx->stream));
             ctx->stats.launches += 2 + 2 * iters;
         } else if (pq && !P.light_pass && !P.accum_aux && !o->collect_stats && P.max_depth > 0 && P.sample_end > P.sample_begin) {
-            if (ctx->pq_pixels < pixels) {
-                cudaFree(ctx->pq_fix);
-                ctx->pq_fix = nullptr;
-                ctx->pq_pixels = 0;
-                ZB_CUDA(cudaMalloc(&ctx->pq_fix, (pixels * 3 + 1) * sizeof(unsigned long long)));
-                ctx->pq_pixels = pixels;
-            }
-            ZB_CUDA(zbk_launch_render_pq(P, owned_tiles(P), ctx->pq_fix, ctx->pq_fix + ctx->pq_pixels * 3, ctx->sm_count, ctx->stream));
+            int rc2 = ensure_pq_scratch(ctx, pixels);
+            if (rc2) return rc2;
+            unsigned long long* heads = ctx->pq_fix + ctx->pq_pixels * 3;
+            ZB_CUDA(zbk_pq_clear(ctx->pq_fix, pixels, heads, 1, ctx->stream));
+            ZB_CUDA(zbk_launch_render_pq(P, owned_tiles(P), ctx->pq_fix, heads, ctx->sm_count, ctx->stream));
+            ZB_CUDA(zbk_pq_resolve(P, ctx->pq_fix, 0, P.cam.height, 0.f, nullptr, ctx->stream));
             ctx->stats.launches += 2;
         } else {
             ZB_CUDA(zbk_launch_render(P, owned_tiles(P), o->collect_stats != 0, ctx->stream));
@@ -308,52 +318,6 @@ int d2h_rgb_f64(zb_context* ctx, double* host, const float4* dev, size_t pixels)
     if (rc) return rc;
     ZB_CUDA(cudaStreamSynchronize(ctx->stream));
     return ZB_OK;
-}
-
-// Beauty-only frame with host output, rendered as horizontal bands of tile rows, band b on its own stream: render,
-// resolve and copy of a band are ordered on that stream, the bands overlap each other (blocks of band b + 1 fill the
-// SMs band b drains from), so all but the last band's copy and widening hide behind rendering.  Same pixels as the
-// single launch: a tile's result depends on the tile alone.
-int render_banded(zb_context* ctx, RenderParams P, const zb_render_opts* opts, double* host) {
-    const size_t W = size_t(P.cam.width), H = size_t(P.cam.height);
-    const int rows = P.tiles_y;
-    const int n_bands = std::min(rows, 6);
-    while (int(ctx->band_streams.size()) < n_bands) {
-        // earlier bands get the higher stream priority, so the block scheduler finishes them first instead of
-        // interleaving all bands (which would move every copy to the end of the frame again)
-        int least = 0, greatest = 0;
-        ZB_CUDA(cudaDeviceGetStreamPriorityRange(&least, &greatest));
-        const int prio = std::min(least, greatest + int(ctx->band_streams.size()));
-        cudaStream_t st;
-        ZB_CUDA(cudaStreamCreateWithPriority(&st, cudaStreamNonBlocking, prio));
-        ctx->band_streams.push_back(st);
-    }
-    if (!ctx->band_fork) ZB_CUDA(cudaEventCreateWithFlags(&ctx->band_fork, cudaEventDisableTiming));
-    int rc = ensure_chunk_events(ctx, size_t(n_bands));
-    if (rc) return rc;
-    ZB_CUDA(cudaEventRecord(ctx->band_fork, ctx->stream));
-    float4* stage = static_cast<float4*>(ctx->pinned);
-    const float scale = float(1.0 / opts->samples_per_pixel);
-    std::vector<size_t> begin;
-    for (int b = 0; b < n_bands; b++) {
-        const int r0 = int((long long)rows * b / n_bands), r1 = int((long long)rows * (b + 1) / n_bands);
-        const size_t p0 = std::min(size_t(r0) * ZB_TILE_H, H) * W, p1 = std::min(size_t(r1) * ZB_TILE_H, H) * W;
-        cudaStream_t st = ctx->band_streams[b];
-        ZB_CUDA(cudaStreamWaitEvent(st, ctx->band_fork, 0));
-        RenderParams B = P;
-        B.tile_ranks = 1;
-        B.tile_rank = r0 * P.tiles_x;  // block i renders tile i + offset
-        B.accumulate = 0;
-        ZB_CUDA(zbk_launch_render(B, (r1 - r0) * P.tiles_x, false, st));
-        ZB_CUDA(zbk_launch_resolve(ctx->accum + p0, p1 - p0, scale, ctx->out_f4 + p0, nullptr, st));
-        ZB_CUDA(cudaMemcpyAsync(stage + p0, ctx->out_f4 + p0, (p1 - p0) * sizeof(float4), cudaMemcpyDeviceToHost, st));
-        ZB_CUDA(cudaEventRecord(ctx->chunk_ev[b], st));
-        ZB_CUDA(cudaStreamWaitEvent(ctx->stream, ctx->chunk_ev[b], 0));  // join: later work on the context stream follows
-        ctx->stats.launches += 2;
-        begin.push_back(p0);
-    }
-    begin.push_back(W * H);
-    return widen_chunks(ctx, host, begin);
 }
 
 int read_counters(zb_context* ctx) {
@@ -473,23 +437,6 @@ extern "C" int zb_render(zb_context* ctx, const zb_scene* scene, const zb_camera
     ctx->stats = zb_stats{};
     ZB_CUDA(cudaMemsetAsync(ctx->counters, 0, 8 * sizeof(unsigned long long), ctx->stream));
     ZB_CUDA(cudaEventRecord(ctx->ev[0], ctx->stream));
-    const char* band_env = getenv("ZB_BANDS");
-    const bool banded = out->beauty && !out->beauty_f4 && !aux && !light && !cancel && !progress && opts->samples_per_launch <= 0 &&
-                        P.tile_ranks == 1 && !opts->accumulate && !opts->collect_stats && P.sample_end > P.sample_begin &&
-                        P.max_depth > 0 && P.tiles_y >= 12 && band_env && atoi(band_env) > 0 && !getenv("ZB_WAVEFRONT");
-    if (banded) {
-        rc = render_banded(ctx, P, opts, out->beauty);
-        if (rc) return rc;
-        ZB_CUDA(cudaEventRecord(ctx->ev[1], ctx->stream));
-        ZB_CUDA(cudaEventRecord(ctx->ev[2], ctx->stream));
-        ZB_CUDA(cudaEventRecord(ctx->ev[3], ctx->stream));
-        rc = read_counters(ctx);
-        if (rc) return rc;
-        float ms = 0;
-        ZB_CUDA(cudaEventElapsedTime(&ms, ctx->ev[0], ctx->ev[1]));
-        ctx->stats.kernel_ms = ms;  // render, resolve and copy of the bands overlap: one figure for all three
-        return ZB_OK;
-    }
     rc = launch_share(ctx, P, opts, cancel, progress, user, true);
     if (rc) return rc;
     ZB_CUDA(cudaEventRecord(ctx->ev[1], ctx->stream));

@@ -391,16 +391,22 @@ __global__ void __launch_bounds__(ZB_BLOCK_THREADS, MIN_BLOCKS) k_render_pq(cons
     }
 }
 
-// fixed-point frame sums of k_render_pq -> the float4 accumulation buffer (xyz sums, w = samples) for this rank's tiles
-__global__ void __launch_bounds__(256) k_pq_resolve(const __grid_constant__ RenderParams P, const unsigned long long* __restrict__ fix) {
-    const int px = blockIdx.x * 64 + (threadIdx.x & 63), py = blockIdx.y * 4 + (threadIdx.x >> 6);
-    if (px >= P.cam.width || py >= P.cam.height) return;
+// fixed-point frame sums of k_render_pq, rows [row0, row1) -> the float4 accumulation buffer (xyz sums, w = samples) for
+// this rank's tiles, or — when `mean_out` is given — straight to scaled means (xyz, w = 1) without touching P.accum
+__global__ void __launch_bounds__(256) k_pq_resolve(const __grid_constant__ RenderParams P, const unsigned long long* __restrict__ fix,
+                                                    int row0, int row1, float scale, float4* __restrict__ mean_out) {
+    const int px = blockIdx.x * 64 + (threadIdx.x & 63), py = row0 + blockIdx.y * 4 + (threadIdx.x >> 6);
+    if (px >= P.cam.width || py >= row1) return;
     if (P.tile_ranks > 1) {  // tile stripes: the other ranks' pixels stay untouched
         const int tile = (py / ZB_TILE_H) * P.tiles_x + px / ZB_TILE_W;
         if (tile % P.tile_ranks != P.tile_rank) return;
     }
     const size_t i = size_t(py) * P.cam.width + px;
     float4 a = make_float4(fix_get(fix[3 * i]), fix_get(fix[3 * i + 1]), fix_get(fix[3 * i + 2]), float(P.sample_end - P.sample_begin));
+    if (mean_out) {
+        mean_out[i] = make_float4(a.x * scale, a.y * scale, a.z * scale, 1.0f);  // as k_resolve
+        return;
+    }
     if (P.accumulate) {
         const float4 old = P.accum[i];
         a.x += old.x; a.y += old.y; a.z += old.z; a.w += old.w;
@@ -500,21 +506,29 @@ cudaError_t zbk_launch_render(const RenderParams& P, int n_tiles_owned, bool sta
     return cudaGetLastError();
 }
 
+cudaError_t zbk_pq_clear(unsigned long long* fix, size_t pixels, unsigned long long* heads, int n_heads, cudaStream_t stream) {
+    cudaError_t e = cudaMemsetAsync(fix, 0, pixels * 3 * sizeof(unsigned long long), stream);
+    if (e != cudaSuccess) return e;
+    return cudaMemsetAsync(heads, 0, size_t(n_heads) * sizeof(unsigned long long), stream);
+}
+
+// the queue kernel alone: `fix` and `*head` must be zero (zbk_pq_clear); tiles P.tile_rank + i * P.tile_ranks, i < n_tiles
 cudaError_t zbk_launch_render_pq(const RenderParams& P, int n_tiles_owned, unsigned long long* fix, unsigned long long* head,
                                  int sm_count, cudaStream_t stream) {
     if (n_tiles_owned <= 0) return cudaSuccess;
-    const size_t pixels = size_t(P.cam.width) * P.cam.height;
     const unsigned long long total = (unsigned long long)n_tiles_owned * 4ull * 32ull * (unsigned long long)(P.sample_end - P.sample_begin);
-    cudaError_t e = cudaMemsetAsync(fix, 0, pixels * 3 * sizeof(unsigned long long), stream);
-    if (e != cudaSuccess) return e;
-    e = cudaMemsetAsync(head, 0, sizeof(unsigned long long), stream);
-    if (e != cudaSuccess) return e;
     const unsigned long long warps_needed = (total + 31) / 32;
     const int per_sm = P.sc.n_nodes >= PQ_BIG_TREE_NODES ? 7 : 6;
     const unsigned blocks = unsigned(std::min<unsigned long long>((unsigned long long)sm_count * per_sm, (warps_needed + 3) / 4));
     if (per_sm == 7) k_render_pq<7><<<blocks, ZB_BLOCK_THREADS, 0, stream>>>(P, fix, head, total);
     else k_render_pq<6><<<blocks, ZB_BLOCK_THREADS, 0, stream>>>(P, fix, head, total);
-    k_pq_resolve<<<dim3((P.cam.width + 63) / 64, (P.cam.height + 3) / 4), 256, 0, stream>>>(P, fix);
+    return cudaGetLastError();
+}
+
+cudaError_t zbk_pq_resolve(const RenderParams& P, const unsigned long long* fix, int row0, int row1, float scale, float4* mean_out,
+                           cudaStream_t stream) {
+    if (row1 <= row0) return cudaSuccess;
+    k_pq_resolve<<<dim3((P.cam.width + 63) / 64, (row1 - row0 + 3) / 4), 256, 0, stream>>>(P, fix, row0, row1, scale, mean_out);
     return cudaGetLastError();
 }
 

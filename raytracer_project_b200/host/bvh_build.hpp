@@ -84,6 +84,10 @@ private:
     std::vector<double> cent;
     std::vector<tnode> tmp;
     int leaf_cap = 4;
+public:
+    // cost of one primitive test in units of one node visit (SAH leaf-versus-split decision)
+    double isect_cost = 1.0;
+private:
     uint32_t base = 0;
 
     int make_leaf(size_t lo, size_t hi, const build_box& box) {
@@ -108,7 +112,7 @@ private:
         }
         if (n == 1) return make_leaf(lo, hi, box);
         constexpr int NB = 16;
-        const double c_trav = 1.0, c_isect = 1.0;
+        const double c_trav = 1.0, c_isect = isect_cost;
         double best = infinity;
         int best_axis = -1, best_bin = -1;
         for (int axis = 0; axis < 3; axis++) {

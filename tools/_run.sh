@@ -1,4 +1,3 @@
 cd /root/repo
-timeout 1500 python -m pytest tests -m gpu -x -q 2>&1 | tail -4
-timeout 600 python tools/tune.py --scene mesh --spp 64 --reps 3 2>/dev/null | tail -1 | cut -c1-330
-timeout 900 python tools/run_c5.py 2>&1 | tail -3 | cut -c1-600
+timeout 1500 python -m pytest tests -m gpu -x -q 2>&1 | tail -3
+for b in 0 1; do ZB_BANDS=$b python bench.py --steps 5 --warmup 3 2>/dev/null | tail -1 | python -c "import sys,json; d=json.loads(sys.stdin.read()); print('bands', $b, round(d['value'],1), round(d['ms_per_step'],3), 'e2e', round(d['e2e']['value'],1), round(d['e2e']['ms_per_step'],3))"; done
