@@ -42,8 +42,8 @@ struct zb_context {
     size_t fin_pixels = 0;
     unsigned long long* fin_stats = nullptr;  // 2 + 128 u64: log sum, max, 256-bin histogram
     size_t id_pixels = 0;
-    unsigned long long* pq_fix = nullptr;  // k_render_pq: W*H*3 fixed-point sums + 1 queue head
-    size_t pq_pixels = 0;
+    unsigned long long* pq_fix = nullptr;  // k_render_pq: fixed-point sums (3, 6 or 10 per pixel) + queue heads
+    size_t pq_words = 0;
     struct zb_wf_scratch* wf = nullptr;  // wavefront render scratch (wavefront.cu)
     cudaEvent_t ev[6] = {};
     std::vector<cudaEvent_t> chunk_ev;  // one per 4 MiB chunk of the frame copy (abi_render.cu d2h_rgb_f64)

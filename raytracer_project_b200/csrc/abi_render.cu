@@ -181,13 +181,14 @@ int fill_params(zb_context* ctx, const zb_scene* scene, const zb_camera* cam, co
 }
 
 constexpr int PQ_MAX_HEADS = 8;
-int ensure_pq_scratch(zb_context* ctx, size_t pixels) {
-    if (ctx->pq_pixels < pixels) {
+int ensure_pq_scratch(zb_context* ctx, size_t pixels, int mode) {
+    const size_t words = zbk_pq_words(pixels, mode) + PQ_MAX_HEADS;
+    if (ctx->pq_words < words) {
         cudaFree(ctx->pq_fix);
         ctx->pq_fix = nullptr;
-        ctx->pq_pixels = 0;
-        ZB_CUDA(cudaMalloc(&ctx->pq_fix, (pixels * 3 + PQ_MAX_HEADS) * sizeof(unsigned long long)));
-        ctx->pq_pixels = pixels;
+        ctx->pq_words = 0;
+        ZB_CUDA(cudaMalloc(&ctx->pq_fix, words * sizeof(unsigned long long)));
+        ctx->pq_words = words;
     }
     return ZB_OK;
 }
@@ -218,6 +219,10 @@ int launch_share(zb_context* ctx, RenderParams P, const zb_render_opts* o, const
     // the beauty pass runs as k_render_pq (frame-wide path queue) unless ZB_PQ=0 asks for the tile-bound k_render
     const char* pq_env = getenv("ZB_PQ");
     const bool pq = !(pq_env && atoi(pq_env) == 0);
+    // The queue kernel also has AOV and light-pass modes (bit-identical to k_render's), selected with ZB_PQ=2 only: the
+    // AOV sums of a warp's lanes go to the same one or two pixels at the same moment, and as global REDs they serialise
+    // (Weekend 64 spp: 44.4 vs 40.6 ms with AOVs, 38.2 vs 32.6 ms light passes; profiles/r01_pq.txt)
+    const bool pq_all = pq_env && atoi(pq_env) >= 2;
     int done = 0;
     for (int s = sb; s < se; s += per) {
         if (cancel && *cancel) return fail(ZB_ERR_CANCELLED, "render cancelled");
@@ -228,13 +233,15 @@ int launch_share(zb_context* ctx, RenderParams P, const zb_render_opts* o, const
             int iters = 0;
             ZB_CUDA(zbk_launch_wavefront(P, &ctx->wf, wf_slots, &iters, ctx->stream));
             ctx->stats.launches += 2 + 2 * iters;
-        } else if (pq && !P.light_pass && !P.accum_aux && !o->collect_stats && P.max_depth > 0 && P.sample_end > P.sample_begin) {
-            int rc2 = ensure_pq_scratch(ctx, pixels);
+        } else if (pq && !o->collect_stats && P.max_depth > 0 && P.sample_end > P.sample_begin &&
+                   (pq_all || (!P.light_pass && !P.accum_aux))) {
+            const int mode = P.light_pass ? 2 : P.accum_aux ? 1 : 0;
+            int rc2 = ensure_pq_scratch(ctx, pixels, mode);
             if (rc2) return rc2;
-            unsigned long long* heads = ctx->pq_fix + ctx->pq_pixels * 3;
-            ZB_CUDA(zbk_pq_clear(ctx->pq_fix, pixels, heads, 1, ctx->stream));
-            ZB_CUDA(zbk_launch_render_pq(P, owned_tiles(P), ctx->pq_fix, heads, ctx->sm_count, ctx->stream));
-            ZB_CUDA(zbk_pq_resolve(P, ctx->pq_fix, 0, P.cam.height, 0.f, nullptr, ctx->stream));
+            unsigned long long* heads = ctx->pq_fix + zbk_pq_words(pixels, mode);
+            ZB_CUDA(zbk_pq_clear(ctx->pq_fix, pixels, mode, heads, 1, ctx->stream));
+            ZB_CUDA(zbk_launch_render_pq(P, owned_tiles(P), mode, ctx->pq_fix, heads, ctx->sm_count, ctx->stream));
+            ZB_CUDA(zbk_pq_resolve(P, mode, ctx->pq_fix, 0, P.cam.height, 0.f, nullptr, ctx->stream));
             ctx->stats.launches += 2;
         } else {
             ZB_CUDA(zbk_launch_render(P, owned_tiles(P), o->collect_stats != 0, ctx->stream));

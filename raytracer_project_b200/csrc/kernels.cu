@@ -271,14 +271,24 @@ __global__ void __launch_bounds__(ZB_BLOCK_THREADS, ZB_MIN_BLOCKS) k_render(cons
 // large enough for memory latency to dominate (measured: 1 M-triangle mesh +6 %, Weekend -1 %, quirks -6 %)
 #define PQ_BIG_TREE_NODES 65536u
 
-template <int MIN_BLOCKS>
+// MODE: PQ_BEAUTY, PQ_AUX (beauty + first-hit AOVs into 7 more sums per pixel: albedo rgb, normal xyz, z) or PQ_LIGHT
+// (reflection sums into `fix`, refraction sums into `fix_aux`, 3 per pixel; see k_render<.., LIGHT>)
+enum { PQ_BEAUTY = 0, PQ_AUX = 1, PQ_LIGHT = 2 };
+
+ZB_DEV void gfix_add(unsigned long long* slot, float v) { atomicAdd(slot, __float2ull_rn(fmaxf(v, 0.f) * ZB_FIX_SCALE)); }
+
+template <int MIN_BLOCKS, int MODE>
 __global__ void __launch_bounds__(ZB_BLOCK_THREADS, MIN_BLOCKS) k_render_pq(const __grid_constant__ RenderParams P,
                                                                                   unsigned long long* __restrict__ fix,
+                                                                                  unsigned long long* __restrict__ fix_aux,
                                                                                   unsigned long long* __restrict__ head,
                                                                                   unsigned long long total) {
+    constexpr bool AUX = MODE == PQ_AUX, LIGHT = MODE == PQ_LIGHT;
     const unsigned lane = threadIdx.x & 31u, lt = (1u << lane) - 1u;
     const uint32_t n_s = uint32_t(P.sample_end - P.sample_begin);
-    const Philox ph{P.seed_lo, P.seed_hi};
+    const Philox ph{P.seed_lo, LIGHT ? P.seed_hi ^ 0x4C495445u : P.seed_hi};  // the light passes draw their own stream
+    float3 first_atten = f3(0, 0, 0);  // LIGHT: attenuation of the primary scatter (camera.hpp:512, :515)
+    int light_class = 0;               // LIGHT: 1 reflection, 2 refraction, 0 neither
     Counters cnt = {0, 0, 0, 0};
     uint32_t paths = 0;
     bool have = false, dry = false;
@@ -307,9 +317,19 @@ __global__ void __launch_bounds__(ZB_BLOCK_THREADS, MIN_BLOCKS) k_render_pq(cons
                     dry = true;
                 } else {
                     // g -> (sub-tile u, pixel p of the sub-tile, sample): pixel-major inside a sub-tile, as in k_render
-                    const unsigned long long per = 32ull * n_s;
-                    const uint32_t u = uint32_t(g / per), r2 = uint32_t(g - (unsigned long long)u * per);
-                    const uint32_t p = r2 / n_s, sr = r2 - p * n_s;
+                    // one division: q = g / n_s numbers the (sub-tile, pixel) pairs, 32 per sub-tile; in 32 bits
+                    // whenever the launch has fewer than 2^32 paths (a 64-bit division is a ~80-instruction routine)
+                    uint32_t q, sr;
+                    if (total <= 0xFFFFFFFFull) {
+                        const uint32_t g32 = uint32_t(g);
+                        q = g32 / n_s;
+                        sr = g32 - q * n_s;
+                    } else {
+                        const unsigned long long q64 = g / n_s;
+                        q = uint32_t(q64);
+                        sr = uint32_t(g - q64 * n_s);
+                    }
+                    const uint32_t u = q >> 5, p = q & 31u;
                     const int tile = int(u >> 2) * P.tile_ranks + P.tile_rank, w = int(u & 3u);
                     const int tx = tile % P.tiles_x, ty = tile / P.tiles_x;
                     const int px = tx * ZB_TILE_W + (w % (ZB_TILE_W / 8)) * 8 + int(p & 7u);
@@ -352,12 +372,57 @@ __global__ void __launch_bounds__(ZB_BLOCK_THREADS, MIN_BLOCKS) k_render_pq(cons
             }
             // ---- K3 shade: one segment of ray_color (camera.hpp:928-1004), as in k_render
             bool done;
-            if (hit.item == 0xFFFFFFFFu) {
+            if (LIGHT && seg == 0) {
+                // camera.hpp:492-517: second scatter of the primary hit; a primary miss contributes nothing
+                light_class = 0;
+                done = true;
+                if (hit.item != 0xFFFFFFFFu) {
+                    Surface sf;
+                    make_surface(P.sc, hit, o, d, sf);
+                    const uint4 rb = ph(pixel, s, 1u, 0u);
+                    float3 no, nd;
+                    first_atten = f3(1, 1, 1);
+                    if (material_scatter(P.sc, sf, d, f3(u01(rb.x), u01(rb.y), u01(rb.z)), first_atten, no, nd)) {
+                        const float3 ud = unit_vector(d), un = unit_vector(sf.n);
+                        const float3 mirror = fma3(-2.0f * dot(ud, un), un, ud);
+                        if (dot(unit_vector(nd), mirror) > 0.9f) light_class = 1;
+                        else if (dot(nd, sf.n) < 0.f) light_class = 2;
+                        if (light_class) {  // otherwise the sample lands in neither buffer: skip its path
+                            o = no;
+                            d = nd;
+                            seg = 1;
+                            done = P.max_depth <= 1;
+                        }
+                    }
+                }
+            } else if (hit.item == 0xFFFFFFFFu) {
                 L += beta * background(P.sc, P.env, d);
+                if (AUX && seg == 0 && int(s) < P.aux_samples && P.use_normal) {  // camera.hpp:518-526
+                    unsigned long long* a = fix_aux + 7 * size_t(pixel);
+                    gfix_add(a + 3, 0.5f);
+                    gfix_add(a + 4, 0.5f);
+                    gfix_add(a + 5, 1.0f);
+                }
                 done = true;
             } else {
                 Surface sf;
                 make_surface(P.sc, hit, o, d, sf);
+                if (AUX && seg == 0 && int(s) < P.aux_samples) {  // K8 first-hit AOVs (camera.hpp:464-488)
+                    unsigned long long* a = fix_aux + 7 * size_t(pixel);
+                    if (P.use_albedo) {
+                        const float3 al = material_get_albedo(P.sc, sf);
+                        gfix_add(a + 0, al.x);
+                        gfix_add(a + 1, al.y);
+                        gfix_add(a + 2, al.z);
+                    }
+                    if (P.use_normal) {
+                        const float3 n = unit_vector(sf.n);
+                        gfix_add(a + 3, (dot(n, P.cam.u) + 1.f) * 0.5f);
+                        gfix_add(a + 4, (dot(n, P.cam.v) + 1.f) * 0.5f);
+                        gfix_add(a + 5, (dot(n, P.cam.w) + 1.f) * 0.5f);
+                    }
+                    if (P.use_z) gfix_add(a + 6, 1.0f - clamp01(hit.t * P.inv_z_max));
+                }
                 L += beta * material_emitted(P.sc, sf);
                 const uint4 rb = ph(pixel, s, uint32_t(seg + 1), 0u);
                 float3 atten = f3(1, 1, 1), no, nd;
@@ -375,10 +440,22 @@ __global__ void __launch_bounds__(ZB_BLOCK_THREADS, MIN_BLOCKS) k_render_pq(cons
                 }
             }
             if (done) {  // K5 accumulate
-                unsigned long long* f = fix + 3 * size_t(pixel);
-                atomicAdd(f + 0, __float2ull_rn(fmaxf(L.x, 0.f) * ZB_FIX_SCALE));
-                atomicAdd(f + 1, __float2ull_rn(fmaxf(L.y, 0.f) * ZB_FIX_SCALE));
-                atomicAdd(f + 2, __float2ull_rn(fmaxf(L.z, 0.f) * ZB_FIX_SCALE));
+                if (LIGHT) {
+                    if (light_class) {
+                        const float luma = 0.2126f * length(L);  // vector length, not luminance (camera.hpp:500)
+                        if (luma > 2.0f) L *= 2.0f / luma;
+                        L = first_atten * L;
+                        unsigned long long* f = (light_class == 1 ? fix : fix_aux) + 3 * size_t(pixel);
+                        gfix_add(f + 0, L.x);
+                        gfix_add(f + 1, L.y);
+                        gfix_add(f + 2, L.z);
+                    }
+                } else {
+                    unsigned long long* f = fix + 3 * size_t(pixel);
+                    gfix_add(f + 0, L.x);
+                    gfix_add(f + 1, L.y);
+                    gfix_add(f + 2, L.z);
+                }
                 have = false;
             }
         }
@@ -394,7 +471,8 @@ __global__ void __launch_bounds__(ZB_BLOCK_THREADS, MIN_BLOCKS) k_render_pq(cons
 // fixed-point frame sums of k_render_pq, rows [row0, row1) -> the float4 accumulation buffer (xyz sums, w = samples) for
 // this rank's tiles, or — when `mean_out` is given — straight to scaled means (xyz, w = 1) without touching P.accum
 __global__ void __launch_bounds__(256) k_pq_resolve(const __grid_constant__ RenderParams P, const unsigned long long* __restrict__ fix,
-                                                    int row0, int row1, float scale, float4* __restrict__ mean_out) {
+                                                    const unsigned long long* __restrict__ fix_aux, int mode, int row0, int row1,
+                                                    float scale, float4* __restrict__ mean_out) {
     const int px = blockIdx.x * 64 + (threadIdx.x & 63), py = row0 + blockIdx.y * 4 + (threadIdx.x >> 6);
     if (px >= P.cam.width || py >= row1) return;
     if (P.tile_ranks > 1) {  // tile stripes: the other ranks' pixels stay untouched
@@ -412,6 +490,31 @@ __global__ void __launch_bounds__(256) k_pq_resolve(const __grid_constant__ Rend
         a.x += old.x; a.y += old.y; a.z += old.z; a.w += old.w;
     }
     P.accum[i] = a;
+    if (!fix_aux) return;
+    const size_t n = size_t(P.cam.width) * P.cam.height;
+    if (mode == PQ_LIGHT) {  // refraction sums -> plane 0 of accum_aux, like k_render<.., LIGHT>
+        float4 r = make_float4(fix_get(fix_aux[3 * i]), fix_get(fix_aux[3 * i + 1]), fix_get(fix_aux[3 * i + 2]), float(P.sample_end - P.sample_begin));
+        if (P.accumulate) {
+            const float4 old = P.accum_aux[i];
+            r.x += old.x; r.y += old.y; r.z += old.z; r.w += old.w;
+        }
+        P.accum_aux[i] = r;
+    } else {  // albedo, normal, z planes
+        const unsigned long long* q = fix_aux + 7 * i;
+        const float z = fix_get(q[6]);
+        float4 a0 = make_float4(fix_get(q[0]), fix_get(q[1]), fix_get(q[2]), 0.f);
+        float4 a1 = make_float4(fix_get(q[3]), fix_get(q[4]), fix_get(q[5]), 0.f);
+        float4 a2 = make_float4(z, z, z, 0.f);
+        if (P.accumulate) {
+            const float4 b0 = P.accum_aux[i], b1 = P.accum_aux[n + i], b2 = P.accum_aux[2 * n + i];
+            a0.x += b0.x; a0.y += b0.y; a0.z += b0.z;
+            a1.x += b1.x; a1.y += b1.y; a1.z += b1.z;
+            a2.x += b2.x; a2.y += b2.y; a2.z += b2.z;
+        }
+        P.accum_aux[i] = a0;
+        P.accum_aux[n + i] = a1;
+        P.accum_aux[2 * n + i] = a2;
+    }
 }
 
 __global__ void __launch_bounds__(128) k_primary_ids(const __grid_constant__ RenderParams P, uint32_t* leaf_id,
@@ -506,29 +609,39 @@ cudaError_t zbk_launch_render(const RenderParams& P, int n_tiles_owned, bool sta
     return cudaGetLastError();
 }
 
-cudaError_t zbk_pq_clear(unsigned long long* fix, size_t pixels, unsigned long long* heads, int n_heads, cudaStream_t stream) {
-    cudaError_t e = cudaMemsetAsync(fix, 0, pixels * 3 * sizeof(unsigned long long), stream);
+size_t zbk_pq_words(size_t pixels, int mode) { return pixels * (mode == PQ_AUX ? 10 : mode == PQ_LIGHT ? 6 : 3); }
+
+cudaError_t zbk_pq_clear(unsigned long long* fix, size_t pixels, int mode, unsigned long long* heads, int n_heads, cudaStream_t stream) {
+    cudaError_t e = cudaMemsetAsync(fix, 0, zbk_pq_words(pixels, mode) * sizeof(unsigned long long), stream);
     if (e != cudaSuccess) return e;
     return cudaMemsetAsync(heads, 0, size_t(n_heads) * sizeof(unsigned long long), stream);
 }
 
-// the queue kernel alone: `fix` and `*head` must be zero (zbk_pq_clear); tiles P.tile_rank + i * P.tile_ranks, i < n_tiles
-cudaError_t zbk_launch_render_pq(const RenderParams& P, int n_tiles_owned, unsigned long long* fix, unsigned long long* head,
+// the queue kernel alone: the sums and `*head` must be zero (zbk_pq_clear); tiles P.tile_rank + i * P.tile_ranks,
+// i < n_tiles.  The aux sums follow the 3 * pixels beauty sums in `fix`.
+cudaError_t zbk_launch_render_pq(const RenderParams& P, int n_tiles_owned, int mode, unsigned long long* fix, unsigned long long* head,
                                  int sm_count, cudaStream_t stream) {
     if (n_tiles_owned <= 0) return cudaSuccess;
+    const size_t pixels = size_t(P.cam.width) * P.cam.height;
+    unsigned long long* fix_aux = mode == PQ_BEAUTY ? nullptr : fix + 3 * pixels;
     const unsigned long long total = (unsigned long long)n_tiles_owned * 4ull * 32ull * (unsigned long long)(P.sample_end - P.sample_begin);
     const unsigned long long warps_needed = (total + 31) / 32;
     const int per_sm = P.sc.n_nodes >= PQ_BIG_TREE_NODES ? 7 : 6;
     const unsigned blocks = unsigned(std::min<unsigned long long>((unsigned long long)sm_count * per_sm, (warps_needed + 3) / 4));
-    if (per_sm == 7) k_render_pq<7><<<blocks, ZB_BLOCK_THREADS, 0, stream>>>(P, fix, head, total);
-    else k_render_pq<6><<<blocks, ZB_BLOCK_THREADS, 0, stream>>>(P, fix, head, total);
+#define PQ_LAUNCH(B, M) k_render_pq<B, M><<<blocks, ZB_BLOCK_THREADS, 0, stream>>>(P, fix, fix_aux, head, total)
+    if (mode == PQ_AUX) { if (per_sm == 7) PQ_LAUNCH(7, PQ_AUX); else PQ_LAUNCH(6, PQ_AUX); }
+    else if (mode == PQ_LIGHT) { if (per_sm == 7) PQ_LAUNCH(7, PQ_LIGHT); else PQ_LAUNCH(6, PQ_LIGHT); }
+    else { if (per_sm == 7) PQ_LAUNCH(7, PQ_BEAUTY); else PQ_LAUNCH(6, PQ_BEAUTY); }
+#undef PQ_LAUNCH
     return cudaGetLastError();
 }
 
-cudaError_t zbk_pq_resolve(const RenderParams& P, const unsigned long long* fix, int row0, int row1, float scale, float4* mean_out,
-                           cudaStream_t stream) {
+cudaError_t zbk_pq_resolve(const RenderParams& P, int mode, const unsigned long long* fix, int row0, int row1, float scale,
+                           float4* mean_out, cudaStream_t stream) {
     if (row1 <= row0) return cudaSuccess;
-    k_pq_resolve<<<dim3((P.cam.width + 63) / 64, (row1 - row0 + 3) / 4), 256, 0, stream>>>(P, fix, row0, row1, scale, mean_out);
+    const size_t pixels = size_t(P.cam.width) * P.cam.height;
+    const unsigned long long* fix_aux = mode == PQ_BEAUTY ? nullptr : fix + 3 * pixels;
+    k_pq_resolve<<<dim3((P.cam.width + 63) / 64, (row1 - row0 + 3) / 4), 256, 0, stream>>>(P, fix, fix_aux, mode, row0, row1, scale, mean_out);
     return cudaGetLastError();
 }
 

@@ -7,13 +7,15 @@
 #include "scene_dev.cuh"
 
 cudaError_t zbk_launch_render(const RenderParams& P, int n_tiles_owned, bool stats, cudaStream_t stream);
-// beauty pass with a frame-wide path queue (k_render_pq): fix = W*H*3 u64 fixed-point sums, head = one u64 queue head
-// per launch; clear, launch (one or several disjoint tile ranges), then resolve rows into P.accum or into scaled means
-cudaError_t zbk_pq_clear(unsigned long long* fix, size_t pixels, unsigned long long* heads, int n_heads, cudaStream_t stream);
-cudaError_t zbk_launch_render_pq(const RenderParams& P, int n_tiles_owned, unsigned long long* fix, unsigned long long* head,
+// render with a frame-wide path queue (k_render_pq).  mode: 0 beauty, 1 beauty + first-hit AOVs, 2 light passes.
+// fix = zbk_pq_words(pixels, mode) u64 fixed-point sums, head = one u64 queue head per launch; clear, launch (one or
+// several disjoint tile ranges), then resolve rows into P.accum / P.accum_aux or (beauty) into scaled means
+size_t zbk_pq_words(size_t pixels, int mode);
+cudaError_t zbk_pq_clear(unsigned long long* fix, size_t pixels, int mode, unsigned long long* heads, int n_heads, cudaStream_t stream);
+cudaError_t zbk_launch_render_pq(const RenderParams& P, int n_tiles_owned, int mode, unsigned long long* fix, unsigned long long* head,
                                  int sm_count, cudaStream_t stream);
-cudaError_t zbk_pq_resolve(const RenderParams& P, const unsigned long long* fix, int row0, int row1, float scale, float4* mean_out,
-                           cudaStream_t stream);
+cudaError_t zbk_pq_resolve(const RenderParams& P, int mode, const unsigned long long* fix, int row0, int row1, float scale,
+                           float4* mean_out, cudaStream_t stream);
 cudaError_t zbk_launch_primary_ids(const RenderParams& P, uint32_t* leaf_id, uint32_t* prim_id, float* t,
                                    cudaStream_t stream);
 cudaError_t zbk_launch_resolve(const float4* accum, size_t n, float scale, float4* out_f4, double* out_f64,

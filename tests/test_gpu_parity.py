@@ -675,13 +675,23 @@ def test_path_queue_kernel_equals_tile_kernel(name, gpu_ctx, tmp_path, weekend_s
     else:
         _, _, _, wh, _ = GOLDEN_SCENES[name]
         sc, cfg, _ = _load_scene(gpu_ctx, tmp_path, name, wh, 24)
+    import copy
+    full = copy.copy(cfg)  # AOV and light-pass modes of the queue kernel
+    full.use_albedo = full.use_normal = full.use_z_depth = full.use_reflection = full.use_refraction = True
     monkeypatch.setenv("ZB_PQ", "0")
     a = sc.render(cfg, seed=5)["beauty"]
     a_tiles = [sc.render(cfg, seed=5, tile=(r, 3))["beauty"] for r in range(3)]
+    a_full = sc.render(full, seed=5)
     monkeypatch.delenv("ZB_PQ")
     b = sc.render(cfg, seed=5)["beauty"]
     b_tiles = [sc.render(cfg, seed=5, tile=(r, 3))["beauty"] for r in range(3)]
     c = sc.render(cfg, seed=5, samples_per_launch=5)["beauty"]
+    monkeypatch.setenv("ZB_PQ", "2")  # the queue kernel's AOV and light-pass modes (not the default: slower, see abi_render.cu)
+    b_full = sc.render(full, seed=5)
+    b_full_batched = sc.render(full, seed=5, samples_per_launch=7)
+    for key in ("beauty", "albedo", "normal", "z_depth", "reflection", "refraction"):
+        assert np.array_equal(a_full[key], b_full[key]), key
+        assert np.allclose(b_full[key], b_full_batched[key], rtol=2e-6, atol=1e-7), key
     if name != "weekend":
         sc.close()
     assert np.array_equal(a, b), np.abs(a - b).max()
