@@ -160,6 +160,9 @@ int fill_params(zb_context* ctx, const zb_scene* scene, const zb_camera* cam, co
     P.counters = ctx->counters;
     P.seed_lo = uint32_t(o->seed);
     P.seed_hi = uint32_t(o->seed >> 32);
+    static_assert(ZB_PHILOX_WORDS <= 24, "RenderParams::pk is too small");
+    philox_expand_key(P.seed_lo, P.seed_hi, P.pk[0]);
+    philox_expand_key(P.seed_lo, P.seed_hi ^ 0x4C495445u, P.pk[1]);  // the light passes draw their own stream
     int sb = o->sample_begin, se = o->sample_end;
     if (sb == 0 && se == 0) se = o->samples_per_pixel;
     if (sb < 0 || se < sb || se > o->samples_per_pixel) return fail(ZB_ERR_INVALID, "render: bad sample range");

@@ -65,7 +65,7 @@ __global__ void __launch_bounds__(ZB_BLOCK_THREADS, ZB_MIN_BLOCKS) k_render(cons
 
     const int n_s = P.sample_end - P.sample_begin;
     const int total = (ty < P.tiles_y && P.max_depth > 0) ? 32 * n_s : 0;
-    const Philox ph{P.seed_lo, LIGHT ? P.seed_hi ^ 0x4C495445u : P.seed_hi};  // the light passes draw their own stream
+    const Philox ph{P.pk[LIGHT ? 1 : 0]};  // the light passes draw their own stream
     Counters cnt = {0, 0, 0, 0};
     uint32_t paths = 0;
 
@@ -286,7 +286,7 @@ __global__ void __launch_bounds__(ZB_BLOCK_THREADS, MIN_BLOCKS) k_render_pq(cons
     constexpr bool AUX = MODE == PQ_AUX, LIGHT = MODE == PQ_LIGHT;
     const unsigned lane = threadIdx.x & 31u, lt = (1u << lane) - 1u;
     const uint32_t n_s = uint32_t(P.sample_end - P.sample_begin);
-    const Philox ph{P.seed_lo, LIGHT ? P.seed_hi ^ 0x4C495445u : P.seed_hi};  // the light passes draw their own stream
+    const Philox ph{P.pk[LIGHT ? 1 : 0]};  // the light passes draw their own stream
     float3 first_atten = f3(0, 0, 0);  // LIGHT: attenuation of the primary scatter (camera.hpp:512, :515)
     int light_class = 0;               // LIGHT: 1 reflection, 2 refraction, 0 neither
     Counters cnt = {0, 0, 0, 0};
@@ -527,7 +527,7 @@ __global__ void __launch_bounds__(128) k_primary_ids(const __grid_constant__ Ren
                   float(P.cam.pix00_rel_d[1] + px * P.cam.du_d[1] + py * P.cam.dv_d[1]),
                   float(P.cam.pix00_rel_d[2] + px * P.cam.du_d[2] + py * P.cam.dv_d[2]));
     Counters cnt = {0, 0, 0, 0};
-    MediumRng mr{Philox{P.seed_lo, P.seed_hi}, uint32_t(idx), 0u, 0u};
+    MediumRng mr{Philox{P.pk[0]}, uint32_t(idx), 0u, 0u};
     Hit hit;
     uint32_t lid = 0xFFFFFFFFu, pid = 0;
     float t = INFINITY;
@@ -550,7 +550,7 @@ __global__ void __launch_bounds__(128) k_probe(const __grid_constant__ RenderPar
     if (i >= n) return;
     const float3 o = f3(org[3 * i], org[3 * i + 1], org[3 * i + 2]), d = f3(dir[3 * i], dir[3 * i + 1], dir[3 * i + 2]);
     Counters cnt = {0, 0, 0, 0};
-    MediumRng mr{Philox{P.seed_lo, P.seed_hi}, uint32_t(i), 0u, 0u};
+    MediumRng mr{Philox{P.pk[0]}, uint32_t(i), 0u, 0u};
     Hit hit;
     zb_probe r;
     memset(&r, 0, sizeof(r));

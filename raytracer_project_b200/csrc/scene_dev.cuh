@@ -57,6 +57,7 @@ struct RenderParams {
     float4* accum_aux;  // 3 planes of W*H: albedo, normal, z-depth sums; may be null
     unsigned long long* counters;  // [0] rays [1] node visits [2] box tests [3] prim tests [4] instance visits [5] paths
     uint32_t seed_lo, seed_hi;
+    uint32_t pk[2][24];            // Philox round keys of the seed (vecmath.cuh): [0] beauty, [1] light passes (seed_hi ^ "LITE")
     int sample_begin, sample_end;  // global sample indices rendered by this launch
     int max_depth;
     int aux_samples;               // clamp(spp/8, 64, 1024) (camera.hpp:433)

@@ -56,24 +56,30 @@ ZB_DEV float3 xform_vector_t(const Affine& m, float3 v) {
 #ifndef ZB_PHILOX_ROUNDS
 #define ZB_PHILOX_ROUNDS 10
 #endif
+// The key schedule (key + r * Weyl constants) is expanded on the host into 2 * rounds words that live in the kernel
+// parameters, so each round is two wide multiplies and two three-input XORs with a constant-bank operand.
+#define ZB_PHILOX_WORDS (2 * ZB_PHILOX_ROUNDS)
 struct Philox {
-    uint32_t key0, key1;
+    const uint32_t* rk;  // round keys: rk[2 r] = key0 + r * 0x9E3779B9, rk[2 r + 1] = key1 + r * 0xBB67AE85
     ZB_DEV uint4 operator()(uint32_t c0, uint32_t c1, uint32_t c2, uint32_t c3) const {
-        uint32_t k0 = key0, k1 = key1;
 #pragma unroll
         for (int r = 0; r < ZB_PHILOX_ROUNDS; r++) {
             uint32_t hi0 = __umulhi(0xD2511F53u, c0), lo0 = 0xD2511F53u * c0;
             uint32_t hi1 = __umulhi(0xCD9E8D57u, c2), lo1 = 0xCD9E8D57u * c2;
-            c0 = hi1 ^ c1 ^ k0;
+            c0 = hi1 ^ c1 ^ rk[2 * r];
             c1 = lo1;
-            c2 = hi0 ^ c3 ^ k1;
+            c2 = hi0 ^ c3 ^ rk[2 * r + 1];
             c3 = lo0;
-            k0 += 0x9E3779B9u;
-            k1 += 0xBB67AE85u;
         }
         return make_uint4(c0, c1, c2, c3);
     }
 };
+inline void philox_expand_key(uint32_t key0, uint32_t key1, uint32_t* rk) {  // host side
+    for (int r = 0; r < ZB_PHILOX_ROUNDS; r++) {
+        rk[2 * r] = key0 + uint32_t(r) * 0x9E3779B9u;
+        rk[2 * r + 1] = key1 + uint32_t(r) * 0xBB67AE85u;
+    }
+}
 // uniform in [0,1) with 24 bits, the analogue of random_double() (common.hpp:29-34)
 ZB_DEV float u01(uint32_t x) { return float(x >> 8) * (1.0f / 16777216.0f); }
 // uniform in (0,1): safe argument for log()

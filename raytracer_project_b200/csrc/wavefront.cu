@@ -105,7 +105,7 @@ ZB_DEV void wf_store_path(const WfState& S, uint32_t slot, float3 o, float3 d, u
 // first queue: every slot starts a path (iteration 0 reads queue[0] / cnt[0])
 __global__ void __launch_bounds__(128) k_wf_init(const __grid_constant__ RenderParams P, const WfState S) {
     const uint32_t slot = blockIdx.x * blockDim.x + threadIdx.x;
-    const Philox ph{P.seed_lo, P.seed_hi};
+    const Philox ph{P.pk[0]};
     uint32_t pixel = 0, s = 0;
     float3 o, d;
     const bool alive = wf_next_path(P, S, ph, slot < S.n_slots, pixel, s, o, d);
@@ -125,7 +125,7 @@ __global__ void __launch_bounds__(128, WF_TRACE_BLOCKS) k_wf_trace(const __grid_
     const uint32_t count = S.cnt[S.iter % 3u];
     const uint32_t* q_in = S.queue[S.iter & 1u];
     uint32_t* fetch = S.fetch + (S.iter & 1u);
-    const Philox ph{P.seed_lo, P.seed_hi};
+    const Philox ph{P.pk[0]};
     int stack[ZB_STACK];
     Counters cnt = {0, 0, 0, 0};
     RayWalk w;
@@ -195,7 +195,7 @@ __global__ void __launch_bounds__(128) k_wf_shade(const __grid_constant__ Render
     const uint32_t* q_in = S.queue[S.iter & 1u];
     uint32_t* q_out = S.queue[(S.iter & 1u) ^ 1u];
     uint32_t* n_out = S.cnt + (S.iter + 1u) % 3u;
-    const Philox ph{P.seed_lo, P.seed_hi};
+    const Philox ph{P.pk[0]};
     if (blockIdx.x == 0 && threadIdx.x == 0) {  // counters of later iterations (nobody reads or writes them now)
         S.cnt[(S.iter + 2u) % 3u] = 0;
         S.fetch[(S.iter & 1u) ^ 1u] = 0;

@@ -250,7 +250,7 @@ __global__ void __launch_bounds__(128) k_wireframe(const __grid_constant__ Rende
     const int px = blockIdx.x * 32 + (threadIdx.x & 31), py = blockIdx.y * 4 + (threadIdx.x >> 5);
     if (px >= P.cam.width || py >= P.cam.height) return;
     const uint32_t pixel = uint32_t(py) * uint32_t(P.cam.width) + uint32_t(px);
-    const Philox ph{P.seed_lo, P.seed_hi};
+    const Philox ph{P.pk[0]};
     float3 sum = f3(0, 0, 0);
     for (int s = P.sample_begin; s < P.sample_end; s++) {
         // K1 raygen, the same draws as the beauty pass (camera.hpp:784-794, :817, :822)
