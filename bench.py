@@ -282,13 +282,13 @@ def ours(args):
             "kernel_ms_per_step": kernel_ms,
             "e2e": {"value": e2e_value, "unit": "Mpaths/s", "ms_per_step": e2e_ms_per_step,
                     "h2d_bytes_per_step": scene_bytes + 512,
-                    "d2h_bytes_per_step": n_pix * 16, "checksum": checksum,
+                    "d2h_bytes_per_step": n_pix * 12, "checksum": checksum,
                     "parts_ms": {"scene_upload": sum(p[0] for p in e2e_parts) / len(e2e_parts),
                                  "render_resolve_d2h": sum(p[1] for p in e2e_parts) / len(e2e_parts),
                                  "scene_free": sum(p[2] for p in e2e_parts) / len(e2e_parts)},
-                    "note": "frame crosses PCIe as float4 means (16 B/pixel) and is widened to the reference's "
+                    "note": "frame crosses PCIe as packed RGB float means (12 B/pixel) and is widened to the reference's "
                             "3-double layout by host threads while later chunks are in flight"},
-            "gpu_launches": 3 * args.steps,  # k_render_pq + k_pq_resolve (zb_render_device) + k_resolve per step
+            "gpu_launches": 3 * args.steps,  # k_render_pq + k_pq_resolve (zb_render_device) + k_resolve per step (device-timed leg)
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": hbm_peak, "unit": "GB/s", "frac": achieved / hbm_peak,
                          "traffic": NCU_DRAM_BYTES_PER_LAUNCH if world == 1 else None,
                          "traffic_source": "dram__bytes_read.sum + dram__bytes_write.sum of k_render_pq on this workload, "

@@ -62,6 +62,7 @@ extern "C" int zb_context_destroy(zb_context* ctx) {
     cudaFree(ctx->fin_stats);
     zbk_wavefront_free(ctx->wf);
     cudaFree(ctx->pq_fix);
+    cudaFree(ctx->rgb_pack);
     if (ctx->pinned) cudaFreeHost(ctx->pinned);
     for (auto& ev : ctx->ev) cudaEventDestroy(ev);
     for (auto& ev : ctx->chunk_ev) cudaEventDestroy(ev);

@@ -33,6 +33,8 @@ struct zb_context {
     float4* accum_aux = nullptr;
     size_t accum_pixels = 0;
     float4* out_f4 = nullptr;
+    float* rgb_pack = nullptr;  // packed RGB floats of the frame being copied to the host (d2h_rgb_f64)
+    size_t rgb_pack_pixels = 0;
     void* pinned = nullptr;
     size_t pinned_bytes = 0;
     uint32_t* id_scratch = nullptr;

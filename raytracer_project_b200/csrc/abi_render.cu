@@ -6,6 +6,8 @@
 
 #include "abi_internal.h"
 
+void zbh_widen_f32_f64(const float* s, double* d, size_t n);  // host_glue.cpp
+
 namespace {
 
 struct d3 {
@@ -266,11 +268,11 @@ int d2h(zb_context* ctx, void* host, const void* dev, size_t bytes) {
     return ZB_OK;
 }
 
-// Host side of the frame copy: chunk c (pixels [begin[c], begin[c + 1])) is widened from the pinned float4 stage into
-// the caller's 3-double layout (camera.hpp:531) as soon as its event has fired; up to 8 host threads.
+// Host side of the frame copy: chunk c (pixels [begin[c], begin[c + 1])) is widened from the pinned stage of packed RGB
+// floats into the caller's 3-double layout (camera.hpp:531) as soon as its event has fired; up to 8 host threads.
 int widen_chunks(zb_context* ctx, double* host, const std::vector<size_t>& begin) {
     const size_t n_chunks = begin.size() - 1;
-    const float4* stage = static_cast<const float4*>(ctx->pinned);
+    const float* stage = static_cast<const float*>(ctx->pinned);
     const unsigned hw = std::max(1u, std::thread::hardware_concurrency());
     const size_t n_thr = std::min<size_t>(std::min<size_t>(hw, 8), n_chunks);
     std::atomic<size_t> next{0};
@@ -280,14 +282,8 @@ int widen_chunks(zb_context* ctx, double* host, const std::vector<size_t>& begin
             const size_t c = next.fetch_add(1);
             if (c >= n_chunks) return;
             if (cudaEventSynchronize(ctx->chunk_ev[c]) != cudaSuccess) { err.store(1); return; }
-            const size_t b = begin[c], n = begin[c + 1] - b;
-            const float4* src = stage + b;
-            double* dst = host + 3 * b;
-            for (size_t i = 0; i < n; i++) {
-                dst[3 * i + 0] = double(src[i].x);
-                dst[3 * i + 1] = double(src[i].y);
-                dst[3 * i + 2] = double(src[i].z);
-            }
+            const size_t b = 3 * begin[c], e = 3 * begin[c + 1];
+            zbh_widen_f32_f64(stage + b, host + b, e - b);
         }
     };
     std::vector<std::thread> pool;
@@ -307,20 +303,30 @@ int ensure_chunk_events(zb_context* ctx, size_t n) {
     return ZB_OK;
 }
 
-// Device float4 means -> the reference's host layout (3 doubles per pixel, camera.hpp:531).  The frame
-// crosses PCIe as float4 (16 B/pixel instead of 24) in chunks; while chunk c+1 is in flight, host threads
-// widen chunk c into the caller's buffer, so the copy, the widening and the pageable-memory write overlap.
+// Device float4 means -> the reference's host layout (3 doubles per pixel, camera.hpp:531).  The frame is packed to
+// RGB floats on the device and crosses PCIe at 12 B/pixel (instead of 24 as doubles) in chunks; while chunk c+1 is in
+// flight, host threads widen chunk c into the caller's buffer, so the copy, the widening and the pageable-memory
+// write overlap.
 int d2h_rgb_f64(zb_context* ctx, double* host, const float4* dev, size_t pixels) {
-    const size_t chunk = size_t(1) << 18;  // 256 Ki pixels = 4 MiB per copy
+    if (ctx->rgb_pack_pixels < pixels) {
+        cudaFree(ctx->rgb_pack);
+        ctx->rgb_pack = nullptr;
+        ctx->rgb_pack_pixels = 0;
+        ZB_CUDA(cudaMalloc(&ctx->rgb_pack, pixels * 3 * sizeof(float)));
+        ctx->rgb_pack_pixels = pixels;
+    }
+    ZB_CUDA(zbk_launch_pack_rgb(dev, pixels, ctx->rgb_pack, ctx->stream));
+    ctx->stats.launches++;
+    const size_t chunk = size_t(1) << 18;  // 256 Ki pixels = 3 MiB per copy
     const size_t n_chunks = (pixels + chunk - 1) / chunk;
     int rc = ensure_chunk_events(ctx, n_chunks);
     if (rc) return rc;
-    float4* stage = static_cast<float4*>(ctx->pinned);
+    float* stage = static_cast<float*>(ctx->pinned);
     std::vector<size_t> begin;
     for (size_t c = 0; c < n_chunks; c++) {
         const size_t b = c * chunk, n = std::min(chunk, pixels - b);
         begin.push_back(b);
-        ZB_CUDA(cudaMemcpyAsync(stage + b, dev + b, n * sizeof(float4), cudaMemcpyDeviceToHost, ctx->stream));
+        ZB_CUDA(cudaMemcpyAsync(stage + 3 * b, ctx->rgb_pack + 3 * b, n * 3 * sizeof(float), cudaMemcpyDeviceToHost, ctx->stream));
         ZB_CUDA(cudaEventRecord(ctx->chunk_ev[c], ctx->stream));
     }
     begin.push_back(pixels);

@@ -262,3 +262,30 @@ extern "C" const char* zb_pass_file_name(int render_pass) {
                                   "render_Reflections.png", "render_Refractions.png", "render_Z-Depth.png"};
     return render_pass >= 0 && render_pass < 7 ? names[render_pass] : nullptr;
 }
+
+// ------------------------------------------------------------------ host side of the frame copy
+// float -> double widening of a chunk of the frame into the caller's buffer (abi_render.cu widen_chunks).  The AVX2
+// form converts 8 floats per step and writes with streaming stores: the destination is written once and never read, so
+// skipping the read-for-ownership halves the memory traffic of this step.
+#if defined(__x86_64__)
+#include <immintrin.h>
+__attribute__((target("avx2"))) static void widen_avx2(const float* s, double* d, size_t n) {
+    size_t i = 0;
+    while (i < n && (reinterpret_cast<uintptr_t>(d + i) & 31u)) { d[i] = double(s[i]); i++; }
+    for (; i + 8 <= n; i += 8) {
+        const __m256 v = _mm256_loadu_ps(s + i);
+        _mm256_stream_pd(d + i, _mm256_cvtps_pd(_mm256_castps256_ps128(v)));
+        _mm256_stream_pd(d + i + 4, _mm256_cvtps_pd(_mm256_extractf128_ps(v, 1)));
+    }
+    for (; i < n; i++) d[i] = double(s[i]);
+    _mm_sfence();
+}
+#endif
+
+void zbh_widen_f32_f64(const float* s, double* d, size_t n) {
+#if defined(__x86_64__)
+    static const bool avx2 = __builtin_cpu_supports("avx2");
+    if (avx2) { widen_avx2(s, d, n); return; }
+#endif
+    for (size_t i = 0; i < n; i++) d[i] = double(s[i]);
+}

@@ -652,6 +652,22 @@ cudaError_t zbk_launch_primary_ids(const RenderParams& P, uint32_t* leaf_id, uin
     return cudaGetLastError();
 }
 
+// float4 means -> packed RGB floats (12 B / pixel): what crosses PCIe on the way to the reference's 3-double layout
+__global__ void __launch_bounds__(256) k_pack_rgb(const float4* __restrict__ in, size_t n, float* __restrict__ out) {
+    const size_t i = size_t(blockIdx.x) * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const float4 a = in[i];
+    out[3 * i + 0] = a.x;
+    out[3 * i + 1] = a.y;
+    out[3 * i + 2] = a.z;
+}
+
+cudaError_t zbk_launch_pack_rgb(const float4* in, size_t n, float* out, cudaStream_t stream) {
+    if (!n) return cudaSuccess;
+    k_pack_rgb<<<unsigned((n + 255) / 256), 256, 0, stream>>>(in, n, out);
+    return cudaGetLastError();
+}
+
 cudaError_t zbk_launch_resolve(const float4* accum, size_t n, float scale, float4* out_f4, double* out_f64,
                                cudaStream_t stream) {
     if (n == 0) return cudaSuccess;

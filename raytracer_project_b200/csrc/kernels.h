@@ -20,6 +20,7 @@ cudaError_t zbk_launch_primary_ids(const RenderParams& P, uint32_t* leaf_id, uin
                                    cudaStream_t stream);
 cudaError_t zbk_launch_resolve(const float4* accum, size_t n, float scale, float4* out_f4, double* out_f64,
                                cudaStream_t stream);
+cudaError_t zbk_launch_pack_rgb(const float4* in, size_t n, float* out, cudaStream_t stream);
 cudaError_t zbk_launch_probe(const RenderParams& P, size_t n, const float* org, const float* dir, zb_probe* out,
                              cudaStream_t stream);
 // nodes (lo, hi) -> (centre, half extent) in place, when the traversal is compiled for that encoding (ZB_BOX_CH)
