@@ -238,6 +238,21 @@ int launch_share(zb_context* ctx, RenderParams P, const zb_render_opts* o, const
             int iters = 0;
             ZB_CUDA(zbk_launch_wavefront(P, &ctx->wf, wf_slots, &iters, ctx->stream));
             ctx->stats.launches += 2 + 2 * iters;
+        } else if (pq && !pq_all && !o->collect_stats && P.max_depth > 0 && P.sample_end > P.sample_begin && !P.light_pass && P.accum_aux &&
+                   P.sc.n_nodes < 65536u) {
+            // beauty + AOVs: the queue kernel for the beauty sums, the AOV planes from a primary-ray pass of their own
+            // (1080p x 64 spp against k_render with AOVs: quirks 62.7 -> 52.5 ms, Weekend 40.7 -> 41.0; on the 1 M-triangle
+            // mesh the second set of primary rays costs more than the queue wins, 80.3 -> 84.3, so big trees stay with k_render)
+            RenderParams B = P;
+            B.accum_aux = nullptr;
+            int rc2 = ensure_pq_scratch(ctx, pixels, 0);
+            if (rc2) return rc2;
+            unsigned long long* heads = ctx->pq_fix + zbk_pq_words(pixels, 0);
+            ZB_CUDA(zbk_pq_clear(ctx->pq_fix, pixels, 0, heads, 1, ctx->stream));
+            ZB_CUDA(zbk_launch_render_pq(B, owned_tiles(B), 0, ctx->pq_fix, heads, ctx->sm_count, ctx->stream));
+            ZB_CUDA(zbk_pq_resolve(B, 0, ctx->pq_fix, 0, B.cam.height, 0.f, nullptr, ctx->stream));
+            ZB_CUDA(zbk_launch_aov_pass(P, owned_tiles(P), ctx->stream));
+            ctx->stats.launches += 3;
         } else if (pq && !o->collect_stats && P.max_depth > 0 && P.sample_end > P.sample_begin &&
                    (pq_all || (!P.light_pass && !P.accum_aux))) {
             const int mode = P.light_pass ? 2 : P.accum_aux ? 1 : 0;

@@ -468,6 +468,71 @@ __global__ void __launch_bounds__(ZB_BLOCK_THREADS, MIN_BLOCKS) k_render_pq(cons
     }
 }
 
+// First-hit AOVs (K8, camera.hpp:464-488, :518-526) as a pass of their own beside k_render_pq: one thread per pixel walks
+// the pixel's first aux_samples samples, regenerates the camera ray of (pixel, sample) — the same Philox draws as the
+// beauty pass, so the same primary hit — and sums albedo, view-space normal and z in 64-bit fixed point in registers
+// (the same integers k_render adds up in shared memory, so the planes are bit-identical to its output).  Primary rays
+// of an 8x4 sub-tile at the same sample index are coherent: 133 M of them cost ~3 ms on the headline frame.
+__global__ void __launch_bounds__(ZB_BLOCK_THREADS, 6) k_aov_pass(const __grid_constant__ RenderParams P) {
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int tile = blockIdx.x * P.tile_ranks + P.tile_rank;
+    const int tx = tile % P.tiles_x, ty = tile / P.tiles_x;
+    const int px = tx * ZB_TILE_W + (warp % (ZB_TILE_W / 8)) * 8 + (lane & 7), py = ty * ZB_TILE_H + (warp / (ZB_TILE_W / 8)) * 4 + (lane >> 3);
+    if (px >= P.cam.width || py >= P.cam.height || ty >= P.tiles_y) return;
+    const uint32_t pixel = uint32_t(py) * uint32_t(P.cam.width) + uint32_t(px);
+    const Philox ph{P.pk[0]};
+    Counters cnt = {0, 0, 0, 0};
+    unsigned long long acc[7] = {0, 0, 0, 0, 0, 0, 0};
+    auto add = [&](int k, float v) { acc[k] += __float2ull_rn(fmaxf(v, 0.f) * ZB_FIX_SCALE); };
+    const int s_end = min(P.sample_end, P.aux_samples);
+    for (int s = P.sample_begin; s < s_end; s++) {
+        const uint4 r0 = ph(pixel, uint32_t(s), 0u, 0u);
+        float3 d = P.cam.pix00_rel + (float(px) + u01(r0.x) - 0.5f) * P.cam.du + (float(py) + u01(r0.y) - 0.5f) * P.cam.dv;
+        float3 o = P.cam.center;
+        if (P.cam.defocus) {
+            float rr = sqrtf(u01(r0.z)), sn, cs;
+            sincospif(2.0f * u01(r0.w), &sn, &cs);
+            const float3 off = (rr * cs) * P.cam.disk_u + (rr * sn) * P.cam.disk_v;
+            o += off;
+            d = d - off;
+        }
+        Hit hit;
+        const MediumRng mr{ph, pixel, uint32_t(s), 1u};
+        trace<false>(P.sc, o, d, 0.001f, INFINITY, mr, hit, cnt);
+        if (hit.item == 0xFFFFFFFFu) {
+            if (P.use_normal) { add(3, 0.5f); add(4, 0.5f); add(5, 1.0f); }  // camera.hpp:518-526
+            continue;
+        }
+        Surface sf;
+        make_surface(P.sc, hit, o, d, sf);
+        if (P.use_albedo) {
+            const float3 a = material_get_albedo(P.sc, sf);
+            add(0, a.x); add(1, a.y); add(2, a.z);
+        }
+        if (P.use_normal) {
+            const float3 n = unit_vector(sf.n);
+            add(3, (dot(n, P.cam.u) + 1.f) * 0.5f);
+            add(4, (dot(n, P.cam.v) + 1.f) * 0.5f);
+            add(5, (dot(n, P.cam.w) + 1.f) * 0.5f);
+        }
+        if (P.use_z) add(6, 1.0f - clamp01(hit.t * P.inv_z_max));
+    }
+    const size_t n = size_t(P.cam.width) * P.cam.height, i = pixel;
+    const float z = fix_get(acc[6]);
+    float4 a0 = make_float4(fix_get(acc[0]), fix_get(acc[1]), fix_get(acc[2]), 0.f);
+    float4 a1 = make_float4(fix_get(acc[3]), fix_get(acc[4]), fix_get(acc[5]), 0.f);
+    float4 a2 = make_float4(z, z, z, 0.f);
+    if (P.accumulate) {
+        const float4 b0 = P.accum_aux[i], b1 = P.accum_aux[n + i], b2 = P.accum_aux[2 * n + i];
+        a0.x += b0.x; a0.y += b0.y; a0.z += b0.z;
+        a1.x += b1.x; a1.y += b1.y; a1.z += b1.z;
+        a2.x += b2.x; a2.y += b2.y; a2.z += b2.z;
+    }
+    P.accum_aux[i] = a0;
+    P.accum_aux[n + i] = a1;
+    P.accum_aux[2 * n + i] = a2;
+}
+
 // fixed-point frame sums of k_render_pq, rows [row0, row1) -> the float4 accumulation buffer (xyz sums, w = samples) for
 // this rank's tiles, or — when `mean_out` is given — straight to scaled means (xyz, w = 1) without touching P.accum
 __global__ void __launch_bounds__(256) k_pq_resolve(const __grid_constant__ RenderParams P, const unsigned long long* __restrict__ fix,
@@ -633,6 +698,12 @@ cudaError_t zbk_launch_render_pq(const RenderParams& P, int n_tiles_owned, int m
     else if (mode == PQ_LIGHT) { if (per_sm == 7) PQ_LAUNCH(7, PQ_LIGHT); else PQ_LAUNCH(6, PQ_LIGHT); }
     else { if (per_sm == 7) PQ_LAUNCH(7, PQ_BEAUTY); else PQ_LAUNCH(6, PQ_BEAUTY); }
 #undef PQ_LAUNCH
+    return cudaGetLastError();
+}
+
+cudaError_t zbk_launch_aov_pass(const RenderParams& P, int n_tiles_owned, cudaStream_t stream) {
+    if (n_tiles_owned <= 0 || !P.accum_aux) return cudaSuccess;
+    k_aov_pass<<<n_tiles_owned, ZB_BLOCK_THREADS, 0, stream>>>(P);
     return cudaGetLastError();
 }
 

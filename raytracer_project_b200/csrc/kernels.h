@@ -16,6 +16,8 @@ cudaError_t zbk_launch_render_pq(const RenderParams& P, int n_tiles_owned, int m
                                  int sm_count, cudaStream_t stream);
 cudaError_t zbk_pq_resolve(const RenderParams& P, int mode, const unsigned long long* fix, int row0, int row1, float scale,
                            float4* mean_out, cudaStream_t stream);
+// first-hit AOV planes of this rank's tiles into P.accum_aux, as a pass beside the beauty queue kernel
+cudaError_t zbk_launch_aov_pass(const RenderParams& P, int n_tiles_owned, cudaStream_t stream);
 cudaError_t zbk_launch_primary_ids(const RenderParams& P, uint32_t* leaf_id, uint32_t* prim_id, float* t,
                                    cudaStream_t stream);
 cudaError_t zbk_launch_resolve(const float4* accum, size_t n, float scale, float4* out_f4, double* out_f64,

@@ -686,6 +686,13 @@ def test_path_queue_kernel_equals_tile_kernel(name, gpu_ctx, tmp_path, weekend_s
     b = sc.render(cfg, seed=5)["beauty"]
     b_tiles = [sc.render(cfg, seed=5, tile=(r, 3))["beauty"] for r in range(3)]
     c = sc.render(cfg, seed=5, samples_per_launch=5)["beauty"]
+    d_full = sc.render(full, seed=5)  # default: queue kernel + AOV primary-ray pass; light passes by k_render
+    d_full_batched = sc.render(full, seed=5, samples_per_launch=7)
+    d_tiles = [sc.render(full, seed=5, tile=(r, 2)) for r in range(2)]
+    for key in ("beauty", "albedo", "normal", "z_depth", "reflection", "refraction"):
+        assert np.array_equal(a_full[key], d_full[key]), key
+        assert np.allclose(d_full[key], d_full_batched[key], rtol=2e-6, atol=1e-7), key
+        assert np.array_equal(d_tiles[0][key] + d_tiles[1][key], d_full[key]), key
     monkeypatch.setenv("ZB_PQ", "2")  # the queue kernel's AOV and light-pass modes (not the default: slower, see abi_render.cu)
     b_full = sc.render(full, seed=5)
     b_full_batched = sc.render(full, seed=5, samples_per_launch=7)
