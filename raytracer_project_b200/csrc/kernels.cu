@@ -258,7 +258,7 @@ __global__ void __launch_bounds__(ZB_BLOCK_THREADS, ZB_MIN_BLOCKS) k_render(cons
 // k_render binds a warp to one 8x4 sub-tile: when the sub-tile's queue runs dry the lanes of the warp go idle one by
 // one until the longest path ends, then the block ends and a new one starts.  That drain is paid once per sub-tile —
 // under 1 % of the work at 64 samples per pixel, 13 % at the 10 spp of config C1 and 9 % on each GPU of an 8-GPU
-// sample-slice frame (8 spp per GPU).  Here warps are persistent and take the frame's paths in batches of PQ_BATCH
+// sample-slice frame (8 spp per GPU).  Here warps are persistent and take the frame's paths in batches of 64..256
 // consecutive indices from one global counter (same order: tile, sub-tile, pixel-major, sample), so lanes only run
 // dry at the end of the frame.  Lanes that need a path are served at the top of the segment loop, where the warp is
 // converged, by ballot rank from the warp's batch (registers, no shared-memory atomics).  Per-pixel sums are 64-bit
@@ -282,7 +282,7 @@ __global__ void __launch_bounds__(ZB_BLOCK_THREADS, MIN_BLOCKS) k_render_pq(cons
                                                                                   unsigned long long* __restrict__ fix,
                                                                                   unsigned long long* __restrict__ fix_aux,
                                                                                   unsigned long long* __restrict__ head,
-                                                                                  unsigned long long total) {
+                                                                                  unsigned long long total, unsigned batch) {
     constexpr bool AUX = MODE == PQ_AUX, LIGHT = MODE == PQ_LIGHT;
     const unsigned lane = threadIdx.x & 31u, lt = (1u << lane) - 1u;
     const uint32_t n_s = uint32_t(P.sample_end - P.sample_begin);
@@ -307,7 +307,7 @@ __global__ void __launch_bounds__(ZB_BLOCK_THREADS, MIN_BLOCKS) k_render_pq(cons
             if (avail < want) {
                 // fixed batches: shrinking them towards the end of the frame ("guided" scheduling) was measured and
                 // cost more in the segment loop than the shorter tail returned (profiles/r01_pq.txt)
-                if (lane == 0) base2 = atomicAdd(head, (unsigned long long)PQ_BATCH);
+                if (lane == 0) base2 = atomicAdd(head, (unsigned long long)batch);
                 base2 = __shfl_sync(0xFFFFFFFFu, base2, 0);
             }
             if (!have && !dry) {
@@ -358,7 +358,7 @@ __global__ void __launch_bounds__(ZB_BLOCK_THREADS, MIN_BLOCKS) k_render_pq(cons
             }
             if (avail < want) {
                 w_pos = base2 + (want - avail);
-                w_end = base2 + PQ_BATCH;
+                w_end = base2 + batch;
             } else {
                 w_pos += want;
             }
@@ -693,7 +693,12 @@ cudaError_t zbk_launch_render_pq(const RenderParams& P, int n_tiles_owned, int m
     const unsigned long long warps_needed = (total + 31) / 32;
     const int per_sm = P.sc.n_nodes >= PQ_BIG_TREE_NODES ? 7 : 6;
     const unsigned blocks = unsigned(std::min<unsigned long long>((unsigned long long)sm_count * per_sm, (warps_needed + 3) / 4));
-#define PQ_LAUNCH(B, M) k_render_pq<B, M><<<blocks, ZB_BLOCK_THREADS, 0, stream>>>(P, fix, fix_aux, head, total)
+    // paths per grab: 256 when every warp will grab many times; short launches (few samples per pixel, small images,
+    // one GPU's slice of a multi-GPU frame) end better balanced with smaller batches.  Measured, 1080p Weekend:
+    // 64 spp 35.10 / 34.66 / 34.42 ms with 64 / 128 / 256, 8 spp 4.44 / 4.46 / 4.52, 1200x675 x 10 spp 2.23 / 2.25 / 2.36
+    const unsigned long long per_warp = total / (4ull * blocks);
+    const unsigned batch = per_warp >= 64ull * PQ_BATCH ? PQ_BATCH : per_warp >= 64ull * (PQ_BATCH / 2) ? PQ_BATCH / 2 : PQ_BATCH / 4;
+#define PQ_LAUNCH(B, M) k_render_pq<B, M><<<blocks, ZB_BLOCK_THREADS, 0, stream>>>(P, fix, fix_aux, head, total, batch)
     if (mode == PQ_AUX) { if (per_sm == 7) PQ_LAUNCH(7, PQ_AUX); else PQ_LAUNCH(6, PQ_AUX); }
     else if (mode == PQ_LIGHT) { if (per_sm == 7) PQ_LAUNCH(7, PQ_LIGHT); else PQ_LAUNCH(6, PQ_LIGHT); }
     else { if (per_sm == 7) PQ_LAUNCH(7, PQ_BEAUTY); else PQ_LAUNCH(6, PQ_BEAUTY); }
