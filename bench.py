@@ -294,7 +294,7 @@ def ours(args):
                          "traffic_source": "dram__bytes_read.sum + dram__bytes_write.sum of k_render_pq on this workload, "
                                            "ncu --set full capture summarised in profiles/r01_k_render_pq_raw_key.txt",
                          "peak_kind": f"{peak_kind} burst copy bandwidth",
-                         "kernel": "k_render_pq<6>", "algorithmic_bytes_per_launch": per_gpu_bytes,
+                         "kernel": "k_render_pq<8, BEAUTY, LEAN>", "algorithmic_bytes_per_launch": per_gpu_bytes,
                          "note": "scene (60 KB) is L1/L2-resident: algorithmic bytes are served by L1, so this "
                                  "fraction can exceed 1; the binding roofline is FP32/issue (roofline_fp32)"},
             "roofline_fp32": {"achieved": alg_flop / world / (kernel_ms * 1e-3) * 1e-12, "peak": fp32_peak,

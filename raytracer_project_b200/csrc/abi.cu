@@ -251,6 +251,10 @@ extern "C" int zb_scene_upload(zb_context* ctx, const zb_flat_scene* f, zb_scene
     }
     d.n_items = f->n_items;
     d.n_media = f->n_media;
+    d.lean = f->n_media == 0;
+    for (uint32_t i = 0; i < f->n_items && d.lean; i++) d.lean = (f->items[i].kind_flags & 0xFFu) == ZB_ITEM_SPHERE;
+    for (uint32_t i = 0; i < f->n_materials && d.lean; i++)
+        d.lean = f->materials[i].albedo_tex == ZB_NO_TEXTURE && f->materials[i].bump_tex == ZB_NO_TEXTURE;
     s->env_hdr_texture = f->pad;
     ZB_CUDA(cudaStreamSynchronize(ctx->stream));  // host arrays may be freed by the caller on return
     *out = s;

@@ -17,7 +17,9 @@ struct SceneDev {
     const float4* spheres_obj;  // 1 x float4 per object-space sphere
     const uchar4* texels_u8;
     const float4* texels_f32;
-    uint32_t n_nodes, n_items, n_media, pad;
+    uint32_t n_nodes, n_items, n_media;
+    uint32_t lean;  // 1: every item is an inline sphere, no material has a texture or a bump map, no media
+
 };
 
 // camera::initialize (camera.hpp:358-402) evaluated in double on the host, then narrowed.

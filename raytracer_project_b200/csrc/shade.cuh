@@ -82,6 +82,8 @@ ZB_DEV void tri_surface(const SceneDev& sc, uint32_t tri, float3 o, float3 d, Su
 }
 
 // Rebuild the reference's final hit_record for the winning item.
+// LEAN (SceneDev::lean): every item is an inline sphere and no material carries a texture or a bump map.
+template <bool LEAN = false>
 ZB_DEV void make_surface(const SceneDev& sc, const Hit& hit, float3 o, float3 d, Surface& sf, bool force_uv = false) {
     float4 g = __ldg(sc.items + 2 * size_t(hit.item));
     float4 mf = __ldg(sc.items + 2 * size_t(hit.item) + 1);
@@ -94,8 +96,8 @@ ZB_DEV void make_surface(const SceneDev& sc, const Hit& hit, float3 o, float3 d,
     sf.m0 = load_mat0(sc, sf.material);
     sf.m1 = load_mat1(sc, sf.material);
     // sphere uv / tangent frame (sphere.hpp:44-58) feed only texture lookups and bump mapping
-    const bool want_uv = force_uv || __float_as_uint(sf.m0.y) != ZB_NO_TEXTURE || __float_as_uint(sf.m0.z) != ZB_NO_TEXTURE;
-    if (kind == ZB_ITEM_SPHERE) {
+    const bool want_uv = !LEAN && (force_uv || __float_as_uint(sf.m0.y) != ZB_NO_TEXTURE || __float_as_uint(sf.m0.z) != ZB_NO_TEXTURE);
+    if (LEAN || kind == ZB_ITEM_SPHERE) {
         sf.p = fma3(hit.t, d, o);
         sphere_surface(g, sf.p, d, sf, want_uv);
         if (kf & ZB_FLAG_FORCE_FRONT) sf.front_face = true;
@@ -182,8 +184,10 @@ ZB_DEV float3 random_unit_vector(float x1, float x2) {
 }
 
 // material::emitted (material.hpp:12-14, :261-263)
+template <bool LEAN = false>
 ZB_DEV float3 material_emitted(const SceneDev& sc, const Surface& sf) {
     if (__float_as_uint(sf.m0.x) != ZB_MAT_LIGHT) return f3(0, 0, 0);
+    if (LEAN) return f3(sf.m1.x, sf.m1.y, sf.m1.z);
     return material_albedo_tex(sc, sf.m0, sf.m1, sf);
 }
 
@@ -200,33 +204,34 @@ ZB_DEV float3 material_get_albedo(const SceneDev& sc, const Surface& sf) {
 
 // material::scatter.  xi = (x, y: unit vector; z: dielectric choice).  Returns false when the path
 // ends here (light, absorbed metal sample).
+template <bool LEAN = false>
 ZB_DEV bool material_scatter(const SceneDev& sc, const Surface& sf, float3 d_in, float3 xi, float3& atten,
                              float3& o_out, float3& d_out) {
     const float4 m0 = sf.m0, m1 = sf.m1;
     uint32_t type = __float_as_uint(m0.x);
     const float ray_epsilon = 0.0001f;  // common.hpp:16
     if (type == ZB_MAT_LAMBERTIAN) {  // material.hpp:74-96
-        float3 wn = bumped_normal(sc, m0, sf);
+        float3 wn = LEAN ? sf.n : bumped_normal(sc, m0, sf);
         float3 dir = wn + random_unit_vector(xi.x, xi.y);
         if (fabsf(dir.x) < 1e-8f && fabsf(dir.y) < 1e-8f && fabsf(dir.z) < 1e-8f) dir = wn;
         o_out = fma3(ray_epsilon, sf.n, sf.p);
         d_out = dir;
-        atten = material_albedo_tex(sc, m0, m1, sf);
+        atten = LEAN ? f3(m1.x, m1.y, m1.z) : material_albedo_tex(sc, m0, m1, sf);
         return true;
     }
     if (type == ZB_MAT_METAL) {  // material.hpp:129-151
-        float3 wn = bumped_normal(sc, m0, sf);
+        float3 wn = LEAN ? sf.n : bumped_normal(sc, m0, sf);
         float3 v = unit_vector(d_in);
         float3 refl = fma3(-2.0f * dot(v, wn), wn, v);
         float3 dir = unit_vector(fma3(m1.w, random_unit_vector(xi.x, xi.y), refl));
         o_out = fma3(ray_epsilon, sf.n, sf.p);
         d_out = dir;
-        atten = material_albedo_tex(sc, m0, m1, sf);
+        atten = LEAN ? f3(m1.x, m1.y, m1.z) : material_albedo_tex(sc, m0, m1, sf);
         return dot(dir, sf.n) > 0.f;
     }
     if (type == ZB_MAT_DIELECTRIC) {  // material.hpp:192-224, :237-241; vec3.hpp:204-214
         atten = f3(m1.x, m1.y, m1.z);
-        float3 wn = bumped_normal(sc, m0, sf);
+        float3 wn = LEAN ? sf.n : bumped_normal(sc, m0, sf);
         float ri = sf.front_face ? 1.0f / m1.w : m1.w;
         float3 ud = unit_vector(d_in);
         float cos_t = fminf(dot(-ud, wn), 1.0f);
@@ -248,10 +253,10 @@ ZB_DEV bool material_scatter(const SceneDev& sc, const Surface& sf, float3 d_in,
         d_out = dir;
         return true;
     }
-    if (type == ZB_MAT_ISOTROPIC) {  // constant_medium.hpp:14-18
+    if (!LEAN && type == ZB_MAT_ISOTROPIC) {  // constant_medium.hpp:14-18
         o_out = sf.p;
         d_out = random_unit_vector(xi.x, xi.y);
-        atten = material_albedo_tex(sc, m0, m1, sf);
+        atten = LEAN ? f3(m1.x, m1.y, m1.z) : material_albedo_tex(sc, m0, m1, sf);
         return true;
     }
     return false;  // diffuse_light never scatters (material.hpp:255-259)

@@ -203,12 +203,20 @@ struct RayBox {
 // primitive tests of TLAS leaf `code` (items first .. first + n).  Returns true when the ray has to dive
 // into a mesh BLAS: the rest of the leaf, the exit marker and the BLAS root are then on the stack and
 // (ro, rd) is the ray in the object space of instance item `blas_item`.
-template <bool STATS>
+// LEAN: instantiation for scenes whose every item is an inline sphere (SceneDev::lean): only the geometry half of the
+// item is read, and none of the instance / mesh / cube / triangle / medium code is compiled in.
+template <bool STATS, bool LEAN = false>
 ZB_DEV bool tlas_leaf(const SceneDev& sc, uint32_t code, float3 o, float3 d, float tmin, const MediumRng& rng, Hit& hit,
                       int* stack, int& sp, float3& ro, float3& rd, uint32_t& blas_item, Counters& cnt) {
     const uint32_t first = code >> 3, end = first + (code & 7u) + 1u;
     for (uint32_t i = first; i < end; i++) {
         float4 g = __ldg(sc.items + 2 * size_t(i));
+        if (LEAN) {
+            if (STATS) cnt.prims++;
+            float ts;
+            if (hit_sphere(g, o, d, tmin, hit.t, ts)) { hit.t = ts; hit.item = i; }
+            continue;
+        }
         float4 mf = __ldg(sc.items + 2 * size_t(i) + 1);
         uint32_t kind = __float_as_uint(mf.x) & 0xFFu, aux = __float_as_uint(mf.w);
         if (STATS) cnt.prims++;
@@ -320,9 +328,11 @@ struct RayWalk {
     }
 
     // (o, d) is the world-space ray given to begin()
-    template <bool STATS>
+    template <bool STATS, bool LEAN = false>
     ZB_DEV void leaf_step(const SceneDev& sc, float3 o, float3 d, float tmin, const MediumRng& rng, int* stack, Counters& cnt) {
-        if (cur == ZB_EXIT_INSTANCE) {
+        if (LEAN) {
+            tlas_leaf<STATS, true>(sc, ~uint32_t(cur), o, d, tmin, rng, hit, stack, sp, ro, rd, blas_item, cnt);
+        } else if (cur == ZB_EXIT_INSTANCE) {
             in_blas = false;
             ro = o;
             rd = d;
@@ -353,7 +363,7 @@ struct RayWalk {
 // Closest hit of one ray, run to completion.  "while-while" traversal (Aila & Laine 2009): every lane first descends
 // through inner nodes until it holds a leaf, then the warp runs the primitive tests together; this keeps more lanes
 // on the same instruction than one loop that alternates between a node step and a leaf step.
-template <bool STATS>
+template <bool STATS, bool LEAN = false>
 ZB_DEV bool trace(const SceneDev& sc, float3 o, float3 d, float tmin, float tmax, const MediumRng& rng, Hit& hit,
                   Counters& cnt) {
     int stack[ZB_STACK];
@@ -363,7 +373,7 @@ ZB_DEV bool trace(const SceneDev& sc, float3 o, float3 d, float tmin, float tmax
     while (w.cur != ZB_TRAVERSAL_DONE) {
         while (w.cur >= 0) w.node_step<STATS>(sc, tmin, stack, cnt);
         if (w.cur == ZB_TRAVERSAL_DONE) break;
-        w.leaf_step<STATS>(sc, o, d, tmin, rng, stack, cnt);
+        w.leaf_step<STATS, LEAN>(sc, o, d, tmin, rng, stack, cnt);
     }
     hit = w.hit;
     return hit.item != 0xFFFFFFFFu;

@@ -545,6 +545,21 @@ def test_wavefront_render_equals_megakernel(name, gpu_ctx, tmp_path, weekend_sce
     assert abs(a.mean() - b.mean()) < 1e-3 * a.mean()
 
 
+def test_lean_instantiation_equals_general_queue_kernel(weekend_scene, monkeypatch):
+    """Plain scenes (every item an inline sphere, untextured materials, solid-colour environment) run the LEAN
+    instantiation of k_render_pq; ZB_NO_LEAN=1 forces the general one.  Same arithmetic on the paths a plain scene
+    takes, so the frames are equal bit for bit, for every resident-blocks variant."""
+    cfg = scenes.weekend(seed=1, width=203, height=90, spp=24)[1]
+    monkeypatch.setenv("ZB_NO_LEAN", "1")
+    a = weekend_scene.render(cfg, seed=9)["beauty"]
+    monkeypatch.delenv("ZB_NO_LEAN")
+    b = weekend_scene.render(cfg, seed=9)["beauty"]
+    assert np.array_equal(a, b)
+    for blocks in ("6", "7"):
+        monkeypatch.setenv("ZB_LEAN_BLOCKS", blocks)
+        assert np.array_equal(a, weekend_scene.render(cfg, seed=9)["beauty"]), blocks
+
+
 # ------------------------------------------------------------------ image export (SURVEY 8(f) f4)
 def test_save_pass_png_matches_reference_export(gpu_ctx, tmp_path):
     """zb_save_pass (finishing chain of the pass on the device -> 8-bit PNG) against the pixels of the PNGs the
