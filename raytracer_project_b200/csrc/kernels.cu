@@ -278,8 +278,9 @@ enum { PQ_BEAUTY = 0, PQ_AUX = 1, PQ_LIGHT = 2 };
 
 ZB_DEV void gfix_add(unsigned long long* slot, float v) { atomicAdd(slot, __float2ull_rn(fmaxf(v, 0.f) * ZB_FIX_SCALE)); }
 
-// LEAN: instantiation for SceneDev::lean scenes under a solid-colour environment (see zbk_launch_render_pq)
-template <int MIN_BLOCKS, int MODE, bool LEAN = false>
+// F: scene features compiled in (ZB_F_*, scene_dev.cuh); zbk_launch_render_pq picks the smallest instantiation that covers
+// SceneDev::features and the environment of the render
+template <int MIN_BLOCKS, int MODE, uint32_t F = ZB_F_ALL>
 __global__ void __launch_bounds__(ZB_BLOCK_THREADS, MIN_BLOCKS) k_render_pq(const __grid_constant__ RenderParams P,
                                                                                   unsigned long long* __restrict__ fix,
                                                                                   unsigned long long* __restrict__ fix_aux,
@@ -370,7 +371,7 @@ __global__ void __launch_bounds__(ZB_BLOCK_THREADS, MIN_BLOCKS) k_render_pq(cons
             Hit hit;
             {
                 MediumRng mr{ph, pixel, s, uint32_t(seg + 1)};
-                trace<false, LEAN>(P.sc, o, d, 0.001f, INFINITY, mr, hit, cnt);
+                trace<false, F>(P.sc, o, d, 0.001f, INFINITY, mr, hit, cnt);
             }
             // ---- K3 shade: one segment of ray_color (camera.hpp:928-1004), as in k_render
             bool done;
@@ -380,11 +381,11 @@ __global__ void __launch_bounds__(ZB_BLOCK_THREADS, MIN_BLOCKS) k_render_pq(cons
                 done = true;
                 if (hit.item != 0xFFFFFFFFu) {
                     Surface sf;
-                    make_surface<LEAN>(P.sc, hit, o, d, sf);
+                    make_surface<F>(P.sc, hit, o, d, sf);
                     const uint4 rb = ph(pixel, s, 1u, 0u);
                     float3 no, nd;
                     first_atten = f3(1, 1, 1);
-                    if (material_scatter<LEAN>(P.sc, sf, d, f3(u01(rb.x), u01(rb.y), u01(rb.z)), first_atten, no, nd)) {
+                    if (material_scatter<F>(P.sc, sf, d, f3(u01(rb.x), u01(rb.y), u01(rb.z)), first_atten, no, nd)) {
                         const float3 ud = unit_vector(d), un = unit_vector(sf.n);
                         const float3 mirror = fma3(-2.0f * dot(ud, un), un, ud);
                         if (dot(unit_vector(nd), mirror) > 0.9f) light_class = 1;
@@ -398,7 +399,7 @@ __global__ void __launch_bounds__(ZB_BLOCK_THREADS, MIN_BLOCKS) k_render_pq(cons
                     }
                 }
             } else if (hit.item == 0xFFFFFFFFu) {
-                L += beta * (LEAN ? P.env.background : background(P.sc, P.env, d));
+                L += beta * ((F & ZB_F_ENV) ? background(P.sc, P.env, d) : P.env.background);
                 if (AUX && seg == 0 && int(s) < P.aux_samples && P.use_normal) {  // camera.hpp:518-526
                     unsigned long long* a = fix_aux + 7 * size_t(pixel);
                     gfix_add(a + 3, 0.5f);
@@ -408,7 +409,7 @@ __global__ void __launch_bounds__(ZB_BLOCK_THREADS, MIN_BLOCKS) k_render_pq(cons
                 done = true;
             } else {
                 Surface sf;
-                make_surface<LEAN>(P.sc, hit, o, d, sf);
+                make_surface<F>(P.sc, hit, o, d, sf);
                 if (AUX && seg == 0 && int(s) < P.aux_samples) {  // K8 first-hit AOVs (camera.hpp:464-488)
                     unsigned long long* a = fix_aux + 7 * size_t(pixel);
                     if (P.use_albedo) {
@@ -425,10 +426,10 @@ __global__ void __launch_bounds__(ZB_BLOCK_THREADS, MIN_BLOCKS) k_render_pq(cons
                     }
                     if (P.use_z) gfix_add(a + 6, 1.0f - clamp01(hit.t * P.inv_z_max));
                 }
-                L += beta * material_emitted<LEAN>(P.sc, sf);
+                L += beta * material_emitted<F>(P.sc, sf);
                 const uint4 rb = ph(pixel, s, uint32_t(seg + 1), 0u);
                 float3 atten = f3(1, 1, 1), no, nd;
-                done = !material_scatter<LEAN>(P.sc, sf, d, f3(u01(rb.x), u01(rb.y), u01(rb.z)), atten, no, nd);
+                done = !material_scatter<F>(P.sc, sf, d, f3(u01(rb.x), u01(rb.y), u01(rb.z)), atten, no, nd);
                 if (!done) {
                     beta *= atten;
                     o = no;
@@ -693,12 +694,20 @@ cudaError_t zbk_launch_render_pq(const RenderParams& P, int n_tiles_owned, int m
     unsigned long long* fix_aux = mode == PQ_BEAUTY ? nullptr : fix + 3 * pixels;
     const unsigned long long total = (unsigned long long)n_tiles_owned * 4ull * 32ull * (unsigned long long)(P.sample_end - P.sample_begin);
     const unsigned long long warps_needed = (total + 31) / 32;
-    // plain scenes (inline spheres, untextured materials, solid-colour environment: the Weekend configs) run the LEAN
-    // instantiation; ZB_NO_LEAN=1 forces the general kernel (A/B runs, equality tests)
+    // Beauty renders run the smallest compiled feature set that covers the scene and its environment (ZB_F_*, scene_dev.cuh):
+    //   PLAIN  inline spheres, untextured materials, solid-colour environment (Weekend): 64 registers, 8 blocks per SM
+    //   BOXES  + loose triangles, cubes, instances of them, media (Cornell)
+    //   MESH   instances, meshes, triangles, textures (large-mesh configs), solid-colour environment
+    //   NOMESH everything but meshes and triangles (exterior: HDR map, bump maps, instanced cubes / spheres, media)
+    // ZB_NO_LEAN=1 forces the general kernel (A/B runs, equality tests).
+    constexpr uint32_t F_PLAIN = 0, F_BOXES = ZB_F_INST | ZB_F_CUBE | ZB_F_TRI | ZB_F_MEDIA,
+                       F_MESH = ZB_F_INST | ZB_F_MESH | ZB_F_TRI | ZB_F_TEX, F_NOMESH = ZB_F_ALL & ~(ZB_F_MESH | ZB_F_TRI);
     const bool no_lean = getenv("ZB_NO_LEAN") && atoi(getenv("ZB_NO_LEAN")) != 0;
     const int lean_blocks = getenv("ZB_LEAN_BLOCKS") ? atoi(getenv("ZB_LEAN_BLOCKS")) : 8;
-    const bool lean = !no_lean && mode == PQ_BEAUTY && P.sc.lean && P.env.mode == ZB_ENV_SOLID_COLOR;
-    const int per_sm = lean ? std::min(std::max(lean_blocks, 6), 8) : P.sc.n_nodes >= PQ_BIG_TREE_NODES ? 7 : 6;
+    const uint32_t need = (P.sc.features & ZB_F_ALL) | (P.env.mode == ZB_ENV_SOLID_COLOR ? 0u : uint32_t(ZB_F_ENV));
+    auto covers = [&](uint32_t f) { return !no_lean && mode == PQ_BEAUTY && (need & ~f) == 0; };
+    const uint32_t feat = covers(F_PLAIN) ? F_PLAIN : covers(F_BOXES) ? F_BOXES : covers(F_MESH) ? F_MESH : covers(F_NOMESH) ? F_NOMESH : uint32_t(ZB_F_ALL);
+    const int per_sm = feat == F_PLAIN ? std::min(std::max(lean_blocks, 6), 8) : P.sc.n_nodes >= PQ_BIG_TREE_NODES ? 7 : 6;
     const unsigned blocks = unsigned(std::min<unsigned long long>((unsigned long long)sm_count * per_sm, (warps_needed + 3) / 4));
     // paths per grab: 256 when every warp will grab many times; short launches (few samples per pixel, small images,
     // one GPU's slice of a multi-GPU frame) end better balanced with smaller batches.  Measured, 1080p Weekend:
@@ -706,13 +715,16 @@ cudaError_t zbk_launch_render_pq(const RenderParams& P, int n_tiles_owned, int m
     const unsigned long long per_warp = total / (4ull * blocks);
     const unsigned batch = per_warp >= 64ull * PQ_BATCH ? PQ_BATCH : per_warp >= 64ull * (PQ_BATCH / 2) ? PQ_BATCH / 2 : PQ_BATCH / 4;
 #define PQ_LAUNCH(B, M) k_render_pq<B, M><<<blocks, ZB_BLOCK_THREADS, 0, stream>>>(P, fix, fix_aux, head, total, batch)
-#define PQ_LAUNCH_LEAN(B) k_render_pq<B, PQ_BEAUTY, true><<<blocks, ZB_BLOCK_THREADS, 0, stream>>>(P, fix, fix_aux, head, total, batch)
-    if (lean) { if (per_sm == 6) PQ_LAUNCH_LEAN(6); else if (per_sm == 7) PQ_LAUNCH_LEAN(7); else PQ_LAUNCH_LEAN(8); }
+#define PQ_LAUNCH_F(B, FEAT) k_render_pq<B, PQ_BEAUTY, FEAT><<<blocks, ZB_BLOCK_THREADS, 0, stream>>>(P, fix, fix_aux, head, total, batch)
+    if (feat == F_PLAIN) { if (per_sm == 6) PQ_LAUNCH_F(6, F_PLAIN); else if (per_sm == 7) PQ_LAUNCH_F(7, F_PLAIN); else PQ_LAUNCH_F(8, F_PLAIN); }
+    else if (feat == F_BOXES) { if (per_sm == 7) PQ_LAUNCH_F(7, F_BOXES); else PQ_LAUNCH_F(6, F_BOXES); }
+    else if (feat == F_MESH) { if (per_sm == 7) PQ_LAUNCH_F(7, F_MESH); else PQ_LAUNCH_F(6, F_MESH); }
+    else if (feat == F_NOMESH) { if (per_sm == 7) PQ_LAUNCH_F(7, F_NOMESH); else PQ_LAUNCH_F(6, F_NOMESH); }
     else if (mode == PQ_AUX) { if (per_sm == 7) PQ_LAUNCH(7, PQ_AUX); else PQ_LAUNCH(6, PQ_AUX); }
     else if (mode == PQ_LIGHT) { if (per_sm == 7) PQ_LAUNCH(7, PQ_LIGHT); else PQ_LAUNCH(6, PQ_LIGHT); }
     else { if (per_sm == 7) PQ_LAUNCH(7, PQ_BEAUTY); else PQ_LAUNCH(6, PQ_BEAUTY); }
 #undef PQ_LAUNCH
-#undef PQ_LAUNCH_LEAN
+#undef PQ_LAUNCH_F
     return cudaGetLastError();
 }
 

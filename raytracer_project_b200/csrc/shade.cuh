@@ -82,8 +82,8 @@ ZB_DEV void tri_surface(const SceneDev& sc, uint32_t tri, float3 o, float3 d, Su
 }
 
 // Rebuild the reference's final hit_record for the winning item.
-// LEAN (SceneDev::lean): every item is an inline sphere and no material carries a texture or a bump map.
-template <bool LEAN = false>
+// F: the scene features compiled in (ZB_F_*, scene_dev.cuh)
+template <uint32_t F = ZB_F_ALL>
 ZB_DEV void make_surface(const SceneDev& sc, const Hit& hit, float3 o, float3 d, Surface& sf, bool force_uv = false) {
     float4 g = __ldg(sc.items + 2 * size_t(hit.item));
     float4 mf = __ldg(sc.items + 2 * size_t(hit.item) + 1);
@@ -96,30 +96,30 @@ ZB_DEV void make_surface(const SceneDev& sc, const Hit& hit, float3 o, float3 d,
     sf.m0 = load_mat0(sc, sf.material);
     sf.m1 = load_mat1(sc, sf.material);
     // sphere uv / tangent frame (sphere.hpp:44-58) feed only texture lookups and bump mapping
-    const bool want_uv = !LEAN && (force_uv || __float_as_uint(sf.m0.y) != ZB_NO_TEXTURE || __float_as_uint(sf.m0.z) != ZB_NO_TEXTURE);
-    if (LEAN || kind == ZB_ITEM_SPHERE) {
+    const bool want_uv = (F & ZB_F_TEX) && (force_uv || __float_as_uint(sf.m0.y) != ZB_NO_TEXTURE || __float_as_uint(sf.m0.z) != ZB_NO_TEXTURE);
+    if (!(F & ZB_F_GEOM) || kind == ZB_ITEM_SPHERE) {
         sf.p = fma3(hit.t, d, o);
         sphere_surface(g, sf.p, d, sf, want_uv);
         if (kf & ZB_FLAG_FORCE_FRONT) sf.front_face = true;
-    } else if (kind == ZB_ITEM_CUBE) {
+    } else if ((F & ZB_F_CUBE) && kind == ZB_ITEM_CUBE) {
         sf.p = fma3(hit.t, d, o);
         cube_surface(sc, aux, sf.p, d, sf);
-    } else if (kind == ZB_ITEM_TRIANGLE) {
+    } else if ((F & ZB_F_TRI) && kind == ZB_ITEM_TRIANGLE) {
         sf.p = fma3(hit.t, d, o);
         tri_surface(sc, aux, o, d, sf);
-    } else if (kind == ZB_ITEM_MEDIUM) {
+    } else if ((F & ZB_F_MEDIA) && kind == ZB_ITEM_MEDIUM) {
         sf.p = fma3(hit.t, d, o);
         sf.n = f3(1, 0, 0);
         sf.front_face = true;
-    } else {  // instance: evaluate in object space, then bring p and the normal back
+    } else if (F & ZB_F_INST) {  // instance: evaluate in object space, then bring p and the normal back
         const float4* ip = sc.instances + 8 * size_t(aux);
         InstanceHead ih = load_instance_head(sc, aux);
         Affine o2w{__ldg(ip + 3), __ldg(ip + 4), __ldg(ip + 5)};
         float3 lo = xform_point(ih.w2o, o), ld = xform_vector(ih.w2o, d);
         float3 lp = fma3(hit.t, ld, lo);
         if (ih.geom_kind == ZB_GEOM_SPHERE) sphere_surface(__ldg(sc.spheres_obj + ih.geom_index), lp, ld, sf, want_uv);
-        else if (ih.geom_kind == ZB_GEOM_CUBE) cube_surface(sc, ih.geom_index, lp, ld, sf);
-        else tri_surface(sc, hit.prim, lo, ld, sf);
+        else if ((F & ZB_F_CUBE) && ih.geom_kind == ZB_GEOM_CUBE) cube_surface(sc, ih.geom_index, lp, ld, sf);
+        else if (F & ZB_F_TRI) tri_surface(sc, hit.prim, lo, ld, sf);
         sf.p = xform_point(o2w, lp);
         // rotate_*: n rotated; scale: unit(n / s) (scale.hpp:32-33) == normalise(W2O^T n)
         float3 wn = xform_vector_t(ih.w2o, sf.n);
@@ -184,10 +184,10 @@ ZB_DEV float3 random_unit_vector(float x1, float x2) {
 }
 
 // material::emitted (material.hpp:12-14, :261-263)
-template <bool LEAN = false>
+template <uint32_t F = ZB_F_ALL>
 ZB_DEV float3 material_emitted(const SceneDev& sc, const Surface& sf) {
     if (__float_as_uint(sf.m0.x) != ZB_MAT_LIGHT) return f3(0, 0, 0);
-    if (LEAN) return f3(sf.m1.x, sf.m1.y, sf.m1.z);
+    if (!(F & ZB_F_TEX)) return f3(sf.m1.x, sf.m1.y, sf.m1.z);
     return material_albedo_tex(sc, sf.m0, sf.m1, sf);
 }
 
@@ -204,34 +204,34 @@ ZB_DEV float3 material_get_albedo(const SceneDev& sc, const Surface& sf) {
 
 // material::scatter.  xi = (x, y: unit vector; z: dielectric choice).  Returns false when the path
 // ends here (light, absorbed metal sample).
-template <bool LEAN = false>
+template <uint32_t F = ZB_F_ALL>
 ZB_DEV bool material_scatter(const SceneDev& sc, const Surface& sf, float3 d_in, float3 xi, float3& atten,
                              float3& o_out, float3& d_out) {
     const float4 m0 = sf.m0, m1 = sf.m1;
     uint32_t type = __float_as_uint(m0.x);
     const float ray_epsilon = 0.0001f;  // common.hpp:16
     if (type == ZB_MAT_LAMBERTIAN) {  // material.hpp:74-96
-        float3 wn = LEAN ? sf.n : bumped_normal(sc, m0, sf);
+        float3 wn = (F & ZB_F_TEX) ? bumped_normal(sc, m0, sf) : sf.n;
         float3 dir = wn + random_unit_vector(xi.x, xi.y);
         if (fabsf(dir.x) < 1e-8f && fabsf(dir.y) < 1e-8f && fabsf(dir.z) < 1e-8f) dir = wn;
         o_out = fma3(ray_epsilon, sf.n, sf.p);
         d_out = dir;
-        atten = LEAN ? f3(m1.x, m1.y, m1.z) : material_albedo_tex(sc, m0, m1, sf);
+        atten = (F & ZB_F_TEX) ? material_albedo_tex(sc, m0, m1, sf) : f3(m1.x, m1.y, m1.z);
         return true;
     }
     if (type == ZB_MAT_METAL) {  // material.hpp:129-151
-        float3 wn = LEAN ? sf.n : bumped_normal(sc, m0, sf);
+        float3 wn = (F & ZB_F_TEX) ? bumped_normal(sc, m0, sf) : sf.n;
         float3 v = unit_vector(d_in);
         float3 refl = fma3(-2.0f * dot(v, wn), wn, v);
         float3 dir = unit_vector(fma3(m1.w, random_unit_vector(xi.x, xi.y), refl));
         o_out = fma3(ray_epsilon, sf.n, sf.p);
         d_out = dir;
-        atten = LEAN ? f3(m1.x, m1.y, m1.z) : material_albedo_tex(sc, m0, m1, sf);
+        atten = (F & ZB_F_TEX) ? material_albedo_tex(sc, m0, m1, sf) : f3(m1.x, m1.y, m1.z);
         return dot(dir, sf.n) > 0.f;
     }
     if (type == ZB_MAT_DIELECTRIC) {  // material.hpp:192-224, :237-241; vec3.hpp:204-214
         atten = f3(m1.x, m1.y, m1.z);
-        float3 wn = LEAN ? sf.n : bumped_normal(sc, m0, sf);
+        float3 wn = (F & ZB_F_TEX) ? bumped_normal(sc, m0, sf) : sf.n;
         float ri = sf.front_face ? 1.0f / m1.w : m1.w;
         float3 ud = unit_vector(d_in);
         float cos_t = fminf(dot(-ud, wn), 1.0f);
@@ -253,10 +253,10 @@ ZB_DEV bool material_scatter(const SceneDev& sc, const Surface& sf, float3 d_in,
         d_out = dir;
         return true;
     }
-    if (!LEAN && type == ZB_MAT_ISOTROPIC) {  // constant_medium.hpp:14-18
+    if ((F & ZB_F_MEDIA) && type == ZB_MAT_ISOTROPIC) {  // constant_medium.hpp:14-18
         o_out = sf.p;
         d_out = random_unit_vector(xi.x, xi.y);
-        atten = LEAN ? f3(m1.x, m1.y, m1.z) : material_albedo_tex(sc, m0, m1, sf);
+        atten = (F & ZB_F_TEX) ? material_albedo_tex(sc, m0, m1, sf) : f3(m1.x, m1.y, m1.z);
         return true;
     }
     return false;  // diffuse_light never scatters (material.hpp:255-259)

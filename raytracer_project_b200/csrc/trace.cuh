@@ -141,35 +141,39 @@ ZB_DEV InstanceHead load_instance_head(const SceneDev& sc, uint32_t idx) {
 }
 
 // boundary->hit() of a constant_medium for sphere / cube boundaries (optionally instanced)
+template <uint32_t F = ZB_F_ALL>
 ZB_DEV bool hit_simple_geom(const SceneDev& sc, uint32_t geom_kind, uint32_t geom_index, float3 o, float3 d,
                             float tmin, float tmax, float& t) {
     if (geom_kind == ZB_GEOM_SPHERE) return hit_sphere(__ldg(sc.spheres_obj + geom_index), o, d, tmin, tmax, t);
-    if (geom_kind == ZB_GEOM_CUBE) return hit_cube(f3(__ldg(sc.cubes + 2 * size_t(geom_index))), o, d, tmin, tmax, t);
-    if (geom_kind == ZB_GEOM_TRIANGLE) {
+    if ((F & ZB_F_CUBE) && geom_kind == ZB_GEOM_CUBE) return hit_cube(f3(__ldg(sc.cubes + 2 * size_t(geom_index))), o, d, tmin, tmax, t);
+    if ((F & ZB_F_TRI) && geom_kind == ZB_GEOM_TRIANGLE) {
         const float4* tp = sc.tris + 3 * size_t(geom_index);
         return hit_tri(f3(__ldg(tp)), f3(__ldg(tp + 1)), f3(__ldg(tp + 2)), o, d, tmin, tmax, t);
     }
     return false;
 }
 
+template <uint32_t F = ZB_F_ALL>
 ZB_DEV bool hit_medium_boundary(const SceneDev& sc, float4 m0, float4 sph, float3 o, float3 d, float tmin, float tmax,
                                 float& t) {
     uint32_t kind = __float_as_uint(m0.x), index = __float_as_uint(m0.y);
     if (kind == ZB_ITEM_SPHERE) return hit_sphere(sph, o, d, tmin, tmax, t);
-    if (kind == ZB_ITEM_CUBE) return hit_cube(f3(__ldg(sc.cubes + 2 * size_t(index))), o, d, tmin, tmax, t);
+    if ((F & ZB_F_CUBE) && kind == ZB_ITEM_CUBE) return hit_cube(f3(__ldg(sc.cubes + 2 * size_t(index))), o, d, tmin, tmax, t);
+    if (!(F & ZB_F_INST)) return false;
     InstanceHead ih = load_instance_head(sc, index);
-    return hit_simple_geom(sc, ih.geom_kind, ih.geom_index, xform_point(ih.w2o, o), xform_vector(ih.w2o, d), tmin,
+    return hit_simple_geom<F>(sc, ih.geom_kind, ih.geom_index, xform_point(ih.w2o, o), xform_vector(ih.w2o, d), tmin,
                            tmax, t);
 }
 
 // constant_medium::hit (constant_medium.hpp:39-77)
+template <uint32_t F = ZB_F_ALL>
 ZB_DEV bool hit_medium(const SceneDev& sc, uint32_t medium, float3 o, float3 d, float tmin, float tmax,
                        const MediumRng& rng, float& t_out) {
     float4 m0 = __ldg(sc.media + 2 * size_t(medium));
     float4 sph = __ldg(sc.media + 2 * size_t(medium) + 1);
     float t1, t2;
-    if (!hit_medium_boundary(sc, m0, sph, o, d, -INFINITY, INFINITY, t1)) return false;
-    if (!hit_medium_boundary(sc, m0, sph, o, d, t1 + 0.0001f, INFINITY, t2)) return false;
+    if (!hit_medium_boundary<F>(sc, m0, sph, o, d, -INFINITY, INFINITY, t1)) return false;
+    if (!hit_medium_boundary<F>(sc, m0, sph, o, d, t1 + 0.0001f, INFINITY, t2)) return false;
     if (t1 < tmin) t1 = tmin;
     if (t2 > tmax) t2 = tmax;
     if (t1 >= t2) return false;
@@ -203,15 +207,14 @@ struct RayBox {
 // primitive tests of TLAS leaf `code` (items first .. first + n).  Returns true when the ray has to dive
 // into a mesh BLAS: the rest of the leaf, the exit marker and the BLAS root are then on the stack and
 // (ro, rd) is the ray in the object space of instance item `blas_item`.
-// LEAN: instantiation for scenes whose every item is an inline sphere (SceneDev::lean): only the geometry half of the
-// item is read, and none of the instance / mesh / cube / triangle / medium code is compiled in.
-template <bool STATS, bool LEAN = false>
+// F without any ZB_F_GEOM bit: every item is an inline sphere, only the geometry half of the item is read.
+template <bool STATS, uint32_t F = ZB_F_ALL>
 ZB_DEV bool tlas_leaf(const SceneDev& sc, uint32_t code, float3 o, float3 d, float tmin, const MediumRng& rng, Hit& hit,
                       int* stack, int& sp, float3& ro, float3& rd, uint32_t& blas_item, Counters& cnt) {
     const uint32_t first = code >> 3, end = first + (code & 7u) + 1u;
     for (uint32_t i = first; i < end; i++) {
         float4 g = __ldg(sc.items + 2 * size_t(i));
-        if (LEAN) {
+        if (!(F & ZB_F_GEOM)) {
             if (STATS) cnt.prims++;
             float ts;
             if (hit_sphere(g, o, d, tmin, hit.t, ts)) { hit.t = ts; hit.item = i; }
@@ -223,11 +226,11 @@ ZB_DEV bool tlas_leaf(const SceneDev& sc, uint32_t code, float3 o, float3 d, flo
         float t;
         if (kind == ZB_ITEM_SPHERE) {
             if (hit_sphere(g, o, d, tmin, hit.t, t)) { hit.t = t; hit.item = i; }
-        } else if (kind == ZB_ITEM_INSTANCE) {
+        } else if ((F & ZB_F_INST) && kind == ZB_ITEM_INSTANCE) {
             InstanceHead ih = load_instance_head(sc, aux);
             if (STATS) cnt.insts++;
             float3 lo = xform_point(ih.w2o, o), ld = xform_vector(ih.w2o, d);
-            if (ih.geom_kind == ZB_GEOM_MESH) {
+            if ((F & ZB_F_MESH) && ih.geom_kind == ZB_GEOM_MESH) {
                 // defer the rest of this leaf, then dive into the BLAS in object space
                 if (sp + 3 > ZB_STACK) return false;
                 if (i + 1 < end) stack[sp++] = int(~(((i + 1) << 3) | (end - i - 2)));
@@ -238,22 +241,22 @@ ZB_DEV bool tlas_leaf(const SceneDev& sc, uint32_t code, float3 o, float3 d, flo
                 rd = ld;
                 return true;
             }
-            if (hit_simple_geom(sc, ih.geom_kind, ih.geom_index, lo, ld, tmin, hit.t, t)) {
+            if (hit_simple_geom<F>(sc, ih.geom_kind, ih.geom_index, lo, ld, tmin, hit.t, t)) {
                 hit.t = t;
                 hit.item = i;
                 hit.prim = ih.geom_index;
             }
-        } else if (kind == ZB_ITEM_CUBE) {
+        } else if ((F & ZB_F_CUBE) && kind == ZB_ITEM_CUBE) {
             if (hit_cube(f3(__ldg(sc.cubes + 2 * size_t(aux))), o, d, tmin, hit.t, t)) { hit.t = t; hit.item = i; }
-        } else if (kind == ZB_ITEM_TRIANGLE) {
+        } else if ((F & ZB_F_TRI) && kind == ZB_ITEM_TRIANGLE) {
             const float4* tp = sc.tris + 3 * size_t(aux);
             if (hit_tri(f3(__ldg(tp)), f3(__ldg(tp + 1)), f3(__ldg(tp + 2)), o, d, tmin, hit.t, t)) {
                 hit.t = t;
                 hit.item = i;
                 hit.prim = aux;
             }
-        } else {  // ZB_ITEM_MEDIUM
-            if (hit_medium(sc, aux, o, d, tmin, hit.t, rng, t)) { hit.t = t; hit.item = i; }
+        } else if ((F & ZB_F_MEDIA) && kind == ZB_ITEM_MEDIUM) {
+            if (hit_medium<F>(sc, aux, o, d, tmin, hit.t, rng, t)) { hit.t = t; hit.item = i; }
         }
     }
     return false;
@@ -328,10 +331,10 @@ struct RayWalk {
     }
 
     // (o, d) is the world-space ray given to begin()
-    template <bool STATS, bool LEAN = false>
+    template <bool STATS, uint32_t F = ZB_F_ALL>
     ZB_DEV void leaf_step(const SceneDev& sc, float3 o, float3 d, float tmin, const MediumRng& rng, int* stack, Counters& cnt) {
-        if (LEAN) {
-            tlas_leaf<STATS, true>(sc, ~uint32_t(cur), o, d, tmin, rng, hit, stack, sp, ro, rd, blas_item, cnt);
+        if (!(F & ZB_F_MESH)) {
+            tlas_leaf<STATS, F>(sc, ~uint32_t(cur), o, d, tmin, rng, hit, stack, sp, ro, rd, blas_item, cnt);
         } else if (cur == ZB_EXIT_INSTANCE) {
             in_blas = false;
             ro = o;
@@ -352,7 +355,7 @@ struct RayWalk {
                     hit.prim = i;
                 }
             }
-        } else if (tlas_leaf<STATS>(sc, ~uint32_t(cur), o, d, tmin, rng, hit, stack, sp, ro, rd, blas_item, cnt)) {
+        } else if (tlas_leaf<STATS, F>(sc, ~uint32_t(cur), o, d, tmin, rng, hit, stack, sp, ro, rd, blas_item, cnt)) {
             in_blas = true;
             rb.set(ro, rd);
         }
@@ -363,7 +366,7 @@ struct RayWalk {
 // Closest hit of one ray, run to completion.  "while-while" traversal (Aila & Laine 2009): every lane first descends
 // through inner nodes until it holds a leaf, then the warp runs the primitive tests together; this keeps more lanes
 // on the same instruction than one loop that alternates between a node step and a leaf step.
-template <bool STATS, bool LEAN = false>
+template <bool STATS, uint32_t F = ZB_F_ALL>
 ZB_DEV bool trace(const SceneDev& sc, float3 o, float3 d, float tmin, float tmax, const MediumRng& rng, Hit& hit,
                   Counters& cnt) {
     int stack[ZB_STACK];
@@ -373,7 +376,7 @@ ZB_DEV bool trace(const SceneDev& sc, float3 o, float3 d, float tmin, float tmax
     while (w.cur != ZB_TRAVERSAL_DONE) {
         while (w.cur >= 0) w.node_step<STATS>(sc, tmin, stack, cnt);
         if (w.cur == ZB_TRAVERSAL_DONE) break;
-        w.leaf_step<STATS, LEAN>(sc, o, d, tmin, rng, stack, cnt);
+        w.leaf_step<STATS, F>(sc, o, d, tmin, rng, stack, cnt);
     }
     hit = w.hit;
     return hit.item != 0xFFFFFFFFu;
