@@ -685,6 +685,20 @@ cudaError_t zbk_pq_clear(unsigned long long* fix, size_t pixels, int mode, unsig
     return cudaMemsetAsync(heads, 0, size_t(n_heads) * sizeof(unsigned long long), stream);
 }
 
+// beauty instantiation for feature set F at B resident blocks per SM (5..8: 96 / 80 / 72 / 64 registers)
+template <uint32_t F>
+static void pq_launch_beauty(int per_sm, unsigned blocks, cudaStream_t stream, const RenderParams& P, unsigned long long* fix,
+                             unsigned long long* head, unsigned long long total, unsigned batch) {
+    switch (per_sm) {
+        case 5: k_render_pq<5, PQ_BEAUTY, F><<<blocks, ZB_BLOCK_THREADS, 0, stream>>>(P, fix, nullptr, head, total, batch); break;
+        case 6: k_render_pq<6, PQ_BEAUTY, F><<<blocks, ZB_BLOCK_THREADS, 0, stream>>>(P, fix, nullptr, head, total, batch); break;
+        case 7: k_render_pq<7, PQ_BEAUTY, F><<<blocks, ZB_BLOCK_THREADS, 0, stream>>>(P, fix, nullptr, head, total, batch); break;
+        case 9: k_render_pq<9, PQ_BEAUTY, F><<<blocks, ZB_BLOCK_THREADS, 0, stream>>>(P, fix, nullptr, head, total, batch); break;
+        case 10: k_render_pq<10, PQ_BEAUTY, F><<<blocks, ZB_BLOCK_THREADS, 0, stream>>>(P, fix, nullptr, head, total, batch); break;
+        default: k_render_pq<8, PQ_BEAUTY, F><<<blocks, ZB_BLOCK_THREADS, 0, stream>>>(P, fix, nullptr, head, total, batch); break;
+    }
+}
+
 // the queue kernel alone: the sums and `*head` must be zero (zbk_pq_clear); tiles P.tile_rank + i * P.tile_ranks,
 // i < n_tiles.  The aux sums follow the 3 * pixels beauty sums in `fix`.
 cudaError_t zbk_launch_render_pq(const RenderParams& P, int n_tiles_owned, int mode, unsigned long long* fix, unsigned long long* head,
@@ -695,19 +709,24 @@ cudaError_t zbk_launch_render_pq(const RenderParams& P, int n_tiles_owned, int m
     const unsigned long long total = (unsigned long long)n_tiles_owned * 4ull * 32ull * (unsigned long long)(P.sample_end - P.sample_begin);
     const unsigned long long warps_needed = (total + 31) / 32;
     // Beauty renders run the smallest compiled feature set that covers the scene and its environment (ZB_F_*, scene_dev.cuh):
-    //   PLAIN  inline spheres, untextured materials, solid-colour environment (Weekend): 64 registers, 8 blocks per SM
-    //   BOXES  + loose triangles, cubes, instances of them, media (Cornell)
-    //   MESH   instances, meshes, triangles, textures (large-mesh configs), solid-colour environment
-    //   NOMESH everything but meshes and triangles (exterior: HDR map, bump maps, instanced cubes / spheres, media)
-    // ZB_NO_LEAN=1 forces the general kernel (A/B runs, equality tests).
-    constexpr uint32_t F_PLAIN = 0, F_BOXES = ZB_F_INST | ZB_F_CUBE | ZB_F_TRI | ZB_F_MEDIA,
-                       F_MESH = ZB_F_INST | ZB_F_MESH | ZB_F_TRI | ZB_F_TEX, F_NOMESH = ZB_F_ALL & ~(ZB_F_MESH | ZB_F_TRI);
+    //   PLAIN   inline spheres, untextured materials, solid-colour environment (Weekend)
+    //   BOXES   + loose triangles, cubes, instances of them, media (Cornell)
+    //   MESH0   instances, meshes, triangles (spheres + large mesh), MESH: + textures (mesh config with the material library)
+    //   NOMESH  everything but meshes and triangles (exterior: HDR map, bump maps, instanced cubes / spheres, media)
+    // ZB_NO_LEAN=1 forces the general kernel (A/B runs, equality tests); ZB_PQ_BLOCKS=5..8 overrides the resident blocks per SM.
+    constexpr uint32_t F_PLAIN = 0, F_BOXES = ZB_F_INST | ZB_F_CUBE | ZB_F_TRI | ZB_F_MEDIA, F_MESH0 = ZB_F_INST | ZB_F_MESH | ZB_F_TRI,
+                       F_MESH = F_MESH0 | ZB_F_TEX, F_NOMESH = ZB_F_ALL & ~(ZB_F_MESH | ZB_F_TRI);
     const bool no_lean = getenv("ZB_NO_LEAN") && atoi(getenv("ZB_NO_LEAN")) != 0;
-    const int lean_blocks = getenv("ZB_LEAN_BLOCKS") ? atoi(getenv("ZB_LEAN_BLOCKS")) : 8;
+    const int env_blocks = getenv("ZB_PQ_BLOCKS") ? atoi(getenv("ZB_PQ_BLOCKS")) : 0;
     const uint32_t need = (P.sc.features & ZB_F_ALL) | (P.env.mode == ZB_ENV_SOLID_COLOR ? 0u : uint32_t(ZB_F_ENV));
     auto covers = [&](uint32_t f) { return !no_lean && mode == PQ_BEAUTY && (need & ~f) == 0; };
-    const uint32_t feat = covers(F_PLAIN) ? F_PLAIN : covers(F_BOXES) ? F_BOXES : covers(F_MESH) ? F_MESH : covers(F_NOMESH) ? F_NOMESH : uint32_t(ZB_F_ALL);
-    const int per_sm = feat == F_PLAIN ? std::min(std::max(lean_blocks, 6), 8) : P.sc.n_nodes >= PQ_BIG_TREE_NODES ? 7 : 6;
+    const uint32_t feat = covers(F_PLAIN) ? F_PLAIN : covers(F_BOXES) ? F_BOXES : covers(F_MESH0) ? F_MESH0 : covers(F_MESH) ? F_MESH
+                        : covers(F_NOMESH) ? F_NOMESH : uint32_t(ZB_F_ALL);
+    const bool big_tree = P.sc.n_nodes >= PQ_BIG_TREE_NODES;
+    // resident blocks per SM, measured per feature set at 1080p x 16 spp with 5 / 6 / 7 / 8 blocks (profiles/r01_feature_sets.txt):
+    // Cornell 15.31 / 14.42 / 14.14 / 14.07 ms, exterior 18.74 / 18.17 / 17.42 / 17.83, mesh 17.95 / 16.86 / 16.67 / 16.04
+    int per_sm = feat == ZB_F_ALL ? (big_tree ? 7 : 6) : feat == F_NOMESH ? 7 : 8;
+    if (feat != ZB_F_ALL && env_blocks >= 5 && env_blocks <= 10) per_sm = env_blocks;
     const unsigned blocks = unsigned(std::min<unsigned long long>((unsigned long long)sm_count * per_sm, (warps_needed + 3) / 4));
     // paths per grab: 256 when every warp will grab many times; short launches (few samples per pixel, small images,
     // one GPU's slice of a multi-GPU frame) end better balanced with smaller batches.  Measured, 1080p Weekend:
@@ -715,16 +734,15 @@ cudaError_t zbk_launch_render_pq(const RenderParams& P, int n_tiles_owned, int m
     const unsigned long long per_warp = total / (4ull * blocks);
     const unsigned batch = per_warp >= 64ull * PQ_BATCH ? PQ_BATCH : per_warp >= 64ull * (PQ_BATCH / 2) ? PQ_BATCH / 2 : PQ_BATCH / 4;
 #define PQ_LAUNCH(B, M) k_render_pq<B, M><<<blocks, ZB_BLOCK_THREADS, 0, stream>>>(P, fix, fix_aux, head, total, batch)
-#define PQ_LAUNCH_F(B, FEAT) k_render_pq<B, PQ_BEAUTY, FEAT><<<blocks, ZB_BLOCK_THREADS, 0, stream>>>(P, fix, fix_aux, head, total, batch)
-    if (feat == F_PLAIN) { if (per_sm == 6) PQ_LAUNCH_F(6, F_PLAIN); else if (per_sm == 7) PQ_LAUNCH_F(7, F_PLAIN); else PQ_LAUNCH_F(8, F_PLAIN); }
-    else if (feat == F_BOXES) { if (per_sm == 7) PQ_LAUNCH_F(7, F_BOXES); else PQ_LAUNCH_F(6, F_BOXES); }
-    else if (feat == F_MESH) { if (per_sm == 7) PQ_LAUNCH_F(7, F_MESH); else PQ_LAUNCH_F(6, F_MESH); }
-    else if (feat == F_NOMESH) { if (per_sm == 7) PQ_LAUNCH_F(7, F_NOMESH); else PQ_LAUNCH_F(6, F_NOMESH); }
+    if (feat == F_PLAIN) pq_launch_beauty<F_PLAIN>(per_sm, blocks, stream, P, fix, head, total, batch);
+    else if (feat == F_BOXES) pq_launch_beauty<F_BOXES>(per_sm, blocks, stream, P, fix, head, total, batch);
+    else if (feat == F_MESH0) pq_launch_beauty<F_MESH0>(per_sm, blocks, stream, P, fix, head, total, batch);
+    else if (feat == F_MESH) pq_launch_beauty<F_MESH>(per_sm, blocks, stream, P, fix, head, total, batch);
+    else if (feat == F_NOMESH) pq_launch_beauty<F_NOMESH>(per_sm, blocks, stream, P, fix, head, total, batch);
     else if (mode == PQ_AUX) { if (per_sm == 7) PQ_LAUNCH(7, PQ_AUX); else PQ_LAUNCH(6, PQ_AUX); }
     else if (mode == PQ_LIGHT) { if (per_sm == 7) PQ_LAUNCH(7, PQ_LIGHT); else PQ_LAUNCH(6, PQ_LIGHT); }
     else { if (per_sm == 7) PQ_LAUNCH(7, PQ_BEAUTY); else PQ_LAUNCH(6, PQ_BEAUTY); }
 #undef PQ_LAUNCH
-#undef PQ_LAUNCH_F
     return cudaGetLastError();
 }
 
