@@ -93,7 +93,7 @@ __global__ void __launch_bounds__(ZB_BLOCK_THREADS, ZB_MIN_BLOCKS) k_render(cons
             o = P.cam.center;
             if (P.cam.defocus) {
                 float rr = sqrtf(u01(r0.z)), sn, cs;
-                sincospif(2.0f * u01(r0.w), &sn, &cs);
+                sincos_turn(u01(r0.w), &sn, &cs);
                 float3 off = (rr * cs) * P.cam.disk_u + (rr * sn) * P.cam.disk_v;
                 o += off;
                 d = d - off;
@@ -299,6 +299,10 @@ __global__ void __launch_bounds__(ZB_BLOCK_THREADS, MIN_BLOCKS) k_render_pq(cons
     uint32_t pixel = 0, s = 0;
     float3 o = f3(0, 0, 0), d = f3(0, 0, 1), L = f3(0, 0, 0), beta = f3(1, 1, 1);
     unsigned long long w_pos = 0, w_end = 0;  // the warp's batch of path indices (warp-uniform)
+    // exact division of a 32-bit number by n: high word of x * ceil(2^64 / n) (error < 2^-32 of a quotient step); the
+    // two reciprocals cost one 64-bit division each per persistent thread instead of three 32-bit divisions per path
+    const uint32_t tiles_x = uint32_t(P.tiles_x);
+    const unsigned long long m_ns = n_s > 1u ? ~0ull / n_s + 1ull : 0ull, m_tx = tiles_x > 1u ? ~0ull / tiles_x + 1ull : 0ull;
     for (;;) {
         // ---- lanes without a path take the next ones of the warp's batch; out-of-image pixels are skipped
         for (;;) {
@@ -325,7 +329,7 @@ __global__ void __launch_bounds__(ZB_BLOCK_THREADS, MIN_BLOCKS) k_render_pq(cons
                     uint32_t q, sr;
                     if (total <= 0xFFFFFFFFull) {
                         const uint32_t g32 = uint32_t(g);
-                        q = g32 / n_s;
+                        q = n_s > 1u ? uint32_t(__umul64hi(g32, m_ns)) : g32;
                         sr = g32 - q * n_s;
                     } else {
                         const unsigned long long q64 = g / n_s;
@@ -334,7 +338,7 @@ __global__ void __launch_bounds__(ZB_BLOCK_THREADS, MIN_BLOCKS) k_render_pq(cons
                     }
                     const uint32_t u = q >> 5, p = q & 31u;
                     const int tile = int(u >> 2) * P.tile_ranks + P.tile_rank, w = int(u & 3u);
-                    const int tx = tile % P.tiles_x, ty = tile / P.tiles_x;
+                    const int ty = tiles_x > 1u ? int(__umul64hi(uint32_t(tile), m_tx)) : tile, tx = tile - ty * int(tiles_x);
                     const int px = tx * ZB_TILE_W + (w % (ZB_TILE_W / 8)) * 8 + int(p & 7u);
                     const int py = ty * ZB_TILE_H + (w / (ZB_TILE_W / 8)) * 4 + int(p >> 3);
                     if (px < P.cam.width && py < P.cam.height && ty < P.tiles_y) {
@@ -346,7 +350,7 @@ __global__ void __launch_bounds__(ZB_BLOCK_THREADS, MIN_BLOCKS) k_render_pq(cons
                         o = P.cam.center;
                         if (P.cam.defocus) {
                             float rr = sqrtf(u01(r0.z)), sn, cs;
-                            sincospif(2.0f * u01(r0.w), &sn, &cs);
+                            sincos_turn(u01(r0.w), &sn, &cs);
                             const float3 off = (rr * cs) * P.cam.disk_u + (rr * sn) * P.cam.disk_v;
                             o += off;
                             d = d - off;
@@ -494,7 +498,7 @@ __global__ void __launch_bounds__(ZB_BLOCK_THREADS, 6) k_aov_pass(const __grid_c
         float3 o = P.cam.center;
         if (P.cam.defocus) {
             float rr = sqrtf(u01(r0.z)), sn, cs;
-            sincospif(2.0f * u01(r0.w), &sn, &cs);
+            sincos_turn(u01(r0.w), &sn, &cs);
             const float3 off = (rr * cs) * P.cam.disk_u + (rr * sn) * P.cam.disk_v;
             o += off;
             d = d - off;

@@ -179,7 +179,7 @@ ZB_DEV float3 random_unit_vector(float x1, float x2) {
     float z = 1.0f - 2.0f * x1;
     float r = sqrtf(fmaxf(0.f, 1.0f - z * z));
     float s, c;
-    sincospif(2.0f * x2, &s, &c);
+    sincos_turn(x2, &s, &c);
     return f3(r * c, r * s, z);
 }
 

@@ -33,6 +33,14 @@ ZB_DEV float3 unit_vector(float3 v) {
 ZB_DEV float max3(float a, float b, float c) { return fmaxf(a, fmaxf(b, c)); }
 ZB_DEV float min3(float a, float b, float c) { return fminf(a, fminf(b, c)); }
 
+// sin and cos of 2 pi x for x in [0, 1): two MUFU evaluations on the angle moved to [-pi, pi), where their absolute error is
+// ~2^-21 (5 instructions instead of the ~28 of sincospif; the results only steer sampled directions)
+ZB_DEV void sincos_turn(float x, float* s, float* c) {
+    const float a = 6.283185307179586f * (x - 0.5f);
+    *s = -__sinf(a);
+    *c = -__cosf(a);
+}
+
 // row-major 3x4 affine held in three float4 rows
 struct Affine {
     float4 r0, r1, r2;

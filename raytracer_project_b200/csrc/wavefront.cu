@@ -43,7 +43,7 @@ ZB_DEV void wf_camera_ray(const RenderParams& P, const Philox& ph, int px, int p
     o = P.cam.center;
     if (P.cam.defocus) {
         float rr = sqrtf(u01(r0.z)), sn, cs;
-        sincospif(2.0f * u01(r0.w), &sn, &cs);
+        sincos_turn(u01(r0.w), &sn, &cs);
         float3 off = (rr * cs) * P.cam.disk_u + (rr * sn) * P.cam.disk_v;
         o += off;
         d = d - off;

@@ -259,7 +259,7 @@ __global__ void __launch_bounds__(128) k_wireframe(const __grid_constant__ Rende
         float3 o = P.cam.center;
         if (P.cam.defocus) {
             float rr = sqrtf(u01(r0.z)), sn, cs;
-            sincospif(2.0f * u01(r0.w), &sn, &cs);
+            sincos_turn(u01(r0.w), &sn, &cs);
             const float3 off = (rr * cs) * P.cam.disk_u + (rr * sn) * P.cam.disk_v;
             o += off;
             d = d - off;
