@@ -92,7 +92,7 @@ __global__ void __launch_bounds__(ZB_BLOCK_THREADS, ZB_MIN_BLOCKS) k_render(cons
             d = P.cam.pix00_rel + (float(px) + u01(r0.x) - 0.5f) * P.cam.du + (float(py) + u01(r0.y) - 0.5f) * P.cam.dv;
             o = P.cam.center;
             if (P.cam.defocus) {
-                float rr = sqrtf(u01(r0.z)), sn, cs;
+                float rr = sqrt_fast(u01(r0.z)), sn, cs;
                 sincos_turn(u01(r0.w), &sn, &cs);
                 float3 off = (rr * cs) * P.cam.disk_u + (rr * sn) * P.cam.disk_v;
                 o += off;
@@ -349,7 +349,7 @@ __global__ void __launch_bounds__(ZB_BLOCK_THREADS, MIN_BLOCKS) k_render_pq(cons
                         d = P.cam.pix00_rel + (float(px) + u01(r0.x) - 0.5f) * P.cam.du + (float(py) + u01(r0.y) - 0.5f) * P.cam.dv;
                         o = P.cam.center;
                         if (P.cam.defocus) {
-                            float rr = sqrtf(u01(r0.z)), sn, cs;
+                            float rr = sqrt_fast(u01(r0.z)), sn, cs;
                             sincos_turn(u01(r0.w), &sn, &cs);
                             const float3 off = (rr * cs) * P.cam.disk_u + (rr * sn) * P.cam.disk_v;
                             o += off;
@@ -497,7 +497,7 @@ __global__ void __launch_bounds__(ZB_BLOCK_THREADS, 6) k_aov_pass(const __grid_c
         float3 d = P.cam.pix00_rel + (float(px) + u01(r0.x) - 0.5f) * P.cam.du + (float(py) + u01(r0.y) - 0.5f) * P.cam.dv;
         float3 o = P.cam.center;
         if (P.cam.defocus) {
-            float rr = sqrtf(u01(r0.z)), sn, cs;
+            float rr = sqrt_fast(u01(r0.z)), sn, cs;
             sincos_turn(u01(r0.w), &sn, &cs);
             const float3 off = (rr * cs) * P.cam.disk_u + (rr * sn) * P.cam.disk_v;
             o += off;

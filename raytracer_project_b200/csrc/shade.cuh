@@ -21,7 +21,7 @@ ZB_DEV float4 load_mat1(const SceneDev& sc, uint32_t m) { return __ldg(sc.materi
 
 // sphere.hpp:41-58 (outward normal, face flip, uv, tangent frame from the FLIPPED normal)
 ZB_DEV void sphere_surface(float4 s, float3 p, float3 d, Surface& sf, bool want_uv) {
-    float3 on = (1.0f / s.w) * f3(p.x - s.x, p.y - s.y, p.z - s.z);
+    float3 on = __fdividef(1.0f, s.w) * f3(p.x - s.x, p.y - s.y, p.z - s.z);
     sf.front_face = dot(d, on) < 0.f;
     sf.n = sf.front_face ? on : -on;
     if (want_uv) {
@@ -177,7 +177,7 @@ ZB_DEV float3 bumped_normal(const SceneDev& sc, float4 m0, const Surface& sf) {
 // random_unit_vector (vec3.hpp:184-191): uniform on the sphere; direct map instead of rejection
 ZB_DEV float3 random_unit_vector(float x1, float x2) {
     float z = 1.0f - 2.0f * x1;
-    float r = sqrtf(fmaxf(0.f, 1.0f - z * z));
+    float r = sqrt_fast(fmaxf(0.f, 1.0f - z * z));
     float s, c;
     sincos_turn(x2, &s, &c);
     return f3(r * c, r * s, z);

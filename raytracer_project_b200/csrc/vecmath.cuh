@@ -41,6 +41,13 @@ ZB_DEV void sincos_turn(float x, float* s, float* c) {
     *c = -__cosf(a);
 }
 
+// MUFU square root (~1 ulp), for values that only steer sampled directions
+ZB_DEV float sqrt_fast(float x) {
+    float r;
+    asm("sqrt.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
+    return r;
+}
+
 // row-major 3x4 affine held in three float4 rows
 struct Affine {
     float4 r0, r1, r2;

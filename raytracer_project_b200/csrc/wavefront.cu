@@ -42,7 +42,7 @@ ZB_DEV void wf_camera_ray(const RenderParams& P, const Philox& ph, int px, int p
     d = P.cam.pix00_rel + (float(px) + u01(r0.x) - 0.5f) * P.cam.du + (float(py) + u01(r0.y) - 0.5f) * P.cam.dv;
     o = P.cam.center;
     if (P.cam.defocus) {
-        float rr = sqrtf(u01(r0.z)), sn, cs;
+        float rr = sqrt_fast(u01(r0.z)), sn, cs;
         sincos_turn(u01(r0.w), &sn, &cs);
         float3 off = (rr * cs) * P.cam.disk_u + (rr * sn) * P.cam.disk_v;
         o += off;

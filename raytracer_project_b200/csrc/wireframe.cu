@@ -258,7 +258,7 @@ __global__ void __launch_bounds__(128) k_wireframe(const __grid_constant__ Rende
         float3 d = P.cam.pix00_rel + (float(px) + u01(r0.x) - 0.5f) * P.cam.du + (float(py) + u01(r0.y) - 0.5f) * P.cam.dv;
         float3 o = P.cam.center;
         if (P.cam.defocus) {
-            float rr = sqrtf(u01(r0.z)), sn, cs;
+            float rr = sqrt_fast(u01(r0.z)), sn, cs;
             sincos_turn(u01(r0.w), &sn, &cs);
             const float3 off = (rr * cs) * P.cam.disk_u + (rr * sn) * P.cam.disk_v;
             o += off;
