@@ -32,10 +32,10 @@ sys.path.insert(0, ROOT)
 
 WIDTH, HEIGHT, SPP, DEPTH = 1920, 1080, 64, 50
 WORKLOAD = f"weekend_seed1_{WIDTH}x{HEIGHT}_{SPP}spp_depth{DEPTH}"
-# DRAM traffic of one k_render_pq launch on the headline frame (ncu, profiles/r01_k_render_pq_raw_key.txt): 50.3 MB read +
-# 8.0 MB written while the kernel runs — the 60 KB scene is L1-resident; the traffic is the 50 MB of 64-bit fixed-point
+# DRAM traffic of one k_render_pq launch on the headline frame (ncu, profiles/r01_k_render_pq_plain_final_raw_key.txt): 50.3 MB read +
+# 5.1 MB written while the kernel runs — the 60 KB scene is L1-resident; the traffic is the 50 MB of 64-bit fixed-point
 # per-pixel sums (zeroed before the launch, RED.ADDed in L2) entering and partly leaving the 126 MB L2.
-NCU_DRAM_BYTES_PER_LAUNCH = 50284288 + 7954944
+NCU_DRAM_BYTES_PER_LAUNCH = 50264576 + 5082368
 HARNESS = os.path.join(ROOT, "oracle", "_ref", "ref_harness")   # the unmodified reference (kind "reference")
 PORT = os.path.join(ROOT, "oracle", "_build", "zoracle")         # CPU restatement, used only if the former is absent
 
@@ -292,9 +292,9 @@ def ours(args):
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": hbm_peak, "unit": "GB/s", "frac": achieved / hbm_peak,
                          "traffic": NCU_DRAM_BYTES_PER_LAUNCH if world == 1 else None,
                          "traffic_source": "dram__bytes_read.sum + dram__bytes_write.sum of k_render_pq on this workload, "
-                                           "ncu --set full capture summarised in profiles/r01_k_render_pq_raw_key.txt",
+                                           "ncu --set full capture summarised in profiles/r01_k_render_pq_plain_final_raw_key.txt",
                          "peak_kind": f"{peak_kind} burst copy bandwidth",
-                         "kernel": "k_render_pq<8, BEAUTY, LEAN>", "algorithmic_bytes_per_launch": per_gpu_bytes,
+                         "kernel": "k_render_pq<8, PQ_BEAUTY, PLAIN>", "algorithmic_bytes_per_launch": per_gpu_bytes,
                          "note": "scene (60 KB) is L1/L2-resident: algorithmic bytes are served by L1, so this "
                                  "fraction can exceed 1; the binding roofline is FP32/issue (roofline_fp32)"},
             "roofline_fp32": {"achieved": alg_flop / world / (kernel_ms * 1e-3) * 1e-12, "peak": fp32_peak,
