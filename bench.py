@@ -36,6 +36,9 @@ WORKLOAD = f"weekend_seed1_{WIDTH}x{HEIGHT}_{SPP}spp_depth{DEPTH}"
 # 5.1 MB written while the kernel runs — the 60 KB scene is L1-resident; the traffic is the 50 MB of 64-bit fixed-point
 # per-pixel sums (zeroed before the launch, RED.ADDed in L2) entering and partly leaving the 126 MB L2.
 NCU_DRAM_BYTES_PER_LAUNCH = 50264576 + 5082368
+# warp instructions of the same launch (smsp__inst_executed.sum, same capture); the kernel is bound by instruction issue
+# (4 schedulers per SM, one warp instruction per cycle each), so this is the roofline that explains `value`
+NCU_WARP_INST_PER_LAUNCH = 23784447142
 HARNESS = os.path.join(ROOT, "oracle", "_ref", "ref_harness")   # the unmodified reference (kind "reference")
 PORT = os.path.join(ROOT, "oracle", "_build", "zoracle")         # CPU restatement, used only if the former is absent
 
@@ -296,9 +299,16 @@ def ours(args):
                          "peak_kind": f"{peak_kind} burst copy bandwidth",
                          "kernel": "k_render_pq<8, PQ_BEAUTY, PLAIN>", "algorithmic_bytes_per_launch": per_gpu_bytes,
                          "note": "scene (60 KB) is L1/L2-resident: algorithmic bytes are served by L1, so this "
-                                 "fraction can exceed 1; the binding roofline is FP32/issue (roofline_fp32)"},
+                                 "fraction can exceed 1; the binding roofline is instruction issue (roofline_issue, roofline_fp32)"},
             "roofline_fp32": {"achieved": alg_flop / world / (kernel_ms * 1e-3) * 1e-12, "peak": fp32_peak,
                               "unit": "TFLOP/s", "frac": alg_flop / world / (kernel_ms * 1e-3) * 1e-12 / fp32_peak},
+            "roofline_issue": ({"achieved": NCU_WARP_INST_PER_LAUNCH / (kernel_ms * 1e-3) * 1e-9,
+                                "peak": info["sm_count"] * 4 * sm_max * 1e6 * 1e-9, "unit": "G warp-inst/s",
+                                "frac": NCU_WARP_INST_PER_LAUNCH / (kernel_ms * 1e-3) / (info["sm_count"] * 4 * sm_max * 1e6),
+                                "lanes_per_instruction": 15.13,
+                                "source": "smsp__inst_executed.sum of one k_render_pq launch on this workload "
+                                          "(profiles/r01_k_render_pq_plain_final_raw_key.txt) / live kernel time"}
+                               if world == 1 else None),
             "clocks": clocks,
             "mean_radiance": mean_gpu,
             "wall_ms_per_step_incl_flush": (t_wall1 - t_wall0) * 1e3 / args.steps,

@@ -18,6 +18,9 @@
 // Slab tests use MUFU.RCP reciprocals (~1 ulp) of the ray direction; the far distance is inflated by
 // 10 ulp so that the box test stays conservative (Ize 2013).  Measured -2 % frame time vs IEEE divides.
 #define ZB_BOX_INFLATE 1.0000012f
+#ifndef ZB_BRANCHLESS_POP
+#define ZB_BRANCHLESS_POP 0  // measured: Weekend +7 % time, mesh -1.3 % (profiles/r01_feature_sets.txt)
+#endif
 #define ZB_EXIT_INSTANCE ((int)0x80000000)
 
 struct Hit {
@@ -322,12 +325,22 @@ struct RayWalk {
         const int cl = __float_as_int(nc.x), cr = __float_as_int(nc.y);
         const bool right_first = hr && (!hl || rn < ln);
         int next = right_first ? cr : cl;
+#if ZB_BRANCHLESS_POP
+        // push and pop without a divergent branch (and its convergence barrier): a predicated store of the far child, an
+        // unconditional load of the slot below the top (in bounds: the sentinel keeps sp >= 1), selects for sp and cur
+        const bool any = hl || hr, both = hl && hr;
+        if (both) stack[sp] = right_first ? cl : cr;
+        const int top = stack[sp - 1];
+        sp = both ? min(sp + 1, ZB_STACK - 1) : any ? sp : sp - 1;  // deeper than any tree the host builder emits (bvh_build.hpp)
+        cur = any ? next : top;
+#else
         if (hl && hr) {
             stack[sp] = right_first ? cl : cr;
-            sp = min(sp + 1, ZB_STACK - 1);  // deeper than any tree the host builder emits (bvh_build.hpp)
+            sp = min(sp + 1, ZB_STACK - 1);
         }
         if (!(hl || hr)) next = stack[--sp];
         cur = next;
+#endif
     }
 
     // (o, d) is the world-space ray given to begin()
