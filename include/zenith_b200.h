@@ -391,6 +391,24 @@ int zb_flat_scene_from_zscene_text(const char* text, size_t len, const zb_flat_s
  * meshes drops from seconds to milliseconds, at a lower tree quality.  Exactly one of path / text is given. */
 #define ZB_FLATTEN_GPU_BLAS 1u
 int zb_flat_scene_from_zscene_ex(const char* path, const char* text, size_t len, uint32_t flags, const zb_flat_scene** out);
+/* Scene features (SceneDev::features; template parameter F of the render kernels, csrc/trace.cuh, shade.cuh, kernels.cu).
+ * The render kernel is compiled for several feature sets: code for item kinds, textures and environments a scene does
+ * not use is left out, which shrinks the kernel (instruction-cache misses were 1.07 stall cycles per issue in the
+ * 5.8 k-instruction general kernel) and its register count.  A launch picks the smallest compiled superset of the
+ * scene's bits.  No counterpart in the reference (virtual dispatch over shared_ptr<hittable> / <material>). */
+enum {
+    ZB_F_INST = 1,   /* instance items (translate / rotate / scale chains)                   */
+    ZB_F_MESH = 2,   /* mesh instances: BLAS traversal in object space                       */
+    ZB_F_CUBE = 4,   /* cubes (items, instanced, or medium boundaries)                       */
+    ZB_F_TRI = 8,    /* triangles (loose items, instanced, or mesh faces)                    */
+    ZB_F_MEDIA = 16, /* constant_medium items, isotropic phase function                      */
+    ZB_F_TEX = 32,   /* textured or bump-mapped materials                                    */
+    ZB_F_ENV = 64,   /* HDR-map or physical-sun environment (0: solid colour); per render    */
+    ZB_F_GEOM = 1 | 2 | 4 | 8 | 16, /* none of these: every item is an inline sphere         */
+    ZB_F_ALL = 127
+};
+/* The ZB_F_* bits a flattened scene needs (all but ZB_F_ENV, which depends on the render's environment). Host only. */
+int zb_flat_scene_features(const zb_flat_scene* flat, uint32_t* features);
 /* Flat scene on disk ("ZBFS" container): written once, loaded by every rank / later run without
  * re-parsing assets or re-building the BVH.  A loaded scene is released with zb_flat_scene_free. */
 int zb_flat_scene_save(const zb_flat_scene* flat, const char* path);

@@ -145,6 +145,7 @@ SYMBOLS = {
     "zb_flat_scene_from_zscene": (C.c_int, [C.c_char_p, C.POINTER(C.POINTER(FlatScene))]),
     "zb_flat_scene_from_zscene_text": (C.c_int, [C.c_char_p, C.c_size_t, C.POINTER(C.POINTER(FlatScene))]),
     "zb_flat_scene_from_zscene_ex": (C.c_int, [C.c_char_p, C.c_char_p, C.c_size_t, C.c_uint32, C.POINTER(C.POINTER(FlatScene))]),
+    "zb_flat_scene_features": (C.c_int, [C.POINTER(FlatScene), C.POINTER(C.c_uint32)]),
     "zb_flat_scene_save": (C.c_int, [C.POINTER(FlatScene), C.c_char_p]),
     "zb_flat_scene_load": (C.c_int, [C.c_char_p, C.POINTER(C.POINTER(FlatScene))]),
     "zb_flat_scene_free": (C.c_int, [C.POINTER(FlatScene)]),

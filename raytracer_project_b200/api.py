@@ -32,6 +32,16 @@ def flatten_zscene(text: str | None = None, path: str | None = None, gpu_blas: b
     return out
 
 
+FEATURES = {"INST": 1, "MESH": 2, "CUBE": 4, "TRI": 8, "MEDIA": 16, "TEX": 32, "ENV": 64}
+
+
+def flat_features(flat) -> int:
+    """zb_flat_scene_features: the ZB_F_* bits the scene needs (the render kernel runs the smallest compiled superset)."""
+    out = C.c_uint32(0)
+    check(_lib.load().zb_flat_scene_features(flat, C.byref(out)))
+    return out.value
+
+
 def save_flat(flat, path: str):
     """zb_flat_scene_save: the flattened scene as a ZBFS file."""
     check(_lib.load().zb_flat_scene_save(flat, path.encode()))

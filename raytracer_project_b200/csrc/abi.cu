@@ -251,24 +251,9 @@ extern "C" int zb_scene_upload(zb_context* ctx, const zb_flat_scene* f, zb_scene
     }
     d.n_items = f->n_items;
     d.n_media = f->n_media;
-    // scene features (ZB_F_*, scene_dev.cuh): which code a render kernel has to carry for this scene
-    uint32_t feat = 0;
-    for (uint32_t i = 0; i < f->n_items; i++) {
-        const uint32_t kind = f->items[i].kind_flags & 0xFFu;
-        feat |= kind == ZB_ITEM_INSTANCE ? ZB_F_INST : kind == ZB_ITEM_CUBE ? ZB_F_CUBE : kind == ZB_ITEM_TRIANGLE ? ZB_F_TRI
-              : kind == ZB_ITEM_MEDIUM ? ZB_F_MEDIA : 0u;
-    }
-    for (uint32_t i = 0; i < f->n_instances; i++) {
-        const uint32_t g = f->instances[i].geom_kind;
-        feat |= g == ZB_GEOM_MESH ? uint32_t(ZB_F_MESH | ZB_F_TRI) : g == ZB_GEOM_CUBE ? ZB_F_CUBE : g == ZB_GEOM_TRIANGLE ? ZB_F_TRI : 0u;
-    }
-    for (uint32_t i = 0; i < f->n_media; i++) {
-        const uint32_t k = f->media[i].boundary_kind;
-        feat |= ZB_F_MEDIA | (k == ZB_ITEM_CUBE ? ZB_F_CUBE : k == ZB_ITEM_INSTANCE ? ZB_F_INST : 0u);
-    }
-    for (uint32_t i = 0; i < f->n_materials; i++)
-        if (f->materials[i].albedo_tex != ZB_NO_TEXTURE || f->materials[i].bump_tex != ZB_NO_TEXTURE) feat |= ZB_F_TEX;
-    d.features = feat;
+    // scene features (ZB_F_*): which code a render kernel has to carry for this scene
+    d.features = 0;
+    zb_flat_scene_features(f, &d.features);
     s->env_hdr_texture = f->pad;
     ZB_CUDA(cudaStreamSynchronize(ctx->stream));  // host arrays may be freed by the caller on return
     *out = s;

@@ -110,6 +110,28 @@ template <class T> bool get(std::ifstream& f, std::vector<T>& v) {
 template <class T> std::vector<T> span_of(const T* p, uint64_t n) { return p && n ? std::vector<T>(p, p + n) : std::vector<T>(); }
 }  // namespace
 
+extern "C" int zb_flat_scene_features(const zb_flat_scene* f, uint32_t* features) {
+    if (!f || !features) return fail_host(ZB_ERR_INVALID, "zb_flat_scene_features: NULL argument");
+    uint32_t feat = 0;
+    for (uint32_t i = 0; i < f->n_items; i++) {
+        const uint32_t kind = f->items[i].kind_flags & 0xFFu;
+        feat |= kind == ZB_ITEM_INSTANCE ? ZB_F_INST : kind == ZB_ITEM_CUBE ? ZB_F_CUBE : kind == ZB_ITEM_TRIANGLE ? ZB_F_TRI
+              : kind == ZB_ITEM_MEDIUM ? ZB_F_MEDIA : 0u;
+    }
+    for (uint32_t i = 0; i < f->n_instances; i++) {
+        const uint32_t g = f->instances[i].geom_kind;
+        feat |= g == ZB_GEOM_MESH ? uint32_t(ZB_F_MESH | ZB_F_TRI) : g == ZB_GEOM_CUBE ? ZB_F_CUBE : g == ZB_GEOM_TRIANGLE ? ZB_F_TRI : 0u;
+    }
+    for (uint32_t i = 0; i < f->n_media; i++) {
+        const uint32_t k = f->media[i].boundary_kind;
+        feat |= ZB_F_MEDIA | (k == ZB_ITEM_CUBE ? ZB_F_CUBE : k == ZB_ITEM_INSTANCE ? ZB_F_INST : 0u);
+    }
+    for (uint32_t i = 0; i < f->n_materials; i++)
+        if (f->materials[i].albedo_tex != ZB_NO_TEXTURE || f->materials[i].bump_tex != ZB_NO_TEXTURE) feat |= ZB_F_TEX;
+    *features = feat;
+    return ZB_OK;
+}
+
 extern "C" int zb_flat_scene_save(const zb_flat_scene* v, const char* path) {
     if (!v || !path) return fail_host(ZB_ERR_INVALID, "zb_flat_scene_save: NULL argument");
     std::ofstream f(path, std::ios::binary);

@@ -278,7 +278,7 @@ enum { PQ_BEAUTY = 0, PQ_AUX = 1, PQ_LIGHT = 2 };
 
 ZB_DEV void gfix_add(unsigned long long* slot, float v) { atomicAdd(slot, __float2ull_rn(fmaxf(v, 0.f) * ZB_FIX_SCALE)); }
 
-// F: scene features compiled in (ZB_F_*, scene_dev.cuh); zbk_launch_render_pq picks the smallest instantiation that covers
+// F: scene features compiled in (ZB_F_*, include/zenith_b200.h); zbk_launch_render_pq picks the smallest instantiation that covers
 // SceneDev::features and the environment of the render
 template <int MIN_BLOCKS, int MODE, uint32_t F = ZB_F_ALL>
 __global__ void __launch_bounds__(ZB_BLOCK_THREADS, MIN_BLOCKS) k_render_pq(const __grid_constant__ RenderParams P,
@@ -712,7 +712,7 @@ cudaError_t zbk_launch_render_pq(const RenderParams& P, int n_tiles_owned, int m
     unsigned long long* fix_aux = mode == PQ_BEAUTY ? nullptr : fix + 3 * pixels;
     const unsigned long long total = (unsigned long long)n_tiles_owned * 4ull * 32ull * (unsigned long long)(P.sample_end - P.sample_begin);
     const unsigned long long warps_needed = (total + 31) / 32;
-    // Beauty renders run the smallest compiled feature set that covers the scene and its environment (ZB_F_*, scene_dev.cuh):
+    // Beauty renders run the smallest compiled feature set that covers the scene and its environment (ZB_F_*, include/zenith_b200.h):
     //   PLAIN   inline spheres, untextured materials, solid-colour environment (Weekend)
     //   BOXES   + loose triangles, cubes, instances of them, media (Cornell)
     //   MESH0   instances, meshes, triangles (spheres + large mesh), MESH: + textures (mesh config with the material library)

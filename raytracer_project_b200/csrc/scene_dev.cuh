@@ -2,24 +2,10 @@
 // All arrays are read-only for the whole render and are fetched through the non-coherent path
 // (__ldg, 16-byte vectors).  Layouts are the zb_* PODs of include/zenith_b200.h viewed as float4s.
 #pragma once
+#include "../../include/zenith_b200.h"
 #include "vecmath.cuh"
 
-// Scene features a kernel instantiation is compiled for (template parameter F of trace / make_surface / material_*):
-// code for item kinds, textures and environments a scene does not use is left out, which shrinks the render kernel
-// (instruction-cache misses were 1.07 stall cycles per issue in the 5.8 k-instruction general kernel) and its register
-// count.  SceneDev::features holds the bits a scene needs; a launch picks the smallest compiled superset.
-enum : uint32_t {
-    ZB_F_INST = 1,    // instance items (translate / rotate / scale chains)
-    ZB_F_MESH = 2,    // mesh instances: BLAS traversal in object space
-    ZB_F_CUBE = 4,    // cubes (items, instanced, or medium boundaries)
-    ZB_F_TRI = 8,     // triangles (loose items, instanced, or mesh faces)
-    ZB_F_MEDIA = 16,  // constant_medium items, isotropic phase function
-    ZB_F_TEX = 32,    // textured or bump-mapped materials
-    ZB_F_ENV = 64,    // HDR-map or physical-sun environment (0: solid colour)
-    ZB_F_GEOM = ZB_F_INST | ZB_F_MESH | ZB_F_CUBE | ZB_F_TRI | ZB_F_MEDIA,  // none of these: every item is an inline sphere
-    ZB_F_ALL = 127
-};
-
+// ZB_F_* scene-feature bits: include/zenith_b200.h
 struct SceneDev {
     const float4* nodes;        // 4 x float4 per zb_bvh_node (64 B)
     const float4* items;        // 2 x float4 per zb_item (32 B)

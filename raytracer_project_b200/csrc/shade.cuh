@@ -82,7 +82,7 @@ ZB_DEV void tri_surface(const SceneDev& sc, uint32_t tri, float3 o, float3 d, Su
 }
 
 // Rebuild the reference's final hit_record for the winning item.
-// F: the scene features compiled in (ZB_F_*, scene_dev.cuh)
+// F: the scene features compiled in (ZB_F_*, include/zenith_b200.h)
 template <uint32_t F = ZB_F_ALL>
 ZB_DEV void make_surface(const SceneDev& sc, const Hit& hit, float3 o, float3 d, Surface& sf, bool force_uv = false) {
     float4 g = __ldg(sc.items + 2 * size_t(hit.item));

@@ -108,6 +108,31 @@ def test_flatten_wrappers_and_flags():
     api.free_flat(flat)
 
 
+def test_scene_feature_bits(tmp_path):
+    """zb_flat_scene_features: the ZB_F_* bits that select the render-kernel instantiation (smallest compiled superset).
+    Weekend (BASELINE C1 / headline) must be PLAIN = 0: inline spheres, untextured materials."""
+    F = api.FEATURES
+    cases = {
+        "weekend": (scenes.weekend(seed=1, width=64, height=36, spp=1), 0),
+        "cornell": (scenes.cornell(width=64, height=36, spp=1), F["INST"] | F["CUBE"] | F["TRI"] | F["MEDIA"]),
+        "mesh": (scenes.mesh(width=64, height=36, spp=1, grid=24, knots=2), F["INST"] | F["MESH"] | F["TRI"]),
+    }
+    for name, (out, want) in cases.items():
+        txt, cfg = out[0], out[1]
+        if len(out) > 2 and out[2]:
+            flat = api.flatten_zscene(path=scenes.materialize(str(tmp_path / name), txt, cfg, out[2]))
+        else:
+            flat = api.flatten_zscene(txt)
+        got = api.flat_features(flat)
+        api.free_flat(flat)
+        assert got == want, (name, got, want)
+    txt, cfg, files = scenes.exterior(width=64, height=36, spp=1, small=20)
+    flat = api.flatten_zscene(path=scenes.materialize(str(tmp_path / "exterior"), txt, cfg, files))
+    got = api.flat_features(flat)
+    api.free_flat(flat)
+    assert got & F["TEX"] and not got & (F["MESH"] | F["ENV"]), got  # ENV is per render, never a scene bit
+
+
 def test_zscene_errors_are_reported():
     with pytest.raises(_lib.ZbError) as e:
         api.flatten_zscene("obj a sphere 0 0 0 1 nomat\nworld a\n")
