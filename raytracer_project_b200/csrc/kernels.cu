@@ -42,7 +42,8 @@ ZB_DEV float fix_get(unsigned long long v) { return float(double((long long)v) *
 // (same termination rules), the luma clamp 0.2126 |c| <= 2, and the split by direction — "specular" when the
 // scattered direction is within acos(0.9) of the mirror direction, "transmitted" when it crosses the surface.
 // Reflection sums go to accum, refraction sums to plane 0 of accum_aux.
-template <bool STATS, bool LIGHT>
+// F: scene features compiled in (ZB_F_*, include/zenith_b200.h); the light passes run the smallest covering set
+template <bool STATS, bool LIGHT, uint32_t F = ZB_F_ALL>
 __global__ void __launch_bounds__(ZB_BLOCK_THREADS, ZB_MIN_BLOCKS) k_render(const __grid_constant__ RenderParams P) {
     constexpr int WARPS = ZB_BLOCK_THREADS / 32;
     __shared__ unsigned long long s_sum[WARPS][32][3];
@@ -114,7 +115,7 @@ __global__ void __launch_bounds__(ZB_BLOCK_THREADS, ZB_MIN_BLOCKS) k_render(cons
         Hit hit;
         {
             MediumRng mr{ph, pixel, s, uint32_t(seg + 1)};
-            trace<STATS>(P.sc, o, d, 0.001f, INFINITY, mr, hit, cnt);
+            trace<STATS, F>(P.sc, o, d, 0.001f, INFINITY, mr, hit, cnt);
         }
         {
             // ---- K3 shade: one segment of ray_color (camera.hpp:928-1004)
@@ -125,11 +126,11 @@ __global__ void __launch_bounds__(ZB_BLOCK_THREADS, ZB_MIN_BLOCKS) k_render(cons
                 done = true;
                 if (hit.item != 0xFFFFFFFFu) {
                     Surface sf;
-                    make_surface(P.sc, hit, o, d, sf);
+                    make_surface<F>(P.sc, hit, o, d, sf);
                     uint4 rb = ph(pixel, s, 1u, 0u);
                     float3 no, nd;
                     first_atten = f3(1, 1, 1);
-                    if (material_scatter(P.sc, sf, d, f3(u01(rb.x), u01(rb.y), u01(rb.z)), first_atten, no, nd)) {
+                    if (material_scatter<F>(P.sc, sf, d, f3(u01(rb.x), u01(rb.y), u01(rb.z)), first_atten, no, nd)) {
                         float3 ud = unit_vector(d), un = unit_vector(sf.n);
                         float3 mirror = fma3(-2.0f * dot(ud, un), un, ud);
                         if (dot(unit_vector(nd), mirror) > 0.9f) light_class = 1;
@@ -143,7 +144,7 @@ __global__ void __launch_bounds__(ZB_BLOCK_THREADS, ZB_MIN_BLOCKS) k_render(cons
                     }
                 }
             } else if (hit.item == 0xFFFFFFFFu) {
-                L += beta * background(P.sc, P.env, d);
+                L += beta * ((F & ZB_F_ENV) ? background(P.sc, P.env, d) : P.env.background);
                 if (!LIGHT && seg == 0 && aux_on && int(s) < P.aux_samples && P.use_normal) {  // camera.hpp:518-526
                     fix_add(&s_aux[warp][p][3], 0.5f);
                     fix_add(&s_aux[warp][p][4], 0.5f);
@@ -152,10 +153,10 @@ __global__ void __launch_bounds__(ZB_BLOCK_THREADS, ZB_MIN_BLOCKS) k_render(cons
                 done = true;
             } else {
                 Surface sf;
-                make_surface(P.sc, hit, o, d, sf);
+                make_surface<F>(P.sc, hit, o, d, sf);
                 if (!LIGHT && seg == 0 && aux_on && int(s) < P.aux_samples) {  // K8 first-hit AOVs (camera.hpp:464-488)
                     if (P.use_albedo) {
-                        float3 a = material_get_albedo(P.sc, sf);
+                        float3 a = material_get_albedo<F>(P.sc, sf);
                         fix_add(&s_aux[warp][p][0], a.x);
                         fix_add(&s_aux[warp][p][1], a.y);
                         fix_add(&s_aux[warp][p][2], a.z);
@@ -168,10 +169,10 @@ __global__ void __launch_bounds__(ZB_BLOCK_THREADS, ZB_MIN_BLOCKS) k_render(cons
                     }
                     if (P.use_z) fix_add(&s_aux[warp][p][6], 1.0f - clamp01(hit.t * P.inv_z_max));
                 }
-                L += beta * material_emitted(P.sc, sf);
+                L += beta * material_emitted<F>(P.sc, sf);
                 uint4 rb = ph(pixel, s, uint32_t(seg + 1), 0u);
                 float3 atten = f3(1, 1, 1), no, nd;
-                done = !material_scatter(P.sc, sf, d, f3(u01(rb.x), u01(rb.y), u01(rb.z)), atten, no, nd);
+                done = !material_scatter<F>(P.sc, sf, d, f3(u01(rb.x), u01(rb.y), u01(rb.z)), atten, no, nd);
                 if (!done) {
                     beta *= atten;
                     o = no;
@@ -480,6 +481,7 @@ __global__ void __launch_bounds__(ZB_BLOCK_THREADS, MIN_BLOCKS) k_render_pq(cons
 // beauty pass, so the same primary hit — and sums albedo, view-space normal and z in 64-bit fixed point in registers
 // (the same integers k_render adds up in shared memory, so the planes are bit-identical to its output).  Primary rays
 // of an 8x4 sub-tile at the same sample index are coherent: 133 M of them cost ~3 ms on the headline frame.
+template <uint32_t F>
 __global__ void __launch_bounds__(ZB_BLOCK_THREADS, 6) k_aov_pass(const __grid_constant__ RenderParams P) {
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int tile = blockIdx.x * P.tile_ranks + P.tile_rank;
@@ -505,15 +507,15 @@ __global__ void __launch_bounds__(ZB_BLOCK_THREADS, 6) k_aov_pass(const __grid_c
         }
         Hit hit;
         const MediumRng mr{ph, pixel, uint32_t(s), 1u};
-        trace<false>(P.sc, o, d, 0.001f, INFINITY, mr, hit, cnt);
+        trace<false, F>(P.sc, o, d, 0.001f, INFINITY, mr, hit, cnt);
         if (hit.item == 0xFFFFFFFFu) {
             if (P.use_normal) { add(3, 0.5f); add(4, 0.5f); add(5, 1.0f); }  // camera.hpp:518-526
             continue;
         }
         Surface sf;
-        make_surface(P.sc, hit, o, d, sf);
+        make_surface<F>(P.sc, hit, o, d, sf);
         if (P.use_albedo) {
-            const float3 a = material_get_albedo(P.sc, sf);
+            const float3 a = material_get_albedo<F>(P.sc, sf);
             add(0, a.x); add(1, a.y); add(2, a.z);
         }
         if (P.use_normal) {
@@ -671,11 +673,41 @@ __global__ void __launch_bounds__(256) k_resolve(const float4* __restrict__ accu
     }
 }
 
+// Feature sets the render kernels are compiled for (ZB_F_*, include/zenith_b200.h), smallest first:
+//   PLAIN   inline spheres, untextured materials, solid-colour environment (Weekend)
+//   BOXES   + loose triangles, cubes, instances of them, media (Cornell)
+//   MESH0   instances, meshes, triangles (mesh configs), MESH: + textures
+//   NOMESH  everything but meshes and triangles (exterior: HDR map, bump maps, instanced cubes / spheres, media)
+// ZB_NO_LEAN=1 forces the general kernels (A/B runs, equality tests).
+namespace {
+constexpr uint32_t F_PLAIN = 0, F_BOXES = ZB_F_INST | ZB_F_CUBE | ZB_F_TRI | ZB_F_MEDIA, F_MESH0 = ZB_F_INST | ZB_F_MESH | ZB_F_TRI,
+                   F_MESH = F_MESH0 | ZB_F_TEX, F_NOMESH = ZB_F_ALL & ~(ZB_F_MESH | ZB_F_TRI);
+uint32_t pick_feature_set(const RenderParams& P) {
+    if (getenv("ZB_NO_LEAN") && atoi(getenv("ZB_NO_LEAN")) != 0) return ZB_F_ALL;
+    const uint32_t need = (P.sc.features & ZB_F_ALL) | (P.env.mode == ZB_ENV_SOLID_COLOR ? 0u : uint32_t(ZB_F_ENV));
+    for (uint32_t f : {F_PLAIN, F_BOXES, F_MESH0, F_MESH, F_NOMESH})
+        if ((need & ~f) == 0) return f;
+    return ZB_F_ALL;
+}
+}  // namespace
+#define ZB_FOR_FEATURE_SET(feat, CALL)                                      \
+    switch (feat) {                                                         \
+        case F_PLAIN: { constexpr uint32_t F = F_PLAIN; CALL; } break;      \
+        case F_BOXES: { constexpr uint32_t F = F_BOXES; CALL; } break;      \
+        case F_MESH0: { constexpr uint32_t F = F_MESH0; CALL; } break;      \
+        case F_MESH: { constexpr uint32_t F = F_MESH; CALL; } break;        \
+        case F_NOMESH: { constexpr uint32_t F = F_NOMESH; CALL; } break;    \
+        default: { constexpr uint32_t F = ZB_F_ALL; CALL; } break;          \
+    }
+
 cudaError_t zbk_launch_render(const RenderParams& P, int n_tiles_owned, bool stats, cudaStream_t stream) {
     if (n_tiles_owned <= 0) return cudaSuccess;
     // A shared-memory ray-pool variant of this kernel was measured 20-40 % slower on the headline frame
     // (profiles/r01_pool_vs_queue.txt) and removed.
-    if (P.light_pass) k_render<false, true><<<n_tiles_owned, ZB_BLOCK_THREADS, 0, stream>>>(P);
+    if (P.light_pass) {
+        const uint32_t feat = pick_feature_set(P);
+        ZB_FOR_FEATURE_SET(feat, (k_render<false, true, F><<<n_tiles_owned, ZB_BLOCK_THREADS, 0, stream>>>(P)));
+    }
     else if (stats) k_render<true, false><<<n_tiles_owned, ZB_BLOCK_THREADS, 0, stream>>>(P);
     else k_render<false, false><<<n_tiles_owned, ZB_BLOCK_THREADS, 0, stream>>>(P);
     return cudaGetLastError();
@@ -712,20 +744,10 @@ cudaError_t zbk_launch_render_pq(const RenderParams& P, int n_tiles_owned, int m
     unsigned long long* fix_aux = mode == PQ_BEAUTY ? nullptr : fix + 3 * pixels;
     const unsigned long long total = (unsigned long long)n_tiles_owned * 4ull * 32ull * (unsigned long long)(P.sample_end - P.sample_begin);
     const unsigned long long warps_needed = (total + 31) / 32;
-    // Beauty renders run the smallest compiled feature set that covers the scene and its environment (ZB_F_*, include/zenith_b200.h):
-    //   PLAIN   inline spheres, untextured materials, solid-colour environment (Weekend)
-    //   BOXES   + loose triangles, cubes, instances of them, media (Cornell)
-    //   MESH0   instances, meshes, triangles (spheres + large mesh), MESH: + textures (mesh config with the material library)
-    //   NOMESH  everything but meshes and triangles (exterior: HDR map, bump maps, instanced cubes / spheres, media)
-    // ZB_NO_LEAN=1 forces the general kernel (A/B runs, equality tests); ZB_PQ_BLOCKS=5..8 overrides the resident blocks per SM.
-    constexpr uint32_t F_PLAIN = 0, F_BOXES = ZB_F_INST | ZB_F_CUBE | ZB_F_TRI | ZB_F_MEDIA, F_MESH0 = ZB_F_INST | ZB_F_MESH | ZB_F_TRI,
-                       F_MESH = F_MESH0 | ZB_F_TEX, F_NOMESH = ZB_F_ALL & ~(ZB_F_MESH | ZB_F_TRI);
-    const bool no_lean = getenv("ZB_NO_LEAN") && atoi(getenv("ZB_NO_LEAN")) != 0;
+    // beauty renders run the smallest compiled feature set that covers the scene and its environment (pick_feature_set);
+    // ZB_PQ_BLOCKS=5..10 overrides the resident blocks per SM of the specialised instantiations
     const int env_blocks = getenv("ZB_PQ_BLOCKS") ? atoi(getenv("ZB_PQ_BLOCKS")) : 0;
-    const uint32_t need = (P.sc.features & ZB_F_ALL) | (P.env.mode == ZB_ENV_SOLID_COLOR ? 0u : uint32_t(ZB_F_ENV));
-    auto covers = [&](uint32_t f) { return !no_lean && mode == PQ_BEAUTY && (need & ~f) == 0; };
-    const uint32_t feat = covers(F_PLAIN) ? F_PLAIN : covers(F_BOXES) ? F_BOXES : covers(F_MESH0) ? F_MESH0 : covers(F_MESH) ? F_MESH
-                        : covers(F_NOMESH) ? F_NOMESH : uint32_t(ZB_F_ALL);
+    const uint32_t feat = mode == PQ_BEAUTY ? pick_feature_set(P) : uint32_t(ZB_F_ALL);
     const bool big_tree = P.sc.n_nodes >= PQ_BIG_TREE_NODES;
     // resident blocks per SM, measured per feature set at 1080p x 16 spp with 5 / 6 / 7 / 8 blocks (profiles/r01_feature_sets.txt):
     // Cornell 15.31 / 14.42 / 14.14 / 14.07 ms, exterior 18.74 / 18.17 / 17.42 / 17.83, mesh 17.95 / 16.86 / 16.67 / 16.04
@@ -738,11 +760,7 @@ cudaError_t zbk_launch_render_pq(const RenderParams& P, int n_tiles_owned, int m
     const unsigned long long per_warp = total / (4ull * blocks);
     const unsigned batch = per_warp >= 64ull * PQ_BATCH ? PQ_BATCH : per_warp >= 64ull * (PQ_BATCH / 2) ? PQ_BATCH / 2 : PQ_BATCH / 4;
 #define PQ_LAUNCH(B, M) k_render_pq<B, M><<<blocks, ZB_BLOCK_THREADS, 0, stream>>>(P, fix, fix_aux, head, total, batch)
-    if (feat == F_PLAIN) pq_launch_beauty<F_PLAIN>(per_sm, blocks, stream, P, fix, head, total, batch);
-    else if (feat == F_BOXES) pq_launch_beauty<F_BOXES>(per_sm, blocks, stream, P, fix, head, total, batch);
-    else if (feat == F_MESH0) pq_launch_beauty<F_MESH0>(per_sm, blocks, stream, P, fix, head, total, batch);
-    else if (feat == F_MESH) pq_launch_beauty<F_MESH>(per_sm, blocks, stream, P, fix, head, total, batch);
-    else if (feat == F_NOMESH) pq_launch_beauty<F_NOMESH>(per_sm, blocks, stream, P, fix, head, total, batch);
+    if (feat != ZB_F_ALL) { ZB_FOR_FEATURE_SET(feat, (pq_launch_beauty<F>(per_sm, blocks, stream, P, fix, head, total, batch))); }
     else if (mode == PQ_AUX) { if (per_sm == 7) PQ_LAUNCH(7, PQ_AUX); else PQ_LAUNCH(6, PQ_AUX); }
     else if (mode == PQ_LIGHT) { if (per_sm == 7) PQ_LAUNCH(7, PQ_LIGHT); else PQ_LAUNCH(6, PQ_LIGHT); }
     else { if (per_sm == 7) PQ_LAUNCH(7, PQ_BEAUTY); else PQ_LAUNCH(6, PQ_BEAUTY); }
@@ -752,7 +770,8 @@ cudaError_t zbk_launch_render_pq(const RenderParams& P, int n_tiles_owned, int m
 
 cudaError_t zbk_launch_aov_pass(const RenderParams& P, int n_tiles_owned, cudaStream_t stream) {
     if (n_tiles_owned <= 0 || !P.accum_aux) return cudaSuccess;
-    k_aov_pass<<<n_tiles_owned, ZB_BLOCK_THREADS, 0, stream>>>(P);
+    const uint32_t feat = pick_feature_set(P);
+    ZB_FOR_FEATURE_SET(feat, (k_aov_pass<F><<<n_tiles_owned, ZB_BLOCK_THREADS, 0, stream>>>(P)));
     return cudaGetLastError();
 }
 

@@ -192,12 +192,13 @@ ZB_DEV float3 material_emitted(const SceneDev& sc, const Surface& sf) {
 }
 
 // material::get_albedo (material.hpp:28-30, :98-100, :153-155, :226-228, :265-272)
+template <uint32_t F = ZB_F_ALL>
 ZB_DEV float3 material_get_albedo(const SceneDev& sc, const Surface& sf) {
     const float4 m0 = sf.m0, m1 = sf.m1;
     uint32_t type = __float_as_uint(m0.x);
     if (type == ZB_MAT_DIELECTRIC) return f3(1, 1, 1);
     if (type == ZB_MAT_ISOTROPIC) return f3(0, 0, 0);
-    float3 a = material_albedo_tex(sc, m0, m1, sf);
+    float3 a = (F & ZB_F_TEX) ? material_albedo_tex(sc, m0, m1, sf) : f3(m1.x, m1.y, m1.z);
     if (type == ZB_MAT_LIGHT) return f3(fminf(a.x, 1.f), fminf(a.y, 1.f), fminf(a.z, 1.f));
     return a;
 }
