@@ -721,18 +721,14 @@ cudaError_t zbk_pq_clear(unsigned long long* fix, size_t pixels, int mode, unsig
     return cudaMemsetAsync(heads, 0, size_t(n_heads) * sizeof(unsigned long long), stream);
 }
 
-// beauty instantiation for feature set F at B resident blocks per SM (5..8: 96 / 80 / 72 / 64 registers)
+// beauty instantiation for feature set F at 6 / 7 / 8 resident blocks per SM (80 / 72 / 64 registers; 5, 9 and 10 were
+// measured too and never won, profiles/r01_feature_sets.txt); the general kernel is built for 6 and 7 only
 template <uint32_t F>
 static void pq_launch_beauty(int per_sm, unsigned blocks, cudaStream_t stream, const RenderParams& P, unsigned long long* fix,
                              unsigned long long* head, unsigned long long total, unsigned batch) {
-    switch (per_sm) {
-        case 5: k_render_pq<5, PQ_BEAUTY, F><<<blocks, ZB_BLOCK_THREADS, 0, stream>>>(P, fix, nullptr, head, total, batch); break;
-        case 6: k_render_pq<6, PQ_BEAUTY, F><<<blocks, ZB_BLOCK_THREADS, 0, stream>>>(P, fix, nullptr, head, total, batch); break;
-        case 7: k_render_pq<7, PQ_BEAUTY, F><<<blocks, ZB_BLOCK_THREADS, 0, stream>>>(P, fix, nullptr, head, total, batch); break;
-        case 9: k_render_pq<9, PQ_BEAUTY, F><<<blocks, ZB_BLOCK_THREADS, 0, stream>>>(P, fix, nullptr, head, total, batch); break;
-        case 10: k_render_pq<10, PQ_BEAUTY, F><<<blocks, ZB_BLOCK_THREADS, 0, stream>>>(P, fix, nullptr, head, total, batch); break;
-        default: k_render_pq<8, PQ_BEAUTY, F><<<blocks, ZB_BLOCK_THREADS, 0, stream>>>(P, fix, nullptr, head, total, batch); break;
-    }
+    if (per_sm <= 6) k_render_pq<6, PQ_BEAUTY, F><<<blocks, ZB_BLOCK_THREADS, 0, stream>>>(P, fix, nullptr, head, total, batch);
+    else if (per_sm == 7 || F == ZB_F_ALL) k_render_pq<7, PQ_BEAUTY, F><<<blocks, ZB_BLOCK_THREADS, 0, stream>>>(P, fix, nullptr, head, total, batch);
+    else if constexpr (F != ZB_F_ALL) k_render_pq<8, PQ_BEAUTY, F><<<blocks, ZB_BLOCK_THREADS, 0, stream>>>(P, fix, nullptr, head, total, batch);
 }
 
 // the queue kernel alone: the sums and `*head` must be zero (zbk_pq_clear); tiles P.tile_rank + i * P.tile_ranks,
@@ -745,14 +741,14 @@ cudaError_t zbk_launch_render_pq(const RenderParams& P, int n_tiles_owned, int m
     const unsigned long long total = (unsigned long long)n_tiles_owned * 4ull * 32ull * (unsigned long long)(P.sample_end - P.sample_begin);
     const unsigned long long warps_needed = (total + 31) / 32;
     // beauty renders run the smallest compiled feature set that covers the scene and its environment (pick_feature_set);
-    // ZB_PQ_BLOCKS=5..10 overrides the resident blocks per SM of the specialised instantiations
+    // ZB_PQ_BLOCKS=6..8 overrides the resident blocks per SM of the specialised instantiations
     const int env_blocks = getenv("ZB_PQ_BLOCKS") ? atoi(getenv("ZB_PQ_BLOCKS")) : 0;
     const uint32_t feat = mode == PQ_BEAUTY ? pick_feature_set(P) : uint32_t(ZB_F_ALL);
     const bool big_tree = P.sc.n_nodes >= PQ_BIG_TREE_NODES;
     // resident blocks per SM, measured per feature set at 1080p x 16 spp with 5 / 6 / 7 / 8 blocks (profiles/r01_feature_sets.txt):
     // Cornell 15.31 / 14.42 / 14.14 / 14.07 ms, exterior 18.74 / 18.17 / 17.42 / 17.83, mesh 17.95 / 16.86 / 16.67 / 16.04
     int per_sm = feat == ZB_F_ALL ? (big_tree ? 7 : 6) : feat == F_NOMESH ? 7 : 8;
-    if (feat != ZB_F_ALL && env_blocks >= 5 && env_blocks <= 10) per_sm = env_blocks;
+    if (feat != ZB_F_ALL && env_blocks >= 6 && env_blocks <= 8) per_sm = env_blocks;
     const unsigned blocks = unsigned(std::min<unsigned long long>((unsigned long long)sm_count * per_sm, (warps_needed + 3) / 4));
     // paths per grab: 256 when every warp will grab many times; short launches (few samples per pixel, small images,
     // one GPU's slice of a multi-GPU frame) end better balanced with smaller batches.  Measured, 1080p Weekend:
@@ -760,10 +756,9 @@ cudaError_t zbk_launch_render_pq(const RenderParams& P, int n_tiles_owned, int m
     const unsigned long long per_warp = total / (4ull * blocks);
     const unsigned batch = per_warp >= 64ull * PQ_BATCH ? PQ_BATCH : per_warp >= 64ull * (PQ_BATCH / 2) ? PQ_BATCH / 2 : PQ_BATCH / 4;
 #define PQ_LAUNCH(B, M) k_render_pq<B, M><<<blocks, ZB_BLOCK_THREADS, 0, stream>>>(P, fix, fix_aux, head, total, batch)
-    if (feat != ZB_F_ALL) { ZB_FOR_FEATURE_SET(feat, (pq_launch_beauty<F>(per_sm, blocks, stream, P, fix, head, total, batch))); }
-    else if (mode == PQ_AUX) { if (per_sm == 7) PQ_LAUNCH(7, PQ_AUX); else PQ_LAUNCH(6, PQ_AUX); }
+    if (mode == PQ_AUX) { if (per_sm == 7) PQ_LAUNCH(7, PQ_AUX); else PQ_LAUNCH(6, PQ_AUX); }
     else if (mode == PQ_LIGHT) { if (per_sm == 7) PQ_LAUNCH(7, PQ_LIGHT); else PQ_LAUNCH(6, PQ_LIGHT); }
-    else { if (per_sm == 7) PQ_LAUNCH(7, PQ_BEAUTY); else PQ_LAUNCH(6, PQ_BEAUTY); }
+    else { ZB_FOR_FEATURE_SET(feat, (pq_launch_beauty<F>(per_sm, blocks, stream, P, fix, head, total, batch))); }
 #undef PQ_LAUNCH
     return cudaGetLastError();
 }

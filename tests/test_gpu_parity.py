@@ -555,7 +555,7 @@ def test_lean_instantiation_equals_general_queue_kernel(weekend_scene, monkeypat
     monkeypatch.delenv("ZB_NO_LEAN")
     b = weekend_scene.render(cfg, seed=9)["beauty"]
     assert np.array_equal(a, b)
-    for blocks in ("5", "6", "7"):
+    for blocks in ("6", "7"):
         monkeypatch.setenv("ZB_PQ_BLOCKS", blocks)
         assert np.array_equal(a, weekend_scene.render(cfg, seed=9)["beauty"]), blocks
 
