@@ -675,17 +675,20 @@ __global__ void __launch_bounds__(256) k_resolve(const float4* __restrict__ accu
 
 // Feature sets the render kernels are compiled for (ZB_F_*, include/zenith_b200.h), smallest first:
 //   PLAIN   inline spheres, untextured materials, solid-colour environment (Weekend)
+//   SPHTE   inline spheres with textures and / or a sky or HDR environment
 //   BOXES   + loose triangles, cubes, instances of them, media (Cornell)
 //   MESH0   instances, meshes, triangles (mesh configs), MESH: + textures
 //   NOMESH  everything but meshes and triangles (exterior: HDR map, bump maps, instanced cubes / spheres, media)
+//   NOMEDIA everything but participating media
 // ZB_NO_LEAN=1 forces the general kernels (A/B runs, equality tests).
 namespace {
 constexpr uint32_t F_PLAIN = 0, F_BOXES = ZB_F_INST | ZB_F_CUBE | ZB_F_TRI | ZB_F_MEDIA, F_MESH0 = ZB_F_INST | ZB_F_MESH | ZB_F_TRI,
-                   F_MESH = F_MESH0 | ZB_F_TEX, F_NOMESH = ZB_F_ALL & ~(ZB_F_MESH | ZB_F_TRI);
+                   F_MESH = F_MESH0 | ZB_F_TEX, F_NOMESH = ZB_F_ALL & ~(ZB_F_MESH | ZB_F_TRI), F_SPHTE = ZB_F_TEX | ZB_F_ENV,
+                   F_NOMEDIA = ZB_F_ALL & ~ZB_F_MEDIA;
 uint32_t pick_feature_set(const RenderParams& P) {
     if (getenv("ZB_NO_LEAN") && atoi(getenv("ZB_NO_LEAN")) != 0) return ZB_F_ALL;
     const uint32_t need = (P.sc.features & ZB_F_ALL) | (P.env.mode == ZB_ENV_SOLID_COLOR ? 0u : uint32_t(ZB_F_ENV));
-    for (uint32_t f : {F_PLAIN, F_BOXES, F_MESH0, F_MESH, F_NOMESH})
+    for (uint32_t f : {F_PLAIN, F_SPHTE, F_BOXES, F_MESH0, F_MESH, F_NOMESH, F_NOMEDIA})
         if ((need & ~f) == 0) return f;
     return ZB_F_ALL;
 }
@@ -697,6 +700,8 @@ uint32_t pick_feature_set(const RenderParams& P) {
         case F_MESH0: { constexpr uint32_t F = F_MESH0; CALL; } break;      \
         case F_MESH: { constexpr uint32_t F = F_MESH; CALL; } break;        \
         case F_NOMESH: { constexpr uint32_t F = F_NOMESH; CALL; } break;    \
+        case F_SPHTE: { constexpr uint32_t F = F_SPHTE; CALL; } break;      \
+        case F_NOMEDIA: { constexpr uint32_t F = F_NOMEDIA; CALL; } break;  \
         default: { constexpr uint32_t F = ZB_F_ALL; CALL; } break;          \
     }
 
@@ -747,7 +752,7 @@ cudaError_t zbk_launch_render_pq(const RenderParams& P, int n_tiles_owned, int m
     const bool big_tree = P.sc.n_nodes >= PQ_BIG_TREE_NODES;
     // resident blocks per SM, measured per feature set at 1080p x 16 spp with 5 / 6 / 7 / 8 blocks (profiles/r01_feature_sets.txt):
     // Cornell 15.31 / 14.42 / 14.14 / 14.07 ms, exterior 18.74 / 18.17 / 17.42 / 17.83, mesh 17.95 / 16.86 / 16.67 / 16.04
-    int per_sm = feat == ZB_F_ALL ? (big_tree ? 7 : 6) : feat == F_NOMESH ? 7 : 8;
+    int per_sm = feat == ZB_F_ALL ? (big_tree ? 7 : 6) : (feat == F_NOMESH || feat == F_NOMEDIA) ? 7 : 8;
     if (feat != ZB_F_ALL && env_blocks >= 6 && env_blocks <= 8) per_sm = env_blocks;
     const unsigned blocks = unsigned(std::min<unsigned long long>((unsigned long long)sm_count * per_sm, (warps_needed + 3) / 4));
     // paths per grab: 256 when every warp will grab many times; short launches (few samples per pixel, small images,

@@ -558,6 +558,19 @@ def test_lean_instantiation_equals_general_queue_kernel(weekend_scene, monkeypat
     for blocks in ("6", "7"):
         monkeypatch.setenv("ZB_PQ_BLOCKS", blocks)
         assert np.array_equal(a, weekend_scene.render(cfg, seed=9)["beauty"]), blocks
+    monkeypatch.delenv("ZB_PQ_BLOCKS")
+    # the same spheres under the procedural sky: the "spheres + textures / environment" set against the general kernel
+    import copy
+    sky = copy.copy(cfg)
+    sky.env_mode = "sun"
+    full = copy.copy(sky)
+    full.use_albedo = full.use_normal = full.use_z_depth = full.use_reflection = full.use_refraction = True
+    b = weekend_scene.render(full, seed=9)
+    monkeypatch.setenv("ZB_NO_LEAN", "1")
+    a = weekend_scene.render(full, seed=9)
+    for key in ("beauty", "albedo", "normal", "z_depth", "reflection", "refraction"):
+        assert np.array_equal(a[key], b[key]), key
+    assert not np.array_equal(a["beauty"], weekend_scene.render(cfg, seed=9)["beauty"])  # the sky is not the solid colour
 
 
 # ------------------------------------------------------------------ image export
