@@ -476,6 +476,157 @@ __global__ void __launch_bounds__(ZB_BLOCK_THREADS, MIN_BLOCKS) k_render_pq(cons
     }
 }
 
+// k_render_pqr — k_render_pq's beauty pass with RESUMABLE traversal: the traversal state of a lane (RayWalk + its stack) lives
+// across iterations of the warp's main loop, and the warp leaves the traversal loop as soon as fewer than `thresh` of its lanes
+// still hold an unfinished ray while others wait with a finished one.  The finished lanes are shaded and get their next ray (or
+// the next path of the batch) while the others keep their state, so the node loop runs with more lanes than when every
+// segment ends with the slowest ray of the warp.  Same paths, same arithmetic per path, order-free fixed-point sums: the frame
+// is bit-identical to k_render_pq's.
+template <int MIN_BLOCKS, uint32_t F>
+__global__ void __launch_bounds__(ZB_BLOCK_THREADS, MIN_BLOCKS) k_render_pqr(const __grid_constant__ RenderParams P,
+                                                                                   unsigned long long* __restrict__ fix,
+                                                                                   unsigned long long* __restrict__ head,
+                                                                                   unsigned long long total, unsigned batch, unsigned thresh) {
+    const unsigned lane = threadIdx.x & 31u, lt = (1u << lane) - 1u;
+    const uint32_t n_s = uint32_t(P.sample_end - P.sample_begin);
+    const Philox ph{P.pk[0]};
+    Counters cnt = {0, 0, 0, 0};
+    uint32_t paths = 0;
+    bool have = false, dry = false;
+    int seg = 0;
+    uint32_t pixel = 0, s = 0;
+    float3 o = f3(0, 0, 0), d = f3(0, 0, 1), L = f3(0, 0, 0), beta = f3(1, 1, 1);
+    unsigned long long w_pos = 0, w_end = 0;
+    const uint32_t tiles_x = uint32_t(P.tiles_x);
+    const unsigned long long m_ns = n_s > 1u ? ~0ull / n_s + 1ull : 0ull, m_tx = tiles_x > 1u ? ~0ull / tiles_x + 1ull : 0ull;
+    int stack[ZB_STACK];
+    RayWalk w;
+    w.begin(P.sc, o, d, INFINITY, stack);
+    w.cur = ZB_TRAVERSAL_DONE;
+    for (;;) {
+        // ---- lanes without a path take the next ones of the warp's batch (as in k_render_pq)
+        for (;;) {
+            const unsigned need = __ballot_sync(0xFFFFFFFFu, !have && !dry);
+            if (!need) break;
+            const unsigned want = __popc(need);
+            const unsigned long long avail = w_end - w_pos;
+            unsigned long long base2 = 0;
+            if (avail < want) {
+                if (lane == 0) base2 = atomicAdd(head, (unsigned long long)batch);
+                base2 = __shfl_sync(0xFFFFFFFFu, base2, 0);
+            }
+            if (!have && !dry) {
+                const unsigned r = __popc(need & lt);
+                const unsigned long long g = r < avail ? w_pos + r : base2 + (r - avail);
+                if (g >= total) {
+                    dry = true;
+                } else {
+                    uint32_t q, sr;
+                    if (total <= 0xFFFFFFFFull) {
+                        const uint32_t g32 = uint32_t(g);
+                        q = n_s > 1u ? uint32_t(__umul64hi(g32, m_ns)) : g32;
+                        sr = g32 - q * n_s;
+                    } else {
+                        const unsigned long long q64 = g / n_s;
+                        q = uint32_t(q64);
+                        sr = uint32_t(g - q64 * n_s);
+                    }
+                    const uint32_t u = q >> 5, p = q & 31u;
+                    const int tile = int(u >> 2) * P.tile_ranks + P.tile_rank, wq = int(u & 3u);
+                    const int ty = tiles_x > 1u ? int(__umul64hi(uint32_t(tile), m_tx)) : tile, tx = tile - ty * int(tiles_x);
+                    const int px = tx * ZB_TILE_W + (wq % (ZB_TILE_W / 8)) * 8 + int(p & 7u);
+                    const int py = ty * ZB_TILE_H + (wq / (ZB_TILE_W / 8)) * 4 + int(p >> 3);
+                    if (px < P.cam.width && py < P.cam.height && ty < P.tiles_y) {
+                        s = uint32_t(P.sample_begin) + sr;
+                        pixel = uint32_t(py) * uint32_t(P.cam.width) + uint32_t(px);
+                        const uint4 r0 = ph(pixel, s, 0u, 0u);
+                        d = P.cam.pix00_rel + (float(px) + u01(r0.x) - 0.5f) * P.cam.du + (float(py) + u01(r0.y) - 0.5f) * P.cam.dv;
+                        o = P.cam.center;
+                        if (P.cam.defocus) {
+                            float rr = sqrt_fast(u01(r0.z)), sn, cs;
+                            sincos_turn(u01(r0.w), &sn, &cs);
+                            const float3 off = (rr * cs) * P.cam.disk_u + (rr * sn) * P.cam.disk_v;
+                            o += off;
+                            d = d - off;
+                        }
+                        seg = 0;
+                        L = f3(0, 0, 0);
+                        beta = f3(1, 1, 1);
+                        paths++;
+                        have = true;
+                        cnt.rays++;
+                        w.begin(P.sc, o, d, INFINITY, stack);
+                    }
+                }
+            }
+            if (avail < want) {
+                w_pos = base2 + (want - avail);
+                w_end = base2 + batch;
+            } else {
+                w_pos += want;
+            }
+        }
+        const unsigned holders = __ballot_sync(0xFFFFFFFFu, have);
+        if (!holders) break;
+        // ---- K2 traverse: while-while rounds until too few lanes still hold an unfinished ray
+        for (;;) {
+            const bool trav = have && w.cur != ZB_TRAVERSAL_DONE;
+            const unsigned m = __ballot_sync(0xFFFFFFFFu, trav);
+            if (!m || (unsigned(__popc(m)) < thresh && m != holders)) break;
+            if (trav) {
+                while (w.cur >= 0) w.node_step<false>(P.sc, 0.001f, stack, cnt);
+                if (w.cur != ZB_TRAVERSAL_DONE) {
+                    const MediumRng mr{ph, pixel, s, uint32_t(seg + 1)};
+                    w.leaf_step<false, F>(P.sc, o, d, 0.001f, mr, stack, cnt);
+                }
+            }
+        }
+        // ---- K3 shade the lanes whose ray is finished: one segment of ray_color (camera.hpp:928-1004), as in k_render_pq
+        if (have && w.cur == ZB_TRAVERSAL_DONE) {
+            const Hit hit = w.hit;
+            bool done;
+            if (hit.item == 0xFFFFFFFFu) {
+                L += beta * ((F & ZB_F_ENV) ? background(P.sc, P.env, d) : P.env.background);
+                done = true;
+            } else {
+                Surface sf;
+                make_surface<F>(P.sc, hit, o, d, sf);
+                L += beta * material_emitted<F>(P.sc, sf);
+                const uint4 rb = ph(pixel, s, uint32_t(seg + 1), 0u);
+                float3 atten = f3(1, 1, 1), no, nd;
+                done = !material_scatter<F>(P.sc, sf, d, f3(u01(rb.x), u01(rb.y), u01(rb.z)), atten, no, nd);
+                if (!done) {
+                    beta *= atten;
+                    o = no;
+                    d = nd;
+                    if (seg >= 12) {  // camera.hpp:968-983
+                        const float pr = fminf(fmaxf(max3(beta.x, beta.y, beta.z), 0.05f), 0.95f);
+                        if (dot(beta, beta) < 1e-8f || u01(rb.w) > pr) done = true;
+                        beta *= 1.0f / pr;
+                    }
+                    if (++seg >= P.max_depth) done = true;
+                }
+            }
+            if (done) {  // K5 accumulate
+                unsigned long long* f = fix + 3 * size_t(pixel);
+                gfix_add(f + 0, L.x);
+                gfix_add(f + 1, L.y);
+                gfix_add(f + 2, L.z);
+                have = false;
+            } else {
+                cnt.rays++;
+                w.begin(P.sc, o, d, INFINITY, stack);
+            }
+        }
+    }
+    uint32_t v[2] = {cnt.rays, paths};
+#pragma unroll
+    for (int k = 0; k < 2; k++) {
+        const uint32_t x = __reduce_add_sync(0xFFFFFFFFu, v[k]);
+        if (lane == 0 && x) atomicAdd(P.counters + (k ? 4 : 0), (unsigned long long)x);
+    }
+}
+
 // First-hit AOVs (K8, camera.hpp:464-488, :518-526) as a pass of their own beside k_render_pq: one thread per pixel walks
 // the pixel's first aux_samples samples, regenerates the camera ray of (pixel, sample) — the same Philox draws as the
 // beauty pass, so the same primary hit — and sums albedo, view-space normal and z in 64-bit fixed point in registers
@@ -761,7 +912,13 @@ cudaError_t zbk_launch_render_pq(const RenderParams& P, int n_tiles_owned, int m
     const unsigned long long per_warp = total / (4ull * blocks);
     const unsigned batch = per_warp >= 64ull * PQ_BATCH ? PQ_BATCH : per_warp >= 64ull * (PQ_BATCH / 2) ? PQ_BATCH / 2 : PQ_BATCH / 4;
 #define PQ_LAUNCH(B, M) k_render_pq<B, M><<<blocks, ZB_BLOCK_THREADS, 0, stream>>>(P, fix, fix_aux, head, total, batch)
-    if (mode == PQ_AUX) { if (per_sm == 7) PQ_LAUNCH(7, PQ_AUX); else PQ_LAUNCH(6, PQ_AUX); }
+    const int resume = getenv("ZB_PQ_RESUME") ? atoi(getenv("ZB_PQ_RESUME")) : 0;  // experiment: resumable traversal (k_render_pqr)
+    if (mode == PQ_BEAUTY && feat == F_PLAIN && resume > 0) {
+        if (per_sm == 7) k_render_pqr<7, F_PLAIN><<<blocks, ZB_BLOCK_THREADS, 0, stream>>>(P, fix, head, total, batch, unsigned(resume));
+        else if (per_sm == 6) k_render_pqr<6, F_PLAIN><<<blocks, ZB_BLOCK_THREADS, 0, stream>>>(P, fix, head, total, batch, unsigned(resume));
+        else k_render_pqr<8, F_PLAIN><<<blocks, ZB_BLOCK_THREADS, 0, stream>>>(P, fix, head, total, batch, unsigned(resume));
+    }
+    else if (mode == PQ_AUX) { if (per_sm == 7) PQ_LAUNCH(7, PQ_AUX); else PQ_LAUNCH(6, PQ_AUX); }
     else if (mode == PQ_LIGHT) { if (per_sm == 7) PQ_LAUNCH(7, PQ_LIGHT); else PQ_LAUNCH(6, PQ_LIGHT); }
     else { ZB_FOR_FEATURE_SET(feat, (pq_launch_beauty<F>(per_sm, blocks, stream, P, fix, head, total, batch))); }
 #undef PQ_LAUNCH

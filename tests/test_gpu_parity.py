@@ -559,6 +559,11 @@ def test_lean_instantiation_equals_general_queue_kernel(weekend_scene, monkeypat
         monkeypatch.setenv("ZB_PQ_BLOCKS", blocks)
         assert np.array_equal(a, weekend_scene.render(cfg, seed=9)["beauty"]), blocks
     monkeypatch.delenv("ZB_PQ_BLOCKS")
+    # resumable traversal (k_render_pqr, an opt-in experiment): other scheduling of the same paths
+    for thresh in ("8", "24"):
+        monkeypatch.setenv("ZB_PQ_RESUME", thresh)
+        assert np.array_equal(a, weekend_scene.render(cfg, seed=9)["beauty"]), thresh
+    monkeypatch.delenv("ZB_PQ_RESUME")
     # the same spheres under the procedural sky: the "spheres + textures / environment" set against the general kernel
     import copy
     sky = copy.copy(cfg)
