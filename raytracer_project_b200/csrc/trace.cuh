@@ -18,6 +18,9 @@
 // Slab tests use MUFU.RCP reciprocals (~1 ulp) of the ray direction; the far distance is inflated by
 // 10 ulp so that the box test stays conservative (Ize 2013).  Measured -2 % frame time vs IEEE divides.
 #define ZB_BOX_INFLATE 1.0000012f
+#ifndef ZB_MEDIUM_ONE_SOLVE
+#define ZB_MEDIUM_ONE_SOLVE 1
+#endif
 #ifndef ZB_BRANCHLESS_POP
 #define ZB_BRANCHLESS_POP 0  // measured: Weekend +7 % time, mesh -1.3 % (profiles/r01_feature_sets.txt)
 #endif
@@ -168,6 +171,26 @@ ZB_DEV bool hit_medium_boundary(const SceneDev& sc, float4 m0, float4 sph, float
                            tmax, t);
 }
 
+// both roots of hit_sphere's quadratic in one evaluation (same arithmetic, so lo / hi are the values hit_sphere returns)
+ZB_DEV bool sphere_roots(float4 s, float3 o, float3 d, float& lo, float& hi) {
+    float3 oc = f3(s.x - o.x, s.y - o.y, s.z - o.z);
+    float a = dot(d, d);
+    float h = dot(d, oc);
+    float inv_a = __frcp_rn(a);
+    float3 l = fma3(-h * inv_a, d, oc);
+    float disc = fmaf(s.w, s.w, -dot(l, l));
+    if (disc < 0.f) return false;
+    double ocx = double(s.x) - double(o.x), ocy = double(s.y) - double(o.y), ocz = double(s.z) - double(o.z);
+    float c = float(fma(ocx, ocx, fma(ocy, ocy, fma(ocz, ocz, -double(s.w) * double(s.w)))));
+    float sq = sqrtf(a * disc);
+    float q = h + copysignf(sq, h);
+    float ta = q * inv_a;
+    float tb = q != 0.f ? c / q : ta;
+    lo = fminf(ta, tb);
+    hi = fmaxf(ta, tb);
+    return true;
+}
+
 // constant_medium::hit (constant_medium.hpp:39-77)
 template <uint32_t F = ZB_F_ALL>
 ZB_DEV bool hit_medium(const SceneDev& sc, uint32_t medium, float3 o, float3 d, float tmin, float tmax,
@@ -175,8 +198,19 @@ ZB_DEV bool hit_medium(const SceneDev& sc, uint32_t medium, float3 o, float3 d, 
     float4 m0 = __ldg(sc.media + 2 * size_t(medium));
     float4 sph = __ldg(sc.media + 2 * size_t(medium) + 1);
     float t1, t2;
-    if (!hit_medium_boundary<F>(sc, m0, sph, o, d, -INFINITY, INFINITY, t1)) return false;
-    if (!hit_medium_boundary<F>(sc, m0, sph, o, d, t1 + 0.0001f, INFINITY, t2)) return false;
+    if (ZB_MEDIUM_ONE_SOLVE && __float_as_uint(m0.x) == ZB_ITEM_SPHERE) {
+        // inline sphere boundary: boundary->hit(r, universe) is the nearer root, boundary->hit(r, [t1 + 1e-4, inf)) the
+        // farther one if it lies beyond t1 + 1e-4 — one solve of the quadratic instead of two
+        if (!sphere_roots(sph, o, d, t1, t2)) return false;
+        if (!(t1 > -INFINITY && t1 < INFINITY)) {  // hit_sphere's strict interval test on the nearer root, then the farther
+            if (!(t2 > -INFINITY && t2 < INFINITY)) return false;
+            t1 = t2;
+        }
+        if (!(t2 > t1 + 0.0001f && t2 < INFINITY)) return false;
+    } else {
+        if (!hit_medium_boundary<F>(sc, m0, sph, o, d, -INFINITY, INFINITY, t1)) return false;
+        if (!hit_medium_boundary<F>(sc, m0, sph, o, d, t1 + 0.0001f, INFINITY, t2)) return false;
+    }
     if (t1 < tmin) t1 = tmin;
     if (t2 > tmax) t2 = tmax;
     if (t1 >= t2) return false;
