@@ -22,7 +22,7 @@
 extern "C" {
 #endif
 
-#define ZB_ABI_VERSION 2
+#define ZB_ABI_VERSION 3
 
 typedef enum zb_status {
     ZB_OK = 0,
@@ -53,6 +53,12 @@ typedef struct zb_bvh_node {
     uint32_t pad0, pad1;
 } zb_bvh_node;
 #define ZB_CHILD_EMPTY ((int32_t)0x80000000)
+/* Depth caps (inner nodes on a root-to-leaf path) both builders keep — the host binned-SAH builder falls back to median
+ * splits where SAH would exceed them, the device LBVH is measured after the build — and zb_scene_upload verifies: the
+ * per-ray traversal stack (csrc/trace.cuh) holds one deferred child per level.  The reference's recursive traversal
+ * (bvh.hpp:46-54) has no such bound; its median-split tree is log2(N) deep by construction (bvh.hpp:15-44). */
+#define ZB_MAX_TLAS_DEPTH 22
+#define ZB_MAX_BLAS_DEPTH 38
 
 /* Top-level leaf item, 32 B.  One per leaf object of the world (DFS order of the scene graph
  * gives `leaf_id`; items are stored in BVH leaf order).  Spheres that sit directly in the world
@@ -229,7 +235,8 @@ typedef struct zb_stats {
     double resolve_ms; /* device time of the resolve kernel                             */
     double h2d_ms, d2h_ms;
     uint32_t launches; /* kernels launched by the last render                           */
-    uint32_t pad;
+    uint32_t stack_overflows; /* traversal-stack overflow events of the last render (saturating): must be 0; zb_render
+                                 returns ZB_ERR_UNSUPPORTED otherwise                                                 */
 } zb_stats;
 
 typedef struct zb_context zb_context;
@@ -243,6 +250,14 @@ const char* zb_last_error(void);
 int zb_context_create(int device, zb_context** out);
 int zb_context_set_stream(zb_context* ctx, void* stream);
 int zb_context_destroy(zb_context* ctx);
+/* A/B switches for measurements and equality tests; product defaults need none of them.  Read once from the environment at
+ * context creation (ZB_PQ, ZB_NO_LEAN, ZB_PQ_BLOCKS, ZB_GATHER_P2P), changed afterwards only here.  Keys: "pq" (0 tile-bound
+ * k_render, 1 path-queue beauty kernel, 2 also its AOV / light modes), "no_lean" (1: general kernels), "pq_blocks" (6..8),
+ * "gather_p2p" (multi-GPU combine: 1 fused peer-memory kernel, 0 staged copies); a library built with -DZB_EXPERIMENTS
+ * (zb_build_flags() & ZB_BUILD_EXPERIMENTS) adds "pq_resume", "wavefront", "wf_slots" for the rejected kernel forms. */
+int zb_context_set_tuning(zb_context* ctx, const char* key, long long value);
+#define ZB_BUILD_EXPERIMENTS 1
+int zb_build_flags(void);
 int zb_device_info(zb_context* ctx, int* sm_count, int* cc_major, int* cc_minor, size_t* l2_bytes);
 
 /* copies the flat scene to the GPU; the caller keeps ownership of the host arrays */

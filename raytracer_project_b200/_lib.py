@@ -85,7 +85,7 @@ class Stats(C.Structure):
     _fields_ = [("paths", C.c_uint64), ("rays", C.c_uint64), ("node_visits", C.c_uint64), ("box_tests", C.c_uint64),
                 ("prim_tests", C.c_uint64), ("instance_visits", C.c_uint64), ("kernel_ms", C.c_double),
                 ("resolve_ms", C.c_double), ("h2d_ms", C.c_double), ("d2h_ms", C.c_double), ("launches", C.c_uint32),
-                ("pad", C.c_uint32)]
+                ("stack_overflows", C.c_uint32)]
 
 
 PROGRESS_FN = C.CFUNCTYPE(None, C.c_int, C.c_void_p)
@@ -113,6 +113,8 @@ SYMBOLS = {
     "zb_context_create": (C.c_int, [C.c_int, C.POINTER(C.c_void_p)]),
     "zb_context_set_stream": (C.c_int, [C.c_void_p, C.c_void_p]),
     "zb_context_destroy": (C.c_int, [C.c_void_p]),
+    "zb_context_set_tuning": (C.c_int, [C.c_void_p, C.c_char_p, C.c_longlong]),
+    "zb_build_flags": (C.c_int, []),
     "zb_device_info": (C.c_int, [C.c_void_p, C.POINTER(C.c_int), C.POINTER(C.c_int), C.POINTER(C.c_int), C.POINTER(C.c_size_t)]),
     "zb_scene_upload": (C.c_int, [C.c_void_p, C.POINTER(FlatScene), C.POINTER(C.c_void_p)]),
     "zb_scene_destroy": (C.c_int, [C.c_void_p]),

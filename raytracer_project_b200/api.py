@@ -208,6 +208,11 @@ def post_text(pass_kind=0, **kw) -> str:
     return "\n".join(lines) + "\n"
 
 
+def has_experiments() -> bool:
+    """True when the library was built with -DZB_EXPERIMENTS (wavefront kernels, k_render_pqr)."""
+    return bool(_lib.load().zb_build_flags() & 1)
+
+
 class Context:
     def __init__(self, device: int = 0, stream: int | None = None):
         self.lib = _lib.load()
@@ -226,6 +231,10 @@ class Context:
 
     def __exit__(self, *a):
         self.close()
+
+    def set_tuning(self, key: str, value: int):
+        """zb_context_set_tuning: A/B switches ("pq", "no_lean", "pq_blocks", ...); the product defaults need none."""
+        check(self.lib.zb_context_set_tuning(self.h, key.encode(), int(value)))
 
     def device_info(self):
         sm, ma, mi, l2 = C.c_int(), C.c_int(), C.c_int(), C.c_size_t()

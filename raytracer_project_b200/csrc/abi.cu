@@ -28,6 +28,7 @@ extern "C" int zb_context_create(int device, zb_context** out) {
     c->cc_major = prop.major;
     c->cc_minor = prop.minor;
     c->l2_bytes = size_t(prop.l2CacheSize);
+    c->tuning = zbk_tuning_from_env();
     ZB_CUDA(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
     c->own_stream = true;
     ZB_CUDA(cudaMalloc(&c->counters, 8 * sizeof(unsigned long long)));
@@ -47,6 +48,31 @@ extern "C" int zb_context_set_stream(zb_context* ctx, void* stream) {
     return ZB_OK;
 }
 
+extern "C" int zb_build_flags(void) {
+#ifdef ZB_EXPERIMENTS
+    return ZB_BUILD_EXPERIMENTS;
+#else
+    return 0;
+#endif
+}
+
+extern "C" int zb_context_set_tuning(zb_context* ctx, const char* key, long long value) {
+    if (!ctx || !key) return fail(ZB_ERR_INVALID, "zb_context_set_tuning: NULL argument");
+    const std::string k = key;
+    ZbTuning& t = ctx->tuning;
+    if (k == "pq") t.pq = int(value);
+    else if (k == "no_lean") t.no_lean = value != 0;
+    else if (k == "pq_blocks") t.pq_blocks = int(value);
+    else if (k == "gather_p2p") t.gather_p2p = int(value);
+#ifdef ZB_EXPERIMENTS
+    else if (k == "pq_resume") t.pq_resume = int(value);
+    else if (k == "wavefront") t.wavefront = value != 0;
+    else if (k == "wf_slots") t.wf_slots = value;
+#endif
+    else return fail(ZB_ERR_INVALID, "zb_context_set_tuning: unknown key '" + k + "'");
+    return ZB_OK;
+}
+
 extern "C" int zb_context_destroy(zb_context* ctx) {
     if (!ctx) return ZB_OK;
     cudaSetDevice(ctx->device);
@@ -60,7 +86,9 @@ extern "C" int zb_context_destroy(zb_context* ctx) {
     cudaFree(ctx->fin_b);
     cudaFree(ctx->fin_in);
     cudaFree(ctx->fin_stats);
+#ifdef ZB_EXPERIMENTS
     zbk_wavefront_free(ctx->wf);
+#endif
     cudaFree(ctx->pq_fix);
     cudaFree(ctx->rgb_pack);
     if (ctx->pinned) cudaFreeHost(ctx->pinned);
@@ -111,6 +139,34 @@ static int validate(const zb_flat_scene* f) {
                 uint32_t code = ~uint32_t(c), first = code >> 3, end = first + (code & 7u) + 1u;
                 if (end > (tlas ? f->n_items : f->n_tris)) return fail(ZB_ERR_INVALID, "flat scene: leaf range out of bounds");
             }
+        }
+    }
+    // tree depth (inner nodes on a root-to-leaf path) of the TLAS and of every host-built BLAS against the caps the
+    // traversal stack is sized for; also rejects cycles (a node reached at a depth beyond the cap ends the walk)
+    {
+        std::vector<std::pair<uint32_t, int>> todo;
+        auto depth_of = [&](uint32_t root, int cap) -> int {
+            int deepest = 0;
+            todo.clear();
+            todo.push_back({root, 1});
+            while (!todo.empty()) {
+                auto [n, d] = todo.back();
+                todo.pop_back();
+                deepest = std::max(deepest, d);
+                if (d > cap) return d;
+                for (int32_t c : {f->nodes[n].left, f->nodes[n].right})
+                    if (c >= 0) todo.push_back({uint32_t(c), d + 1});
+            }
+            return deepest;
+        };
+        if (f->n_tlas_nodes && depth_of(0, ZB_MAX_TLAS_DEPTH) > ZB_MAX_TLAS_DEPTH)
+            return fail(ZB_ERR_INVALID, "flat scene: TLAS deeper than ZB_MAX_TLAS_DEPTH (or cyclic)");
+        for (uint32_t m = 0; m < f->n_meshes; m++) {
+            const zb_mesh& zm = f->meshes[m];
+            if (zm.node_count == 0) continue;
+            if (zm.node_root >= f->n_nodes) return fail(ZB_ERR_INVALID, "flat scene: mesh BLAS root out of range");
+            if (depth_of(zm.node_root, ZB_MAX_BLAS_DEPTH) > ZB_MAX_BLAS_DEPTH)
+                return fail(ZB_ERR_INVALID, "flat scene: mesh BLAS deeper than ZB_MAX_BLAS_DEPTH (or cyclic)");
         }
     }
     for (uint32_t i = 0; i < f->n_items; i++) {
@@ -251,6 +307,7 @@ extern "C" int zb_scene_upload(zb_context* ctx, const zb_flat_scene* f, zb_scene
     }
     d.n_items = f->n_items;
     d.n_media = f->n_media;
+    d.overflow = ctx->counters + 6;
     // scene features (ZB_F_*): which code a render kernel has to carry for this scene
     d.features = 0;
     zb_flat_scene_features(f, &d.features);

@@ -50,6 +50,7 @@ struct zb_context {
     cudaEvent_t ev[6] = {};
     std::vector<cudaEvent_t> chunk_ev;  // one per 4 MiB chunk of the frame copy (abi_render.cu d2h_rgb_f64)
     zb_stats stats{};
+    ZbTuning tuning{};  // A/B switches: environment at creation, zb_context_set_tuning afterwards
 };
 
 struct zb_scene {

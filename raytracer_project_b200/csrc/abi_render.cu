@@ -216,29 +216,31 @@ int launch_share(zb_context* ctx, RenderParams P, const zb_render_opts* o, const
         ZB_CUDA(cudaMemsetAsync(P.accum, 0, pixels * sizeof(float4), ctx->stream));
         if (P.accum_aux) ZB_CUDA(cudaMemsetAsync(P.accum_aux, 0, 3 * pixels * sizeof(float4), ctx->stream));
     }
-    // experimental: ZB_WAVEFRONT=1 renders the beauty pass with the wavefront kernels (ZB_WF_SLOTS = path slots)
-    const char* wf_env = getenv("ZB_WAVEFRONT");
-    const bool wavefront = wf_env && atoi(wf_env) > 0 && !o->collect_stats;
-    const char* wf_slots_env = getenv("ZB_WF_SLOTS");
-    const size_t wf_slots = wf_slots_env ? size_t(atoll(wf_slots_env)) : 0;
-    // the beauty pass runs as k_render_pq (frame-wide path queue) unless ZB_PQ=0 asks for the tile-bound k_render
-    const char* pq_env = getenv("ZB_PQ");
-    const bool pq = !(pq_env && atoi(pq_env) == 0);
-    // The queue kernel also has AOV and light-pass modes (bit-identical to k_render's), selected with ZB_PQ=2 only: the
-    // AOV sums of a warp's lanes go to the same one or two pixels at the same moment, and as global REDs they serialise
-    // (Weekend 64 spp: 44.4 vs 40.6 ms with AOVs, 38.2 vs 32.6 ms light passes; profiles/r01_pq.txt)
-    const bool pq_all = pq_env && atoi(pq_env) >= 2;
+    // A/B switches (ZbTuning, read once at context creation).  pq: the beauty pass runs as k_render_pq (frame-wide path
+    // queue) unless 0 asks for the tile-bound k_render; 2 also selects the queue kernel's AOV and light-pass modes
+    // (bit-identical to k_render's but slower: the AOV sums of a warp's lanes go to the same one or two pixels at the
+    // same moment and serialise as global REDs — Weekend 64 spp: 44.4 vs 40.6 ms with AOVs, 38.2 vs 32.6 ms light
+    // passes; profiles/r01_pq.txt)
+    const ZbTuning& tn = ctx->tuning;
+    const bool pq = tn.pq != 0, pq_all = tn.pq >= 2;
+#ifdef ZB_EXPERIMENTS
+    const bool wavefront = tn.wavefront && !o->collect_stats;
+    const size_t wf_slots = size_t(std::max(0ll, tn.wf_slots));
+#endif
     int done = 0;
     for (int s = sb; s < se; s += per) {
         if (cancel && *cancel) return fail(ZB_ERR_CANCELLED, "render cancelled");
         P.sample_begin = s;
         P.sample_end = std::min(s + per, se);
         P.accumulate = (s > sb || keep) ? 1 : 0;
+#ifdef ZB_EXPERIMENTS
         if (wavefront && zbk_wavefront_supported(P)) {
             int iters = 0;
             ZB_CUDA(zbk_launch_wavefront(P, &ctx->wf, wf_slots, &iters, ctx->stream));
             ctx->stats.launches += 2 + 2 * iters;
-        } else if (pq && !pq_all && !o->collect_stats && P.max_depth > 0 && P.sample_end > P.sample_begin && !P.light_pass && P.accum_aux &&
+        } else
+#endif
+        if (pq && !pq_all && !o->collect_stats && P.max_depth > 0 && P.sample_end > P.sample_begin && !P.light_pass && P.accum_aux &&
                    P.sc.n_nodes < 65536u) {
             // beauty + AOVs: the queue kernel for the beauty sums, the AOV planes from a primary-ray pass of their own
             // (1080p x 64 spp against k_render with AOVs: quirks 62.7 -> 52.5 ms, Weekend 40.7 -> 41.0; on the 1 M-triangle
@@ -249,9 +251,9 @@ int launch_share(zb_context* ctx, RenderParams P, const zb_render_opts* o, const
             if (rc2) return rc2;
             unsigned long long* heads = ctx->pq_fix + zbk_pq_words(pixels, 0);
             ZB_CUDA(zbk_pq_clear(ctx->pq_fix, pixels, 0, heads, 1, ctx->stream));
-            ZB_CUDA(zbk_launch_render_pq(B, owned_tiles(B), 0, ctx->pq_fix, heads, ctx->sm_count, ctx->stream));
+            ZB_CUDA(zbk_launch_render_pq(B, owned_tiles(B), 0, ctx->pq_fix, heads, ctx->sm_count, tn, ctx->stream));
             ZB_CUDA(zbk_pq_resolve(B, 0, ctx->pq_fix, 0, B.cam.height, 0.f, nullptr, ctx->stream));
-            ZB_CUDA(zbk_launch_aov_pass(P, owned_tiles(P), ctx->stream));
+            ZB_CUDA(zbk_launch_aov_pass(P, owned_tiles(P), tn, ctx->stream));
             ctx->stats.launches += 3;
         } else if (pq && !o->collect_stats && P.max_depth > 0 && P.sample_end > P.sample_begin &&
                    (pq_all || (!P.light_pass && !P.accum_aux))) {
@@ -260,11 +262,11 @@ int launch_share(zb_context* ctx, RenderParams P, const zb_render_opts* o, const
             if (rc2) return rc2;
             unsigned long long* heads = ctx->pq_fix + zbk_pq_words(pixels, mode);
             ZB_CUDA(zbk_pq_clear(ctx->pq_fix, pixels, mode, heads, 1, ctx->stream));
-            ZB_CUDA(zbk_launch_render_pq(P, owned_tiles(P), mode, ctx->pq_fix, heads, ctx->sm_count, ctx->stream));
+            ZB_CUDA(zbk_launch_render_pq(P, owned_tiles(P), mode, ctx->pq_fix, heads, ctx->sm_count, tn, ctx->stream));
             ZB_CUDA(zbk_pq_resolve(P, mode, ctx->pq_fix, 0, P.cam.height, 0.f, nullptr, ctx->stream));
             ctx->stats.launches += 2;
         } else {
-            ZB_CUDA(zbk_launch_render(P, owned_tiles(P), o->collect_stats != 0, ctx->stream));
+            ZB_CUDA(zbk_launch_render(P, owned_tiles(P), o->collect_stats != 0, tn, ctx->stream));
             ctx->stats.launches++;
         }
         done = P.sample_end - sb;
@@ -361,7 +363,15 @@ int read_counters(zb_context* ctx) {
     ctx->stats.prim_tests = c[2];
     ctx->stats.instance_visits = c[3];
     ctx->stats.paths = c[4];
+    ctx->stats.stack_overflows = uint32_t(std::min<unsigned long long>(c[6], 0xFFFFFFFFull));
     return ZB_OK;
+}
+
+// a ray that ran out of traversal stack has dropped geometry: the frame is not the scene's (csrc/trace.cuh)
+int check_overflow(zb_context* ctx, const char* who) {
+    if (ctx->stats.stack_overflows == 0) return ZB_OK;
+    return fail(ZB_ERR_UNSUPPORTED, std::string(who) + ": " + std::to_string(ctx->stats.stack_overflows) +
+                                        " traversal-stack overflows (tree deeper than the depth caps); outputs are incomplete");
 }
 
 }  // namespace
@@ -515,6 +525,8 @@ extern "C" int zb_render(zb_context* ctx, const zb_scene* scene, const zb_camera
     ctx->stats.resolve_ms = ms;
     ZB_CUDA(cudaEventElapsedTime(&ms, ctx->ev[2], ctx->ev[3]));
     ctx->stats.d2h_ms = ms;
+    rc = check_overflow(ctx, "zb_render");
+    if (rc) return rc;
     if (progress) progress(cam->image_height, user);  // camera.hpp:576-578
     return ZB_OK;
 }
@@ -539,13 +551,15 @@ extern "C" int zb_primary_ids(zb_context* ctx, const zb_scene* scene, const zb_c
     uint32_t* d_leaf = ctx->id_scratch;
     uint32_t* d_prim = ctx->id_scratch + pixels;
     float* d_t = reinterpret_cast<float*>(ctx->id_scratch + 2 * pixels);
+    ZB_CUDA(cudaMemsetAsync(ctx->counters + 6, 0, sizeof(unsigned long long), ctx->stream));
     ZB_CUDA(zbk_launch_primary_ids(P, d_leaf, d_prim, d_t, ctx->stream));
     ctx->stats.launches++;
     if (leaf_id) ZB_CUDA(cudaMemcpyAsync(leaf_id, d_leaf, pixels * 4, cudaMemcpyDeviceToHost, ctx->stream));
     if (prim_id) ZB_CUDA(cudaMemcpyAsync(prim_id, d_prim, pixels * 4, cudaMemcpyDeviceToHost, ctx->stream));
     if (t) ZB_CUDA(cudaMemcpyAsync(t, d_t, pixels * 4, cudaMemcpyDeviceToHost, ctx->stream));
-    ZB_CUDA(cudaStreamSynchronize(ctx->stream));
-    return ZB_OK;
+    rc = read_counters(ctx);
+    if (rc) return rc;
+    return check_overflow(ctx, "zb_primary_ids");
 }
 
 extern "C" int zb_probe_rays(zb_context* ctx, const zb_scene* scene, const zb_environment* env, size_t n,
@@ -560,7 +574,8 @@ extern "C" int zb_probe_rays(zb_context* ctx, const zb_scene* scene, const zb_en
     if (rc || n == 0) return rc;
     float *d_o = nullptr, *d_d = nullptr;
     zb_probe* d_out = nullptr;
-    cudaError_t e = cudaMalloc(&d_o, n * 12);
+    cudaError_t e = cudaMemsetAsync(ctx->counters + 6, 0, sizeof(unsigned long long), ctx->stream);
+    if (e == cudaSuccess) e = cudaMalloc(&d_o, n * 12);
     if (e == cudaSuccess) e = cudaMalloc(&d_d, n * 12);
     if (e == cudaSuccess) e = cudaMalloc(&d_out, n * sizeof(zb_probe));
     if (e == cudaSuccess) e = cudaMemcpyAsync(d_o, origins, n * 12, cudaMemcpyHostToDevice, ctx->stream);
@@ -573,7 +588,9 @@ extern "C" int zb_probe_rays(zb_context* ctx, const zb_scene* scene, const zb_en
     cudaFree(d_out);
     if (e != cudaSuccess) return fail(ZB_ERR_CUDA, std::string("zb_probe_rays: ") + cudaGetErrorString(e));
     ctx->stats.launches++;
-    return ZB_OK;
+    rc = read_counters(ctx);
+    if (rc) return rc;
+    return check_overflow(ctx, "zb_probe_rays");
 }
 
 extern "C" int zb_checkpoint_save(zb_context* ctx, const char* path, const void* accum_f4, int width, int height,

@@ -476,6 +476,7 @@ __global__ void __launch_bounds__(ZB_BLOCK_THREADS, MIN_BLOCKS) k_render_pq(cons
     }
 }
 
+#ifdef ZB_EXPERIMENTS  // measured 1..22 % slower than k_render_pq at every threshold (profiles/r01_traversal_experiments.txt)
 // k_render_pqr — k_render_pq's beauty pass with RESUMABLE traversal: the traversal state of a lane (RayWalk + its stack) lives
 // across iterations of the warp's main loop, and the warp leaves the traversal loop as soon as fewer than `thresh` of its lanes
 // still hold an unfinished ray while others wait with a finished one.  The finished lanes are shaded and get their next ray (or
@@ -626,6 +627,8 @@ __global__ void __launch_bounds__(ZB_BLOCK_THREADS, MIN_BLOCKS) k_render_pqr(con
         if (lane == 0 && x) atomicAdd(P.counters + (k ? 4 : 0), (unsigned long long)x);
     }
 }
+
+#endif  // ZB_EXPERIMENTS
 
 // First-hit AOVs (K8, camera.hpp:464-488, :518-526) as a pass of their own beside k_render_pq: one thread per pixel walks
 // the pixel's first aux_samples samples, regenerates the camera ray of (pixel, sample) — the same Philox draws as the
@@ -836,8 +839,8 @@ namespace {
 constexpr uint32_t F_PLAIN = 0, F_BOXES = ZB_F_INST | ZB_F_CUBE | ZB_F_TRI | ZB_F_MEDIA, F_MESH0 = ZB_F_INST | ZB_F_MESH | ZB_F_TRI,
                    F_MESH = F_MESH0 | ZB_F_TEX, F_NOMESH = ZB_F_ALL & ~(ZB_F_MESH | ZB_F_TRI), F_SPHTE = ZB_F_TEX | ZB_F_ENV,
                    F_NOMEDIA = ZB_F_ALL & ~ZB_F_MEDIA;
-uint32_t pick_feature_set(const RenderParams& P) {
-    if (getenv("ZB_NO_LEAN") && atoi(getenv("ZB_NO_LEAN")) != 0) return ZB_F_ALL;
+uint32_t pick_feature_set(const RenderParams& P, const ZbTuning& tn) {
+    if (tn.no_lean) return ZB_F_ALL;
     const uint32_t need = (P.sc.features & ZB_F_ALL) | (P.env.mode == ZB_ENV_SOLID_COLOR ? 0u : uint32_t(ZB_F_ENV));
     for (uint32_t f : {F_PLAIN, F_SPHTE, F_BOXES, F_MESH0, F_MESH, F_NOMESH, F_NOMEDIA})
         if ((need & ~f) == 0) return f;
@@ -856,12 +859,25 @@ uint32_t pick_feature_set(const RenderParams& P) {
         default: { constexpr uint32_t F = ZB_F_ALL; CALL; } break;          \
     }
 
-cudaError_t zbk_launch_render(const RenderParams& P, int n_tiles_owned, bool stats, cudaStream_t stream) {
+ZbTuning zbk_tuning_from_env() {
+    ZbTuning t;
+    auto num = [](const char* name, long long dflt) { const char* e = getenv(name); return e ? atoll(e) : dflt; };
+    t.pq = int(num("ZB_PQ", t.pq));
+    t.no_lean = num("ZB_NO_LEAN", 0) != 0;
+    t.pq_blocks = int(num("ZB_PQ_BLOCKS", 0));
+    t.pq_resume = int(num("ZB_PQ_RESUME", 0));
+    t.wavefront = num("ZB_WAVEFRONT", 0) > 0;
+    t.wf_slots = num("ZB_WF_SLOTS", 0);
+    t.gather_p2p = int(num("ZB_GATHER_P2P", 1));
+    return t;
+}
+
+cudaError_t zbk_launch_render(const RenderParams& P, int n_tiles_owned, bool stats, const ZbTuning& tn, cudaStream_t stream) {
     if (n_tiles_owned <= 0) return cudaSuccess;
     // A shared-memory ray-pool variant of this kernel was measured 20-40 % slower on the headline frame
     // (profiles/r01_pool_vs_queue.txt) and removed.
     if (P.light_pass) {
-        const uint32_t feat = pick_feature_set(P);
+        const uint32_t feat = pick_feature_set(P, tn);
         ZB_FOR_FEATURE_SET(feat, (k_render<false, true, F><<<n_tiles_owned, ZB_BLOCK_THREADS, 0, stream>>>(P)));
     }
     else if (stats) k_render<true, false><<<n_tiles_owned, ZB_BLOCK_THREADS, 0, stream>>>(P);
@@ -890,7 +906,7 @@ static void pq_launch_beauty(int per_sm, unsigned blocks, cudaStream_t stream, c
 // the queue kernel alone: the sums and `*head` must be zero (zbk_pq_clear); tiles P.tile_rank + i * P.tile_ranks,
 // i < n_tiles.  The aux sums follow the 3 * pixels beauty sums in `fix`.
 cudaError_t zbk_launch_render_pq(const RenderParams& P, int n_tiles_owned, int mode, unsigned long long* fix, unsigned long long* head,
-                                 int sm_count, cudaStream_t stream) {
+                                 int sm_count, const ZbTuning& tn, cudaStream_t stream) {
     if (n_tiles_owned <= 0) return cudaSuccess;
     const size_t pixels = size_t(P.cam.width) * P.cam.height;
     unsigned long long* fix_aux = mode == PQ_BEAUTY ? nullptr : fix + 3 * pixels;
@@ -898,8 +914,8 @@ cudaError_t zbk_launch_render_pq(const RenderParams& P, int n_tiles_owned, int m
     const unsigned long long warps_needed = (total + 31) / 32;
     // beauty renders run the smallest compiled feature set that covers the scene and its environment (pick_feature_set);
     // ZB_PQ_BLOCKS=6..8 overrides the resident blocks per SM of the specialised instantiations
-    const int env_blocks = getenv("ZB_PQ_BLOCKS") ? atoi(getenv("ZB_PQ_BLOCKS")) : 0;
-    const uint32_t feat = mode == PQ_BEAUTY ? pick_feature_set(P) : uint32_t(ZB_F_ALL);
+    const int env_blocks = tn.pq_blocks;
+    const uint32_t feat = mode == PQ_BEAUTY ? pick_feature_set(P, tn) : uint32_t(ZB_F_ALL);
     const bool big_tree = P.sc.n_nodes >= PQ_BIG_TREE_NODES;
     // resident blocks per SM, measured per feature set at 1080p x 16 spp with 5 / 6 / 7 / 8 blocks (profiles/r01_feature_sets.txt):
     // Cornell 15.31 / 14.42 / 14.14 / 14.07 ms, exterior 18.74 / 18.17 / 17.42 / 17.83, mesh 17.95 / 16.86 / 16.67 / 16.04
@@ -912,22 +928,25 @@ cudaError_t zbk_launch_render_pq(const RenderParams& P, int n_tiles_owned, int m
     const unsigned long long per_warp = total / (4ull * blocks);
     const unsigned batch = per_warp >= 64ull * PQ_BATCH ? PQ_BATCH : per_warp >= 64ull * (PQ_BATCH / 2) ? PQ_BATCH / 2 : PQ_BATCH / 4;
 #define PQ_LAUNCH(B, M) k_render_pq<B, M><<<blocks, ZB_BLOCK_THREADS, 0, stream>>>(P, fix, fix_aux, head, total, batch)
-    const int resume = getenv("ZB_PQ_RESUME") ? atoi(getenv("ZB_PQ_RESUME")) : 0;  // experiment: resumable traversal (k_render_pqr)
+#ifdef ZB_EXPERIMENTS
+    const int resume = tn.pq_resume;  // experiment: resumable traversal (k_render_pqr)
     if (mode == PQ_BEAUTY && feat == F_PLAIN && resume > 0) {
         if (per_sm == 7) k_render_pqr<7, F_PLAIN><<<blocks, ZB_BLOCK_THREADS, 0, stream>>>(P, fix, head, total, batch, unsigned(resume));
         else if (per_sm == 6) k_render_pqr<6, F_PLAIN><<<blocks, ZB_BLOCK_THREADS, 0, stream>>>(P, fix, head, total, batch, unsigned(resume));
         else k_render_pqr<8, F_PLAIN><<<blocks, ZB_BLOCK_THREADS, 0, stream>>>(P, fix, head, total, batch, unsigned(resume));
     }
-    else if (mode == PQ_AUX) { if (per_sm == 7) PQ_LAUNCH(7, PQ_AUX); else PQ_LAUNCH(6, PQ_AUX); }
+    else
+#endif
+    if (mode == PQ_AUX) { if (per_sm == 7) PQ_LAUNCH(7, PQ_AUX); else PQ_LAUNCH(6, PQ_AUX); }
     else if (mode == PQ_LIGHT) { if (per_sm == 7) PQ_LAUNCH(7, PQ_LIGHT); else PQ_LAUNCH(6, PQ_LIGHT); }
     else { ZB_FOR_FEATURE_SET(feat, (pq_launch_beauty<F>(per_sm, blocks, stream, P, fix, head, total, batch))); }
 #undef PQ_LAUNCH
     return cudaGetLastError();
 }
 
-cudaError_t zbk_launch_aov_pass(const RenderParams& P, int n_tiles_owned, cudaStream_t stream) {
+cudaError_t zbk_launch_aov_pass(const RenderParams& P, int n_tiles_owned, const ZbTuning& tn, cudaStream_t stream) {
     if (n_tiles_owned <= 0 || !P.accum_aux) return cudaSuccess;
-    const uint32_t feat = pick_feature_set(P);
+    const uint32_t feat = pick_feature_set(P, tn);
     ZB_FOR_FEATURE_SET(feat, (k_aov_pass<F><<<n_tiles_owned, ZB_BLOCK_THREADS, 0, stream>>>(P)));
     return cudaGetLastError();
 }

@@ -162,6 +162,19 @@ __global__ void __launch_bounds__(256) k_alive(const int2* __restrict__ range, i
     alive[i] = (i == 0 || r.y - r.x + 1 > LBVH_LEAF_MAX) ? 1 : 0;
 }
 
+// depth of the emitted tree: surviving inner nodes above each sorted triangle, maximum over the mesh.  A Karras tree over
+// 30-bit codes plus the index tie-break can be deeper than the traversal stack allows (ZB_MAX_BLAS_DEPTH); the build
+// then fails loudly instead of handing the renderer a tree whose deferred children it would drop.
+__global__ void __launch_bounds__(256) k_depth(const int* __restrict__ parent_int, const int* __restrict__ parent_leaf,
+                                               const int* __restrict__ alive, int n, int* __restrict__ max_depth) {
+    const int k = blockIdx.x * blockDim.x + threadIdx.x;
+    int d = 0;
+    if (k < n)
+        for (int node = parent_leaf[k]; node >= 0; node = parent_int[node]) d += alive[node];
+    d = __reduce_max_sync(0xFFFFFFFFu, d);
+    if ((threadIdx.x & 31) == 0 && d > 0) atomicMax(max_depth, d);
+}
+
 // pass 5b: the renderer's 64-byte node (zb_bvh_node: both child boxes in the parent) for every surviving node
 __global__ void __launch_bounds__(256) k_emit(const int2* __restrict__ child, const int2* __restrict__ range, const int* __restrict__ alive,
                                               const int* __restrict__ compact, const float* __restrict__ leaf_box,
@@ -244,13 +257,13 @@ int zbk_build_blas_device(zb_context* ctx, const float4* tris_in, const float4* 
     uint32_t *bounds, *keys, *keys2, *ids, *ids2;
     float *leaf_box, *node_box;
     int2 *child, *range;
-    int *parent_int, *parent_leaf, *visits, *alive, *compact;
+    int *parent_int, *parent_leaf, *visits, *alive, *compact, *max_depth;
     ZB_CUDA(sc.get(&bounds, 6));
     ZB_CUDA(sc.get(&keys, n)); ZB_CUDA(sc.get(&keys2, n)); ZB_CUDA(sc.get(&ids, n)); ZB_CUDA(sc.get(&ids2, n));
     ZB_CUDA(sc.get(&leaf_box, 6 * size_t(n))); ZB_CUDA(sc.get(&node_box, 6 * size_t(n)));
     ZB_CUDA(sc.get(&child, n)); ZB_CUDA(sc.get(&range, n));
     ZB_CUDA(sc.get(&parent_int, n)); ZB_CUDA(sc.get(&parent_leaf, n)); ZB_CUDA(sc.get(&visits, n));
-    ZB_CUDA(sc.get(&alive, n)); ZB_CUDA(sc.get(&compact, n + 1));
+    ZB_CUDA(sc.get(&alive, n)); ZB_CUDA(sc.get(&compact, n + 1)); ZB_CUDA(sc.get(&max_depth, 1));
     const uint32_t init[6] = {0xFFFFFFFFu, 0xFFFFFFFFu, 0xFFFFFFFFu, 0u, 0u, 0u};
     ZB_CUDA(cudaMemcpyAsync(bounds, init, sizeof(init), cudaMemcpyHostToDevice, st));
     k_centroid_bounds<<<std::min(nb, unsigned(ctx->sm_count) * 8u), 256, 0, st>>>(tris_in, n, bounds);
@@ -278,6 +291,8 @@ int zbk_build_blas_device(zb_context* ctx, const float4* tris_in, const float4* 
     k_hierarchy<<<nbi, 256, 0, st>>>(keys2, int(n), child, range, parent_int, parent_leaf);
     k_fit<<<nb, 256, 0, st>>>(tris_in, ids2, int(n), child, parent_int, parent_leaf, leaf_box, node_box, visits);
     k_alive<<<nbi, 256, 0, st>>>(range, n_int, alive);
+    ZB_CUDA(cudaMemsetAsync(max_depth, 0, sizeof(int), st));
+    k_depth<<<nb, 256, 0, st>>>(parent_int, parent_leaf, alive, int(n), max_depth);
     ZB_CUDA(cudaGetLastError());
     size_t scan_bytes = 0;
     ZB_CUDA(cub::DeviceScan::ExclusiveSum(nullptr, scan_bytes, alive, compact, n_int + 1, st));
@@ -287,10 +302,14 @@ int zbk_build_blas_device(zb_context* ctx, const float4* tris_in, const float4* 
     ZB_CUDA(cub::DeviceScan::ExclusiveSum(scan_tmp, scan_bytes, alive, compact, n_int + 1, st));
     k_emit<<<nbi, 256, 0, st>>>(child, range, alive, compact, leaf_box, node_box, n_int, tri_first, int(node_base), nodes_out);
     ZB_CUDA(cudaGetLastError());
-    ctx->stats.launches += 5;
-    int total = 0;
+    ctx->stats.launches += 6;
+    int total = 0, depth = 0;
     ZB_CUDA(cudaMemcpyAsync(&total, compact + n_int, sizeof(int), cudaMemcpyDeviceToHost, st));
+    ZB_CUDA(cudaMemcpyAsync(&depth, max_depth, sizeof(int), cudaMemcpyDeviceToHost, st));
     ZB_CUDA(cudaStreamSynchronize(st));
+    if (depth > ZB_MAX_BLAS_DEPTH)
+        return fail(ZB_ERR_UNSUPPORTED, "device LBVH of a mesh is " + std::to_string(depth) + " levels deep (cap " +
+                                            std::to_string(ZB_MAX_BLAS_DEPTH) + "): flatten without ZB_FLATTEN_GPU_BLAS for this scene");
     *n_nodes = uint32_t(total);
     return ZB_OK;
 }

@@ -21,7 +21,10 @@ struct SceneDev {
     const float4* texels_f32;
     uint32_t n_nodes, n_items, n_media;
     uint32_t features;  // ZB_F_* bits the scene needs, set by zb_scene_upload
-
+    // traversal-stack overflow events (trace.cuh): one u64 in the owning context's counter block, never null.  The
+    // builders bound the tree depth so that this stays 0 (ZB_MAX_TLAS_DEPTH / ZB_MAX_BLAS_DEPTH); a non-zero count
+    // turns the render into ZB_ERR_UNSUPPORTED instead of a frame with missing geometry.
+    unsigned long long* overflow;
 };
 
 // camera::initialize (camera.hpp:358-402) evaluated in double on the host, then narrowed.

@@ -12,6 +12,10 @@
 #include "scene_dev.cuh"
 
 #define ZB_STACK 64
+// Stack budget of one ray: the sentinel, at most one deferred child per TLAS level, three entries for a dive into a
+// mesh (rest of the leaf, exit marker, BLAS root) and one deferred child per BLAS level:
+//   1 + ZB_MAX_TLAS_DEPTH + 3 + ZB_MAX_BLAS_DEPTH <= ZB_STACK   (include/zenith_b200.h; checked by zb_scene_upload)
+static_assert(1 + ZB_MAX_TLAS_DEPTH + 3 + ZB_MAX_BLAS_DEPTH <= ZB_STACK, "traversal stack too small for the depth caps");
 #ifndef ZB_BOX_CH
 #define ZB_BOX_CH 1
 #endif
@@ -269,7 +273,10 @@ ZB_DEV bool tlas_leaf(const SceneDev& sc, uint32_t code, float3 o, float3 d, flo
             float3 lo = xform_point(ih.w2o, o), ld = xform_vector(ih.w2o, d);
             if ((F & ZB_F_MESH) && ih.geom_kind == ZB_GEOM_MESH) {
                 // defer the rest of this leaf, then dive into the BLAS in object space
-                if (sp + 3 > ZB_STACK) return false;
+                if (sp + 3 > ZB_STACK) {  // cannot happen for a scene zb_scene_upload accepted; counted, never silent
+                    atomicAdd(sc.overflow, 1ull);
+                    return false;
+                }
                 if (i + 1 < end) stack[sp++] = int(~(((i + 1) << 3) | (end - i - 2)));
                 stack[sp++] = ZB_EXIT_INSTANCE;
                 stack[sp++] = int(ih.node_root);
@@ -365,12 +372,14 @@ struct RayWalk {
         const bool any = hl || hr, both = hl && hr;
         if (both) stack[sp] = right_first ? cl : cr;
         const int top = stack[sp - 1];
-        sp = both ? min(sp + 1, ZB_STACK - 1) : any ? sp : sp - 1;  // deeper than any tree the host builder emits (bvh_build.hpp)
+        if (both && sp >= ZB_STACK - 1) atomicAdd(sc.overflow, 1ull);
+        sp = both ? min(sp + 1, ZB_STACK - 1) : any ? sp : sp - 1;
         cur = any ? next : top;
 #else
         if (hl && hr) {
             stack[sp] = right_first ? cl : cr;
-            sp = min(sp + 1, ZB_STACK - 1);
+            if (sp < ZB_STACK - 1) sp++;
+            else atomicAdd(sc.overflow, 1ull);  // deferred subtree lost: counted (zb_stats::stack_overflows), the render fails
         }
         if (!(hl || hr)) next = stack[--sp];
         cur = next;

@@ -16,6 +16,7 @@
 // Same RNG keys, estimator, termination rules and shading code (shade.cuh) as the megakernel.
 // State per slot: 5 float4 = 80 B; per ray and bounce the two kernels move ~200 B, served from L2 when the slot count
 // is kept below ~1 M.
+#ifdef ZB_EXPERIMENTS  // rejected form, kept for A/B runs only (build.sh: ZB_EXPERIMENTS=1)
 #include "shade.cuh"
 #include "kernels.h"
 
@@ -381,3 +382,5 @@ cudaError_t zbk_launch_wavefront(const RenderParams& P, zb_wf_scratch** scratch,
     if (iterations) *iterations = iters;
     return cudaGetLastError();
 }
+
+#endif  // ZB_EXPERIMENTS

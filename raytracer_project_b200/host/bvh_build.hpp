@@ -42,9 +42,13 @@ public:
     // boxes: one per primitive.  On return `order[i]` is the primitive stored at leaf slot i and
     // `nodes` holds the tree (root = nodes[0]); leaves reference [first, first+count) of `order`.
     // leaf_base is added to every leaf `first` (so several BLASes can share one primitive array).
+    // max_depth: cap on the number of inner nodes along any root-to-leaf path (ZB_MAX_TLAS_DEPTH / ZB_MAX_BLAS_DEPTH;
+    // the device traversal stack holds one deferred child per level).  SAH splits are taken while both children can
+    // still be finished by balanced median splits within the cap; from there on the subtree is split by count.
     void build(const std::vector<build_box>& boxes, int max_leaf, uint32_t leaf_base, std::vector<zb_bvh_node>& nodes,
-               std::vector<uint32_t>& order) {
+               std::vector<uint32_t>& order, int max_depth = ZB_MAX_BLAS_DEPTH) {
         in = &boxes;
+        depth_cap = std::max(1, max_depth);
         leaf_cap = std::max(1, std::min(max_leaf, 8));
         base = leaf_base;
         const size_t n = boxes.size();
@@ -57,7 +61,7 @@ public:
         for (size_t i = 0; i < n; i++)
             for (int k = 0; k < 3; k++) cent[3 * i + k] = 0.5 * (boxes[i].lo[k] + boxes[i].hi[k]);
         ord = &order;
-        int root = split(0, n);
+        int root = split(0, n, 0);
         if (tmp[root].count > 0) {  // single-leaf scene: wrap it so the root is always an inner node
             tnode r;
             r.box = tmp[root].box;
@@ -84,6 +88,13 @@ private:
     std::vector<double> cent;
     std::vector<tnode> tmp;
     int leaf_cap = 4;
+    int depth_cap = ZB_MAX_BLAS_DEPTH;
+    // inner levels a balanced (split-by-count) tree over n primitives needs, this node included; 0 = one leaf
+    int balanced_levels(size_t n) const {
+        int l = 0;
+        while (n > size_t(leaf_cap)) { n = (n + 1) / 2; l++; }
+        return l;
+    }
 public:
     // cost of one primitive test in units of one node visit (SAH leaf-versus-split decision)
     double isect_cost = 1.0;
@@ -99,7 +110,7 @@ private:
         return int(tmp.size()) - 1;
     }
 
-    int split(size_t lo, size_t hi) {
+    int split(size_t lo, size_t hi, int depth) {  // depth = inner nodes above this one
         auto& o = *ord;
         const size_t n = hi - lo;
         build_box box = build_box::empty(), cbox = build_box::empty();
@@ -145,10 +156,31 @@ private:
         const double leaf_cost = c_isect * double(n);
         const double ha = box.half_area();
         const double split_cost = ha > 0 ? c_trav + c_isect * best / ha : infinity;
-        if (n <= size_t(leaf_cap) && (best_axis < 0 || leaf_cost <= split_cost)) return make_leaf(lo, hi, box);
+        if (n <= size_t(leaf_cap) && (best_axis < 0 || leaf_cost <= split_cost || depth >= depth_cap)) return make_leaf(lo, hi, box);
         size_t mid;
-        if (best_axis < 0) {  // all centroids coincide: split by count
-            mid = lo + n / 2;
+        bool by_count = best_axis < 0;  // all centroids coincide: split by count
+        if (!by_count) {
+            // would the SAH split leave a child that cannot be finished within the depth cap?
+            size_t nl = 0;
+            {
+                double ext = cbox.hi[best_axis] - cbox.lo[best_axis];
+                double k1 = NB * (1 - 1e-9) / ext;
+                for (size_t i = lo; i < hi; i++) {
+                    int b = int(k1 * (cent[3 * o[i] + best_axis] - cbox.lo[best_axis]));
+                    nl += std::max(0, std::min(NB - 1, b)) <= best_bin ? 1 : 0;
+                }
+            }
+            if (nl == 0 || nl == n) nl = n / 2;
+            if (depth + 1 + std::max(balanced_levels(nl), balanced_levels(n - nl)) > depth_cap) by_count = true;
+        }
+        if (by_count) {
+            mid = lo + (n + 1) / 2;
+            int axis = 0;
+            for (int k = 1; k < 3; k++)
+                if (cbox.hi[k] - cbox.lo[k] > cbox.hi[axis] - cbox.lo[axis]) axis = k;
+            if (best_axis >= 0)  // depth-capped: median along the widest centroid axis
+                std::nth_element(o.begin() + lo, o.begin() + mid, o.begin() + hi,
+                                 [&](uint32_t a, uint32_t b) { return cent[3 * a + axis] < cent[3 * b + axis]; });
         } else {
             double ext = cbox.hi[best_axis] - cbox.lo[best_axis];
             double k1 = NB * (1 - 1e-9) / ext;
@@ -163,8 +195,8 @@ private:
         int self = int(tmp.size());
         tmp.emplace_back();
         tmp[self].box = box;
-        int l = split(lo, mid);
-        int r = split(mid, hi);
+        int l = split(lo, mid, depth + 1);
+        int r = split(mid, hi, depth + 1);
         tmp[self].left = l;
         tmp[self].right = r;
         return self;

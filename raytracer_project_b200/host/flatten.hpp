@@ -90,7 +90,7 @@ public:
         // item wherever a split is possible.  Measured against 1.0: exterior -3.3 %, quirks -2.8 %, Weekend +-0.2 %;
         // an exact sweep SAH instead of 16 bins changed nothing (profiles/r01_pq.txt)
         b.isect_cost = 1.5;
-        b.build(item_boxes, tlas_leaf, 0, tl, order);
+        b.build(item_boxes, tlas_leaf, 0, tl, order, ZB_MAX_TLAS_DEPTH);
         std::vector<zb_item> sorted(order.size());
         for (size_t i = 0; i < order.size(); i++) sorted[i] = out->items[order[i]];
         out->items.swap(sorted);
@@ -387,7 +387,7 @@ private:
             } else {
                 bvh_builder b;
                 std::vector<uint32_t> order;
-                b.build(boxes, blas_leaf, first, nd, order);
+                b.build(boxes, blas_leaf, first, nd, order, ZB_MAX_BLAS_DEPTH);
                 for (uint32_t slot : order) push_tri(m.tris[slot].v, m.tris[slot].n, slot);
             }
             zb_mesh zm{0, 0, first, uint32_t(m.tris.size())};

@@ -274,6 +274,18 @@ def materialize(directory: str, text: str, cfg: RenderConfig, files: dict | None
     return os.path.join(directory, "s.zscene")
 
 
+ASSET_DIR = __import__("os").path.join(__import__("os").path.dirname(__import__("os").path.dirname(__import__("os").path.abspath(__file__))),
+                                     "tests", "golden", "assets")
+
+
+def shipped_asset(rel: str) -> bytes:
+    """Bytes of one of the reference's shipped assets (assets/models/*.obj, assets/bump_maps/*.jpg,
+    assets/textures/*), committed as test vectors under tests/golden/assets/."""
+    import os
+    with open(os.path.join(ASSET_DIR, rel), "rb") as f:
+        return f.read()
+
+
 def _quad(w: SceneWriter, p0, p1, p2, p3, n, mat):
     """A quad as the two triangles the reference needs (it has no quad primitive)."""
     return [w.triangle(p0, p1, p2, n, n, n, mat), w.triangle(p0, p2, p3, n, n, n, mat)]
@@ -353,13 +365,15 @@ def _torus_obj(nu: int = 48, nv: int = 24, R: float = 1.0, r: float = 0.35) -> s
 
 
 def mesh(seed: int = 3, width: int = 1920, height: int = 1080, spp: int = 64, max_depth: int = 50, grid: int = 708,
-         knots: int = 12):
+         knots: int = 12, shipped: bool = False):
     """C3: an OBJ heightfield of 2 (grid-1)^2 triangles (grid 708 -> 999 698) loaded by
     model(path, nullptr, 1.0) under a material_instance, plus `knots` instances of one shared torus OBJ as
-    translate(rotate_y(scale(model))) with library-style materials (scene_management.hpp:57-99)."""
+    translate(rotate_y(scale(model))) with library-style materials (scene_management.hpp:57-99).  shipped=True instances
+    the reference's own assets/models/torus_knot.obj (4 860 triangles) instead of the synthetic torus."""
     rng = random.Random(seed)
     w = SceneWriter()
-    files = {"heightfield.obj": _heightfield_obj(grid, seed), "torus.obj": _torus_obj()}
+    files = {"heightfield.obj": _heightfield_obj(grid, seed),
+             "torus.obj": shipped_asset("models/torus_knot.obj") if shipped else _torus_obj()}
     ground = w.lambertian((0.45, 0.55, 0.35))
     objs = [w.matinst(w.model("heightfield.obj", None, 1.0), ground)]
     checker = w.tex_checker(0.5, w.tex_solid((0.1, 0.1, 0.1)), w.tex_solid((0.9, 0.9, 0.9)))
@@ -369,7 +383,7 @@ def mesh(seed: int = 3, width: int = 1920, height: int = 1080, spp: int = 64, ma
     for k in range(knots):
         ang = 2 * math.pi * k / max(knots, 1)
         rad = 2.2 + 1.6 * rng.random()
-        s = 0.35 + 0.4 * rng.random()
+        s = (0.35 + 0.4 * rng.random()) * (0.45 if shipped else 1.0)  # the shipped knot spans about +-2.3 units
         inst = w.rotate("y", w.scale(torus, (s, s * (0.7 + 0.6 * rng.random()), s)), rng.random() * math.pi)
         inst = w.matinst(inst, mats[k % len(mats)])
         objs.append(w.translate(inst, (rad * math.cos(ang), 0.9 + 0.8 * rng.random(), rad * math.sin(ang))))
@@ -425,7 +439,7 @@ def _noise_tex(size: int, seed: int, octaves: int = 4, channels: int = 1):
 
 
 def exterior(seed: int = 4, width: int = 1920, height: int = 1080, spp: int = 128, max_depth: int = 50, small: int = 200,
-             hdr_size: int = 2048, sun_radiance: float = 5.0e4):
+             hdr_size: int = 2048, sun_radiance: float = 5.0e4, shipped: bool = False):
     """C4: HDRI-lit exterior with thin-lens DOF (defocus_angle 3.0, focus_dist 9.0):
     r=1000 ground with a reflective checker metal, bump-mapped mirror / gold / wood spheres, a bumpy-glass
     2x2x2 cube, and `small` instanced cubes/spheres built exactly like the reference's demo grid
@@ -436,13 +450,22 @@ def exterior(seed: int = 4, width: int = 1920, height: int = 1080, spp: int = 12
     rng = random.Random(seed)
     w = SceneWriter()
     files = {}
-    files.update(ztex.ldr_pair("scratches.png", _noise_tex(512, seed * 10 + 1, octaves=6)))
-    files.update(ztex.ldr_pair("woodbump.png", _noise_tex(512, seed * 10 + 2, octaves=3)))
-    files.update(ztex.ldr_pair("concrete.png", _noise_tex(256, seed * 10 + 3, octaves=5)))
-    files.update(ztex.ldr_pair("wood.png", _noise_tex(512, seed * 10 + 4, octaves=4, channels=3)))
+    if shipped:
+        # the reference's own JPEGs under their own relative paths (scene_management.hpp:51-54, :67-68): baseline and
+        # progressive, 4:2:0 and 4:4:4 — decoded by stb_image there and by host/jpeg_png.hpp here, no side-car dumps
+        names = ("assets/bump_maps/scratches_bump_map.jpg", "assets/bump_maps/wood_bump_map.jpg",
+                 "assets/bump_maps/concrete_bump_map.jpg", "assets/textures/fine-wood.jpg")
+        for n in names:
+            files[n] = shipped_asset(n[len("assets/"):])
+    else:
+        names = ("scratches.png", "woodbump.png", "concrete.png", "wood.png")
+        files.update(ztex.ldr_pair("scratches.png", _noise_tex(512, seed * 10 + 1, octaves=6)))
+        files.update(ztex.ldr_pair("woodbump.png", _noise_tex(512, seed * 10 + 2, octaves=3)))
+        files.update(ztex.ldr_pair("concrete.png", _noise_tex(256, seed * 10 + 3, octaves=5)))
+        files.update(ztex.ldr_pair("wood.png", _noise_tex(512, seed * 10 + 4, octaves=4, channels=3)))
     files.update(ztex.hdr_pair("sky.hdr", _sky_hdr(hdr_size, hdr_size // 2, sun_radiance)))
-    scratches, woodbump, concrete = (w.tex_image(n) for n in ("scratches.png", "woodbump.png", "concrete.png"))
-    wood = w.tex_image("wood.png")
+    scratches, woodbump, concrete = (w.tex_image(n) for n in names[:3])
+    wood = w.tex_image(names[3])
     checker = w.tex_checker(0.5, w.tex_solid((0.1, 0.1, 0.1)), w.tex_solid((0.9, 0.9, 0.9)))
     objs = [w.matinst(w.sphere((0, -1000, 0), 1000.0, None), w.metal(tex=checker, fuzz=0.02))]
     objs.append(w.translate(w.matinst(w.sphere((0, 0, 0), 1.0, None), w.metal((1, 1, 1), 0.0, bump=scratches, strength=1.0)), (0, 1, 0)))
@@ -529,6 +552,38 @@ def quirks(seed: int = 5, width: int = 640, height: int = 360, spp: int = 64, ma
         env_mode=env, background=(0.6, 0.7, 0.9), env_intensity=1.0, sun_direction=(0.6, 0.45, 0.5),
         sun_color=(1.0, 0.95, 0.85), sun_intensity=1.0, sun_size=1.0)
     return w.text(), cfg, {}
+
+
+def shipped_models(seed: int = 6, width: int = 640, height: int = 360, spp: int = 64, max_depth: int = 50):
+    """The reference's five shipped OBJ models (assets/models/, loaded with the scales of sceneAssetsLoader,
+    scene_management.hpp:36-43: torus 0.4, bowl 0.02, cylinder / pyramid / torus_knot 0.4) on a ground sphere, each under
+    the wrapper chains the demo scene uses (material_instance, rotate_x / rotate_y, translate).  cylinder.obj carries
+    quads and n-gons (TinyObj fan triangulation), bowl.obj coincident faces, pyramid.obj no normals (flat shading)."""
+    rng = random.Random(seed)
+    w = SceneWriter()
+    names = ("torus", "bowl", "cylinder", "pyramid", "torus_knot")
+    files = {f"assets/models/{n}.obj": shipped_asset(f"models/{n}.obj") for n in names}
+    scales = {"torus": 0.4, "bowl": 0.02, "cylinder": 0.4, "pyramid": 0.4, "torus_knot": 0.4}
+    models = {n: w.model(f"assets/models/{n}.obj", None, scales[n]) for n in names}
+    mats = [w.lambertian((0.8, 0.1, 0.1)), w.metal((1.0, 0.8, 0.4), 0.0), w.dielectric(1.5), w.metal((0.89, 0.58, 0.51), 0.2),
+            w.lambertian((0.1, 0.4, 0.9)), w.light((0.0, 2.0, 4.0))]
+    objs = [w.sphere((0, -1000, 0), 1000.0, w.lambertian((0.5, 0.5, 0.5)))]
+    k = 0
+    for row, z in enumerate((-2.2, 0.0, 2.2)):
+        for col, n in enumerate(names):
+            o = w.matinst(models[n], mats[k % len(mats)])
+            if row == 1:
+                o = w.rotate("y", o, rng.random() * 3.0)               # radians (Appendix A q3)
+            elif row == 2:
+                o = w.rotate("y", w.rotate("x", o, -30.0 + 60.0 * rng.random()), rng.random() * 3.0)  # degrees, then radians
+            objs.append(w.translate(o, (-4.4 + 2.2 * col + 0.3 * rng.random(), 0.0 if row < 2 else 0.6, z)))
+            k += 1
+    w.world(w.container("bvh", objs, name="world"))
+    cfg = RenderConfig(
+        image_width=width, image_height=height, samples_per_pixel=spp, max_depth=max_depth, vfov=34.0,
+        lookfrom=(1.0, 6.5, 10.5), lookat=(0.0, 0.4, 0.0), vup=(0.0, 1.0, 0.0), defocus_angle=0.0, focus_dist=10.0,
+        env_mode="solid", background=(0.7, 0.8, 1.0), env_intensity=1.0)
+    return w.text(), cfg, files
 
 
 def wire_demo(seed: int = 7, width: int = 240, height: int = 135, spp: int = 64, max_depth: int = 50):

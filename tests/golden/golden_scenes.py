@@ -7,10 +7,19 @@ EXACTLY on the shared diagonals / corner edges of the wall quads, where the refe
 tests leave cracks (both triangles reject) — exact ties, not errors, but they would dominate the count.
 The exterior fixture uses a sun of radiance 60 instead of the config's 5e4: without light sampling (the
 reference has none) a 1-degree 5e4 sun puts 9 % fireflies noise on a 4096-spp reference, which would hide any
-bias; the estimator is the same."""
+bias; the estimator is the same.
+Round 2 adds the BASELINE configs at their STATED sizes (ids / probe fixtures only; stats size None): "mesh_full" = C3
+(999 698-triangle heightfield + 12 instances of the reference's shipped torus_knot.obj), "big" = C5's geometry (C1 spheres
++ 10 000 712-triangle heightfield), "exterior_shipped" = C4 on the reference's own JPEG bump maps / wood texture, and
+"models" = the five shipped OBJ files."""
 GOLDEN_SCENES = {
     "cornell": ("cornell", dict(seed=2), (641, 360), (200, 112), dict(fog=False)),
     "mesh": ("mesh", dict(seed=3, grid=120, knots=8), (640, 360), (200, 112), {}),
     "exterior": ("exterior", dict(seed=4, small=120, hdr_size=512, sun_radiance=60.0), (640, 360), (200, 112), {}),
     "quirks": ("quirks", dict(seed=5), (640, 360), (200, 112), {}),
+    "mesh_full": ("mesh", dict(seed=3, grid=708, knots=12, shipped=True), (640, 360), None, {}),
+    "exterior_shipped": ("exterior", dict(seed=4, small=200, hdr_size=1024, sun_radiance=60.0, shipped=True), (640, 360), (200, 112), {}),
+    "models": ("shipped_models", dict(seed=6), (640, 360), None, {}),
+    "big": ("big", dict(seed=5, grid=2237), (480, 270), None, {}),
 }
+STATS_BATCHES = 64  # x 256 spp = 16 384 reference samples per pixel: noise ~0.2 %, so the plain 1 % rRMSE gate holds

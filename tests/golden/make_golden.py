@@ -272,7 +272,7 @@ def weekend_stats():
 
 # Reduced-size instances of configs C2-C4 and the quirk scene: same generators as the bench, sized so the
 # reference finishes 4096 spp in minutes on 8 cores.  GOLDEN_SCENES is shared with tests/test_gpu_parity.py.
-from tests.golden.golden_scenes import GOLDEN_SCENES  # noqa: E402
+from tests.golden.golden_scenes import GOLDEN_SCENES, STATS_BATCHES  # noqa: E402
 
 
 def scene_targets():
@@ -284,11 +284,13 @@ def scene_targets():
 
         def stats(name=name, gen=gen, kw=kw, wh=stats_wh):
             txt, cfg, files = getattr(scenes, gen)(width=wh[0], height=wh[1], spp=256, **kw)
-            make_stats(f"{name}_{wh[0]}x{wh[1]}", txt, cfg, 16, files)
+            make_stats(f"{name}_{wh[0]}x{wh[1]}", txt, cfg, STATS_BATCHES, files)
         def probe(name=name, gen=gen, kw={**kw, **ids_kw}, wh=ids_wh):
             txt, cfg, files = getattr(scenes, gen)(width=wh[0], height=wh[1], spp=1, **kw)
             make_probe(name, txt, cfg, files)
-        t[f"{name}_ids"], t[f"{name}_stats"], t[f"{name}_probe"] = ids, stats, probe
+        t[f"{name}_ids"], t[f"{name}_probe"] = ids, probe
+        if stats_wh:
+            t[f"{name}_stats"] = stats
     return t
 
 

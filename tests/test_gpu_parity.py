@@ -518,22 +518,25 @@ def test_checkpoint_resume_and_scene_file_reproduce_the_frame(gpu_ctx, tmp_path)
 
 @pytest.mark.parametrize("name", ["weekend"] + list(GOLDEN_SCENES))
 def test_wavefront_render_equals_megakernel(name, gpu_ctx, tmp_path, weekend_scene, monkeypatch):
-    """The wavefront kernels (wavefront.cu, ZB_WAVEFRONT=1) draw the same random numbers and run the same shading
+    """(experiments build only) The wavefront kernels (wavefront.cu, tuning key "wavefront") draw the same random numbers and run the same shading
     code as k_render, and both sum paths in 64-bit fixed point: per-path radiance may differ only by the
     compiler's contraction choices, so the frames agree to fp32 rounding."""
+    if not api.has_experiments():
+        pytest.skip("library built without -DZB_EXPERIMENTS (the wavefront form is a rejected experiment)")
     if name == "weekend":
         sc, cfg = weekend_scene, scenes.weekend(seed=1, width=203, height=90, spp=24)[1]  # 203: ragged tile edge
     else:
         _, _, _, wh, _ = GOLDEN_SCENES[name]
         sc, cfg, _ = _load_scene(gpu_ctx, tmp_path, name, wh, 24)
-    monkeypatch.delenv("ZB_WAVEFRONT", raising=False)
+    gpu_ctx.set_tuning("wavefront", 0)
     a = sc.render(cfg, seed=5)["beauty"]
-    monkeypatch.setenv("ZB_WAVEFRONT", "1")
-    monkeypatch.setenv("ZB_WF_SLOTS", "4096")  # far fewer slots than paths: regeneration and many iterations
+    gpu_ctx.set_tuning("wavefront", 1)
+    gpu_ctx.set_tuning("wf_slots", 4096)  # far fewer slots than paths: regeneration and many iterations
     b = sc.render(cfg, seed=5)["beauty"]
     c = sc.render(cfg, seed=5)["beauty"]
-    monkeypatch.setenv("ZB_WF_SLOTS", "0")
+    gpu_ctx.set_tuning("wf_slots", 0)
     d = sc.render(cfg, seed=5)["beauty"]
+    gpu_ctx.set_tuning("wavefront", 0)
     if name != "weekend":
         sc.close()
     assert np.array_equal(b, c) and np.array_equal(b, d), "wavefront frame depends on scheduling"
@@ -545,25 +548,26 @@ def test_wavefront_render_equals_megakernel(name, gpu_ctx, tmp_path, weekend_sce
     assert abs(a.mean() - b.mean()) < 1e-3 * a.mean()
 
 
-def test_lean_instantiation_equals_general_queue_kernel(weekend_scene, monkeypatch):
+def test_lean_instantiation_equals_general_queue_kernel(weekend_scene, gpu_ctx):
     """Plain scenes (every item an inline sphere, untextured materials, solid-colour environment) run the LEAN
     instantiation of k_render_pq; ZB_NO_LEAN=1 forces the general one.  Same arithmetic on the paths a plain scene
     takes, so the frames are equal bit for bit, for every resident-blocks variant."""
     cfg = scenes.weekend(seed=1, width=203, height=90, spp=24)[1]
-    monkeypatch.setenv("ZB_NO_LEAN", "1")
+    gpu_ctx.set_tuning("no_lean", 1)
     a = weekend_scene.render(cfg, seed=9)["beauty"]
-    monkeypatch.delenv("ZB_NO_LEAN")
+    gpu_ctx.set_tuning("no_lean", 0)
     b = weekend_scene.render(cfg, seed=9)["beauty"]
     assert np.array_equal(a, b)
-    for blocks in ("6", "7"):
-        monkeypatch.setenv("ZB_PQ_BLOCKS", blocks)
+    for blocks in (6, 7):
+        gpu_ctx.set_tuning("pq_blocks", blocks)
         assert np.array_equal(a, weekend_scene.render(cfg, seed=9)["beauty"]), blocks
-    monkeypatch.delenv("ZB_PQ_BLOCKS")
-    # resumable traversal (k_render_pqr, an opt-in experiment): other scheduling of the same paths
-    for thresh in ("8", "24"):
-        monkeypatch.setenv("ZB_PQ_RESUME", thresh)
-        assert np.array_equal(a, weekend_scene.render(cfg, seed=9)["beauty"]), thresh
-    monkeypatch.delenv("ZB_PQ_RESUME")
+    gpu_ctx.set_tuning("pq_blocks", 0)
+    if api.has_experiments():
+        # resumable traversal (k_render_pqr, a rejected experiment): other scheduling of the same paths
+        for thresh in (8, 24):
+            gpu_ctx.set_tuning("pq_resume", thresh)
+            assert np.array_equal(a, weekend_scene.render(cfg, seed=9)["beauty"]), thresh
+        gpu_ctx.set_tuning("pq_resume", 0)
     # the same spheres under the procedural sky: the "spheres + textures / environment" set against the general kernel
     import copy
     sky = copy.copy(cfg)
@@ -571,8 +575,9 @@ def test_lean_instantiation_equals_general_queue_kernel(weekend_scene, monkeypat
     full = copy.copy(sky)
     full.use_albedo = full.use_normal = full.use_z_depth = full.use_reflection = full.use_refraction = True
     b = weekend_scene.render(full, seed=9)
-    monkeypatch.setenv("ZB_NO_LEAN", "1")
+    gpu_ctx.set_tuning("no_lean", 1)
     a = weekend_scene.render(full, seed=9)
+    gpu_ctx.set_tuning("no_lean", 0)
     for key in ("beauty", "albedo", "normal", "z_depth", "reflection", "refraction"):
         assert np.array_equal(a[key], b[key]), key
     assert not np.array_equal(a["beauty"], weekend_scene.render(cfg, seed=9)["beauty"])  # the sky is not the solid colour
@@ -711,11 +716,11 @@ def test_path_queue_kernel_equals_tile_kernel(name, gpu_ctx, tmp_path, weekend_s
     import copy
     full = copy.copy(cfg)  # AOV and light-pass modes of the queue kernel
     full.use_albedo = full.use_normal = full.use_z_depth = full.use_reflection = full.use_refraction = True
-    monkeypatch.setenv("ZB_PQ", "0")
+    gpu_ctx.set_tuning("pq", 0)
     a = sc.render(cfg, seed=5)["beauty"]
     a_tiles = [sc.render(cfg, seed=5, tile=(r, 3))["beauty"] for r in range(3)]
     a_full = sc.render(full, seed=5)
-    monkeypatch.delenv("ZB_PQ")
+    gpu_ctx.set_tuning("pq", 1)
     b = sc.render(cfg, seed=5)["beauty"]
     b_tiles = [sc.render(cfg, seed=5, tile=(r, 3))["beauty"] for r in range(3)]
     c = sc.render(cfg, seed=5, samples_per_launch=5)["beauty"]
@@ -726,9 +731,10 @@ def test_path_queue_kernel_equals_tile_kernel(name, gpu_ctx, tmp_path, weekend_s
         assert np.array_equal(a_full[key], d_full[key]), key
         assert np.allclose(d_full[key], d_full_batched[key], rtol=2e-6, atol=1e-7), key
         assert np.array_equal(d_tiles[0][key] + d_tiles[1][key], d_full[key]), key
-    monkeypatch.setenv("ZB_PQ", "2")  # the queue kernel's AOV and light-pass modes (not the default: slower, see abi_render.cu)
+    gpu_ctx.set_tuning("pq", 2)  # the queue kernel's AOV and light-pass modes (not the default: slower, see abi_render.cu)
     b_full = sc.render(full, seed=5)
     b_full_batched = sc.render(full, seed=5, samples_per_launch=7)
+    gpu_ctx.set_tuning("pq", 1)
     for key in ("beauty", "albedo", "normal", "z_depth", "reflection", "refraction"):
         assert np.array_equal(a_full[key], b_full[key]), key
         assert np.allclose(b_full[key], b_full_batched[key], rtol=2e-6, atol=1e-7), key
