@@ -23,3 +23,11 @@ GOLDEN_SCENES = {
     "big": ("big", dict(seed=5, grid=2237), (480, 270), None, {}),
 }
 STATS_BATCHES = 64  # x 256 spp = 16 384 reference samples per pixel: noise ~0.2 %, so the plain 1 % rRMSE gate holds
+
+# Quirk q13 (found in round 2): rotate_y builds its bounding box with the WORLD->LOCAL rotation (rotate_y.hpp:26-27 use
+# the formulas of :47-48) although hit() maps local->world with the opposite sign (:63-64), so the box of anything under
+# rotate_y is the inner box turned by -theta.  Geometry outside that box is found or missed by the reference depending on
+# the boxes of its random tree's ancestors (bvh.hpp:17); the product bounds instances with the true box and always finds
+# it.  Leaves under rotate_y over a non-symmetric mesh: a pixel where the product hits such a leaf NEARER than the
+# reference's answer is this quirk, not a tie, and is left out of the agreement count (44 of 230 400 pixels in "models").
+Q13_LEAVES = {"models": set(range(6, 16))}

