@@ -14,6 +14,23 @@
 
 #include "math.hpp"
 
+// The reference's own decoder (third-party, public domain; host/third_party/README.md): static copy per translation unit,
+// so header-only users (tests/cpp, oracle/zoracle.cpp) need no extra object file.
+#if defined(__GNUC__)
+#pragma GCC diagnostic push
+#pragma GCC diagnostic ignored "-Wunused-function"
+#pragma GCC diagnostic ignored "-Wunused-but-set-variable"
+#pragma GCC diagnostic ignored "-Wsign-compare"
+#endif
+#ifndef STBI_INCLUDE_STB_IMAGE_H
+#define STB_IMAGE_STATIC
+#define STB_IMAGE_IMPLEMENTATION
+#include "../third_party/stb_image.h"
+#endif
+#if defined(__GNUC__)
+#pragma GCC diagnostic pop
+#endif
+
 namespace zenith {
 
 class texture {
@@ -42,12 +59,11 @@ public:
     shared_ptr<texture> odd, even;
 };
 
-// image_texture(filename, is_hdr) texture.hpp:14-43.  The reference decodes JPG/PNG/HDR with the
-// stb_image it vendors; this host decodes Radiance .hdr itself and reads everything else from a
-// ".zbtex" raw dump ("ZBTX" u32 width u32 height u32 is_float, then RGB8 or RGB32F rows, top row
-// first) so both sides see identical bytes (the oracle harness writes the dumps with the reference's
-// own decoder; raytracer_project_b200/ztex.py writes them from numpy arrays).
-// A file that cannot be read gives the reference's "missing" texture (cyan, texture.hpp:52-54).
+// image_texture(filename, is_hdr) texture.hpp:14-43.  Decoded like the reference does, with the stb_image it vendors:
+// stbi_loadf(.., 3) when is_hdr, else stbi_load(.., 3) (texture.hpp:23, :31) — JPEG (baseline and progressive), PNG, HDR
+// and the rest of stb's formats, texel for texel.  A ".zbtex" raw dump ("ZBTX" u32 width u32 height u32 is_float, then
+// RGB8 or RGB32F rows, top row first) is read when the file itself is one, or as a side-car "NAME.zbtex" cache when NAME
+// cannot be decoded.  A file that cannot be read gives the reference's "missing" texture (cyan, texture.hpp:52-54).
 class image_texture : public texture {
 public:
     image_texture(const char* filename, bool is_hdr = false) : is_float(is_hdr) { load(filename); }
@@ -61,14 +77,29 @@ public:
     std::vector<float> f32;
 
 private:
-    // "NAME.zbtex" beside the image wins (same texels as the oracle's decoder); a file that is itself a
-    // ZBTX dump is read directly; Radiance .hdr files are decoded natively (RGBE, flat or RLE scanlines,
-    // value = mantissa * 2^(E-136) as stb_image does); anything else is "missing".
     void load(const char* filename) {
         std::string path(filename);
-        if (read_zbtex(path + ".zbtex") || read_zbtex(path) || read_radiance_hdr(path)) return;
-        std::cerr << "ERROR: Could not load texture (need a .zbtex dump or a Radiance .hdr): " << filename << "\n";
+        if (read_zbtex(path) || read_stb(path) || read_zbtex(path + ".zbtex") || read_radiance_hdr(path)) return;
+        std::cerr << (is_float ? "ERROR: Could not load HDR: " : "ERROR: Could not load texture: ") << filename << "\n";  // texture.hpp:25, :34
         width = height = 0;
+    }
+
+    bool read_stb(const std::string& path) {
+        int w = 0, h = 0, comp = 3;
+        if (is_float) {
+            float* d = stbi_loadf(path.c_str(), &w, &h, &comp, 3);
+            if (!d) return false;
+            f32.assign(d, d + size_t(w) * h * 3);
+            stbi_image_free(d);
+        } else {
+            unsigned char* d = stbi_load(path.c_str(), &w, &h, &comp, 3);
+            if (!d) return false;
+            u8.assign(d, d + size_t(w) * h * 3);
+            stbi_image_free(d);
+        }
+        width = w;
+        height = h;
+        return true;
     }
 
     bool read_zbtex(const std::string& path) {

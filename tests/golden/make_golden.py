@@ -248,6 +248,30 @@ def make_probe(name, scene_text, cfg, files=None, n=6000, seed=99):
     print(name, "probe", info, "hit fraction", float(np.isfinite(rec[:, 0]).mean()))
 
 
+SHIPPED_IMAGES = ["bump_maps/concrete_bump_map.jpg", "bump_maps/scratches_bump_map.jpg", "bump_maps/water_bump_map.jpg",
+                  "bump_maps/wood_bump_map.jpg", "textures/fine-wood.jpg", "textures/wood_box.png"]
+
+
+def texels():
+    """stb_image decode of every shipped texture by the reference harness (texture.hpp:31): size, sha256 and a few probe
+    texels of the RGB8 buffer, so the host's decode can be checked texel for texel without the harness."""
+    import hashlib
+    d = scratch_dir()
+    out = {}
+    for rel in SHIPPED_IMAGES:
+        src = os.path.join(GOLDEN, "assets", rel)
+        dump = os.path.join(d, "t.zbtex")
+        info = run_harness(["decode", src, dump, "0"], d)
+        raw = open(dump, "rb").read()
+        w, h, is_float = np.frombuffer(raw[4:16], np.uint32)
+        px = np.frombuffer(raw[16:], np.uint8).reshape(int(h), int(w), 3)
+        out[rel] = {"width": int(w), "height": int(h), "sha256": hashlib.sha256(px.tobytes()).hexdigest(),
+                    "probe": px[::max(int(h) // 7, 1), ::max(int(w) // 5, 1)].reshape(-1, 3)[:24].tolist()}
+        print("texels", rel, info, out[rel]["sha256"][:12])
+    with open(os.path.join(GOLDEN, "shipped_texels.json"), "w") as f:
+        json.dump(out, f, indent=1)
+
+
 def quirks_aov():
     txt, cfg, files = scenes.quirks(seed=5, width=320, height=180, spp=512)
     cfg.z_depth_max_dist = 15.0
@@ -294,7 +318,7 @@ def scene_targets():
     return t
 
 
-TARGETS = {"finish": finish, "export": export, "wire": wire, "quirks_aov": quirks_aov, "quirks_light": quirks_light, "weekend_ids": weekend_ids, "weekend_probe": weekend_probe, "weekend_stats": weekend_stats, **scene_targets()}
+TARGETS = {"texels": texels, "finish": finish, "export": export, "wire": wire, "quirks_aov": quirks_aov, "quirks_light": quirks_light, "weekend_ids": weekend_ids, "weekend_probe": weekend_probe, "weekend_stats": weekend_stats, **scene_targets()}
 
 if __name__ == "__main__":
     names = sys.argv[1:] or list(TARGETS)

@@ -240,3 +240,25 @@ def test_png_and_hdr_writers_round_trip(tmp_path):
     assert [api.pass_file_name(i) for i in (0, 2, 6)] == ["render_RGB.png", "render_Albedo.png", "render_Z-Depth.png"]
     with pytest.raises(_lib.ZbError):
         api.write_png(str(tmp_path / "missing_dir" / "x.png"), rgb)
+
+
+def test_image_texture_decodes_shipped_jpeg_png_like_the_reference(tmp_path):
+    """image_texture("x.jpg") with no side-car file: the host decodes the reference's shipped textures (baseline and
+    progressive JPEG, 4:2:0 and 4:4:4, PNG) to exactly the texels the reference's stbi_load produced
+    (tests/golden/shipped_texels.json, made by oracle/_ref/ref_harness decode; texture.hpp:31)."""
+    import hashlib
+    import json
+    gold = json.load(open(os.path.join(os.path.dirname(__file__), "golden", "shipped_texels.json")))
+    for rel, g in gold.items():
+        src = os.path.join(scenes.ASSET_DIR, rel)
+        txt = f"tex t image {src} 0\nmat m lambertian tex t\nobj s sphere 0 0 0 1 m\nobj w bvh s\nworld w\n"
+        flat = api.flatten_zscene(txt)
+        f = flat.contents
+        tex = np.ctypeslib.as_array(C.cast(f.textures, C.POINTER(C.c_uint32)), (f.n_textures, 8))
+        img = [t for t in tex if t[0] == 2]
+        assert len(img) == 1, (rel, tex[:, 0])
+        w, h, first = int(img[0][1]), int(img[0][2]), int(img[0][3])
+        assert (w, h) == (g["width"], g["height"]), rel
+        px = np.ctypeslib.as_array(C.cast(f.texels_u8, C.POINTER(C.c_uint8)), (f.n_texels_u8, 4))[first:first + w * h, :3].copy()
+        api.free_flat(flat)
+        assert hashlib.sha256(px.tobytes()).hexdigest() == g["sha256"], rel

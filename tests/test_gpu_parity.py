@@ -44,7 +44,7 @@ def test_weekend_primary_ids_match_reference(weekend_scene):
     assert np.quantile(rel, 0.999) < 2e-4, np.quantile(rel, 0.999)
     assert rel.max() < 5e-3, rel.max()
     # every mismatch sits on a silhouette: one of its 8 neighbours in the reference image has the GPU's id
-    ys, xs = np.nonzero(~same & ~q13)
+    ys, xs = np.nonzero(~same)
     g = np.pad(gold["leaf"], 1, mode="edge")
     for y, x in zip(ys, xs):
         assert leaf[y, x] in g[y:y + 3, x:x + 3], (y, x)
@@ -159,7 +159,10 @@ def test_scene_primary_ids_match_reference(name, gpu_ctx, tmp_path):
     # triangle.hpp:62) where either neighbour is a legitimate answer
     face_same = (prim == gold["tri"])[hit]
     print(f"{name}: face-id agreement {face_same.mean() * 100:.4f} %")
-    assert face_same.mean() >= 0.999
+    # the shipped bowl.obj carries coincident (duplicated) faces: another face at the SAME t is a tie, not a miss
+    tie = face_same | (rel < 1e-5)
+    print(f"{name}: face-id agreement counting equal-t ties {tie.mean() * 100:.4f} %")
+    assert tie.mean() >= 0.999 and face_same.mean() >= (0.995 if name == "models" else 0.999)
     ys, xs = np.nonzero(~same & ~q13)
     g = np.pad(gold["leaf"], 1, mode="edge")
     for y, x in zip(ys, xs):
