@@ -276,6 +276,18 @@ int zb_render(zb_context* ctx, const zb_scene* scene, const zb_camera* cam, cons
 int zb_render_device(zb_context* ctx, const zb_scene* scene, const zb_camera* cam,
                      const zb_environment* env, const zb_render_opts* opts, void* accum_f4,
                      void* accum_aux_f4);
+/* zb_render_device's beauty pass WITHOUT any device allocation.  No counterpart in the reference: added
+ * for callers that cannot call cudaMalloc (CUDA graph capture, tight serving loops, harnesses that
+ * forbid it).  The kernel's scratch (64-bit fixed-point per-pixel sums + queue head) lives in a static __device__ array
+ * sized for ZB_NOALLOC_MAX_PIXELS pixels (24 MiB, held by every GPU that loads the library until exit); larger frames are
+ * rejected with ZB_ERR_INVALID.  Beauty only (no aux planes, light_pass, collect_stats); sample ranges, tile stripes and
+ * `accumulate` work as in zb_render_device and the sums written to accum_f4 are bit-identical to its.  Asynchronous on the
+ * context stream.  All calls on one GPU share the array: each call clears what it uses first, and calls that OVERLAP on
+ * the GPU (other streams / contexts) race. */
+#define ZB_NOALLOC_MAX_PIXELS (1u << 20)
+int zb_render_device_noalloc(zb_context* ctx, const zb_scene* scene, const zb_camera* cam, const zb_environment* env,
+                             const zb_render_opts* opts, void* accum_f4);
+size_t zb_noalloc_max_pixels(void);
 /* K5 resolve: out_f4[i] = accum_f4[i] * scale (device -> device), or to the reference's double RGB */
 int zb_resolve_device(zb_context* ctx, const void* accum_f4, size_t n_pixels, double scale, void* out_f4,
                       void* out_rgb_f64);

@@ -124,6 +124,9 @@ SYMBOLS = {
     "zb_read_frame": (C.c_int, [C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p]),
     "zb_render_device": (C.c_int, [C.c_void_p, C.c_void_p, C.POINTER(Camera), C.POINTER(Environment),
                                    C.POINTER(RenderOpts), C.c_void_p, C.c_void_p]),
+    "zb_render_device_noalloc": (C.c_int, [C.c_void_p, C.c_void_p, C.POINTER(Camera), C.POINTER(Environment),
+                                           C.POINTER(RenderOpts), C.c_void_p]),
+    "zb_noalloc_max_pixels": (C.c_size_t, []),
     "zb_resolve_device": (C.c_int, [C.c_void_p, C.c_void_p, C.c_size_t, C.c_double, C.c_void_p, C.c_void_p]),
     "zb_primary_ids": (C.c_int, [C.c_void_p, C.c_void_p, C.POINTER(Camera), C.c_void_p, C.c_void_p, C.c_void_p]),
     "zb_get_stats": (C.c_int, [C.c_void_p, C.POINTER(Stats)]),

@@ -340,6 +340,14 @@ class Scene:
         check(self.ctx.lib.zb_render_device(self.ctx.h, self.h, C.byref(cam), C.byref(env), C.byref(o),
                                             C.c_void_p(accum_ptr), C.c_void_p(aux_ptr) if aux_ptr else None))
 
+    def render_device_noalloc(self, cfg: RenderConfig, accum_ptr: int, seed=1, sample_range=None, tile=None, accumulate=False):
+        """zb_render_device_noalloc: the beauty pass of render_device with its scratch in a static device array (no
+        device allocation; frames of at most zb_noalloc_max_pixels() pixels)."""
+        cam, env = camera_struct(cfg), env_struct(cfg)
+        o = opts_struct(cfg, seed, sample_range, tile, False, 0)
+        o.accumulate = int(accumulate)
+        check(self.ctx.lib.zb_render_device_noalloc(self.ctx.h, self.h, C.byref(cam), C.byref(env), C.byref(o), C.c_void_p(accum_ptr)))
+
     def render_bvh_debug_device(self, cfg: RenderConfig, accum_ptr: int, level=-1, thickness=0.01, seed=1, sample_range=None):
         """zb_render_bvh_debug_device: the reference's BVH debug view (bvh.hpp:56-110), sums into a device float4 buffer."""
         cam, env = camera_struct(cfg), env_struct(cfg)

@@ -61,3 +61,8 @@ struct zb_scene {
     size_t bytes = 0;
 };
 
+
+// abi_render.cu helpers shared with the other translation units
+int zbr_fill_params(zb_context* ctx, const zb_scene* scene, const zb_camera* cam, const zb_environment* env,
+                    const zb_render_opts* o, RenderParams& P);
+int zbr_owned_tiles(const RenderParams& P);

@@ -376,6 +376,13 @@ int check_overflow(zb_context* ctx, const char* who) {
 
 }  // namespace
 
+// exported to the other translation units of the library (noalloc.cu)
+int zbr_fill_params(zb_context* ctx, const zb_scene* scene, const zb_camera* cam, const zb_environment* env,
+                    const zb_render_opts* o, RenderParams& P) {
+    return fill_params(ctx, scene, cam, env, o, P);
+}
+int zbr_owned_tiles(const RenderParams& P) { return owned_tiles(P); }
+
 extern "C" int zb_render_device(zb_context* ctx, const zb_scene* scene, const zb_camera* cam,
                                 const zb_environment* env, const zb_render_opts* opts, void* accum_f4,
                                 void* accum_aux_f4) {
