@@ -14,7 +14,7 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 
 def test_header_symbols_all_exported(lib):
     hdr = open(os.path.join(ROOT, "include", "zenith_b200.h")).read()
-    declared = set(re.findall(r"^(?:int|double|const char\*)\s+(zb_\w+)\s*\(", hdr, flags=re.M))
+    declared = set(re.findall(r"^(?:int|double|size_t|const char\*)\s+(zb_\w+)\s*\(", hdr, flags=re.M))
     assert declared, "no declarations parsed"
     assert declared == set(_lib.SYMBOLS), declared ^ set(_lib.SYMBOLS)
     for name in declared:
