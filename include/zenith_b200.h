@@ -194,14 +194,17 @@ typedef struct zb_environment {
     double sun_intensity, sun_size;
 } zb_environment;
 
-enum { ZB_PARTITION_SAMPLES = 0, ZB_PARTITION_TILES = 1 };
+/* how a multi-GPU context splits a frame: AUTO = sample slices when every GPU gets >= 8 samples per pixel,
+ * else tile stripes; both give the same bits (integer sums) */
+enum { ZB_PARTITION_AUTO = 0, ZB_PARTITION_SAMPLES = 1, ZB_PARTITION_TILES = 2 };
 /* camera.hpp:28-31, :53-57 and post_processor::z_depth_max_dist (camera.hpp:247). */
 typedef struct zb_render_opts {
     int32_t samples_per_pixel;
     int32_t max_depth;
     uint64_t seed;
     /* this rank's share of the frame (multi-GPU) */
-    int32_t sample_begin, sample_end; /* [begin,end) of the global sample index; 0,spp = all  */
+    int32_t sample_begin, sample_end; /* [begin,end) of the global sample index; (0,spp) or a zeroed (0,0) = all; an EMPTY
+                                         share is written as begin == end > 0 (e.g. spp,spp), never as (0,0)            */
     int32_t tile_rank, tile_ranks;    /* tile stripes: this rank owns tiles t % ranks == rank  */
     int32_t use_albedo, use_normal, use_z_depth;
     double z_depth_max_dist;
@@ -215,6 +218,8 @@ typedef struct zb_render_opts {
     int32_t light_pass;
     int32_t accumulate;               /* zb_render_device: 1 = add this call's samples to the sums already in accum_f4
                                          (progressive rendering, resume from a checkpoint) instead of overwriting */
+    int32_t partition;                /* multi-GPU contexts: ZB_PARTITION_*; ignored on one GPU                          */
+    int32_t reserved;
 } zb_render_opts;
 
 /* Host-side outputs in the reference's own layout: row-major, top row first, 3 doubles per pixel
@@ -237,6 +242,9 @@ typedef struct zb_stats {
     uint32_t launches; /* kernels launched by the last render                           */
     uint32_t stack_overflows; /* traversal-stack overflow events of the last render (saturating): must be 0; zb_render
                                  returns ZB_ERR_UNSUPPORTED otherwise                                                 */
+    uint32_t kernel_pick;     /* k_render_pq instantiation of the last render: (blocks per SM << 16) | (mode << 8) | ZB_F_* set;
+                                 ties measured instruction counts (profiles/) to the code that ran                  */
+    uint32_t n_gpus;          /* GPUs that rendered the last frame                                                   */
 } zb_stats;
 
 typedef struct zb_context zb_context;
@@ -248,6 +256,27 @@ const char* zb_last_error(void);
 
 /* one context per process/GPU; `stream` is a cudaStream_t (or NULL for the default stream) */
 int zb_context_create(int device, zb_context** out);
+/* ---- multi-GPU.  In the reference ALL parallelism lives inside the one blocking camera::render call
+ * (thread fan-out camera.hpp:426-427, static row split :557-566, joins :569-573); so it does here.
+ * zb_context_create_multi: one process drives n GPUs of one node (peer access enabled between all pairs).  The returned
+ * context is used like any other: zb_scene_upload replicates the scene on every GPU, zb_render partitions the frame
+ * (zb_render_opts::partition), every GPU gathers + resolves its own band of rows from all GPUs' 64-bit integer sums over
+ * NVLink and copies that band home over its own PCIe link.  The frame is bit-identical to the one-GPU frame.
+ * zb_primary_ids, zb_probe_rays, the *_device entry points and the finishing chain run on the first device.  A device
+ * may be listed more than once (its ranks then share that GPU): of no use in production, it lets the whole path run
+ * where a single GPU is present. */
+int zb_context_create_multi(const int* device_ids, int n_devices, zb_context** out);
+int zb_context_device_count(zb_context* ctx);
+/* One process per GPU (torchrun / MPI launchers): every rank creates a plain context, exports a handle (CUDA IPC handles of
+ * its sum buffers and its render-done event, sized for frames of up to max_pixels), the caller's own transport gathers the
+ * n handles, and every rank joins with the same array and the same shared-memory name (a POSIX shm object holding the
+ * host barrier, e.g. "/zb_<job id>").  From then on zb_render on these contexts is COLLECTIVE: all ranks call it with the
+ * same arguments; each writes its band of rows into its `out` buffers — which may be one buffer in shared memory mapped by
+ * all ranks, so that the whole frame lands in one place without a gather on the host.  cancel / progress are ignored. */
+typedef struct zb_group_handle { unsigned char opaque[256]; } zb_group_handle;
+int zb_group_export(zb_context* ctx, size_t max_pixels, zb_group_handle* out);
+int zb_group_join(zb_context* ctx, int rank, int n_ranks, const zb_group_handle* all, const char* shm_name);
+int zb_group_leave(zb_context* ctx);
 int zb_context_set_stream(zb_context* ctx, void* stream);
 int zb_context_destroy(zb_context* ctx);
 /* A/B switches for measurements and equality tests; product defaults need none of them.  Read once from the environment at

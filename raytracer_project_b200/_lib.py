@@ -73,7 +73,11 @@ class RenderOpts(C.Structure):
                 ("tile_ranks", C.c_int32), ("use_albedo", C.c_int32), ("use_normal", C.c_int32),
                 ("use_z_depth", C.c_int32), ("z_depth_max_dist", C.c_double), ("collect_stats", C.c_int32),
                 ("samples_per_launch", C.c_int32), ("use_reflection", C.c_int32), ("use_refraction", C.c_int32),
-                ("light_pass", C.c_int32), ("accumulate", C.c_int32)]
+                ("light_pass", C.c_int32), ("accumulate", C.c_int32), ("partition", C.c_int32), ("reserved", C.c_int32)]
+
+
+class GroupHandle(C.Structure):
+    _fields_ = [("opaque", C.c_ubyte * 256)]
 
 
 class Outputs(C.Structure):
@@ -85,7 +89,7 @@ class Stats(C.Structure):
     _fields_ = [("paths", C.c_uint64), ("rays", C.c_uint64), ("node_visits", C.c_uint64), ("box_tests", C.c_uint64),
                 ("prim_tests", C.c_uint64), ("instance_visits", C.c_uint64), ("kernel_ms", C.c_double),
                 ("resolve_ms", C.c_double), ("h2d_ms", C.c_double), ("d2h_ms", C.c_double), ("launches", C.c_uint32),
-                ("stack_overflows", C.c_uint32)]
+                ("stack_overflows", C.c_uint32), ("kernel_pick", C.c_uint32), ("n_gpus", C.c_uint32)]
 
 
 PROGRESS_FN = C.CFUNCTYPE(None, C.c_int, C.c_void_p)
@@ -111,6 +115,11 @@ SYMBOLS = {
     "zb_abi_version": (C.c_int, []),
     "zb_last_error": (C.c_char_p, []),
     "zb_context_create": (C.c_int, [C.c_int, C.POINTER(C.c_void_p)]),
+    "zb_context_create_multi": (C.c_int, [C.POINTER(C.c_int), C.c_int, C.POINTER(C.c_void_p)]),
+    "zb_context_device_count": (C.c_int, [C.c_void_p]),
+    "zb_group_export": (C.c_int, [C.c_void_p, C.c_size_t, C.POINTER(GroupHandle)]),
+    "zb_group_join": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.POINTER(GroupHandle), C.c_char_p]),
+    "zb_group_leave": (C.c_int, [C.c_void_p]),
     "zb_context_set_stream": (C.c_int, [C.c_void_p, C.c_void_p]),
     "zb_context_destroy": (C.c_int, [C.c_void_p]),
     "zb_context_set_tuning": (C.c_int, [C.c_void_p, C.c_char_p, C.c_longlong]),

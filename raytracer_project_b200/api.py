@@ -82,10 +82,18 @@ def env_struct(cfg: RenderConfig) -> Environment:
     return env
 
 
-def opts_struct(cfg: RenderConfig, seed=1, sample_range=None, tile=None, stats=False, samples_per_launch=0) -> RenderOpts:
+PARTITION = {"auto": 0, "samples": 1, "tiles": 2}
+
+
+def opts_struct(cfg: RenderConfig, seed=1, sample_range=None, tile=None, stats=False, samples_per_launch=0,
+                partition="auto") -> RenderOpts:
     o = RenderOpts()
     o.samples_per_pixel, o.max_depth, o.seed = cfg.samples_per_pixel, cfg.max_depth, seed
     o.sample_begin, o.sample_end = sample_range if sample_range else (0, cfg.samples_per_pixel)
+    if sample_range and sample_range[0] == sample_range[1]:
+        # an EMPTY share (a rank left without samples): (0, 0) would read as "all samples" in the C struct
+        o.sample_begin = o.sample_end = cfg.samples_per_pixel
+    o.partition = PARTITION[partition]
     o.tile_rank, o.tile_ranks = tile if tile else (0, 1)
     o.use_albedo, o.use_normal, o.use_z_depth = int(cfg.use_albedo), int(cfg.use_normal), int(cfg.use_z_depth)
     o.z_depth_max_dist = cfg.z_depth_max_dist
@@ -214,10 +222,16 @@ def has_experiments() -> bool:
 
 
 class Context:
-    def __init__(self, device: int = 0, stream: int | None = None):
+    def __init__(self, device: int | list = 0, stream: int | None = None):
+        """device: one index, or a list of indices for a multi-GPU context (zb_context_create_multi: one process drives
+        all of them; upload / render / primary_ids are used exactly as on one GPU)."""
         self.lib = _lib.load()
         self.h = C.c_void_p()
-        check(self.lib.zb_context_create(device, C.byref(self.h)))
+        if isinstance(device, (list, tuple)):
+            arr = (C.c_int * len(device))(*device)
+            check(self.lib.zb_context_create_multi(arr, len(device), C.byref(self.h)))
+        else:
+            check(self.lib.zb_context_create(device, C.byref(self.h)))
         if stream is not None:
             check(self.lib.zb_context_set_stream(self.h, C.c_void_p(stream)))
 
@@ -235,6 +249,24 @@ class Context:
     def set_tuning(self, key: str, value: int):
         """zb_context_set_tuning: A/B switches ("pq", "no_lean", "pq_blocks", ...); the product defaults need none."""
         check(self.lib.zb_context_set_tuning(self.h, key.encode(), int(value)))
+
+    def device_count(self) -> int:
+        return int(self.lib.zb_context_device_count(self.h))
+
+    # ---- one process per GPU (torchrun): CUDA IPC handles carried by the caller's transport
+    def group_export(self, max_pixels: int) -> bytes:
+        h = _lib.GroupHandle()
+        check(self.lib.zb_group_export(self.h, max_pixels, C.byref(h)))
+        return bytes(h.opaque)
+
+    def group_join(self, rank: int, handles: list, shm_name: str):
+        arr = (_lib.GroupHandle * len(handles))()
+        for i, b in enumerate(handles):
+            C.memmove(C.byref(arr[i]), b, 256)
+        check(self.lib.zb_group_join(self.h, rank, len(handles), arr, shm_name.encode()))
+
+    def group_leave(self):
+        check(self.lib.zb_group_leave(self.h))
 
     def device_info(self):
         sm, ma, mi, l2 = C.c_int(), C.c_int(), C.c_int(), C.c_size_t()
@@ -287,7 +319,7 @@ class Context:
     def stats(self) -> dict:
         st = Stats()
         check(self.lib.zb_get_stats(self.h, C.byref(st)))
-        return {k: getattr(st, k) for k, _ in Stats._fields_ if k != "pad"}
+        return {k: getattr(st, k) for k, _ in Stats._fields_}
 
 
 class Scene:
@@ -300,14 +332,19 @@ class Scene:
             self.h = C.c_void_p()
 
     def render(self, cfg: RenderConfig, seed=1, stats=False, want_f4=False, sample_range=None, tile=None,
-               samples_per_launch=0, progress=None, cancel=None, beauty_out=None):
+               samples_per_launch=0, progress=None, cancel=None, beauty_out=None, partition="auto", no_host=False):
         """zb_render: returns dict of (H, W, 3) float64 arrays like the reference's buffers.  beauty_out: a caller-owned
         C-contiguous float64 array of W*H*3 elements to fill instead of a new one (the reference's render_accumulator
         is sized once by reset_accumulator and reused, camera.hpp:209-233)."""
         n = cfg.image_width * cfg.image_height
         cam, env = camera_struct(cfg), env_struct(cfg)
-        o = opts_struct(cfg, seed, sample_range, tile, stats, samples_per_launch)
+        o = opts_struct(cfg, seed, sample_range, tile, stats, samples_per_launch, partition)
         out = Outputs()
+        if no_host:
+            # device-only frame (timing): the resolved, packed frame stays in the context's staging buffer on the device
+            check(self.ctx.lib.zb_render(self.ctx.h, self.h, C.byref(cam), C.byref(env), C.byref(o), C.byref(out), None,
+                                         C.cast(None, _lib.PROGRESS_FN), None))
+            return {}
         if beauty_out is not None:
             assert beauty_out.dtype == np.float64 and beauty_out.flags.c_contiguous and beauty_out.size == 3 * n
             res = {"beauty": beauty_out.reshape(cfg.image_height, cfg.image_width, 3)}
@@ -328,6 +365,22 @@ class Scene:
                                      cb, None))
         assert n == res["beauty"].shape[0] * res["beauty"].shape[1]
         return res
+
+    def render_into(self, cfg: RenderConfig, buffers: dict, seed=1, partition="auto", samples_per_launch=0):
+        """zb_render into caller-owned (H, W, 3) float64 arrays keyed like render()'s result — e.g. views of one frame in
+        shared memory that all ranks of a multi-process group write their bands into."""
+        cam, env = camera_struct(cfg), env_struct(cfg)
+        o = opts_struct(cfg, seed, None, None, False, samples_per_launch, partition)
+        out = Outputs()
+        n = cfg.image_width * cfg.image_height
+        for key, flag in (("beauty", True), ("albedo", cfg.use_albedo), ("normal", cfg.use_normal), ("z_depth", cfg.use_z_depth),
+                          ("reflection", cfg.use_reflection), ("refraction", cfg.use_refraction)):
+            if flag and key in buffers:
+                a = buffers[key]
+                assert a.dtype == np.float64 and a.flags.c_contiguous and a.size == 3 * n, key
+                setattr(out, key, a.ctypes.data)
+        check(self.ctx.lib.zb_render(self.ctx.h, self.h, C.byref(cam), C.byref(env), C.byref(o), C.byref(out), None,
+                                     C.cast(None, _lib.PROGRESS_FN), None))
 
     def render_device(self, cfg: RenderConfig, accum_ptr: int, aux_ptr: int = 0, seed=1, sample_range=None, tile=None,
                       stats=False, light_pass=False, accumulate=False, samples_per_launch=0):

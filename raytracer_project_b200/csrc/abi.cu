@@ -75,9 +75,24 @@ extern "C" int zb_context_set_tuning(zb_context* ctx, const char* key, long long
 
 extern "C" int zb_context_destroy(zb_context* ctx) {
     if (!ctx) return ZB_OK;
+    if (ctx->group) {
+        // the leader of a single-process group owns the other members
+        std::vector<zb_context*> others;
+        if (!ctx->group->multi_process)
+            for (zb_context* m : ctx->group->local)
+                if (m != ctx) others.push_back(m);
+        for (zb_context* m : ctx->group->local) {
+            cudaSetDevice(m->device);
+            cudaStreamSynchronize(m->stream);
+        }
+        if (ctx->group->multi_process) zb_group_leave(ctx);
+        else zbg_release(ctx);
+        for (zb_context* m : others) zb_context_destroy(m);
+    }
     cudaSetDevice(ctx->device);
     cudaStreamSynchronize(ctx->stream);
     cudaFree(ctx->counters);
+    cudaFree(ctx->arena);
     cudaFree(ctx->accum);
     cudaFree(ctx->accum_aux);
     cudaFree(ctx->out_f4);
@@ -110,17 +125,50 @@ extern "C" int zb_device_info(zb_context* ctx, int* sm_count, int* cc_major, int
 
 // ------------------------------------------------------------------------------------ scene
 
+// Scene arrays live in ONE device allocation (the arena): a render step that re-uploads its scene (bench e2e, GUI edits)
+// pays one cudaMalloc / cudaFree at most — none when the context's cached arena fits (zb_context::arena) — instead of
+// a dozen of each, which cost more than the copy of a small scene.
+static size_t arena_round(size_t bytes) { return (bytes + 255) & ~size_t(255); }
+
 template <class T>
 static int upload(zb_scene* s, const void* host, size_t count, size_t elem, const T** dev) {
     *dev = nullptr;
     if (count == 0) return ZB_OK;
     if (!host) return fail(ZB_ERR_INVALID, "zb_scene_upload: array pointer is NULL but its count is not 0");
+    const size_t bytes = count * elem;
     void* d = nullptr;
-    ZB_CUDA(cudaMalloc(&d, count * elem));
-    s->allocs.push_back(d);
-    ZB_CUDA(cudaMemcpyAsync(d, host, count * elem, cudaMemcpyHostToDevice, s->ctx->stream));
-    s->bytes += count * elem;
+    if (s->arena && s->arena_used + arena_round(bytes) <= s->arena_bytes) {
+        d = static_cast<char*>(s->arena) + s->arena_used;
+        s->arena_used += arena_round(bytes);
+    } else {
+        ZB_CUDA(cudaMalloc(&d, bytes));
+        s->allocs.push_back(d);
+    }
+    ZB_CUDA(cudaMemcpyAsync(d, host, bytes, cudaMemcpyHostToDevice, s->ctx->stream));
+    s->bytes += bytes;
     *dev = static_cast<const T*>(d);
+    return ZB_OK;
+}
+
+// take the context's cached arena if it is free and large enough, else allocate one of `bytes`
+static int arena_acquire(zb_scene* s, size_t bytes) {
+    zb_context* c = s->ctx;
+    if (c->arena && !c->arena_in_use && c->arena_bytes >= bytes) {
+        s->arena = c->arena;
+        s->arena_bytes = c->arena_bytes;
+        s->arena_from_ctx = true;
+        c->arena_in_use = true;
+        return ZB_OK;
+    }
+    ZB_CUDA(cudaMalloc(&s->arena, bytes));
+    s->arena_bytes = bytes;
+    if (!c->arena_in_use) {  // becomes the context's cached arena (the old, smaller one is released)
+        if (c->arena) cudaFree(c->arena);
+        c->arena = s->arena;
+        c->arena_bytes = bytes;
+        c->arena_in_use = true;
+        s->arena_from_ctx = true;
+    }
     return ZB_OK;
 }
 
@@ -263,16 +311,55 @@ static int build_device_blas(zb_scene* s, const zb_flat_scene* f, std::vector<zb
     return ZB_OK;
 }
 
+static int upload_one(zb_context* ctx, const zb_flat_scene* f, zb_scene** out);
+
 extern "C" int zb_scene_upload(zb_context* ctx, const zb_flat_scene* f, zb_scene** out) {
     if (!ctx || !f || !out) return fail(ZB_ERR_INVALID, "zb_scene_upload: NULL argument");
     int rc = validate(f);
     if (rc) return rc;
+    zb_scene* s = nullptr;
+    rc = upload_one(ctx, f, &s);
+    if (rc) return rc;
+    // a multi-GPU context keeps a replica on every member (the scene is read-only and small next to 180 GB of HBM)
+    if (ctx->group && !ctx->group->multi_process && ctx->group->n > 1 && ctx->group->local[0] == ctx) {
+        for (zb_context* m : ctx->group->local) {
+            if (m == ctx) continue;
+            zb_scene* rep = nullptr;
+            rc = upload_one(m, f, &rep);
+            if (rc) {
+                zb_scene_destroy(s);
+                return rc;
+            }
+            s->replicas.push_back(rep);
+        }
+        cudaSetDevice(ctx->device);
+    }
+    *out = s;
+    return ZB_OK;
+}
+
+static int upload_one(zb_context* ctx, const zb_flat_scene* f, zb_scene** out) {
+    int rc = ZB_OK;
     ZB_CUDA(cudaSetDevice(ctx->device));
     zb_scene* s = new zb_scene();
     s->ctx = ctx;
     SceneDev& d = s->dev;
     bool device_blas = false;
     for (uint32_t m = 0; m < f->n_meshes; m++) device_blas |= f->meshes[m].node_count == 0 && f->meshes[m].tri_count > 0;
+    {
+        size_t need = 0;
+        if (!device_blas) need += arena_round(size_t(f->n_nodes) * sizeof(zb_bvh_node));
+        need += arena_round(size_t(f->n_items) * sizeof(zb_item)) + arena_round(size_t(f->n_cubes) * sizeof(zb_cube)) +
+                arena_round(size_t(f->n_tris) * sizeof(zb_tri)) + arena_round(size_t(f->n_tris) * sizeof(zb_tri_normals)) +
+                arena_round(size_t(f->n_instances) * sizeof(zb_instance)) + arena_round(size_t(f->n_media) * sizeof(zb_medium)) +
+                arena_round(size_t(f->n_materials) * sizeof(zb_material)) + arena_round(size_t(f->n_textures) * sizeof(zb_texture)) +
+                arena_round(size_t(f->n_spheres_obj) * 16) + arena_round(size_t(f->n_texels_u8) * 4) + arena_round(size_t(f->n_texels_f32) * 16);
+        if (need) rc = arena_acquire(s, need);
+        if (rc) {
+            delete s;
+            return rc;
+        }
+    }
     if (!device_blas) rc = upload(s, f->nodes, f->n_nodes, sizeof(zb_bvh_node), &d.nodes);
     if (!rc) rc = upload(s, f->items, f->n_items, sizeof(zb_item), &d.items);
     if (!rc) rc = upload(s, f->cubes, f->n_cubes, sizeof(zb_cube), &d.cubes);
@@ -319,9 +406,15 @@ extern "C" int zb_scene_upload(zb_context* ctx, const zb_flat_scene* f, zb_scene
 
 extern "C" int zb_scene_destroy(zb_scene* s) {
     if (!s) return ZB_OK;
+    for (zb_scene* rep : s->replicas) zb_scene_destroy(rep);
+    s->replicas.clear();
     cudaSetDevice(s->ctx->device);
     cudaStreamSynchronize(s->ctx->stream);
     for (void* p : s->allocs) cudaFree(p);
+    if (s->arena) {
+        if (s->arena_from_ctx && s->ctx->arena == s->arena) s->ctx->arena_in_use = false;  // stays cached for the next upload
+        else cudaFree(s->arena);
+    }
     delete s;
     return ZB_OK;
 }

@@ -21,13 +21,23 @@ inline int fail(int code, const std::string& msg) {
             return fail(ZB_ERR_CUDA, std::string(#expr) + ": " + cudaGetErrorString(e__));                \
     } while (0)
 
+#define ZB_MAX_GROUP 16
+struct zb_group;
+
 struct zb_context {
     int device = 0;
+    // multi-GPU group this context belongs to (group.cu): null for a plain single-GPU context until its first render.  A
+    // context made by zb_context_create_multi is the leader (rank 0) and owns the other members.
+    zb_group* group = nullptr;
+    int group_rank = 0;
     cudaStream_t stream = nullptr;
     bool own_stream = false;
     int sm_count = 0, cc_major = 0, cc_minor = 0;
     size_t l2_bytes = 0;
     unsigned long long* counters = nullptr;  // 8 x u64 on the device
+    void* arena = nullptr;  // scene arena kept across zb_scene_destroy / zb_scene_upload (abi.cu)
+    size_t arena_bytes = 0;
+    bool arena_in_use = false;
     // scratch reused across renders
     float4* accum = nullptr;
     float4* accum_aux = nullptr;
@@ -55,8 +65,12 @@ struct zb_context {
 
 struct zb_scene {
     zb_context* ctx = nullptr;
+    std::vector<zb_scene*> replicas;  // scene of a multi-device context: copies on the other members
     SceneDev dev{};
     std::vector<void*> allocs;
+    void* arena = nullptr;  // one allocation holding the scene arrays (abi.cu); the context's cached arena when arena_from_ctx
+    size_t arena_bytes = 0, arena_used = 0;
+    bool arena_from_ctx = false;
     uint32_t env_hdr_texture = ZB_NO_TEXTURE;
     size_t bytes = 0;
 };
@@ -66,3 +80,41 @@ struct zb_scene {
 int zbr_fill_params(zb_context* ctx, const zb_scene* scene, const zb_camera* cam, const zb_environment* env,
                     const zb_render_opts* o, RenderParams& P);
 int zbr_owned_tiles(const RenderParams& P);
+
+int zbr_read_counters(zb_context* ctx);
+int zbr_check_overflow(zb_context* ctx, const char* who);
+
+// One frame copy in flight: packed RGB floats on the device -> this context's pinned stage -> the caller's 3-double rows.
+// zbr_copy_issue enqueues the chunked copies (+ one event per chunk) on the context stream; zbr_widen_all runs host
+// threads over the chunks of any number of contexts as their events fire.
+struct FrameCopy {
+    zb_context* ctx = nullptr;
+    std::vector<size_t> begin;      // chunk boundaries, in floats, relative to stage / dst
+    const float* stage = nullptr;   // pinned
+    double* dst = nullptr;          // caller memory (pageable or shared)
+    size_t first_event = 0;
+};
+int zbr_copy_issue(zb_context* ctx, const float* dev_rgb, size_t n_floats, double* dst, size_t stage_offset_floats,
+                   std::vector<FrameCopy>& jobs);
+int zbr_widen_all(std::vector<FrameCopy>& jobs);
+int zbr_ensure_pinned(zb_context* ctx, size_t bytes);
+
+// ---- group.cu: a set of n GPUs that renders one frame together
+struct zb_group {
+    int n = 1;                       // ranks in the group
+    bool multi_process = false;      // members are separate processes (CUDA IPC handles, host barrier in shared memory)
+    std::vector<zb_context*> local;  // members owned by this process: all n (zb_context_create_multi) or one (zb_group_join)
+    // per rank, double-buffered by frame parity: fixed-point sums (this process's view: own pointer or peer mapping)
+    unsigned long long* fix[2][ZB_MAX_GROUP] = {};
+    size_t fix_words = 0;            // capacity of every buffer, in u64 words (sums + queue heads)
+    cudaEvent_t render_done[ZB_MAX_GROUP] = {};  // recorded by rank r after its render kernels (interprocess when multi_process)
+    unsigned long long frame = 0;
+    void* shm = nullptr;             // multi-process: host barrier block in POSIX shared memory
+    size_t shm_bytes = 0;
+    std::string shm_name;
+    bool opened[ZB_MAX_GROUP] = {};  // which peer mappings / events this process opened (to close them)
+};
+int zbg_render(zb_context* ctx, const zb_scene* scene, const zb_camera* cam, const zb_environment* env,
+               const zb_render_opts* opts, zb_outputs* out, const volatile int* cancel, zb_progress_fn progress, void* user);
+bool zbg_fast_path(const zb_context* ctx, const zb_render_opts* opts, const zb_outputs* out);
+void zbg_release(zb_context* ctx);

@@ -137,15 +137,7 @@ int ensure_scratch(zb_context* ctx, size_t pixels, bool aux) {
         ctx->accum_pixels = pixels;
     }
     if (aux && !ctx->accum_aux) ZB_CUDA(cudaMalloc(&ctx->accum_aux, 3 * ctx->accum_pixels * sizeof(float4)));
-    size_t need = pixels * 3 * sizeof(double);
-    if (ctx->pinned_bytes < need) {
-        if (ctx->pinned) cudaFreeHost(ctx->pinned);
-        ctx->pinned = nullptr;
-        ctx->pinned_bytes = 0;
-        ZB_CUDA(cudaMallocHost(&ctx->pinned, need));
-        ctx->pinned_bytes = need;
-    }
-    return ZB_OK;
+    return zbr_ensure_pinned(ctx, pixels * sizeof(float4));
 }
 
 int fill_params(zb_context* ctx, const zb_scene* scene, const zb_camera* cam, const zb_environment* env,
@@ -285,22 +277,81 @@ int d2h(zb_context* ctx, void* host, const void* dev, size_t bytes) {
     return ZB_OK;
 }
 
-// Host side of the frame copy: chunk c (pixels [begin[c], begin[c + 1])) is widened from the pinned stage of packed RGB
-// floats into the caller's 3-double layout (camera.hpp:531) as soon as its event has fired; up to 8 host threads.
-int widen_chunks(zb_context* ctx, double* host, const std::vector<size_t>& begin) {
-    const size_t n_chunks = begin.size() - 1;
-    const float* stage = static_cast<const float*>(ctx->pinned);
+int ensure_chunk_events(zb_context* ctx, size_t n) {
+    while (ctx->chunk_ev.size() < n) {
+        cudaEvent_t e;
+        ZB_CUDA(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+        ctx->chunk_ev.push_back(e);
+    }
+    return ZB_OK;
+}
+}  // namespace
+
+int zbr_ensure_pinned(zb_context* ctx, size_t bytes) {
+    if (ctx->pinned_bytes >= bytes) return ZB_OK;
+    if (ctx->pinned) cudaFreeHost(ctx->pinned);
+    ctx->pinned = nullptr;
+    ctx->pinned_bytes = 0;
+    ZB_CUDA(cudaMallocHost(&ctx->pinned, bytes));
+    ctx->pinned_bytes = bytes;
+    return ZB_OK;
+}
+
+// Packed RGB floats on the device (12 B/pixel instead of 24 as doubles) -> this context's pinned stage, in chunks of
+// 3 MiB with one event each, asynchronously on the context stream.  The chunks are widened into the caller's 3-double
+// layout (camera.hpp:531) by zbr_widen_all while later chunks — of this and of other GPUs — are still in flight.
+int zbr_copy_issue(zb_context* ctx, const float* dev_rgb, size_t n_floats, double* dst, size_t stage_offset_floats,
+                   std::vector<FrameCopy>& jobs) {
+    if (!n_floats) return ZB_OK;
+    if ((stage_offset_floats + n_floats) * sizeof(float) > ctx->pinned_bytes) return fail(ZB_ERR_INVALID, "frame copy: pinned stage too small");
+    const size_t chunk = size_t(3) << 18;  // 768 Ki floats = 3 MiB per copy
+    const size_t n_chunks = (n_floats + chunk - 1) / chunk;
+    size_t first = 0;
+    for (const FrameCopy& j : jobs)
+        if (j.ctx == ctx) first = std::max(first, j.first_event + j.begin.size() - 1);
+    int rc = ensure_chunk_events(ctx, first + n_chunks);
+    if (rc) return rc;
+    FrameCopy job;
+    job.ctx = ctx;
+    job.stage = static_cast<const float*>(ctx->pinned) + stage_offset_floats;
+    job.dst = dst;
+    job.first_event = first;
+    float* stage = static_cast<float*>(ctx->pinned) + stage_offset_floats;
+    for (size_t c = 0; c < n_chunks; c++) {
+        const size_t b = c * chunk, n = std::min(chunk, n_floats - b);
+        job.begin.push_back(b);
+        ZB_CUDA(cudaMemcpyAsync(stage + b, dev_rgb + b, n * sizeof(float), cudaMemcpyDeviceToHost, ctx->stream));
+        ZB_CUDA(cudaEventRecord(ctx->chunk_ev[first + c], ctx->stream));
+    }
+    job.begin.push_back(n_floats);
+    jobs.push_back(std::move(job));
+    return ZB_OK;
+}
+
+// Host side of the frame copies: every chunk is widened from its pinned stage into the caller's doubles as soon as its
+// event has fired; up to 8 host threads share the chunks of all jobs (round-robin over the jobs, so that every GPU's
+// first chunk is served first).
+int zbr_widen_all(std::vector<FrameCopy>& jobs) {
+    struct Item { const FrameCopy* job; size_t chunk; };
+    std::vector<Item> items;
+    size_t longest = 0;
+    for (const FrameCopy& j : jobs) longest = std::max(longest, j.begin.size() - 1);
+    for (size_t c = 0; c < longest; c++)
+        for (const FrameCopy& j : jobs)
+            if (c + 1 < j.begin.size()) items.push_back({&j, c});
+    if (items.empty()) return ZB_OK;
     const unsigned hw = std::max(1u, std::thread::hardware_concurrency());
-    const size_t n_thr = std::min<size_t>(std::min<size_t>(hw, 8), n_chunks);
+    const size_t n_thr = std::min<size_t>(std::min<size_t>(hw, 8), items.size());
     std::atomic<size_t> next{0};
     std::atomic<int> err{0};
     auto work = [&]() {
         for (;;) {
-            const size_t c = next.fetch_add(1);
-            if (c >= n_chunks) return;
-            if (cudaEventSynchronize(ctx->chunk_ev[c]) != cudaSuccess) { err.store(1); return; }
-            const size_t b = 3 * begin[c], e = 3 * begin[c + 1];
-            zbh_widen_f32_f64(stage + b, host + b, e - b);
+            const size_t k = next.fetch_add(1);
+            if (k >= items.size()) return;
+            const FrameCopy& j = *items[k].job;
+            if (cudaEventSynchronize(j.ctx->chunk_ev[j.first_event + items[k].chunk]) != cudaSuccess) { err.store(1); return; }
+            const size_t b = j.begin[items[k].chunk], e = j.begin[items[k].chunk + 1];
+            zbh_widen_f32_f64(j.stage + b, j.dst + b, e - b);
         }
     };
     std::vector<std::thread> pool;
@@ -311,19 +362,9 @@ int widen_chunks(zb_context* ctx, double* host, const std::vector<size_t>& begin
     return ZB_OK;
 }
 
-int ensure_chunk_events(zb_context* ctx, size_t n) {
-    while (ctx->chunk_ev.size() < n) {
-        cudaEvent_t e;
-        ZB_CUDA(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
-        ctx->chunk_ev.push_back(e);
-    }
-    return ZB_OK;
-}
-
-// Device float4 means -> the reference's host layout (3 doubles per pixel, camera.hpp:531).  The frame is packed to
-// RGB floats on the device and crosses PCIe at 12 B/pixel (instead of 24 as doubles) in chunks; while chunk c+1 is in
-// flight, host threads widen chunk c into the caller's buffer, so the copy, the widening and the pageable-memory
-// write overlap.
+namespace {
+// Device float4 means -> the reference's host layout (3 doubles per pixel, camera.hpp:531): packed to RGB floats on the
+// device, then zbr_copy_issue / zbr_widen_all.
 int d2h_rgb_f64(zb_context* ctx, double* host, const float4* dev, size_t pixels) {
     if (ctx->rgb_pack_pixels < pixels) {
         cudaFree(ctx->rgb_pack);
@@ -332,22 +373,13 @@ int d2h_rgb_f64(zb_context* ctx, double* host, const float4* dev, size_t pixels)
         ZB_CUDA(cudaMalloc(&ctx->rgb_pack, pixels * 3 * sizeof(float)));
         ctx->rgb_pack_pixels = pixels;
     }
+    int rc = zbr_ensure_pinned(ctx, pixels * 3 * sizeof(float));
+    if (rc) return rc;
     ZB_CUDA(zbk_launch_pack_rgb(dev, pixels, ctx->rgb_pack, ctx->stream));
     ctx->stats.launches++;
-    const size_t chunk = size_t(1) << 18;  // 256 Ki pixels = 3 MiB per copy
-    const size_t n_chunks = (pixels + chunk - 1) / chunk;
-    int rc = ensure_chunk_events(ctx, n_chunks);
-    if (rc) return rc;
-    float* stage = static_cast<float*>(ctx->pinned);
-    std::vector<size_t> begin;
-    for (size_t c = 0; c < n_chunks; c++) {
-        const size_t b = c * chunk, n = std::min(chunk, pixels - b);
-        begin.push_back(b);
-        ZB_CUDA(cudaMemcpyAsync(stage + 3 * b, ctx->rgb_pack + 3 * b, n * 3 * sizeof(float), cudaMemcpyDeviceToHost, ctx->stream));
-        ZB_CUDA(cudaEventRecord(ctx->chunk_ev[c], ctx->stream));
-    }
-    begin.push_back(pixels);
-    rc = widen_chunks(ctx, host, begin);
+    std::vector<FrameCopy> jobs;
+    rc = zbr_copy_issue(ctx, ctx->rgb_pack, pixels * 3, host, 0, jobs);
+    if (!rc) rc = zbr_widen_all(jobs);
     if (rc) return rc;
     ZB_CUDA(cudaStreamSynchronize(ctx->stream));
     return ZB_OK;
@@ -382,6 +414,8 @@ int zbr_fill_params(zb_context* ctx, const zb_scene* scene, const zb_camera* cam
     return fill_params(ctx, scene, cam, env, o, P);
 }
 int zbr_owned_tiles(const RenderParams& P) { return owned_tiles(P); }
+int zbr_read_counters(zb_context* ctx) { return read_counters(ctx); }
+int zbr_check_overflow(zb_context* ctx, const char* who) { return check_overflow(ctx, who); }
 
 extern "C" int zb_render_device(zb_context* ctx, const zb_scene* scene, const zb_camera* cam,
                                 const zb_environment* env, const zb_render_opts* opts, void* accum_f4,
@@ -452,14 +486,6 @@ extern "C" int zb_resolve_device(zb_context* ctx, const void* accum_f4, size_t n
 extern "C" int zb_read_frame(zb_context* ctx, const void* mean_f4, size_t n_pixels, double* out_rgb_f64) {
     if (!ctx || !mean_f4 || !out_rgb_f64) return fail(ZB_ERR_INVALID, "zb_read_frame: NULL argument");
     ZB_CUDA(cudaSetDevice(ctx->device));
-    const size_t need = n_pixels * sizeof(float4);
-    if (ctx->pinned_bytes < need) {
-        if (ctx->pinned) cudaFreeHost(ctx->pinned);
-        ctx->pinned = nullptr;
-        ctx->pinned_bytes = 0;
-        ZB_CUDA(cudaMallocHost(&ctx->pinned, need));
-        ctx->pinned_bytes = need;
-    }
     return d2h_rgb_f64(ctx, out_rgb_f64, static_cast<const float4*>(mean_f4), n_pixels);
 }
 
@@ -474,6 +500,51 @@ extern "C" int zb_render(zb_context* ctx, const zb_scene* scene, const zb_camera
     const size_t pixels = size_t(cam->image_width) * cam->image_height;
     const bool light = (opts->use_reflection && out->reflection) || (opts->use_refraction && out->refraction);
     const bool aux = out->albedo || out->normal || out->z_depth;
+    const bool multi = ctx->group && ctx->group->n > 1;
+    if (zbg_fast_path(ctx, opts, out)) {
+        // The product path (group.cu): path-queue kernel into 64-bit fixed-point sums, one fused resolve (+ gather over the
+        // group's GPUs) that packs the frame for the copy home.  A plain context is a group of one.  On a multi-GPU
+        // context this returns all requested buffers; on a single GPU the light passes follow below (k_render<LIGHT>).
+        rc = zbg_render(ctx, scene, cam, env, opts, out, cancel, progress, user);
+        if (rc) return rc;
+        if (multi || !light) {
+            if (progress) progress(cam->image_height, user);  // camera.hpp:576-578
+            return ZB_OK;
+        }
+        rc = ensure_scratch(ctx, pixels, true);
+        if (rc) return rc;
+        const zb_stats beauty_stats = ctx->stats;
+        ZB_CUDA(cudaMemsetAsync(ctx->counters, 0, 8 * sizeof(unsigned long long), ctx->stream));
+        ZB_CUDA(cudaEventRecord(ctx->ev[4], ctx->stream));
+        P.accum = ctx->accum;
+        P.accum_aux = ctx->accum_aux;
+        P.light_pass = 1;
+        rc = launch_share(ctx, P, opts, cancel, nullptr, nullptr, true);
+        double* light_out[2] = {opts->use_reflection ? out->reflection : nullptr, opts->use_refraction ? out->refraction : nullptr};
+        const float4* light_src[2] = {ctx->accum, ctx->accum_aux};
+        for (int k = 0; k < 2 && !rc; k++) {
+            if (!light_out[k]) continue;
+            ZB_CUDA(zbk_launch_resolve(light_src[k], pixels, float(1.0 / opts->samples_per_pixel), ctx->out_f4, nullptr, ctx->stream));
+            ctx->stats.launches++;
+            rc = d2h_rgb_f64(ctx, light_out[k], ctx->out_f4, pixels);
+        }
+        if (rc) return rc;
+        ZB_CUDA(cudaEventRecord(ctx->ev[5], ctx->stream));
+        rc = read_counters(ctx);
+        if (rc) return rc;
+        float lms = 0;
+        ZB_CUDA(cudaEventElapsedTime(&lms, ctx->ev[4], ctx->ev[5]));
+        const uint32_t light_launches = ctx->stats.launches - beauty_stats.launches, light_overflows = ctx->stats.stack_overflows;
+        ctx->stats = beauty_stats;  // paths / rays keep the beauty pass's meaning (light passes are not counted)
+        ctx->stats.launches += light_launches;
+        ctx->stats.stack_overflows += light_overflows;
+        ctx->stats.kernel_ms += lms;
+        rc = check_overflow(ctx, "zb_render");
+        if (rc) return rc;
+        if (progress) progress(cam->image_height, user);
+        return ZB_OK;
+    }
+    // ---- general path: STATS kernel, tile-bound k_render (tuning pq = 0), the queue kernel's own AOV / light modes (pq = 2), beauty_f4
     P.light_pass = 0;
     rc = ensure_scratch(ctx, pixels, aux || light);
     if (rc) return rc;
@@ -646,8 +717,10 @@ extern "C" int zb_checkpoint_load(zb_context* ctx, const char* path, void* accum
 
 extern "C" int zb_get_stats(zb_context* ctx, zb_stats* out) {
     if (!ctx || !out) return fail(ZB_ERR_INVALID, "zb_get_stats: NULL argument");
-    int rc = read_counters(ctx);
-    if (rc) return rc;
+    if (ctx->stats.n_gpus == 0) {  // a frame rendered through the group path already holds the sums over its GPUs
+        int rc = read_counters(ctx);
+        if (rc) return rc;
+    }
     *out = ctx->stats;
     return ZB_OK;
 }

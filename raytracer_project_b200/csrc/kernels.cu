@@ -636,7 +636,8 @@ __global__ void __launch_bounds__(ZB_BLOCK_THREADS, MIN_BLOCKS) k_render_pqr(con
 // (the same integers k_render adds up in shared memory, so the planes are bit-identical to its output).  Primary rays
 // of an 8x4 sub-tile at the same sample index are coherent: 133 M of them cost ~3 ms on the headline frame.
 template <uint32_t F>
-__global__ void __launch_bounds__(ZB_BLOCK_THREADS, 6) k_aov_pass(const __grid_constant__ RenderParams P) {
+__global__ void __launch_bounds__(ZB_BLOCK_THREADS, 6) k_aov_pass(const __grid_constant__ RenderParams P,
+                                                                  unsigned long long* __restrict__ fix_aux) {
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int tile = blockIdx.x * P.tile_ranks + P.tile_rank;
     const int tx = tile % P.tiles_x, ty = tile / P.tiles_x;
@@ -681,6 +682,13 @@ __global__ void __launch_bounds__(ZB_BLOCK_THREADS, 6) k_aov_pass(const __grid_c
         if (P.use_z) add(6, 1.0f - clamp01(hit.t * P.inv_z_max));
     }
     const size_t n = size_t(P.cam.width) * P.cam.height, i = pixel;
+    if (fix_aux) {
+        // fused-resolve / multi-GPU form (group.cu): the integer sums themselves, 7 words per pixel, added to what earlier
+        // sample batches left there (one thread per pixel, launches are stream-ordered: no atomics needed)
+#pragma unroll
+        for (int k = 0; k < 7; k++) fix_aux[7 * i + k] += acc[k];
+        return;
+    }
     const float z = fix_get(acc[6]);
     float4 a0 = make_float4(fix_get(acc[0]), fix_get(acc[1]), fix_get(acc[2]), 0.f);
     float4 a1 = make_float4(fix_get(acc[3]), fix_get(acc[4]), fix_get(acc[5]), 0.f);
@@ -885,6 +893,9 @@ cudaError_t zbk_launch_render(const RenderParams& P, int n_tiles_owned, bool sta
     return cudaGetLastError();
 }
 
+static thread_local uint32_t g_last_pq_pick = 0;
+uint32_t zbk_last_pq_pick() { return g_last_pq_pick; }
+
 size_t zbk_pq_words(size_t pixels, int mode) { return pixels * (mode == PQ_AUX ? 10 : mode == PQ_LIGHT ? 6 : 3); }
 
 cudaError_t zbk_pq_clear(unsigned long long* fix, size_t pixels, int mode, unsigned long long* heads, int n_heads, cudaStream_t stream) {
@@ -927,6 +938,7 @@ cudaError_t zbk_launch_render_pq(const RenderParams& P, int n_tiles_owned, int m
     // 64 spp 35.10 / 34.66 / 34.42 ms with 64 / 128 / 256, 8 spp 4.44 / 4.46 / 4.52, 1200x675 x 10 spp 2.23 / 2.25 / 2.36
     const unsigned long long per_warp = total / (4ull * blocks);
     const unsigned batch = per_warp >= 64ull * PQ_BATCH ? PQ_BATCH : per_warp >= 64ull * (PQ_BATCH / 2) ? PQ_BATCH / 2 : PQ_BATCH / 4;
+    g_last_pq_pick = (uint32_t(feat == ZB_F_ALL ? std::min(std::max(per_sm, 6), 7) : per_sm) << 16) | (uint32_t(mode) << 8) | feat;
 #define PQ_LAUNCH(B, M) k_render_pq<B, M><<<blocks, ZB_BLOCK_THREADS, 0, stream>>>(P, fix, fix_aux, head, total, batch)
 #ifdef ZB_EXPERIMENTS
     const int resume = tn.pq_resume;  // experiment: resumable traversal (k_render_pqr)
@@ -947,7 +959,15 @@ cudaError_t zbk_launch_render_pq(const RenderParams& P, int n_tiles_owned, int m
 cudaError_t zbk_launch_aov_pass(const RenderParams& P, int n_tiles_owned, const ZbTuning& tn, cudaStream_t stream) {
     if (n_tiles_owned <= 0 || !P.accum_aux) return cudaSuccess;
     const uint32_t feat = pick_feature_set(P, tn);
-    ZB_FOR_FEATURE_SET(feat, (k_aov_pass<F><<<n_tiles_owned, ZB_BLOCK_THREADS, 0, stream>>>(P)));
+    ZB_FOR_FEATURE_SET(feat, (k_aov_pass<F><<<n_tiles_owned, ZB_BLOCK_THREADS, 0, stream>>>(P, nullptr)));
+    return cudaGetLastError();
+}
+
+cudaError_t zbk_launch_aov_pass_fixed(const RenderParams& P, int n_tiles_owned, unsigned long long* fix_aux, const ZbTuning& tn,
+                                      cudaStream_t stream) {
+    if (n_tiles_owned <= 0 || !fix_aux) return cudaSuccess;
+    const uint32_t feat = pick_feature_set(P, tn);
+    ZB_FOR_FEATURE_SET(feat, (k_aov_pass<F><<<n_tiles_owned, ZB_BLOCK_THREADS, 0, stream>>>(P, fix_aux)));
     return cudaGetLastError();
 }
 

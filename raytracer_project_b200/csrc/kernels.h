@@ -24,6 +24,8 @@ cudaError_t zbk_launch_render(const RenderParams& P, int n_tiles_owned, bool sta
 // fix = zbk_pq_words(pixels, mode) u64 fixed-point sums, head = one u64 queue head per launch; clear, launch (one or
 // several disjoint tile ranges), then resolve rows into P.accum / P.accum_aux or (beauty) into scaled means
 size_t zbk_pq_words(size_t pixels, int mode);
+// the instantiation the calling thread's last zbk_launch_render_pq ran: (blocks per SM << 16) | (mode << 8) | feature set
+uint32_t zbk_last_pq_pick();
 cudaError_t zbk_pq_clear(unsigned long long* fix, size_t pixels, int mode, unsigned long long* heads, int n_heads, cudaStream_t stream);
 cudaError_t zbk_launch_render_pq(const RenderParams& P, int n_tiles_owned, int mode, unsigned long long* fix, unsigned long long* head,
                                  int sm_count, const ZbTuning& tn, cudaStream_t stream);
@@ -31,6 +33,9 @@ cudaError_t zbk_pq_resolve(const RenderParams& P, int mode, const unsigned long 
                            float4* mean_out, cudaStream_t stream);
 // first-hit AOV planes of this rank's tiles into P.accum_aux, as a pass beside the beauty queue kernel
 cudaError_t zbk_launch_aov_pass(const RenderParams& P, int n_tiles_owned, const ZbTuning& tn, cudaStream_t stream);
+// the same pass adding its 64-bit fixed-point sums (7 words per pixel) to fix_aux instead of writing float planes
+cudaError_t zbk_launch_aov_pass_fixed(const RenderParams& P, int n_tiles_owned, unsigned long long* fix_aux, const ZbTuning& tn,
+                                      cudaStream_t stream);
 cudaError_t zbk_launch_primary_ids(const RenderParams& P, uint32_t* leaf_id, uint32_t* prim_id, float* t,
                                    cudaStream_t stream);
 cudaError_t zbk_launch_resolve(const float4* accum, size_t n, float scale, float4* out_f4, double* out_f64,

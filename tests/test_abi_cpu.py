@@ -26,7 +26,8 @@ def test_struct_sizes_match_header():
     # the PODs of include/zenith_b200.h as laid out by the C compiler
     assert C.sizeof(_lib.Camera) == 8 + 8 + 72 + 16
     assert C.sizeof(_lib.Environment) == 8 + 24 + 8 + 24 + 48 + 16
-    assert C.sizeof(_lib.Stats) == 6 * 8 + 4 * 8 + 8
+    assert C.sizeof(_lib.Stats) == 6 * 8 + 4 * 8 + 16
+    assert C.sizeof(_lib.RenderOpts) == 88 and C.sizeof(_lib.GroupHandle) == 256
 
 
 def _views(f):
