@@ -401,6 +401,8 @@ static int render_impl(zb_context* ctx, const zb_scene* scene, const zb_camera* 
         const zb_scene* sc;
         RenderParams P;
         int row0, row1, s0, s1;
+        uint64_t paths, rays;  // of the beauty pass (the light passes are not counted)
+        uint32_t overflows;
     };
     std::vector<Member> M;
     for (zb_context* c : G->local) {
@@ -558,6 +560,20 @@ static int render_impl(zb_context* ctx, const zb_scene* scene, const zb_camera* 
             if (pass == 0) ZB_CUDA(cudaEventRecord(m.c->ev[3], m.c->stream));
             ZB_CUDA(cudaStreamSynchronize(m.c->stream));
         }
+        if (pass == 0 && light) {  // keep the beauty pass's counters apart from the light passes'
+            for (Member& m : M) {
+                ZB_CUDA(cudaSetDevice(m.c->device));
+                const uint32_t launches = m.c->stats.launches, pick = m.c->stats.kernel_pick;
+                rc = zbr_read_counters(m.c);
+                if (rc) return rc;
+                m.paths = m.c->stats.paths;
+                m.rays = m.c->stats.rays;
+                m.overflows = m.c->stats.stack_overflows;
+                m.c->stats.launches = launches;
+                m.c->stats.kernel_pick = pick;
+                ZB_CUDA(cudaMemsetAsync(m.c->counters, 0, 8 * sizeof(unsigned long long), m.c->stream));
+            }
+        }
         rc = host_barrier(G);  // the frame is complete in the caller's buffer of every rank
         if (rc) return rc;
     }
@@ -576,10 +592,10 @@ static int render_impl(zb_context* ctx, const zb_scene* scene, const zb_camera* 
         total.resolve_ms = std::max(total.resolve_ms, double(ms));
         ZB_CUDA(cudaEventElapsedTime(&ms, c->ev[2], c->ev[3]));
         total.d2h_ms = std::max(total.d2h_ms, double(ms));
-        total.paths += c->stats.paths;
-        total.rays += c->stats.rays;
+        total.paths += light ? m.paths : c->stats.paths;
+        total.rays += light ? m.rays : c->stats.rays;
         total.launches += launches;
-        total.stack_overflows += c->stats.stack_overflows;
+        total.stack_overflows += c->stats.stack_overflows + (light ? m.overflows : 0u);
         if (c == ctx || !total.kernel_pick) total.kernel_pick = pick;
     }
     ZB_CUDA(cudaSetDevice(ctx->device));
