@@ -26,4 +26,6 @@ done
 g++ -O2 -std=c++20 -fPIC -Wall $EXP -c host_glue.cpp -o $B/host_glue.o &
 wait
 $NVCC $ARCH -shared -o $OUT $OBJS $B/host_glue.o -cudart static -lz -lrt -lpthread
+# SHA-1 of every kernel's SASS (ties ncu instruction counts under profiles/ to the code that runs; tools/sass_hash.py)
+if [ "$OUT" = "../libzenith_b200.so" ]; then python3 ../../tools/sass_hash.py $OUT ../_build/sass_hashes.json || true; fi
 echo "built $OUT"
