@@ -213,6 +213,8 @@ def ours(args):
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
     if world > 1:
+        if os.environ.get("NCCL_DEBUG", "").upper() == "VERSION":
+            os.environ["NCCL_DEBUG"] = "WARN"  # NCCL prints its version banner on STDOUT, in front of the JSON line
         dist.init_process_group("nccl", device_id=dev)
     name = args.config
     _, _, WIDTH, HEIGHT, SPP, _, described = CONFIGS[name]
