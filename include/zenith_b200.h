@@ -350,6 +350,23 @@ typedef struct zb_probe {
 int zb_probe_rays(zb_context* ctx, const zb_scene* scene, const zb_environment* env, size_t n,
                   const float* origins, const float* directions, zb_probe* out);
 
+/* Known-answer probe (parity tool): ONE device function of the shading code per case, on explicit inputs, so that each can
+ * be compared with the reference function it restates — refract / reflect (vec3.hpp:204-214), dielectric::reflectance
+ * (material.hpp:237-241), texture::value (texture.hpp:50-78, :96-98, :118-126; index = textures[] index),
+ * material::get_bumped_normal (material.hpp:35-54; index = materials[] index), sphere::get_sphere_uv (sphere.hpp:70-79),
+ * camera::get_background_color (camera.hpp:828-925).  Argument layouts: csrc/kernels.cu k_kat.  Host pointers; blocking. */
+enum { ZB_KAT_REFRACT = 0, ZB_KAT_REFLECT = 1, ZB_KAT_REFLECTANCE = 2, ZB_KAT_TEXTURE = 3, ZB_KAT_BUMP = 4,
+       ZB_KAT_SPHERE_UV = 5, ZB_KAT_BACKGROUND = 6 };
+typedef struct zb_kat_case {
+    uint32_t op, index;
+    float a[14];
+} zb_kat_case;
+typedef struct zb_kat_result {
+    float r[4]; /* r[3] < 0: unknown op */
+} zb_kat_result;
+int zb_kat_eval(zb_context* ctx, const zb_scene* scene, const zb_environment* env, size_t n, const zb_kat_case* cases,
+                zb_kat_result* out);
+
 /* Accumulation checkpoint: the float4 radiance sums + how many samples of which seed they hold, so a
  * progressive render can stop and resume (the Philox counter carries the global sample index, so samples
  * [0, k) + [k, n) give the frame of [0, n)).  "ZBCK" file: magic, u32 width, height, samples_done, reserved, u64 seed,

@@ -581,7 +581,7 @@ static int cmd_decode(const std::string& in, const std::string& out, bool is_hdr
     return 0;
 }
 
-int cmd_kat(const std::string& out);  // ref_kat.inc
+int cmd_kat(const std::string& scene, const std::string& cfg_path, const std::string& out);  // ref_kat.inc
 
 #include "ref_kat.inc"
 
@@ -594,9 +594,9 @@ int main(int argc, char** argv) {
     if (a.size() >= 4 && a[0] == "finish") return cmd_finish(a[1], a[2], a[3]);
     if (a.size() >= 4 && a[0] == "export") return cmd_export(a[1], a[2], a[3]);
     if (a.size() >= 4 && a[0] == "decode") return cmd_decode(a[1], a[2], a[3] == "1");
-    if (a.size() >= 2 && a[0] == "kat") return cmd_kat(a[1]);
+    if (a.size() >= 4 && a[0] == "kat") return cmd_kat(a[1], a[2], a[3]);
     std::fprintf(stderr,
                  "usage: ref_harness ids SCENE CFG OUT | render SCENE CFG OUT|- [--count-rays] | stats SCENE CFG OUT N |\n"
-                 "       decode IN OUT.zbtex ISHDR | kat OUT.json\n");
+                 "       decode IN OUT.zbtex ISHDR | kat SCENE CFG OUT.json\n");
     return 1;
 }

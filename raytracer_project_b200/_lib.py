@@ -130,6 +130,7 @@ SYMBOLS = {
     "zb_render": (C.c_int, [C.c_void_p, C.c_void_p, C.POINTER(Camera), C.POINTER(Environment), C.POINTER(RenderOpts),
                             C.POINTER(Outputs), C.POINTER(C.c_int), PROGRESS_FN, C.c_void_p]),
     "zb_probe_rays": (C.c_int, [C.c_void_p, C.c_void_p, C.POINTER(Environment), C.c_size_t, C.c_void_p, C.c_void_p, C.c_void_p]),
+    "zb_kat_eval": (C.c_int, [C.c_void_p, C.c_void_p, C.POINTER(Environment), C.c_size_t, C.c_void_p, C.c_void_p]),
     "zb_read_frame": (C.c_int, [C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p]),
     "zb_render_device": (C.c_int, [C.c_void_p, C.c_void_p, C.POINTER(Camera), C.POINTER(Environment),
                                    C.POINTER(RenderOpts), C.c_void_p, C.c_void_p]),

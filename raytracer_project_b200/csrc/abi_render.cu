@@ -671,6 +671,30 @@ extern "C" int zb_probe_rays(zb_context* ctx, const zb_scene* scene, const zb_en
     return check_overflow(ctx, "zb_probe_rays");
 }
 
+extern "C" int zb_kat_eval(zb_context* ctx, const zb_scene* scene, const zb_environment* env, size_t n, const zb_kat_case* cases,
+                           zb_kat_result* out) {
+    if (!ctx || !scene || !env || (n && (!cases || !out))) return fail(ZB_ERR_INVALID, "zb_kat_eval: NULL argument");
+    if (scene->ctx != ctx) return fail(ZB_ERR_INVALID, "zb_kat_eval: scene belongs to another context");
+    ZB_CUDA(cudaSetDevice(ctx->device));
+    RenderParams P;
+    std::memset(&P, 0, sizeof(P));
+    P.sc = scene->dev;
+    int rc = setup_env(env, scene, P.env);
+    if (rc || n == 0) return rc;
+    zb_kat_case* d_in = nullptr;
+    zb_kat_result* d_out = nullptr;
+    cudaError_t e = cudaMalloc(&d_in, n * sizeof(zb_kat_case));
+    if (e == cudaSuccess) e = cudaMalloc(&d_out, n * sizeof(zb_kat_result));
+    if (e == cudaSuccess) e = cudaMemcpyAsync(d_in, cases, n * sizeof(zb_kat_case), cudaMemcpyHostToDevice, ctx->stream);
+    if (e == cudaSuccess) e = zbk_launch_kat(P, n, d_in, d_out, ctx->stream);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(out, d_out, n * sizeof(zb_kat_result), cudaMemcpyDeviceToHost, ctx->stream);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
+    cudaFree(d_in);
+    cudaFree(d_out);
+    if (e != cudaSuccess) return fail(ZB_ERR_CUDA, std::string("zb_kat_eval: ") + cudaGetErrorString(e));
+    return ZB_OK;
+}
+
 extern "C" int zb_checkpoint_save(zb_context* ctx, const char* path, const void* accum_f4, int width, int height,
                                   int samples_done, uint64_t seed) {
     if (!ctx || !path || !accum_f4 || width < 1 || height < 1) return fail(ZB_ERR_INVALID, "zb_checkpoint_save: bad argument");

@@ -813,6 +813,55 @@ __global__ void __launch_bounds__(128) k_probe(const __grid_constant__ RenderPar
     out[i] = r;
 }
 
+// Known-answer probe (zb_kat_eval): single device functions of the shading code on explicit inputs, one thread per case.
+__global__ void __launch_bounds__(128) k_kat(const __grid_constant__ RenderParams P, size_t n, const zb_kat_case* __restrict__ in,
+                                             zb_kat_result* __restrict__ out) {
+    const size_t i = size_t(blockIdx.x) * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const zb_kat_case c = in[i];
+    const float* a = c.a;
+    float3 r = f3(0, 0, 0);
+    float w = 0.f;
+    switch (c.op) {
+        case ZB_KAT_REFRACT: {  // a: unit direction (3), normal facing it (3), eta ratio
+            const float3 ud = f3(a[0], a[1], a[2]), wn = f3(a[3], a[4], a[5]);
+            r = refract_dir(ud, wn, a[6], fminf(dot(-ud, wn), 1.0f));
+        } break;
+        case ZB_KAT_REFLECT: r = reflect_dir(f3(a[0], a[1], a[2]), f3(a[3], a[4], a[5])); break;
+        case ZB_KAT_REFLECTANCE: r.x = schlick_reflectance(a[0], a[1]); break;
+        case ZB_KAT_TEXTURE: r = texture_value(P.sc, c.index, a[0], a[1], f3(a[2], a[3], a[4])); break;
+        case ZB_KAT_BUMP: {  // index: material; a: u, v, normal (3), tangent (3), bitangent (3), p (3)
+            Surface sf;
+            sf.u = a[0];
+            sf.v = a[1];
+            sf.n = f3(a[2], a[3], a[4]);
+            sf.tangent = f3(a[5], a[6], a[7]);
+            sf.bitangent = f3(a[8], a[9], a[10]);
+            sf.p = f3(a[11], a[12], a[13]);
+            r = bumped_normal(P.sc, load_mat0(P.sc, c.index), sf);
+        } break;
+        case ZB_KAT_SPHERE_UV: {  // a: unit outward normal; the uv of sphere_surface for a unit sphere at the origin, seen from outside
+            Surface sf;
+            const float3 on = f3(a[0], a[1], a[2]);
+            sphere_surface(make_float4(0.f, 0.f, 0.f, 1.f), on, -on, sf, true);
+            r.x = sf.u;
+            r.y = sf.v;
+        } break;
+        case ZB_KAT_BACKGROUND: r = background(P.sc, P.env, f3(a[0], a[1], a[2])); break;
+        default: w = -1.f; break;
+    }
+    out[i].r[0] = r.x;
+    out[i].r[1] = r.y;
+    out[i].r[2] = r.z;
+    out[i].r[3] = w;
+}
+
+cudaError_t zbk_launch_kat(const RenderParams& P, size_t n, const zb_kat_case* in, zb_kat_result* out, cudaStream_t stream) {
+    if (n == 0) return cudaSuccess;
+    k_kat<<<unsigned((n + 127) / 128), 128, 0, stream>>>(P, n, in, out);
+    return cudaGetLastError();
+}
+
 cudaError_t zbk_launch_probe(const RenderParams& P, size_t n, const float* org, const float* dir, zb_probe* out,
                              cudaStream_t stream) {
     if (n == 0) return cudaSuccess;

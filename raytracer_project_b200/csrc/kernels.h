@@ -43,6 +43,7 @@ cudaError_t zbk_launch_resolve(const float4* accum, size_t n, float scale, float
 cudaError_t zbk_launch_pack_rgb(const float4* in, size_t n, float* out, cudaStream_t stream);
 cudaError_t zbk_launch_probe(const RenderParams& P, size_t n, const float* org, const float* dir, zb_probe* out,
                              cudaStream_t stream);
+cudaError_t zbk_launch_kat(const RenderParams& P, size_t n, const zb_kat_case* in, zb_kat_result* out, cudaStream_t stream);
 // nodes (lo, hi) -> (centre, half extent) in place, when the traversal is compiled for that encoding (ZB_BOX_CH)
 cudaError_t zbk_convert_nodes(float4* nodes, uint32_t n, cudaStream_t stream);
 bool zbk_nodes_center_half();

@@ -203,6 +203,21 @@ ZB_DEV float3 material_get_albedo(const SceneDev& sc, const Surface& sf) {
     return a;
 }
 
+// reflect (vec3.hpp:204-206), refract (vec3.hpp:209-214) and dielectric::reflectance (Schlick, material.hpp:237-241) as the
+// scatter code below evaluates them; also reached one by one through zb_kat_eval (known-answer tests)
+ZB_DEV float3 reflect_dir(float3 v, float3 n) { return fma3(-2.0f * dot(v, n), n, v); }
+ZB_DEV float3 refract_dir(float3 ud, float3 wn, float ri, float cos_t) {
+    float3 perp = ri * fma3(cos_t, wn, ud);
+    float3 par = -sqrtf(fabsf(1.0f - dot(perp, perp))) * wn;
+    return perp + par;
+}
+ZB_DEV float schlick_reflectance(float cos_t, float ri) {
+    float r0 = (1.f - ri) / (1.f + ri);
+    r0 *= r0;
+    float om = 1.f - cos_t, om2 = om * om;
+    return r0 + (1.f - r0) * om2 * om2 * om;
+}
+
 // material::scatter.  xi = (x, y: unit vector; z: dielectric choice).  Returns false when the path
 // ends here (light, absorbed metal sample).
 template <uint32_t F = ZB_F_ALL>
@@ -237,18 +252,10 @@ ZB_DEV bool material_scatter(const SceneDev& sc, const Surface& sf, float3 d_in,
         float3 ud = unit_vector(d_in);
         float cos_t = fminf(dot(-ud, wn), 1.0f);
         float sin_t = sqrtf(fmaxf(0.f, 1.0f - cos_t * cos_t));
-        float r0 = (1.f - ri) / (1.f + ri);
-        r0 *= r0;
-        float om = 1.f - cos_t, om2 = om * om;
-        float refl = r0 + (1.f - r0) * om2 * om2 * om;
+        float refl = schlick_reflectance(cos_t, ri);
         float3 dir;
-        if (ri * sin_t > 1.0f || refl > xi.z) {
-            dir = fma3(-2.0f * dot(ud, wn), wn, ud);
-        } else {
-            float3 perp = ri * fma3(cos_t, wn, ud);
-            float3 par = -sqrtf(fabsf(1.0f - dot(perp, perp))) * wn;
-            dir = perp + par;
-        }
+        if (ri * sin_t > 1.0f || refl > xi.z) dir = reflect_dir(ud, wn);
+        else dir = refract_dir(ud, wn, ri, cos_t);
         float side = dot(dir, sf.n) > 0.f ? ray_epsilon : -ray_epsilon;
         o_out = fma3(side, sf.n, sf.p);
         d_out = dir;

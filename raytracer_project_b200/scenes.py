@@ -586,6 +586,32 @@ def shipped_models(seed: int = 6, width: int = 640, height: int = 360, spp: int 
     return w.text(), cfg, files
 
 
+def kat_scene(env: str = "solid"):
+    """Scene of the per-function known-answer tests (tests/golden/kat.json): every texture kind — solids, a checker,
+    the reference's shipped JPEGs (baseline 4:2:0 fine-wood, progressive 4:4:4 wood bump, baseline scratches, progressive
+    concrete) — and one bump-mapped material of each type, on spheres so that the flattener keeps them; `env` picks the
+    environment whose get_background_color is probed (solid | hdr with yaw / tilt / roll | sun)."""
+    from . import ztex
+    w = SceneWriter()
+    names = {"wood": "assets/textures/fine-wood.jpg", "woodbump": "assets/bump_maps/wood_bump_map.jpg",
+             "scratches": "assets/bump_maps/scratches_bump_map.jpg", "concrete": "assets/bump_maps/concrete_bump_map.jpg"}
+    files = {p: shipped_asset(p[len("assets/"):]) for p in names.values()}
+    files.update(ztex.hdr_pair("sky.hdr", _sky_hdr(256, 128, 60.0)))
+    tex = {k: w.tex_image(p, name="t_" + k) for k, p in names.items()}
+    checker = w.tex_checker(0.7, w.tex_solid((0.15, 0.2, 0.1), name="t_odd"), w.tex_solid((0.9, 0.85, 0.8), name="t_even"), name="t_checker")
+    mats = [w.lambertian(tex=tex["wood"], bump=tex["woodbump"], strength=8.0, name="m_wood"),
+            w.metal((1.0, 0.8, 0.4), 0.0, bump=tex["scratches"], strength=-1.0, name="m_gold"),
+            w.dielectric(1.5, bump=tex["concrete"], strength=0.02, name="m_glass"),
+            w.lambertian(tex=checker, name="m_checker")]
+    objs = [w.sphere((2.0 * k - 3.0, 0.5, 0.0), 0.5, m) for k, m in enumerate(mats)]
+    w.world(w.container("bvh", objs, name="world"))
+    w.lines.append("envmap sky.hdr")
+    cfg = RenderConfig(image_width=64, image_height=36, samples_per_pixel=1, env_mode=env, background=(0.3, 0.5, 0.9), env_intensity=1.25,
+                       hdr_path="sky.hdr", hdri_rotation=0.5, hdri_tilt=-0.2, hdri_roll=0.3, sun_direction=(0.6, 0.45, 0.5),
+                       sun_color=(1.0, 0.95, 0.85), sun_intensity=1.5, sun_size=2.0)
+    return w.text(), cfg, files
+
+
 def wire_demo(seed: int = 7, width: int = 240, height: int = 135, spp: int = 64, max_depth: int = 50):
     """Scene of the BVH debug-view tests: 24 seeded spheres, two cubes and a lamp inside a region
     the camera sees whole, so the root box of the tree (level 0 — the one level that does not depend on how the

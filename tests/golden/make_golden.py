@@ -272,6 +272,23 @@ def texels():
         json.dump(out, f, indent=1)
 
 
+def kat():
+    """Per-function known answers (oracle/ref_kat.inc): the reference's refract / reflect / reflectance / texture::value /
+    get_bumped_normal / get_sphere_uv on the KAT scene, and get_background_color for the three environment modes."""
+    cases, digests = [], {}
+    for env in ("solid", "hdr", "sun"):
+        txt, cfg, files = scenes.kat_scene(env)
+        d = scratch_dir()
+        scenes.materialize(d, txt, cfg, files)
+        print("kat", env, run_harness(["kat", "s.zscene", "s.cfg", "kat.json"], d))
+        got = json.load(open(os.path.join(d, "kat.json")))["cases"]
+        cases += [c for c in got if c["op"] == "background" or env == "solid"]
+        digests[env] = scene_digest(txt, cfg, files)
+    with open(os.path.join(GOLDEN, "kat.json"), "w") as f:
+        json.dump({"digests": digests, "cases": cases}, f)
+    print("kat cases:", len(cases))
+
+
 def quirks_aov():
     txt, cfg, files = scenes.quirks(seed=5, width=320, height=180, spp=512)
     cfg.z_depth_max_dist = 15.0
@@ -318,7 +335,7 @@ def scene_targets():
     return t
 
 
-TARGETS = {"texels": texels, "finish": finish, "export": export, "wire": wire, "quirks_aov": quirks_aov, "quirks_light": quirks_light, "weekend_ids": weekend_ids, "weekend_probe": weekend_probe, "weekend_stats": weekend_stats, **scene_targets()}
+TARGETS = {"texels": texels, "kat": kat, "finish": finish, "export": export, "wire": wire, "quirks_aov": quirks_aov, "quirks_light": quirks_light, "weekend_ids": weekend_ids, "weekend_probe": weekend_probe, "weekend_stats": weekend_stats, **scene_targets()}
 
 if __name__ == "__main__":
     names = sys.argv[1:] or list(TARGETS)

@@ -60,7 +60,8 @@ def test_oracle_reproduces_quirks_ids():
 
 
 def test_golden_fixtures_are_complete():
-    need = ["weekend_1200x675_ids.npz", "weekend_300x169_stats.npz", "weekend_probe.npz", "quirks_320x180_aov.npz"]
+    need = ["weekend_1200x675_ids.npz", "weekend_300x169_stats.npz", "weekend_probe.npz", "quirks_320x180_aov.npz", "kat.json",
+            "shipped_texels.json"]
     for name, (_, _, ids_wh, stats_wh, _) in GOLDEN_SCENES.items():
         need += [f"{name}_{ids_wh[0]}x{ids_wh[1]}_ids.npz", f"{name}_probe.npz"]
         if stats_wh:
