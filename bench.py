@@ -235,17 +235,25 @@ def ours(args):
     # ---- the scene: flattened once by rank 0 (host BVH build), shared with the other ranks as a ZBFS file
     job = bcast(f"{os.getpid()}_{int(time.time()) % 100000}")
     txt, cfg, files = make_scene(name)
-    zbfs = f"/tmp/zb_bench_{name}_{job}.zbfs"
+    # ZB_BENCH_CACHE=dir keeps the flattened scene of a config as dir/NAME.zbfs for later runs on the same box (the host
+    # BVH build of the 10 M-triangle config takes ~100 s, during which every GPU of the box idles)
+    cache = os.environ.get("ZB_BENCH_CACHE")
+    zbfs = os.path.join(cache, f"{name}.zbfs") if cache else f"/tmp/zb_bench_{name}_{job}.zbfs"
     t_prep = time.time()
     if not files:
         flat = api.flatten_zscene(txt)
+    elif cache and os.path.exists(zbfs):
+        barrier()
+        flat = api.load_flat(zbfs)
     else:
         flat0 = None
         if rank == 0:
             d = tempfile.mkdtemp(prefix="zb_bench_")
             flat0 = api.flatten_zscene(path=scenes.materialize(d, txt, cfg, files))
-            if world > 1:
-                api.save_flat(flat0, zbfs)
+            if world > 1 or cache:
+                os.makedirs(os.path.dirname(zbfs), exist_ok=True)
+                api.save_flat(flat0, zbfs + ".tmp")
+                os.rename(zbfs + ".tmp", zbfs)
             shutil.rmtree(d, ignore_errors=True)
         barrier()
         flat = flat0 if rank == 0 else api.load_flat(zbfs)
@@ -423,7 +431,7 @@ def ours(args):
     del host_rgb
     barrier()
     if rank == 0:
-        for p in (frame_path, zbfs):
+        for p in (frame_path,) + (() if cache else (zbfs,)):
             if os.path.exists(p):
                 os.remove(p)
     scene.close()

@@ -263,3 +263,52 @@ def test_image_texture_decodes_shipped_jpeg_png_like_the_reference(tmp_path):
         px = np.ctypeslib.as_array(C.cast(f.texels_u8, C.POINTER(C.c_uint8)), (f.n_texels_u8, 4))[first:first + w * h, :3].copy()
         api.free_flat(flat)
         assert hashlib.sha256(px.tobytes()).hexdigest() == g["sha256"], rel
+
+
+def _tree_depth(nodes_i32, root, n_nodes):
+    depth, todo = 0, [(root, 1)]
+    while todo:
+        n, d = todo.pop()
+        depth = max(depth, d)
+        assert d <= 200, "cycle"
+        for c in nodes_i32[n, 12:14]:
+            if c >= 0:
+                assert c < n_nodes
+                todo.append((int(c), d + 1))
+    return depth
+
+
+def test_builders_bound_tree_depth_on_degenerate_scenes(tmp_path):
+    """The traversal stack holds one deferred child per level (csrc/trace.cuh): the host builder must keep the TLAS within
+    ZB_MAX_TLAS_DEPTH and every BLAS within ZB_MAX_BLAS_DEPTH whatever SAH would like — geometrically spaced objects (SAH
+    peels one object per level: a 3000-deep comb without the cap) and a mesh whose triangles share one centroid."""
+    w = scenes.SceneWriter()
+    m = w.lambertian((0.5, 0.5, 0.5))
+    objs = [w.sphere((1.02 ** k, 0.0, 0.0), 0.004 * 1.02 ** k, m) for k in range(3000)]
+    # 4096 coincident-centroid triangles (a fan of thin slivers around the origin) + geometrically growing ones
+    obj = ["v 0 0 0"]
+    import math
+    for k in range(4097):
+        a = 2 * math.pi * k / 4097
+        obj.append("v %.6f %.6f 0" % (math.cos(a), math.sin(a)))
+        obj.append("v %.6f %.6f 0" % (-math.cos(a), -math.sin(a)))
+    for k in range(4096):
+        obj.append(f"f {2 * k + 2} {2 * k + 4} {2 * k + 3}")  # (c, c', -c): centroid ~ 0 for all
+    for k in range(600):
+        s = 1.05 ** k
+        obj.append("v %.6f 0 5\nv %.6f %.6f 5\nv %.6f 0 5" % (s, s, 0.01 * s, 1.02 * s))
+        n = 1 + 2 * 4097 + 3 * k
+        obj.append(f"f {n + 1} {n + 2} {n + 3}")
+    (tmp_path / "fan.obj").write_text("\n".join(obj) + "\n")
+    objs.append(w.model("fan.obj", m, 1.0))
+    w.world(w.container("bvh", objs, name="world"))
+    (tmp_path / "s.zscene").write_text(w.text())
+    flat = api.flatten_zscene(path=str(tmp_path / "s.zscene"))
+    f = flat.contents
+    nodes = np.ctypeslib.as_array(C.cast(f.nodes, C.POINTER(C.c_int32)), (f.n_nodes, 16))
+    tlas = _tree_depth(nodes, 0, f.n_nodes)
+    meshes = np.ctypeslib.as_array(C.cast(f.meshes, C.POINTER(C.c_uint32)), (f.n_meshes, 4))
+    blas = max(_tree_depth(nodes, int(r[0]), f.n_nodes) for r in meshes)
+    print("TLAS depth", tlas, "BLAS depth", blas, "items", f.n_items, "tris", f.n_tris)
+    api.free_flat(flat)
+    assert f.n_items >= 3001 and tlas <= 22 and blas <= 38, (tlas, blas)  # ZB_MAX_TLAS_DEPTH / ZB_MAX_BLAS_DEPTH
