@@ -7,6 +7,7 @@
 #include <cmath>
 #include <limits>
 #include <memory>
+#include <random>
 
 namespace zenith {
 
@@ -17,6 +18,16 @@ constexpr double infinity = std::numeric_limits<double>::infinity();
 constexpr double pi = 3.14159265358979323846;
 
 inline double degrees_to_radians(double d) { return d * pi / 180.0; }
+
+// common.hpp:29-45: the scene-construction randomness of the reference's API (random_device-seeded mt19937; scene code such
+// as load_materials() and build_geometry() calls these; the GPU render never does — it draws from Philox)
+inline double random_double() {
+    static thread_local std::mt19937 gen{std::random_device{}()};
+    static thread_local std::uniform_real_distribution<double> dist(0.0, 1.0);
+    return dist(gen);
+}
+inline double random_double(double lo, double hi) { return lo + (hi - lo) * random_double(); }
+inline int random_int(int lo, int hi) { return static_cast<int>(random_double(lo, hi + 1)); }
 
 struct vec3 {
     double e[3];
@@ -33,6 +44,8 @@ struct vec3 {
     vec3& operator/=(double t) { return *this *= 1.0 / t; }
     double length_squared() const { return e[0] * e[0] + e[1] * e[1] + e[2] * e[2]; }
     double length() const { return std::sqrt(length_squared()); }
+    static vec3 random() { return vec3(random_double(), random_double(), random_double()); }  // vec3.hpp:98-103
+    static vec3 random(double lo, double hi) { return vec3(random_double(lo, hi), random_double(lo, hi), random_double(lo, hi)); }
 };
 using point3 = vec3;
 using color = vec3;

@@ -312,3 +312,42 @@ def test_builders_bound_tree_depth_on_degenerate_scenes(tmp_path):
     print("TLAS depth", tlas, "BLAS depth", blas, "items", f.n_items, "tris", f.n_tris)
     api.free_flat(flat)
     assert f.n_items >= 3001 and tlas <= 22 and blas <= 38, (tlas, blas)  # ZB_MAX_TLAS_DEPTH / ZB_MAX_BLAS_DEPTH
+
+
+@pytest.mark.skipif(not os.path.isdir("/root/reference"), reason="needs the reference sources (build container only)")
+def test_reference_load_materials_compiles_against_host_api(tmp_path):
+    """the reference's OWN material-library code — load_materials(), scene_management.hpp:49-100, 36 add()
+    calls with image textures, bump maps, checker textures, color::random — is the compile contract of the host scene API.
+    Its text is read from /root/reference at test time (nothing is copied into the repository), compiled under
+    `using namespace zenith;` and run where the shipped assets are: every material must exist and the JPEG textures decode."""
+    import subprocess
+    src = open("/root/reference/scene_management.hpp").read().splitlines()
+    start = next(i for i, l in enumerate(src) if l.startswith("void load_materials("))
+    end = next(i for i in range(start, len(src)) if src[i].startswith("}"))
+    body = "\n".join(src[start:end + 1])
+    assert body.count("mat_lib.add(") >= 36
+    host = os.path.join(ROOT, "raytracer_project_b200", "host")
+    (tmp_path / "t.cpp").write_text(f'''
+#include "zenith/scene.hpp"
+#include "zenith/materials.hpp"
+#include <cstdio>
+using namespace zenith;
+using std::make_shared;
+{body}
+int main() {{
+    MaterialLibrary lib;
+    load_materials(lib);
+    auto wood = std::dynamic_pointer_cast<lambertian>(lib.get("wood_bumpy_texture"));
+    auto img = wood ? std::dynamic_pointer_cast<image_texture>(wood->tex) : nullptr;
+    std::printf("%zu %d %d %zu\\n", lib.get_material_names().size(), img ? img->width : -1, img ? img->height : -1,
+                lib.get_emissive_names().size());
+    return 0;
+}}
+''')
+    r = subprocess.run(["g++", "-std=c++20", "-O1", "-I", host, "-I", os.path.join(ROOT, "include"), "t.cpp", "-o", "t"], cwd=tmp_path,
+                       capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr[-3000:]
+    os.symlink(os.path.join(ROOT, "tests", "golden", "assets"), tmp_path / "assets")
+    out = subprocess.run(["./t"], cwd=tmp_path, capture_output=True, text=True, check=True).stdout.split()
+    n, w, h, emissive = (int(x) for x in out)
+    assert n >= 33 and (w, h) == (280, 280) and emissive >= 7, out
