@@ -450,7 +450,11 @@ def main():
     ap.add_argument("--config", default="headline", choices=list(CONFIGS))
     ap.add_argument("--partition", default="auto", choices=["auto", "samples", "tiles"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--spp", type=int, default=0, help="profiling runs only: override the config's samples per pixel (the workload name says so)")
     args = ap.parse_args()
+    if args.spp > 0:
+        c = CONFIGS[args.config]
+        CONFIGS[args.config] = c[:4] + (args.spp,) + c[5:]
     if args.impl == "reference":
         return reference_arm(args)
     world = int(os.environ.get("WORLD_SIZE", "1"))

@@ -304,7 +304,9 @@ int zbr_copy_issue(zb_context* ctx, const float* dev_rgb, size_t n_floats, doubl
                    std::vector<FrameCopy>& jobs) {
     if (!n_floats) return ZB_OK;
     if ((stage_offset_floats + n_floats) * sizeof(float) > ctx->pinned_bytes) return fail(ZB_ERR_INVALID, "frame copy: pinned stage too small");
-    const size_t chunk = size_t(3) << 18;  // 768 Ki floats = 3 MiB per copy
+    // 3 MiB per copy for a whole frame; an eighth of the job (>= 256 KiB) for the small bands of a multi-GPU frame, so that
+    // the copy of chunk c + 1 overlaps the widening of chunk c there too
+    const size_t chunk = std::min(size_t(3) << 18, std::max(size_t(1) << 16, (n_floats / 8 + 1023) & ~size_t(1023)));
     const size_t n_chunks = (n_floats + chunk - 1) / chunk;
     size_t first = 0;
     for (const FrameCopy& j : jobs)
@@ -341,7 +343,10 @@ int zbr_widen_all(std::vector<FrameCopy>& jobs) {
             if (c + 1 < j.begin.size()) items.push_back({&j, c});
     if (items.empty()) return ZB_OK;
     const unsigned hw = std::max(1u, std::thread::hardware_concurrency());
-    const size_t n_thr = std::min<size_t>(std::min<size_t>(hw, 8), items.size());
+    size_t total_floats = 0;
+    for (const FrameCopy& j : jobs) total_floats += j.begin.back();
+    // one thread per 256 Ki floats of work, at most 8: the ranks of a process group share the host's cores
+    const size_t n_thr = std::min(std::min<size_t>(std::min<size_t>(hw, 8), items.size()), total_floats / (size_t(1) << 18) + 1);
     std::atomic<size_t> next{0};
     std::atomic<int> err{0};
     auto work = [&]() {
