@@ -22,7 +22,7 @@
 extern "C" {
 #endif
 
-#define ZB_ABI_VERSION 3
+#define ZB_ABI_VERSION 4
 
 typedef enum zb_status {
     ZB_OK = 0,
@@ -59,6 +59,23 @@ typedef struct zb_bvh_node {
  * (bvh.hpp:46-54) has no such bound; its median-split tree is log2(N) deep by construction (bvh.hpp:15-44). */
 #define ZB_MAX_TLAS_DEPTH 22
 #define ZB_MAX_BLAS_DEPTH 38
+
+/* 8-wide compressed BVH node, 80 B (five 16-byte loads), built by the host for scenes with meshes beside the binary tree
+ * (host/wide_bvh.hpp; layout after Ylitie, Karras, Laine 2017).  Child i: lo = p + qlo[axis][i] * 2^(e[axis] - 127),
+ * hi likewise, rounded outwards.  meta[i]: high 3 bits = primitives of a leaf child (1..4; 1 for an inner child, 0 = empty
+ * slot), low 5 bits = 24 + i for an inner child, else the offset of the leaf's first primitive from prim_base.  Inner
+ * children are the consecutive nodes child_base + popcount(imask below slot i); a node's leaf primitives (TLAS items or
+ * BLAS triangles, <= 24) are consecutive from prim_base.  Both trees address the same primitive arrays. */
+typedef struct zb_wide_node {
+    float p[3];
+    uint8_t e[3];
+    uint8_t imask;
+    uint32_t child_base;
+    uint32_t prim_base;
+    uint8_t meta[8];
+    uint8_t qlo[3][8];
+    uint8_t qhi[3][8];
+} zb_wide_node;
 
 /* Top-level leaf item, 32 B.  One per leaf object of the world (DFS order of the scene graph
  * gives `leaf_id`; items are stored in BVH leaf order).  Spheres that sit directly in the world
@@ -106,7 +123,7 @@ typedef struct zb_instance {
     uint32_t geom_kind;
     uint32_t geom_index; /* spheres_obj[] / cubes[] / meshes[] / tris[] */
     uint32_t flags;      /* ZB_FLAG_FORCE_FRONT */
-    uint32_t pad[5];
+    uint32_t pad[5];     /* mesh instances: pad[0] = BLAS root in nodes[], pad[1] = BLAS root in wide_nodes[] */
 } zb_instance;
 
 typedef struct zb_mesh {
@@ -170,6 +187,12 @@ typedef struct zb_flat_scene {
     const float* texels_f32;   /* RGBA32F */
     uint32_t n_leaves;         /* number of leaf ids handed out */
     uint32_t pad;
+    /* optional 8-wide tree over the same primitives (n_wide_nodes == 0: none; the renderer then walks the binary tree):
+     * TLAS root = wide_nodes[0], BLAS roots in zb_instance::pad[1].  wide_stack_need = traversal-stack entries a ray can
+     * hold: deepest TLAS path + deepest BLAS path + 4. */
+    uint32_t n_wide_nodes;
+    uint32_t wide_stack_need;
+    const zb_wide_node* wide_nodes;
 } zb_flat_scene;
 
 /* The 13 public camera parameters (camera.hpp:26-42); derived quantities are computed in double by
@@ -282,7 +305,7 @@ int zb_context_destroy(zb_context* ctx);
 /* A/B switches for measurements and equality tests; product defaults need none of them.  Read once from the environment at
  * context creation (ZB_PQ, ZB_NO_LEAN, ZB_PQ_BLOCKS, ZB_GATHER_P2P), changed afterwards only here.  Keys: "pq" (0 tile-bound
  * k_render, 1 path-queue beauty kernel, 2 also its AOV / light modes), "no_lean" (1: general kernels), "pq_blocks" (6..8),
- * "gather_p2p" (multi-GPU combine: 1 fused peer-memory kernel, 0 staged copies); a library built with -DZB_EXPERIMENTS
+ * "gather_p2p" (reserved), "wide" (1: walk the 8-wide tree where a scene has one, 0: the binary tree); a library built with -DZB_EXPERIMENTS
  * (zb_build_flags() & ZB_BUILD_EXPERIMENTS) adds "pq_resume", "wavefront", "wf_slots" for the rejected kernel forms. */
 int zb_context_set_tuning(zb_context* ctx, const char* key, long long value);
 #define ZB_BUILD_EXPERIMENTS 1
@@ -463,6 +486,8 @@ int zb_flat_scene_from_zscene_text(const char* text, size_t len, const zb_flat_s
  * let zb_scene_upload build linear BVHs on the device (csrc/lbvh.cu): time-to-first-pixel for multi-million-triangle
  * meshes drops from seconds to milliseconds, at a lower tree quality.  Exactly one of path / text is given. */
 #define ZB_FLATTEN_GPU_BLAS 1u
+#define ZB_FLATTEN_WIDE_ALL 2u /* also build the 8-wide tree for scenes without meshes (A/B measurements) */
+#define ZB_FLATTEN_NO_WIDE 4u  /* never build the 8-wide tree */
 int zb_flat_scene_from_zscene_ex(const char* path, const char* text, size_t len, uint32_t flags, const zb_flat_scene** out);
 /* Scene features (SceneDev::features; template parameter F of the render kernels, csrc/trace.cuh, shade.cuh, kernels.cu).
  * The render kernel is compiled for several feature sets: code for item kinds, textures and environments a scene does

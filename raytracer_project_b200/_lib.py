@@ -33,6 +33,7 @@ class FlatScene(C.Structure):
         ("tri_normals", C.c_void_p), ("instances", C.c_void_p), ("meshes", C.c_void_p), ("media", C.c_void_p),
         ("materials", C.c_void_p), ("textures", C.c_void_p), ("spheres_obj", C.c_void_p),
         ("texels_u8", C.c_void_p), ("texels_f32", C.c_void_p), ("n_leaves", C.c_uint32), ("pad", C.c_uint32),
+        ("n_wide_nodes", C.c_uint32), ("wide_stack_need", C.c_uint32), ("wide_nodes", C.c_void_p),
     ]
 
     def meshes_array(self):
@@ -43,7 +44,7 @@ class FlatScene(C.Structure):
 
     def nbytes(self) -> int:
         """Bytes zb_scene_upload copies to the device for this scene."""
-        return (self.n_nodes * 64 + self.n_items * 32 + self.n_cubes * 32 + self.n_tris * 96 + self.n_instances * 128
+        return (self.n_nodes * 64 + self.n_wide_nodes * 80 + self.n_items * 32 + self.n_cubes * 32 + self.n_tris * 96 + self.n_instances * 128
                 + self.n_media * 32 + self.n_materials * 32 + self.n_textures * 32 + self.n_spheres_obj * 16
                 + self.n_texels_u8 * 4 + self.n_texels_f32 * 16)
 

@@ -64,6 +64,7 @@ extern "C" int zb_context_set_tuning(zb_context* ctx, const char* key, long long
     else if (k == "no_lean") t.no_lean = value != 0;
     else if (k == "pq_blocks") t.pq_blocks = int(value);
     else if (k == "gather_p2p") t.gather_p2p = int(value);
+    else if (k == "wide") t.wide = value != 0;
 #ifdef ZB_EXPERIMENTS
     else if (k == "pq_resume") t.pq_resume = int(value);
     else if (k == "wavefront") t.wavefront = value != 0;
@@ -217,6 +218,34 @@ static int validate(const zb_flat_scene* f) {
                 return fail(ZB_ERR_INVALID, "flat scene: mesh BLAS deeper than ZB_MAX_BLAS_DEPTH (or cyclic)");
         }
     }
+    // the optional 8-wide tree: every index a traversal can form stays inside the arrays, and the stack need fits
+    if (f->n_wide_nodes) {
+        if (!f->wide_nodes) return fail(ZB_ERR_INVALID, "flat scene: wide_nodes is NULL but n_wide_nodes is not 0");
+        if (f->wide_stack_need == 0 || f->wide_stack_need > 31) return fail(ZB_ERR_INVALID, "flat scene: 8-wide tree deeper than the traversal stack (wide_stack_need > 31)");
+        for (uint32_t i = 0; i < f->n_wide_nodes; i++) {
+            const zb_wide_node& w = f->wide_nodes[i];
+            uint32_t n_inner = 0, max_prim = 0;
+            for (int s2 = 0; s2 < 8; s2++) {
+                const uint32_t cnt = w.meta[s2] >> 5, idx = w.meta[s2] & 31u;
+                if (cnt == 0) continue;
+                if (idx >= 24) {
+                    if (cnt != 1 || idx != 24u + uint32_t(s2) || !((w.imask >> s2) & 1)) return fail(ZB_ERR_INVALID, "flat scene: malformed inner child in an 8-wide node");
+                    n_inner++;
+                } else {
+                    if (cnt > 4 || idx + cnt > 24 || ((w.imask >> s2) & 1)) return fail(ZB_ERR_INVALID, "flat scene: malformed leaf child in an 8-wide node");
+                    max_prim = std::max(max_prim, idx + cnt);
+                }
+            }
+            if (uint32_t(__builtin_popcount(w.imask)) != n_inner) return fail(ZB_ERR_INVALID, "flat scene: 8-wide imask does not match its children");
+            if (n_inner && (w.child_base <= i || uint64_t(w.child_base) + n_inner > f->n_wide_nodes))
+                return fail(ZB_ERR_INVALID, "flat scene: 8-wide child range out of bounds (children must follow their parent)");
+            if (uint64_t(w.prim_base) + max_prim > std::max(f->n_items, f->n_tris)) return fail(ZB_ERR_INVALID, "flat scene: 8-wide primitive range out of bounds");
+            if (w.e[0] > 239 || w.e[1] > 239 || w.e[2] > 239) return fail(ZB_ERR_INVALID, "flat scene: 8-wide node exponent out of range");
+        }
+        for (uint32_t i = 0; i < f->n_instances; i++)
+            if (f->instances[i].geom_kind == ZB_GEOM_MESH && f->instances[i].pad[1] >= f->n_wide_nodes)
+                return fail(ZB_ERR_INVALID, "flat scene: instance 8-wide BLAS root out of range");
+    }
     for (uint32_t i = 0; i < f->n_items; i++) {
         const zb_item& it = f->items[i];
         uint32_t kind = it.kind_flags & 0xFFu;
@@ -348,7 +377,7 @@ static int upload_one(zb_context* ctx, const zb_flat_scene* f, zb_scene** out) {
     for (uint32_t m = 0; m < f->n_meshes; m++) device_blas |= f->meshes[m].node_count == 0 && f->meshes[m].tri_count > 0;
     {
         size_t need = 0;
-        if (!device_blas) need += arena_round(size_t(f->n_nodes) * sizeof(zb_bvh_node));
+        if (!device_blas) need += arena_round(size_t(f->n_nodes) * sizeof(zb_bvh_node)) + arena_round(size_t(f->n_wide_nodes) * sizeof(zb_wide_node));
         need += arena_round(size_t(f->n_items) * sizeof(zb_item)) + arena_round(size_t(f->n_cubes) * sizeof(zb_cube)) +
                 arena_round(size_t(f->n_tris) * sizeof(zb_tri)) + arena_round(size_t(f->n_tris) * sizeof(zb_tri_normals)) +
                 arena_round(size_t(f->n_instances) * sizeof(zb_instance)) + arena_round(size_t(f->n_media) * sizeof(zb_medium)) +
@@ -361,6 +390,7 @@ static int upload_one(zb_context* ctx, const zb_flat_scene* f, zb_scene** out) {
         }
     }
     if (!device_blas) rc = upload(s, f->nodes, f->n_nodes, sizeof(zb_bvh_node), &d.nodes);
+    if (!rc && !device_blas) rc = upload(s, f->wide_nodes, f->n_wide_nodes, sizeof(zb_wide_node), &s->wide);
     if (!rc) rc = upload(s, f->items, f->n_items, sizeof(zb_item), &d.items);
     if (!rc) rc = upload(s, f->cubes, f->n_cubes, sizeof(zb_cube), &d.cubes);
     if (!rc) rc = upload(s, f->tris, f->n_tris, sizeof(zb_tri), &d.tris);
@@ -395,6 +425,7 @@ static int upload_one(zb_context* ctx, const zb_flat_scene* f, zb_scene** out) {
     d.n_items = f->n_items;
     d.n_media = f->n_media;
     d.overflow = ctx->counters + 6;
+    d.wide = s->wide;  // fill_params drops it when tuning wide = 0
     // scene features (ZB_F_*): which code a render kernel has to carry for this scene
     d.features = 0;
     zb_flat_scene_features(f, &d.features);

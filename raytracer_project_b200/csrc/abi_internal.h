@@ -65,6 +65,7 @@ struct zb_context {
 
 struct zb_scene {
     zb_context* ctx = nullptr;
+    const float4* wide = nullptr;  // the scene's 8-wide tree on the device (null: none)
     std::vector<zb_scene*> replicas;  // scene of a multi-device context: copies on the other members
     SceneDev dev{};
     std::vector<void*> allocs;

@@ -147,6 +147,7 @@ int fill_params(zb_context* ctx, const zb_scene* scene, const zb_camera* cam, co
     if (o->samples_per_pixel < 1 || o->max_depth < 0) return fail(ZB_ERR_INVALID, "render: bad spp / max_depth");
     std::memset(&P, 0, sizeof(P));
     P.sc = scene->dev;
+    if (!ctx->tuning.wide) P.sc.wide = nullptr;
     int rc = setup_camera(cam, P.cam);
     if (rc) return rc;
     rc = setup_env(env, scene, P.env);
@@ -621,6 +622,7 @@ extern "C" int zb_primary_ids(zb_context* ctx, const zb_scene* scene, const zb_c
     RenderParams P;
     std::memset(&P, 0, sizeof(P));
     P.sc = scene->dev;
+    if (!ctx->tuning.wide) P.sc.wide = nullptr;
     int rc = setup_camera(cam, P.cam);
     if (rc) return rc;
     const size_t pixels = size_t(cam->image_width) * cam->image_height;
@@ -653,6 +655,7 @@ extern "C" int zb_probe_rays(zb_context* ctx, const zb_scene* scene, const zb_en
     RenderParams P;
     std::memset(&P, 0, sizeof(P));
     P.sc = scene->dev;
+    if (!ctx->tuning.wide) P.sc.wide = nullptr;
     int rc = setup_env(env, scene, P.env);
     if (rc || n == 0) return rc;
     float *d_o = nullptr, *d_d = nullptr;

@@ -37,6 +37,10 @@ int load(std::istream& in, const std::string& base_dir, const zb_flat_scene** ou
         std::shared_ptr<hittable> world = ld.build_world();
         flattener fl;
         fl.gpu_blas = (flags & ZB_FLATTEN_GPU_BLAS) != 0;
+        fl.wide_all = (flags & ZB_FLATTEN_WIDE_ALL) != 0;
+        if (flags & ZB_FLATTEN_NO_WIDE) fl.wide = -1;
+        if (const char* e = std::getenv("ZB_WIDE_ALL")) fl.wide_all = std::atoi(e) != 0;  // A/B runs: 8-wide tree for TLAS-only scenes too
+        if (const char* e = std::getenv("ZB_NO_WIDE")) { if (std::atoi(e) != 0) fl.wide = -1; }
         if (const char* e = std::getenv("ZB_TLAS_LEAF")) fl.tlas_leaf = std::max(1, std::min(8, std::atoi(e)));  // tuning knobs
         if (const char* e = std::getenv("ZB_BLAS_LEAF")) fl.blas_leaf = std::max(1, std::min(8, std::atoi(e)));
         EnvironmentSettings env;
@@ -88,7 +92,8 @@ extern "C" int zb_flat_scene_from_zscene_ex(const char* path, const char* text, 
 // "ZBFS" container: a flattened scene written once (rank 0, or an offline tool) and loaded by every rank / every
 // later run without re-parsing OBJ files and re-building the BVH.  Little-endian PODs exactly as in zenith_b200.h:
 //   char magic[4] = "ZBFS"; u32 abi_version; u32 n_tlas_nodes, n_leaves, env_hdr_texture, reserved;
-//   then 13 sections, each = u64 byte count + payload padded to 16 bytes, in the order of zb_flat_scene's pointers.
+//   (reserved = wide_stack_need), then 14 sections, each = u64 byte count + payload padded to 16 bytes, in the order of
+//   zb_flat_scene's pointers (the 8-wide nodes last).
 namespace {
 template <class T> bool put(std::ofstream& f, const std::vector<T>& v) {
     const uint64_t bytes = uint64_t(v.size()) * sizeof(T);
@@ -136,7 +141,7 @@ extern "C" int zb_flat_scene_save(const zb_flat_scene* v, const char* path) {
     if (!v || !path) return fail_host(ZB_ERR_INVALID, "zb_flat_scene_save: NULL argument");
     std::ofstream f(path, std::ios::binary);
     if (!f) return fail_host(ZB_ERR_IO, std::string("cannot create ") + path);
-    const uint32_t hdr[5] = {v->abi_version, v->n_tlas_nodes, v->n_leaves, v->pad, 0u};
+    const uint32_t hdr[5] = {v->abi_version, v->n_tlas_nodes, v->n_leaves, v->pad, v->wide_stack_need};
     f.write("ZBFS", 4);
     f.write(reinterpret_cast<const char*>(hdr), sizeof(hdr));
     bool ok = put(f, span_of(v->nodes, v->n_nodes)) && put(f, span_of(v->items, v->n_items)) && put(f, span_of(v->cubes, v->n_cubes)) &&
@@ -144,7 +149,8 @@ extern "C" int zb_flat_scene_save(const zb_flat_scene* v, const char* path) {
               put(f, span_of(v->instances, v->n_instances)) && put(f, span_of(v->meshes, v->n_meshes)) &&
               put(f, span_of(v->media, v->n_media)) && put(f, span_of(v->materials, v->n_materials)) &&
               put(f, span_of(v->textures, v->n_textures)) && put(f, span_of(v->spheres_obj, uint64_t(v->n_spheres_obj) * 4)) &&
-              put(f, span_of(v->texels_u8, v->n_texels_u8 * 4)) && put(f, span_of(v->texels_f32, v->n_texels_f32 * 4));
+              put(f, span_of(v->texels_u8, v->n_texels_u8 * 4)) && put(f, span_of(v->texels_f32, v->n_texels_f32 * 4)) &&
+              put(f, span_of(v->wide_nodes, v->n_wide_nodes));
     f.close();
     if (!ok || !f) return fail_host(ZB_ERR_IO, std::string("short write to ") + path);
     return ZB_OK;
@@ -164,9 +170,10 @@ extern "C" int zb_flat_scene_load(const char* path, const zb_flat_scene** out) {
     fs->n_tlas_nodes = hdr[1];
     fs->n_leaves = hdr[2];
     fs->env_hdr_texture = hdr[3];
+    fs->wide_stack_need = hdr[4];
     bool ok = get(f, fs->nodes) && get(f, fs->items) && get(f, fs->cubes) && get(f, fs->tris) && get(f, fs->tri_normals) &&
               get(f, fs->instances) && get(f, fs->meshes) && get(f, fs->media) && get(f, fs->materials) && get(f, fs->textures) &&
-              get(f, fs->spheres_obj) && get(f, fs->texels_u8) && get(f, fs->texels_f32);
+              get(f, fs->spheres_obj) && get(f, fs->texels_u8) && get(f, fs->texels_f32) && get(f, fs->wide_nodes);
     if (!ok || fs->tris.size() != fs->tri_normals.size()) return fail_host(ZB_ERR_INVALID, std::string(path) + ": truncated or malformed flat scene");
     const zb_flat_scene* view = fs->finish();  // zb_scene_upload validates every index before anything is used
     std::lock_guard<std::mutex> lock(g_mu);

@@ -926,6 +926,7 @@ ZbTuning zbk_tuning_from_env() {
     t.wavefront = num("ZB_WAVEFRONT", 0) > 0;
     t.wf_slots = num("ZB_WF_SLOTS", 0);
     t.gather_p2p = int(num("ZB_GATHER_P2P", 1));
+    t.wide = int(num("ZB_WIDE", 1));
     return t;
 }
 

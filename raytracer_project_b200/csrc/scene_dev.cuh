@@ -19,6 +19,7 @@ struct SceneDev {
     const float4* spheres_obj;  // 1 x float4 per object-space sphere
     const uchar4* texels_u8;
     const float4* texels_f32;
+    const float4* wide;         // 5 x float4 per zb_wide_node (80 B); null: walk the binary tree (no wide tree, or tuning wide = 0)
     uint32_t n_nodes, n_items, n_media;
     uint32_t features;  // ZB_F_* bits the scene needs, set by zb_scene_upload
     // traversal-stack overflow events (trace.cuh): one u64 in the owning context's counter block, never null.  The

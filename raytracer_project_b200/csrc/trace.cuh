@@ -132,7 +132,7 @@ ZB_DEV bool hit_tri(float3 v0, float3 v1, float3 v2, float3 o, float3 d, float t
 
 struct InstanceHead {
     Affine w2o;
-    uint32_t geom_kind, geom_index, flags, node_root;
+    uint32_t geom_kind, geom_index, flags, node_root, wide_root;
 };
 ZB_DEV InstanceHead load_instance_head(const SceneDev& sc, uint32_t idx) {
     const float4* p = sc.instances + 8 * size_t(idx);
@@ -146,7 +146,7 @@ ZB_DEV InstanceHead load_instance_head(const SceneDev& sc, uint32_t idx) {
     h.geom_index = __float_as_uint(m.y);
     h.flags = __float_as_uint(m.z);
     h.node_root = __float_as_uint(m.w);
-    (void)m2;
+    h.wide_root = __float_as_uint(m2.x);
     return h;
 }
 
@@ -424,12 +424,192 @@ struct RayWalk {
     }
 };
 
+// ---------------------------------------------------------------------------------- 8-wide compressed tree
+// Traversal of the zb_wide_node tree (host/wide_bvh.hpp; Ylitie, Karras, Laine 2017): one visit = five 16-byte loads and
+// eight slab tests on 8-bit boxes.  A quantised coordinate q is turned into the float 1 + q 2^-15 by ONE byte permute
+// (q into mantissa bits 8..15 of 0x3F800000) and the slab distance t = (p + q 2^e - o) / d into ONE FFMA, f * A + C with
+// A = 2^(e+15) / d and C = (p - o) / d - A, both per node and axis.  The stack holds GROUPS, not nodes: (child base, hit
+// bits of the inner children in bits 24..31 | imask) or (primitive base, hit bits of up to 24 primitives); inner children
+// are taken highest bit first, which — their bit being 24 + (slot XOR ray octant) — is front to back.  Stack need per ray:
+// one group per level plus three for a dive into a mesh (zb_flat_scene::wide_stack_need <= ZB_WSTACK - 1, checked at upload).
+#define ZB_WSTACK 32
+#define ZB_WSTACK_CANARY 0xFFFFFFFEu
+#ifndef ZB_WIDE_ANY
+#ifdef ZB_EXPERIMENTS
+#define ZB_WIDE_ANY 1  // experiments build: kernels of every feature set carry the wide traversal (A/B on TLAS-only scenes)
+#else
+#define ZB_WIDE_ANY 0
+#endif
+#endif
+
+ZB_DEV uint32_t ray_octant(float3 d) { return (d.x >= 0.f ? 4u : 0u) | (d.y >= 0.f ? 2u : 0u) | (d.z >= 0.f ? 1u : 0u); }
+
+template <bool STATS, uint32_t F>
+ZB_DEV bool trace_wide(const SceneDev& sc, float3 o, float3 d, float tmin, float tmax, const MediumRng& rng, Hit& hit, Counters& cnt) {
+    uint2 stack[ZB_WSTACK];
+    int sp = 0;
+    stack[ZB_WSTACK - 1] = make_uint2(ZB_WSTACK_CANARY, ZB_WSTACK_CANARY);
+    cnt.rays++;
+    hit.t = tmax;
+    hit.item = 0xFFFFFFFFu;
+    hit.prim = 0;
+    float3 ro = o, rd = d;
+    RayBox rb;
+    rb.set(o, d);
+    uint32_t oct = ray_octant(d);
+    bool in_blas = false;
+    uint32_t blas_item = 0;
+    uint2 G = make_uint2(0u, 0x80000000u), T = make_uint2(0u, 0u);
+    for (;;) {
+        if (G.y & 0xFF000000u) {
+            // ---- take the nearest pending inner child of the group and visit it
+            const uint32_t bit = 31u - uint32_t(__clz(G.y));
+            G.y &= ~(1u << bit);
+            const uint32_t slot = (bit - 24u) ^ oct;
+            const uint32_t ni = G.x + uint32_t(__popc(G.y & 0xFFu & ((1u << slot) - 1u)));
+            if (G.y & 0xFF000000u) {
+                stack[sp] = G;
+                sp = min(sp + 1, ZB_WSTACK - 1);
+            }
+            const float4* np = sc.wide + 5 * size_t(ni);
+            const float4 n0 = __ldg(np), n1 = __ldg(np + 1), n2 = __ldg(np + 2), n3 = __ldg(np + 3), n4 = __ldg(np + 4);
+            if (STATS) cnt.nodes++;
+            const uint32_t ew = __float_as_uint(n0.w);
+            const float ax = __uint_as_float(((ew & 0xFFu) + 15u) << 23) * rb.inv.x;
+            const float ay = __uint_as_float((((ew >> 8) & 0xFFu) + 15u) << 23) * rb.inv.y;
+            const float az = __uint_as_float((((ew >> 16) & 0xFFu) + 15u) << 23) * rb.inv.z;
+            const float cx = fmaf(n0.x, rb.inv.x, -rb.ood.x) - ax, cy = fmaf(n0.y, rb.inv.y, -rb.ood.y) - ay,
+                        cz = fmaf(n0.z, rb.inv.z, -rb.ood.z) - az;
+            const bool xn = rb.inv.x < 0.f, yn = rb.inv.y < 0.f, zn = rb.inv.z < 0.f;
+            // words of the near / far planes per axis: lo planes are near for a positive direction
+            const uint32_t lox[2] = {__float_as_uint(n2.x), __float_as_uint(n2.y)}, loy[2] = {__float_as_uint(n2.z), __float_as_uint(n2.w)},
+                           loz[2] = {__float_as_uint(n3.x), __float_as_uint(n3.y)}, hix[2] = {__float_as_uint(n3.z), __float_as_uint(n3.w)},
+                           hiy[2] = {__float_as_uint(n4.x), __float_as_uint(n4.y)}, hiz[2] = {__float_as_uint(n4.z), __float_as_uint(n4.w)};
+            const uint32_t metaw[2] = {__float_as_uint(n1.z), __float_as_uint(n1.w)};
+            uint32_t mask = 0;
+#pragma unroll
+            for (int w = 0; w < 2; w++) {
+                const uint32_t nx = xn ? hix[w] : lox[w], fx = xn ? lox[w] : hix[w];
+                const uint32_t ny = yn ? hiy[w] : loy[w], fy = yn ? loy[w] : hiy[w];
+                const uint32_t nz = zn ? hiz[w] : loz[w], fz = zn ? loz[w] : hiz[w];
+#pragma unroll
+                for (int b = 0; b < 4; b++) {
+                    const uint32_t sel = 0x7604u | (uint32_t(b) << 4);
+                    const float tnx = fmaf(__uint_as_float(__byte_perm(nx, 0x3F800000u, sel)), ax, cx);
+                    const float tny = fmaf(__uint_as_float(__byte_perm(ny, 0x3F800000u, sel)), ay, cy);
+                    const float tnz = fmaf(__uint_as_float(__byte_perm(nz, 0x3F800000u, sel)), az, cz);
+                    const float tfx = fmaf(__uint_as_float(__byte_perm(fx, 0x3F800000u, sel)), ax, cx);
+                    const float tfy = fmaf(__uint_as_float(__byte_perm(fy, 0x3F800000u, sel)), ay, cy);
+                    const float tfz = fmaf(__uint_as_float(__byte_perm(fz, 0x3F800000u, sel)), az, cz);
+                    const float tn = fmaxf(max3(tnx, tny, tnz), tmin);
+                    const float tf = fminf(min3(tfx, tfy, tfz), hit.t) * ZB_BOX_INFLATE;
+                    const uint32_t m = (metaw[w] >> (8 * b)) & 0xFFu;
+                    uint32_t idx = m & 31u;
+                    idx ^= idx >= 24u ? oct : 0u;
+                    const uint32_t bits = ((1u << (m >> 5)) - 1u) << idx;
+                    if (tn <= tf) mask |= bits;
+                }
+            }
+            G = make_uint2(__float_as_uint(n1.x), (mask & 0xFF000000u) | (ew >> 24));
+            T = make_uint2(__float_as_uint(n1.y), mask & 0x00FFFFFFu);
+        } else {
+            T = G;  // a primitive group popped from the stack
+            G = make_uint2(0u, 0u);
+        }
+        // ---- the primitives of the group
+        while (T.y) {
+            const uint32_t j = uint32_t(__ffs(int(T.y))) - 1u;
+            T.y &= T.y - 1u;
+            const uint32_t i = T.x + j;
+            if (STATS) cnt.prims++;
+            float t;
+            if ((F & ZB_F_MESH) && in_blas) {
+                const float4* tp = sc.tris + 3 * size_t(i);
+                const float4 a = __ldg(tp), b = __ldg(tp + 1), c = __ldg(tp + 2);
+                if (hit_tri(f3(a), f3(b), f3(c), ro, rd, tmin, hit.t, t)) {
+                    hit.t = t;
+                    hit.item = blas_item;
+                    hit.prim = i;
+                }
+                continue;
+            }
+            const float4 g = __ldg(sc.items + 2 * size_t(i));
+            if (!(F & ZB_F_GEOM)) {
+                if (hit_sphere(g, o, d, tmin, hit.t, t)) { hit.t = t; hit.item = i; }
+                continue;
+            }
+            const float4 mf = __ldg(sc.items + 2 * size_t(i) + 1);
+            const uint32_t kind = __float_as_uint(mf.x) & 0xFFu, aux = __float_as_uint(mf.w);
+            if (kind == ZB_ITEM_SPHERE) {
+                if (hit_sphere(g, o, d, tmin, hit.t, t)) { hit.t = t; hit.item = i; }
+            } else if ((F & ZB_F_INST) && kind == ZB_ITEM_INSTANCE) {
+                const InstanceHead ih = load_instance_head(sc, aux);
+                if (STATS) cnt.insts++;
+                const float3 lo = xform_point(ih.w2o, o), ld = xform_vector(ih.w2o, d);
+                if ((F & ZB_F_MESH) && ih.geom_kind == ZB_GEOM_MESH) {
+                    // dive into the mesh: what is left of this level, the way back, then the BLAS root in object space
+                    if (G.y & 0xFF000000u) { stack[sp] = G; sp = min(sp + 1, ZB_WSTACK - 1); }
+                    if (T.y) { stack[sp] = T; sp = min(sp + 1, ZB_WSTACK - 1); }
+                    stack[sp] = make_uint2(0xFFFFFFFFu, 0u);
+                    sp = min(sp + 1, ZB_WSTACK - 1);
+                    in_blas = true;
+                    blas_item = i;
+                    ro = lo;
+                    rd = ld;
+                    rb.set(ro, rd);
+                    oct = ray_octant(rd);
+                    G = make_uint2(ih.wide_root, 0x80000000u);
+                    T = make_uint2(0u, 0u);
+                    break;
+                }
+                if (hit_simple_geom<F>(sc, ih.geom_kind, ih.geom_index, lo, ld, tmin, hit.t, t)) {
+                    hit.t = t;
+                    hit.item = i;
+                    hit.prim = ih.geom_index;
+                }
+            } else if ((F & ZB_F_CUBE) && kind == ZB_ITEM_CUBE) {
+                if (hit_cube(f3(__ldg(sc.cubes + 2 * size_t(aux))), o, d, tmin, hit.t, t)) { hit.t = t; hit.item = i; }
+            } else if ((F & ZB_F_TRI) && kind == ZB_ITEM_TRIANGLE) {
+                const float4* tp = sc.tris + 3 * size_t(aux);
+                if (hit_tri(f3(__ldg(tp)), f3(__ldg(tp + 1)), f3(__ldg(tp + 2)), o, d, tmin, hit.t, t)) {
+                    hit.t = t;
+                    hit.item = i;
+                    hit.prim = aux;
+                }
+            } else if ((F & ZB_F_MEDIA) && kind == ZB_ITEM_MEDIUM) {
+                if (hit_medium<F>(sc, aux, o, d, tmin, hit.t, rng, t)) { hit.t = t; hit.item = i; }
+            }
+        }
+        // ---- next group
+        if (!(G.y & 0xFF000000u)) {
+            bool done = false;
+            for (;;) {
+                if (sp == 0) { done = true; break; }
+                G = stack[--sp];
+                if (G.y != 0u) break;
+                // the way back out of a mesh: the world-space ray again
+                in_blas = false;
+                ro = o;
+                rd = d;
+                rb.set(o, d);
+                oct = ray_octant(d);
+            }
+            if (done) break;
+        }
+    }
+    if (stack[ZB_WSTACK - 1].x != ZB_WSTACK_CANARY) atomicAdd(sc.overflow, 1ull);
+    return hit.item != 0xFFFFFFFFu;
+}
+
 // Closest hit of one ray, run to completion.  "while-while" traversal (Aila & Laine 2009): every lane first descends
 // through inner nodes until it holds a leaf, then the warp runs the primitive tests together; this keeps more lanes
 // on the same instruction than one loop that alternates between a node step and a leaf step.
 template <bool STATS, uint32_t F = ZB_F_ALL>
 ZB_DEV bool trace(const SceneDev& sc, float3 o, float3 d, float tmin, float tmax, const MediumRng& rng, Hit& hit,
                   Counters& cnt) {
+    if constexpr ((F & ZB_F_MESH) != 0 || ZB_WIDE_ANY) {
+        if (sc.wide) return trace_wide<STATS, F>(sc, o, d, tmin, tmax, rng, hit, cnt);  // warp-uniform: a launch parameter
+    }
     int stack[ZB_STACK];
     cnt.rays++;
     RayWalk w;

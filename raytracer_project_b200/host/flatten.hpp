@@ -12,6 +12,7 @@
 #include <unordered_map>
 
 #include "bvh_build.hpp"
+#include "wide_bvh.hpp"
 #include "zenith/environment.hpp"
 #include "zenith/model.hpp"
 #include "zenith/scene.hpp"
@@ -20,6 +21,8 @@ namespace zenith {
 
 struct flat_scene {
     std::vector<zb_bvh_node> nodes;
+    std::vector<zb_wide_node> wide_nodes;
+    uint32_t wide_stack_need = 0;
     std::vector<zb_item> items;
     std::vector<zb_cube> cubes;
     std::vector<zb_tri> tris;
@@ -66,6 +69,9 @@ struct flat_scene {
         view.texels_f32 = texels_f32.data();
         view.n_leaves = n_leaves;
         view.pad = env_hdr_texture;
+        view.n_wide_nodes = uint32_t(wide_nodes.size());
+        view.wide_stack_need = wide_stack_need;
+        view.wide_nodes = wide_nodes.empty() ? nullptr : wide_nodes.data();
         return &view;
     }
 };
@@ -76,6 +82,10 @@ public:
     // true: leave every mesh BLAS to the device builder (csrc/lbvh.cu): triangles are emitted in face
     // order, the mesh carries node_count == 0 and zb_scene_upload builds a linear BVH for it on the GPU
     bool gpu_blas = false;
+    // 8-wide compressed tree beside the binary one (host/wide_bvh.hpp): built for scenes with host-built mesh BLASes — the
+    // memory-latency-bound regime it pays in — or for every scene when wide_all is set (A/B runs).  -1 = never.
+    int wide = 1;
+    bool wide_all = false;
 
     std::unique_ptr<flat_scene> run(const hittable& world, const EnvironmentSettings* env = nullptr) {
         out = std::make_unique<flat_scene>();
@@ -91,6 +101,20 @@ public:
         // an exact sweep SAH instead of 16 bins changed nothing (profiles/r01_pq.txt)
         b.isect_cost = 1.5;
         b.build(item_boxes, tlas_leaf, 0, tl, order, ZB_MAX_TLAS_DEPTH);
+        std::vector<zb_wide_node> tlw;
+        int tlas_wide_depth = 0;
+        const bool want_wide = wide >= 0 && tlas_leaf <= 4 && (wide_all || (!out->meshes.empty() && wide > 0));
+        if (want_wide) {
+            std::vector<uint32_t> perm;
+            wide_builder wb;
+            if (wb.build(tl, 0, uint32_t(order.size()), tlw, perm, tlas_wide_depth)) {
+                std::vector<uint32_t> o2(order.size());
+                for (size_t i = 0; i < order.size(); i++) o2[i] = order[perm[i]];
+                order.swap(o2);
+            } else {
+                tlw.clear();
+            }
+        }
         std::vector<zb_item> sorted(order.size());
         for (size_t i = 0; i < order.size(); i++) sorted[i] = out->items[order[i]];
         out->items.swap(sorted);
@@ -109,6 +133,27 @@ public:
         }
         for (auto& inst : out->instances)
             if (inst.geom_kind == ZB_GEOM_MESH) inst.pad[0] = out->meshes[inst.geom_index].node_root;
+        // the wide trees: TLAS first (root 0), every mesh's BLAS after it; roots into zb_instance::pad[1]
+        if (!tlw.empty()) {
+            std::vector<zb_wide_node> allw = tlw;
+            std::vector<uint32_t> wroot(out->meshes.size(), 0);
+            bool complete = true;
+            for (size_t m = 0; m < out->meshes.size(); m++) {
+                if (blas_wide[m].empty()) { complete = false; break; }
+                wroot[m] = uint32_t(allw.size());
+                for (zb_wide_node nd : blas_wide[m]) {
+                    nd.child_base += wroot[m];
+                    allw.push_back(nd);
+                }
+            }
+            if (complete) {
+                for (auto& inst : out->instances)
+                    if (inst.geom_kind == ZB_GEOM_MESH) inst.pad[1] = wroot[inst.geom_index];
+                out->wide_nodes.swap(allw);
+                out->wide_stack_need = uint32_t(tlas_wide_depth + blas_wide_depth + 4);
+            }
+        }
+        blas_wide.clear();
         out->nodes.swap(all);
         out->finish();
         blas_nodes.clear();
@@ -119,6 +164,8 @@ private:
     std::unique_ptr<flat_scene> out;
     std::vector<build_box> item_boxes;
     std::vector<std::vector<zb_bvh_node>> blas_nodes;
+    std::vector<std::vector<zb_wide_node>> blas_wide;
+    int blas_wide_depth = 0;
     std::unordered_map<const material*, uint32_t> mat_ids;
     std::unordered_map<const texture*, uint32_t> tex_ids;
     std::unordered_map<const hittable*, uint32_t> mesh_ids, sphere_obj_ids, cube_ids;
@@ -388,8 +435,22 @@ private:
                 bvh_builder b;
                 std::vector<uint32_t> order;
                 b.build(boxes, blas_leaf, first, nd, order, ZB_MAX_BLAS_DEPTH);
-                for (uint32_t slot : order) push_tri(m.tris[slot].v, m.tris[slot].n, slot);
+                std::vector<zb_wide_node> wn;
+                std::vector<uint32_t> perm;
+                int wdepth = 0;
+                wide_builder wb;
+                if (wide >= 0 && blas_leaf <= 4 && wb.build(nd, first, uint32_t(order.size()), wn, perm, wdepth)) {
+                    // triangles go out in the wide tree's order (both trees' leaves were remapped to it)
+                    for (uint32_t k : perm) push_tri(m.tris[order[k]].v, m.tris[order[k]].n, order[k]);
+                    blas_wide_depth = std::max(blas_wide_depth, wdepth);
+                } else {
+                    if (wide >= 0) wide = -1;  // one mesh without a wide tree: the scene ships none
+                    wn.clear();
+                    for (uint32_t slot : order) push_tri(m.tris[slot].v, m.tris[slot].n, slot);
+                }
+                blas_wide.push_back(std::move(wn));
             }
+            if (gpu_blas) { blas_wide.emplace_back(); wide = -1; }
             zb_mesh zm{0, 0, first, uint32_t(m.tris.size())};
             out->meshes.push_back(zm);
             blas_nodes.push_back(std::move(nd));

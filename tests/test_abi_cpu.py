@@ -19,7 +19,7 @@ def test_header_symbols_all_exported(lib):
     assert declared == set(_lib.SYMBOLS), declared ^ set(_lib.SYMBOLS)
     for name in declared:
         assert hasattr(lib, name), name
-    assert lib.zb_abi_version() == 3
+    assert lib.zb_abi_version() == 4
 
 
 def test_struct_sizes_match_header():
