@@ -334,15 +334,23 @@ def ours(args):
     e2e_ms, e2e_parts = [], []
     e2e_warm = args.warmup if name != "c5" else 0
     n_e2e = args.steps if name != "c5" else 1
+
+    def rank_barrier():
+        """barrier + device synchronise on both sides of an e2e step: the group's own host barrier (zb_group_barrier:
+        stream synchronise, then a shared-memory barrier over the ranks) — every rank's GPU is idle when it returns"""
+        torch.cuda.synchronize()
+        ctx.group_barrier()
+
     for k in range(e2e_warm + n_e2e):
         barrier()
+        rank_barrier()
         t0 = time.perf_counter()
         sc2 = ctx.upload(flat)  # H2D of the flattened scene
         t_up = time.perf_counter()
         sc2.render(cfg, seed=1, beauty_out=host_rgb, partition=args.partition, samples_per_launch=spl)  # blocking, collective
         t_render = time.perf_counter()
         sc2.close()
-        barrier()
+        rank_barrier()
         t1 = time.perf_counter()
         if k >= e2e_warm:
             e2e_ms.append((t1 - t0) * 1e3)

@@ -187,7 +187,7 @@ typedef struct zb_flat_scene {
     const float* texels_f32;   /* RGBA32F */
     uint32_t n_leaves;         /* number of leaf ids handed out */
     uint32_t pad;
-    /* optional 8-wide tree over the same primitives (n_wide_nodes == 0: none; the renderer then walks the binary tree):
+    /* optional 8-wide tree over the same primitives (n_wide_nodes == 0, the default: none; the renderer walks the binary tree):
      * TLAS root = wide_nodes[0], BLAS roots in zb_instance::pad[1].  wide_stack_need = traversal-stack entries a ray can
      * hold: deepest TLAS path + deepest BLAS path + 4. */
     uint32_t n_wide_nodes;
@@ -299,6 +299,8 @@ int zb_context_device_count(zb_context* ctx);
 typedef struct zb_group_handle { unsigned char opaque[256]; } zb_group_handle;
 int zb_group_export(zb_context* ctx, size_t max_pixels, zb_group_handle* out);
 int zb_group_join(zb_context* ctx, int rank, int n_ranks, const zb_group_handle* all, const char* shm_name);
+/* stream synchronise + barrier over the ranks of the group (shared-memory host barrier; plain stream sync elsewhere) */
+int zb_group_barrier(zb_context* ctx);
 int zb_group_leave(zb_context* ctx);
 int zb_context_set_stream(zb_context* ctx, void* stream);
 int zb_context_destroy(zb_context* ctx);
@@ -486,8 +488,9 @@ int zb_flat_scene_from_zscene_text(const char* text, size_t len, const zb_flat_s
  * let zb_scene_upload build linear BVHs on the device (csrc/lbvh.cu): time-to-first-pixel for multi-million-triangle
  * meshes drops from seconds to milliseconds, at a lower tree quality.  Exactly one of path / text is given. */
 #define ZB_FLATTEN_GPU_BLAS 1u
-#define ZB_FLATTEN_WIDE_ALL 2u /* also build the 8-wide tree for scenes without meshes (A/B measurements) */
-#define ZB_FLATTEN_NO_WIDE 4u  /* never build the 8-wide tree */
+#define ZB_FLATTEN_WIDE 2u     /* also build the 8-wide compressed tree (zb_wide_node) for scenes with host-built mesh BLASes.
+                                  Off by default: measured slower than the binary tree (profiles/r02_wide_bvh.txt) */
+#define ZB_FLATTEN_WIDE_ALL 4u /* ... and for scenes without meshes too (A/B measurements) */
 int zb_flat_scene_from_zscene_ex(const char* path, const char* text, size_t len, uint32_t flags, const zb_flat_scene** out);
 /* Scene features (SceneDev::features; template parameter F of the render kernels, csrc/trace.cuh, shade.cuh, kernels.cu).
  * The render kernel is compiled for several feature sets: code for item kinds, textures and environments a scene does

@@ -120,6 +120,7 @@ SYMBOLS = {
     "zb_context_device_count": (C.c_int, [C.c_void_p]),
     "zb_group_export": (C.c_int, [C.c_void_p, C.c_size_t, C.POINTER(GroupHandle)]),
     "zb_group_join": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.POINTER(GroupHandle), C.c_char_p]),
+    "zb_group_barrier": (C.c_int, [C.c_void_p]),
     "zb_group_leave": (C.c_int, [C.c_void_p]),
     "zb_context_set_stream": (C.c_int, [C.c_void_p, C.c_void_p]),
     "zb_context_destroy": (C.c_int, [C.c_void_p]),

@@ -15,15 +15,17 @@ from ._lib import Camera, Environment, FlatScene, Outputs, RenderOpts, Stats, ch
 from .scenes import RenderConfig
 
 
-def flatten_zscene(text: str | None = None, path: str | None = None, gpu_blas: bool = False):
+def flatten_zscene(text: str | None = None, path: str | None = None, gpu_blas: bool = False, wide: int = 0):
     """zscene text/file -> host scene API -> flatten(); returns a ctypes pointer to zb_flat_scene.
-    gpu_blas: leave the mesh BLAS builds to the device (linear BVH, csrc/lbvh.cu) at zb_scene_upload."""
+    gpu_blas: leave the mesh BLAS builds to the device (linear BVH, csrc/lbvh.cu) at zb_scene_upload.
+    wide: 1 = also build the 8-wide compressed tree for scenes with meshes, 2 = for every scene (A/B; off by default)."""
     lib = _lib.load()
     out = C.POINTER(FlatScene)()
-    if gpu_blas:
+    if gpu_blas or wide:
         data = text.encode() if text is not None else None
+        flags = (1 if gpu_blas else 0) | (2 if wide == 1 else 0) | (4 if wide >= 2 else 0)
         check(lib.zb_flat_scene_from_zscene_ex(path.encode() if path is not None else None, data, len(data) if data else 0,
-                                               1, C.byref(out)))
+                                               flags, C.byref(out)))
     elif path is not None:
         check(lib.zb_flat_scene_from_zscene(path.encode(), C.byref(out)))
     else:
@@ -264,6 +266,10 @@ class Context:
         for i, b in enumerate(handles):
             C.memmove(C.byref(arr[i]), b, 256)
         check(self.lib.zb_group_join(self.h, rank, len(handles), arr, shm_name.encode()))
+
+    def group_barrier(self):
+        """zb_group_barrier: synchronise this context's stream, then wait for the other ranks of the process group."""
+        check(self.lib.zb_group_barrier(self.h))
 
     def group_leave(self):
         check(self.lib.zb_group_leave(self.h))

@@ -352,6 +352,16 @@ extern "C" int zb_group_join(zb_context* ctx, int rank, int n_ranks, const zb_gr
     return host_barrier(G);
 }
 
+// Synchronise the context's stream, then meet the other ranks of a process group (host barrier in shared memory: a few
+// microseconds, against ~0.1 ms for a collective-library barrier).  On any other context: the stream synchronisation only.
+extern "C" int zb_group_barrier(zb_context* ctx) {
+    if (!ctx) return fail(ZB_ERR_INVALID, "zb_group_barrier: ctx is NULL");
+    ZB_CUDA(cudaSetDevice(ctx->device));
+    ZB_CUDA(cudaStreamSynchronize(ctx->stream));
+    if (ctx->group && ctx->group->multi_process && ctx->group->n > 1) return host_barrier(ctx->group);
+    return ZB_OK;
+}
+
 extern "C" int zb_group_leave(zb_context* ctx) {
     if (!ctx || !ctx->group) return ZB_OK;
     cudaSetDevice(ctx->device);

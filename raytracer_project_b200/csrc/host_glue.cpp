@@ -37,10 +37,12 @@ int load(std::istream& in, const std::string& base_dir, const zb_flat_scene** ou
         std::shared_ptr<hittable> world = ld.build_world();
         flattener fl;
         fl.gpu_blas = (flags & ZB_FLATTEN_GPU_BLAS) != 0;
-        fl.wide_all = (flags & ZB_FLATTEN_WIDE_ALL) != 0;
-        if (flags & ZB_FLATTEN_NO_WIDE) fl.wide = -1;
-        if (const char* e = std::getenv("ZB_WIDE_ALL")) fl.wide_all = std::atoi(e) != 0;  // A/B runs: 8-wide tree for TLAS-only scenes too
-        if (const char* e = std::getenv("ZB_NO_WIDE")) { if (std::atoi(e) != 0) fl.wide = -1; }
+        if (flags & ZB_FLATTEN_WIDE) fl.wide = 1;
+        if (flags & ZB_FLATTEN_WIDE_ALL) { fl.wide = 1; fl.wide_all = true; }
+        if (const char* e = std::getenv("ZB_WIDE_BUILD")) {  // A/B runs: 1 = for scenes with meshes, 2 = for every scene
+            fl.wide = std::atoi(e) > 0 ? 1 : fl.wide;
+            fl.wide_all = std::atoi(e) > 1;
+        }
         if (const char* e = std::getenv("ZB_TLAS_LEAF")) fl.tlas_leaf = std::max(1, std::min(8, std::atoi(e)));  // tuning knobs
         if (const char* e = std::getenv("ZB_BLAS_LEAF")) fl.blas_leaf = std::max(1, std::min(8, std::atoi(e)));
         EnvironmentSettings env;

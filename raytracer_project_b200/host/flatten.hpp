@@ -82,9 +82,10 @@ public:
     // true: leave every mesh BLAS to the device builder (csrc/lbvh.cu): triangles are emitted in face
     // order, the mesh carries node_count == 0 and zb_scene_upload builds a linear BVH for it on the GPU
     bool gpu_blas = false;
-    // 8-wide compressed tree beside the binary one (host/wide_bvh.hpp): built for scenes with host-built mesh BLASes — the
-    // memory-latency-bound regime it pays in — or for every scene when wide_all is set (A/B runs).  -1 = never.
-    int wide = 1;
+    // 8-wide compressed tree beside the binary one (host/wide_bvh.hpp).  OFF by default: measured 2.2x slower than the
+    // binary tree on the 1 M and 10 M triangle configs (profiles/r02_wide_bvh.txt: these kernels are issue-bound, not
+    // DRAM-bound).  1 = build it for scenes with host-built mesh BLASes, wide_all = for every scene (A/B runs), -1 = never.
+    int wide = 0;
     bool wide_all = false;
 
     std::unique_ptr<flat_scene> run(const hittable& world, const EnvironmentSettings* env = nullptr) {

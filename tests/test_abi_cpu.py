@@ -351,3 +351,74 @@ int main() {{
     out = subprocess.run(["./t"], cwd=tmp_path, capture_output=True, text=True, check=True).stdout.split()
     n, w, h, emissive = (int(x) for x in out)
     assert n >= 33 and (w, h) == (280, 280) and emissive >= 7, out
+
+
+WIDE_NODE = np.dtype([("p", "f4", 3), ("e", "u1", 3), ("imask", "u1"), ("child_base", "u4"), ("prim_base", "u4"), ("meta", "u1", 8),
+                      ("qlo", "u1", (3, 8)), ("qhi", "u1", (3, 8))])
+
+
+def test_wide_tree_covers_every_primitive_conservatively(tmp_path):
+    """The 8-wide compressed tree of a mesh scene (host/wide_bvh.hpp): 80-byte nodes; every TLAS item and every triangle is
+    referenced by exactly one leaf child; a child's dequantised box contains the triangles (or child boxes) below it; inner
+    children follow their parent and sit in slot order; the binary tree's leaves address the same (re-ordered) primitives."""
+    assert WIDE_NODE.itemsize == 80
+    txt, cfg, files = scenes.mesh(width=64, height=36, spp=1, grid=40, knots=3, shipped=True)
+    flat = api.flatten_zscene(path=scenes.materialize(str(tmp_path), txt, cfg, files), wide=1)
+    f = flat.contents
+    assert f.n_wide_nodes > 0 and 0 < f.wide_stack_need <= 31
+    wide = np.frombuffer(C.string_at(f.wide_nodes, f.n_wide_nodes * 80), WIDE_NODE)
+    tris = np.ctypeslib.as_array(C.cast(f.tris, C.POINTER(C.c_float)), (f.n_tris, 3, 4))[:, :, :3].astype(np.float64)
+    inst = np.ctypeslib.as_array(C.cast(f.instances, C.POINTER(C.c_uint32)), (f.n_instances, 32))
+    seen_items, seen_tris = np.zeros(f.n_items, int), np.zeros(f.n_tris, int)
+
+    def walk(ni, in_blas, depth=1):
+        """returns the TRUE bounds of the triangles below node ni (a child's own quantised boxes may stick out of the box its
+        parent holds for it — both contain the geometry, which is what closest hits need)"""
+        n = wide[ni]
+        scale = np.ldexp(1.0, n["e"].astype(int) - 127)
+        lo_all, hi_all = [np.full(3, np.inf)], [np.full(3, -np.inf)]
+        inner = 0
+        for s in range(8):
+            cnt, idx = int(n["meta"][s]) >> 5, int(n["meta"][s]) & 31
+            if cnt == 0:
+                continue
+            lo = n["p"].astype(np.float64) + n["qlo"][:, s] * scale
+            hi = n["p"].astype(np.float64) + n["qhi"][:, s] * scale
+            if idx >= 24:
+                assert idx == 24 + s and (int(n["imask"]) >> s) & 1
+                child = int(n["child_base"]) + bin(int(n["imask"]) & ((1 << s) - 1)).count("1")
+                assert child > ni
+                clo, chi = walk(child, in_blas, depth + 1)
+                if in_blas:
+                    assert np.all(lo <= clo + 1e-9) and np.all(hi >= chi - 1e-9), (ni, s)
+                inner += 1
+            else:
+                clo, chi = np.full(3, np.inf), np.full(3, -np.inf)
+                for j in range(cnt):
+                    prim = int(n["prim_base"]) + idx + j
+                    if in_blas:
+                        seen_tris[prim] += 1
+                        clo, chi = np.minimum(clo, tris[prim].min(0)), np.maximum(chi, tris[prim].max(0))
+                    else:
+                        seen_items[prim] += 1
+                if in_blas:
+                    assert np.all(lo <= clo + 1e-9) and np.all(hi >= chi - 1e-9), (ni, s)
+            lo_all.append(clo)
+            hi_all.append(chi)
+        assert inner == bin(int(n["imask"])).count("1")
+        return np.min(lo_all, 0), np.max(hi_all, 0)
+
+    walk(0, False)
+    for root in sorted({int(r[28]) for r in inst if r[24] == 2}):  # zb_instance: geom_kind == MESH -> pad[1]
+        walk(root, True)
+    assert np.all(seen_items == 1) and np.all(seen_tris == 1)
+    # the binary tree addresses the same primitive order: its leaves still cover every triangle once
+    nodes = np.ctypeslib.as_array(C.cast(f.nodes, C.POINTER(C.c_int32)), (f.n_nodes, 16))
+    cover = np.zeros(f.n_tris, int)
+    for n in range(f.n_tlas_nodes, f.n_nodes):
+        for c in nodes[n, 12:14]:
+            if c < 0 and c != -2**31:
+                code = (~int(c)) & 0xFFFFFFFF
+                cover[(code >> 3):(code >> 3) + (code & 7) + 1] += 1
+    assert np.all(cover == 1)
+    api.free_flat(flat)

@@ -772,3 +772,42 @@ def test_path_queue_kernel_equals_tile_kernel(name, gpu_ctx, tmp_path, weekend_s
     for r in range(3):
         assert np.array_equal(a_tiles[r], b_tiles[r]), r
     assert np.allclose(b, c, rtol=2e-6, atol=1e-7)
+
+
+# ------------------------------------------------------------------ 8-wide compressed tree (host/wide_bvh.hpp, trace_wide)
+@pytest.mark.parametrize("name", ["mesh", "models", "exterior"])
+def test_wide_tree_traversal_equals_binary_tree(name, gpu_ctx, tmp_path):
+    """Closest hits do not depend on the tree: primary ids, hit distances and rendered frames through the 8-wide compressed
+    tree (an opt-in: measured slower, profiles/r02_wide_bvh.txt) equal those through the binary tree (wide = 0), except where
+    two primitives are hit at the same t (shared triangle edges: the traversal order decides the tie).  `exterior` has no
+    mesh and therefore no wide tree: both settings run the same code."""
+    gen, kw, wh, _, ids_kw = GOLDEN_SCENES[name]
+    txt, cfg, files = getattr(scenes, gen)(width=wh[0], height=wh[1], spp=8, **{**kw, **ids_kw})
+    flat = api.flatten_zscene(path=scenes.materialize(str(tmp_path), txt, cfg, files), wide=1)
+    assert (flat.contents.n_wide_nodes > 0) == (name != "exterior")
+    sc = gpu_ctx.upload(flat)
+    api.free_flat(flat)
+    try:
+        gpu_ctx.set_tuning("wide", 0)
+        leaf0, prim0, t0 = sc.primary_ids(cfg)
+        img0 = sc.render(cfg, seed=3)["beauty"]
+        st0 = sc.render(cfg, seed=3, stats=True) and gpu_ctx.stats()
+        gpu_ctx.set_tuning("wide", 1)
+        leaf1, prim1, t1 = sc.primary_ids(cfg)
+        img1 = sc.render(cfg, seed=3)["beauty"]
+        st1 = sc.render(cfg, seed=3, stats=True) and gpu_ctx.stats()
+    finally:
+        gpu_ctx.set_tuning("wide", 1)
+        sc.close()
+    assert np.array_equal(leaf0, leaf1)
+    assert np.array_equal(t0, t1)
+    same = prim0 == prim1
+    print(f"{name}: face ids equal on {same.mean() * 100:.4f} %; node visits / ray {st0['node_visits'] / st0['rays']:.2f} (binary) "
+          f"-> {st1['node_visits'] / st1['rays']:.2f} (8-wide); primitive tests / ray {st0['prim_tests'] / st0['rays']:.2f} -> {st1['prim_tests'] / st1['rays']:.2f}")
+    assert same.mean() > 0.999
+    assert st0["stack_overflows"] == 0 and st1["stack_overflows"] == 0
+    close = np.isclose(img0, img1, rtol=1e-5, atol=1e-6)
+    assert close.mean() > 0.995, close.mean()  # an edge tie can pick the neighbouring facet's normal for a path
+    assert abs(img0.mean() - img1.mean()) < 2e-3 * img0.mean()
+    if name != "exterior":
+        assert st1["node_visits"] < 0.8 * st0["node_visits"]
