@@ -27,6 +27,155 @@ ZB_DEV void fix_add(unsigned long long* slot, float v) {
 }
 ZB_DEV float fix_get(unsigned long long v) { return float(double((long long)v) * ZB_FIX_INV); }
 
+// ---------------------------------------------------------------------------------------------------------------
+// Pieces shared by every render kernel (one copy each; all force-inlined).
+
+// K1 raygen: get_ray (camera.hpp:784-794), sample_square (:817), defocus disk (:822) for (pixel, sample), from the Philox
+// draw (pixel, s, bounce 0, stream 0) — so every kernel that regenerates a camera ray gets the same one.
+ZB_DEV void camera_ray(const RenderParams& P, const Philox& ph, int px, int py, uint32_t pixel, uint32_t s, float3& o, float3& d) {
+    const uint4 r0 = ph(pixel, s, 0u, 0u);
+    d = P.cam.pix00_rel + (float(px) + u01(r0.x) - 0.5f) * P.cam.du + (float(py) + u01(r0.y) - 0.5f) * P.cam.dv;
+    o = P.cam.center;
+    if (P.cam.defocus) {
+        float rr = sqrt_fast(u01(r0.z)), sn, cs;
+        sincos_turn(u01(r0.w), &sn, &cs);
+        const float3 off = (rr * cs) * P.cam.disk_u + (rr * sn) * P.cam.disk_v;
+        o += off;
+        d = d - off;
+    }
+}
+
+// Path index g of a launch -> pixel and sample: tile, 8x4 sub-tile, pixel-major inside the sub-tile, sample (the order every
+// kernel takes paths in).  Exact division of a 32-bit number by n: high word of x * ceil(2^64 / n) (error < 2^-32 of a
+// quotient step); the two reciprocals cost one 64-bit division each per persistent thread instead of three 32-bit
+// divisions per path.  Returns false for a pixel outside the image (ragged tile edge).
+struct PathDecoder {
+    uint32_t n_s, tiles_x;
+    unsigned long long m_ns, m_tx;
+    ZB_DEV void init(const RenderParams& P) {
+        n_s = uint32_t(P.sample_end - P.sample_begin);
+        tiles_x = uint32_t(P.tiles_x);
+        m_ns = n_s > 1u ? ~0ull / n_s + 1ull : 0ull;
+        m_tx = tiles_x > 1u ? ~0ull / tiles_x + 1ull : 0ull;
+    }
+    ZB_DEV bool decode(const RenderParams& P, unsigned long long g, unsigned long long total, int& px, int& py, uint32_t& s) const {
+        // one division: q = g / n_s numbers the (sub-tile, pixel) pairs, 32 per sub-tile; in 32 bits whenever the
+        // launch has fewer than 2^32 paths (a 64-bit division is a ~80-instruction routine)
+        uint32_t q, sr;
+        if (total <= 0xFFFFFFFFull) {
+            const uint32_t g32 = uint32_t(g);
+            q = n_s > 1u ? uint32_t(__umul64hi(g32, m_ns)) : g32;
+            sr = g32 - q * n_s;
+        } else {
+            const unsigned long long q64 = g / n_s;
+            q = uint32_t(q64);
+            sr = uint32_t(g - q64 * n_s);
+        }
+        const uint32_t u = q >> 5, p = q & 31u;
+        const int tile = int(u >> 2) * P.tile_ranks + P.tile_rank, w = int(u & 3u);
+        const int ty = tiles_x > 1u ? int(__umul64hi(uint32_t(tile), m_tx)) : tile, tx = tile - ty * int(tiles_x);
+        px = tx * ZB_TILE_W + (w % (ZB_TILE_W / 8)) * 8 + int(p & 7u);
+        py = ty * ZB_TILE_H + (w / (ZB_TILE_W / 8)) * 4 + int(p >> 3);
+        s = uint32_t(P.sample_begin) + sr;
+        return px < P.cam.width && py < P.cam.height && ty < P.tiles_y;
+    }
+};
+
+// State of one path between segments.
+struct PathState {
+    int seg;
+    uint32_t pixel, s;
+    float3 o, d, L, beta;
+    float3 first_atten;  // LIGHT: attenuation of the primary scatter (camera.hpp:512, :515)
+    int light_class;     // LIGHT: 1 reflection, 2 refraction, 0 neither
+    ZB_DEV void start(uint32_t pixel_, uint32_t s_) {
+        pixel = pixel_;
+        s = s_;
+        seg = 0;
+        L = f3(0, 0, 0);
+        beta = f3(1, 1, 1);
+    }
+};
+
+// K3 shade: one segment of ray_color (camera.hpp:928-1004) after the closest-hit query of (st.o, st.d) returned `hit`;
+// returns true when the path is finished (st.L then holds its radiance).  LIGHT = the reflection / refraction passes
+// (camera.hpp:492-517): at segment 0 a second scatter of the primary hit decides the class of the sample; a primary miss
+// or a sample of neither class ends at once.  `aov(sf, hit_something)` is called for the primary segment of beauty paths.
+template <bool LIGHT, uint32_t F, class Aov>
+ZB_DEV bool shade_segment(const RenderParams& P, const Philox& ph, const Hit& hit, PathState& st, Aov&& aov) {
+    if (LIGHT && st.seg == 0) {
+        st.light_class = 0;
+        if (hit.item == 0xFFFFFFFFu) return true;
+        Surface sf;
+        make_surface<F>(P.sc, hit, st.o, st.d, sf);
+        const uint4 rb = ph(st.pixel, st.s, 1u, 0u);
+        float3 no, nd;
+        st.first_atten = f3(1, 1, 1);
+        if (!material_scatter<F>(P.sc, sf, st.d, f3(u01(rb.x), u01(rb.y), u01(rb.z)), st.first_atten, no, nd)) return true;
+        const float3 ud = unit_vector(st.d), un = unit_vector(sf.n);
+        const float3 mirror = fma3(-2.0f * dot(ud, un), un, ud);
+        if (dot(unit_vector(nd), mirror) > 0.9f) st.light_class = 1;
+        else if (dot(nd, sf.n) < 0.f) st.light_class = 2;
+        if (!st.light_class) return true;  // the sample lands in neither buffer: skip its path
+        st.o = no;
+        st.d = nd;
+        st.seg = 1;
+        return P.max_depth <= 1;
+    }
+    if (hit.item == 0xFFFFFFFFu) {
+        st.L += st.beta * ((F & ZB_F_ENV) ? background(P.sc, P.env, st.d) : P.env.background);
+        if (!LIGHT && st.seg == 0) aov(static_cast<const Surface*>(nullptr), 0.f);
+        return true;
+    }
+    Surface sf;
+    make_surface<F>(P.sc, hit, st.o, st.d, sf);
+    if (!LIGHT && st.seg == 0) aov(&sf, hit.t);
+    st.L += st.beta * material_emitted<F>(P.sc, sf);
+    const uint4 rb = ph(st.pixel, st.s, uint32_t(st.seg + 1), 0u);
+    float3 atten = f3(1, 1, 1), no, nd;
+    if (!material_scatter<F>(P.sc, sf, st.d, f3(u01(rb.x), u01(rb.y), u01(rb.z)), atten, no, nd)) return true;
+    st.beta *= atten;
+    st.o = no;
+    st.d = nd;
+    bool done = false;
+    // ray_color's loop index is seg - 1; its `i > 10` rules start at seg 12 (camera.hpp:968-983)
+    if (st.seg >= 12) {
+        const float pr = fminf(fmaxf(max3(st.beta.x, st.beta.y, st.beta.z), 0.05f), 0.95f);
+        if (dot(st.beta, st.beta) < 1e-8f || u01(rb.w) > pr) done = true;
+        st.beta *= 1.0f / pr;
+    }
+    if (++st.seg >= P.max_depth) done = true;  // hard stop keeps the light gathered so far
+    return done;
+}
+
+// radiance of a finished LIGHT path: luma clamp 0.2126 |c| <= 2 on the vector length (camera.hpp:500), then the primary attenuation
+ZB_DEV float3 light_pass_value(const PathState& st) {
+    float3 L = st.L;
+    const float luma = 0.2126f * length(L);
+    if (luma > 2.0f) L *= 2.0f / luma;
+    return st.first_atten * L;
+}
+
+// first-hit AOV values (K8, camera.hpp:464-488, :518-526): albedo rgb, view-space normal xyz, 1 - clamp(t / z_max); sf == null: miss
+template <uint32_t F, class Add>
+ZB_DEV void aov_values(const RenderParams& P, const Surface* sf, float t, Add&& add) {
+    if (!sf) {
+        if (P.use_normal) { add(3, 0.5f); add(4, 0.5f); add(5, 1.0f); }
+        return;
+    }
+    if (P.use_albedo) {
+        const float3 a = material_get_albedo<F>(P.sc, *sf);
+        add(0, a.x); add(1, a.y); add(2, a.z);
+    }
+    if (P.use_normal) {
+        const float3 n = unit_vector(sf->n);
+        add(3, (dot(n, P.cam.u) + 1.f) * 0.5f);
+        add(4, (dot(n, P.cam.v) + 1.f) * 0.5f);
+        add(5, (dot(n, P.cam.w) + 1.f) * 0.5f);
+    }
+    if (P.use_z) add(6, 1.0f - clamp01(t * P.inv_z_max));
+}
+
 // Work decomposition.  A block renders a 16x8 pixel tile (tiles are dealt to ranks round-robin for the
 // tile-stripe partition); each of its four warps owns an 8x4 sub-tile and works through the
 // 32 x n_samples paths of that sub-tile as a queue: a lane whose path has ended takes the next
@@ -72,11 +221,13 @@ __global__ void __launch_bounds__(ZB_BLOCK_THREADS, ZB_MIN_BLOCKS) k_render(cons
     uint32_t paths = 0;
 
     // path state of this lane
-    int p = 0, seg = 0;
-    uint32_t pixel = 0, s = 0;
-    float3 o = f3(0, 0, 0), d = f3(0, 0, 0), L = f3(0, 0, 0), beta = f3(1, 1, 1);
-    float3 first_atten = f3(0, 0, 0);  // LIGHT: attenuation of the primary scatter (camera.hpp:512, :515)
-    int light_class = 0;               // LIGHT: 1 reflection, 2 refraction, 0 neither
+    int p = 0;
+    PathState st;
+    st.start(0u, 0u);
+    st.o = f3(0, 0, 0);
+    st.d = f3(0, 0, 0);
+    st.first_atten = f3(0, 0, 0);
+    st.light_class = 0;
 
     // next path of this warp's queue whose pixel lies inside the image
     auto fetch = [&]() -> bool {
@@ -86,22 +237,8 @@ __global__ void __launch_bounds__(ZB_BLOCK_THREADS, ZB_MIN_BLOCKS) k_render(cons
             p = k / n_s;
             int px = px0 + (p & 7), py = py0 + (p >> 3);
             if (px >= P.cam.width || py >= P.cam.height) continue;
-            s = uint32_t(P.sample_begin + (k - p * n_s));
-            pixel = uint32_t(py) * uint32_t(P.cam.width) + uint32_t(px);
-            // ---- K1 raygen: get_ray (camera.hpp:784-794), sample_square (:817), defocus disk (:822)
-            uint4 r0 = ph(pixel, s, 0u, 0u);
-            d = P.cam.pix00_rel + (float(px) + u01(r0.x) - 0.5f) * P.cam.du + (float(py) + u01(r0.y) - 0.5f) * P.cam.dv;
-            o = P.cam.center;
-            if (P.cam.defocus) {
-                float rr = sqrt_fast(u01(r0.z)), sn, cs;
-                sincos_turn(u01(r0.w), &sn, &cs);
-                float3 off = (rr * cs) * P.cam.disk_u + (rr * sn) * P.cam.disk_v;
-                o += off;
-                d = d - off;
-            }
-            seg = 0;
-            L = f3(0, 0, 0);
-            beta = f3(1, 1, 1);
+            st.start(uint32_t(py) * uint32_t(P.cam.width) + uint32_t(px), uint32_t(P.sample_begin + (k - p * n_s)));
+            camera_ray(P, ph, px, py, st.pixel, st.s, st.o, st.d);
             paths++;
             return true;
         }
@@ -114,96 +251,28 @@ __global__ void __launch_bounds__(ZB_BLOCK_THREADS, ZB_MIN_BLOCKS) k_render(cons
     while (have) {
         Hit hit;
         {
-            MediumRng mr{ph, pixel, s, uint32_t(seg + 1)};
-            trace<STATS, F>(P.sc, o, d, 0.001f, INFINITY, mr, hit, cnt);
+            MediumRng mr{ph, st.pixel, st.s, uint32_t(st.seg + 1)};
+            trace<STATS, F>(P.sc, st.o, st.d, 0.001f, INFINITY, mr, hit, cnt);
         }
-        {
-            // ---- K3 shade: one segment of ray_color (camera.hpp:928-1004)
-            bool done;
-            if (LIGHT && seg == 0) {
-                // camera.hpp:492-517: second scatter of the primary hit; a primary miss contributes nothing
-                light_class = 0;
-                done = true;
-                if (hit.item != 0xFFFFFFFFu) {
-                    Surface sf;
-                    make_surface<F>(P.sc, hit, o, d, sf);
-                    uint4 rb = ph(pixel, s, 1u, 0u);
-                    float3 no, nd;
-                    first_atten = f3(1, 1, 1);
-                    if (material_scatter<F>(P.sc, sf, d, f3(u01(rb.x), u01(rb.y), u01(rb.z)), first_atten, no, nd)) {
-                        float3 ud = unit_vector(d), un = unit_vector(sf.n);
-                        float3 mirror = fma3(-2.0f * dot(ud, un), un, ud);
-                        if (dot(unit_vector(nd), mirror) > 0.9f) light_class = 1;
-                        else if (dot(nd, sf.n) < 0.f) light_class = 2;
-                        if (light_class) {  // otherwise the sample lands in neither buffer: skip its path
-                            o = no;
-                            d = nd;
-                            seg = 1;
-                            done = P.max_depth <= 1;
-                        }
-                    }
+        const bool done = shade_segment<LIGHT, F>(P, ph, hit, st, [&](const Surface* sf, float t) {
+            if (aux_on && int(st.s) < P.aux_samples)
+                aov_values<F>(P, sf, t, [&](int k, float v) { fix_add(&s_aux[warp][p][k], v); });
+        });
+        if (done) {
+            if (LIGHT) {
+                if (st.light_class) {
+                    const float3 L = light_pass_value(st);
+                    unsigned long long* dst = st.light_class == 1 ? s_sum[warp][p] : s_aux[warp][p];
+                    fix_add(dst + 0, L.x);
+                    fix_add(dst + 1, L.y);
+                    fix_add(dst + 2, L.z);
                 }
-            } else if (hit.item == 0xFFFFFFFFu) {
-                L += beta * ((F & ZB_F_ENV) ? background(P.sc, P.env, d) : P.env.background);
-                if (!LIGHT && seg == 0 && aux_on && int(s) < P.aux_samples && P.use_normal) {  // camera.hpp:518-526
-                    fix_add(&s_aux[warp][p][3], 0.5f);
-                    fix_add(&s_aux[warp][p][4], 0.5f);
-                    fix_add(&s_aux[warp][p][5], 1.0f);
-                }
-                done = true;
             } else {
-                Surface sf;
-                make_surface<F>(P.sc, hit, o, d, sf);
-                if (!LIGHT && seg == 0 && aux_on && int(s) < P.aux_samples) {  // K8 first-hit AOVs (camera.hpp:464-488)
-                    if (P.use_albedo) {
-                        float3 a = material_get_albedo<F>(P.sc, sf);
-                        fix_add(&s_aux[warp][p][0], a.x);
-                        fix_add(&s_aux[warp][p][1], a.y);
-                        fix_add(&s_aux[warp][p][2], a.z);
-                    }
-                    if (P.use_normal) {
-                        float3 n = unit_vector(sf.n);
-                        fix_add(&s_aux[warp][p][3], (dot(n, P.cam.u) + 1.f) * 0.5f);
-                        fix_add(&s_aux[warp][p][4], (dot(n, P.cam.v) + 1.f) * 0.5f);
-                        fix_add(&s_aux[warp][p][5], (dot(n, P.cam.w) + 1.f) * 0.5f);
-                    }
-                    if (P.use_z) fix_add(&s_aux[warp][p][6], 1.0f - clamp01(hit.t * P.inv_z_max));
-                }
-                L += beta * material_emitted<F>(P.sc, sf);
-                uint4 rb = ph(pixel, s, uint32_t(seg + 1), 0u);
-                float3 atten = f3(1, 1, 1), no, nd;
-                done = !material_scatter<F>(P.sc, sf, d, f3(u01(rb.x), u01(rb.y), u01(rb.z)), atten, no, nd);
-                if (!done) {
-                    beta *= atten;
-                    o = no;
-                    d = nd;
-                    // ray_color's loop index is seg-1; its `i > 10` rules start at seg 12 (camera.hpp:968-983)
-                    if (seg >= 12) {
-                        float pr = fminf(fmaxf(max3(beta.x, beta.y, beta.z), 0.05f), 0.95f);
-                        if (dot(beta, beta) < 1e-8f || u01(rb.w) > pr) done = true;
-                        beta *= 1.0f / pr;
-                    }
-                    if (++seg >= P.max_depth) done = true;  // hard stop keeps the light gathered so far
-                }
+                fix_add(&s_sum[warp][p][0], st.L.x);
+                fix_add(&s_sum[warp][p][1], st.L.y);
+                fix_add(&s_sum[warp][p][2], st.L.z);
             }
-            if (done) {
-                if (LIGHT) {
-                    if (light_class) {
-                        float luma = 0.2126f * length(L);  // vector length, not luminance (camera.hpp:500)
-                        if (luma > 2.0f) L *= 2.0f / luma;
-                        L = first_atten * L;
-                        unsigned long long* dst = light_class == 1 ? s_sum[warp][p] : s_aux[warp][p];
-                        fix_add(dst + 0, L.x);
-                        fix_add(dst + 1, L.y);
-                        fix_add(dst + 2, L.z);
-                    }
-                } else {
-                    fix_add(&s_sum[warp][p][0], L.x);
-                    fix_add(&s_sum[warp][p][1], L.y);
-                    fix_add(&s_sum[warp][p][2], L.z);
-                }
-                have = fetch();
-            }
+            have = fetch();
         }
     }
     __syncwarp();
@@ -289,21 +358,19 @@ __global__ void __launch_bounds__(ZB_BLOCK_THREADS, MIN_BLOCKS) k_render_pq(cons
                                                                                   unsigned long long total, unsigned batch) {
     constexpr bool AUX = MODE == PQ_AUX, LIGHT = MODE == PQ_LIGHT;
     const unsigned lane = threadIdx.x & 31u, lt = (1u << lane) - 1u;
-    const uint32_t n_s = uint32_t(P.sample_end - P.sample_begin);
     const Philox ph{P.pk[LIGHT ? 1 : 0]};  // the light passes draw their own stream
-    float3 first_atten = f3(0, 0, 0);  // LIGHT: attenuation of the primary scatter (camera.hpp:512, :515)
-    int light_class = 0;               // LIGHT: 1 reflection, 2 refraction, 0 neither
     Counters cnt = {0, 0, 0, 0};
     uint32_t paths = 0;
     bool have = false, dry = false;
-    int seg = 0;
-    uint32_t pixel = 0, s = 0;
-    float3 o = f3(0, 0, 0), d = f3(0, 0, 1), L = f3(0, 0, 0), beta = f3(1, 1, 1);
+    PathState st;
+    st.start(0u, 0u);
+    st.o = f3(0, 0, 0);
+    st.d = f3(0, 0, 1);
+    st.first_atten = f3(0, 0, 0);
+    st.light_class = 0;
     unsigned long long w_pos = 0, w_end = 0;  // the warp's batch of path indices (warp-uniform)
-    // exact division of a 32-bit number by n: high word of x * ceil(2^64 / n) (error < 2^-32 of a quotient step); the
-    // two reciprocals cost one 64-bit division each per persistent thread instead of three 32-bit divisions per path
-    const uint32_t tiles_x = uint32_t(P.tiles_x);
-    const unsigned long long m_ns = n_s > 1u ? ~0ull / n_s + 1ull : 0ull, m_tx = tiles_x > 1u ? ~0ull / tiles_x + 1ull : 0ull;
+    PathDecoder dec;
+    dec.init(P);
     for (;;) {
         // ---- lanes without a path take the next ones of the warp's batch; out-of-image pixels are skipped
         for (;;) {
@@ -324,41 +391,11 @@ __global__ void __launch_bounds__(ZB_BLOCK_THREADS, MIN_BLOCKS) k_render_pq(cons
                 if (g >= total) {
                     dry = true;
                 } else {
-                    // g -> (sub-tile u, pixel p of the sub-tile, sample): pixel-major inside a sub-tile, as in k_render
-                    // one division: q = g / n_s numbers the (sub-tile, pixel) pairs, 32 per sub-tile; in 32 bits
-                    // whenever the launch has fewer than 2^32 paths (a 64-bit division is a ~80-instruction routine)
-                    uint32_t q, sr;
-                    if (total <= 0xFFFFFFFFull) {
-                        const uint32_t g32 = uint32_t(g);
-                        q = n_s > 1u ? uint32_t(__umul64hi(g32, m_ns)) : g32;
-                        sr = g32 - q * n_s;
-                    } else {
-                        const unsigned long long q64 = g / n_s;
-                        q = uint32_t(q64);
-                        sr = uint32_t(g - q64 * n_s);
-                    }
-                    const uint32_t u = q >> 5, p = q & 31u;
-                    const int tile = int(u >> 2) * P.tile_ranks + P.tile_rank, w = int(u & 3u);
-                    const int ty = tiles_x > 1u ? int(__umul64hi(uint32_t(tile), m_tx)) : tile, tx = tile - ty * int(tiles_x);
-                    const int px = tx * ZB_TILE_W + (w % (ZB_TILE_W / 8)) * 8 + int(p & 7u);
-                    const int py = ty * ZB_TILE_H + (w / (ZB_TILE_W / 8)) * 4 + int(p >> 3);
-                    if (px < P.cam.width && py < P.cam.height && ty < P.tiles_y) {
-                        s = uint32_t(P.sample_begin) + sr;
-                        pixel = uint32_t(py) * uint32_t(P.cam.width) + uint32_t(px);
-                        // ---- K1 raygen: get_ray (camera.hpp:784-794), sample_square (:817), defocus disk (:822)
-                        const uint4 r0 = ph(pixel, s, 0u, 0u);
-                        d = P.cam.pix00_rel + (float(px) + u01(r0.x) - 0.5f) * P.cam.du + (float(py) + u01(r0.y) - 0.5f) * P.cam.dv;
-                        o = P.cam.center;
-                        if (P.cam.defocus) {
-                            float rr = sqrt_fast(u01(r0.z)), sn, cs;
-                            sincos_turn(u01(r0.w), &sn, &cs);
-                            const float3 off = (rr * cs) * P.cam.disk_u + (rr * sn) * P.cam.disk_v;
-                            o += off;
-                            d = d - off;
-                        }
-                        seg = 0;
-                        L = f3(0, 0, 0);
-                        beta = f3(1, 1, 1);
+                    int px, py;
+                    uint32_t s;
+                    if (dec.decode(P, g, total, px, py, s)) {
+                        st.start(uint32_t(py) * uint32_t(P.cam.width) + uint32_t(px), s);
+                        camera_ray(P, ph, px, py, st.pixel, st.s, st.o, st.d);
                         paths++;
                         have = true;
                     }
@@ -375,94 +412,29 @@ __global__ void __launch_bounds__(ZB_BLOCK_THREADS, MIN_BLOCKS) k_render_pq(cons
         if (have) {
             Hit hit;
             {
-                MediumRng mr{ph, pixel, s, uint32_t(seg + 1)};
-                trace<false, F>(P.sc, o, d, 0.001f, INFINITY, mr, hit, cnt);
+                MediumRng mr{ph, st.pixel, st.s, uint32_t(st.seg + 1)};
+                trace<false, F>(P.sc, st.o, st.d, 0.001f, INFINITY, mr, hit, cnt);
             }
-            // ---- K3 shade: one segment of ray_color (camera.hpp:928-1004), as in k_render
-            bool done;
-            if (LIGHT && seg == 0) {
-                // camera.hpp:492-517: second scatter of the primary hit; a primary miss contributes nothing
-                light_class = 0;
-                done = true;
-                if (hit.item != 0xFFFFFFFFu) {
-                    Surface sf;
-                    make_surface<F>(P.sc, hit, o, d, sf);
-                    const uint4 rb = ph(pixel, s, 1u, 0u);
-                    float3 no, nd;
-                    first_atten = f3(1, 1, 1);
-                    if (material_scatter<F>(P.sc, sf, d, f3(u01(rb.x), u01(rb.y), u01(rb.z)), first_atten, no, nd)) {
-                        const float3 ud = unit_vector(d), un = unit_vector(sf.n);
-                        const float3 mirror = fma3(-2.0f * dot(ud, un), un, ud);
-                        if (dot(unit_vector(nd), mirror) > 0.9f) light_class = 1;
-                        else if (dot(nd, sf.n) < 0.f) light_class = 2;
-                        if (light_class) {  // otherwise the sample lands in neither buffer: skip its path
-                            o = no;
-                            d = nd;
-                            seg = 1;
-                            done = P.max_depth <= 1;
-                        }
-                    }
+            const bool done = shade_segment<LIGHT, F>(P, ph, hit, st, [&](const Surface* sf, float t) {
+                if (AUX && int(st.s) < P.aux_samples) {
+                    unsigned long long* a = fix_aux + 7 * size_t(st.pixel);
+                    aov_values<F>(P, sf, t, [&](int k, float v) { gfix_add(a + k, v); });
                 }
-            } else if (hit.item == 0xFFFFFFFFu) {
-                L += beta * ((F & ZB_F_ENV) ? background(P.sc, P.env, d) : P.env.background);
-                if (AUX && seg == 0 && int(s) < P.aux_samples && P.use_normal) {  // camera.hpp:518-526
-                    unsigned long long* a = fix_aux + 7 * size_t(pixel);
-                    gfix_add(a + 3, 0.5f);
-                    gfix_add(a + 4, 0.5f);
-                    gfix_add(a + 5, 1.0f);
-                }
-                done = true;
-            } else {
-                Surface sf;
-                make_surface<F>(P.sc, hit, o, d, sf);
-                if (AUX && seg == 0 && int(s) < P.aux_samples) {  // K8 first-hit AOVs (camera.hpp:464-488)
-                    unsigned long long* a = fix_aux + 7 * size_t(pixel);
-                    if (P.use_albedo) {
-                        const float3 al = material_get_albedo(P.sc, sf);
-                        gfix_add(a + 0, al.x);
-                        gfix_add(a + 1, al.y);
-                        gfix_add(a + 2, al.z);
-                    }
-                    if (P.use_normal) {
-                        const float3 n = unit_vector(sf.n);
-                        gfix_add(a + 3, (dot(n, P.cam.u) + 1.f) * 0.5f);
-                        gfix_add(a + 4, (dot(n, P.cam.v) + 1.f) * 0.5f);
-                        gfix_add(a + 5, (dot(n, P.cam.w) + 1.f) * 0.5f);
-                    }
-                    if (P.use_z) gfix_add(a + 6, 1.0f - clamp01(hit.t * P.inv_z_max));
-                }
-                L += beta * material_emitted<F>(P.sc, sf);
-                const uint4 rb = ph(pixel, s, uint32_t(seg + 1), 0u);
-                float3 atten = f3(1, 1, 1), no, nd;
-                done = !material_scatter<F>(P.sc, sf, d, f3(u01(rb.x), u01(rb.y), u01(rb.z)), atten, no, nd);
-                if (!done) {
-                    beta *= atten;
-                    o = no;
-                    d = nd;
-                    if (seg >= 12) {  // camera.hpp:968-983
-                        const float pr = fminf(fmaxf(max3(beta.x, beta.y, beta.z), 0.05f), 0.95f);
-                        if (dot(beta, beta) < 1e-8f || u01(rb.w) > pr) done = true;
-                        beta *= 1.0f / pr;
-                    }
-                    if (++seg >= P.max_depth) done = true;
-                }
-            }
+            });
             if (done) {  // K5 accumulate
                 if (LIGHT) {
-                    if (light_class) {
-                        const float luma = 0.2126f * length(L);  // vector length, not luminance (camera.hpp:500)
-                        if (luma > 2.0f) L *= 2.0f / luma;
-                        L = first_atten * L;
-                        unsigned long long* f = (light_class == 1 ? fix : fix_aux) + 3 * size_t(pixel);
+                    if (st.light_class) {
+                        const float3 L = light_pass_value(st);
+                        unsigned long long* f = (st.light_class == 1 ? fix : fix_aux) + 3 * size_t(st.pixel);
                         gfix_add(f + 0, L.x);
                         gfix_add(f + 1, L.y);
                         gfix_add(f + 2, L.z);
                     }
                 } else {
-                    unsigned long long* f = fix + 3 * size_t(pixel);
-                    gfix_add(f + 0, L.x);
-                    gfix_add(f + 1, L.y);
-                    gfix_add(f + 2, L.z);
+                    unsigned long long* f = fix + 3 * size_t(st.pixel);
+                    gfix_add(f + 0, st.L.x);
+                    gfix_add(f + 1, st.L.y);
+                    gfix_add(f + 2, st.L.z);
                 }
                 have = false;
             }
@@ -489,20 +461,22 @@ __global__ void __launch_bounds__(ZB_BLOCK_THREADS, MIN_BLOCKS) k_render_pqr(con
                                                                                    unsigned long long* __restrict__ head,
                                                                                    unsigned long long total, unsigned batch, unsigned thresh) {
     const unsigned lane = threadIdx.x & 31u, lt = (1u << lane) - 1u;
-    const uint32_t n_s = uint32_t(P.sample_end - P.sample_begin);
     const Philox ph{P.pk[0]};
     Counters cnt = {0, 0, 0, 0};
     uint32_t paths = 0;
     bool have = false, dry = false;
-    int seg = 0;
-    uint32_t pixel = 0, s = 0;
-    float3 o = f3(0, 0, 0), d = f3(0, 0, 1), L = f3(0, 0, 0), beta = f3(1, 1, 1);
+    PathState st;
+    st.start(0u, 0u);
+    st.o = f3(0, 0, 0);
+    st.d = f3(0, 0, 1);
+    st.first_atten = f3(0, 0, 0);
+    st.light_class = 0;
     unsigned long long w_pos = 0, w_end = 0;
-    const uint32_t tiles_x = uint32_t(P.tiles_x);
-    const unsigned long long m_ns = n_s > 1u ? ~0ull / n_s + 1ull : 0ull, m_tx = tiles_x > 1u ? ~0ull / tiles_x + 1ull : 0ull;
+    PathDecoder dec;
+    dec.init(P);
     int stack[ZB_STACK];
     RayWalk w;
-    w.begin(P.sc, o, d, INFINITY, stack);
+    w.begin(P.sc, st.o, st.d, INFINITY, stack);
     w.cur = ZB_TRAVERSAL_DONE;
     for (;;) {
         // ---- lanes without a path take the next ones of the warp's batch (as in k_render_pq)
@@ -522,41 +496,15 @@ __global__ void __launch_bounds__(ZB_BLOCK_THREADS, MIN_BLOCKS) k_render_pqr(con
                 if (g >= total) {
                     dry = true;
                 } else {
-                    uint32_t q, sr;
-                    if (total <= 0xFFFFFFFFull) {
-                        const uint32_t g32 = uint32_t(g);
-                        q = n_s > 1u ? uint32_t(__umul64hi(g32, m_ns)) : g32;
-                        sr = g32 - q * n_s;
-                    } else {
-                        const unsigned long long q64 = g / n_s;
-                        q = uint32_t(q64);
-                        sr = uint32_t(g - q64 * n_s);
-                    }
-                    const uint32_t u = q >> 5, p = q & 31u;
-                    const int tile = int(u >> 2) * P.tile_ranks + P.tile_rank, wq = int(u & 3u);
-                    const int ty = tiles_x > 1u ? int(__umul64hi(uint32_t(tile), m_tx)) : tile, tx = tile - ty * int(tiles_x);
-                    const int px = tx * ZB_TILE_W + (wq % (ZB_TILE_W / 8)) * 8 + int(p & 7u);
-                    const int py = ty * ZB_TILE_H + (wq / (ZB_TILE_W / 8)) * 4 + int(p >> 3);
-                    if (px < P.cam.width && py < P.cam.height && ty < P.tiles_y) {
-                        s = uint32_t(P.sample_begin) + sr;
-                        pixel = uint32_t(py) * uint32_t(P.cam.width) + uint32_t(px);
-                        const uint4 r0 = ph(pixel, s, 0u, 0u);
-                        d = P.cam.pix00_rel + (float(px) + u01(r0.x) - 0.5f) * P.cam.du + (float(py) + u01(r0.y) - 0.5f) * P.cam.dv;
-                        o = P.cam.center;
-                        if (P.cam.defocus) {
-                            float rr = sqrt_fast(u01(r0.z)), sn, cs;
-                            sincos_turn(u01(r0.w), &sn, &cs);
-                            const float3 off = (rr * cs) * P.cam.disk_u + (rr * sn) * P.cam.disk_v;
-                            o += off;
-                            d = d - off;
-                        }
-                        seg = 0;
-                        L = f3(0, 0, 0);
-                        beta = f3(1, 1, 1);
+                    int px, py;
+                    uint32_t s;
+                    if (dec.decode(P, g, total, px, py, s)) {
+                        st.start(uint32_t(py) * uint32_t(P.cam.width) + uint32_t(px), s);
+                        camera_ray(P, ph, px, py, st.pixel, st.s, st.o, st.d);
                         paths++;
                         have = true;
                         cnt.rays++;
-                        w.begin(P.sc, o, d, INFINITY, stack);
+                        w.begin(P.sc, st.o, st.d, INFINITY, stack);
                     }
                 }
             }
@@ -577,46 +525,24 @@ __global__ void __launch_bounds__(ZB_BLOCK_THREADS, MIN_BLOCKS) k_render_pqr(con
             if (trav) {
                 while (w.cur >= 0) w.node_step<false>(P.sc, 0.001f, stack, cnt);
                 if (w.cur != ZB_TRAVERSAL_DONE) {
-                    const MediumRng mr{ph, pixel, s, uint32_t(seg + 1)};
-                    w.leaf_step<false, F>(P.sc, o, d, 0.001f, mr, stack, cnt);
+                    const MediumRng mr{ph, st.pixel, st.s, uint32_t(st.seg + 1)};
+                    w.leaf_step<false, F>(P.sc, st.o, st.d, 0.001f, mr, stack, cnt);
                 }
             }
         }
-        // ---- K3 shade the lanes whose ray is finished: one segment of ray_color (camera.hpp:928-1004), as in k_render_pq
+        // ---- K3 shade the lanes whose ray is finished, as in k_render_pq
         if (have && w.cur == ZB_TRAVERSAL_DONE) {
             const Hit hit = w.hit;
-            bool done;
-            if (hit.item == 0xFFFFFFFFu) {
-                L += beta * ((F & ZB_F_ENV) ? background(P.sc, P.env, d) : P.env.background);
-                done = true;
-            } else {
-                Surface sf;
-                make_surface<F>(P.sc, hit, o, d, sf);
-                L += beta * material_emitted<F>(P.sc, sf);
-                const uint4 rb = ph(pixel, s, uint32_t(seg + 1), 0u);
-                float3 atten = f3(1, 1, 1), no, nd;
-                done = !material_scatter<F>(P.sc, sf, d, f3(u01(rb.x), u01(rb.y), u01(rb.z)), atten, no, nd);
-                if (!done) {
-                    beta *= atten;
-                    o = no;
-                    d = nd;
-                    if (seg >= 12) {  // camera.hpp:968-983
-                        const float pr = fminf(fmaxf(max3(beta.x, beta.y, beta.z), 0.05f), 0.95f);
-                        if (dot(beta, beta) < 1e-8f || u01(rb.w) > pr) done = true;
-                        beta *= 1.0f / pr;
-                    }
-                    if (++seg >= P.max_depth) done = true;
-                }
-            }
+            const bool done = shade_segment<false, F>(P, ph, hit, st, [](const Surface*, float) {});
             if (done) {  // K5 accumulate
-                unsigned long long* f = fix + 3 * size_t(pixel);
-                gfix_add(f + 0, L.x);
-                gfix_add(f + 1, L.y);
-                gfix_add(f + 2, L.z);
+                unsigned long long* f = fix + 3 * size_t(st.pixel);
+                gfix_add(f + 0, st.L.x);
+                gfix_add(f + 1, st.L.y);
+                gfix_add(f + 2, st.L.z);
                 have = false;
             } else {
                 cnt.rays++;
-                w.begin(P.sc, o, d, INFINITY, stack);
+                w.begin(P.sc, st.o, st.d, INFINITY, stack);
             }
         }
     }
@@ -650,36 +576,18 @@ __global__ void __launch_bounds__(ZB_BLOCK_THREADS, 6) k_aov_pass(const __grid_c
     auto add = [&](int k, float v) { acc[k] += __float2ull_rn(fmaxf(v, 0.f) * ZB_FIX_SCALE); };
     const int s_end = min(P.sample_end, P.aux_samples);
     for (int s = P.sample_begin; s < s_end; s++) {
-        const uint4 r0 = ph(pixel, uint32_t(s), 0u, 0u);
-        float3 d = P.cam.pix00_rel + (float(px) + u01(r0.x) - 0.5f) * P.cam.du + (float(py) + u01(r0.y) - 0.5f) * P.cam.dv;
-        float3 o = P.cam.center;
-        if (P.cam.defocus) {
-            float rr = sqrt_fast(u01(r0.z)), sn, cs;
-            sincos_turn(u01(r0.w), &sn, &cs);
-            const float3 off = (rr * cs) * P.cam.disk_u + (rr * sn) * P.cam.disk_v;
-            o += off;
-            d = d - off;
-        }
+        float3 o, d;
+        camera_ray(P, ph, px, py, pixel, uint32_t(s), o, d);
         Hit hit;
         const MediumRng mr{ph, pixel, uint32_t(s), 1u};
         trace<false, F>(P.sc, o, d, 0.001f, INFINITY, mr, hit, cnt);
         if (hit.item == 0xFFFFFFFFu) {
-            if (P.use_normal) { add(3, 0.5f); add(4, 0.5f); add(5, 1.0f); }  // camera.hpp:518-526
+            aov_values<F>(P, nullptr, 0.f, add);
             continue;
         }
         Surface sf;
         make_surface<F>(P.sc, hit, o, d, sf);
-        if (P.use_albedo) {
-            const float3 a = material_get_albedo<F>(P.sc, sf);
-            add(0, a.x); add(1, a.y); add(2, a.z);
-        }
-        if (P.use_normal) {
-            const float3 n = unit_vector(sf.n);
-            add(3, (dot(n, P.cam.u) + 1.f) * 0.5f);
-            add(4, (dot(n, P.cam.v) + 1.f) * 0.5f);
-            add(5, (dot(n, P.cam.w) + 1.f) * 0.5f);
-        }
-        if (P.use_z) add(6, 1.0f - clamp01(hit.t * P.inv_z_max));
+        aov_values<F>(P, &sf, hit.t, add);
     }
     const size_t n = size_t(P.cam.width) * P.cam.height, i = pixel;
     if (fix_aux) {
