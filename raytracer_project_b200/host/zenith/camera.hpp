@@ -127,6 +127,9 @@ public:
 
     // backend knobs (no counterpart in the reference)
     int device = 0;
+    // more than one entry: the frame is rendered by all of these GPUs (zb_context_create_multi); render() stays one
+    // blocking call that fills the same buffers — the reference's thread fan-out (camera.hpp:426-427) by other means
+    std::vector<int> devices;
     uint64_t seed = 0x5EED0001ull;
     int rc = ZB_OK;            // status of the last render()
     std::string last_error;
@@ -147,6 +150,11 @@ public:
     // Call after editing the scene graph in place (the reference rebuilds its BVH at main.cpp:1492-1500).
     void invalidate_scene() { cached_world = nullptr; }
 
+    int create_context() {
+        if (devices.size() > 1) return zb_context_create_multi(devices.data(), int(devices.size()), &ctx);
+        return zb_context_create(devices.empty() ? device : devices[0], &ctx);
+    }
+
     void render(const hittable& world, const EnvironmentSettings& env, const post_processor& post, std::atomic<bool>& render_flag) {
         last_error.clear();
         if (image_width < 1) image_width = 1;  // camera::initialize (camera.hpp:359-366)
@@ -155,7 +163,7 @@ public:
         lines_rendered.store(0);
         const size_t n = size_t(image_width) * image_height;
         if (render_accumulator.size() < n) { set_error(ZB_ERR_INVALID, "camera::render: call reset_accumulator() first (camera.hpp:209)"); return; }
-        if (!ctx && (rc = zb_context_create(device, &ctx)) != ZB_OK) { set_error(rc, zb_last_error()); return; }
+        if (!ctx && (rc = create_context()) != ZB_OK) { set_error(rc, zb_last_error()); return; }
         if (cached_world != &world || cached_hdr != env.hdr_texture.get()) {
             if (scene) zb_scene_destroy(scene);
             scene = nullptr;
@@ -243,7 +251,7 @@ public:
         const std::vector<color>& source = get_active_buffer();
         if (source.size() < size_t(w) * size_t(h) || w < 1 || h < 1) return;
         final_framebuffer.resize(source.size());
-        if (!ctx && (rc = zb_context_create(device, &ctx)) != ZB_OK) { set_error(rc, zb_last_error()); return; }
+        if (!ctx && (rc = create_context()) != ZB_OK) { set_error(rc, zb_last_error()); return; }
         const bool beauty = current_display_pass == render_pass::RGB || current_display_pass == render_pass::DENOISE;
         const bool light = current_display_pass == render_pass::REFLECTIONS || current_display_pass == render_pass::REFRACTIONS;
         const zb_post p = post.to_abi();
@@ -266,7 +274,7 @@ public:
             default: break;
         }
         if (src->size() < size_t(image_width) * size_t(image_height)) { set_error(ZB_ERR_INVALID, "save_render_pass: the pass buffer is empty"); return; }
-        if (!ctx && (rc = zb_context_create(device, &ctx)) != ZB_OK) { set_error(rc, zb_last_error()); return; }
+        if (!ctx && (rc = create_context()) != ZB_OK) { set_error(rc, zb_last_error()); return; }
         const zb_post p = pp.to_abi();
         rc = zb_save_pass_f64(ctx, reinterpret_cast<const double*>(src->data()), image_width, image_height, &p, int(pass), ("output/" + filename).c_str());
         if (rc != ZB_OK) set_error(rc, zb_last_error());

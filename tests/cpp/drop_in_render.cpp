@@ -24,7 +24,7 @@ static bool finite_nonzero(const std::vector<color>& b) {
 }
 
 int main(int argc, char** argv) {
-    if (argc < 8) { std::fprintf(stderr, "usage: drop_in_render SCENE OUT W H SPP DEPTH SEED\n"); return 2; }
+    if (argc < 8) { std::fprintf(stderr, "usage: drop_in_render SCENE OUT W H SPP DEPTH SEED [DEVICES]\n"); return 2; }
     // ---- 1. a zscene world through camera::render
     std::ifstream in(argv[1]);
     if (!in) return 2;
@@ -48,6 +48,11 @@ int main(int argc, char** argv) {
     cam.vup = vec3(0, 1, 0);
     cam.defocus_angle = 0.6;
     cam.focus_dist = 10.0;
+    if (argc > 8)  // "0,1,..": render on several GPUs through the same call (camera::devices)
+        for (const char* p = argv[8]; *p;) {
+            cam.devices.push_back(int(std::strtol(p, const_cast<char**>(&p), 10)));
+            if (*p == ',') p++;
+        }
     cam.use_albedo_buffer = cam.use_normal_buffer = cam.use_z_depth_buffer = true;
     cam.use_reflection = cam.use_refraction = true;
     std::atomic<bool> is_rendering{true};

@@ -389,7 +389,8 @@ def test_light_passes_match_reference(gpu_ctx, tmp_path):
         assert rrmse < 0.06  # the 2048-spp reference carries ~5 % noise of its own on these sparse buffers
 
 
-def test_drop_in_camera_render_equals_abi_render(weekend_scene, tmp_path):
+@pytest.mark.parametrize("devices", ["", "0,0,0"])
+def test_drop_in_camera_render_equals_abi_render(weekend_scene, tmp_path, devices):
     """The reference-shaped C++ entry point zenith::camera::render (host/zenith/camera.hpp; camera.hpp:236) fills its
     std::vector<color> buffers with exactly what zb_render returns for the same scene, camera and seed; the same
     program also renders a hand-built scene written like the reference's scene code and checks lines_rendered /
@@ -405,7 +406,8 @@ def test_drop_in_camera_render_equals_abi_render(weekend_scene, tmp_path):
     cfg.use_albedo = cfg.use_normal = cfg.use_z_depth = cfg.use_reflection = cfg.use_refraction = True
     (tmp_path / "w.zscene").write_text(txt)
     out = tmp_path / "out.bin"
-    r = subprocess.run([exe, str(tmp_path / "w.zscene"), str(out), str(W), str(H), str(SPP), str(DEPTH), str(SEED)],
+    # devices = "0,0,0": zenith::camera::devices -> zb_context_create_multi (three ranks, here on one GPU): the same buffers
+    r = subprocess.run([exe, str(tmp_path / "w.zscene"), str(out), str(W), str(H), str(SPP), str(DEPTH), str(SEED)] + ([devices] if devices else []),
                        capture_output=True, text=True)
     assert r.returncode == 0, r.stderr
     bufs = np.frombuffer(out.read_bytes(), np.float64).reshape(6, H, W, 3)
