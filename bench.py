@@ -238,7 +238,7 @@ def ours(args):
     # ZB_BENCH_CACHE=dir keeps the flattened scene of a config as dir/NAME.zbfs for later runs on the same box (the host
     # BVH build of the 10 M-triangle config takes ~100 s, during which every GPU of the box idles)
     cache = os.environ.get("ZB_BENCH_CACHE")
-    zbfs = os.path.join(cache, f"{name}.zbfs") if cache else f"/tmp/zb_bench_{name}_{job}.zbfs"
+    zbfs = os.path.join(cache, f"{name}{'_lbvh' if args.gpu_blas else ''}.zbfs") if cache else f"/tmp/zb_bench_{name}_{job}.zbfs"
     t_prep = time.time()
     if not files:
         flat = api.flatten_zscene(txt)
@@ -249,7 +249,7 @@ def ours(args):
         flat0 = None
         if rank == 0:
             d = tempfile.mkdtemp(prefix="zb_bench_")
-            flat0 = api.flatten_zscene(path=scenes.materialize(d, txt, cfg, files))
+            flat0 = api.flatten_zscene(path=scenes.materialize(d, txt, cfg, files), gpu_blas=args.gpu_blas)
             if world > 1 or cache:
                 os.makedirs(os.path.dirname(zbfs), exist_ok=True)
                 api.save_flat(flat0, zbfs + ".tmp")
@@ -405,7 +405,8 @@ def ours(args):
                        "l2_flush_between_steps": True, "scene_bytes": scene_bytes, "scene_prep_s": round(prep_s, 2),
                        "rays_per_path": rays / max(paths_counted, 1.0), "node_visits_per_ray": node_visits / max(rays, 1.0),
                        "prim_tests_per_ray": prim_tests / max(rays, 1.0), "kernel": kernel_name(pick),
-                       "feature_set": FEATURE_NAMES.get(feat, str(feat))},
+                       "feature_set": FEATURE_NAMES.get(feat, str(feat)),
+                       "blas": "device LBVH" if args.gpu_blas else "host binned SAH"},
             "kernel_ms_per_step": kernel_ms,
             "e2e": {"value": e2e_value, "unit": "Mpaths/s", "ms_per_step": e2e_ms_per_step,
                     "h2d_bytes_per_step": (scene_bytes + 512) * world, "d2h_bytes_per_step": n_pix * 12, "checksum": checksum,
@@ -458,6 +459,7 @@ def main():
     ap.add_argument("--config", default="headline", choices=list(CONFIGS))
     ap.add_argument("--partition", default="auto", choices=["auto", "samples", "tiles"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--gpu-blas", action="store_true", help="mesh BLASes built on the device at upload (linear BVH, csrc/lbvh.cu) instead of the host SAH build")
     ap.add_argument("--spp", type=int, default=0, help="profiling runs only: override the config's samples per pixel (the workload name says so)")
     args = ap.parse_args()
     if args.spp > 0:

@@ -2,8 +2,8 @@
 // every GUI restart (bvh.hpp:11-44 via model.hpp:95, main.cpp:1492-1500) for meshes the flattener marked
 // "build on device" (zb_mesh::node_count == 0).
 //
-// Linear BVH (Lauterbach 2009, Karras 2012): 30-bit Morton codes of the triangle centroids, radix sort
-// (cub::DeviceRadixSort — library code, like cuBLAS for a GEMM), one thread per internal node finds its key range
+// Linear BVH (Lauterbach 2009, Karras 2012): 30-bit Morton codes of the triangle centroids, an LSD radix sort of our own
+// (k_sort_hist / k_sort_scan / k_sort_scatter below), one thread per internal node finds its key range
 // and split, a bottom-up pass fits the boxes, and an emit pass writes the renderer's 64-byte nodes (both child boxes
 // in the parent): subtrees of <= 4 triangles become one leaf, because a subtree of the sorted order is a contiguous
 // triangle range.  Triangles and normals are permuted into sorted order.  Closest-hit results do not depend on the
@@ -11,8 +11,7 @@
 //
 // All passes stream over n elements: HBM-bound.  Bytes per triangle: bounds 48 read; morton 48 + 8; sort 4 passes x
 // 16; hierarchy ~40; fit ~72; emit ~64 per alive node; permute 192 read + 192 written.
-#include <cub/device/device_radix_sort.cuh>
-#include <cub/device/device_scan.cuh>
+#include <algorithm>
 
 #include "abi_internal.h"
 #include "vecmath.cuh"
@@ -57,6 +56,121 @@ __global__ void __launch_bounds__(256) k_centroid_bounds(const float4* __restric
         atomicMin(bounds + 0, f2ord(lo.x)); atomicMin(bounds + 1, f2ord(lo.y)); atomicMin(bounds + 2, f2ord(lo.z));
         atomicMax(bounds + 3, f2ord(hi.x)); atomicMax(bounds + 4, f2ord(hi.y)); atomicMax(bounds + 5, f2ord(hi.z));
     }
+}
+
+// ---- own LSD radix sort of (30-bit Morton key, triangle id) pairs: four passes of 8 bits.  Per pass: per-tile digit
+// histograms, one scan over (digit, tile) counts, a STABLE scatter.  A tile = 256 threads x 8 keys; inside a tile keys are
+// ranked step by step (key j of every thread in step j): __match_any_sync groups the lanes of a warp with equal digits,
+// shared-memory counters order the warps and carry the running count of every digit from step to step.
+// HBM-bound: per pass 8 B read (histogram) + 8 B read + 8 B written (scatter) per pair.
+#define SORT_THREADS 256
+#define SORT_ITEMS 8
+#define SORT_TILE (SORT_THREADS * SORT_ITEMS)
+
+__global__ void __launch_bounds__(SORT_THREADS) k_sort_hist(const uint32_t* __restrict__ keys, uint32_t n, int shift, uint32_t n_tiles,
+                                                            uint32_t* __restrict__ counts) {  // counts[digit * n_tiles + tile]
+    __shared__ uint32_t h[256];
+    h[threadIdx.x] = 0;
+    __syncthreads();
+    const uint32_t base = blockIdx.x * SORT_TILE;
+#pragma unroll
+    for (int j = 0; j < SORT_ITEMS; j++) {
+        const uint32_t i = base + j * SORT_THREADS + threadIdx.x;
+        if (i < n) atomicAdd(&h[(keys[i] >> shift) & 255u], 1u);
+    }
+    __syncthreads();
+    counts[threadIdx.x * n_tiles + blockIdx.x] = h[threadIdx.x];
+}
+
+// exclusive scan of counts[] (256 * n_tiles entries, digit-major) in place: one block, sequential chunks of 1024
+__global__ void __launch_bounds__(1024) k_sort_scan(uint32_t* __restrict__ counts, uint32_t total) {
+    __shared__ uint32_t warp_sum[32];
+    __shared__ uint32_t carry;
+    if (threadIdx.x == 0) carry = 0;
+    __syncthreads();
+    for (uint32_t start = 0; start < total; start += 1024) {
+        const uint32_t i = start + threadIdx.x;
+        const uint32_t v = i < total ? counts[i] : 0u;
+        uint32_t x = v;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const uint32_t y = __shfl_up_sync(0xFFFFFFFFu, x, o);
+            if ((threadIdx.x & 31) >= o) x += y;
+        }
+        if ((threadIdx.x & 31) == 31) warp_sum[threadIdx.x >> 5] = x;
+        __syncthreads();
+        if (threadIdx.x < 32) {
+            uint32_t w = warp_sum[threadIdx.x];
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+                const uint32_t y = __shfl_up_sync(0xFFFFFFFFu, w, o);
+                if (threadIdx.x >= o) w += y;
+            }
+            warp_sum[threadIdx.x] = w;  // inclusive over warps
+        }
+        __syncthreads();
+        const uint32_t before = carry + (threadIdx.x >= 32 ? warp_sum[(threadIdx.x >> 5) - 1] : 0u);
+        if (i < total) counts[i] = before + x - v;
+        __syncthreads();
+        if (threadIdx.x == 1023) carry = before + x;
+        __syncthreads();
+    }
+}
+
+__global__ void __launch_bounds__(SORT_THREADS) k_sort_scatter(const uint32_t* __restrict__ keys_in, const uint32_t* __restrict__ vals_in,
+                                                               uint32_t n, int shift, uint32_t n_tiles, const uint32_t* __restrict__ offsets,
+                                                               uint32_t* __restrict__ keys_out, uint32_t* __restrict__ vals_out) {
+    constexpr int WARPS = SORT_THREADS / 32;
+    __shared__ uint32_t running[256];          // next output slot of every digit for this tile
+    __shared__ uint32_t warp_count[WARPS][256];
+    const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
+    running[threadIdx.x] = offsets[threadIdx.x * n_tiles + blockIdx.x];
+    const uint32_t base = blockIdx.x * SORT_TILE;
+    for (int j = 0; j < SORT_ITEMS; j++) {
+#pragma unroll
+        for (int w = 0; w < WARPS; w++) warp_count[w][threadIdx.x] = 0;
+        __syncthreads();
+        const uint32_t i = base + j * SORT_THREADS + threadIdx.x;
+        const bool live = i < n;
+        const uint32_t key = live ? keys_in[i] : 0xFFFFFFFFu;
+        const uint32_t d = live ? (key >> shift) & 255u : 256u + lane;  // dead lanes match nobody
+        const uint32_t peers = __match_any_sync(0xFFFFFFFFu, d);
+        const uint32_t rank = __popc(peers & ((1u << lane) - 1u));
+        if (live && rank == 0) warp_count[warp][d] = __popc(peers);
+        __syncthreads();
+        if (live) {
+            uint32_t at = running[d] + rank;
+            for (uint32_t w = 0; w < warp; w++) at += warp_count[w][d];
+            keys_out[at] = key;
+            vals_out[at] = vals_in[i];
+        }
+        __syncthreads();
+        uint32_t add = 0;
+#pragma unroll
+        for (int w = 0; w < WARPS; w++) add += warp_count[w][threadIdx.x];
+        running[threadIdx.x] += add;
+        __syncthreads();
+    }
+}
+
+// sorts (keys, vals) by the low `bits` bits of the keys; result in (keys_out, vals_out) = the caller's second pair of
+// buffers when the number of passes is odd, else back in (keys, vals): returns which.  counts: 256 * n_tiles words.
+int radix_sort_pairs(uint32_t* keys, uint32_t* vals, uint32_t* keys2, uint32_t* vals2, uint32_t n, int bits, uint32_t* counts,
+                     cudaStream_t st, bool* in_second) {
+    const uint32_t n_tiles = (n + SORT_TILE - 1) / SORT_TILE;
+    uint32_t *ki = keys, *vi = vals, *ko = keys2, *vo = vals2;
+    bool second = false;
+    for (int shift = 0; shift < bits; shift += 8) {
+        k_sort_hist<<<n_tiles, SORT_THREADS, 0, st>>>(ki, n, shift, n_tiles, counts);
+        k_sort_scan<<<1, 1024, 0, st>>>(counts, 256u * n_tiles);
+        k_sort_scatter<<<n_tiles, SORT_THREADS, 0, st>>>(ki, vi, n, shift, n_tiles, counts, ko, vo);
+        ZB_CUDA(cudaGetLastError());
+        std::swap(ki, ko);
+        std::swap(vi, vo);
+        second = !second;
+    }
+    *in_second = second;
+    return ZB_OK;
 }
 
 ZB_DEV uint32_t expand10(uint32_t v) {  // 10 bits -> every third bit
@@ -130,7 +244,8 @@ __global__ void __launch_bounds__(256) k_hierarchy(const uint32_t* __restrict__ 
 __global__ void __launch_bounds__(256) k_fit(const float4* __restrict__ tris, const uint32_t* __restrict__ ids, int n,
                                              const int2* __restrict__ child, const int* __restrict__ parent_int,
                                              const int* __restrict__ parent_leaf, float* __restrict__ leaf_box,
-                                             float* __restrict__ node_box, int* __restrict__ visits) {
+                                             float* __restrict__ node_box, int* __restrict__ visits, const int2* __restrict__ range,
+                                             float* __restrict__ cost, int* __restrict__ collapse) {
     const int k = blockIdx.x * blockDim.x + threadIdx.x;
     if (k >= n) return;
     TriBox b = tri_box(tris + 3 * size_t(ids[k]));
@@ -150,16 +265,39 @@ __global__ void __launch_bounds__(256) k_fit(const float4* __restrict__ tris, co
         const volatile float* vr = r;
         o[0] = fminf(vl[0], vr[0]); o[1] = fminf(vl[1], vr[1]); o[2] = fminf(vl[2], vr[2]);
         o[3] = fmaxf(vl[3], vr[3]); o[4] = fmaxf(vl[4], vr[4]); o[5] = fmaxf(vl[5], vr[5]);
+        // surface-area heuristic, bottom-up (traversal step = primitive test = 1, as the host builder counts): a subtree of
+        // <= LBVH_LEAF_MAX triangles becomes ONE leaf only where that is cheaper than keeping its split.  (Collapsing every
+        // such subtree, as round 1 did, doubled the triangle tests per ray against the SAH tree: 8.4 vs 4.2.)
+        auto half_area = [](const volatile float* b) {
+            const float dx = b[3] - b[0], dy = b[4] - b[1], dz = b[5] - b[2];
+            return dx * dy + dy * dz + dz * dx;
+        };
+        const volatile float* vc = cost;
+        const float cl = c.x >= 0 ? vc[c.x] : half_area(vl), cr = c.y >= 0 ? vc[c.y] : half_area(vr);
+        const float a_node = half_area(o);
+        const int2 rg = range[node];
+        const int count = rg.y - rg.x + 1;
+        const float split_cost = a_node + cl + cr, leaf_cost = float(count) * a_node;
+        const bool leaf = count <= LBVH_LEAF_MAX && leaf_cost <= split_cost;
+        cost[node] = leaf ? leaf_cost : split_cost;
+        collapse[node] = leaf ? 1 : 0;
         node = parent_int[node];
     }
 }
 
-// pass 5a: an internal node survives when its range is larger than a leaf (its ancestors then survive too)
-__global__ void __launch_bounds__(256) k_alive(const int2* __restrict__ range, int n_int, int* __restrict__ alive) {
+// pass 5a: an internal node survives as an inner node unless it or one of its ancestors was collapsed into a leaf
+// (only subtrees of <= LBVH_LEAF_MAX triangles can be, so the walk up is at most three steps)
+__global__ void __launch_bounds__(256) k_alive(const int2* __restrict__ range, const int* __restrict__ collapse,
+                                               const int* __restrict__ parent_int, int n_int, int* __restrict__ alive) {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n_int) return;
-    const int2 r = range[i];
-    alive[i] = (i == 0 || r.y - r.x + 1 > LBVH_LEAF_MAX) ? 1 : 0;
+    int dead = 0;
+    for (int a = i; a > 0; a = parent_int[a]) {
+        const int2 r = range[a];
+        if (r.y - r.x + 1 > LBVH_LEAF_MAX) break;
+        dead |= collapse[a];
+    }
+    alive[i] = (i == 0 || !dead) ? 1 : 0;
 }
 
 // depth of the emitted tree: surviving inner nodes above each sorted triangle, maximum over the mesh.  A Karras tree over
@@ -194,7 +332,7 @@ __global__ void __launch_bounds__(256) k_emit(const int2* __restrict__ child, co
         } else {
             const int2 r = range[cc[k]];
             box[k] = node_box + 6 * size_t(cc[k]);
-            if (r.y - r.x + 1 <= LBVH_LEAF_MAX) code[k] = int(~(((tri_first + uint32_t(r.x)) << 3) | uint32_t(r.y - r.x)));
+            if (!alive[cc[k]]) code[k] = int(~(((tri_first + uint32_t(r.x)) << 3) | uint32_t(r.y - r.x)));  // collapsed: one leaf
             else code[k] = node_base + compact[cc[k]];
         }
     }
@@ -257,29 +395,37 @@ int zbk_build_blas_device(zb_context* ctx, const float4* tris_in, const float4* 
     uint32_t *bounds, *keys, *keys2, *ids, *ids2;
     float *leaf_box, *node_box;
     int2 *child, *range;
-    int *parent_int, *parent_leaf, *visits, *alive, *compact, *max_depth;
+    int *parent_int, *parent_leaf, *visits, *alive, *compact, *max_depth, *collapse;
+    float* cost;
     ZB_CUDA(sc.get(&bounds, 6));
     ZB_CUDA(sc.get(&keys, n)); ZB_CUDA(sc.get(&keys2, n)); ZB_CUDA(sc.get(&ids, n)); ZB_CUDA(sc.get(&ids2, n));
     ZB_CUDA(sc.get(&leaf_box, 6 * size_t(n))); ZB_CUDA(sc.get(&node_box, 6 * size_t(n)));
     ZB_CUDA(sc.get(&child, n)); ZB_CUDA(sc.get(&range, n));
     ZB_CUDA(sc.get(&parent_int, n)); ZB_CUDA(sc.get(&parent_leaf, n)); ZB_CUDA(sc.get(&visits, n));
     ZB_CUDA(sc.get(&alive, n)); ZB_CUDA(sc.get(&compact, n + 1)); ZB_CUDA(sc.get(&max_depth, 1));
+    ZB_CUDA(sc.get(&collapse, n)); ZB_CUDA(sc.get(&cost, n));
     const uint32_t init[6] = {0xFFFFFFFFu, 0xFFFFFFFFu, 0xFFFFFFFFu, 0u, 0u, 0u};
     ZB_CUDA(cudaMemcpyAsync(bounds, init, sizeof(init), cudaMemcpyHostToDevice, st));
     k_centroid_bounds<<<std::min(nb, unsigned(ctx->sm_count) * 8u), 256, 0, st>>>(tris_in, n, bounds);
     k_morton<<<nb, 256, 0, st>>>(tris_in, n, bounds, keys, ids);
     ZB_CUDA(cudaGetLastError());
-    size_t tmp_bytes = 0;
-    ZB_CUDA(cub::DeviceRadixSort::SortPairs(nullptr, tmp_bytes, keys, keys2, ids, ids2, int(n), 0, 30, st));
-    void* tmp = nullptr;
-    ZB_CUDA(sc.get(reinterpret_cast<char**>(&tmp), tmp_bytes));
-    ZB_CUDA(cub::DeviceRadixSort::SortPairs(tmp, tmp_bytes, keys, keys2, ids, ids2, int(n), 0, 30, st));
+    uint32_t* sort_counts;
+    ZB_CUDA(sc.get(&sort_counts, 256 * size_t((n + SORT_TILE - 1) / SORT_TILE)));
+    bool in_second = false;
+    {
+        int rc = radix_sort_pairs(keys, ids, keys2, ids2, n, 30, sort_counts, st, &in_second);
+        if (rc) return rc;
+    }
+    if (!in_second) {  // the rest of the build reads the sorted pairs from (keys2, ids2)
+        std::swap(keys, keys2);
+        std::swap(ids, ids2);
+    }
     k_permute<<<(3 * n + 255) / 256, 256, 0, st>>>(tris_in, nrm_in, ids2, n, tris_out, nrm_out);
     ZB_CUDA(cudaGetLastError());
     ctx->stats.launches += 4;
     if (n == 1) {
         ZB_CUDA(cudaMemsetAsync(visits, 0, sizeof(int), st));
-        k_fit<<<1, 256, 0, st>>>(tris_in, ids2, 1, child, parent_int, parent_leaf, leaf_box, node_box, visits);
+        k_fit<<<1, 256, 0, st>>>(tris_in, ids2, 1, child, parent_int, parent_leaf, leaf_box, node_box, visits, range, cost, collapse);
         k_emit_single<<<1, 1, 0, st>>>(leaf_box, tri_first, nodes_out);
         ZB_CUDA(cudaGetLastError());
         *n_nodes = 1;
@@ -289,17 +435,15 @@ int zbk_build_blas_device(zb_context* ctx, const float4* tris_in, const float4* 
     const unsigned nbi = (n_int + 255) / 256;
     ZB_CUDA(cudaMemsetAsync(visits, 0, size_t(n) * sizeof(int), st));
     k_hierarchy<<<nbi, 256, 0, st>>>(keys2, int(n), child, range, parent_int, parent_leaf);
-    k_fit<<<nb, 256, 0, st>>>(tris_in, ids2, int(n), child, parent_int, parent_leaf, leaf_box, node_box, visits);
-    k_alive<<<nbi, 256, 0, st>>>(range, n_int, alive);
+    k_fit<<<nb, 256, 0, st>>>(tris_in, ids2, int(n), child, parent_int, parent_leaf, leaf_box, node_box, visits, range, cost, collapse);
+    k_alive<<<nbi, 256, 0, st>>>(range, collapse, parent_int, n_int, alive);
     ZB_CUDA(cudaMemsetAsync(max_depth, 0, sizeof(int), st));
     k_depth<<<nb, 256, 0, st>>>(parent_int, parent_leaf, alive, int(n), max_depth);
     ZB_CUDA(cudaGetLastError());
-    size_t scan_bytes = 0;
-    ZB_CUDA(cub::DeviceScan::ExclusiveSum(nullptr, scan_bytes, alive, compact, n_int + 1, st));
-    void* scan_tmp = nullptr;
-    ZB_CUDA(sc.get(reinterpret_cast<char**>(&scan_tmp), scan_bytes));
+    // compact[i] = number of surviving nodes before i (own exclusive scan, in place on a copy of alive[])
     ZB_CUDA(cudaMemsetAsync(alive + n_int, 0, sizeof(int), st));
-    ZB_CUDA(cub::DeviceScan::ExclusiveSum(scan_tmp, scan_bytes, alive, compact, n_int + 1, st));
+    ZB_CUDA(cudaMemcpyAsync(compact, alive, size_t(n_int + 1) * sizeof(int), cudaMemcpyDeviceToDevice, st));
+    k_sort_scan<<<1, 1024, 0, st>>>(reinterpret_cast<uint32_t*>(compact), uint32_t(n_int + 1));
     k_emit<<<nbi, 256, 0, st>>>(child, range, alive, compact, leaf_box, node_box, n_int, tri_first, int(node_base), nodes_out);
     ZB_CUDA(cudaGetLastError());
     ctx->stats.launches += 6;
