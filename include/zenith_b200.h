@@ -193,6 +193,9 @@ typedef struct zb_flat_scene {
     uint32_t n_wide_nodes;
     uint32_t wide_stack_need;
     const zb_wide_node* wide_nodes;
+    /* optional: world-space bounds of every item, 8 floats each (lo.xyz, 0, hi.xyz, 0), in items[] order — the
+     * reference's bounding_box() of the leaf object.  Needed by zb_scene_refit only; NULL = the scene cannot be refitted. */
+    const float* item_bounds;
 } zb_flat_scene;
 
 /* The 13 public camera parameters (camera.hpp:26-42); derived quantities are computed in double by
@@ -317,6 +320,15 @@ int zb_device_info(zb_context* ctx, int* sm_count, int* cc_major, int* cc_minor,
 /* copies the flat scene to the GPU; the caller keeps ownership of the host arrays */
 int zb_scene_upload(zb_context* ctx, const zb_flat_scene* flat, zb_scene** out);
 int zb_scene_destroy(zb_scene* scene);
+/* Transform-only scene edit without re-flattening (the reference rebuilds geometry and BVH on every GUI
+ * restart, main.cpp:1492-1500): `instances` = the scene's instance table with NEW transforms (same count, same geometry
+ * references — e.g. the table of a re-run flattener, or the uploaded one with w2o / o2w edited).  The table is copied to the
+ * GPU(s), the world boxes of the items that reference instances are recomputed from the object-space bounds of their
+ * geometry, and the TLAS is refitted bottom-up ON THE DEVICE with its topology unchanged; BLASes, materials and textures
+ * are untouched.  One small kernel (k_refit_tlas): well under a millisecond for thousands of items.  Closest hits equal
+ * those of a freshly flattened scene; a heavily rearranged scene traverses faster after a full re-flatten (SAH topology).
+ * Needs zb_flat_scene::item_bounds at upload and host-built BLASes; an 8-wide tree, if any, is dropped (not refitted). */
+int zb_scene_refit(zb_scene* scene, const zb_instance* instances, uint32_t n_instances);
 
 /* Drop-in for camera::render's hot part (camera.hpp:236-250 -> :404-579): blocking; fills host
  * buffers.  `cancel` mirrors render_flag inverted (non-zero = stop, camera.hpp:441). */

@@ -33,7 +33,7 @@ class FlatScene(C.Structure):
         ("tri_normals", C.c_void_p), ("instances", C.c_void_p), ("meshes", C.c_void_p), ("media", C.c_void_p),
         ("materials", C.c_void_p), ("textures", C.c_void_p), ("spheres_obj", C.c_void_p),
         ("texels_u8", C.c_void_p), ("texels_f32", C.c_void_p), ("n_leaves", C.c_uint32), ("pad", C.c_uint32),
-        ("n_wide_nodes", C.c_uint32), ("wide_stack_need", C.c_uint32), ("wide_nodes", C.c_void_p),
+        ("n_wide_nodes", C.c_uint32), ("wide_stack_need", C.c_uint32), ("wide_nodes", C.c_void_p), ("item_bounds", C.c_void_p),
     ]
 
     def meshes_array(self):
@@ -129,6 +129,7 @@ SYMBOLS = {
     "zb_device_info": (C.c_int, [C.c_void_p, C.POINTER(C.c_int), C.POINTER(C.c_int), C.POINTER(C.c_int), C.POINTER(C.c_size_t)]),
     "zb_scene_upload": (C.c_int, [C.c_void_p, C.POINTER(FlatScene), C.POINTER(C.c_void_p)]),
     "zb_scene_destroy": (C.c_int, [C.c_void_p]),
+    "zb_scene_refit": (C.c_int, [C.c_void_p, C.c_void_p, C.c_uint32]),
     "zb_render": (C.c_int, [C.c_void_p, C.c_void_p, C.POINTER(Camera), C.POINTER(Environment), C.POINTER(RenderOpts),
                             C.POINTER(Outputs), C.POINTER(C.c_int), PROGRESS_FN, C.c_void_p]),
     "zb_probe_rays": (C.c_int, [C.c_void_p, C.c_void_p, C.POINTER(Environment), C.c_size_t, C.c_void_p, C.c_void_p, C.c_void_p]),

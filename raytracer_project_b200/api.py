@@ -372,6 +372,11 @@ class Scene:
         assert n == res["beauty"].shape[0] * res["beauty"].shape[1]
         return res
 
+    def refit(self, flat_with_new_transforms):
+        """zb_scene_refit: take the instance table (new transforms, same geometry) of another flattened scene."""
+        f = flat_with_new_transforms.contents
+        check(self.ctx.lib.zb_scene_refit(self.h, f.instances, f.n_instances))
+
     def render_into(self, cfg: RenderConfig, buffers: dict, seed=1, partition="auto", samples_per_launch=0):
         """zb_render into caller-owned (H, W, 3) float64 arrays keyed like render()'s result — e.g. views of one frame in
         shared memory that all ranks of a multi-process group write their bands into."""

@@ -422,6 +422,13 @@ static int upload_one(zb_context* ctx, const zb_flat_scene* f, zb_scene** out) {
         zb_scene_destroy(s);
         return rc;
     }
+    if (!device_blas) {
+        rc = zbr_prepare_refit(s, f, instances);
+        if (rc) {
+            zb_scene_destroy(s);
+            return rc;
+        }
+    }
     d.n_items = f->n_items;
     d.n_media = f->n_media;
     d.overflow = ctx->counters + 6;

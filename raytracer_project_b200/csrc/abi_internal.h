@@ -66,6 +66,16 @@ struct zb_context {
 struct zb_scene {
     zb_context* ctx = nullptr;
     const float4* wide = nullptr;  // the scene's 8-wide tree on the device (null: none)
+    struct refit_state {  // what zb_scene_refit needs (refit.cu); ready == false: the scene cannot be refitted
+        bool ready = false;
+        float4* inst_bounds = nullptr;   // object-space bounds of every instance's geometry
+        float4* item_bounds = nullptr;   // world bounds of every item
+        float4* node_bounds = nullptr;   // scratch: bounds of every TLAS node
+        uint32_t* order = nullptr;       // TLAS nodes grouped by level, deepest first
+        std::vector<uint32_t> level_start;
+        std::vector<zb_instance> host_instances;
+        uint32_t n_tlas_nodes = 0, n_items = 0;
+    } refit;
     std::vector<zb_scene*> replicas;  // scene of a multi-device context: copies on the other members
     SceneDev dev{};
     std::vector<void*> allocs;
@@ -119,3 +129,6 @@ int zbg_render(zb_context* ctx, const zb_scene* scene, const zb_camera* cam, con
                const zb_render_opts* opts, zb_outputs* out, const volatile int* cancel, zb_progress_fn progress, void* user);
 bool zbg_fast_path(const zb_context* ctx, const zb_render_opts* opts, const zb_outputs* out);
 void zbg_release(zb_context* ctx);
+
+// refit.cu
+int zbr_prepare_refit(zb_scene* s, const zb_flat_scene* f, const zb_instance* instances);

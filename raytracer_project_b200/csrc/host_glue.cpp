@@ -94,8 +94,8 @@ extern "C" int zb_flat_scene_from_zscene_ex(const char* path, const char* text, 
 // "ZBFS" container: a flattened scene written once (rank 0, or an offline tool) and loaded by every rank / every
 // later run without re-parsing OBJ files and re-building the BVH.  Little-endian PODs exactly as in zenith_b200.h:
 //   char magic[4] = "ZBFS"; u32 abi_version; u32 n_tlas_nodes, n_leaves, env_hdr_texture, reserved;
-//   (reserved = wide_stack_need), then 14 sections, each = u64 byte count + payload padded to 16 bytes, in the order of
-//   zb_flat_scene's pointers (the 8-wide nodes last).
+//   (reserved = wide_stack_need), then 15 sections, each = u64 byte count + payload padded to 16 bytes, in the order of
+//   zb_flat_scene's pointers (the 8-wide nodes and the item bounds last).
 namespace {
 template <class T> bool put(std::ofstream& f, const std::vector<T>& v) {
     const uint64_t bytes = uint64_t(v.size()) * sizeof(T);
@@ -152,7 +152,8 @@ extern "C" int zb_flat_scene_save(const zb_flat_scene* v, const char* path) {
               put(f, span_of(v->media, v->n_media)) && put(f, span_of(v->materials, v->n_materials)) &&
               put(f, span_of(v->textures, v->n_textures)) && put(f, span_of(v->spheres_obj, uint64_t(v->n_spheres_obj) * 4)) &&
               put(f, span_of(v->texels_u8, v->n_texels_u8 * 4)) && put(f, span_of(v->texels_f32, v->n_texels_f32 * 4)) &&
-              put(f, span_of(v->wide_nodes, v->n_wide_nodes));
+              put(f, span_of(v->wide_nodes, v->n_wide_nodes)) &&
+              put(f, span_of(v->item_bounds, v->item_bounds ? uint64_t(v->n_items) * 8 : 0));
     f.close();
     if (!ok || !f) return fail_host(ZB_ERR_IO, std::string("short write to ") + path);
     return ZB_OK;
@@ -175,7 +176,7 @@ extern "C" int zb_flat_scene_load(const char* path, const zb_flat_scene** out) {
     fs->wide_stack_need = hdr[4];
     bool ok = get(f, fs->nodes) && get(f, fs->items) && get(f, fs->cubes) && get(f, fs->tris) && get(f, fs->tri_normals) &&
               get(f, fs->instances) && get(f, fs->meshes) && get(f, fs->media) && get(f, fs->materials) && get(f, fs->textures) &&
-              get(f, fs->spheres_obj) && get(f, fs->texels_u8) && get(f, fs->texels_f32) && get(f, fs->wide_nodes);
+              get(f, fs->spheres_obj) && get(f, fs->texels_u8) && get(f, fs->texels_f32) && get(f, fs->wide_nodes) && get(f, fs->item_bounds);
     if (!ok || fs->tris.size() != fs->tri_normals.size()) return fail_host(ZB_ERR_INVALID, std::string(path) + ": truncated or malformed flat scene");
     const zb_flat_scene* view = fs->finish();  // zb_scene_upload validates every index before anything is used
     std::lock_guard<std::mutex> lock(g_mu);

@@ -23,6 +23,7 @@ struct flat_scene {
     std::vector<zb_bvh_node> nodes;
     std::vector<zb_wide_node> wide_nodes;
     uint32_t wide_stack_need = 0;
+    std::vector<float> item_bounds;  // 8 floats per item, items[] order
     std::vector<zb_item> items;
     std::vector<zb_cube> cubes;
     std::vector<zb_tri> tris;
@@ -72,6 +73,7 @@ struct flat_scene {
         view.n_wide_nodes = uint32_t(wide_nodes.size());
         view.wide_stack_need = wide_stack_need;
         view.wide_nodes = wide_nodes.empty() ? nullptr : wide_nodes.data();
+        view.item_bounds = item_bounds.size() == items.size() * 8 ? item_bounds.data() : nullptr;
         return &view;
     }
 };
@@ -119,6 +121,13 @@ public:
         std::vector<zb_item> sorted(order.size());
         for (size_t i = 0; i < order.size(); i++) sorted[i] = out->items[order[i]];
         out->items.swap(sorted);
+        out->item_bounds.resize(order.size() * 8);
+        for (size_t i = 0; i < order.size(); i++) {
+            const build_box& bb = item_boxes[order[i]];
+            float* q = &out->item_bounds[8 * i];
+            for (int k = 0; k < 3; k++) { q[k] = round_down(bb.lo[k]); q[4 + k] = round_up(bb.hi[k]); }
+            q[3] = q[7] = 0.f;
+        }
         out->n_tlas_nodes = uint32_t(tl.size());
         // BLAS nodes were collected with mesh-local child indices; append them after the TLAS
         std::vector<zb_bvh_node> all = tl;

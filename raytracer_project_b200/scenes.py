@@ -612,6 +612,36 @@ def kat_scene(env: str = "solid"):
     return w.text(), cfg, files
 
 
+def refit_demo(move: float = 0.0, width: int = 320, height: int = 180, spp: int = 16):
+    """Scene of the zb_scene_refit test: plain spheres (their items never move), and instances of every geometry kind —
+    cube under translate(rotate_y), sphere under translate(scale), two shipped OBJ meshes under translate(rotate_x(scale)),
+    a fog whose boundary is a scaled sphere — whose wrapper parameters depend on `move`; the object graph (and therefore
+    the instance table's geometry references) is the same for every value of `move`."""
+    w = SceneWriter()
+    files = {"assets/models/torus.obj": shipped_asset("models/torus.obj"), "assets/models/pyramid.obj": shipped_asset("models/pyramid.obj")}
+    grey, red, gold, glass = w.lambertian((0.5, 0.5, 0.5)), w.lambertian((0.8, 0.15, 0.1)), w.metal((1.0, 0.8, 0.4), 0.1), w.dielectric(1.5)
+    objs = [w.sphere((0, -300, 0), 300.0, grey), w.sphere((-3.5, 0.5, 1.0), 0.5, gold), w.sphere((3.6, 0.4, 1.4), 0.4, red),
+            w.sphere((0.0, 4.0, 0.0), 0.7, w.light((5.0, 4.5, 4.0)))]
+    m = move
+    box = w.cube((-0.4, -0.4, -0.4), (0.4, 0.4, 0.4), red)
+    objs.append(w.translate(w.rotate("y", box, 0.3 + 0.9 * m), (-2.0 + 1.5 * m, 0.4, -0.5 + 0.8 * m)))
+    objs.append(w.translate(w.rotate("y", box, 1.1 - 0.5 * m), (2.2 - 0.7 * m, 0.4, -1.0)))
+    ball = w.sphere((0, 0, 0), 0.5, glass)
+    objs.append(w.translate(w.scale(ball, (1.0 + 0.5 * m, 0.7, 1.0)), (0.0 + 0.6 * m, 0.35 + 0.3 * m, 1.2)))
+    torus = w.model("assets/models/torus.obj", None, 0.25)
+    pyramid = w.model("assets/models/pyramid.obj", None, 0.4)
+    objs.append(w.translate(w.rotate("x", w.scale(w.matinst(torus, gold), (1.0, 1.0 + 0.5 * m, 1.0)), 20.0 + 40.0 * m), (-0.8 - 0.9 * m, 0.5, -1.8 + 0.5 * m)))
+    objs.append(w.translate(w.rotate("x", w.scale(w.matinst(torus, red), (0.8, 0.8, 0.8)), -15.0 * m), (1.0 + 0.8 * m, 0.3 + 0.4 * m, 0.2)))
+    objs.append(w.translate(w.rotate("y", w.matinst(pyramid, gold), 0.4 + m), (3.0 - 1.2 * m, 0.0, -2.2 + 0.6 * m)))
+    room = w.container("bvh", objs, name="room")
+    fog = w.medium(w.scale(w.sphere((0, 0.5, 0), 2.5, None), (1.0 + 0.4 * m, 0.6, 1.0)), 0.05, rgb=(0.9, 0.9, 1.0))
+    w.world(w.container("list", [room, fog], name="world"))
+    cfg = RenderConfig(
+        image_width=width, image_height=height, samples_per_pixel=spp, max_depth=20, vfov=38.0, lookfrom=(0.5, 2.4, 7.0),
+        lookat=(0.2, 0.4, 0.0), vup=(0.0, 1.0, 0.0), defocus_angle=0.0, focus_dist=8.0, env_mode="solid", background=(0.6, 0.7, 0.9))
+    return w.text(), cfg, files
+
+
 def wire_demo(seed: int = 7, width: int = 240, height: int = 135, spp: int = 64, max_depth: int = 50):
     """Scene of the BVH debug-view tests: 24 seeded spheres, two cubes and a lamp inside a region
     the camera sees whole, so the root box of the tree (level 0 — the one level that does not depend on how the

@@ -813,3 +813,45 @@ def test_wide_tree_traversal_equals_binary_tree(name, gpu_ctx, tmp_path):
     assert abs(img0.mean() - img1.mean()) < 2e-3 * img0.mean()
     if name != "exterior":
         assert st1["node_visits"] < 0.8 * st0["node_visits"]
+
+
+# ------------------------------------------------------------------ transform-only edits
+def test_scene_refit_equals_fresh_flatten(gpu_ctx, tmp_path):
+    """zb_scene_refit: the scene uploaded at move = 0, handed the instance table of the same graph flattened at move = 1
+    (every wrapper's translation / rotation / scale changed, the fog's boundary too), must answer every ray like a fresh
+    flatten + upload of the moved scene — same primary ids and distances, same frame — while only the TLAS boxes were
+    refitted on the device (topology of move = 0, BLASes untouched); and back again."""
+    import time
+    flats = {}
+    for m in (0.0, 1.0):
+        txt, cfg, files = scenes.refit_demo(move=m)
+        d = tmp_path / f"m{int(m)}"
+        flats[m] = api.flatten_zscene(path=scenes.materialize(str(d), txt, cfg, files))
+    f0, f1 = flats[0.0].contents, flats[1.0].contents
+    assert f0.n_instances == f1.n_instances >= 7 and f0.n_items == f1.n_items and f0.item_bounds
+    sc = gpu_ctx.upload(flats[0.0])
+    fresh = {m: gpu_ctx.upload(flats[m]) for m in (0.0, 1.0)}
+    ids0 = sc.primary_ids(cfg)
+    for m in (1.0, 0.0, 1.0):
+        t0 = time.perf_counter()
+        sc.refit(flats[m])
+        dt = (time.perf_counter() - t0) * 1e3
+        leaf, prim, t = sc.primary_ids(cfg)
+        leaf_f, prim_f, t_f = fresh[m].primary_ids(cfg)
+        print(f"move {m}: refit {dt:.3f} ms (upload of the instance table + k_refit_tlas + sync); hit fraction {(leaf != 0xFFFFFFFF).mean():.3f}")
+        assert np.array_equal(leaf, leaf_f) and np.array_equal(prim, prim_f) and np.array_equal(t, t_f), m
+        a, b = sc.render(cfg, seed=4)["beauty"], fresh[m].render(cfg, seed=4)["beauty"]
+        assert np.array_equal(a, b), (m, np.abs(a - b).max())
+        assert dt < 5.0
+    assert not np.array_equal(ids0[0], leaf)  # the edit is visible
+    assert gpu_ctx.stats()["stack_overflows"] == 0
+    # anything but a transform is refused
+    other, _, files2 = scenes.quirks()
+    (tmp_path / "q").mkdir()
+    q = api.flatten_zscene(path=scenes.materialize(str(tmp_path / "q"), other, cfg, files2))
+    with pytest.raises(api._lib.ZbError):
+        sc.refit(q)
+    for s in [sc] + list(fresh.values()):
+        s.close()
+    for f in list(flats.values()) + [q]:
+        api.free_flat(f)
