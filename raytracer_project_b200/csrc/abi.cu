@@ -65,6 +65,7 @@ extern "C" int zb_context_set_tuning(zb_context* ctx, const char* key, long long
     else if (k == "pq_blocks") t.pq_blocks = int(value);
     else if (k == "gather_p2p") t.gather_p2p = int(value);
     else if (k == "wide") t.wide = value != 0;
+    else if (k == "fuse_finish") t.fuse_finish = value != 0;
 #ifdef ZB_EXPERIMENTS
     else if (k == "pq_resume") t.pq_resume = int(value);
     else if (k == "wavefront") t.wavefront = value != 0;

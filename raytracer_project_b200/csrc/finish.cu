@@ -147,18 +147,19 @@ ZB_DEV float3 clamp_gamma(float3 c) {
 ZB_DEV float aces1(float v) {  // common.hpp:48-64
     if (isnan(v) || isinf(v)) return 0.f;
     float x = fmaxf(0.f, v);
-    return (x * (2.51f * x + 0.03f)) / (x * (2.43f * x + 0.59f) + 0.14f);
+    return __fdividef(x * (2.51f * x + 0.03f), x * (2.43f * x + 0.59f) + 0.14f);  // MUFU.RCP + FMUL (2 ulp); the IEEE divide is ~10 instructions
 }
 // color_processing.hpp:280-306
 ZB_DEV float3 rgb_to_hsv(float3 c) {
     float mx = fmaxf(c.x, fmaxf(c.y, c.z)), mn = fminf(c.x, fminf(c.y, c.z));
     float d = mx - mn, h = 0.f;
-    float s = mx < 1e-6f ? 0.f : d / mx;
+    float s = mx < 1e-6f ? 0.f : __fdividef(d, mx);
     if (mx != mn) {
-        if (mx == c.x) h = (c.y - c.z) / d + (c.y < c.z ? 6.f : 0.f);
-        else if (mx == c.y) h = (c.z - c.x) / d + 2.f;
-        else h = (c.x - c.y) / d + 4.f;
-        h /= 6.f;
+        const float inv_d = __fdividef(1.0f, d);
+        if (mx == c.x) h = (c.y - c.z) * inv_d + (c.y < c.z ? 6.f : 0.f);
+        else if (mx == c.y) h = (c.z - c.x) * inv_d + 2.f;
+        else h = (c.x - c.y) * inv_d + 4.f;
+        h *= (1.0f / 6.f);
     }
     return f3(h * 360.f, s, mx);
 }
@@ -193,8 +194,10 @@ ZB_DEV float3 process(float3 c, float u, float v, const PostDev& P) {
     if (fabsf(P.saturation - 1.0f) > 0.001f || fabsf(P.hue_shift) > 0.001f) {
         float luma = luminance(c);
         if (luma > 0.0001f) {
-            float3 hsv = rgb_to_hsv((1.0f / luma) * c);
-            hsv.x = fmodf(hsv.x + P.hue_shift, 360.f);
+            float3 hsv = rgb_to_hsv(__fdividef(1.0f, luma) * c);
+            // fmodf(h + shift, 360) as h - 360 trunc(h / 360): fmodf is a ~40-instruction loop, this is four
+            hsv.x += P.hue_shift;
+            hsv.x = fmaf(-360.f, truncf(hsv.x * (1.0f / 360.f)), hsv.x);
             if (hsv.x < 0.f) hsv.x += 360.f;
             hsv.y = fminf(fmaxf(hsv.y * P.saturation, 0.f), 1.f);
             c = luma * hsv_to_rgb(hsv);
@@ -274,6 +277,143 @@ __global__ void __launch_bounds__(128) k_finish(const float4* __restrict__ src, 
                 if (x0 + k < W) out_u8[row + x0 + k] = packed[k];
         }
     }
+}
+
+// ---------------------------------------------------------------------------------- fused beauty chain with bloom
+// update_post_processing with bloom as ONE pass over the frame (radius <= ZB_FUSED_MAX_R; the reference's default is 4):
+// a block owns a 64x32 tile and stages, in shared memory, (1) the bright pass of the tile + (r + 1) halo and the exposed
+// colour of the tile + 1, (2) the horizontal tent blur of those rows, (3) the vertical blur of the tile + 1 — the bloom
+// plane the 5-tap sharpening needs at its four neighbours — then (4) sharpens, runs process() and stores RGBA8 / float4.
+// Same arithmetic, in the same order, as k_bloom_h + k_bloom_v + k_finish.  Algorithmic bytes: 16 in + 4 (RGBA8) or 16
+// (float4) out per pixel instead of 100 (two float4 planes written and re-read, sharpening taps through L2); the halo
+// (1.5x the tile at r = 4) is shared with the neighbouring tiles through L2.
+#define ZB_FUSED_MAX_R 6
+#define ZB_FT_W 64
+#define ZB_FT_H 32
+__global__ void __launch_bounds__(256) k_finish_fused(const float4* __restrict__ src, int W, int H, PostDev P, float4* __restrict__ out_f4,
+                                                      uchar4* __restrict__ out_u8) {
+    extern __shared__ float smem[];
+    const int r = P.bloom_radius, h = r + 1;
+    const int RA = ZB_FT_H + 2 * h, CA = ZB_FT_W + 2 * h, CB = ZB_FT_W + 2, RD = ZB_FT_H + 2;
+    float* A = smem;                    // [3][RA][CA] bright pass; re-used as C = [3][RD][CB] bloom after stage 2
+    float* B = A + 3 * RA * CA;         // [3][RA][CB] horizontally blurred
+    float* D = B + 3 * RA * CB;         // [3][RD][CB] exposed colour ev * src
+    float* Cb = A;
+    const int x0 = blockIdx.x * ZB_FT_W, y0 = blockIdx.y * ZB_FT_H;
+    const float inv_r1 = 1.0f / float(r + 1);
+    // ---- 1: bright pass over the tile + h halo, exposed colour over the tile + 1
+    for (int i = threadIdx.x; i < RA * CA; i += 256) {
+        const int cy = i / CA, cx = i - cy * CA;
+        const int gx = x0 - h + cx, gy = y0 - h + cy;
+        float3 b = f3(0, 0, 0), e = f3(0, 0, 0);
+        if (gx >= 0 && gx < W && gy >= 0 && gy < H) {
+            const float4 p = __ldg(src + size_t(gy) * W + gx);
+            b = bright_pass(p, P);
+            e = P.ev * f3(p);
+        }
+        A[i] = b.x;
+        A[RA * CA + i] = b.y;
+        A[2 * RA * CA + i] = b.z;
+        const int dx = cx - r, dy = cy - r;  // position in the tile + 1 region
+        if (dx >= 0 && dx < CB && dy >= 0 && dy < RD) {
+            const int j = dy * CB + dx;
+            D[j] = e.x;
+            D[RD * CB + j] = e.y;
+            D[2 * RD * CB + j] = e.z;
+        }
+    }
+    __syncthreads();
+    // ---- 2: horizontal tent blur (bloom.hpp:48-67) of every staged row, for the columns of the tile + 1
+    for (int i = threadIdx.x; i < RA * CB; i += 256) {
+        const int cy = i / CB, x = i - cy * CB;
+        const int gx = x0 - 1 + x;
+        float3 sum = f3(0, 0, 0);
+        float total = 0.f;
+        if (gx >= 0 && gx < W) {
+            const float* a = A + cy * CA + x + r;  // column of gx in A = x - 1 + h = x + r
+            for (int o = -r; o <= r; o++) {
+                if (gx + o < 0 || gx + o >= W) continue;
+                const float w = 1.0f - float(abs(o)) * inv_r1;
+                sum += w * f3(a[o], a[RA * CA + o], a[2 * RA * CA + o]);
+                total += w;
+            }
+        }
+        const float inv = total > 0.f ? 1.0f / total : 0.f;
+        B[i] = sum.x * inv;
+        B[RA * CB + i] = sum.y * inv;
+        B[2 * RA * CB + i] = sum.z * inv;
+    }
+    __syncthreads();
+    // ---- 3: vertical blur for the rows of the tile + 1 (A is dead: the bloom plane takes its place)
+    for (int i = threadIdx.x; i < RD * CB; i += 256) {
+        const int y = i / CB, x = i - y * CB;
+        const int gy = y0 - 1 + y;
+        float3 sum = f3(0, 0, 0);
+        float total = 0.f;
+        if (gy >= 0 && gy < H) {
+            const float* b = B + (y + r) * CB + x;  // row of gy in B = y - 1 + h = y + r
+            for (int o = -r; o <= r; o++) {
+                if (gy + o < 0 || gy + o >= H) continue;
+                const float w = 1.0f - float(abs(o)) * inv_r1;
+                sum += w * f3(b[o * CB], b[RA * CB + o * CB], b[2 * RA * CB + o * CB]);
+                total += w;
+            }
+        }
+        const float inv = total > 0.f ? 1.0f / total : 0.f;
+        Cb[i] = sum.x * inv;
+        Cb[RD * CB + i] = sum.y * inv;
+        Cb[2 * RD * CB + i] = sum.z * inv;
+    }
+    __syncthreads();
+    // ---- 4: t = ev * src + bloom, 5-tap sharpening of interior pixels, process(), store; 4 consecutive pixels per thread
+    auto tap = [&](int tx, int ty) {  // tile coordinates, -1 .. tile size
+        const int j = (ty + 1) * CB + tx + 1;
+        float3 t = f3(D[j], D[RD * CB + j], D[2 * RD * CB + j]);
+        t += f3(Cb[j], Cb[RD * CB + j], Cb[2 * RD * CB + j]);
+        return t;
+    };
+    const float inv_w = 1.0f / float(W - 1);
+    for (int q = threadIdx.x; q < ZB_FT_W * ZB_FT_H / 4; q += 256) {
+        const int ty = q / (ZB_FT_W / 4), tx0 = (q - ty * (ZB_FT_W / 4)) * 4;
+        const int y = y0 + ty, xg0 = x0 + tx0;
+        if (y >= H || xg0 >= W) continue;
+        const float v = float(y) / float(H - 1);
+        uchar4 packed[4];
+        float3 res[4];
+#pragma unroll
+        for (int k = 0; k < 4; k++) {
+            const int x = xg0 + k;
+            const float3 c = tap(tx0 + k, ty);
+            float3 o = c;
+            if (P.sharpen && y >= 1 && y < H - 1 && x >= 1 && x < W - 1) {  // color_processing.hpp:218-219
+                const float3 sum = 5.0f * c - tap(tx0 + k, ty - 1) - tap(tx0 + k, ty + 1) - tap(tx0 + k - 1, ty) - tap(tx0 + k + 1, ty);
+                o = (1.0f - P.sharpen_amount) * c + P.sharpen_amount * sum;
+            }
+            o = process(o, float(x) * inv_w, v, P);
+            res[k] = o;
+            packed[k] = make_uchar4((unsigned char)(255.999f * o.x), (unsigned char)(255.999f * o.y), (unsigned char)(255.999f * o.z), 255);
+        }
+        const size_t row = size_t(y) * W;
+        if (out_f4) {
+#pragma unroll
+            for (int k = 0; k < 4; k++)
+                if (xg0 + k < W) out_f4[row + xg0 + k] = make_float4(res[k].x, res[k].y, res[k].z, 1.0f);
+        }
+        if (out_u8) {
+            if (xg0 + 4 <= W && (W % 4) == 0) {
+                *reinterpret_cast<uint4*>(out_u8 + row + xg0) = *reinterpret_cast<uint4*>(packed);
+            } else {
+#pragma unroll
+                for (int k = 0; k < 4; k++)
+                    if (xg0 + k < W) out_u8[row + xg0 + k] = packed[k];
+            }
+        }
+    }
+}
+
+size_t fused_smem_bytes(int r) {
+    const int h = r + 1, RA = ZB_FT_H + 2 * h, CA = ZB_FT_W + 2 * h, CB = ZB_FT_W + 2, RD = ZB_FT_H + 2;
+    return sizeof(float) * 3 * size_t(RA * CA + RA * CB + RD * CB);
 }
 
 // ---------------------------------------------------------------------------------- C ABI
@@ -363,6 +503,20 @@ extern "C" int zb_finish_device(zb_context* ctx, const void* mean_f4, int width,
     const size_t pixels = size_t(width) * height;
     const float4* src = static_cast<const float4*>(mean_f4);
     const float4* overlay = nullptr;
+    if (pass_kind == ZB_PASS_BEAUTY && P.bloom && P.bloom_radius <= ZB_FUSED_MAX_R && ctx->tuning.fuse_finish) {
+        // bloom + sharpening + process() in one pass over shared-memory tiles
+        const size_t smem = fused_smem_bytes(P.bloom_radius);
+        static bool attr_set[64] = {};
+        if (ctx->device < 64 && !attr_set[ctx->device]) {
+            ZB_CUDA(cudaFuncSetAttribute(k_finish_fused, cudaFuncAttributeMaxDynamicSharedMemorySize, int(fused_smem_bytes(ZB_FUSED_MAX_R))));
+            attr_set[ctx->device] = true;
+        }
+        k_finish_fused<<<dim3((width + ZB_FT_W - 1) / ZB_FT_W, (height + ZB_FT_H - 1) / ZB_FT_H), 256, smem, ctx->stream>>>(
+            src, width, height, P, static_cast<float4*>(out_f4), static_cast<uchar4*>(out_rgba8));
+        ZB_CUDA(cudaGetLastError());
+        ctx->stats.launches++;
+        return ZB_OK;
+    }
     if (pass_kind == ZB_PASS_BEAUTY && P.bloom) {
         int rc = ensure_finish_scratch(ctx, pixels, true);
         if (rc) return rc;

@@ -855,3 +855,30 @@ def test_scene_refit_equals_fresh_flatten(gpu_ctx, tmp_path):
         s.close()
     for f in list(flats.values()) + [q]:
         api.free_flat(f)
+
+
+def test_fused_finishing_kernel_equals_three_kernel_chain(gpu_ctx):
+    """k_finish_fused (bloom + sharpening + process() in one pass over shared-memory tiles) against k_bloom_h + k_bloom_v +
+    k_finish on a frame whose size is not a multiple of the tile (ragged edges, image borders inside the halo), for several
+    radii and parameter sets: the same arithmetic in the same order, so the float4 results agree to rounding and the
+    RGBA8 results to one step on a vanishing fraction of the channels."""
+    import torch
+    W, H = 203, 117
+    g = torch.Generator(device="cuda").manual_seed(7)
+    src = (torch.rand(W * H, 4, device="cuda", generator=g) ** 3) * 6.0
+    for kw in (dict(use_bloom=1), dict(use_bloom=1, bloom_radius=1, use_sharpening=1), dict(use_bloom=1, bloom_radius=6, use_sharpening=1, use_aces=1),
+               dict(use_bloom=1, bloom_radius=3, bloom_threshold=0.5, bloom_intensity=0.8, use_sharpening=1, saturation=1.3, hue_shift=25.0, contrast=1.1)):
+        outs = {}
+        for fuse in (1, 0):
+            gpu_ctx.set_tuning("fuse_finish", fuse)
+            f4 = torch.zeros(W * H, 4, device="cuda")
+            u8 = torch.zeros(W * H, 4, device="cuda", dtype=torch.uint8)
+            gpu_ctx.finish_device(src.data_ptr(), W, H, api.post_struct(**kw), 0, f4.data_ptr(), u8.data_ptr())
+            torch.cuda.synchronize()
+            outs[fuse] = (f4.cpu().numpy(), u8.cpu().numpy().astype(np.int32))
+        gpu_ctx.set_tuning("fuse_finish", 1)
+        df = np.abs(outs[1][0] - outs[0][0]).max()
+        du = np.abs(outs[1][1] - outs[0][1])
+        print(kw, "max |float4 diff|", df, "RGBA8 steps differing", float((du != 0).mean()))
+        assert df < 2e-6 and du.max() <= 1 and (du != 0).mean() < 1e-3, (kw, df, du.max())
+        assert outs[1][0][:, :3].mean() > 0.05

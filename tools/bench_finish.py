@@ -44,7 +44,10 @@ cases = {
     "finish_plain_f4": (lambda: ctx.finish_device(src.data_ptr(), a.width, a.height, api.post_struct(), 0, out_f4.data_ptr(), 0), 32),
     "finish_plain_rgba8": (lambda: ctx.finish_device(src.data_ptr(), a.width, a.height, api.post_struct(), 0, 0, out_u8.data_ptr()), 20),
     "finish_sharpen_aces_hsv_rgba8": (lambda: ctx.finish_device(src.data_ptr(), a.width, a.height, api.post_struct(use_sharpening=1, use_aces=1, saturation=1.2, hue_shift=10.0), 0, 0, out_u8.data_ptr()), 20),
-    "finish_bloom_sharpen_rgba8 (3 kernels)": (lambda: ctx.finish_device(src.data_ptr(), a.width, a.height, api.post_struct(use_bloom=1, use_sharpening=1, use_aces=1), 0, 0, out_u8.data_ptr()), 32 + 32 + 36),
+    "finish_bloom_sharpen_aces_rgba8 (k_finish_fused, 20 B/px)": (lambda: ctx.finish_device(src.data_ptr(), a.width, a.height, api.post_struct(use_bloom=1, use_sharpening=1, use_aces=1), 0, 0, out_u8.data_ptr()), 20),
+    "finish_bloom_sharpen_aces_f4 (k_finish_fused, 32 B/px)": (lambda: ctx.finish_device(src.data_ptr(), a.width, a.height, api.post_struct(use_bloom=1, use_sharpening=1, use_aces=1), 0, out_f4.data_ptr(), 0), 32),
+    "finish_bloom_sharpen_aces_rgba8 (3 kernels, 100 B/px)": (lambda: (ctx.set_tuning("fuse_finish", 0), ctx.finish_device(src.data_ptr(), a.width, a.height, api.post_struct(use_bloom=1, use_sharpening=1, use_aces=1), 0, 0, out_u8.data_ptr()), ctx.set_tuning("fuse_finish", 1)), 32 + 32 + 36),
+    "finish_bloom_r8_rgba8 (radius 8 > fused limit: 3 kernels)": (lambda: ctx.finish_device(src.data_ptr(), a.width, a.height, api.post_struct(use_bloom=1, bloom_radius=8), 0, 0, out_u8.data_ptr()), 32 + 32 + 36),
     "aux_pass_rgba8": (lambda: ctx.finish_device(src.data_ptr(), a.width, a.height, api.post_struct(), 2, 0, out_u8.data_ptr()), 20),
 }
 for name, (fn, bpp) in cases.items():
