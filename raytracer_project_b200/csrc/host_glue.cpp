@@ -19,6 +19,8 @@ using namespace zenith;
 #include "../host/zscene.hpp"
 
 std::string& zb_err_slot();
+extern "C" void zbi_pin_flat_scene(const zb_flat_scene* f, int pin);  // abi.cu: page-lock the large arrays for fast uploads
+
 static int fail_host(int code, const std::string& msg) {
     zb_err_slot() = msg;
     return code;
@@ -49,6 +51,7 @@ int load(std::istream& in, const std::string& base_dir, const zb_flat_scene** ou
         if (!ld.env_hdr_path.empty()) env.load_hdr(ld.path_of(ld.env_hdr_path));  // environment.hpp:46-69
         std::unique_ptr<flat_scene> fs = fl.run(*world, &env);
         const zb_flat_scene* view = &fs->view;
+        zbi_pin_flat_scene(view, 1);
         std::lock_guard<std::mutex> lock(g_mu);
         g_live[view] = std::move(fs);
         *out = view;
@@ -179,6 +182,7 @@ extern "C" int zb_flat_scene_load(const char* path, const zb_flat_scene** out) {
               get(f, fs->spheres_obj) && get(f, fs->texels_u8) && get(f, fs->texels_f32) && get(f, fs->wide_nodes) && get(f, fs->item_bounds);
     if (!ok || fs->tris.size() != fs->tri_normals.size()) return fail_host(ZB_ERR_INVALID, std::string(path) + ": truncated or malformed flat scene");
     const zb_flat_scene* view = fs->finish();  // zb_scene_upload validates every index before anything is used
+    zbi_pin_flat_scene(view, 1);
     std::lock_guard<std::mutex> lock(g_mu);
     g_live[view] = std::move(fs);
     *out = view;
@@ -187,6 +191,7 @@ extern "C" int zb_flat_scene_load(const char* path, const zb_flat_scene** out) {
 
 extern "C" int zb_flat_scene_free(const zb_flat_scene* flat) {
     std::lock_guard<std::mutex> lock(g_mu);
+    if (g_live.count(flat)) zbi_pin_flat_scene(flat, 0);
     g_live.erase(flat);
     return ZB_OK;
 }
