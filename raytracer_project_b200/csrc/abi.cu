@@ -68,6 +68,7 @@ extern "C" int zb_context_set_tuning(zb_context* ctx, const char* key, long long
     else if (k == "fuse_finish") t.fuse_finish = value != 0;
 #ifdef ZB_EXPERIMENTS
     else if (k == "pq_resume") t.pq_resume = int(value);
+    else if (k == "pq_redeal") t.pq_redeal = int(value);
     else if (k == "wavefront") t.wavefront = value != 0;
     else if (k == "wf_slots") t.wf_slots = value;
 #endif

@@ -148,6 +148,7 @@ int fill_params(zb_context* ctx, const zb_scene* scene, const zb_camera* cam, co
     std::memset(&P, 0, sizeof(P));
     P.sc = scene->dev;
     if (!ctx->tuning.wide) P.sc.wide = nullptr;
+    P.exp_flags = ctx->tuning.pq_redeal;
     int rc = setup_camera(cam, P.cam);
     if (rc) return rc;
     rc = setup_env(env, scene, P.env);

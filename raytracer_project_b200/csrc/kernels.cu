@@ -408,6 +408,40 @@ __global__ void __launch_bounds__(ZB_BLOCK_THREADS, MIN_BLOCKS) k_render_pq(cons
                 w_pos += want;
             }
         }
+#ifdef ZB_EXPERIMENTS
+        // VERDICT r1 item 6 (experiment, tuning "pq_redeal"): coherence between bounces.  1 = every segment of the block starts
+        // at a block-wide barrier (what any re-dealing inside a persistent block needs); 2 = the block's 128 rays are also
+        // re-dealt to the lanes by the octant of their direction (counting sort through shared memory), so that a warp
+        // traces rays of one or two octants.  Order-free fixed-point sums: the frame is bit-identical either way.
+        if (MODE == PQ_BEAUTY && P.exp_flags) {
+            if (!__syncthreads_or(have ? 1 : 0)) break;
+            if (P.exp_flags & 2) {
+                __shared__ int s_cnt[ZB_BLOCK_THREADS / 32][9];
+                __shared__ float s_state[ZB_BLOCK_THREADS][16];
+                const int warp = threadIdx.x >> 5;
+                const uint32_t key = have ? ray_octant(st.d) : 8u;
+                if (threadIdx.x < 36) s_cnt[threadIdx.x / 9][threadIdx.x % 9] = 0;
+                __syncthreads();
+                const unsigned peers = __match_any_sync(0xFFFFFFFFu, key);
+                const int rank = __popc(peers & lt);
+                if (rank == 0) s_cnt[warp][key] = __popc(peers);
+                __syncthreads();
+                int at = rank;
+                for (uint32_t b = 0; b < key; b++)
+                    for (int w2 = 0; w2 < ZB_BLOCK_THREADS / 32; w2++) at += s_cnt[w2][b];
+                for (int w2 = 0; w2 < warp; w2++) at += s_cnt[w2][key];
+                float* q = s_state[at];
+                q[0] = __uint_as_float(st.pixel); q[1] = __uint_as_float(st.s); q[2] = __int_as_float(st.seg); q[3] = have ? 1.f : 0.f;
+                q[4] = st.o.x; q[5] = st.o.y; q[6] = st.o.z; q[7] = st.d.x; q[8] = st.d.y; q[9] = st.d.z;
+                q[10] = st.L.x; q[11] = st.L.y; q[12] = st.L.z; q[13] = st.beta.x; q[14] = st.beta.y; q[15] = st.beta.z;
+                __syncthreads();
+                const float* r = s_state[threadIdx.x];
+                st.pixel = __float_as_uint(r[0]); st.s = __float_as_uint(r[1]); st.seg = __float_as_int(r[2]); have = r[3] != 0.f;
+                st.o = f3(r[4], r[5], r[6]); st.d = f3(r[7], r[8], r[9]);
+                st.L = f3(r[10], r[11], r[12]); st.beta = f3(r[13], r[14], r[15]);
+            }
+        } else
+#endif
         if (!__any_sync(0xFFFFFFFFu, have)) break;
         if (have) {
             Hit hit;
@@ -835,6 +869,7 @@ ZbTuning zbk_tuning_from_env() {
     t.wf_slots = num("ZB_WF_SLOTS", 0);
     t.gather_p2p = int(num("ZB_GATHER_P2P", 1));
     t.wide = int(num("ZB_WIDE", 1));
+    t.pq_redeal = int(num("ZB_PQ_REDEAL", 0));
     return t;
 }
 

@@ -15,6 +15,7 @@ struct ZbTuning {
     int pq_resume = 0;   // experiments build: k_render_pqr threshold
     int wavefront = 0;   // experiments build: wavefront kernels for the beauty pass
     long long wf_slots = 0;
+    int pq_redeal = 0;   // experiments build: 1 = block-synchronous segments in k_render_pq, 2 = + rays re-dealt by direction octant
     int fuse_finish = 1; // finishing chain with bloom: 1 = one fused pass (k_finish_fused, radius <= 6), 0 = three kernels (A/B)
     int wide = 1;        // 1: walk the scene's 8-wide compressed tree where it has one; 0: always the binary tree
     int gather_p2p = 1;  // multi-GPU combine: 1 = fused peer-memory resolve-gather kernel, 0 = staged copies (A/B)

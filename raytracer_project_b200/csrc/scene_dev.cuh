@@ -75,6 +75,7 @@ struct RenderParams {
     int tiles_x, tiles_y;
     int accumulate;                // 0: overwrite accum, 1: add to it
     int light_pass;                // 1: reflection / refraction passes (camera.hpp:492-517) instead of beauty
+    int exp_flags;                 // experiments build only (tuning "pq_redeal"): 1 = block-synchronous segments, 2 = + re-deal rays by octant
 };
 
 #ifndef ZB_TILE_W
