@@ -147,8 +147,74 @@ public:
         lines_rendered.store(0);
     }
 
-    // Call after editing the scene graph in place (the reference rebuilds its BVH at main.cpp:1492-1500).
+    // The uploaded scene is re-used while the world object AND a content stamp of its graph stay the same: the stamp
+    // (FNV-1a over every object's kind, bounding box, wrapper matrices, material pointer and parameters; a mesh counts
+    // by pointer, triangle count and box) catches in-place edits and a new world allocated at an old address — the
+    // reference's GUI replaces bvh_world on every restart (main.cpp:1492-1500).  invalidate_scene() forces a re-flatten.
     void invalidate_scene() { cached_world = nullptr; }
+
+    static void stamp_mix(uint64_t& h, const void* p, size_t n) {
+        const unsigned char* b = static_cast<const unsigned char*>(p);
+        for (size_t i = 0; i < n; i++) { h ^= b[i]; h *= 1099511628211ull; }
+    }
+    static void stamp_material(uint64_t& h, const material* m) {
+        stamp_mix(h, &m, sizeof(m));
+        if (!m) return;
+        const int k = int(m->kind());
+        const void* t = m->tex.get();
+        const void* b = m->bump.get();
+        stamp_mix(h, &k, sizeof(k));
+        stamp_mix(h, &t, sizeof(t));
+        stamp_mix(h, &b, sizeof(b));
+        stamp_mix(h, &m->bump_strength, sizeof(double));
+        stamp_mix(h, &m->param, sizeof(double));
+        stamp_mix(h, &m->tint, sizeof(color));
+    }
+    static void stamp_object(uint64_t& h, const hittable& o) {
+        using K = hittable::kind_t;
+        const int k = int(o.kind());
+        const aabb box = o.bounding_box();
+        const double bb[6] = {box.x.min, box.x.max, box.y.min, box.y.max, box.z.min, box.z.max};
+        stamp_mix(h, &k, sizeof(k));
+        stamp_mix(h, bb, sizeof(bb));
+        switch (o.kind()) {
+            case K::list: for (auto& c : static_cast<const hittable_list&>(o).objects) stamp_object(h, *c); break;
+            case K::bvh: for (auto& c : static_cast<const bvh_node&>(o).objects) stamp_object(h, *c); break;
+            case K::sphere: stamp_material(h, static_cast<const sphere&>(o).mat.get()); break;
+            case K::triangle: stamp_material(h, static_cast<const triangle&>(o).mat.get()); break;
+            case K::cube: stamp_material(h, static_cast<const cube&>(o).mat.get()); break;
+            case K::translate: case K::rotate_x: case K::rotate_y: case K::rotate_z: case K::scale: {
+                auto& w = static_cast<const transform_wrapper&>(o);
+                const affine m = w.object_to_world();
+                stamp_mix(h, m.m, sizeof(m.m));
+                stamp_object(h, *w.ptr);
+            } break;
+            case K::material_instance: {
+                auto& mi = static_cast<const material_instance&>(o);
+                stamp_material(h, mi.new_material.get());
+                stamp_object(h, *mi.object);
+            } break;
+            case K::constant_medium: {
+                auto& cm = static_cast<const constant_medium&>(o);
+                stamp_mix(h, &cm.neg_inv_density, sizeof(double));
+                stamp_material(h, cm.phase_function.get());
+                stamp_object(h, *cm.boundary);
+            } break;
+            case K::model: {
+                auto& md = static_cast<const model&>(o);
+                const void* p = &md;
+                const size_t nt = md.tris.size();
+                stamp_mix(h, &p, sizeof(p));
+                stamp_mix(h, &nt, sizeof(nt));
+                stamp_material(h, md.mat.get());
+            } break;
+        }
+    }
+    static uint64_t scene_stamp(const hittable& world) {
+        uint64_t h = 1469598103934665603ull;
+        stamp_object(h, world);
+        return h;
+    }
 
     int create_context() {
         if (devices.size() > 1) return zb_context_create_multi(devices.data(), int(devices.size()), &ctx);
@@ -164,7 +230,8 @@ public:
         const size_t n = size_t(image_width) * image_height;
         if (render_accumulator.size() < n) { set_error(ZB_ERR_INVALID, "camera::render: call reset_accumulator() first (camera.hpp:209)"); return; }
         if (!ctx && (rc = create_context()) != ZB_OK) { set_error(rc, zb_last_error()); return; }
-        if (cached_world != &world || cached_hdr != env.hdr_texture.get()) {
+        const uint64_t stamp = scene_stamp(world);
+        if (cached_world != &world || cached_stamp != stamp || cached_hdr != env.hdr_texture.get()) {
             if (scene) zb_scene_destroy(scene);
             scene = nullptr;
             flattener fl;
@@ -172,6 +239,7 @@ public:
             hdr_texture_id = flat->env_hdr_texture;
             if ((rc = zb_scene_upload(ctx, &flat->view, &scene)) != ZB_OK) { set_error(rc, zb_last_error()); return; }
             cached_world = &world;
+            cached_stamp = stamp;
             cached_hdr = env.hdr_texture.get();
         }
         zb_camera c{};
@@ -307,6 +375,7 @@ private:
     zb_context* ctx = nullptr;
     zb_scene* scene = nullptr;
     const hittable* cached_world = nullptr;
+    uint64_t cached_stamp = 0;
     const void* cached_hdr = nullptr;
     uint32_t hdr_texture_id = ZB_NO_TEXTURE;
 };
