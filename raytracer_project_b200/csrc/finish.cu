@@ -290,17 +290,19 @@ __global__ void __launch_bounds__(128) k_finish(const float4* __restrict__ src, 
 #define ZB_FUSED_MAX_R 6
 #define ZB_FT_W 64
 #define ZB_FT_H 32
+template <int R>
 __global__ void __launch_bounds__(256) k_finish_fused(const float4* __restrict__ src, int W, int H, PostDev P, float4* __restrict__ out_f4,
                                                       uchar4* __restrict__ out_u8) {
     extern __shared__ float smem[];
-    const int r = P.bloom_radius, h = r + 1;
-    const int RA = ZB_FT_H + 2 * h, CA = ZB_FT_W + 2 * h, CB = ZB_FT_W + 2, RD = ZB_FT_H + 2;
+    // the radius is a template parameter: every index below divides by a compile-time constant
+    constexpr int r = R, h = r + 1;
+    constexpr int RA = ZB_FT_H + 2 * h, CA = ZB_FT_W + 2 * h, CB = ZB_FT_W + 2, RD = ZB_FT_H + 2;
     float* A = smem;                    // [3][RA][CA] bright pass; re-used as C = [3][RD][CB] bloom after stage 2
     float* B = A + 3 * RA * CA;         // [3][RA][CB] horizontally blurred
     float* D = B + 3 * RA * CB;         // [3][RD][CB] exposed colour ev * src
     float* Cb = A;
     const int x0 = blockIdx.x * ZB_FT_W, y0 = blockIdx.y * ZB_FT_H;
-    const float inv_r1 = 1.0f / float(r + 1);
+    constexpr float inv_r1 = 1.0f / float(r + 1);
     // ---- 1: bright pass over the tile + h halo, exposed colour over the tile + 1
     for (int i = threadIdx.x; i < RA * CA; i += 256) {
         const int cy = i / CA, cx = i - cy * CA;
@@ -331,9 +333,10 @@ __global__ void __launch_bounds__(256) k_finish_fused(const float4* __restrict__
         float total = 0.f;
         if (gx >= 0 && gx < W) {
             const float* a = A + cy * CA + x + r;  // column of gx in A = x - 1 + h = x + r
+#pragma unroll
             for (int o = -r; o <= r; o++) {
                 if (gx + o < 0 || gx + o >= W) continue;
-                const float w = 1.0f - float(abs(o)) * inv_r1;
+                const float w = 1.0f - float(o < 0 ? -o : o) * inv_r1;
                 sum += w * f3(a[o], a[RA * CA + o], a[2 * RA * CA + o]);
                 total += w;
             }
@@ -352,9 +355,10 @@ __global__ void __launch_bounds__(256) k_finish_fused(const float4* __restrict__
         float total = 0.f;
         if (gy >= 0 && gy < H) {
             const float* b = B + (y + r) * CB + x;  // row of gy in B = y - 1 + h = y + r
+#pragma unroll
             for (int o = -r; o <= r; o++) {
                 if (gy + o < 0 || gy + o >= H) continue;
-                const float w = 1.0f - float(abs(o)) * inv_r1;
+                const float w = 1.0f - float(o < 0 ? -o : o) * inv_r1;
                 sum += w * f3(b[o * CB], b[RA * CB + o * CB], b[2 * RA * CB + o * CB]);
                 total += w;
             }
@@ -365,49 +369,31 @@ __global__ void __launch_bounds__(256) k_finish_fused(const float4* __restrict__
         Cb[2 * RD * CB + i] = sum.z * inv;
     }
     __syncthreads();
-    // ---- 4: t = ev * src + bloom, 5-tap sharpening of interior pixels, process(), store; 4 consecutive pixels per thread
+    // ---- 4: t = ev * src + bloom, 5-tap sharpening of interior pixels, process(), store.  One pixel per thread and step,
+    // consecutive threads on consecutive pixels: conflict-free shared-memory reads, coalesced stores (a warp writes 128 B
+    // of RGBA8 or 512 B of float4)
     auto tap = [&](int tx, int ty) {  // tile coordinates, -1 .. tile size
         const int j = (ty + 1) * CB + tx + 1;
         float3 t = f3(D[j], D[RD * CB + j], D[2 * RD * CB + j]);
         t += f3(Cb[j], Cb[RD * CB + j], Cb[2 * RD * CB + j]);
         return t;
     };
-    const float inv_w = 1.0f / float(W - 1);
-    for (int q = threadIdx.x; q < ZB_FT_W * ZB_FT_H / 4; q += 256) {
-        const int ty = q / (ZB_FT_W / 4), tx0 = (q - ty * (ZB_FT_W / 4)) * 4;
-        const int y = y0 + ty, xg0 = x0 + tx0;
-        if (y >= H || xg0 >= W) continue;
-        const float v = float(y) / float(H - 1);
-        uchar4 packed[4];
-        float3 res[4];
-#pragma unroll
-        for (int k = 0; k < 4; k++) {
-            const int x = xg0 + k;
-            const float3 c = tap(tx0 + k, ty);
-            float3 o = c;
-            if (P.sharpen && y >= 1 && y < H - 1 && x >= 1 && x < W - 1) {  // color_processing.hpp:218-219
-                const float3 sum = 5.0f * c - tap(tx0 + k, ty - 1) - tap(tx0 + k, ty + 1) - tap(tx0 + k - 1, ty) - tap(tx0 + k + 1, ty);
-                o = (1.0f - P.sharpen_amount) * c + P.sharpen_amount * sum;
-            }
-            o = process(o, float(x) * inv_w, v, P);
-            res[k] = o;
-            packed[k] = make_uchar4((unsigned char)(255.999f * o.x), (unsigned char)(255.999f * o.y), (unsigned char)(255.999f * o.z), 255);
+    const float inv_w = 1.0f / float(W - 1), inv_h = 1.0f / float(H - 1);
+    for (int q = threadIdx.x; q < ZB_FT_W * ZB_FT_H; q += 256) {
+        const int ty = q / ZB_FT_W, tx = q - ty * ZB_FT_W;
+        const int y = y0 + ty, x = x0 + tx;
+        if (y >= H || x >= W) continue;
+        const float3 c = tap(tx, ty);
+        float3 o = c;
+        if (P.sharpen && y >= 1 && y < H - 1 && x >= 1 && x < W - 1) {  // color_processing.hpp:218-219
+            const float3 sum = 5.0f * c - tap(tx, ty - 1) - tap(tx, ty + 1) - tap(tx - 1, ty) - tap(tx + 1, ty);
+            o = (1.0f - P.sharpen_amount) * c + P.sharpen_amount * sum;
         }
-        const size_t row = size_t(y) * W;
-        if (out_f4) {
-#pragma unroll
-            for (int k = 0; k < 4; k++)
-                if (xg0 + k < W) out_f4[row + xg0 + k] = make_float4(res[k].x, res[k].y, res[k].z, 1.0f);
-        }
-        if (out_u8) {
-            if (xg0 + 4 <= W && (W % 4) == 0) {
-                *reinterpret_cast<uint4*>(out_u8 + row + xg0) = *reinterpret_cast<uint4*>(packed);
-            } else {
-#pragma unroll
-                for (int k = 0; k < 4; k++)
-                    if (xg0 + k < W) out_u8[row + xg0 + k] = packed[k];
-            }
-        }
+        o = process(o, float(x) * inv_w, float(y) / float(H - 1), P);
+        (void)inv_h;
+        const size_t at = size_t(y) * W + x;
+        if (out_f4) out_f4[at] = make_float4(o.x, o.y, o.z, 1.0f);
+        if (out_u8) out_u8[at] = make_uchar4((unsigned char)(255.999f * o.x), (unsigned char)(255.999f * o.y), (unsigned char)(255.999f * o.z), 255);
     }
 }
 
@@ -506,13 +492,19 @@ extern "C" int zb_finish_device(zb_context* ctx, const void* mean_f4, int width,
     if (pass_kind == ZB_PASS_BEAUTY && P.bloom && P.bloom_radius <= ZB_FUSED_MAX_R && ctx->tuning.fuse_finish) {
         // bloom + sharpening + process() in one pass over shared-memory tiles
         const size_t smem = fused_smem_bytes(P.bloom_radius);
-        static bool attr_set[64] = {};
-        if (ctx->device < 64 && !attr_set[ctx->device]) {
-            ZB_CUDA(cudaFuncSetAttribute(k_finish_fused, cudaFuncAttributeMaxDynamicSharedMemorySize, int(fused_smem_bytes(ZB_FUSED_MAX_R))));
-            attr_set[ctx->device] = true;
+        const dim3 grid((width + ZB_FT_W - 1) / ZB_FT_W, (height + ZB_FT_H - 1) / ZB_FT_H);
+        float4* o4 = static_cast<float4*>(out_f4);
+        uchar4* o8 = static_cast<uchar4*>(out_rgba8);
+#define ZB_FUSED_CASE(RR)                                                                                                          \
+    case RR:                                                                                                                       \
+        ZB_CUDA(cudaFuncSetAttribute(k_finish_fused<RR>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(fused_smem_bytes(RR)))); \
+        k_finish_fused<RR><<<grid, 256, smem, ctx->stream>>>(src, width, height, P, o4, o8);                                       \
+        break;
+        switch (P.bloom_radius) {
+            ZB_FUSED_CASE(0) ZB_FUSED_CASE(1) ZB_FUSED_CASE(2) ZB_FUSED_CASE(3) ZB_FUSED_CASE(4) ZB_FUSED_CASE(5) ZB_FUSED_CASE(6)
+            default: return fail(ZB_ERR_INVALID, "zb_finish_device: bloom radius outside the fused range");
         }
-        k_finish_fused<<<dim3((width + ZB_FT_W - 1) / ZB_FT_W, (height + ZB_FT_H - 1) / ZB_FT_H), 256, smem, ctx->stream>>>(
-            src, width, height, P, static_cast<float4*>(out_f4), static_cast<uchar4*>(out_rgba8));
+#undef ZB_FUSED_CASE
         ZB_CUDA(cudaGetLastError());
         ctx->stats.launches++;
         return ZB_OK;
