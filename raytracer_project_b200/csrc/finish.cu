@@ -290,34 +290,84 @@ __global__ void __launch_bounds__(128) k_finish(const float4* __restrict__ src, 
 #define ZB_FUSED_MAX_R 6
 #define ZB_FT_W 64
 #define ZB_FT_H 32
+// Row pitches of the shared-memory planes are ODD: a warp whose lanes walk down a column (the horizontal blur's strips) then
+// touches 32 different banks.
+#define ZB_FT_CB (ZB_FT_W + 3)
+#define ZB_FT_CA(r) ((ZB_FT_W + 2 * ((r) + 1)) | 1)
+
+// One strip of S outputs of the tent blur (bloom.hpp:48-67) along a line of one channel, the 2R + S inputs held in
+// registers: (2R + S) / S shared-memory loads per output instead of 2R + 1.  in[(k + o) * IS] is tap o of output k,
+// out[k * OS] the output; g0 = image coordinate of output 0, G = image extent along the line.  CHECK: some tap or output may
+// lie outside the image (border tiles) — weights of missing taps are left out of the normalisation, outputs outside are 0.
+// The weights 1 - |o| / (R + 1) are added and applied in the reference's order o = -R .. R.
+template <int R, int S, int IS, int OS, bool CHECK, bool ACCUM>
+__device__ __forceinline__ void tent_strip(const float* __restrict__ in, float* __restrict__ out, int g0, int G, float inv_all) {
+    constexpr float inv_r1 = 1.0f / float(R + 1);
+    float win[S + 2 * R];
+#pragma unroll
+    for (int j = 0; j < S + 2 * R; j++) win[j] = in[(j - R) * IS];
+#pragma unroll
+    for (int k = 0; k < S; k++) {
+        float sum = 0.f, inv = inv_all;
+        if (!CHECK) {
+#pragma unroll
+            for (int o = -R; o <= R; o++) sum += (1.0f - float(o < 0 ? -o : o) * inv_r1) * win[k + o + R];
+        } else {
+            const int g = g0 + k;
+            float total = 0.f;
+            if (g >= 0 && g < G) {
+#pragma unroll
+                for (int o = -R; o <= R; o++) {
+                    if (g + o < 0 || g + o >= G) continue;
+                    const float w = 1.0f - float(o < 0 ? -o : o) * inv_r1;
+                    sum += w * win[k + o + R];
+                    total += w;
+                }
+            }
+            inv = total > 0.f ? 1.0f / total : 0.f;
+        }
+        if (ACCUM) out[k * OS] += sum * inv;
+        else out[k * OS] = sum * inv;
+    }
+}
+
 template <int R>
 __global__ void __launch_bounds__(256) k_finish_fused(const float4* __restrict__ src, int W, int H, PostDev P, float4* __restrict__ out_f4,
                                                       uchar4* __restrict__ out_u8) {
     extern __shared__ float smem[];
     // the radius is a template parameter: every index below divides by a compile-time constant
     constexpr int r = R, h = r + 1;
-    constexpr int RA = ZB_FT_H + 2 * h, CA = ZB_FT_W + 2 * h, CB = ZB_FT_W + 2, RD = ZB_FT_H + 2;
-    float* A = smem;                    // [3][RA][CA] bright pass; re-used as C = [3][RD][CB] bloom after stage 2
-    float* B = A + 3 * RA * CA;         // [3][RA][CB] horizontally blurred
-    float* D = B + 3 * RA * CB;         // [3][RD][CB] exposed colour ev * src
-    float* Cb = A;
+    constexpr int RA = ZB_FT_H + 2 * h, WA = ZB_FT_W + 2 * h, CA = ZB_FT_CA(R), WB = ZB_FT_W + 2, CB = ZB_FT_CB, RD = ZB_FT_H + 2;
+    float* A = smem;                    // [3][RA][CA] bright pass (WA columns used)
+    float* B = A + 3 * RA * CA;         // [3][RA][CB] horizontally blurred (WB columns used)
+    float* D = B + 3 * RA * CB;         // [3][RD][CB] exposed colour ev * src, then t = ev * src + bloom
     const int x0 = blockIdx.x * ZB_FT_W, y0 = blockIdx.y * ZB_FT_H;
     constexpr float inv_r1 = 1.0f / float(r + 1);
-    // ---- 1: bright pass over the tile + h halo, exposed colour over the tile + 1
-    for (int i = threadIdx.x; i < RA * CA; i += 256) {
-        const int cy = i / CA, cx = i - cy * CA;
+    // ---- 1: bright pass over the tile + h halo, exposed colour over the tile + 1.  All of a thread's pixels are fetched
+    // before the first is used (two blocks of 8 warps per SM cannot hide a DRAM round trip per pixel otherwise); pixels
+    // outside the image are staged as black, which is what bright_pass and ev * src make of them
+    constexpr int N1 = (RA * WA + 255) / 256;
+    float4 px[N1];
+#pragma unroll
+    for (int k = 0; k < N1; k++) {
+        const int i = threadIdx.x + k * 256;
+        const int cy = i / WA, cx = i - cy * WA;
         const int gx = x0 - h + cx, gy = y0 - h + cy;
-        float3 b = f3(0, 0, 0), e = f3(0, 0, 0);
-        if (gx >= 0 && gx < W && gy >= 0 && gy < H) {
-            const float4 p = __ldg(src + size_t(gy) * W + gx);
-            b = bright_pass(p, P);
-            e = P.ev * f3(p);
-        }
-        A[i] = b.x;
-        A[RA * CA + i] = b.y;
-        A[2 * RA * CA + i] = b.z;
+        px[k] = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (i < RA * WA && gx >= 0 && gx < W && gy >= 0 && gy < H) px[k] = __ldg(src + size_t(gy) * W + gx);
+    }
+#pragma unroll
+    for (int k = 0; k < N1; k++) {
+        const int i = threadIdx.x + k * 256;
+        if (i >= RA * WA) break;
+        const int cy = i / WA, cx = i - cy * WA;
+        const float3 b = bright_pass(px[k], P), e = P.ev * f3(px[k]);
+        const int ia = cy * CA + cx;
+        A[ia] = b.x;
+        A[RA * CA + ia] = b.y;
+        A[2 * RA * CA + ia] = b.z;
         const int dx = cx - r, dy = cy - r;  // position in the tile + 1 region
-        if (dx >= 0 && dx < CB && dy >= 0 && dy < RD) {
+        if (dx >= 0 && dx < WB && dy >= 0 && dy < RD) {
             const int j = dy * CB + dx;
             D[j] = e.x;
             D[RD * CB + j] = e.y;
@@ -325,58 +375,45 @@ __global__ void __launch_bounds__(256) k_finish_fused(const float4* __restrict__
         }
     }
     __syncthreads();
-    // ---- 2: horizontal tent blur (bloom.hpp:48-67) of every staged row, for the columns of the tile + 1
-    for (int i = threadIdx.x; i < RA * CB; i += 256) {
-        const int cy = i / CB, x = i - cy * CB;
-        const int gx = x0 - 1 + x;
-        float3 sum = f3(0, 0, 0);
-        float total = 0.f;
-        if (gx >= 0 && gx < W) {
-            const float* a = A + cy * CA + x + r;  // column of gx in A = x - 1 + h = x + r
+    // A block whose staged region lies inside the image (all but the border tiles) skips the per-tap bounds checks; the sum
+    // of the weights is then the same constant for every pixel (added in the same order as the checked loop adds them).
+    const bool x_in = x0 - h >= 0 && x0 + ZB_FT_W + h <= W, y_in = y0 - h >= 0 && y0 + ZB_FT_H + h <= H;
+    float w_all = 0.f;
 #pragma unroll
-            for (int o = -r; o <= r; o++) {
-                if (gx + o < 0 || gx + o >= W) continue;
-                const float w = 1.0f - float(o < 0 ? -o : o) * inv_r1;
-                sum += w * f3(a[o], a[RA * CA + o], a[2 * RA * CA + o]);
-                total += w;
-            }
-        }
-        const float inv = total > 0.f ? 1.0f / total : 0.f;
-        B[i] = sum.x * inv;
-        B[RA * CB + i] = sum.y * inv;
-        B[2 * RA * CB + i] = sum.z * inv;
+    for (int o = -r; o <= r; o++) w_all += 1.0f - float(o < 0 ? -o : o) * inv_r1;
+    const float inv_all = 1.0f / w_all;
+    // ---- 2: horizontal blur of every staged row for the columns of the tile + 1: strips of SH outputs; consecutive lanes
+    // take consecutive rows (odd pitch: conflict-free)
+    constexpr int SH = 11, NSH = WB / SH;
+    static_assert(NSH * SH == WB, "strip length divides the blurred width");
+    for (int i = threadIdx.x; i < 3 * NSH * RA; i += 256) {
+        const int cy = i % RA, t = i / RA, strip = t % NSH, c = t / NSH;
+        const int x = strip * SH;
+        const float* a = A + c * RA * CA + cy * CA + x + r;  // column of output x in A = x - 1 + h
+        float* o = B + c * RA * CB + cy * CB + x;
+        if (x_in) tent_strip<R, SH, 1, 1, false, false>(a, o, x0 - 1 + x, W, inv_all);
+        else tent_strip<R, SH, 1, 1, true, false>(a, o, x0 - 1 + x, W, inv_all);
     }
     __syncthreads();
-    // ---- 3: vertical blur for the rows of the tile + 1 (A is dead: the bloom plane takes its place)
-    for (int i = threadIdx.x; i < RD * CB; i += 256) {
-        const int y = i / CB, x = i - y * CB;
-        const int gy = y0 - 1 + y;
-        float3 sum = f3(0, 0, 0);
-        float total = 0.f;
-        if (gy >= 0 && gy < H) {
-            const float* b = B + (y + r) * CB + x;  // row of gy in B = y - 1 + h = y + r
-#pragma unroll
-            for (int o = -r; o <= r; o++) {
-                if (gy + o < 0 || gy + o >= H) continue;
-                const float w = 1.0f - float(o < 0 ? -o : o) * inv_r1;
-                sum += w * f3(b[o * CB], b[RA * CB + o * CB], b[2 * RA * CB + o * CB]);
-                total += w;
-            }
-        }
-        const float inv = total > 0.f ? 1.0f / total : 0.f;
-        Cb[i] = sum.x * inv;
-        Cb[RD * CB + i] = sum.y * inv;
-        Cb[2 * RD * CB + i] = sum.z * inv;
+    // ---- 3: vertical blur for the rows of the tile + 1, added to the exposed colour in place (D becomes t): strips of SV
+    // rows, consecutive lanes on consecutive columns
+    constexpr int SV = 17, NSV = RD / SV;
+    static_assert(NSV * SV == RD, "strip length divides the blurred height");
+    for (int i = threadIdx.x; i < 3 * NSV * WB; i += 256) {
+        const int x = i % WB, t = i / WB, strip = t % NSV, c = t / NSV;
+        const int y = strip * SV;
+        const float* b = B + c * RA * CB + (y + r) * CB + x;  // row of output y in B = y - 1 + h
+        float* o = D + c * RD * CB + y * CB + x;
+        if (y_in) tent_strip<R, SV, CB, CB, false, true>(b, o, y0 - 1 + y, H, inv_all);
+        else tent_strip<R, SV, CB, CB, true, true>(b, o, y0 - 1 + y, H, inv_all);
     }
     __syncthreads();
-    // ---- 4: t = ev * src + bloom, 5-tap sharpening of interior pixels, process(), store.  One pixel per thread and step,
-    // consecutive threads on consecutive pixels: conflict-free shared-memory reads, coalesced stores (a warp writes 128 B
-    // of RGBA8 or 512 B of float4)
+    // ---- 4: 5-tap sharpening of interior pixels on t, process(), store.  One pixel per thread and step, consecutive
+    // threads on consecutive pixels: conflict-free shared-memory reads, coalesced stores (a warp writes 128 B of RGBA8 or
+    // 512 B of float4)
     auto tap = [&](int tx, int ty) {  // tile coordinates, -1 .. tile size
         const int j = (ty + 1) * CB + tx + 1;
-        float3 t = f3(D[j], D[RD * CB + j], D[2 * RD * CB + j]);
-        t += f3(Cb[j], Cb[RD * CB + j], Cb[2 * RD * CB + j]);
-        return t;
+        return f3(D[j], D[RD * CB + j], D[2 * RD * CB + j]);
     };
     const float inv_w = 1.0f / float(W - 1), inv_h = 1.0f / float(H - 1);
     for (int q = threadIdx.x; q < ZB_FT_W * ZB_FT_H; q += 256) {
@@ -398,7 +435,7 @@ __global__ void __launch_bounds__(256) k_finish_fused(const float4* __restrict__
 }
 
 size_t fused_smem_bytes(int r) {
-    const int h = r + 1, RA = ZB_FT_H + 2 * h, CA = ZB_FT_W + 2 * h, CB = ZB_FT_W + 2, RD = ZB_FT_H + 2;
+    const int h = r + 1, RA = ZB_FT_H + 2 * h, CA = ZB_FT_CA(r), CB = ZB_FT_CB, RD = ZB_FT_H + 2;
     return sizeof(float) * 3 * size_t(RA * CA + RA * CB + RD * CB);
 }
 

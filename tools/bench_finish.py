@@ -11,6 +11,7 @@ ap = argparse.ArgumentParser()
 ap.add_argument("--width", type=int, default=3840)
 ap.add_argument("--height", type=int, default=2160)
 ap.add_argument("--reps", type=int, default=10)
+ap.add_argument("--profile", action="store_true", help="one launch per case, no timing (for ncu)")
 a = ap.parse_args()
 peak = 6650.0
 p = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "MEASURED_PEAKS.json")
@@ -50,6 +51,12 @@ cases = {
     "finish_bloom_r8_rgba8 (radius 8 > fused limit: 3 kernels)": (lambda: ctx.finish_device(src.data_ptr(), a.width, a.height, api.post_struct(use_bloom=1, bloom_radius=8), 0, 0, out_u8.data_ptr()), 32 + 32 + 36),
     "aux_pass_rgba8": (lambda: ctx.finish_device(src.data_ptr(), a.width, a.height, api.post_struct(), 2, 0, out_u8.data_ptr()), 20),
 }
+if a.profile:
+    for name, (fn, bpp) in cases.items():
+        fn()
+    ctx.analyze_device(src.data_ptr(), n)
+    torch.cuda.synchronize()
+    sys.exit(0)
 for name, (fn, bpp) in cases.items():
     best, mean = timed(fn)
     gbs = n * bpp / (best * 1e-3) * 1e-9

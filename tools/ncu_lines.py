@@ -24,6 +24,7 @@ ap.add_argument("lib")
 ap.add_argument("func", help="substring of the mangled kernel name")
 ap.add_argument("--top", type=int, default=40)
 ap.add_argument("--by", default="inst", choices=["inst", "samples"])
+ap.add_argument("--launch", type=int, default=None, help="index of the launch inside a report that holds several")
 a = ap.parse_args()
 
 tmp = tempfile.mkdtemp(prefix="ncul_")
@@ -49,7 +50,8 @@ for cub in sorted(os.listdir(tmp)):
     if lines_of:
         break
 
-out = subprocess.run(["ncu", "-i", a.rep, "--page", "source", "--csv", "--print-source", "sass"], capture_output=True,
+sel = [] if a.launch is None else ["--launch-skip", str(a.launch), "--launch-count", "1"]
+out = subprocess.run(["ncu", "-i", a.rep, *sel, "--page", "source", "--csv", "--print-source", "sass"], capture_output=True,
                      text=True).stdout
 rows = list(csv.reader(io.StringIO(out)))
 hdr_i = next(i for i, r in enumerate(rows) if r and r[0] == "Address")
