@@ -406,7 +406,7 @@ def ours(args):
                        "rays_per_path": rays / max(paths_counted, 1.0), "node_visits_per_ray": node_visits / max(rays, 1.0),
                        "prim_tests_per_ray": prim_tests / max(rays, 1.0), "kernel": kernel_name(pick),
                        "feature_set": FEATURE_NAMES.get(feat, str(feat)),
-                       "blas": "device LBVH" if args.gpu_blas else "host binned SAH"},
+                       "blas": ("device binned SAH (sah_build.cu)" if os.environ.get("ZB_GPU_BUILDER", "1") != "0" else "device LBVH (lbvh.cu)") if args.gpu_blas else "host binned SAH"},
             "kernel_ms_per_step": kernel_ms,
             "e2e": {"value": e2e_value, "unit": "Mpaths/s", "ms_per_step": e2e_ms_per_step,
                     "h2d_bytes_per_step": (scene_bytes + 512) * world, "d2h_bytes_per_step": n_pix * 12, "checksum": checksum,
@@ -459,7 +459,7 @@ def main():
     ap.add_argument("--config", default="headline", choices=list(CONFIGS))
     ap.add_argument("--partition", default="auto", choices=["auto", "samples", "tiles"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
-    ap.add_argument("--gpu-blas", action="store_true", help="mesh BLASes built on the device at upload (linear BVH, csrc/lbvh.cu) instead of the host SAH build")
+    ap.add_argument("--gpu-blas", action="store_true", help="mesh BLASes built on the device at upload (binned SAH, csrc/sah_build.cu; ZB_GPU_BUILDER=0: linear BVH, csrc/lbvh.cu) instead of the host SAH build")
     ap.add_argument("--spp", type=int, default=0, help="profiling runs only: override the config's samples per pixel (the workload name says so)")
     args = ap.parse_args()
     if args.spp > 0:

@@ -17,7 +17,8 @@ from .scenes import RenderConfig
 
 def flatten_zscene(text: str | None = None, path: str | None = None, gpu_blas: bool = False, wide: int = 0):
     """zscene text/file -> host scene API -> flatten(); returns a ctypes pointer to zb_flat_scene.
-    gpu_blas: leave the mesh BLAS builds to the device (linear BVH, csrc/lbvh.cu) at zb_scene_upload.
+    gpu_blas: leave the mesh BLAS builds to the device at zb_scene_upload (binned SAH, csrc/sah_build.cu; tuning
+    "gpu_builder" 0 = linear BVH, csrc/lbvh.cu).
     wide: 1 = also build the 8-wide compressed tree for scenes with meshes, 2 = for every scene (A/B; off by default)."""
     lib = _lib.load()
     out = C.POINTER(FlatScene)()

@@ -2,6 +2,9 @@
 // Context = one GPU + one stream; scene = device copies of the flat SoA arrays; render = camera and
 // environment set-up in double exactly as camera::initialize (camera.hpp:358-402) followed by the
 // kernels of kernels.cu.  No CPU fallback: without a usable sm_100 device every entry point fails.
+#include <chrono>
+#include <cstdio>
+
 #include "abi_internal.h"
 
 extern "C" int zb_abi_version(void) { return ZB_ABI_VERSION; }
@@ -64,6 +67,8 @@ extern "C" int zb_context_set_tuning(zb_context* ctx, const char* key, long long
     else if (k == "no_lean") t.no_lean = value != 0;
     else if (k == "pq_blocks") t.pq_blocks = int(value);
     else if (k == "gather_p2p") t.gather_p2p = int(value);
+    else if (k == "gpu_builder") t.gpu_builder = int(value);
+    else if (k == "build_timing") t.build_timing = int(value);
     else if (k == "wide") t.wide = value != 0;
     else if (k == "fuse_finish") t.fuse_finish = value != 0;
 #ifdef ZB_EXPERIMENTS
@@ -291,6 +296,9 @@ static int validate(const zb_flat_scene* f) {
 // csrc/lbvh.cu
 int zbk_build_blas_device(zb_context* ctx, const float4* tris_in, const float4* nrm_in, uint32_t n, uint32_t tri_first,
                           uint32_t node_base, float4* tris_out, float4* nrm_out, zb_bvh_node* nodes_out, uint32_t* n_nodes);
+// csrc/sah_build.cu
+int zbk_build_blas_device_sah(zb_context* ctx, const float4* tris_in, const float4* nrm_in, uint32_t n, uint32_t tri_first,
+                              uint32_t node_base, float4* tris_out, float4* nrm_out, zb_bvh_node* nodes_out, uint32_t* n_nodes);
 
 // Meshes the flattener left without a BLAS (node_count == 0): build linear BVHs on the device.
 // d.tris / d.tri_normals already hold the triangles in face order; nodes are appended after the host nodes and
@@ -327,7 +335,20 @@ static int build_device_blas(zb_scene* s, const zb_flat_scene* f, std::vector<zb
         cudaMemcpyAsync(tmp_t, t, bytes, cudaMemcpyDeviceToDevice, s->ctx->stream);
         cudaMemcpyAsync(tmp_n, n, bytes, cudaMemcpyDeviceToDevice, s->ctx->stream);
         uint32_t count = 0;
-        rc = zbk_build_blas_device(s->ctx, tmp_t, tmp_n, zm.tri_count, zm.tri_first, next, t, n, nodes + next, &count);
+        const bool timing = s->ctx->tuning.build_timing != 0;
+        std::chrono::steady_clock::time_point t0;
+        if (timing) {
+            cudaStreamSynchronize(s->ctx->stream);
+            t0 = std::chrono::steady_clock::now();
+        }
+        rc = (s->ctx->tuning.gpu_builder ? zbk_build_blas_device_sah : zbk_build_blas_device)(s->ctx, tmp_t, tmp_n, zm.tri_count, zm.tri_first, next, t,
+                                                                                             n, nodes + next, &count);
+        if (timing) {
+            cudaStreamSynchronize(s->ctx->stream);
+            std::fprintf(stderr, "[zb build] mesh %u: %u triangles, %s: %.3f ms wall (scratch allocation included), %u nodes\n", m, zm.tri_count,
+                         s->ctx->tuning.gpu_builder ? "binned SAH" : "linear BVH",
+                         std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count(), count);
+        }
         roots[m] = next;
         next += count;
     }

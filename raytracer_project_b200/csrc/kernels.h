@@ -18,6 +18,8 @@ struct ZbTuning {
     int pq_redeal = 0;   // experiments build: 1 = block-synchronous segments in k_render_pq, 2 = + rays re-dealt by direction octant
     int fuse_finish = 1; // finishing chain with bloom: 1 = one fused pass (k_finish_fused, radius <= 6), 0 = three kernels (A/B)
     int wide = 1;        // 1: walk the scene's 8-wide compressed tree where it has one; 0: always the binary tree
+    int gpu_builder = 1; // device BLAS build (ZB_FLATTEN_GPU_BLAS): 1 = binned SAH (sah_build.cu), 0 = linear BVH (lbvh.cu)
+    int build_timing = 0; // 1 = device BLAS builders print their phase times to stderr
     int gather_p2p = 1;  // multi-GPU combine: 1 = fused peer-memory resolve-gather kernel, 0 = staged copies (A/B)
 };
 ZbTuning zbk_tuning_from_env();

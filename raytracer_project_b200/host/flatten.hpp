@@ -81,8 +81,9 @@ struct flat_scene {
 class flattener {
 public:
     int tlas_leaf = 4, blas_leaf = 4;
-    // true: leave every mesh BLAS to the device builder (csrc/lbvh.cu): triangles are emitted in face
-    // order, the mesh carries node_count == 0 and zb_scene_upload builds a linear BVH for it on the GPU
+    // true: leave every mesh BLAS to the device builder: triangles are emitted in face order, the mesh
+    // carries node_count == 0 and zb_scene_upload builds its tree on the GPU — binned SAH (csrc/sah_build.cu) unless the
+    // context's tuning "gpu_builder" is 0 (linear BVH, csrc/lbvh.cu)
     bool gpu_blas = false;
     // 8-wide compressed tree beside the binary one (host/wide_bvh.hpp).  OFF by default: measured 2.2x slower than the
     // binary tree on the 1 M and 10 M triangle configs (profiles/r02_wide_bvh.txt: these kernels are issue-bound, not

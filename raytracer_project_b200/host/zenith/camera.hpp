@@ -130,6 +130,10 @@ public:
     // more than one entry: the frame is rendered by all of these GPUs (zb_context_create_multi); render() stays one
     // blocking call that fills the same buffers — the reference's thread fan-out (camera.hpp:426-427) by other means
     std::vector<int> devices;
+    // mesh BLASes are built on the device at upload (binned SAH, csrc/sah_build.cu: 6.5 ms for 1 M triangles against 2.8 s
+    // for the same tree on the host); false = host build (host/bvh_build.hpp).  The reference rebuilds geometry and BVH on
+    // the host at every restart (main.cpp:1492-1500, bvh.hpp:11-44 via model.hpp:95)
+    bool device_blas = true;
     uint64_t seed = 0x5EED0001ull;
     int rc = ZB_OK;            // status of the last render()
     std::string last_error;
@@ -235,6 +239,7 @@ public:
             if (scene) zb_scene_destroy(scene);
             scene = nullptr;
             flattener fl;
+            fl.gpu_blas = device_blas;
             std::unique_ptr<flat_scene> flat = fl.run(world, &env);
             hdr_texture_id = flat->env_hdr_texture;
             if ((rc = zb_scene_upload(ctx, &flat->view, &scene)) != ZB_OK) { set_error(rc, zb_last_error()); return; }
