@@ -327,9 +327,16 @@ int zb_scene_destroy(zb_scene* scene);
  * GPU(s), the world boxes of the items that reference instances are recomputed from the object-space bounds of their
  * geometry, and the TLAS is refitted bottom-up ON THE DEVICE with its topology unchanged; BLASes, materials and textures
  * are untouched.  One small kernel (k_refit_tlas): well under a millisecond for thousands of items.  Closest hits equal
- * those of a freshly flattened scene; a heavily rearranged scene traverses faster after a full re-flatten (SAH topology).
- * Needs zb_flat_scene::item_bounds at upload and host-built BLASes; an 8-wide tree, if any, is dropped (not refitted). */
+ * those of a freshly flattened scene; a heavily rearranged scene traverses faster after zb_scene_rebuild_tlas (SAH
+ * topology).  Needs zb_flat_scene::item_bounds at upload; an 8-wide tree, if any, is dropped (not refitted). */
 int zb_scene_refit(zb_scene* scene, const zb_instance* instances, uint32_t n_instances);
+/* Same edit, but the TLAS TOPOLOGY is rebuilt as well, on the device: new world boxes of the items, then a binned-SAH tree
+ * over them (csrc/sah_build.cu, the builder of the device BLASes, with the flattener's TLAS cost model) written into the
+ * scene's TLAS node region; the items are permuted into the new leaf order.  The flattener pads the TLAS region to
+ * n_items - 1 nodes so that any tree fits; a flat scene without that room fails with ZB_ERR_UNSUPPORTED when the new tree
+ * needs more nodes than the uploaded one had.  Closest hits equal those of a freshly flattened scene; later
+ * zb_scene_refit calls refit the new topology.  Launch-bound: ~1 ms for a few thousand items. */
+int zb_scene_rebuild_tlas(zb_scene* scene, const zb_instance* instances, uint32_t n_instances);
 
 /* Drop-in for camera::render's hot part (camera.hpp:236-250 -> :404-579): blocking; fills host
  * buffers.  `cancel` mirrors render_flag inverted (non-zero = stop, camera.hpp:441). */

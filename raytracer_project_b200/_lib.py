@@ -130,6 +130,7 @@ SYMBOLS = {
     "zb_scene_upload": (C.c_int, [C.c_void_p, C.POINTER(FlatScene), C.POINTER(C.c_void_p)]),
     "zb_scene_destroy": (C.c_int, [C.c_void_p]),
     "zb_scene_refit": (C.c_int, [C.c_void_p, C.c_void_p, C.c_uint32]),
+    "zb_scene_rebuild_tlas": (C.c_int, [C.c_void_p, C.c_void_p, C.c_uint32]),
     "zb_render": (C.c_int, [C.c_void_p, C.c_void_p, C.POINTER(Camera), C.POINTER(Environment), C.POINTER(RenderOpts),
                             C.POINTER(Outputs), C.POINTER(C.c_int), PROGRESS_FN, C.c_void_p]),
     "zb_probe_rays": (C.c_int, [C.c_void_p, C.c_void_p, C.POINTER(Environment), C.c_size_t, C.c_void_p, C.c_void_p, C.c_void_p]),

@@ -378,6 +378,11 @@ class Scene:
         f = flat_with_new_transforms.contents
         check(self.ctx.lib.zb_scene_refit(self.h, f.instances, f.n_instances))
 
+    def rebuild_tlas(self, flat_with_new_transforms):
+        """zb_scene_rebuild_tlas: like refit(), and the TLAS topology is rebuilt on the device over the moved items."""
+        f = flat_with_new_transforms.contents
+        check(self.ctx.lib.zb_scene_rebuild_tlas(self.h, f.instances, f.n_instances))
+
     def render_into(self, cfg: RenderConfig, buffers: dict, seed=1, partition="auto", samples_per_launch=0):
         """zb_render into caller-owned (H, W, 3) float64 arrays keyed like render()'s result — e.g. views of one frame in
         shared memory that all ranks of a multi-process group write their bands into."""

@@ -352,6 +352,12 @@ static int build_device_blas(zb_scene* s, const zb_flat_scene* f, std::vector<zb
         roots[m] = next;
         next += count;
     }
+    // root nodes of the device-built trees (still lo / hi boxes): zb_scene_refit needs every instance's object-space bounds
+    s->device_mesh_roots.assign(f->n_meshes, zb_bvh_node{});
+    for (uint32_t m = 0; m < f->n_meshes && !rc; m++)
+        if (f->meshes[m].node_count == 0 && f->meshes[m].tri_count > 0)
+            cudaMemcpyAsync(&s->device_mesh_roots[m], nodes + roots[m], sizeof(zb_bvh_node), cudaMemcpyDeviceToHost, s->ctx->stream);
+    cudaStreamSynchronize(s->ctx->stream);
     cudaFree(tmp_t);
     cudaFree(tmp_n);
     if (rc) return rc;
@@ -445,12 +451,10 @@ static int upload_one(zb_context* ctx, const zb_flat_scene* f, zb_scene** out) {
         zb_scene_destroy(s);
         return rc;
     }
-    if (!device_blas) {
-        rc = zbr_prepare_refit(s, f, instances);
-        if (rc) {
-            zb_scene_destroy(s);
-            return rc;
-        }
+    rc = zbr_prepare_refit(s, f, instances);
+    if (rc) {
+        zb_scene_destroy(s);
+        return rc;
     }
     d.n_items = f->n_items;
     d.n_media = f->n_media;

@@ -75,7 +75,9 @@ struct zb_scene {
         std::vector<uint32_t> level_start;
         std::vector<zb_instance> host_instances;
         uint32_t n_tlas_nodes = 0, n_items = 0;
+        uint32_t tlas_capacity = 0;      // nodes [0, tlas_capacity) belong to the TLAS (the flattener pads it to n_items - 1)
     } refit;
+    std::vector<zb_bvh_node> device_mesh_roots;  // per mesh: root node (lo / hi boxes) of a BLAS built on the device
     std::vector<zb_scene*> replicas;  // scene of a multi-device context: copies on the other members
     SceneDev dev{};
     std::vector<void*> allocs;

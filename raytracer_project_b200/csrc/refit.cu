@@ -40,9 +40,8 @@ __device__ float2 encode_axis(float lo, float hi, int center_half) {
     return make_float2(c, fmaxf(__fsub_ru(hi, c), __fsub_ru(c, lo)));
 }
 
-__global__ void __launch_bounds__(1024) k_refit_tlas(const __grid_constant__ RefitArgs A) {
-    // ---- phase 1: world boxes of the items whose geometry sits under an instance transform
-    for (uint32_t i = threadIdx.x; i < A.n_items; i += blockDim.x) {
+// world box of item i if its geometry sits under an instance transform (other items keep the flattener's box)
+__device__ void item_world_bounds(const RefitArgs& A, uint32_t i) {
         const float4 mf = A.items[2 * size_t(i) + 1];
         const uint32_t kind = __float_as_uint(mf.x) & 0xFFu, aux = __float_as_uint(mf.w);
         uint32_t inst = 0xFFFFFFFFu;
@@ -51,7 +50,7 @@ __global__ void __launch_bounds__(1024) k_refit_tlas(const __grid_constant__ Ref
             const float4 m0 = A.media[2 * size_t(aux)];
             if (__float_as_uint(m0.x) == ZB_ITEM_INSTANCE) inst = __float_as_uint(m0.y);
         }
-        if (inst == 0xFFFFFFFFu) continue;
+        if (inst == 0xFFFFFFFFu) return;
         const float4* ip = A.instances + 8 * size_t(inst);
         const float4 r0 = ip[3], r1 = ip[4], r2 = ip[5];  // object -> world, row-major 3x4
         const float4 blo = A.inst_bounds[2 * size_t(inst)], bhi = A.inst_bounds[2 * size_t(inst) + 1];
@@ -68,7 +67,16 @@ __global__ void __launch_bounds__(1024) k_refit_tlas(const __grid_constant__ Ref
                                        1e-6f * fmaxf(fabsf(lo.z), fabsf(hi.z)) + 1e-7f);
         A.item_bounds[2 * size_t(i)] = make_float4(lo.x - pad.x, lo.y - pad.y, lo.z - pad.z, 0.f);
         A.item_bounds[2 * size_t(i) + 1] = make_float4(hi.x + pad.x, hi.y + pad.y, hi.z + pad.z, 0.f);
-    }
+}
+
+// the same as a kernel of its own: zb_scene_rebuild_tlas needs the boxes before it builds a new tree
+__global__ void __launch_bounds__(256) k_item_bounds(const __grid_constant__ RefitArgs A) {
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < A.n_items; i += gridDim.x * blockDim.x) item_world_bounds(A, i);
+}
+
+__global__ void __launch_bounds__(1024) k_refit_tlas(const __grid_constant__ RefitArgs A) {
+    // ---- phase 1: world boxes of the items whose geometry sits under an instance transform
+    for (uint32_t i = threadIdx.x; i < A.n_items; i += blockDim.x) item_world_bounds(A, i);
     __syncthreads();
     // ---- phase 2: node boxes, deepest level first
     for (uint32_t g = 0; g < A.n_levels; g++) {
@@ -112,6 +120,35 @@ __global__ void __launch_bounds__(1024) k_refit_tlas(const __grid_constant__ Ref
 
 }  // namespace
 
+// TLAS nodes grouped by level, deepest level first (order[level_start[k] .. level_start[k + 1]) = k-th group); false when
+// the tree is deeper than RefitArgs::level_start has room for
+static bool tlas_levels(const zb_bvh_node* nodes, uint32_t n_tlas, std::vector<uint32_t>& order, std::vector<uint32_t>& level_start) {
+    std::vector<int> level(n_tlas, -1);
+    std::vector<uint32_t> todo{0u};
+    level[0] = 0;
+    int deepest = 0;
+    while (!todo.empty()) {
+        const uint32_t n = todo.back();
+        todo.pop_back();
+        for (int32_t c : {nodes[n].left, nodes[n].right})
+            if (c >= 0 && uint32_t(c) < n_tlas && level[c] < 0) {
+                level[c] = level[n] + 1;
+                deepest = std::max(deepest, level[c]);
+                todo.push_back(uint32_t(c));
+            }
+    }
+    if (deepest + 1 > ZB_MAX_TLAS_DEPTH + 2) return false;
+    order.clear();
+    level_start.clear();
+    for (int l = deepest; l >= 0; l--) {
+        level_start.push_back(uint32_t(order.size()));
+        for (uint32_t n = 0; n < n_tlas; n++)
+            if (level[n] == l) order.push_back(n);
+    }
+    level_start.push_back(uint32_t(order.size()));
+    return true;
+}
+
 // Called by zb_scene_upload after the arrays are on the device: everything a later refit needs.  Leaves s->refit empty
 // (refit unsupported for this scene) when the flat scene carries no item bounds or a mesh without a host BLAS.
 int zbr_prepare_refit(zb_scene* s, const zb_flat_scene* f, const zb_instance* instances) {
@@ -144,8 +181,9 @@ int zbr_prepare_refit(zb_scene* s, const zb_flat_scene* f, const zb_instance* in
             for (int k = 0; k < 3; k++) { lo[k] -= 1e-4f; hi[k] += 1e-4f; }  // triangle::bounding_box pads thin axes (triangle.hpp:84-101)
         } else if (in.geom_kind == ZB_GEOM_MESH) {
             const zb_mesh& m = f->meshes[in.geom_index];
-            if (m.node_count == 0) return ZB_OK;  // device-built BLAS: its root box is not known here
-            const zb_bvh_node& r = f->nodes[m.node_root];
+            if (m.node_count == 0 && in.geom_index >= s->device_mesh_roots.size()) return ZB_OK;
+            const zb_bvh_node& r = m.node_count == 0 ? s->device_mesh_roots[in.geom_index]  // built on the device at upload
+                                                     : f->nodes[m.node_root];
             const float la[3] = {r.lx_ly[0], r.lx_ly[2], r.lz_rz[0]}, lb[3] = {r.lx_ly[1], r.lx_ly[3], r.lz_rz[1]};
             const float ra[3] = {r.rx_ry[0], r.rx_ry[2], r.lz_rz[2]}, rb[3] = {r.rx_ry[1], r.rx_ry[3], r.lz_rz[3]};
             if (r.left != ZB_CHILD_EMPTY) add(la, lb);
@@ -154,29 +192,16 @@ int zbr_prepare_refit(zb_scene* s, const zb_flat_scene* f, const zb_instance* in
         for (int k = 0; k < 3; k++) { ib[8 * size_t(i) + k] = lo[k]; ib[8 * size_t(i) + 4 + k] = hi[k]; }
     }
     // TLAS nodes grouped by level, deepest first
-    std::vector<int> level(f->n_tlas_nodes, -1);
-    std::vector<uint32_t> todo{0u};
-    level[0] = 0;
-    int deepest = 0;
-    while (!todo.empty()) {
-        const uint32_t n = todo.back();
-        todo.pop_back();
-        for (int32_t c : {f->nodes[n].left, f->nodes[n].right})
-            if (c >= 0 && uint32_t(c) < f->n_tlas_nodes && level[c] < 0) {
-                level[c] = level[n] + 1;
-                deepest = std::max(deepest, level[c]);
-                todo.push_back(uint32_t(c));
-            }
-    }
-    if (deepest + 1 > ZB_MAX_TLAS_DEPTH + 2) return ZB_OK;
     std::vector<uint32_t> order;
-    R.level_start.clear();
-    for (int l = deepest; l >= 0; l--) {
-        R.level_start.push_back(uint32_t(order.size()));
-        for (uint32_t n = 0; n < f->n_tlas_nodes; n++)
-            if (level[n] == l) order.push_back(n);
-    }
-    R.level_start.push_back(uint32_t(order.size()));
+    if (!tlas_levels(f->nodes, f->n_tlas_nodes, order, R.level_start)) return ZB_OK;
+    // nodes [0, capacity) belong to the TLAS: the flattener pads the region to n_items - 1 so that any tree over these
+    // items fits (zb_scene_rebuild_tlas); an older flat scene has capacity = its node count
+    uint32_t capacity = f->n_nodes;
+    for (uint32_t m = 0; m < f->n_meshes; m++)
+        if (f->meshes[m].node_count) capacity = std::min(capacity, f->meshes[m].node_root);
+    capacity = std::max(capacity, f->n_tlas_nodes);
+    R.tlas_capacity = capacity;
+    order.resize(capacity, 0u);  // the device array has room for the largest tree
     cudaStream_t st = s->ctx->stream;
     auto put = [&](const void* host, size_t bytes, void** dev) -> int {
         ZB_CUDA(cudaMalloc(dev, std::max<size_t>(bytes, 16)));
@@ -190,7 +215,7 @@ int zbr_prepare_refit(zb_scene* s, const zb_flat_scene* f, const zb_instance* in
     if (rc) return rc;
     {
         void* nb = nullptr;
-        ZB_CUDA(cudaMalloc(&nb, size_t(f->n_tlas_nodes) * 32));
+        ZB_CUDA(cudaMalloc(&nb, size_t(capacity) * 32));
         s->allocs.push_back(nb);
         R.node_bounds = static_cast<float4*>(nb);
     }
@@ -203,15 +228,22 @@ int zbr_prepare_refit(zb_scene* s, const zb_flat_scene* f, const zb_instance* in
     return ZB_OK;
 }
 
-static int refit_one(zb_scene* s, const zb_instance* instances, uint32_t n) {
+// csrc/sah_build.cu
+int zbk_build_tlas_device(zb_context* ctx, float4* items, float4* item_bounds, uint32_t n, zb_bvh_node* nodes_out, uint32_t max_nodes,
+                          uint32_t* n_nodes);
+
+// rebuild = false: boxes of the uploaded topology refitted bottom-up (one kernel).  true: new item boxes, then a new TLAS
+// built over them on the device (binned SAH, sah_build.cu) in the same node region; items are permuted into its leaf order.
+static int refit_one(zb_scene* s, const zb_instance* instances, uint32_t n, bool rebuild) {
     zb_scene::refit_state& R = s->refit;
-    if (!R.ready) return fail(ZB_ERR_UNSUPPORTED, "zb_scene_refit: the scene was uploaded without item bounds, or a mesh BLAS was built on the device");
-    if (n != R.host_instances.size()) return fail(ZB_ERR_INVALID, "zb_scene_refit: instance count differs from the uploaded scene");
+    const char* who = rebuild ? "zb_scene_rebuild_tlas" : "zb_scene_refit";
+    if (!R.ready) return fail(ZB_ERR_UNSUPPORTED, std::string(who) + ": the scene was uploaded without item bounds");
+    if (n != R.host_instances.size()) return fail(ZB_ERR_INVALID, std::string(who) + ": instance count differs from the uploaded scene");
     std::vector<zb_instance> next(instances, instances + n);
     for (uint32_t i = 0; i < n; i++) {
         const zb_instance& old = R.host_instances[i];
         if (next[i].geom_kind != old.geom_kind || next[i].geom_index != old.geom_index)
-            return fail(ZB_ERR_INVALID, "zb_scene_refit: instance " + std::to_string(i) + " references other geometry (transform-only edits; re-flatten for anything else)");
+            return fail(ZB_ERR_INVALID, std::string(who) + ": instance " + std::to_string(i) + " references other geometry (transform-only edits; re-flatten for anything else)");
         next[i].pad[0] = old.pad[0];  // BLAS roots stay the uploaded ones
         next[i].pad[1] = old.pad[1];
     }
@@ -227,25 +259,55 @@ static int refit_one(zb_scene* s, const zb_instance* instances, uint32_t n) {
     A.item_bounds = R.item_bounds;
     A.node_bounds = R.node_bounds;
     A.order = R.order;
-    A.n_levels = uint32_t(R.level_start.size()) - 1;
-    for (size_t k = 0; k < R.level_start.size(); k++) A.level_start[k] = R.level_start[k];
     A.n_items = R.n_items;
     A.center_half = zbk_nodes_center_half() ? 1 : 0;
-    k_refit_tlas<<<1, 1024, 0, ctx->stream>>>(A);
-    ZB_CUDA(cudaGetLastError());
-    ZB_CUDA(cudaStreamSynchronize(ctx->stream));  // `next` is a local; the caller may render at once
+    if (!rebuild) {
+        A.n_levels = uint32_t(R.level_start.size()) - 1;
+        for (size_t k = 0; k < R.level_start.size(); k++) A.level_start[k] = R.level_start[k];
+        k_refit_tlas<<<1, 1024, 0, ctx->stream>>>(A);
+        ZB_CUDA(cudaGetLastError());
+        ZB_CUDA(cudaStreamSynchronize(ctx->stream));  // `next` is a local; the caller may render at once
+        ctx->stats.launches++;
+    } else {
+        k_item_bounds<<<std::max(1u, std::min((R.n_items + 255) / 256, 1024u)), 256, 0, ctx->stream>>>(A);
+        ZB_CUDA(cudaGetLastError());
+        ctx->stats.launches++;
+        zb_bvh_node* tlas = reinterpret_cast<zb_bvh_node*>(A.nodes);
+        uint32_t n_new = 0;
+        int rc = zbk_build_tlas_device(ctx, const_cast<float4*>(s->dev.items), R.item_bounds, R.n_items, tlas, R.tlas_capacity, &n_new);
+        if (rc) return rc;  // nothing but scratch and the item boxes was touched before the build's checks passed
+        cudaError_t e = zbk_convert_nodes(A.nodes, n_new, ctx->stream);
+        if (e != cudaSuccess) return fail(ZB_ERR_CUDA, std::string("zb_scene_rebuild_tlas: node re-encoding: ") + cudaGetErrorString(e));
+        // the new topology's levels, for later refits
+        std::vector<zb_bvh_node> host_nodes(n_new);
+        ZB_CUDA(cudaMemcpyAsync(host_nodes.data(), tlas, size_t(n_new) * sizeof(zb_bvh_node), cudaMemcpyDeviceToHost, ctx->stream));
+        ZB_CUDA(cudaStreamSynchronize(ctx->stream));
+        std::vector<uint32_t> order;
+        if (!tlas_levels(host_nodes.data(), n_new, order, R.level_start)) return fail(ZB_ERR_CUDA, "zb_scene_rebuild_tlas: rebuilt TLAS deeper than the cap");
+        ZB_CUDA(cudaMemcpyAsync(R.order, order.data(), order.size() * sizeof(uint32_t), cudaMemcpyHostToDevice, ctx->stream));
+        ZB_CUDA(cudaStreamSynchronize(ctx->stream));
+        R.n_tlas_nodes = n_new;
+    }
     R.host_instances.swap(next);
     s->wide = nullptr;  // the 8-wide tree (an opt-in) is not refitted
     s->dev.wide = nullptr;
-    ctx->stats.launches++;
     return ZB_OK;
 }
 
 extern "C" int zb_scene_refit(zb_scene* scene, const zb_instance* instances, uint32_t n_instances) {
     if (!scene || (n_instances && !instances)) return fail(ZB_ERR_INVALID, "zb_scene_refit: NULL argument");
-    int rc = refit_one(scene, instances, n_instances);
+    int rc = refit_one(scene, instances, n_instances, false);
     for (zb_scene* rep : scene->replicas)
-        if (!rc) rc = refit_one(rep, instances, n_instances);
+        if (!rc) rc = refit_one(rep, instances, n_instances, false);
+    if (scene->ctx) cudaSetDevice(scene->ctx->device);
+    return rc;
+}
+
+extern "C" int zb_scene_rebuild_tlas(zb_scene* scene, const zb_instance* instances, uint32_t n_instances) {
+    if (!scene || (n_instances && !instances)) return fail(ZB_ERR_INVALID, "zb_scene_rebuild_tlas: NULL argument");
+    int rc = refit_one(scene, instances, n_instances, true);
+    for (zb_scene* rep : scene->replicas)
+        if (!rc) rc = refit_one(rep, instances, n_instances, true);
     if (scene->ctx) cudaSetDevice(scene->ctx->device);
     return rc;
 }

@@ -80,6 +80,23 @@ __global__ void __launch_bounds__(256) k_prep(const float4* __restrict__ tris, u
     seg[i] = n > SB_SMALL ? 0 : -1;
 }
 
+// the same for primitives given by their boxes (TLAS items: 2 float4 each, lo and hi)
+__global__ void __launch_bounds__(256) k_prep_boxes(const float4* __restrict__ boxes, uint32_t n, float4* __restrict__ lo4, float4* __restrict__ hi4,
+                                                    uint32_t* __restrict__ idx, int* __restrict__ seg) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    lo4[i] = boxes[2 * size_t(i)];
+    hi4[i] = boxes[2 * size_t(i) + 1];
+    idx[i] = i;
+    seg[i] = n > SB_SMALL ? 0 : -1;
+}
+__global__ void __launch_bounds__(256) k_permute_pairs(const float4* __restrict__ in, const uint32_t* __restrict__ ids, uint32_t n,
+                                                       float4* __restrict__ out) {
+    const uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;  // one thread per float4
+    if (t >= 2 * n) return;
+    out[t] = in[2 * size_t(ids[t >> 1]) + (t & 1)];
+}
+
 // ---- exclusive scan of n uint32 in place: tile sums, one block over the sums, tiles again
 __global__ void __launch_bounds__(256) k_scan_tiles(const uint32_t* __restrict__ v, uint32_t n, uint32_t* __restrict__ sums) {
     __shared__ uint32_t ws[8];
@@ -419,7 +436,7 @@ ZB_DEV void grow_if(bool on, float3& lo, float3& hi, float3 qlo, float3 qhi) {
 __global__ void __launch_bounds__(128) k_small(const float4* __restrict__ lo4, const float4* __restrict__ hi4, const uint32_t* __restrict__ idx,
                                                const SmallSeg* __restrict__ small, uint32_t n_small, zb_bvh_node* __restrict__ stage,
                                                uint32_t tri_first, uint32_t* __restrict__ out_idx, uint32_t* __restrict__ counters,
-                                               int depth_cap) {
+                                               int depth_cap, float isect_cost) {
     __shared__ int src_of[4][32];
     const int w = threadIdx.x >> 5, me = threadIdx.x & 31;
     const uint32_t sidx = blockIdx.x * 4 + w;
@@ -479,11 +496,11 @@ __global__ void __launch_bounds__(128) k_small(const float4* __restrict__ lo4, c
         }
         const float3 wcen = shfl3(c, wl);
         const float ha = half_area(blo, bhi);
-        const float split_cost = ha > 0.f ? 1.0f + wc / ha : INFINITY;
+        const float split_cost = ha > 0.f ? 1.0f + isect_cost * wc / ha : INFINITY;  // one node visit + the children's expected tests
         // host rule (bvh_build.hpp): a leaf only where <= 4 primitives are cheaper tested than split, or nothing can split
         // them, or the depth cap is reached; the root always splits
         const bool can_split = wc < INFINITY;
-        bool leaf = cnt == 1 || (cnt <= SB_LEAF_MAX && parent >= 0 && (!can_split || float(cnt) <= split_cost || depth >= depth_cap));
+        bool leaf = cnt == 1 || (cnt <= SB_LEAF_MAX && parent >= 0 && (!can_split || isect_cost * float(cnt) <= split_cost || depth >= depth_cap));
         bool by_count = !leaf && (!can_split || depth + 1 + max(balanced_levels(uint32_t(wn)), balanced_levels(uint32_t(cnt - wn))) > depth_cap);
         const int n_left = by_count ? (cnt + 1) / 2 : wn;
         const float cm = axis_of(c, wa), cw = axis_of(wcen, wa);
@@ -596,23 +613,22 @@ int scan_in_place(uint32_t* v, uint32_t count, uint32_t* sums, cudaStream_t st) 
     return ZB_OK;
 }
 
-}  // namespace
+struct CoreParams {
+    uint32_t n;           // primitives (>= 2)
+    uint32_t leaf_first;  // added to every leaf's first position (global position of primitive 0)
+    uint32_t node_base;   // added to every inner child index
+    int depth_cap;        // ZB_MAX_BLAS_DEPTH / ZB_MAX_TLAS_DEPTH
+    float isect_cost;     // cost of one primitive test in node visits (host/bvh_build.hpp isect_cost)
+    uint32_t max_nodes;   // room in nodes_out
+    const char* what;
+};
 
-// Same contract as zbk_build_blas_device (lbvh.cu): tris_in / nrm_in hold n triangles (3 float4 each) in any order;
-// tris_out / nrm_out receive them in leaf order (global position tri_first); nodes_out has room for max(n - 1, 1) nodes,
-// child indices are absolute (node_base + local), the root is nodes_out[0].
-int zbk_build_blas_device_sah(zb_context* ctx, const float4* tris_in, const float4* nrm_in, uint32_t n, uint32_t tri_first,
-                              uint32_t node_base, float4* tris_out, float4* nrm_out, zb_bvh_node* nodes_out, uint32_t* n_nodes) {
+// The build proper.  prep(lo4, hi4, idx, seg) fills boxes / identity order / initial segment ids on the stream;
+// finish(order) receives the device array order[new position] = old position while the scratch is still alive.
+template <class Prep, class Finish>
+int build_core(zb_context* ctx, const CoreParams& cp, zb_bvh_node* nodes_out, uint32_t* n_nodes, Prep prep, Finish finish) {
     cudaStream_t st = ctx->stream;
-    if (n == 1) {
-        k_single<<<1, 1, 0, st>>>(tris_in, tri_first, nodes_out);
-        ZB_CUDA(cudaMemcpyAsync(tris_out, tris_in, 3 * sizeof(float4), cudaMemcpyDeviceToDevice, st));
-        ZB_CUDA(cudaMemcpyAsync(nrm_out, nrm_in, 3 * sizeof(float4), cudaMemcpyDeviceToDevice, st));
-        ZB_CUDA(cudaGetLastError());
-        ctx->stats.launches += 1;
-        *n_nodes = 1;
-        return ZB_OK;
-    }
+    const uint32_t n = cp.n;
     Scratch sc;
     const uint32_t max_segs = n / (SB_SMALL + 1) + 2;
     const unsigned nb = (n + 255) / 256, tiles = (n + SB_CHUNK - 1) / SB_CHUNK;
@@ -633,7 +649,7 @@ int zbk_build_blas_device_sah(zb_context* ctx, const float4* tris_in, const floa
     ZB_CUDA(sc.get(&counters, 4)); ZB_CUDA(sc.get(&out_idx, n)); ZB_CUDA(sc.get(&small, n)); ZB_CUDA(sc.get(&stage, n));
     ZB_CUDA(cudaMemsetAsync(stage, 0, size_t(n) * sizeof(zb_bvh_node), st));
     ZB_CUDA(cudaMemsetAsync(counters, 0, 4 * sizeof(uint32_t), st));
-    k_prep<<<nb, 256, 0, st>>>(tris_in, n, lo4[0], hi4[0], idx[0], seg[0]);
+    prep(lo4[0], hi4[0], idx[0], seg[0]);
     ZB_CUDA(cudaGetLastError());
     uint32_t m = n > SB_SMALL ? 1u : 0u;
     if (m) {
@@ -663,7 +679,7 @@ int zbk_build_blas_device_sah(zb_context* ctx, const float4* tris_in, const floa
         k_seg_prepare<<<(m + 255) / 256, 256, 0, st>>>(segs[cur], m, red, stage);
         k_bin<<<tiles, 256, 0, st>>>(lo4[cur], hi4[cur], seg[cur], n, segs[cur], bins);
         ZB_CUDA(cudaMemsetAsync(counters, 0, sizeof(uint32_t), st));
-        k_decide<<<(m + 127) / 128, 128, 0, st>>>(segs[cur], m, bins, stage, segs[cur ^ 1], counters, small, ZB_MAX_BLAS_DEPTH);
+        k_decide<<<(m + 127) / 128, 128, 0, st>>>(segs[cur], m, bins, stage, segs[cur ^ 1], counters, small, cp.depth_cap);
         k_flags<<<(n + 256) / 256, 256, 0, st>>>(lo4[cur], hi4[cur], seg[cur], n, segs[cur], flags);
         ZB_CUDA(cudaGetLastError());
         if (int rc = scan_in_place(flags, n + 1, sums, st)) return rc;
@@ -680,8 +696,8 @@ int zbk_build_blas_device_sah(zb_context* ctx, const float4* tris_in, const floa
     ZB_CUDA(cudaMemcpyAsync(&n_small, counters + 1, sizeof(uint32_t), cudaMemcpyDeviceToHost, st));
     ZB_CUDA(cudaStreamSynchronize(st));
     if (timing) cudaEventRecord(ev[1], st);
-    k_small<<<(n_small + 3) / 4, 128, 0, st>>>(lo4[cur], hi4[cur], idx[cur], small, n_small, stage, tri_first, out_idx, counters,
-                                               ZB_MAX_BLAS_DEPTH);
+    k_small<<<(n_small + 3) / 4, 128, 0, st>>>(lo4[cur], hi4[cur], idx[cur], small, n_small, stage, cp.leaf_first, out_idx, counters,
+                                               cp.depth_cap, cp.isect_cost);
     if (timing) cudaEventRecord(ev[2], st);
     k_mark<<<(n + 256) / 256, 256, 0, st>>>(stage, n, flags);
     ZB_CUDA(cudaGetLastError());
@@ -691,11 +707,14 @@ int zbk_build_blas_device_sah(zb_context* ctx, const float4* tris_in, const floa
     ZB_CUDA(cudaMemcpyAsync(&total, flags + n, sizeof(uint32_t), cudaMemcpyDeviceToHost, st));
     ZB_CUDA(cudaStreamSynchronize(st));
     if (total == 0 || total > std::max(n - 1, 1u)) return fail(ZB_ERR_CUDA, "device SAH build: inconsistent node count");
-    if (int(info[3]) > ZB_MAX_BLAS_DEPTH)
-        return fail(ZB_ERR_UNSUPPORTED, "device SAH tree of a mesh is " + std::to_string(info[3]) + " levels deep (cap " +
-                                            std::to_string(ZB_MAX_BLAS_DEPTH) + ")");
-    k_compact<<<nb, 256, 0, st>>>(stage, n, flags, info[2], int(node_base), nodes_out);
-    k_permute_tris<<<(3 * n + 255) / 256, 256, 0, st>>>(tris_in, nrm_in, out_idx, n, tris_out, nrm_out);
+    if (total > cp.max_nodes)
+        return fail(ZB_ERR_UNSUPPORTED, std::string("device SAH build: the ") + cp.what + " needs " + std::to_string(total) + " nodes, room for " +
+                                            std::to_string(cp.max_nodes));
+    if (int(info[3]) > cp.depth_cap)
+        return fail(ZB_ERR_UNSUPPORTED, std::string("device SAH tree of a ") + cp.what + " is " + std::to_string(info[3]) + " levels deep (cap " +
+                                            std::to_string(cp.depth_cap) + ")");
+    k_compact<<<nb, 256, 0, st>>>(stage, n, flags, info[2], int(cp.node_base), nodes_out);
+    finish(out_idx);
     ZB_CUDA(cudaGetLastError());
     if (timing) cudaEventRecord(ev[3], st);
     ZB_CUDA(cudaStreamSynchronize(st));  // the scratch buffers are freed on return
@@ -704,11 +723,76 @@ int zbk_build_blas_device_sah(zb_context* ctx, const float4* tris_in, const floa
         cudaEventElapsedTime(&a, ev[0], ev[1]);
         cudaEventElapsedTime(&b, ev[1], ev[2]);
         cudaEventElapsedTime(&c, ev[2], ev[3]);
-        std::fprintf(stderr, "[zb build] device SAH: %u triangles, %d levels %.3f ms, %u warp segments %.3f ms, compact + permute %.3f ms, %u nodes, depth %u\n",
-                     n, levels, a, n_small, b, c, total, info[3]);
+        std::fprintf(stderr, "[zb build] device SAH (%s): %u primitives, %d levels %.3f ms, %u warp segments %.3f ms, compact + permute %.3f ms, %u nodes, depth %u\n",
+                     cp.what, n, levels, a, n_small, b, c, total, info[3]);
         for (auto& e : ev) cudaEventDestroy(e);
     }
     ctx->stats.launches += launches + 7;
     *n_nodes = total;
     return ZB_OK;
+}
+
+}  // namespace
+
+// Same contract as zbk_build_blas_device (lbvh.cu): tris_in / nrm_in hold n triangles (3 float4 each) in any order;
+// tris_out / nrm_out receive them in leaf order (global position tri_first); nodes_out has room for max(n - 1, 1) nodes,
+// child indices are absolute (node_base + local), the root is nodes_out[0].
+int zbk_build_blas_device_sah(zb_context* ctx, const float4* tris_in, const float4* nrm_in, uint32_t n, uint32_t tri_first,
+                              uint32_t node_base, float4* tris_out, float4* nrm_out, zb_bvh_node* nodes_out, uint32_t* n_nodes) {
+    cudaStream_t st = ctx->stream;
+    if (n == 1) {
+        k_single<<<1, 1, 0, st>>>(tris_in, tri_first, nodes_out);
+        ZB_CUDA(cudaMemcpyAsync(tris_out, tris_in, 3 * sizeof(float4), cudaMemcpyDeviceToDevice, st));
+        ZB_CUDA(cudaMemcpyAsync(nrm_out, nrm_in, 3 * sizeof(float4), cudaMemcpyDeviceToDevice, st));
+        ZB_CUDA(cudaGetLastError());
+        ctx->stats.launches += 1;
+        *n_nodes = 1;
+        return ZB_OK;
+    }
+    const CoreParams cp{n, tri_first, node_base, ZB_MAX_BLAS_DEPTH, 1.0f, std::max(n - 1, 1u), "mesh"};
+    return build_core(
+        ctx, cp, nodes_out, n_nodes,
+        [&](float4* lo4, float4* hi4, uint32_t* idx, int* seg) { k_prep<<<(n + 255) / 256, 256, 0, st>>>(tris_in, n, lo4, hi4, idx, seg); },
+        [&](const uint32_t* order) { k_permute_tris<<<(3 * n + 255) / 256, 256, 0, st>>>(tris_in, nrm_in, order, n, tris_out, nrm_out); });
+}
+
+// TLAS over n items from their world boxes (2 float4 each), in place: nodes_out = the scene's TLAS region (root at 0, room
+// for max_nodes), items and item_bounds (2 float4 per item both) are permuted into leaf order through a temporary copy.
+// Same cost model as the flattener's host build (host/flatten.hpp: isect_cost 1.5, leaves of <= 4 items, depth cap
+// ZB_MAX_TLAS_DEPTH).
+int zbk_build_tlas_device(zb_context* ctx, float4* items, float4* item_bounds, uint32_t n, zb_bvh_node* nodes_out, uint32_t max_nodes,
+                          uint32_t* n_nodes) {
+    cudaStream_t st = ctx->stream;
+    if (n == 0) { *n_nodes = 0; return ZB_OK; }
+    float4* tmp = nullptr;
+    ZB_CUDA(cudaMalloc(&tmp, size_t(n) * 4 * sizeof(float4)));
+    cudaMemcpyAsync(tmp, items, size_t(n) * 2 * sizeof(float4), cudaMemcpyDeviceToDevice, st);
+    cudaMemcpyAsync(tmp + 2 * size_t(n), item_bounds, size_t(n) * 2 * sizeof(float4), cudaMemcpyDeviceToDevice, st);
+    int rc = ZB_OK;
+    if (n == 1) {  // one leaf under a root whose right child is empty
+        zb_bvh_node nd{};
+        float4 b[2];
+        cudaMemcpyAsync(b, item_bounds, sizeof(b), cudaMemcpyDeviceToHost, st);
+        cudaStreamSynchronize(st);
+        nd.lx_ly[0] = b[0].x; nd.lx_ly[1] = b[1].x; nd.lx_ly[2] = b[0].y; nd.lx_ly[3] = b[1].y;
+        nd.rx_ry[0] = INFINITY; nd.rx_ry[1] = -INFINITY; nd.rx_ry[2] = INFINITY; nd.rx_ry[3] = -INFINITY;
+        nd.lz_rz[0] = b[0].z; nd.lz_rz[1] = b[1].z; nd.lz_rz[2] = INFINITY; nd.lz_rz[3] = -INFINITY;
+        nd.left = int(~0u);  // first 0, count 1
+        nd.right = ZB_CHILD_EMPTY;
+        cudaMemcpyAsync(nodes_out, &nd, sizeof(nd), cudaMemcpyHostToDevice, st);
+        cudaStreamSynchronize(st);
+        *n_nodes = 1;
+    } else {
+        const CoreParams cp{n, 0u, 0u, ZB_MAX_TLAS_DEPTH, 1.5f, max_nodes, "TLAS"};
+        rc = build_core(
+            ctx, cp, nodes_out, n_nodes,
+            [&](float4* lo4, float4* hi4, uint32_t* idx, int* seg) { k_prep_boxes<<<(n + 255) / 256, 256, 0, st>>>(item_bounds, n, lo4, hi4, idx, seg); },
+            [&](const uint32_t* order) {
+                k_permute_pairs<<<(2 * n + 255) / 256, 256, 0, st>>>(tmp, order, n, items);
+                k_permute_pairs<<<(2 * n + 255) / 256, 256, 0, st>>>(tmp + 2 * size_t(n), order, n, item_bounds);
+            });
+    }
+    cudaStreamSynchronize(st);
+    cudaFree(tmp);
+    return rc;
 }

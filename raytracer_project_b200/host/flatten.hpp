@@ -132,6 +132,15 @@ public:
         out->n_tlas_nodes = uint32_t(tl.size());
         // BLAS nodes were collected with mesh-local child indices; append them after the TLAS
         std::vector<zb_bvh_node> all = tl;
+        // room for any TLAS the device may build over these items later (zb_scene_rebuild_tlas): a binary tree over n items
+        // has at most n - 1 inner nodes.  The spare nodes are unreachable and empty.
+        {
+            zb_bvh_node spare{};
+            spare.lx_ly[0] = spare.lx_ly[2] = spare.rx_ry[0] = spare.rx_ry[2] = spare.lz_rz[0] = spare.lz_rz[2] = INFINITY;
+            spare.lx_ly[1] = spare.lx_ly[3] = spare.rx_ry[1] = spare.rx_ry[3] = spare.lz_rz[1] = spare.lz_rz[3] = -INFINITY;
+            spare.left = spare.right = ZB_CHILD_EMPTY;
+            while (all.size() + 1 < order.size()) all.push_back(spare);
+        }
         for (size_t m = 0; m < out->meshes.size(); m++) {
             uint32_t root = uint32_t(all.size());
             for (zb_bvh_node nd : blas_nodes[m]) {

@@ -929,6 +929,74 @@ def test_scene_refit_equals_fresh_flatten(gpu_ctx, tmp_path):
         api.free_flat(f)
 
 
+@pytest.mark.parametrize("gpu_blas", [False, True], ids=["host_blas", "device_blas"])
+def test_scene_rebuild_tlas_on_device(gpu_ctx, tmp_path, gpu_blas):
+    """zb_scene_rebuild_tlas: the scene uploaded at move = 0 gets the instance table of move = 1 and a NEW TLAS built on the
+    device over the moved items (sah_build.cu).  Every ray is answered like a fresh flatten + upload of the moved scene
+    answers it; a refit of the rebuilt tree back to move = 0 works too (its levels were re-derived); with meshes whose
+    BLAS was built on the device the same holds (their root boxes are read back at upload)."""
+    flats = {}
+    for m in (0.0, 1.0):
+        txt, cfg, files = scenes.refit_demo(move=m)
+        d = tmp_path / f"m{int(m)}"
+        flats[m] = api.flatten_zscene(path=scenes.materialize(str(d), txt, cfg, files), gpu_blas=gpu_blas)
+    sc = gpu_ctx.upload(flats[0.0])
+    fresh = {m: gpu_ctx.upload(flats[m]) for m in (0.0, 1.0)}
+
+    def same_answers(a, b, what):
+        la, pa, ta = a.primary_ids(cfg)
+        lb, pb, tb = b.primary_ids(cfg)
+        assert (la == lb).mean() >= 0.9999 and np.allclose(ta[la == lb], tb[la == lb], rtol=1e-6, atol=0, equal_nan=True), what
+        fa, fb = a.render(cfg, seed=4)["beauty"], b.render(cfg, seed=4)["beauty"]
+        differ = (np.abs(fa - fb).max(axis=2) > 0).mean()
+        print(f"{what}: ids equal on {(la == lb).mean() * 100:.4f} %, frames differ on {differ * 100:.4f} % of the pixels")
+        assert differ < 1e-3, what  # items were re-ordered: exact ties between two items may resolve the other way
+
+    sc.rebuild_tlas(flats[1.0])
+    same_answers(sc, fresh[1.0], "rebuilt at move 1")
+    sc.refit(flats[0.0])
+    same_answers(sc, fresh[0.0], "rebuilt tree refitted back to move 0")
+    sc.rebuild_tlas(flats[0.0])
+    same_answers(sc, fresh[0.0], "rebuilt at move 0")
+    # traversal work of the rebuilt tree against the flattener's tree for the same placement
+    work = {}
+    for key, s in (("rebuilt", sc), ("flattened", fresh[0.0])):
+        s.render(cfg, seed=4, stats=True)
+        st = gpu_ctx.stats()
+        assert st["stack_overflows"] == 0
+        work[key] = (st["node_visits"] + st["prim_tests"]) / st["rays"]
+    print(f"TLAS work per ray: device-rebuilt {work['rebuilt']:.2f}, flattener {work['flattened']:.2f}")
+    assert work["rebuilt"] <= 1.15 * work["flattened"]
+    for s in [sc] + list(fresh.values()):
+        s.close()
+    for f in flats.values():
+        api.free_flat(f)
+
+
+def test_device_tlas_build_over_a_thousand_items(gpu_ctx):
+    """The Weekend scene (485 spheres: phase A of the builder runs, not only the warp phase): TLAS rebuilt on the device
+    from the uploaded boxes answers every primary ray like the flattener's TLAS, with no more traversal work."""
+    txt, cfg = scenes.weekend(seed=1, width=320, height=180, spp=4)
+    flat = api.flatten_zscene(txt)
+    a, b = gpu_ctx.upload(flat), gpu_ctx.upload(flat)
+    b.rebuild_tlas(flat)
+    la, pa, ta = a.primary_ids(cfg)
+    lb, pb, tb = b.primary_ids(cfg)
+    assert np.array_equal(la, lb) and np.array_equal(ta, tb)
+    work = []
+    for s in (a, b):
+        s.render(cfg, seed=2, stats=True)
+        st = gpu_ctx.stats()
+        assert st["stack_overflows"] == 0
+        work.append((st["node_visits"] + st["prim_tests"]) / st["rays"])
+    print(f"Weekend TLAS work per ray: flattener {work[0]:.2f}, device-rebuilt {work[1]:.2f}")
+    assert work[1] <= 1.1 * work[0]
+    fa, fb = a.render(cfg, seed=2)["beauty"], b.render(cfg, seed=2)["beauty"]
+    assert (np.abs(fa - fb).max(axis=2) > 0).mean() < 1e-3
+    a.close(); b.close()
+    api.free_flat(flat)
+
+
 def test_fused_finishing_kernel_equals_three_kernel_chain(gpu_ctx):
     """k_finish_fused (bloom + sharpening + process() in one pass over shared-memory tiles) against k_bloom_h + k_bloom_v +
     k_finish on a frame whose size is not a multiple of the tile (ragged edges, image borders inside the halo), for several
