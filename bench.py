@@ -238,7 +238,7 @@ def ours(args):
     # ZB_BENCH_CACHE=dir keeps the flattened scene of a config as dir/NAME.zbfs for later runs on the same box (the host
     # BVH build of the 10 M-triangle config takes ~100 s, during which every GPU of the box idles)
     cache = os.environ.get("ZB_BENCH_CACHE")
-    zbfs = os.path.join(cache, f"{name}{'_lbvh' if args.gpu_blas else ''}.zbfs") if cache else f"/tmp/zb_bench_{name}_{job}.zbfs"
+    zbfs = os.path.join(cache, f"{name}{'_devblas' if args.gpu_blas else ''}.zbfs") if cache else f"/tmp/zb_bench_{name}_{job}.zbfs"
     t_prep = time.time()
     if not files:
         flat = api.flatten_zscene(txt)
@@ -459,7 +459,10 @@ def main():
     ap.add_argument("--config", default="headline", choices=list(CONFIGS))
     ap.add_argument("--partition", default="auto", choices=["auto", "samples", "tiles"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
-    ap.add_argument("--gpu-blas", action="store_true", help="mesh BLASes built on the device at upload (binned SAH, csrc/sah_build.cu; ZB_GPU_BUILDER=0: linear BVH, csrc/lbvh.cu) instead of the host SAH build")
+    ap.add_argument("--gpu-blas", dest="gpu_blas", action="store_true", default=True,
+                    help="mesh BLASes built on the device at upload (binned SAH, csrc/sah_build.cu; ZB_GPU_BUILDER=0: linear BVH, csrc/lbvh.cu): "
+                         "the default, as in zenith::camera")
+    ap.add_argument("--host-blas", dest="gpu_blas", action="store_false", help="mesh BLASes built by the host flattener (host/bvh_build.hpp)")
     ap.add_argument("--spp", type=int, default=0, help="profiling runs only: override the config's samples per pixel (the workload name says so)")
     args = ap.parse_args()
     if args.spp > 0:

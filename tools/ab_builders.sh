@@ -8,11 +8,11 @@ run() {  # tag config extra-args...
   local tag=$1 cfg=$2; shift 2
   python bench.py --config $cfg --steps 3 --warmup 3 --no-cpu-baseline "$@" > gpurun_out/abb_${cfg}_$tag.json 2> gpurun_out/abb_${cfg}_$tag.err; echo "$cfg $tag rc=$?"
 }
-run host c3
+run host c3 --host-blas
 ZB_GPU_BUILDER=1 run dsah c3 --gpu-blas
 ZB_GPU_BUILDER=0 run lbvh c3 --gpu-blas
 if [ "${WITH_C5:-0}" = 1 ]; then
-  run host c5 --spp 16
+  run host c5 --spp 16 --host-blas
   ZB_GPU_BUILDER=1 run dsah c5 --spp 16 --gpu-blas
   ZB_GPU_BUILDER=0 run lbvh c5 --spp 16 --gpu-blas
 fi

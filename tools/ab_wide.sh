@@ -6,8 +6,8 @@ export ZB_BENCH_CACHE=/tmp/zb_cache
 timeout 600 python -m pytest tests/test_gpu_parity.py -x -q -s -k "wide_tree or primary_ids" 2>&1 | grep -E "face ids|passed|failed|Error|assert" | head -20
 for w in 1 0; do
   for b in ${BLOCKS:-0}; do
-    ZB_WIDE_BUILD=1 ZB_WIDE=$w ZB_PQ_BLOCKS=$b python bench.py --config c3 --steps 3 --warmup 3 --no-cpu-baseline > gpurun_out/ab_c3_w${w}_b$b.json 2> gpurun_out/ab_c3_w${w}_b$b.err; echo "c3 wide=$w blocks=$b rc=$?"
-    ZB_WIDE_BUILD=1 ZB_WIDE=$w ZB_PQ_BLOCKS=$b python bench.py --config c5 --spp 16 --steps 3 --warmup 1 --no-cpu-baseline > gpurun_out/ab_c5_w${w}_b$b.json 2> gpurun_out/ab_c5_w${w}_b$b.err; echo "c5@16spp wide=$w blocks=$b rc=$?"
+    ZB_WIDE_BUILD=1 ZB_WIDE=$w ZB_PQ_BLOCKS=$b python bench.py --config c3 --steps 3 --warmup 3 --no-cpu-baseline --host-blas > gpurun_out/ab_c3_w${w}_b$b.json 2> gpurun_out/ab_c3_w${w}_b$b.err; echo "c3 wide=$w blocks=$b rc=$?"
+    ZB_WIDE_BUILD=1 ZB_WIDE=$w ZB_PQ_BLOCKS=$b python bench.py --config c5 --spp 16 --steps 3 --warmup 1 --no-cpu-baseline --host-blas > gpurun_out/ab_c5_w${w}_b$b.json 2> gpurun_out/ab_c5_w${w}_b$b.err; echo "c5@16spp wide=$w blocks=$b rc=$?"
   done
 done
 python - <<'PY'
