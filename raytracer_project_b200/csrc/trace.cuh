@@ -28,6 +28,10 @@ static_assert(1 + ZB_MAX_TLAS_DEPTH + 3 + ZB_MAX_BLAS_DEPTH <= ZB_STACK, "traver
 #ifndef ZB_BRANCHLESS_POP
 #define ZB_BRANCHLESS_POP 0  // measured: Weekend +7 % time, mesh -1.3 % (profiles/r01_feature_sets.txt)
 #endif
+#ifndef ZB_PREFETCH_FAR
+#define ZB_PREFETCH_FAR 0  // mesh feature sets: prefetch the deferred child's node / first triangle when it is pushed.
+                           // Measured slower: C3 67.4 vs 66.0 ms, C5 at 16 spp 190.1 vs 184.0 ms (profiles/r02_traversal_experiments.txt)
+#endif
 #define ZB_EXIT_INSTANCE ((int)0x80000000)
 
 struct Hit {
@@ -338,7 +342,7 @@ struct RayWalk {
         rb.set(o, d);
     }
 
-    template <bool STATS>
+    template <bool STATS, bool PREFETCH = false>
     ZB_DEV void node_step(const SceneDev& sc, float tmin, int* stack, Counters& cnt) {
         const float4* np = sc.nodes + 4 * size_t(cur);
         const float4 n0 = __ldg(np), n1 = __ldg(np + 1), n2 = __ldg(np + 2);
@@ -385,6 +389,14 @@ struct RayWalk {
             // predicated form of this loop).  A push at the last slot overwrites the canary begin() put there; trace() checks it.
             stack[sp] = right_first ? cl : cr;
             sp = min(sp + 1, ZB_STACK - 1);
+            if (PREFETCH) {
+                // mesh scenes are bound by the latency of dependent node fetches (ncu: long scoreboard 5 stall cycles per issue,
+                // L1 hit 60 %): the deferred child is fetched again only when the stack pops it — ask for its line now
+                const int far = right_first ? cl : cr;
+                const void* p = far >= 0 ? static_cast<const void*>(sc.nodes + 4 * size_t(far))
+                                         : static_cast<const void*>(sc.tris + 3 * size_t((~uint32_t(far)) >> 3));
+                asm volatile("prefetch.global.L1 [%0];" ::"l"(p));
+            }
         }
         if (!(hl || hr)) next = stack[--sp];
         cur = next;
@@ -615,7 +627,7 @@ ZB_DEV bool trace(const SceneDev& sc, float3 o, float3 d, float tmin, float tmax
     RayWalk w;
     w.begin(sc, o, d, tmax, stack);
     while (w.cur != ZB_TRAVERSAL_DONE) {
-        while (w.cur >= 0) w.node_step<STATS>(sc, tmin, stack, cnt);
+        while (w.cur >= 0) w.node_step<STATS, (F & ZB_F_MESH) != 0 && ZB_PREFETCH_FAR != 0>(sc, tmin, stack, cnt);
         if (w.cur == ZB_TRAVERSAL_DONE) break;
         w.leaf_step<STATS, F>(sc, o, d, tmin, rng, stack, cnt);
     }
