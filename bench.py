@@ -267,6 +267,7 @@ def ours(args):
         ctx.group_join(rank, handles, f"/zb_bench_{job}")
     scene = ctx.upload(flat)
     scene_bytes = flat.contents.nbytes()
+    n_meshes = int(flat.contents.n_meshes)
     flush = torch.empty(256 * 1024 * 1024, device=dev, dtype=torch.uint8)  # > 126 MB L2
     spl = 64 if name == "c5" else 0  # progressive launches for the 8.5 G-path frame
 
@@ -406,7 +407,7 @@ def ours(args):
                        "rays_per_path": rays / max(paths_counted, 1.0), "node_visits_per_ray": node_visits / max(rays, 1.0),
                        "prim_tests_per_ray": prim_tests / max(rays, 1.0), "kernel": kernel_name(pick),
                        "feature_set": FEATURE_NAMES.get(feat, str(feat)),
-                       "blas": ("device binned SAH (sah_build.cu)" if os.environ.get("ZB_GPU_BUILDER", "1") != "0" else "device LBVH (lbvh.cu)") if args.gpu_blas else "host binned SAH"},
+                       "blas": "no meshes" if not n_meshes else ("device binned SAH (sah_build.cu)" if os.environ.get("ZB_GPU_BUILDER", "1") != "0" else "device LBVH (lbvh.cu)") if args.gpu_blas else "host binned SAH"},
             "kernel_ms_per_step": kernel_ms,
             "e2e": {"value": e2e_value, "unit": "Mpaths/s", "ms_per_step": e2e_ms_per_step,
                     "h2d_bytes_per_step": (scene_bytes + 512) * world, "d2h_bytes_per_step": n_pix * 12, "checksum": checksum,

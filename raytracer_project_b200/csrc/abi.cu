@@ -101,6 +101,8 @@ extern "C" int zb_context_destroy(zb_context* ctx) {
     cudaStreamSynchronize(ctx->stream);
     cudaFree(ctx->counters);
     cudaFree(ctx->arena);
+    ctx->build_scratch.release();
+    ctx->build_tmp.release();
     cudaFree(ctx->accum);
     cudaFree(ctx->accum_aux);
     cudaFree(ctx->out_f4);
@@ -317,10 +319,14 @@ static int build_device_blas(zb_scene* s, const zb_flat_scene* f, std::vector<zb
     if (f->n_nodes)
         ZB_CUDA(cudaMemcpyAsync(nodes, f->nodes, size_t(f->n_nodes) * sizeof(zb_bvh_node), cudaMemcpyHostToDevice, s->ctx->stream));
     float4 *tmp_t = nullptr, *tmp_n = nullptr;
-    ZB_CUDA(cudaMalloc(&tmp_t, largest * 3 * sizeof(float4)));
-    if (cudaMalloc(&tmp_n, largest * 3 * sizeof(float4)) != cudaSuccess) {
-        cudaFree(tmp_t);
-        return fail(ZB_ERR_CUDA, "zb_scene_upload: out of device memory for the BLAS build");
+    {
+        void* tmp = nullptr;
+        if (s->ctx->build_tmp.get(2 * largest * 3 * sizeof(float4), &tmp) != cudaSuccess) {
+            cudaGetLastError();
+            return fail(ZB_ERR_CUDA, "zb_scene_upload: out of device memory for the BLAS build");
+        }
+        tmp_t = static_cast<float4*>(tmp);
+        tmp_n = tmp_t + largest * 3;
     }
     uint32_t next = f->n_nodes;
     std::vector<uint32_t> roots(f->n_meshes, 0);
@@ -358,8 +364,6 @@ static int build_device_blas(zb_scene* s, const zb_flat_scene* f, std::vector<zb
         if (f->meshes[m].node_count == 0 && f->meshes[m].tri_count > 0)
             cudaMemcpyAsync(&s->device_mesh_roots[m], nodes + roots[m], sizeof(zb_bvh_node), cudaMemcpyDeviceToHost, s->ctx->stream);
     cudaStreamSynchronize(s->ctx->stream);
-    cudaFree(tmp_t);
-    cudaFree(tmp_n);
     if (rc) return rc;
     for (auto& in : instances)
         if (in.geom_kind == ZB_GEOM_MESH) in.pad[0] = roots[in.geom_index];

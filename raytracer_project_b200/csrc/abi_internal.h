@@ -38,6 +38,25 @@ struct zb_context {
     void* arena = nullptr;  // scene arena kept across zb_scene_destroy / zb_scene_upload (abi.cu)
     size_t arena_bytes = 0;
     bool arena_in_use = false;
+    // scratch of the device BVH builds (sah_build.cu) and the triangle copies they read, kept across uploads: a dozen
+    // cudaMalloc / cudaFree of hundreds of MB per upload cost more than the build.  Released by zb_context_destroy.
+    struct cached_buf {
+        void* p = nullptr;
+        size_t bytes = 0;
+        cudaError_t get(size_t need, void** out) {
+            if (bytes < need) {
+                cudaFree(p);
+                p = nullptr;
+                bytes = 0;
+                const cudaError_t e = cudaMalloc(&p, need);
+                if (e != cudaSuccess) return e;
+                bytes = need;
+            }
+            *out = p;
+            return cudaSuccess;
+        }
+        void release() { cudaFree(p); p = nullptr; bytes = 0; }
+    } build_scratch, build_tmp;
     // scratch reused across renders
     float4* accum = nullptr;
     float4* accum_aux = nullptr;

@@ -586,14 +586,16 @@ __global__ void __launch_bounds__(256) k_permute_tris(const float4* __restrict__
     nrm_out[t] = __ldg(nrm_in + src);
 }
 
-// one allocation for all scratch of a build (a dozen cudaMalloc / cudaFree pairs cost more than the build of a small mesh)
+// all scratch of a build is carved from ONE buffer that the context keeps across builds (zb_context::build_scratch)
 struct Scratch {
     char* base = nullptr;
     size_t size = 0, used = 0;
-    ~Scratch() { cudaFree(base); }
-    cudaError_t reserve(size_t bytes) {
-        size = bytes;
-        return cudaMalloc(&base, bytes);
+    cudaError_t reserve(zb_context* ctx, size_t bytes) {
+        void* p = nullptr;
+        const cudaError_t e = ctx->build_scratch.get(bytes, &p);
+        base = static_cast<char*>(p);
+        size = e == cudaSuccess ? bytes : 0;
+        return e;
     }
     template <class T> cudaError_t get(T** p, size_t count) {
         const size_t bytes = (std::max<size_t>(count, 1) * sizeof(T) + 255) & ~size_t(255);
@@ -638,7 +640,7 @@ int build_core(zb_context* ctx, const CoreParams& cp, zb_bvh_node* nodes_out, ui
     Seg* segs[2];
     SmallSeg* small;
     zb_bvh_node* stage;
-    ZB_CUDA(sc.reserve(size_t(n) * (2 * (16 + 16 + 4 + 4) + 4 + 4 + 16 + 64) + size_t(max_segs) * (2 * sizeof(Seg) + 48 + 3 * SB_BINS * 32) +
+    ZB_CUDA(sc.reserve(ctx, size_t(n) * (2 * (16 + 16 + 4 + 4) + 4 + 4 + 16 + 64) + size_t(max_segs) * (2 * sizeof(Seg) + 48 + 3 * SB_BINS * 32) +
                        (size_t(n) / SB_CHUNK + 2) * 4 + 32 * 256));
     for (int k = 0; k < 2; k++) {
         ZB_CUDA(sc.get(&lo4[k], n)); ZB_CUDA(sc.get(&hi4[k], n)); ZB_CUDA(sc.get(&idx[k], n)); ZB_CUDA(sc.get(&seg[k], n));
@@ -717,7 +719,7 @@ int build_core(zb_context* ctx, const CoreParams& cp, zb_bvh_node* nodes_out, ui
     finish(out_idx);
     ZB_CUDA(cudaGetLastError());
     if (timing) cudaEventRecord(ev[3], st);
-    ZB_CUDA(cudaStreamSynchronize(st));  // the scratch buffers are freed on return
+    ZB_CUDA(cudaStreamSynchronize(st));  // the caller may free what prep / finish read
     if (timing) {
         float a = 0, b = 0, c = 0;
         cudaEventElapsedTime(&a, ev[0], ev[1]);
