@@ -69,6 +69,7 @@ extern "C" int zb_context_set_tuning(zb_context* ctx, const char* key, long long
     else if (k == "gather_p2p") t.gather_p2p = int(value);
     else if (k == "gpu_builder") t.gpu_builder = int(value);
     else if (k == "build_timing") t.build_timing = int(value);
+    else if (k == "group_timing") t.group_timing = int(value);
     else if (k == "wide") t.wide = value != 0;
     else if (k == "fuse_finish") t.fuse_finish = value != 0;
 #ifdef ZB_EXPERIMENTS

@@ -26,6 +26,8 @@
 #include <algorithm>
 #include <atomic>
 #include <chrono>
+#include <cstdio>
+#include <string>
 
 #include "abi_internal.h"
 
@@ -371,6 +373,28 @@ extern "C" int zb_group_leave(zb_context* ctx) {
     return ZB_OK;
 }
 
+// opt-in phase timer of one frame (tuning "group_timing" / ZB_GROUP_TIMING=1): wall clock at the phase boundaries, printed by
+// every rank to stderr
+struct PhaseTimer {
+    bool on;
+    std::chrono::steady_clock::time_point t0, last;
+    std::string line;
+    explicit PhaseTimer(bool enabled) : on(enabled) { if (on) t0 = last = std::chrono::steady_clock::now(); }
+    void mark(const char* what) {
+        if (!on) return;
+        const auto now = std::chrono::steady_clock::now();
+        char buf[96];
+        std::snprintf(buf, sizeof(buf), " %s %.3f", what, std::chrono::duration<double, std::milli>(now - last).count());
+        line += buf;
+        last = now;
+    }
+    void done(int rank) {
+        if (!on) return;
+        std::fprintf(stderr, "[zb group] rank %d:%s | total %.3f ms\n", rank, line.c_str(),
+                     std::chrono::duration<double, std::milli>(last - t0).count());
+    }
+};
+
 static int render_impl(zb_context* ctx, const zb_scene* scene, const zb_camera* cam, const zb_environment* env,
                        const zb_render_opts* opts, zb_outputs* out, const volatile int* cancel, zb_progress_fn progress, void* user);
 
@@ -449,6 +473,7 @@ static int render_impl(zb_context* ctx, const zb_scene* scene, const zb_camera* 
     const bool gather_tiles = M[0].P.tile_ranks > 1;  // also a single GPU asked for one tile stripe: only the owner holds sums
 
     std::vector<FrameCopy> jobs;
+    PhaseTimer pt(ctx->tuning.group_timing != 0);
     for (int pass = 0; pass < (light ? 2 : 1); pass++) {
         // beauty + AOVs: the queue kernel for the beauty sums, the AOV sums from a primary-ray pass of their own (k_aov_pass)
         // written as fixed point into the aux words; light passes: the queue kernel's LIGHT mode
@@ -509,8 +534,10 @@ static int render_impl(zb_context* ctx, const zb_scene* scene, const zb_camera* 
             if (pass == 0) ZB_CUDA(cudaEventRecord(m.c->ev[1], m.c->stream));
             ZB_CUDA(cudaEventRecord(G->render_done[m.c->group_rank], m.c->stream));
         }
+        pt.mark("launch");
         rc = host_barrier(G);  // every rank has recorded its event before anybody waits on it
         if (rc) return rc;
+        pt.mark("barrier1");
         // ---- every local member: wait for all ranks' sums, gather + resolve its band, copy it home
         const int planes = gather_mode == PQ_AUX ? 4 : gather_mode == PQ_LIGHT ? 2 : 1;
         for (Member& m : M) {
@@ -562,14 +589,17 @@ static int render_impl(zb_context* ctx, const zb_scene* scene, const zb_camera* 
         }
         (void)gather_tiles;
         G->frame++;
+        pt.mark("issue");
         rc = zbr_widen_all(jobs);
         jobs.clear();
         if (rc) return rc;
+        pt.mark("widen(waits for the kernel)");
         for (Member& m : M) {
             ZB_CUDA(cudaSetDevice(m.c->device));
             if (pass == 0) ZB_CUDA(cudaEventRecord(m.c->ev[3], m.c->stream));
             ZB_CUDA(cudaStreamSynchronize(m.c->stream));
         }
+        pt.mark("sync");
         if (pass == 0 && light) {  // keep the beauty pass's counters apart from the light passes'
             for (Member& m : M) {
                 ZB_CUDA(cudaSetDevice(m.c->device));
@@ -586,9 +616,11 @@ static int render_impl(zb_context* ctx, const zb_scene* scene, const zb_camera* 
         }
         rc = host_barrier(G);  // the frame is complete in the caller's buffer of every rank
         if (rc) return rc;
+        pt.mark("barrier2");
     }
     // ---- statistics: the sums over the local members (multi-process: this rank's own)
     zb_stats total{};
+    PhaseTimer* ptp = &pt;
     for (Member& m : M) {
         zb_context* c = m.c;
         ZB_CUDA(cudaSetDevice(c->device));
@@ -611,5 +643,7 @@ static int render_impl(zb_context* ctx, const zb_scene* scene, const zb_camera* 
     ZB_CUDA(cudaSetDevice(ctx->device));
     total.n_gpus = uint32_t(n);
     ctx->stats = total;
+    ptp->mark("stats");
+    ptp->done(ctx->group_rank);
     return zbr_check_overflow(ctx, "zb_render");
 }

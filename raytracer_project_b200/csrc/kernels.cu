@@ -870,6 +870,7 @@ ZbTuning zbk_tuning_from_env() {
     t.gather_p2p = int(num("ZB_GATHER_P2P", 1));
     t.gpu_builder = int(num("ZB_GPU_BUILDER", 1));
     t.build_timing = int(num("ZB_BUILD_TIMING", 0));
+    t.group_timing = int(num("ZB_GROUP_TIMING", 0));
     t.wide = int(num("ZB_WIDE", 1));
     t.pq_redeal = int(num("ZB_PQ_REDEAL", 0));
     return t;

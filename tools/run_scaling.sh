@@ -16,6 +16,7 @@ timeout 300 python -m pytest tests/test_multi_gpu.py -x -q 2>&1 | tail -2
 for n in 8 4 2 1; do run headline_n$n $n --steps 5 --warmup 3; done
 run c1_n8 8 --config c1 --steps 5 --warmup 3
 run c1_n1 1 --config c1 --steps 5 --warmup 3
+if [ "${C5_ONLY_N8:-0}" = 1 ]; then run c5_n8 8 --config c5 --steps 2 --warmup 1; fi
 if [ "${SKIP_C5:-0}" = 0 ]; then
   run c5_n8 8 --config c5 --steps 2 --warmup 1
   run c5_n8_tiles 8 --config c5 --steps 2 --warmup 1 --partition tiles
