@@ -53,9 +53,9 @@ ZB_DEV float half_area(float3 lo, float3 hi) {
     return (dx < 0.f || dy < 0.f || dz < 0.f) ? 0.f : dx * dy + dy * dz + dz * dx;
 }
 // inner levels a balanced tree over n primitives needs (host/bvh_build.hpp balanced_levels)
-ZB_DEV int balanced_levels(uint32_t n) {
+ZB_DEV int balanced_levels(uint32_t n, uint32_t leaf_max = SB_LEAF_MAX) {
     int l = 0;
-    while (n > SB_LEAF_MAX) { n = (n + 1) / 2; l++; }
+    while (n > leaf_max) { n = (n + 1) / 2; l++; }
     return l;
 }
 // child `side` of a staged node: box and code (zb_bvh_node keeps both children's boxes in the parent)
@@ -436,7 +436,7 @@ ZB_DEV void grow_if(bool on, float3& lo, float3& hi, float3 qlo, float3 qhi) {
 __global__ void __launch_bounds__(128) k_small(const float4* __restrict__ lo4, const float4* __restrict__ hi4, const uint32_t* __restrict__ idx,
                                                const SmallSeg* __restrict__ small, uint32_t n_small, zb_bvh_node* __restrict__ stage,
                                                uint32_t tri_first, uint32_t* __restrict__ out_idx, uint32_t* __restrict__ counters,
-                                               int depth_cap, float isect_cost) {
+                                               int depth_cap, float isect_cost, int leaf_max) {
     __shared__ int src_of[4][32];
     const int w = threadIdx.x >> 5, me = threadIdx.x & 31;
     const uint32_t sidx = blockIdx.x * 4 + w;
@@ -500,8 +500,8 @@ __global__ void __launch_bounds__(128) k_small(const float4* __restrict__ lo4, c
         // host rule (bvh_build.hpp): a leaf only where <= 4 primitives are cheaper tested than split, or nothing can split
         // them, or the depth cap is reached; the root always splits
         const bool can_split = wc < INFINITY;
-        bool leaf = cnt == 1 || (cnt <= SB_LEAF_MAX && parent >= 0 && (!can_split || isect_cost * float(cnt) <= split_cost || depth >= depth_cap));
-        bool by_count = !leaf && (!can_split || depth + 1 + max(balanced_levels(uint32_t(wn)), balanced_levels(uint32_t(cnt - wn))) > depth_cap);
+        bool leaf = cnt == 1 || (cnt <= leaf_max && parent >= 0 && (!can_split || isect_cost * float(cnt) <= split_cost || depth >= depth_cap));
+        bool by_count = !leaf && (!can_split || depth + 1 + max(balanced_levels(uint32_t(wn), leaf_max), balanced_levels(uint32_t(cnt - wn), leaf_max)) > depth_cap);
         const int n_left = by_count ? (cnt + 1) / 2 : wn;
         const float cm = axis_of(c, wa), cw = axis_of(wcen, wa);
         const bool is_left = by_count ? (me - slo) < n_left : (cm < cw || (cm == cw && me < wl));
@@ -623,6 +623,7 @@ struct CoreParams {
     float isect_cost;     // cost of one primitive test in node visits (host/bvh_build.hpp isect_cost)
     uint32_t max_nodes;   // room in nodes_out
     const char* what;
+    int leaf_max = SB_LEAF_MAX;  // primitives per leaf at most (<= 8: three bits of the leaf code)
 };
 
 // The build proper.  prep(lo4, hi4, idx, seg) fills boxes / identity order / initial segment ids on the stream;
@@ -699,7 +700,7 @@ int build_core(zb_context* ctx, const CoreParams& cp, zb_bvh_node* nodes_out, ui
     ZB_CUDA(cudaStreamSynchronize(st));
     if (timing) cudaEventRecord(ev[1], st);
     k_small<<<(n_small + 3) / 4, 128, 0, st>>>(lo4[cur], hi4[cur], idx[cur], small, n_small, stage, cp.leaf_first, out_idx, counters,
-                                               cp.depth_cap, cp.isect_cost);
+                                               cp.depth_cap, cp.isect_cost, cp.leaf_max);
     if (timing) cudaEventRecord(ev[2], st);
     k_mark<<<(n + 256) / 256, 256, 0, st>>>(stage, n, flags);
     ZB_CUDA(cudaGetLastError());
@@ -751,7 +752,10 @@ int zbk_build_blas_device_sah(zb_context* ctx, const float4* tris_in, const floa
         *n_nodes = 1;
         return ZB_OK;
     }
-    const CoreParams cp{n, tri_first, node_base, ZB_MAX_BLAS_DEPTH, 1.0f, std::max(n - 1, 1u), "mesh"};
+    CoreParams cp{n, tri_first, node_base, ZB_MAX_BLAS_DEPTH, 1.0f, std::max(n - 1, 1u), "mesh"};
+    // measurement knobs (tuning "blas_isect_pct", "blas_leaf"); the defaults are the host builder's
+    cp.isect_cost = 0.01f * float(std::max(1, ctx->tuning.blas_isect_pct));
+    cp.leaf_max = std::max(1, std::min(8, ctx->tuning.blas_leaf));
     return build_core(
         ctx, cp, nodes_out, n_nodes,
         [&](float4* lo4, float4* hi4, uint32_t* idx, int* seg) { k_prep<<<(n + 255) / 256, 256, 0, st>>>(tris_in, n, lo4, hi4, idx, seg); },
