@@ -306,9 +306,9 @@ int zbr_copy_issue(zb_context* ctx, const float* dev_rgb, size_t n_floats, doubl
                    std::vector<FrameCopy>& jobs) {
     if (!n_floats) return ZB_OK;
     if ((stage_offset_floats + n_floats) * sizeof(float) > ctx->pinned_bytes) return fail(ZB_ERR_INVALID, "frame copy: pinned stage too small");
-    // 3 MiB per copy for a whole frame; an eighth of the job (>= 256 KiB) for the small bands of a multi-GPU frame, so that
-    // the copy of chunk c + 1 overlaps the widening of chunk c there too
-    const size_t chunk = std::min(size_t(3) << 18, std::max(size_t(1) << 16, (n_floats / 8 + 1023) & ~size_t(1023)));
+    // 3 MiB per copy for a whole frame; a quarter of the job (>= 512 KiB) for the small bands of a multi-GPU frame, so that
+    // the copy of chunk c + 1 overlaps the widening of chunk c there too (every copy costs ~10 us of set-up: not more of them)
+    const size_t chunk = std::min(size_t(3) << 18, std::max(size_t(1) << 17, (n_floats / 4 + 1023) & ~size_t(1023)));
     const size_t n_chunks = (n_floats + chunk - 1) / chunk;
     size_t first = 0;
     for (const FrameCopy& j : jobs)
@@ -336,29 +336,39 @@ int zbr_copy_issue(zb_context* ctx, const float* dev_rgb, size_t n_floats, doubl
 // event has fired; up to 8 host threads share the chunks of all jobs (round-robin over the jobs, so that every GPU's
 // first chunk is served first).
 int zbr_widen_all(std::vector<FrameCopy>& jobs) {
-    struct Item { const FrameCopy* job; size_t chunk; };
+    // A work item is a PIECE of a chunk (<= 32 Ki floats): the chunk that arrives last is then widened by all threads
+    // together instead of by one (a 3 MiB chunk takes one thread ~1 ms — that was most of what the end-to-end frame
+    // added after the kernel).
+    constexpr size_t PIECE = size_t(1) << 15;
+    struct Item { const FrameCopy* job; size_t chunk, begin, end; };
     std::vector<Item> items;
     size_t longest = 0;
     for (const FrameCopy& j : jobs) longest = std::max(longest, j.begin.size() - 1);
     for (size_t c = 0; c < longest; c++)
         for (const FrameCopy& j : jobs)
-            if (c + 1 < j.begin.size()) items.push_back({&j, c});
+            if (c + 1 < j.begin.size())
+                for (size_t b = j.begin[c]; b < j.begin[c + 1]; b += PIECE) items.push_back({&j, c, b, std::min(b + PIECE, j.begin[c + 1])});
     if (items.empty()) return ZB_OK;
     const unsigned hw = std::max(1u, std::thread::hardware_concurrency());
     size_t total_floats = 0;
     for (const FrameCopy& j : jobs) total_floats += j.begin.back();
-    // one thread per 256 Ki floats of work, at most 8: the ranks of a process group share the host's cores
-    const size_t n_thr = std::min(std::min<size_t>(std::min<size_t>(hw, 8), items.size()), total_floats / (size_t(1) << 18) + 1);
+    // one thread per 128 Ki floats of work, at most 8: the ranks of a process group share the host's cores
+    const size_t n_thr = std::min(std::min<size_t>(std::min<size_t>(hw, 8), items.size()), total_floats / (size_t(1) << 17) + 1);
     std::atomic<size_t> next{0};
     std::atomic<int> err{0};
     auto work = [&]() {
+        size_t seen_job = ~size_t(0), seen_chunk = ~size_t(0);  // the last (job, chunk) this thread has waited for
         for (;;) {
             const size_t k = next.fetch_add(1);
             if (k >= items.size()) return;
-            const FrameCopy& j = *items[k].job;
-            if (cudaEventSynchronize(j.ctx->chunk_ev[j.first_event + items[k].chunk]) != cudaSuccess) { err.store(1); return; }
-            const size_t b = j.begin[items[k].chunk], e = j.begin[items[k].chunk + 1];
-            zbh_widen_f32_f64(j.stage + b, j.dst + b, e - b);
+            const Item& it = items[k];
+            const FrameCopy& j = *it.job;
+            if (size_t(it.job - jobs.data()) != seen_job || it.chunk != seen_chunk) {
+                if (cudaEventSynchronize(j.ctx->chunk_ev[j.first_event + it.chunk]) != cudaSuccess) { err.store(1); return; }
+                seen_job = size_t(it.job - jobs.data());
+                seen_chunk = it.chunk;
+            }
+            zbh_widen_f32_f64(j.stage + it.begin, j.dst + it.begin, it.end - it.begin);
         }
     };
     std::vector<std::thread> pool;
