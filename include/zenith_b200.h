@@ -335,7 +335,9 @@ int zb_scene_refit(zb_scene* scene, const zb_instance* instances, uint32_t n_ins
  * scene's TLAS node region; the items are permuted into the new leaf order.  The flattener pads the TLAS region to
  * n_items - 1 nodes so that any tree fits; a flat scene without that room fails with ZB_ERR_UNSUPPORTED when the new tree
  * needs more nodes than the uploaded one had.  Closest hits equal those of a freshly flattened scene; later
- * zb_scene_refit calls refit the new topology.  Launch-bound: ~1 ms for a few thousand items. */
+ * zb_scene_refit calls refit the new topology.  Launch-bound: ~1 ms for a few thousand items.  If either call fails after
+ * its argument checks (CUDA error, no room for the new tree), the instance table is already the new one while the tree is
+ * the old one: refit again or upload the scene again before rendering. */
 int zb_scene_rebuild_tlas(zb_scene* scene, const zb_instance* instances, uint32_t n_instances);
 
 /* Drop-in for camera::render's hot part (camera.hpp:236-250 -> :404-579): blocking; fills host
