@@ -35,6 +35,7 @@ extern "C" int zb_context_create(int device, zb_context** out) {
     ZB_CUDA(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
     c->own_stream = true;
     ZB_CUDA(cudaMalloc(&c->counters, 8 * sizeof(unsigned long long)));
+    ZB_CUDA(cudaMallocHost(&c->counters_host, 8 * sizeof(unsigned long long)));
     for (auto& ev : c->ev) ZB_CUDA(cudaEventCreate(&ev));
     *out = c;
     return ZB_OK;
@@ -103,6 +104,7 @@ extern "C" int zb_context_destroy(zb_context* ctx) {
     cudaSetDevice(ctx->device);
     cudaStreamSynchronize(ctx->stream);
     cudaFree(ctx->counters);
+    cudaFreeHost(ctx->counters_host);
     cudaFree(ctx->arena);
     ctx->build_scratch.release();
     ctx->build_tmp.release();

@@ -35,6 +35,7 @@ struct zb_context {
     int sm_count = 0, cc_major = 0, cc_minor = 0;
     size_t l2_bytes = 0;
     unsigned long long* counters = nullptr;  // 8 x u64 on the device
+    unsigned long long* counters_host = nullptr;  // pinned copy: fetched with the frame's last copies, read after its last sync
     void* arena = nullptr;  // scene arena kept across zb_scene_destroy / zb_scene_upload (abi.cu)
     size_t arena_bytes = 0;
     bool arena_in_use = false;
@@ -114,6 +115,8 @@ int zbr_fill_params(zb_context* ctx, const zb_scene* scene, const zb_camera* cam
 int zbr_owned_tiles(const RenderParams& P);
 
 int zbr_read_counters(zb_context* ctx);
+int zbr_fetch_counters_async(zb_context* ctx);  // enqueue the copy into counters_host ...
+void zbr_take_counters(zb_context* ctx);        // ... and, after a stream sync, move it into ctx->stats
 int zbr_check_overflow(zb_context* ctx, const char* who);
 
 // One frame copy in flight: packed RGB floats on the device -> this context's pinned stage -> the caller's 3-double rows.

@@ -402,10 +402,16 @@ int d2h_rgb_f64(zb_context* ctx, double* host, const float4* dev, size_t pixels)
     return ZB_OK;
 }
 
+void take_counters(zb_context* ctx, const unsigned long long* c);
+
 int read_counters(zb_context* ctx) {
-    unsigned long long c[8];
-    ZB_CUDA(cudaMemcpyAsync(c, ctx->counters, sizeof(c), cudaMemcpyDeviceToHost, ctx->stream));
+    ZB_CUDA(cudaMemcpyAsync(ctx->counters_host, ctx->counters, 8 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, ctx->stream));
     ZB_CUDA(cudaStreamSynchronize(ctx->stream));
+    take_counters(ctx, ctx->counters_host);
+    return ZB_OK;
+}
+
+void take_counters(zb_context* ctx, const unsigned long long* c) {
     ctx->stats.rays = c[0];
     ctx->stats.node_visits = c[1];
     ctx->stats.box_tests = 2 * c[1];
@@ -413,7 +419,6 @@ int read_counters(zb_context* ctx) {
     ctx->stats.instance_visits = c[3];
     ctx->stats.paths = c[4];
     ctx->stats.stack_overflows = uint32_t(std::min<unsigned long long>(c[6], 0xFFFFFFFFull));
-    return ZB_OK;
 }
 
 // a ray that ran out of traversal stack has dropped geometry: the frame is not the scene's (csrc/trace.cuh)
@@ -432,6 +437,11 @@ int zbr_fill_params(zb_context* ctx, const zb_scene* scene, const zb_camera* cam
 }
 int zbr_owned_tiles(const RenderParams& P) { return owned_tiles(P); }
 int zbr_read_counters(zb_context* ctx) { return read_counters(ctx); }
+int zbr_fetch_counters_async(zb_context* ctx) {
+    ZB_CUDA(cudaMemcpyAsync(ctx->counters_host, ctx->counters, 8 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, ctx->stream));
+    return ZB_OK;
+}
+void zbr_take_counters(zb_context* ctx) { take_counters(ctx, ctx->counters_host); }
 int zbr_check_overflow(zb_context* ctx, const char* who) { return check_overflow(ctx, who); }
 
 extern "C" int zb_render_device(zb_context* ctx, const zb_scene* scene, const zb_camera* cam,

@@ -594,9 +594,11 @@ static int render_impl(zb_context* ctx, const zb_scene* scene, const zb_camera* 
         jobs.clear();
         if (rc) return rc;
         pt.mark("widen(waits for the kernel)");
+        const bool last_pass = pass == (light ? 1 : 0);
         for (Member& m : M) {
             ZB_CUDA(cudaSetDevice(m.c->device));
             if (pass == 0) ZB_CUDA(cudaEventRecord(m.c->ev[3], m.c->stream));
+            if (last_pass && (rc = zbr_fetch_counters_async(m.c)) != ZB_OK) return rc;  // rides on this sync: no round trip of its own
             ZB_CUDA(cudaStreamSynchronize(m.c->stream));
         }
         pt.mark("sync");
@@ -625,8 +627,7 @@ static int render_impl(zb_context* ctx, const zb_scene* scene, const zb_camera* 
         zb_context* c = m.c;
         ZB_CUDA(cudaSetDevice(c->device));
         const uint32_t launches = c->stats.launches, pick = c->stats.kernel_pick;
-        rc = zbr_read_counters(c);
-        if (rc) return rc;
+        zbr_take_counters(c);  // fetched before the frame's last stream sync
         float ms = 0;
         ZB_CUDA(cudaEventElapsedTime(&ms, c->ev[0], c->ev[1]));
         total.kernel_ms = std::max(total.kernel_ms, double(ms));
