@@ -71,6 +71,7 @@ extern "C" int zb_context_set_tuning(zb_context* ctx, const char* key, long long
     else if (k == "gpu_builder") t.gpu_builder = int(value);
     else if (k == "build_timing") t.build_timing = int(value);
     else if (k == "group_timing") t.group_timing = int(value);
+    else if (k == "build_check") t.build_check = int(value);
     else if (k == "blas_isect_pct") t.blas_isect_pct = int(value);
     else if (k == "blas_leaf") t.blas_leaf = int(value);
     else if (k == "wide") t.wide = value != 0;

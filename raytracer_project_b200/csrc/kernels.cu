@@ -871,6 +871,7 @@ ZbTuning zbk_tuning_from_env() {
     t.gpu_builder = int(num("ZB_GPU_BUILDER", 1));
     t.build_timing = int(num("ZB_BUILD_TIMING", 0));
     t.group_timing = int(num("ZB_GROUP_TIMING", 0));
+    t.build_check = int(num("ZB_BUILD_CHECK", 0));
     t.blas_isect_pct = int(num("ZB_BLAS_ISECT_PCT", 100));
     t.blas_leaf = int(num("ZB_DEVICE_BLAS_LEAF", 4));
     t.wide = int(num("ZB_WIDE", 1));

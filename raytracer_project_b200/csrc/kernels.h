@@ -20,6 +20,7 @@ struct ZbTuning {
     int wide = 1;        // 1: walk the scene's 8-wide compressed tree where it has one; 0: always the binary tree
     int gpu_builder = 1; // device BLAS build (ZB_FLATTEN_GPU_BLAS): 1 = binned SAH (sah_build.cu), 0 = linear BVH (lbvh.cu)
     int blas_isect_pct = 100, blas_leaf = 4;  // device SAH builder: cost of a triangle test in percent of a node visit, leaf size
+    int build_check = 0;  // 1 = every device SAH build is followed by a structural check of the tree (tests)
     int group_timing = 0; // 1 = zb_render prints the wall-clock phases of every frame to stderr
     int build_timing = 0; // 1 = device BLAS builders print their phase times to stderr
     int gather_p2p = 1;  // multi-GPU combine: 1 = fused peer-memory resolve-gather kernel, 0 = staged copies (A/B)

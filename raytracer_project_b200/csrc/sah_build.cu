@@ -615,6 +615,90 @@ int scan_in_place(uint32_t* v, uint32_t count, uint32_t* sums, cudaStream_t st) 
     return ZB_OK;
 }
 
+// ---- optional structural check of a finished tree (tuning "build_check"; the GPU tests switch it on): every child index
+// and leaf range is in bounds, every node but the root has exactly one parent, every primitive lies in exactly one leaf and
+// inside that leaf's box, and an inner child's box equals the union of the boxes that child node stores.
+// err[0] counts violations, err[1] keeps the first violating node + 1.
+struct TriBoxes {  // primitive p of a mesh: its (padded) triangle box, from the permuted triangles
+    const float4* tris;
+    uint32_t first;
+    ZB_DEV void get(uint32_t p, float3& lo, float3& hi) const {
+        const TriBox b = tri_box(tris + 3 * size_t(p - first));
+        lo = b.lo;
+        hi = b.hi;
+    }
+};
+struct PairBoxes {  // primitive p of a TLAS: the permuted item bounds
+    const float4* boxes;
+    ZB_DEV void get(uint32_t p, float3& lo, float3& hi) const {
+        lo = f3(boxes[2 * size_t(p)]);
+        hi = f3(boxes[2 * size_t(p) + 1]);
+    }
+};
+template <class Boxes>
+__global__ void __launch_bounds__(256) k_validate(const zb_bvh_node* __restrict__ nodes, uint32_t n_nodes, int node_base, uint32_t leaf_first,
+                                                  uint32_t n, Boxes boxes, uint32_t* __restrict__ parents, uint32_t* __restrict__ cover,
+                                                  uint32_t* __restrict__ err) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n_nodes) return;
+    const zb_bvh_node nd = nodes[i];
+    auto bad = [&]() { atomicAdd(err, 1u); atomicCAS(err + 1, 0u, i + 1u); };
+    for (int side = 0; side < 2; side++) {
+        const int code = side ? nd.right : nd.left;
+        const float3 lo = side ? f3(nd.rx_ry[0], nd.rx_ry[2], nd.lz_rz[2]) : f3(nd.lx_ly[0], nd.lx_ly[2], nd.lz_rz[0]);
+        const float3 hi = side ? f3(nd.rx_ry[1], nd.rx_ry[3], nd.lz_rz[3]) : f3(nd.lx_ly[1], nd.lx_ly[3], nd.lz_rz[1]);
+        if (code == ZB_CHILD_EMPTY) { bad(); continue; }  // the builder never leaves a child empty (n >= 2)
+        if (code >= 0) {
+            const int c = code - node_base;
+            if (c < 1 || uint32_t(c) >= n_nodes) { bad(); continue; }
+            atomicAdd(parents + c, 1u);
+            const zb_bvh_node ch = nodes[c];
+            const float3 ulo = f3(fminf(ch.lx_ly[0], ch.rx_ry[0]), fminf(ch.lx_ly[2], ch.rx_ry[2]), fminf(ch.lz_rz[0], ch.lz_rz[2]));
+            const float3 uhi = f3(fmaxf(ch.lx_ly[1], ch.rx_ry[1]), fmaxf(ch.lx_ly[3], ch.rx_ry[3]), fmaxf(ch.lz_rz[1], ch.lz_rz[3]));
+            if (ulo.x != lo.x || ulo.y != lo.y || ulo.z != lo.z || uhi.x != hi.x || uhi.y != hi.y || uhi.z != hi.z) bad();
+        } else {
+            const uint32_t lc = ~uint32_t(code), first = lc >> 3, count = (lc & 7u) + 1u;
+            if (first < leaf_first || first + count > leaf_first + n) { bad(); continue; }
+            float3 ulo = f3(INFINITY, INFINITY, INFINITY), uhi = f3(-INFINITY, -INFINITY, -INFINITY);
+            for (uint32_t p = first; p < first + count; p++) {
+                atomicAdd(cover + (p - leaf_first), 1u);
+                float3 plo, phi;
+                boxes.get(p, plo, phi);
+                ulo = f3(fminf(ulo.x, plo.x), fminf(ulo.y, plo.y), fminf(ulo.z, plo.z));
+                uhi = f3(fmaxf(uhi.x, phi.x), fmaxf(uhi.y, phi.y), fmaxf(uhi.z, phi.z));
+            }
+            if (ulo.x != lo.x || ulo.y != lo.y || ulo.z != lo.z || uhi.x != hi.x || uhi.y != hi.y || uhi.z != hi.z) bad();
+        }
+    }
+}
+__global__ void __launch_bounds__(256) k_validate_counts(const uint32_t* __restrict__ parents, uint32_t n_nodes, const uint32_t* __restrict__ cover,
+                                                         uint32_t n, uint32_t* __restrict__ err) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n_nodes && parents[i] != (i == 0 ? 0u : 1u)) { atomicAdd(err, 1u); atomicCAS(err + 1, 0u, i + 1u); }
+    if (i < n && cover[i] != 1u) { atomicAdd(err, 1u); atomicCAS(err + 1, 0u, 0x80000000u | i); }
+}
+template <class Boxes>
+int validate_tree(zb_context* ctx, const zb_bvh_node* nodes, uint32_t n_nodes, uint32_t node_base, uint32_t leaf_first, uint32_t n, Boxes boxes,
+                  const char* what) {
+    cudaStream_t st = ctx->stream;
+    uint32_t* buf = nullptr;
+    const size_t words = size_t(n_nodes) + n + 2;
+    ZB_CUDA(cudaMalloc(&buf, words * sizeof(uint32_t)));
+    cudaMemsetAsync(buf, 0, words * sizeof(uint32_t), st);
+    uint32_t *err = buf, *parents = buf + 2, *cover = buf + 2 + n_nodes;
+    k_validate<<<(n_nodes + 255) / 256, 256, 0, st>>>(nodes, n_nodes, int(node_base), leaf_first, n, boxes, parents, cover, err);
+    k_validate_counts<<<(std::max(n_nodes, n) + 255) / 256, 256, 0, st>>>(parents, n_nodes, cover, n, err);
+    uint32_t h[2] = {0, 0};
+    cudaMemcpyAsync(h, err, sizeof(h), cudaMemcpyDeviceToHost, st);
+    const cudaError_t e = cudaStreamSynchronize(st);
+    cudaFree(buf);
+    if (e != cudaSuccess) return fail(ZB_ERR_CUDA, std::string("device SAH build check: ") + cudaGetErrorString(e));
+    if (h[0])
+        return fail(ZB_ERR_CUDA, std::string("device SAH build check (") + what + "): " + std::to_string(h[0]) + " violations, first at " +
+                                     ((h[1] & 0x80000000u) ? "primitive " + std::to_string(h[1] & 0x7FFFFFFFu) : "node " + std::to_string(h[1] - 1)));
+    return ZB_OK;
+}
+
 struct CoreParams {
     uint32_t n;           // primitives (>= 2)
     uint32_t leaf_first;  // added to every leaf's first position (global position of primitive 0)
@@ -756,10 +840,12 @@ int zbk_build_blas_device_sah(zb_context* ctx, const float4* tris_in, const floa
     // measurement knobs (tuning "blas_isect_pct", "blas_leaf"); the defaults are the host builder's
     cp.isect_cost = 0.01f * float(std::max(1, ctx->tuning.blas_isect_pct));
     cp.leaf_max = std::max(1, std::min(8, ctx->tuning.blas_leaf));
-    return build_core(
+    int rc = build_core(
         ctx, cp, nodes_out, n_nodes,
         [&](float4* lo4, float4* hi4, uint32_t* idx, int* seg) { k_prep<<<(n + 255) / 256, 256, 0, st>>>(tris_in, n, lo4, hi4, idx, seg); },
         [&](const uint32_t* order) { k_permute_tris<<<(3 * n + 255) / 256, 256, 0, st>>>(tris_in, nrm_in, order, n, tris_out, nrm_out); });
+    if (!rc && ctx->tuning.build_check) rc = validate_tree(ctx, nodes_out, *n_nodes, node_base, tri_first, n, TriBoxes{tris_out, tri_first}, "mesh");
+    return rc;
 }
 
 // TLAS over n items from their world boxes (2 float4 each), in place: nodes_out = the scene's TLAS region (root at 0, room
@@ -800,5 +886,6 @@ int zbk_build_tlas_device(zb_context* ctx, float4* items, float4* item_bounds, u
     }
     cudaStreamSynchronize(st);
     cudaFree(tmp);
+    if (!rc && n > 1 && ctx->tuning.build_check) rc = validate_tree(ctx, nodes_out, *n_nodes, 0u, 0u, n, PairBoxes{item_bounds}, "TLAS");
     return rc;
 }

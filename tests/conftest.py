@@ -24,5 +24,6 @@ def lib():
 def gpu_ctx():
     from raytracer_project_b200 import api
     ctx = api.Context(0)
+    ctx.set_tuning("build_check", 1)  # every device-built tree is structurally checked (csrc/sah_build.cu validate_tree)
     yield ctx
     ctx.close()
