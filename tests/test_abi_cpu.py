@@ -71,6 +71,35 @@ def test_weekend_flatten_counts_and_bvh_invariants():
     api.free_flat(flat)
 
 
+def test_tlas_region_has_room_for_a_device_rebuild():
+    """The flattener pads the TLAS node region to n_items - 1 nodes (zb_scene_rebuild_tlas builds any tree over the items in
+    place); the spare nodes are unreachable and empty, and mesh BLAS roots lie behind the region."""
+    txt, cfg = scenes.weekend(seed=1)
+    flat = api.flatten_zscene(txt)
+    f = flat.contents
+    nodes, _ = _views(f)
+    child = nodes[:, 12:14].copy().view(np.int32)
+    assert f.n_tlas_nodes <= f.n_items - 1 <= f.n_nodes
+    assert np.all(child[f.n_tlas_nodes:f.n_items - 1] == -2**31)
+    reachable = {0}
+    todo = [0]
+    while todo:
+        for c in child[todo.pop()]:
+            if c >= 0 and int(c) not in reachable:
+                reachable.add(int(c))
+                todo.append(int(c))
+    assert reachable == set(range(f.n_tlas_nodes))
+    api.free_flat(flat)
+    txt, cfg, files = scenes.refit_demo()
+    import tempfile
+    with tempfile.TemporaryDirectory() as d:
+        flat = api.flatten_zscene(path=scenes.materialize(d, txt, cfg, files))
+    f = flat.contents
+    roots = [f.meshes_array()[m].node_root for m in range(f.n_meshes)]
+    assert roots and min(roots) >= max(f.n_items - 1, f.n_tlas_nodes)
+    api.free_flat(flat)
+
+
 def test_flatten_wrappers_and_flags():
     w = scenes.SceneWriter()
     glass = w.dielectric(1.5)
