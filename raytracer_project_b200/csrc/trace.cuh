@@ -32,6 +32,10 @@ static_assert(1 + ZB_MAX_TLAS_DEPTH + 3 + ZB_MAX_BLAS_DEPTH <= ZB_STACK, "traver
 #define ZB_PREFETCH_FAR 0  // mesh feature sets: prefetch the deferred child's node / first triangle when it is pushed.
                            // Measured slower: C3 67.4 vs 66.0 ms, C5 at 16 spp 190.1 vs 184.0 ms (profiles/r02_traversal_experiments.txt)
 #endif
+#ifndef ZB_PREFETCH_POP
+#define ZB_PREFETCH_POP 0  // BLAS leaves: prefetch the node the stack hands out next, before the triangle tests.
+                           // Measured slower: C3 66.6 vs 66.1 ms, C5 at 16 spp 186.1 vs 184.2 ms (profiles/r02_traversal_experiments.txt)
+#endif
 #define ZB_EXIT_INSTANCE ((int)0x80000000)
 
 struct Hit {
@@ -417,6 +421,13 @@ struct RayWalk {
             // triangles of a mesh BLAS leaf, in object space
             const uint32_t code = ~uint32_t(cur);
             const uint32_t first = code >> 3, end = first + (code & 7u) + 1u;
+#if ZB_PREFETCH_POP
+            {   // the entry the stack will hand out after this leaf is certain to be fetched: ask for its line before the
+                // triangle tests instead of after them
+                const int nxt = stack[sp - 1];
+                if (nxt >= 0) asm volatile("prefetch.global.L1 [%0];" ::"l"(sc.nodes + 4 * size_t(nxt)));
+            }
+#endif
             for (uint32_t i = first; i < end; i++) {
                 const float4* tp = sc.tris + 3 * size_t(i);
                 float4 a = __ldg(tp), b = __ldg(tp + 1), c = __ldg(tp + 2);
