@@ -255,6 +255,7 @@ def ours(args):
                 api.save_flat(flat0, zbfs + ".tmp")
                 os.rename(zbfs + ".tmp", zbfs)
             shutil.rmtree(d, ignore_errors=True)
+            os.sync()  # the scene files (up to 0.7 GB of OBJ text) and the flat-scene file: no write-back left to run under the timed steps
         barrier()
         flat = flat0 if rank == 0 else api.load_flat(zbfs)
     prep_s = time.time() - t_prep
@@ -351,8 +352,12 @@ def ours(args):
         sc2.render(cfg, seed=1, beauty_out=host_rgb, partition=args.partition, samples_per_launch=spl)  # blocking, collective
         t_render = time.perf_counter()
         sc2.close()
+        t_close = time.perf_counter()
         rank_barrier()
         t1 = time.perf_counter()
+        if os.environ.get("ZB_BENCH_TRACE"):
+            print(f"[bench e2e] step {k}: upload {(t_up - t0) * 1e3:.3f} render {(t_render - t_up) * 1e3:.3f} close {(t_close - t_render) * 1e3:.3f} "
+                  f"barrier {(t1 - t_close) * 1e3:.3f} ms", file=sys.stderr, flush=True)
         if k >= e2e_warm:
             e2e_ms.append((t1 - t0) * 1e3)
             e2e_parts.append(((t_up - t0) * 1e3, (t_render - t_up) * 1e3, (t1 - t_render) * 1e3))
