@@ -53,8 +53,8 @@ typedef struct zb_bvh_node {
     uint32_t pad0, pad1;
 } zb_bvh_node;
 #define ZB_CHILD_EMPTY ((int32_t)0x80000000)
-/* Depth caps (inner nodes on a root-to-leaf path) both builders keep — the host binned-SAH builder falls back to median
- * splits where SAH would exceed them, the device LBVH is measured after the build — and zb_scene_upload verifies: the
+/* Depth caps (inner nodes on a root-to-leaf path) all builders keep — the host and the device binned-SAH builders fall back
+ * to splits by count where SAH would exceed them, the device linear BVH is measured after the build — and zb_scene_upload verifies: the
  * per-ray traversal stack (csrc/trace.cuh) holds one deferred child per level.  The reference's recursive traversal
  * (bvh.hpp:46-54) has no such bound; its median-split tree is log2(N) deep by construction (bvh.hpp:15-44). */
 #define ZB_MAX_TLAS_DEPTH 22
