@@ -307,6 +307,16 @@ int zb_group_barrier(zb_context* ctx);
 int zb_group_leave(zb_context* ctx);
 int zb_context_set_stream(zb_context* ctx, void* stream);
 int zb_context_destroy(zb_context* ctx);
+/* Optional: [ptr, ptr + bytes) is an output buffer the caller hands to zb_render again and again — the reference's
+ * render_accumulator is sized once by reset_accumulator and reused (camera.hpp:209-233) — and stays valid until
+ * zb_context_unregister_output or zb_context_destroy.  The range is page-locked (cudaHostRegister) and zb_render then sends
+ * every finished band of rows straight into it as doubles, one DMA per output plane, instead of staging packed floats and
+ * widening them with host threads: the same values bit for bit, no host work after the kernel (what matters when 8 ranks
+ * share one host's cores).  Applies when EVERY buffer requested in zb_outputs lies inside registered ranges; at most 8
+ * ranges per context; ZB_ERR_UNSUPPORTED (and the staged path stays in use) when the range cannot be page-locked.
+ * No counterpart in the reference (its workers write the accumulator directly, camera.hpp:531). */
+int zb_context_register_output(zb_context* ctx, void* ptr, size_t bytes);
+int zb_context_unregister_output(zb_context* ctx, void* ptr);
 /* A/B switches for measurements and equality tests; product defaults need none of them.  Read once from the environment at
  * context creation (ZB_PQ, ZB_NO_LEAN, ZB_PQ_BLOCKS, ZB_GATHER_P2P), changed afterwards only here.  Keys: "pq" (0 tile-bound
  * k_render, 1 path-queue beauty kernel, 2 also its AOV / light modes), "no_lean" (1: general kernels), "pq_blocks" (6..8),

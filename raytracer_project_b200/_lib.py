@@ -129,6 +129,8 @@ SYMBOLS = {
     "zb_device_info": (C.c_int, [C.c_void_p, C.POINTER(C.c_int), C.POINTER(C.c_int), C.POINTER(C.c_int), C.POINTER(C.c_size_t)]),
     "zb_scene_upload": (C.c_int, [C.c_void_p, C.POINTER(FlatScene), C.POINTER(C.c_void_p)]),
     "zb_scene_destroy": (C.c_int, [C.c_void_p]),
+    "zb_context_register_output": (C.c_int, [C.c_void_p, C.c_void_p, C.c_size_t]),
+    "zb_context_unregister_output": (C.c_int, [C.c_void_p, C.c_void_p]),
     "zb_scene_refit": (C.c_int, [C.c_void_p, C.c_void_p, C.c_uint32]),
     "zb_scene_rebuild_tlas": (C.c_int, [C.c_void_p, C.c_void_p, C.c_uint32]),
     "zb_render": (C.c_int, [C.c_void_p, C.c_void_p, C.POINTER(Camera), C.POINTER(Environment), C.POINTER(RenderOpts),

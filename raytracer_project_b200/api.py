@@ -253,6 +253,18 @@ class Context:
         """zb_context_set_tuning: A/B switches ("pq", "no_lean", "pq_blocks", ...); the product defaults need none."""
         check(self.lib.zb_context_set_tuning(self.h, key.encode(), int(value)))
 
+    def register_output(self, array) -> bool:
+        """zb_context_register_output for a numpy array the caller keeps alive and passes to render(beauty_out=...) /
+        render_into() repeatedly: finished rows are then DMA'd straight into it.  False when it cannot be page-locked."""
+        try:
+            check(self.lib.zb_context_register_output(self.h, array.ctypes.data, array.nbytes))
+            return True
+        except _lib.ZbError:
+            return False
+
+    def unregister_output(self, array):
+        check(self.lib.zb_context_unregister_output(self.h, array.ctypes.data))
+
     def device_count(self) -> int:
         return int(self.lib.zb_context_device_count(self.h))
 

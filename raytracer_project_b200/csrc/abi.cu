@@ -106,6 +106,9 @@ extern "C" int zb_context_destroy(zb_context* ctx) {
     cudaStreamSynchronize(ctx->stream);
     cudaFree(ctx->counters);
     cudaFreeHost(ctx->counters_host);
+    for (const auto& r : ctx->registered_out) cudaHostUnregister(r.ptr);
+    cudaGetLastError();
+    cudaFree(ctx->rgb_pack64);
     cudaFree(ctx->arena);
     ctx->build_scratch.release();
     ctx->build_tmp.release();
@@ -380,6 +383,35 @@ static int build_device_blas(zb_scene* s, const zb_flat_scene* f, std::vector<zb
 }
 
 static int upload_one(zb_context* ctx, const zb_flat_scene* f, zb_scene** out);
+
+extern "C" int zb_context_register_output(zb_context* ctx, void* ptr, size_t bytes) {
+    if (!ctx || !ptr || !bytes) return fail(ZB_ERR_INVALID, "zb_context_register_output: NULL argument");
+    if (ctx->out_registered(ptr, bytes)) return ZB_OK;
+    if (ctx->registered_out.size() >= 8) return fail(ZB_ERR_UNSUPPORTED, "zb_context_register_output: at most 8 ranges per context");
+    ZB_CUDA(cudaSetDevice(ctx->device));
+    const cudaError_t e = cudaHostRegister(ptr, bytes, cudaHostRegisterPortable);
+    if (e != cudaSuccess) {
+        cudaGetLastError();
+        return fail(ZB_ERR_UNSUPPORTED, std::string("zb_context_register_output: the range cannot be page-locked (") + cudaGetErrorString(e) +
+                                            "); zb_render keeps using its staged copy");
+    }
+    ctx->registered_out.push_back({static_cast<char*>(ptr), bytes});
+    return ZB_OK;
+}
+
+extern "C" int zb_context_unregister_output(zb_context* ctx, void* ptr) {
+    if (!ctx) return fail(ZB_ERR_INVALID, "zb_context_unregister_output: NULL context");
+    for (size_t i = 0; i < ctx->registered_out.size(); i++)
+        if (ctx->registered_out[i].ptr == static_cast<char*>(ptr)) {
+            cudaSetDevice(ctx->device);
+            cudaStreamSynchronize(ctx->stream);
+            cudaHostUnregister(ptr);
+            cudaGetLastError();
+            ctx->registered_out.erase(ctx->registered_out.begin() + long(i));
+            return ZB_OK;
+        }
+    return ZB_OK;  // not registered (or its registration had failed): nothing to do
+}
 
 extern "C" int zb_scene_upload(zb_context* ctx, const zb_flat_scene* f, zb_scene** out) {
     if (!ctx || !f || !out) return fail(ZB_ERR_INVALID, "zb_scene_upload: NULL argument");

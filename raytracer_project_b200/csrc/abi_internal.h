@@ -63,6 +63,16 @@ struct zb_context {
     float4* accum_aux = nullptr;
     size_t accum_pixels = 0;
     float4* out_f4 = nullptr;
+    // output buffers the caller registered (zb_context_register_output): page-locked, zb_render DMAs finished rows into them as doubles
+    struct out_range { char* ptr; size_t bytes; };
+    std::vector<out_range> registered_out;
+    bool out_registered(const void* p, size_t bytes) const {
+        for (const out_range& r : registered_out)
+            if (static_cast<const char*>(p) >= r.ptr && static_cast<const char*>(p) + bytes <= r.ptr + r.bytes) return true;
+        return false;
+    }
+    double* rgb_pack64 = nullptr;  // device stage of the direct path: the band as 3 doubles per pixel, per plane
+    size_t rgb_pack64_doubles = 0;
     float* rgb_pack = nullptr;  // packed RGB floats of the frame being copied to the host (d2h_rgb_f64)
     size_t rgb_pack_pixels = 0;
     void* pinned = nullptr;

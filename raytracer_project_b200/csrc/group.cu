@@ -42,6 +42,7 @@ struct GatherArgs {
     int tile_ranks, tiles_x;  // tile stripes: only the owner of a pixel's tile holds sums for it
     float scale, aux_scale;
     float* out;               // planes x band pixels x 3 floats
+    double* out64;            // not NULL: planes x band pixels x 3 DOUBLES instead (the same float values, widened): direct path
 };
 
 __device__ __forceinline__ float fixed_to_float(unsigned long long v) { return float(double((long long)v) * (1.0 / 4194304.0)); }
@@ -69,29 +70,36 @@ __global__ void __launch_bounds__(256) k_gather_resolve(const __grid_constant__ 
         for (int k = 0; k < 7; k++)
             if (k < extra) s[3 + k] += fa[k];
     }
-    float* o = A.out + 3 * t;
-    o[0] = fixed_to_float(s[0]) * A.scale;  // = k_pq_resolve followed by k_resolve: float(sum) * float(1 / spp)
-    o[1] = fixed_to_float(s[1]) * A.scale;
-    o[2] = fixed_to_float(s[2]) * A.scale;
+    float v[12];
+    int planes = 1;
+    v[0] = fixed_to_float(s[0]) * A.scale;  // = k_pq_resolve followed by k_resolve: float(sum) * float(1 / spp)
+    v[1] = fixed_to_float(s[1]) * A.scale;
+    v[2] = fixed_to_float(s[2]) * A.scale;
     if (A.mode == PQ_LIGHT) {
-        float* r = o + 3 * band;
-        r[0] = fixed_to_float(s[3]) * A.scale;
-        r[1] = fixed_to_float(s[4]) * A.scale;
-        r[2] = fixed_to_float(s[5]) * A.scale;
+        planes = 2;
+        v[3] = fixed_to_float(s[3]) * A.scale;
+        v[4] = fixed_to_float(s[4]) * A.scale;
+        v[5] = fixed_to_float(s[5]) * A.scale;
     } else if (A.mode == PQ_AUX) {
-        float* a = o + 3 * band;
-        float* nrm = o + 6 * band;
-        float* z = o + 9 * band;
-        a[0] = fixed_to_float(s[3]) * A.aux_scale;
-        a[1] = fixed_to_float(s[4]) * A.aux_scale;
-        a[2] = fixed_to_float(s[5]) * A.aux_scale;
-        nrm[0] = fixed_to_float(s[6]) * A.aux_scale;
-        nrm[1] = fixed_to_float(s[7]) * A.aux_scale;
-        nrm[2] = fixed_to_float(s[8]) * A.aux_scale;
-        const float zz = fixed_to_float(s[9]) * A.aux_scale;
-        z[0] = zz;
-        z[1] = zz;
-        z[2] = zz;
+        planes = 4;
+#pragma unroll
+        for (int k = 0; k < 6; k++) v[3 + k] = fixed_to_float(s[3 + k]) * A.aux_scale;  // albedo, normal
+        v[9] = v[10] = v[11] = fixed_to_float(s[9]) * A.aux_scale;                      // z-depth
+    }
+#pragma unroll
+    for (int p = 0; p < 4; p++) {
+        if (p >= planes) break;
+        if (A.out64) {  // the float the staged path would widen on the host, widened here
+            double* o = A.out64 + (size_t(p) * band + t) * 3;
+            o[0] = double(v[3 * p]);
+            o[1] = double(v[3 * p + 1]);
+            o[2] = double(v[3 * p + 2]);
+        } else {
+            float* o = A.out + (size_t(p) * band + t) * 3;
+            o[0] = v[3 * p];
+            o[1] = v[3 * p + 1];
+            o[2] = v[3 * p + 2];
+        }
     }
 }
 
@@ -550,8 +558,38 @@ static int render_impl(zb_context* ctx, const zb_scene* scene, const zb_camera* 
                 if (pass == 0) ZB_CUDA(cudaEventRecord(c->ev[2], c->stream));
                 continue;
             }
-            rc = ensure_band_stage(c, size_t(planes) * band * 3);
-            if (rc) return rc;
+            double* dst[4] = {nullptr, nullptr, nullptr, nullptr};
+            if (gather_mode == PQ_LIGHT) {
+                dst[0] = opts->use_reflection ? out->reflection : nullptr;
+                dst[1] = opts->use_refraction ? out->refraction : nullptr;
+            } else {
+                dst[0] = out->beauty;
+                if (gather_mode == PQ_AUX) {
+                    dst[1] = out->albedo;
+                    dst[2] = out->normal;
+                    dst[3] = out->z_depth;
+                }
+            }
+            // direct path: every requested buffer was registered by the caller (zb_context_register_output) — the band
+            // goes home as doubles in one DMA per plane, no pinned stage, no widening on the host
+            bool direct = false;
+            for (int p = 0; p < planes; p++)
+                if (dst[p]) direct = true;
+            for (int p = 0; p < planes; p++)
+                if (dst[p] && !ctx->out_registered(dst[p] + size_t(m.row0) * W * 3, band * 3 * sizeof(double))) direct = false;
+            if (direct) {
+                const size_t need = size_t(planes) * band * 3;
+                if (c->rgb_pack64_doubles < need) {
+                    cudaFree(c->rgb_pack64);
+                    c->rgb_pack64 = nullptr;
+                    c->rgb_pack64_doubles = 0;
+                    ZB_CUDA(cudaMalloc(&c->rgb_pack64, need * sizeof(double)));
+                    c->rgb_pack64_doubles = need;
+                }
+            } else {
+                rc = ensure_band_stage(c, size_t(planes) * band * 3);
+                if (rc) return rc;
+            }
             GatherArgs A{};
             for (int r = 0; r < n; r++) A.fix[r] = G->fix[buf][r];
             A.n = n;
@@ -565,25 +603,19 @@ static int render_impl(zb_context* ctx, const zb_scene* scene, const zb_camera* 
             A.scale = float(scale);
             A.aux_scale = float(aux_scale);
             A.out = c->rgb_pack;
+            A.out64 = direct ? c->rgb_pack64 : nullptr;
             k_gather_resolve<<<unsigned((band + 255) / 256), 256, 0, c->stream>>>(A);
             ZB_CUDA(cudaGetLastError());
             c->stats.launches++;
             if (pass == 0) ZB_CUDA(cudaEventRecord(c->ev[2], c->stream));
-            double* dst[4] = {nullptr, nullptr, nullptr, nullptr};
-            if (gather_mode == PQ_LIGHT) {
-                dst[0] = opts->use_reflection ? out->reflection : nullptr;
-                dst[1] = opts->use_refraction ? out->refraction : nullptr;
-            } else {
-                dst[0] = out->beauty;
-                if (gather_mode == PQ_AUX) {
-                    dst[1] = out->albedo;
-                    dst[2] = out->normal;
-                    dst[3] = out->z_depth;
-                }
-            }
             for (int p = 0; p < planes; p++) {
                 if (!dst[p]) continue;
-                rc = zbr_copy_issue(c, c->rgb_pack + size_t(p) * band * 3, band * 3, dst[p] + size_t(m.row0) * W * 3, size_t(p) * band * 3, jobs);
+                double* home = dst[p] + size_t(m.row0) * W * 3;
+                if (direct) {
+                    ZB_CUDA(cudaMemcpyAsync(home, c->rgb_pack64 + size_t(p) * band * 3, band * 3 * sizeof(double), cudaMemcpyDeviceToHost, c->stream));
+                    continue;
+                }
+                rc = zbr_copy_issue(c, c->rgb_pack + size_t(p) * band * 3, band * 3, home, size_t(p) * band * 3, jobs);
                 if (rc) return rc;
             }
         }

@@ -130,6 +130,8 @@ public:
     // more than one entry: the frame is rendered by all of these GPUs (zb_context_create_multi); render() stays one
     // blocking call that fills the same buffers — the reference's thread fan-out (camera.hpp:426-427) by other means
     std::vector<int> devices;
+    double* registered[6] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};  // output buffers page-locked for direct copies
+    size_t registered_bytes[6] = {0, 0, 0, 0, 0, 0};
     // mesh BLASes are built on the device at upload (binned SAH, csrc/sah_build.cu: 6.5 ms for 1 M triangles against 2.8 s
     // for the same tree on the host); false = host build (host/bvh_build.hpp).  The reference rebuilds geometry and BVH on
     // the host at every restart (main.cpp:1492-1500, bvh.hpp:11-44 via model.hpp:95)
@@ -146,9 +148,31 @@ public:
     // camera.hpp:209-233: sizes every buffer to W*H and clears it; render() never resizes
     void reset_accumulator() {
         const size_t n = size_t(std::max(image_width, 1)) * size_t(std::max(image_height, 1));
+        unregister_outputs();  // the vectors may move
         for (auto* b : {&render_accumulator, &albedo_buffer, &normal_buffer, &z_depth_buffer, &reflection_buffer, &refraction_buffer})
             b->assign(n, color(0, 0, 0));
         lines_rendered.store(0);
+    }
+
+    // zb_context_register_output for the buffers a frame writes; re-done when a vector has moved or grown
+    void register_outputs(const zb_outputs& out) {
+        const size_t bytes = size_t(std::max(image_width, 1)) * size_t(std::max(image_height, 1)) * sizeof(color);
+        double* want[6] = {out.beauty, out.albedo, out.normal, out.z_depth, out.reflection, out.refraction};
+        for (int k = 0; k < 6; k++) {
+            if (want[k] == registered[k] && (!want[k] || registered_bytes[k] == bytes)) continue;
+            if (registered[k]) zb_context_unregister_output(ctx, registered[k]);
+            registered[k] = nullptr;
+            if (want[k] && zb_context_register_output(ctx, want[k], bytes) == ZB_OK) {
+                registered[k] = want[k];
+                registered_bytes[k] = bytes;
+            }
+        }
+    }
+    void unregister_outputs() {
+        for (int k = 0; k < 6; k++) {
+            if (registered[k] && ctx) zb_context_unregister_output(ctx, registered[k]);
+            registered[k] = nullptr;
+        }
     }
 
     // The uploaded scene is re-used while the world object AND a content stamp of its graph stay the same: the stamp
@@ -286,6 +310,9 @@ public:
         out.z_depth = use_z_depth_buffer ? reinterpret_cast<double*>(z_depth_buffer.data()) : nullptr;
         out.reflection = use_reflection ? reinterpret_cast<double*>(reflection_buffer.data()) : nullptr;
         out.refraction = use_refraction ? reinterpret_cast<double*>(refraction_buffer.data()) : nullptr;
+        // several GPUs: let every GPU DMA its rows straight into these buffers (they are sized once and reused,
+        // camera.hpp:209-233) instead of widening eight bands with host threads
+        if (devices.size() > 1) register_outputs(out);
         watch w{this, &render_flag, 0};
         if (!render_flag.load()) return;  // camera.hpp:441-443
         if (global_settings::bvh_debug_mode)  // bvh.hpp:46-48: the traversal itself switches to the debug view
@@ -354,6 +381,7 @@ public:
     }
 
     void release() {
+        unregister_outputs();
         if (scene) zb_scene_destroy(scene);
         if (ctx) zb_context_destroy(ctx);
         scene = nullptr;

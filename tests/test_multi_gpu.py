@@ -96,6 +96,38 @@ def test_multi_context_scene_edits_reach_every_replica(gpu_ctx, tmp_path):
         api.free_flat(f)
 
 
+def test_registered_output_buffers_get_the_same_frame(gpu_ctx, weekend_flat):
+    """zb_context_register_output: finished rows are DMA'd into the caller's page-locked buffers as doubles instead of being
+    staged as floats and widened on the host — all six output buffers equal the staged path's bit for bit, on one GPU and
+    on multi-device contexts; a buffer outside the registered range falls back to the staged path."""
+    from raytracer_project_b200 import api
+    cfg = scenes.weekend(seed=1, width=203, height=91, spp=16)[1]
+    cfg.use_albedo = cfg.use_normal = cfg.use_z_depth = cfg.use_reflection = cfg.use_refraction = True
+    one = gpu_ctx.upload(weekend_flat)
+    ref = one.render(cfg, seed=3)
+    one.close()
+    n = 203 * 91
+    for devs in [[0]] + _device_lists()[:3]:
+        with api.Context(devs if len(devs) > 1 else devs[0]) as ctx:
+            sc = ctx.upload(weekend_flat)
+            pool = np.full((6, n, 3), -1.0)  # one allocation holding the six planes: one registration
+            assert ctx.register_output(pool)
+            bufs = {k: pool[i].reshape(91, 203, 3) for i, k in enumerate(KEYS)}
+            sc.render_into(cfg, bufs, seed=3)
+            for k in KEYS:
+                assert np.array_equal(bufs[k], ref[k]), (devs, k, "direct")
+            # a frame whose beauty buffer is NOT registered: the staged path, same values
+            other = np.full((n, 3), -1.0)
+            bufs2 = dict(bufs, beauty=other.reshape(91, 203, 3))
+            sc.render_into(cfg, bufs2, seed=3)
+            for k in KEYS:
+                assert np.array_equal(bufs2[k], ref[k]), (devs, k, "mixed -> staged")
+            ctx.unregister_output(pool)
+            sc.render_into(cfg, bufs, seed=3)
+            assert np.array_equal(bufs["beauty"], ref["beauty"])
+            sc.close()
+
+
 def test_multi_context_low_spp_takes_tile_stripes(gpu_ctx, weekend_flat):
     """spp < 8 n (config C1's 10 spp on 2+ GPUs): AUTO picks tile stripes; the frame still equals the one-GPU frame."""
     from raytracer_project_b200 import api
