@@ -426,9 +426,12 @@ def ours(args):
                     "parts_ms": {"scene_upload": sum(p[0] for p in e2e_parts) / len(e2e_parts),
                                  "render_gather_d2h": sum(p[1] for p in e2e_parts) / len(e2e_parts),
                                  "scene_free_barrier": sum(p[2] for p in e2e_parts) / len(e2e_parts)},
-                    "note": "every GPU copies its own band of rows home as packed RGB float means (12 B/pixel) over its own "
-                            "PCIe link; host threads of the same rank widen it to the reference's 3-double layout in the "
-                            "caller's (shared) frame while later chunks are in flight"},
+                    "output_registered": bool(direct_out),
+                    "note": ("every GPU copies its own band of rows home over its own PCIe link, as 3 doubles per pixel in one DMA into "
+                             "the caller's registered (page-locked, shared) frame" if direct_out else
+                             "every GPU copies its own band of rows home as packed RGB float means (12 B/pixel) over its own "
+                             "PCIe link; host threads of the same rank widen it to the reference's 3-double layout in the "
+                             "caller's (shared) frame while later chunks are in flight")},
             "gpu_launches": int(n_launch.item()),
             "roofline": roofline,
             "roofline_fp32": fp32,
